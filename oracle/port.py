@@ -1,0 +1,175 @@
+"""ctypes binding of oracle/q4k_oracle.c — the CPU ORACLE (test infrastructure, see q4k_oracle.h).
+
+All arrays are numpy; Q4_K / Q8_K data are uint8 arrays holding the reference's block bytes
+(144 B per 256 weights, 292 B per 256 activations — L/ggml/src/ggml-common.h:291-306, 338-344).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "_build", "libq4k_oracle.so")
+
+QK_K = 256
+Q4K_BLOCK = 144
+Q8K_BLOCK = 292
+ORDER_GENERIC, ORDER_AVX2, ORDER_NEON = 0, 1, 2
+
+_lib = None
+
+
+def build() -> str:
+    """Compile the restatement with gcc (seconds).  Building the checker is not using it."""
+    src = [os.path.join(HERE, f) for f in ("q4k_oracle.c", "q4k_oracle.h")]
+    if os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(s) for s in src):
+        return LIB
+    subprocess.check_call(["make", "-C", HERE, "oracle"], stdout=subprocess.DEVNULL)
+    return LIB
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(LIB)
+        vp, i64, i32, f32p = C.c_void_p, C.c_int64, C.c_int, C.POINTER(C.c_float)
+        L.ora_nearest_int.argtypes = [C.c_float]
+        L.ora_nearest_int.restype = C.c_int
+        L.ora_fp32_to_fp16.argtypes = [C.c_float]
+        L.ora_fp32_to_fp16.restype = C.c_uint16
+        L.ora_fp16_to_fp32.argtypes = [C.c_uint16]
+        L.ora_fp16_to_fp32.restype = C.c_float
+        L.ora_unpack_scales_mins.argtypes = [vp, vp, vp]
+        L.ora_quantize_row_q8_K.argtypes = [vp, vp, i64]
+        L.ora_quantize_row_q4_K.argtypes = [vp, vp, i64]
+        L.ora_dequantize_row_q4_K.argtypes = [vp, vp, i64]
+        L.ora_vec_dot_partials.argtypes = [i32, vp, vp, vp, vp, vp]
+        for name in ("generic", "avx2order", "neonorder"):
+            fn = getattr(L, f"ora_vec_dot_q4_K_q8_K_{name}")
+            fn.argtypes = [i32, f32p, C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, i32]
+            fn.restype = None
+        L.ora_vec_dot_q4_K_q8_K_f64.argtypes = [i32, vp, vp]
+        L.ora_vec_dot_q4_K_q8_K_f64.restype = C.c_double
+        L.ora_mul_mat_q4_K_f32.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, i32]
+        L.ora_mul_mat_q4_K_f32.restype = i32
+        _lib = L
+    return _lib
+
+
+def _p(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def nearest_int(f: float) -> int:
+    return lib().ora_nearest_int(float(np.float32(f)))
+
+
+def fp32_to_fp16_bits(f: float) -> int:
+    return lib().ora_fp32_to_fp16(float(np.float32(f)))
+
+
+def fp16_bits_to_fp32(h: int) -> float:
+    return lib().ora_fp16_to_fp32(int(h))
+
+
+def unpack_scales_mins(packed12: np.ndarray):
+    packed12 = np.ascontiguousarray(packed12, dtype=np.uint8)
+    sc = np.zeros(8, np.uint8)
+    mn = np.zeros(8, np.uint8)
+    lib().ora_unpack_scales_mins(_p(packed12), _p(sc), _p(mn))
+    return sc, mn
+
+
+def quantize_q8_K(x: np.ndarray, zero_init: bool = True) -> np.ndarray:
+    """x: float32 [..., K] -> uint8 [..., K/256*292].  The reference leaves bsums of all-zero blocks
+    unwritten (ggml-quants.c:2568-2573); zero_init makes those bytes 0."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    K = x.shape[-1]
+    assert K % QK_K == 0
+    rows = x.reshape(-1, K)
+    out = (np.zeros if zero_init else np.empty)((rows.shape[0], K // QK_K * Q8K_BLOCK), np.uint8)
+    for r in range(rows.shape[0]):
+        lib().ora_quantize_row_q8_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*x.shape[:-1], -1)
+
+
+def quantize_q4_K(x: np.ndarray) -> np.ndarray:
+    """x: float32 [M, K] -> uint8 [M, K/256*144] (quantize_row_q4_K_ref, no imatrix)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    K = x.shape[-1]
+    assert K % QK_K == 0
+    rows = x.reshape(-1, K)
+    out = np.zeros((rows.shape[0], K // QK_K * Q4K_BLOCK), np.uint8)
+    for r in range(rows.shape[0]):
+        lib().ora_quantize_row_q4_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*x.shape[:-1], -1)
+
+
+def dequantize_q4_K(w: np.ndarray) -> np.ndarray:
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    rows = w.reshape(-1, w.shape[-1])
+    K = rows.shape[1] // Q4K_BLOCK * QK_K
+    out = np.empty((rows.shape[0], K), np.float32)
+    for r in range(rows.shape[0]):
+        lib().ora_dequantize_row_q4_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*w.shape[:-1], K)
+
+
+def vec_dot_partials(wrow: np.ndarray, yrow: np.ndarray):
+    """-> (p[nb,8], sumi[nb], summ[nb]) int32: the bit-exact integer stage."""
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q4K_BLOCK
+    assert yrow.size == nb * Q8K_BLOCK
+    p = np.zeros((nb, 8), np.int32)
+    si = np.zeros(nb, np.int32)
+    sm = np.zeros(nb, np.int32)
+    lib().ora_vec_dot_partials(nb * QK_K, _p(wrow), _p(yrow), _p(p), _p(si), _p(sm))
+    return p, si, sm
+
+
+def vec_dot(wrow: np.ndarray, yrow: np.ndarray, order: int = ORDER_AVX2) -> np.float32:
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q4K_BLOCK
+    s = C.c_float(0)
+    name = {ORDER_GENERIC: "generic", ORDER_AVX2: "avx2order", ORDER_NEON: "neonorder"}[order]
+    getattr(lib(), f"ora_vec_dot_q4_K_q8_K_{name}")(nb * QK_K, C.byref(s), 0, _p(wrow), 0, _p(yrow), 0, 1)
+    return np.float32(s.value)
+
+
+def vec_dot_f64(wrow: np.ndarray, yrow: np.ndarray) -> float:
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q4K_BLOCK
+    return lib().ora_vec_dot_q4_K_q8_K_f64(nb * QK_K, _p(wrow), _p(yrow))
+
+
+def mul_mat(w: np.ndarray, x: np.ndarray, order: int = ORDER_AVX2) -> np.ndarray:
+    """w: uint8 [M, K/256*144]; x: float32 [N, K] -> float32 [N, M] (ggml dst: ne0 = M fastest)."""
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    M = w.shape[0]
+    N, K = x.shape
+    assert w.shape[1] == K // QK_K * Q4K_BLOCK
+    dst = np.zeros((N, M), np.float32)
+    wdata = np.zeros(N * (K // QK_K) * Q8K_BLOCK, np.uint8)
+    rc = lib().ora_mul_mat_q4_K_f32(_p(w), M, K, w.shape[1], _p(x), N, K * 4, _p(dst), M * 4, _p(wdata), order)
+    if rc != 0:
+        raise ValueError(f"ora_mul_mat_q4_K_f32 rc={rc}")
+    return dst
+
+
+def mul_mat_f64(w: np.ndarray, x: np.ndarray) -> np.ndarray:
+    """Double-precision combination of the exact integers: the tie-breaker for tolerance tests."""
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    yq = quantize_q8_K(x)
+    out = np.zeros((yq.shape[0], w.shape[0]), np.float64)
+    for n in range(yq.shape[0]):
+        for m in range(w.shape[0]):
+            out[n, m] = vec_dot_f64(w[m], yq[n])
+    return out

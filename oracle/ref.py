@@ -1,0 +1,168 @@
+"""ctypes binding of oracle/_ref/*.so — the UNMODIFIED reference ggml CPU code (test infrastructure).
+
+oracle/_ref/ is built by `make -C oracle ref` in the build container (where /root/reference exists);
+the built files travel to the GPU box with the snapshot.  Nothing here reads /root/reference at run
+time.  `available()` is False when the prebuilt libraries are missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+REFERENCE_ROOT = "/root/reference/external/llama.cpp"
+
+QK_K, Q4K_BLOCK, Q8K_BLOCK = 256, 144, 292
+
+_libs = None
+
+
+def build() -> bool:
+    """(Re)build oracle/_ref from the reference sources if they are present; returns available()."""
+    if os.path.isdir(REFERENCE_ROOT):
+        subprocess.check_call(["make", "-C", HERE, "-j8", "ref"], stdout=subprocess.DEVNULL)
+    return available()
+
+
+def available() -> bool:
+    return all(os.path.exists(os.path.join(REF_DIR, f))
+               for f in ("libggml-base.so", "libggml-cpu.so", "libggml.so", "libref_shim.so"))
+
+
+def libs():
+    global _libs
+    if _libs is None:
+        if not available():
+            raise RuntimeError("oracle/_ref is not built (run `make -C oracle ref` where /root/reference exists)")
+        mode = C.RTLD_GLOBAL
+        base = C.CDLL(os.path.join(REF_DIR, "libggml-base.so"), mode=mode)
+        cpu = C.CDLL(os.path.join(REF_DIR, "libggml-cpu.so"), mode=mode)
+        ggml = C.CDLL(os.path.join(REF_DIR, "libggml.so"), mode=mode)
+        shim = C.CDLL(os.path.join(REF_DIR, "libref_shim.so"), mode=mode)
+        vp, i64, i32 = C.c_void_p, C.c_int64, C.c_int
+        base.quantize_row_q4_K_ref.argtypes = [vp, vp, i64]
+        base.quantize_row_q8_K_ref.argtypes = [vp, vp, i64]
+        base.dequantize_row_q4_K.argtypes = [vp, vp, i64]
+        cpu.quantize_row_q8_K.argtypes = [vp, vp, i64]
+        for fn in (cpu.ggml_vec_dot_q4_K_q8_K, cpu.ggml_vec_dot_q4_K_q8_K_generic):
+            fn.argtypes = [i32, C.POINTER(C.c_float), C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, i32]
+            fn.restype = None
+        shim.ref_mul_mat_q4k.argtypes = [vp, i64, i64, vp, i64, vp, i32, i32, i32, C.POINTER(C.c_double)]
+        shim.ref_mul_mat_q4k.restype = i32
+        shim.ref_plugin_mul_mat_q4k.argtypes = [C.c_char_p, vp, i64, i64, vp, i64, vp, i32, C.POINTER(C.c_double)]
+        shim.ref_plugin_mul_mat_q4k.restype = i32
+        shim.ref_cpu_has_avx2.restype = i32
+        # ggml-cpu's fp16->fp32 is a lookup table filled by ggml_cpu_init() (ggml-cpu.c:3526-3549);
+        # the reference always reaches vec_dot through backend init, direct callers must do it themselves
+        cpu.ggml_cpu_init()
+        _libs = (base, cpu, ggml, shim)
+    return _libs
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def quantize_q4_K(x: np.ndarray) -> np.ndarray:
+    """quantize_row_q4_K_ref per row (L/ggml/src/ggml-quants.c:1280-1350)."""
+    base = libs()[0]
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    K = x.shape[-1]
+    rows = x.reshape(-1, K)
+    out = np.zeros((rows.shape[0], K // QK_K * Q4K_BLOCK), np.uint8)
+    for r in range(rows.shape[0]):
+        base.quantize_row_q4_K_ref(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*x.shape[:-1], -1)
+
+
+def quantize_q8_K(x: np.ndarray) -> np.ndarray:
+    """quantize_row_q8_K as ggml-cpu exports it (arch/x86/quants.c:493-495 -> ggml-quants.c:2555-2592).
+    Output is zero-initialised: the reference leaves bsums of all-zero blocks unwritten."""
+    cpu = libs()[1]
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    K = x.shape[-1]
+    rows = x.reshape(-1, K)
+    out = np.zeros((rows.shape[0], K // QK_K * Q8K_BLOCK), np.uint8)
+    for r in range(rows.shape[0]):
+        cpu.quantize_row_q8_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*x.shape[:-1], -1)
+
+
+def dequantize_q4_K(w: np.ndarray) -> np.ndarray:
+    base = libs()[0]
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    rows = w.reshape(-1, w.shape[-1])
+    K = rows.shape[1] // Q4K_BLOCK * QK_K
+    out = np.empty((rows.shape[0], K), np.float32)
+    for r in range(rows.shape[0]):
+        base.dequantize_row_q4_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*w.shape[:-1], K)
+
+
+def vec_dot(wrow: np.ndarray, yrow: np.ndarray, generic: bool = False) -> np.float32:
+    """ggml_vec_dot_q4_K_q8_K — the __AVX2__ branch in this build (arch/x86/quants.c:1760-1823)."""
+    cpu = libs()[1]
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q4K_BLOCK
+    s = C.c_float(0)
+    fn = cpu.ggml_vec_dot_q4_K_q8_K_generic if generic else cpu.ggml_vec_dot_q4_K_q8_K
+    fn(nb * QK_K, C.byref(s), 0, _p(wrow), 0, _p(yrow), 0, 1)
+    return np.float32(s.value)
+
+
+def mul_mat_direct(w: np.ndarray, x: np.ndarray) -> np.ndarray:
+    """quantize_row_q8_K + ggml_vec_dot_q4_K_q8_K per (row, col), 1 thread -> float32 [N, M]."""
+    cpu = libs()[1]
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    yq = quantize_q8_K(x)
+    M, N = w.shape[0], yq.shape[0]
+    nb = w.shape[1] // Q4K_BLOCK
+    out = np.zeros((N, M), np.float32)
+    s = C.c_float(0)
+    for n in range(N):
+        for m in range(M):
+            cpu.ggml_vec_dot_q4_K_q8_K(nb * QK_K, C.byref(s), 0, _p(w[m]), 0, _p(yq[n]), 0, 1)
+            out[n, m] = s.value
+    return out
+
+
+def mul_mat(w: np.ndarray, x: np.ndarray, n_threads: int = 1, warmup: int = 0, iters: int = 1):
+    """Whole op: ggml_mul_mat graph on ggml_backend_cpu, weights in a plain CPU buffer
+    (-> ggml_compute_forward_mul_mat -> vec_dot; L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401).
+    Returns (dst float32 [N, M], best_seconds, mean_seconds)."""
+    shim = libs()[3]
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    M = w.shape[0]
+    N, K = x.shape
+    assert w.shape[1] == K // QK_K * Q4K_BLOCK
+    dst = np.zeros((N, M), np.float32)
+    secs = (C.c_double * 2)()
+    rc = shim.ref_mul_mat_q4k(_p(w), M, K, _p(x), N, _p(dst), n_threads, warmup, iters, secs)
+    if rc != 0:
+        raise RuntimeError(f"ref_mul_mat_q4k rc={rc}")
+    return dst, secs[0], secs[1]
+
+
+def plugin_mul_mat(so_path: str, w: np.ndarray, x: np.ndarray, iters: int = 1):
+    """Loads our backend .so through the reference's ggml_backend_load and runs the same graph on it."""
+    shim = libs()[3]
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    M = w.shape[0]
+    N, K = x.shape
+    dst = np.zeros((N, M), np.float32)
+    secs = (C.c_double * 2)()
+    rc = shim.ref_plugin_mul_mat_q4k(so_path.encode(), _p(w), M, K, _p(x), N, _p(dst), iters, secs)
+    if rc != 0:
+        raise RuntimeError(f"ref_plugin_mul_mat_q4k rc={rc}")
+    return dst, secs[0], secs[1]
+
+
+def has_avx2() -> bool:
+    return bool(libs()[3].ref_cpu_has_avx2())
