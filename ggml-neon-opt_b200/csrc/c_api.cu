@@ -1,0 +1,198 @@
+// c_api.cu — the C ABI of include/q4k_b200.h over the kernels of this directory.
+// Argument validation, dispatch (GEMV for N <= 8, tcgen05 GEMM above), error mapping.  No CPU
+// fallback of any kind: if a kernel cannot run, the call fails with a negative code.
+#include "../../include/q4k_b200.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "q4k_common.cuh"
+#include "q4k_kernels.h"
+
+#define Q4K_STR2(x) #x
+#define Q4K_STR(x) Q4K_STR2(x)
+
+namespace q4k {
+
+static std::atomic<int64_t> g_launches{0};
+static thread_local int t_last_cuda_error = 0;
+
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+static int cuda_fail(cudaError_t e) {
+    t_last_cuda_error = (int)e;
+    return Q4K_ERR_CUDA;
+}
+
+static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Q4K_GEMV_ORDER=fast selects the cheaper float association for every batch size; default is the
+// reference's AVX2 order (bit-identical fp32) wherever the GEMV stays HBM-bound with it.
+static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
+static bool gemv_exact_for(int N) {
+    int &mode = g_order_mode;
+    if (mode < 0) {
+        const char *e = getenv("Q4K_GEMV_ORDER");
+        mode = !e ? 0 : (!strcmp(e, "exact") ? 1 : (!strcmp(e, "fast") ? 2 : 0));
+    }
+    if (mode == 1) return true;
+    if (mode == 2) return false;
+    return N <= 2;
+}
+
+}  // namespace q4k
+
+using namespace q4k;
+
+extern "C" {
+
+int q4k_abi_version(void) { return 1; }
+
+const char *q4k_build_info(void) {
+    return "q4k_b200 sm_100a, CUDA " Q4K_STR(CUDART_VERSION) ", built " __DATE__;
+}
+
+int q4k_device_ok(int device) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device) != cudaSuccess) return 0;
+    return major == 10;
+}
+
+int q4k_debug_set_gemv_order(int mode) {
+    if (mode < 0 || mode > 2) return Q4K_ERR_UNSUPPORTED;
+    g_order_mode = mode;
+    return Q4K_OK;
+}
+
+int q4k_last_cuda_error(void) { return t_last_cuda_error; }
+
+int64_t q4k_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int q4k_quantize_q8_K(const float *x_dev, void *y_dev, int64_t k, int64_t nrows, int64_t x_row_stride_bytes, void *stream) {
+    if (k < 0 || nrows < 0 || k % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (k == 0 || nrows == 0) return Q4K_OK;
+    if (!x_dev || !y_dev) return Q4K_ERR_BAD_POINTER;
+    if (x_row_stride_bytes < k * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (reinterpret_cast<uintptr_t>(y_dev) & 3u) return Q4K_ERR_BAD_POINTER;
+    cudaError_t e = launch_quantize_q8_K(x_dev, y_dev, k, nrows, x_row_stride_bytes, (cudaStream_t)stream);
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
+    if (K <= 0 || N <= 0 || K % Q4K_QK_K != 0) return 0;
+    return (size_t)N * (size_t)(K / Q4K_QK_K) * Q4K_BLOCK_Q8K;
+}
+
+int q4k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                   const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
+                   float *dst_dev, int64_t dst_col_stride_bytes, void *stream) {
+    if (M < 0 || N < 0 || K < 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (M == 0 || N == 0) return Q4K_OK;
+    if (!dst_dev) return Q4K_ERR_BAD_POINTER;
+    const int64_t nb = K / Q4K_QK_K;
+    if (K == 0) {        // empty contraction: the reference's vec_dot loop runs zero times -> 0.0f
+        for (int64_t n = 0; n < N; ++n) {
+            cudaError_t e = cudaMemsetAsync((char *)dst_dev + n * dst_col_stride_bytes, 0, (size_t)M * 4, (cudaStream_t)stream);
+            if (e != cudaSuccess) return cuda_fail(e);
+        }
+        return Q4K_OK;
+    }
+    if (!w_dev || !xq_dev) return Q4K_ERR_BAD_POINTER;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (xq_row_stride_bytes < nb * Q4K_BLOCK_Q8K || (xq_row_stride_bytes & 3) || (reinterpret_cast<uintptr_t>(xq_dev) & 3u)) return Q4K_ERR_BAD_SHAPE;
+    if (dst_col_stride_bytes < M * 4 || (dst_col_stride_bytes & 3)) return Q4K_ERR_BAD_SHAPE;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N > Q4K_GEMV_MAX_N) {
+        cudaError_t e = launch_gemm_q4k_q8k(w_dev, M, K, w_row_stride_bytes, xq_dev, N, xq_row_stride_bytes, dst_dev, dst_col_stride_bytes, st);
+        if (e == cudaSuccess) return Q4K_OK;
+        if (e != cudaErrorNotSupported) return cuda_fail(e);
+        // shape the tensor path does not take (yet): same GPU arithmetic, eight columns per pass
+    }
+    for (int64_t n0 = 0; n0 < N; n0 += Q4K_GEMV_MAX_N) {
+        const int nn = (int)((N - n0) < Q4K_GEMV_MAX_N ? (N - n0) : Q4K_GEMV_MAX_N);
+        const bool exact = N <= Q4K_GEMV_MAX_N ? gemv_exact_for(nn) : false;
+        cudaError_t e = launch_gemv_q4k_q8k(w_dev, M, K, w_row_stride_bytes,
+                                            (const char *)xq_dev + n0 * xq_row_stride_bytes, nn, xq_row_stride_bytes,
+                                            (float *)((char *)dst_dev + n0 * dst_col_stride_bytes), dst_col_stride_bytes, exact, st);
+        if (e != cudaSuccess) return cuda_fail(e);
+    }
+    return Q4K_OK;
+}
+
+int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                float *dst_dev, int64_t dst_col_stride_bytes,
+                void *workspace_dev, size_t workspace_bytes, void *stream) {
+    if (M < 0 || N < 0 || K < 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (M == 0 || N == 0) return Q4K_OK;
+    if (K > 0) {
+        if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
+        if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
+        const int rc = q4k_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, stream);
+        if (rc != Q4K_OK) return rc;
+    }
+    return q4k_mul_mat_q8(w_dev, M, K, w_row_stride_bytes, workspace_dev, N, (K / Q4K_QK_K) * Q4K_BLOCK_Q8K,
+                          dst_dev, dst_col_stride_bytes, stream);
+}
+
+int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, size_t bx, const void *vy_dev, size_t by, int nrc) {
+    (void)bs; (void)bx; (void)by;
+    if (nrc != 1) return Q4K_ERR_UNSUPPORTED;      // the reference asserts nrc == 1 on x86 (arch/x86/quants.c:1743)
+    if (n < 0 || n % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (!s_dev) return Q4K_ERR_BAD_POINTER;
+    if (n == 0) {
+        cudaError_t e0 = cudaMemset(s_dev, 0, 4);
+        return e0 == cudaSuccess ? Q4K_OK : cuda_fail(e0);
+    }
+    if (!vx_dev || !vy_dev || !aligned16(vx_dev) || (reinterpret_cast<uintptr_t>(vy_dev) & 3u)) return Q4K_ERR_BAD_POINTER;
+    const int64_t nb = n / Q4K_QK_K;
+    cudaError_t e = launch_gemv_q4k_q8k(vx_dev, 1, n, nb * Q4K_BLOCK_Q4K, vy_dev, 1, nb * Q4K_BLOCK_Q8K, s_dev, 4, true, 0);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
+                       const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
+                       int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev, void *stream) {
+    if (K <= 0 || K % Q4K_QK_K != 0 || row0 < 0 || nrows < 0 || N < 0) return Q4K_ERR_BAD_SHAPE;
+    if (nrows == 0 || N == 0) return Q4K_OK;
+    if (!w_dev || !xq_dev || !p_dev || !sumi_dev || !summ_dev || !aligned16(w_dev) || (w_row_stride_bytes & 15)) return Q4K_ERR_BAD_POINTER;
+    cudaError_t e = launch_debug_partials(w_dev, K, w_row_stride_bytes, row0, nrows, xq_dev, N, xq_row_stride_bytes,
+                                          p_dev, sumi_dev, summ_dev, (cudaStream_t)stream);
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+int q4k_mul_mat_host(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                     const float *x_host, int64_t N, float *dst_host,
+                     void *x_stage_dev, float *dst_stage_dev,
+                     void *workspace_dev, size_t workspace_bytes, void *stream) {
+    if (M < 0 || N < 0 || K < 0) return Q4K_ERR_BAD_SHAPE;
+    if (M == 0 || N == 0) return Q4K_OK;
+    if (!x_host || !dst_host || !x_stage_dev || !dst_stage_dev) return Q4K_ERR_BAD_POINTER;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaSuccess;
+    if (K > 0) e = cudaMemcpyAsync(x_stage_dev, x_host, (size_t)N * K * 4, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return cuda_fail(e);
+    const int rc = q4k_mul_mat(w_dev, M, K, w_row_stride_bytes, (const float *)x_stage_dev, N, K * 4,
+                               dst_stage_dev, M * 4, workspace_dev, workspace_bytes, stream);
+    if (rc != Q4K_OK) return rc;
+    e = cudaMemcpyAsync(dst_host, dst_stage_dev, (size_t)N * M * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+}  // extern "C"

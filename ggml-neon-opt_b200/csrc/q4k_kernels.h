@@ -1,0 +1,30 @@
+// q4k_kernels.h — internal launcher interface between the kernel TUs and the C ABI (c_api.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace q4k {
+
+void count_launch();          // bumps the process-wide kernel launch counter (q4k_kernel_launches)
+
+cudaError_t launch_quantize_q8_K(const float *x, void *y, int64_t k, int64_t nrows, int64_t x_row_stride_bytes,
+                                 cudaStream_t stream);
+
+// GEMV, 1 <= N <= 8.  exact_order: reproduce the reference's AVX2 float accumulation order bit for bit.
+cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                                const void *xq, int N, int64_t xq_row_stride_bytes,
+                                float *dst, int64_t dst_col_stride_bytes, bool exact_order, cudaStream_t stream);
+
+// GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
+cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                                const void *xq, int64_t N, int64_t xq_row_stride_bytes,
+                                float *dst, int64_t dst_col_stride_bytes, cudaStream_t stream);
+
+cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
+                                  const void *xq, int64_t N, int64_t xq_row_stride_bytes,
+                                  int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);
+
+int sm_count();               // multiprocessors of the current device (cached)
+
+}  // namespace q4k

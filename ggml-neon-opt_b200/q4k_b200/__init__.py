@@ -1,0 +1,13 @@
+"""q4k_b200 — Python face of the B200-native Q4_K x Q8_K mul_mat path.
+
+Thin ctypes binding of libq4k_b200.so (include/q4k_b200.h).  torch is used only for device memory and
+streams.  There is no CPU or eager fallback: if the CUDA library is missing or no sm_100 GPU is
+present, the ops raise.
+"""
+from .lib import (Q4K_BLOCK, Q8K_BLOCK, QK_K, HostPlan, Q4KError, abi_version, build_info, debug_partials,
+                  kernel_launches, lib_path, load, mul_mat, mul_mat_host, mul_mat_q8, quantize_q8_K,
+                  vec_dot_q4_K_q8_K, workspace_bytes)
+
+__all__ = ["HostPlan", "Q4K_BLOCK", "Q8K_BLOCK", "QK_K", "Q4KError", "abi_version", "build_info", "debug_partials",
+           "kernel_launches", "lib_path", "load", "mul_mat", "mul_mat_host", "mul_mat_q8", "quantize_q8_K",
+           "vec_dot_q4_K_q8_K", "workspace_bytes"]

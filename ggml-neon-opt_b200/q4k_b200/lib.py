@@ -1,0 +1,178 @@
+"""ctypes binding of libq4k_b200.so — one Python function per entry of include/q4k_b200.h.
+
+Tensors are torch CUDA tensors: Q4_K / Q8_K data as uint8 holding the reference's block bytes
+(L/ggml/src/ggml-common.h:291-306, 338-344), activations / results as float32.  Shapes follow ggml:
+weights [M, K/256*144] (M rows of K), activations [N, K], result [N, M] (M fastest).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+QK_K, Q4K_BLOCK, Q8K_BLOCK = 256, 144, 292
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.normpath(os.path.join(_HERE, "..", "lib", "libq4k_b200.so"))
+_lib = None
+
+_ERR = {-1: "bad shape", -2: "bad pointer", -3: "workspace too small", -4: "CUDA error", -5: "unsupported"}
+
+
+class Q4KError(RuntimeError):
+    def __init__(self, fn: str, rc: int, cuda: int = 0):
+        self.rc, self.cuda = rc, cuda
+        super().__init__(f"{fn} failed: {_ERR.get(rc, rc)} (rc={rc}, cudaError={cuda})")
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def load():
+    """Loads the CUDA library.  Raises if it has not been built — there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError(f"{_LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(nvcc, sm_100a).  q4k_b200 has no CPU fallback.")
+        L = C.CDLL(_LIB_PATH)
+        vp, i64, i32, sz = C.c_void_p, C.c_int64, C.c_int, C.c_size_t
+        L.q4k_abi_version.restype = i32
+        L.q4k_build_info.restype = C.c_char_p
+        L.q4k_device_ok.argtypes = [i32]
+        L.q4k_kernel_launches.restype = i64
+        L.q4k_quantize_q8_K.argtypes = [vp, vp, i64, i64, i64, vp]
+        L.q4k_mul_mat_workspace_bytes.argtypes = [i64, i64]
+        L.q4k_mul_mat_workspace_bytes.restype = sz
+        L.q4k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
+        L.q4k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
+        L.q4k_vec_dot_q4_K_q8_K.argtypes = [i32, vp, sz, vp, sz, vp, sz, i32]
+        L.q4k_debug_partials.argtypes = [vp, i64, i64, i64, i64, vp, i64, i64, vp, vp, vp, vp]
+        L.q4k_mul_mat_host.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
+        _lib = L
+    return _lib
+
+
+def _check(fn: str, rc: int):
+    if rc != 0:
+        raise Q4KError(fn, rc, load().q4k_last_cuda_error())
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev_u8(t: torch.Tensor, name: str):
+    if not (t.is_cuda and t.dtype == torch.uint8 and t.is_contiguous()):
+        raise TypeError(f"{name}: expected a contiguous CUDA uint8 tensor")
+
+
+def abi_version() -> int:
+    return load().q4k_abi_version()
+
+
+def build_info() -> str:
+    return load().q4k_build_info().decode()
+
+
+def kernel_launches() -> int:
+    return load().q4k_kernel_launches()
+
+
+def workspace_bytes(K: int, N: int) -> int:
+    return load().q4k_mul_mat_workspace_bytes(K, N)
+
+
+def quantize_q8_K(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """float32 [N, K] (rows may be strided) -> uint8 [N, K/256*292]; bit-exact quantize_row_q8_K."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1):
+        raise TypeError("x: expected a 2-D CUDA float32 tensor with unit inner stride")
+    N, K = x.shape
+    if K % QK_K:
+        raise ValueError("K must be a multiple of 256")
+    if out is None:
+        out = torch.empty((N, K // QK_K * Q8K_BLOCK), dtype=torch.uint8, device=x.device)
+    _dev_u8(out, "out")
+    with torch.cuda.device(x.device):
+        _check("q4k_quantize_q8_K", load().q4k_quantize_q8_K(x.data_ptr(), out.data_ptr(), K, N, x.stride(0) * 4 if N > 1 else K * 4, _stream()))
+    return out
+
+
+def mul_mat(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None,
+            workspace: torch.Tensor | None = None) -> torch.Tensor:
+    """ggml_mul_mat(Q4_K w [M, K/256*144], F32 x [N, K]) -> float32 [N, M]."""
+    _dev_u8(w, "w")
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.is_contiguous()):
+        raise TypeError("x: expected a contiguous 2-D CUDA float32 tensor")
+    M, N, K = w.shape[0], x.shape[0], x.shape[1]
+    if K % QK_K or w.shape[1] != K // QK_K * Q4K_BLOCK:
+        raise ValueError("shape mismatch between w and x")
+    if out is None:
+        out = torch.empty((N, M), dtype=torch.float32, device=x.device)
+    need = workspace_bytes(K, N)
+    if workspace is None:
+        workspace = torch.empty(max(need, 16), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        _check("q4k_mul_mat", load().q4k_mul_mat(w.data_ptr(), M, K, w.stride(0), x.data_ptr(), N, K * 4,
+                                                 out.data_ptr(), out.stride(0) * 4 if N > 1 else M * 4,
+                                                 workspace.data_ptr(), workspace.numel(), _stream()))
+    return out
+
+
+def mul_mat_q8(w: torch.Tensor, xq: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Same with src1 already Q8_K: xq uint8 [N, K/256*292]."""
+    _dev_u8(w, "w")
+    _dev_u8(xq, "xq")
+    M, N = w.shape[0], xq.shape[0]
+    nb = w.shape[1] // Q4K_BLOCK
+    if xq.shape[1] != nb * Q8K_BLOCK:
+        raise ValueError("shape mismatch between w and xq")
+    if out is None:
+        out = torch.empty((N, M), dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _check("q4k_mul_mat_q8", load().q4k_mul_mat_q8(w.data_ptr(), M, nb * QK_K, w.stride(0), xq.data_ptr(), N, xq.stride(0),
+                                                       out.data_ptr(), out.stride(0) * 4 if N > 1 else M * 4, _stream()))
+    return out
+
+
+def vec_dot_q4_K_q8_K(n: int, s: torch.Tensor, bs: int, vx: torch.Tensor, bx: int, vy: torch.Tensor, by: int, nrc: int) -> None:
+    """ggml_vec_dot_t over device tensors (same argument meaning as the reference's; nrc must be 1)."""
+    with torch.cuda.device(vx.device):
+        torch.cuda.current_stream().synchronize()
+        _check("q4k_vec_dot_q4_K_q8_K", load().q4k_vec_dot_q4_K_q8_K(n, s.data_ptr(), bs, vx.data_ptr(), bx, vy.data_ptr(), by, nrc))
+
+
+def debug_partials(w: torch.Tensor, xq: torch.Tensor, row0: int = 0, nrows: int | None = None):
+    """-> (p [N, nrows, nb, 8], sumi [N, nrows, nb], summ [N, nrows, nb]) int32."""
+    _dev_u8(w, "w")
+    _dev_u8(xq, "xq")
+    nb = w.shape[1] // Q4K_BLOCK
+    nrows = w.shape[0] - row0 if nrows is None else nrows
+    N = xq.shape[0]
+    p = torch.zeros((N, nrows, nb, 8), dtype=torch.int32, device=w.device)
+    si = torch.zeros((N, nrows, nb), dtype=torch.int32, device=w.device)
+    sm = torch.zeros((N, nrows, nb), dtype=torch.int32, device=w.device)
+    with torch.cuda.device(w.device):
+        _check("q4k_debug_partials", load().q4k_debug_partials(w.data_ptr(), nb * QK_K, w.stride(0), row0, nrows, xq.data_ptr(), N,
+                                                               xq.stride(0), p.data_ptr(), si.data_ptr(), sm.data_ptr(), _stream()))
+    return p, si, sm
+
+
+class HostPlan:
+    """Device staging for the host-buffer entry (what the ggml backend plugin does per MUL_MAT node)."""
+
+    def __init__(self, M: int, K: int, N: int, device="cuda"):
+        self.M, self.K, self.N = M, K, N
+        self.x_stage = torch.empty((N, K), dtype=torch.float32, device=device)
+        self.dst_stage = torch.empty((N, M), dtype=torch.float32, device=device)
+        self.ws = torch.empty(max(workspace_bytes(K, N), 16), dtype=torch.uint8, device=device)
+
+
+def mul_mat_host(w: torch.Tensor, x_host: torch.Tensor, dst_host: torch.Tensor, plan: HostPlan) -> None:
+    """x_host [N, K] / dst_host [N, M]: CPU float32 tensors (pinned for speed).  Synchronous."""
+    _dev_u8(w, "w")
+    with torch.cuda.device(w.device):
+        _check("q4k_mul_mat_host", load().q4k_mul_mat_host(w.data_ptr(), plan.M, plan.K, w.stride(0), x_host.data_ptr(), plan.N,
+                                                           dst_host.data_ptr(), plan.x_stage.data_ptr(), plan.dst_stage.data_ptr(),
+                                                           plan.ws.data_ptr(), plan.ws.numel(), _stream()))

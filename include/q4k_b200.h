@@ -1,0 +1,95 @@
+/*
+ * q4k_b200.h — C ABI of the B200-native Q4_K x Q8_K mul_mat path (libq4k_b200.so).
+ *
+ * This is the drop-in boundary under the ggml backend plugin (ggml-neon-opt_b200/backend/) and the
+ * thing tests/bench call through ctypes.  Plain pointers and sizes only; every pointer named *_dev is a
+ * CUDA device pointer, `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ * Every entry returns 0 on success or a negative Q4K_ERR_* code; nothing throws; launches are
+ * asynchronous on `stream` unless the comment says "synchronous".
+ *
+ * Byte layouts are the reference's, unchanged ("L/" = external/llama.cpp/ in the reference):
+ *   block_q4_K  144 B / 256 weights      L/ggml/src/ggml-common.h:291-306
+ *   block_q8_K  292 B / 256 activations  L/ggml/src/ggml-common.h:338-344
+ * Matrix convention is ggml's (L/ggml/src/ggml-cpu/ggml-cpu.c:1221-1224): weights src0 = M rows of K,
+ * activations src1 = N rows of K floats, dst = N columns of M floats (M fastest).
+ */
+#ifndef Q4K_B200_H
+#define Q4K_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define Q4K_QK_K          256
+#define Q4K_BLOCK_Q4K     144
+#define Q4K_BLOCK_Q8K     292
+#define Q4K_GEMV_MAX_N    8      /* batch sizes served by the HBM-bound GEMV; larger N takes the GEMM */
+
+enum {
+    Q4K_OK               =  0,
+    Q4K_ERR_BAD_SHAPE    = -1,   /* K % 256 != 0, negative sizes, strides too small / misaligned */
+    Q4K_ERR_BAD_POINTER  = -2,
+    Q4K_ERR_WORKSPACE    = -3,   /* workspace smaller than q4k_mul_mat_workspace_bytes() */
+    Q4K_ERR_CUDA         = -4,   /* a CUDA runtime call failed; q4k_last_cuda_error() has the code */
+    Q4K_ERR_UNSUPPORTED  = -5,   /* nrc not in {1}, device is not sm_100 ... */
+};
+
+/* library / device ------------------------------------------------------------------------------- */
+int         q4k_abi_version(void);                 /* bumps when a signature changes */
+const char *q4k_build_info(void);                  /* "sm_100a nvcc 12.9 ..." */
+int         q4k_device_ok(int device);             /* 1 if `device` is compute capability 10.x */
+int         q4k_last_cuda_error(void);             /* last cudaError_t seen by this library, per thread */
+int64_t     q4k_kernel_launches(void);             /* kernels launched by this library so far (process-wide) */
+
+/* replaces quantize_row_q8_K (L/ggml/src/ggml-quants.c:2555-2592, bound as from_float of Q8_K at
+ * L/ggml/src/ggml-cpu/ggml-cpu.c:355-357) for `nrows` rows of k floats; row r is read at
+ * x_dev + r*x_row_stride_bytes and written to y_dev + r*(k/256*292).  Bit-exact, except that bsums of
+ * all-zero blocks are written as 0 (the reference leaves them unwritten). */
+int q4k_quantize_q8_K(const float *x_dev, void *y_dev, int64_t k, int64_t nrows,
+                      int64_t x_row_stride_bytes, void *stream);
+
+/* replaces ggml_compute_forward_mul_mat for Q4_K src0 / F32 src1 (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401).
+ * workspace_dev holds the Q8_K copy of src1 (the reference's params->wdata, :1267-1307). */
+size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N);
+int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                float *dst_dev, int64_t dst_col_stride_bytes,
+                void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* same, src1 already Q8_K (vec_dot_type == src1->type branch, ggml-cpu.c:1267): N rows of K/256 blocks */
+int q4k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                   const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
+                   float *dst_dev, int64_t dst_col_stride_bytes, void *stream);
+
+/* ggml_vec_dot_t signature (L/ggml/include/ggml-cpu.h:109; ggml_vec_dot_q4_K_q8_K at
+ * L/ggml/src/ggml-cpu/arch/x86/quants.c:1741) over DEVICE pointers: n = K, s = result, nrc must be 1
+ * (bs/bx/by unused as in the reference's nrc==1 path).  Float accumulation follows the reference's
+ * AVX2 lane order exactly, so the result is bit-identical to the x86 build.  Synchronous. */
+int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, size_t bx,
+                          const void *vy_dev, size_t by, int nrc);
+
+/* debug / parity: integer stage of the dot product for rows [row0,row0+nrows) x all N columns:
+ * p[(n*nrows + r)*nb*8 + b*8 + j], sumi[(n*nrows + r)*nb + b], summ[...] as int32. */
+int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
+                       const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
+                       int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev, void *stream);
+
+/* development knob: 0 = policy (default), 1 = always the reference's AVX2 float order, 2 = never.
+ * Overrides the Q4K_GEMV_ORDER environment variable ("exact" / "fast"). */
+int q4k_debug_set_gemv_order(int mode);
+
+/* host-buffer convenience used by the plugin's e2e path and bench.py's e2e leg: copies x (pinned or
+ * pageable host) to the device, runs q4k_mul_mat, copies dst back.  Weights stay resident (w_dev).
+ * Synchronous. */
+int q4k_mul_mat_host(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                     const float *x_host, int64_t N, float *dst_host,
+                     void *x_stage_dev, float *dst_stage_dev,
+                     void *workspace_dev, size_t workspace_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* Q4K_B200_H */

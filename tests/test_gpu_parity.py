@@ -1,0 +1,115 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact for Q8_K bytes and the int32 partial sums; fp32 outputs bit-identical to the AVX2-order
+oracle where the kernel runs the exact order, else within 1e-5 (tolerance defined in `assert_close`)."""
+import numpy as np
+import pytest
+
+from conftest import make_acts, make_weights
+
+pytestmark = pytest.mark.gpu
+
+
+def t(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def assert_close(got, ref, f64, tol=1e-5):
+    """|got - ref| <= tol * max(|ref|, rms of the column).  Pure elementwise-relative is not meaningful
+    for outputs that are the difference of two large sums: the reference's own variants (generic / AVX2 /
+    NEON order) differ from each other by up to ~7e-5 elementwise on such elements."""
+    rms = np.sqrt((f64 ** 2).mean(axis=1, keepdims=True))
+    bound = tol * np.maximum(np.abs(ref), rms)
+    bad = np.abs(got.astype(np.float64) - ref.astype(np.float64)) > bound
+    assert not bad.any(), f"{bad.sum()} elements off; worst {np.abs(got - ref).max()}"
+
+
+@pytest.mark.parametrize("N,K", [(1, 256), (3, 2048), (8, 4096), (512, 512)])
+def test_quantize_q8k_bit_exact(q4k, N, K):
+    from oracle import port
+    x = make_acts(N, K)
+    x[0, -1] = 0.5 / 127 * np.abs(x[0, -256:]).max()      # lands near a .5 tie after scaling
+    got = q4k.quantize_q8_K(t(x)).cpu().numpy()
+    assert np.array_equal(got, port.quantize_q8_K(x))
+
+
+def test_quantize_q8k_denormals_and_ties(q4k):
+    from oracle import port
+    x = np.zeros((2, 512), np.float32)
+    x[0, :256] = np.float32(1e-40)                          # denormals
+    x[0, 256:] = np.tile(np.array([1.0, -1.0], np.float32), 128)
+    x[1, :256] = np.linspace(-127, 127, 256).astype(np.float32) + 0.5
+    x[1, 256:] = np.float32(3.4e38)
+    got = q4k.quantize_q8_K(t(x)).cpu().numpy()
+    assert np.array_equal(got, port.quantize_q8_K(x))
+
+
+@pytest.mark.parametrize("M,K,N", [(33, 512, 1), (64, 2048, 2), (40, 1024, 5), (16, 4096, 8)])
+def test_int32_partials_bit_exact(q4k, M, K, N):
+    from oracle import port
+    w = make_weights(M, K)
+    xq = port.quantize_q8_K(make_acts(N, K))
+    p, si, sm = [a.cpu().numpy() for a in q4k.debug_partials(t(w), t(xq))]
+    for n in range(N):
+        for m in range(M):
+            rp, rsi, rsm = port.vec_dot_partials(w[m], xq[n])
+            assert np.array_equal(p[n, m], rp) and np.array_equal(si[n, m], rsi) and np.array_equal(sm[n, m], rsm)
+
+
+@pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (100, 512, 1), (257, 2048, 2), (64, 14336, 1), (1, 256, 1)])
+def test_gemv_bit_identical_to_avx2_reference_order(q4k, M, K, N):
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(N, K)
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    ref = port.mul_mat(w, x, port.ORDER_AVX2)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
+@pytest.mark.parametrize("M,K,N", [(300, 2048, 3), (129, 1024, 4), (77, 2048, 5), (64, 4096, 8), (50, 512, 7), (40, 512, 6)])
+def test_gemv_batch_within_tolerance(q4k, M, K, N):
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(N, K)
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+
+
+@pytest.mark.parametrize("N", [9, 32, 100])
+def test_mul_mat_large_batch(q4k, N):
+    from oracle import port
+    M, K = 128, 1024
+    w, x = make_weights(M, K), make_acts(N, K)
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+
+
+def test_vec_dot_signature_bit_identical(q4k):
+    import torch
+    from oracle import port
+    K = 2048
+    w = make_weights(4, K)
+    xq = port.quantize_q8_K(make_acts(1, K))
+    s = torch.zeros(1, device="cuda")
+    for m in range(4):
+        q4k.vec_dot_q4_K_q8_K(K, s, 0, t(w[m]), 0, t(xq[0]), 0, 1)
+        assert np.float32(s.item()).view(np.uint32) == port.vec_dot(w[m], xq[0], port.ORDER_AVX2).view(np.uint32)
+    with pytest.raises(q4k.Q4KError):
+        q4k.vec_dot_q4_K_q8_K(K, s, 0, t(w[0]), 0, t(xq[0]), 0, 2)      # nrc != 1: the reference asserts
+
+
+def test_error_codes_and_empty(q4k):
+    import torch
+    w = t(make_weights(4, 256))
+    with pytest.raises((q4k.Q4KError, ValueError)):
+        q4k.mul_mat(w, torch.zeros((1, 300), device="cuda"))
+    out = q4k.mul_mat(t(make_weights(4, 256)[:0]), torch.zeros((1, 256), device="cuda"))
+    assert out.shape == (1, 0)
+    lib = q4k.load()
+    assert lib.q4k_mul_mat(w.data_ptr(), 4, 256, 144, 0, 1, 1024, 0, 16, 0, 0, 0) in (-2, -3)
+    assert lib.q4k_quantize_q8_K(0, 0, 100, 1, 400, 0) == -1
+
+
+def test_launch_counter_moves(q4k):
+    import torch
+    n0 = q4k.kernel_launches()
+    q4k.mul_mat(t(make_weights(8, 256)), torch.ones((1, 256), device="cuda"))
+    assert q4k.kernel_launches() >= n0 + 2
