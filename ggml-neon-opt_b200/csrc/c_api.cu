@@ -78,6 +78,11 @@ int q4k_debug_set_gemv_order(int mode) {
     return Q4K_OK;
 }
 
+int q4k_debug_set_gemv_config(int cfg) {
+    g_gemv_config = cfg;
+    return Q4K_OK;
+}
+
 int q4k_last_cuda_error(void) { return t_last_cuda_error; }
 
 int64_t q4k_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }

@@ -218,11 +218,23 @@ static cudaError_t launch_cfg(GemvParams p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+// development knob (q4k_debug_set_gemv_config): 0 = heuristic, 1.. = force one of the compiled shapes
+int g_gemv_config = 0;
+
 template <int N, bool EXACT>
 static cudaError_t launch_n(const GemvParams &p, cudaStream_t stream) {
+    if (N > 4) return launch_cfg<N, EXACT, 1, 2, 128>(p, stream);
+    switch (g_gemv_config) {
+        case 1: return launch_cfg<N, EXACT, 1, 4, 128>(p, stream);
+        case 2: return launch_cfg<N, EXACT, 2, 2, 256>(p, stream);
+        case 3: return launch_cfg<N, EXACT, 1, 8, 128>(p, stream);
+        case 4: return launch_cfg<N, EXACT, 2, 4, 256>(p, stream);
+        case 5: return launch_cfg<N, EXACT, 1, 4, 256>(p, stream);
+        case 6: return launch_cfg<N, EXACT, 2, 4, 128>(p, stream);
+        default: break;
+    }
     // small matrices: small CTAs so every SM gets several; large ones: 64-row CTAs, two row sets per lane
     const int64_t tiles16 = (p.M + 15) / 16;
-    if (N > 4) return launch_cfg<N, EXACT, 1, 2, 128>(p, stream);
     if (tiles16 <= (int64_t)sm_count() * 8) return launch_cfg<N, EXACT, 1, 4, 128>(p, stream);
     return launch_cfg<N, EXACT, 2, 2, 256>(p, stream);
 }
@@ -246,6 +258,13 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                 const void *xq, int N, int64_t xq_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, bool exact_order, cudaStream_t stream) {
     if (M == 0 || N == 0) return cudaSuccess;
+    if (g_gemv_config == 0 || g_gemv_config >= 10) {      // production path: TMA-bulk staged kernel
+        const cudaError_t e = launch_gemv_q4k_q8k_tma(w, M, K, w_row_stride_bytes, xq, N, xq_row_stride_bytes, dst,
+                                                      dst_col_stride_bytes, exact_order,
+                                                      g_gemv_config >= 10 ? g_gemv_config - 10 : 0, stream);
+        if (e != cudaErrorNotSupported) return e;
+        // activations too large for one shared-memory residency: the K-tiled direct-load kernel below takes it
+    }
     GemvParams p;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
     p.xq = (const uint8_t *)xq; p.xq_stride = xq_row_stride_bytes;

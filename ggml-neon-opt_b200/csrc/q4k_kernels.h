@@ -16,6 +16,13 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                 const void *xq, int N, int64_t xq_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, bool exact_order, cudaStream_t stream);
 
+// the TMA-bulk staged implementation (gemv_q4k_tma.cu); stages <= 0 = choose; cudaErrorNotSupported if the
+// Q8_K activations do not fit in shared memory
+cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                                    const void *xq, int N, int64_t xq_row_stride_bytes,
+                                    float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
+                                    cudaStream_t stream);
+
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, int64_t N, int64_t xq_row_stride_bytes,
@@ -25,6 +32,7 @@ cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride
                                   const void *xq, int64_t N, int64_t xq_row_stride_bytes,
                                   int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);
 
+extern int g_gemv_config;   // development knob, see gemv_q4k.cu
 int sm_count();               // multiprocessors of the current device (cached)
 
 }  // namespace q4k

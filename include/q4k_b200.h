@@ -80,6 +80,8 @@ int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes,
 /* development knob: 0 = policy (default), 1 = always the reference's AVX2 float order, 2 = never.
  * Overrides the Q4K_GEMV_ORDER environment variable ("exact" / "fast"). */
 int q4k_debug_set_gemv_order(int mode);
+/* development knob: 0 = launch heuristic, 1.. = force a compiled GEMV tile shape (gemv_q4k.cu) */
+int q4k_debug_set_gemv_config(int cfg);
 
 /* host-buffer convenience used by the plugin's e2e path and bench.py's e2e leg: copies x (pinned or
  * pageable host) to the device, runs q4k_mul_mat, copies dst back.  Weights stay resident (w_dev).
