@@ -1,0 +1,435 @@
+#!/usr/bin/env python
+"""bench.py — the driver's measurement contract for the Q4_K x Q8_K mul_mat hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one pass of the hot path over one batch of synthetic input:
+
+  N = 1 (default)  workload "tinyllama-1.1b-q4_k_m-decode-token" (BASELINE.json configs[1]): every
+                   GGML_TYPE_Q4_K mul_mat of ONE decode token of TinyLlama-1.1B Q4_K_M, batch 1, in llama
+                   graph order — 134 mul_mats, 477 167 616 B of Q4_K weights (the Q6_K tensors of the
+                   Q4_K_M mix are not on this path: SURVEY.md §8d C2).  Each mul_mat = quantize_row_q8_K of
+                   its F32 activations + the GEMV, as ggml_compute_forward_mul_mat does
+                   (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401).
+  N > 1 (torchrun) workload "llama3-70b-ffn-rowshard" (configs[4]): the 28672x8192 and 8192x28672 Q4_K
+                   matrices, batch 1, weight rows sharded over the N ranks, F32 output slices all-gathered
+                   (SURVEY.md §8e).  Fixed total work -> "scaling": "strong".
+
+`value` = algorithmic bytes of the step (M*K/256*144 + N*K*4 + M*N*4 per mul_mat) / device
+time, inputs resident in HBM.  `e2e` = the same through the host-buffer C-ABI entry (q4k_mul_mat_host_async):
+pinned host activations in, host results out, copies inside the timed region.  `--impl reference` times the
+UNMODIFIED reference ggml CPU code (oracle/_ref, built by oracle/Makefile) on the host cores on the same
+workload.  oracle/ is used here only as that CPU baseline, never on the measured GPU path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "ggml-neon-opt_b200"))
+
+L2_BYTES = 126 << 20
+HBM_NOMINAL_GBS = 8000.0           # BASELINE.json's stated denominator ("~8 TB/s")
+HBM_FALLBACK_GBS = 6650.0          # /opt/skills/guides/B200_PROFILING.md fallback if MEASURED_PEAKS.json is absent
+Q6K_LAYERS = {0, 1, 4, 7, 10, 13, 16, 19, 20, 21}   # use_more_bits(i, 22), L/src/llama-quant.cpp:185-187
+
+
+def tinyllama_token_matmuls():
+    """(name, M, K) of every Q4_K mul_mat of one TinyLlama-1.1B Q4_K_M decode token, in graph order.
+    n_embd 2048, n_head_kv 4 x 64 = 256, n_ff 5632, 22 layers; attn_v / ffn_down are Q6_K in Q6K_LAYERS
+    (L/src/llama-quant.cpp:302-303, 358-364) and output.weight is Q6_K -> not on this path."""
+    mats = []
+    for il in range(22):
+        mats.append((f"blk.{il}.attn_q", 2048, 2048))
+        mats.append((f"blk.{il}.attn_k", 256, 2048))
+        if il not in Q6K_LAYERS:
+            mats.append((f"blk.{il}.attn_v", 256, 2048))
+        mats.append((f"blk.{il}.attn_output", 2048, 2048))
+        mats.append((f"blk.{il}.ffn_gate", 5632, 2048))
+        mats.append((f"blk.{il}.ffn_up", 5632, 2048))
+        if il not in Q6K_LAYERS:
+            mats.append((f"blk.{il}.ffn_down", 2048, 5632))
+    return mats
+
+
+def ffn70b_matmuls():
+    return [("ffn_up_70b", 28672, 8192), ("ffn_down_70b", 8192, 28672)]
+
+
+def algo_bytes(M, K, N):
+    return M * (K // 256) * 144 + N * K * 4 + M * N * 4
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", p
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)", {}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc, self.thr = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thr = threading.Thread(target=self._read, daemon=True)
+        self.thr.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def rand_q4k(torch, M, K, device, gen):
+    """Random VALID block_q4_K bytes (any byte pattern with finite fp16 d/dmin is a valid block):
+    throughput-only weights, d = 2^-4, dmin = 2^-5.  Parity is tested elsewhere on really quantized weights."""
+    nb = K // 256
+    w = torch.randint(0, 256, (M, nb, 144), dtype=torch.uint8, device=device, generator=gen)
+    w[..., 0] = 0x00; w[..., 1] = 0x2c; w[..., 2] = 0x00; w[..., 3] = 0x28
+    return w.view(M, nb * 144)
+
+
+class MatSet:
+    """Device-resident weights + per-mul_mat activations / results / staging for one workload."""
+
+    def __init__(self, torch, q4k, mats, N, device, seed=1234, row_range=None):
+        self.torch, self.q4k, self.lib, self.N = torch, q4k, q4k.load(), N
+        gen = torch.Generator(device=device)
+        gen.manual_seed(seed)
+        self.items = []
+        for name, M, K in mats:
+            r0, r1 = (0, M) if row_range is None else row_range(M)
+            w = rand_q4k(torch, r1 - r0, K, device, gen)
+            x = torch.randn((N, K), device=device, generator=gen)
+            dst = torch.zeros((N, r1 - r0), device=device)
+            self.items.append(dict(name=name, M=r1 - r0, K=K, M_full=M, w=w, x=x, dst=dst))
+        kmax = max(K for _, _, K in mats)
+        self.ws = torch.empty(max(q4k.workspace_bytes(kmax, N), 16), dtype=torch.uint8, device=device)
+        self.algo_bytes = sum(algo_bytes(it["M"], it["K"], N) for it in self.items)
+        self.weight_bytes = sum(it["w"].numel() for it in self.items)
+
+    def enqueue_device(self):
+        """One step with inputs resident in HBM: quantize + GEMV per mul_mat on the current stream."""
+        st = self.torch.cuda.current_stream().cuda_stream
+        ws, wsn, N, f = self.ws.data_ptr(), self.ws.numel(), self.N, self.lib.q4k_mul_mat
+        for it in self.items:
+            rc = f(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), it["x"].data_ptr(), N, it["K"] * 4,
+                   it["dst"].data_ptr(), it["M"] * 4, ws, wsn, st)
+            if rc != 0:
+                raise RuntimeError(f"q4k_mul_mat rc={rc} cuda={self.lib.q4k_last_cuda_error()}")
+
+    def make_host(self):
+        t = self.torch
+        for it in self.items:
+            it["x_host"] = it["x"].cpu().pin_memory()
+            it["dst_host"] = t.zeros((self.N, it["M"]), dtype=t.float32).pin_memory()
+            it["x_stage"] = t.empty_like(it["x"])
+        self.h2d = sum(it["x_host"].numel() * 4 for it in self.items)
+        self.d2h = sum(it["dst_host"].numel() * 4 for it in self.items)
+
+    def enqueue_host(self):
+        """One step through the host-buffer C-ABI entry: H2D x, quantize, GEMV, D2H dst per mul_mat."""
+        st = self.torch.cuda.current_stream().cuda_stream
+        ws, wsn, N, f = self.ws.data_ptr(), self.ws.numel(), self.N, self.lib.q4k_mul_mat_host_async
+        for it in self.items:
+            rc = f(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), it["x_host"].data_ptr(), N,
+                   it["dst_host"].data_ptr(), it["x_stage"].data_ptr(), it["dst"].data_ptr(), ws, wsn, st)
+            if rc != 0:
+                raise RuntimeError(f"q4k_mul_mat_host_async rc={rc} cuda={self.lib.q4k_last_cuda_error()}")
+
+
+def timed_steps(torch, step_fn, steps, warmup, barrier):
+    """W untimed warm-ups, then exactly K steps between CUDA events on the launching stream, a barrier +
+    synchronize on both sides.  Returns milliseconds for the K steps."""
+    for _ in range(warmup):
+        step_fn()
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step_fn()
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    return e0.elapsed_time(e1)
+
+
+def graph_of(torch, enqueue):
+    """Capture one step into a CUDA graph (the launches are ours; the graph removes host launch latency)."""
+    enqueue()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        enqueue()
+    return g
+
+
+def gemv_shape_table(torch, q4k, device, shapes, steps=20):
+    """Per-shape GEMV figures (quantize + GEMV through q4k_mul_mat), rotating through > 2 x L2 of distinct
+    weight copies so the bytes come from HBM.  Extra evidence; not the headline."""
+    out = []
+    for M, K, N in shapes:
+        wbytes = M * (K // 256) * 144
+        copies = max(2, (2 * L2_BYTES + wbytes) // wbytes + 1)
+        ms = MatSet(torch, q4k, [(f"copy{i}", M, K) for i in range(copies)], N, device, seed=99)
+        g = graph_of(torch, ms.enqueue_device)
+        for _ in range(3):
+            g.replay()
+        t = timed_steps(torch, g.replay, steps, 2, lambda: None) / (steps * copies)
+        b = algo_bytes(M, K, N)
+        out.append({"M": M, "K": K, "N": N, "us": round(t * 1e3, 3), "gbs": round(b / t / 1e6, 1),
+                    "weight_copies": copies})
+        del ms, g
+        torch.cuda.empty_cache()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def reference_step_seconds(mats, N, threads, warmup, iters):
+    """The UNMODIFIED reference (oracle/_ref: ggml_mul_mat graph on ggml_backend_cpu -> ggml_compute_forward_mul_mat
+    -> quantize_row_q8_K + ggml_vec_dot_q4_K_q8_K, AVX2 branch) on the whole mul_mat set.  mean seconds per step."""
+    from oracle import ref
+    if not ref.available():
+        raise RuntimeError("oracle/_ref is not built (make -C oracle ref in the build container)")
+    best, mean, _ = ref.mul_mat_set([(M, K) for _, M, K in mats], N, threads, warmup, iters)
+    return best, mean
+
+
+def cpu_baseline_obj(mats, N, total_bytes, budget_s=20.0):
+    """Reference CPU code on this box's host cores, bounded to ~budget_s of CPU wall time."""
+    threads = host_threads()
+    t0 = time.time()
+    best, mean = reference_step_seconds(mats, N, threads, 1, 2)
+    iters = int(max(2, min(20, (budget_s - (time.time() - t0)) / max(mean, 1e-4))))
+    best2, mean2 = reference_step_seconds(mats, N, threads, 1, iters)
+    mean = min(mean, mean2)
+    return {"value": round(total_bytes / mean / 1e9, 3), "unit": "GB/s", "cores": threads, "kind": "reference",
+            "sample": f"whole step ({len(mats)} Q4_K mul_mats, N={N}) x {iters} iterations, ggml CPU backend, AVX2 vec_dot, "
+                      f"plain CPU buffer (no repack), ggml threadpool (no OpenMP); mean step {mean * 1e3:.2f} ms, "
+                      f"best {min(best, best2) * 1e3:.2f} ms",
+            "steps_per_s": round(1.0 / mean, 2)}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    mats = tinyllama_token_matmuls() if args.workload == "tinyllama-token" else ffn70b_matmuls()
+    N = args.batch
+    total = sum(algo_bytes(M, K, N) for _, M, K in mats)
+    threads = host_threads()
+    _, mean = reference_step_seconds(mats, N, threads, max(args.warmup, 1), max(args.steps, 1))
+    val = total / mean / 1e9
+    line = {"impl": "reference", "metric": "q4k_gemv_hbm_gbs", "value": round(val, 3), "unit": "GB/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(mean * 1e3, 4),
+            "higher_is_better": True, "scaling": "weak" if args.workload == "tinyllama-token" else "strong",
+            "vs_baseline": None, "dtype": "int8 x uint4 -> int32, f32 scales", "data": "synthetic",
+            "config": {"workload": workload_name(args.workload), "batch": N, "mul_mats": len(mats),
+                       "threads": threads, "path": "ggml_backend_cpu / ggml_compute_forward_mul_mat / AVX2 vec_dot"},
+            "cpu_baseline": {"value": round(val, 3), "unit": "GB/s", "cores": threads, "kind": "reference",
+                             "sample": f"whole step x {args.steps} iterations"},
+            "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "decode_tok_s": round(1.0 / mean, 2) if args.workload == "tinyllama-token" else None,
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(w):
+    return {"tinyllama-token": "tinyllama-1.1b-q4_k_m-decode-token (configs[1]): 134 Q4_K mul_mats, batch 1",
+            "ffn70b": "llama3-70b-ffn-rowshard (configs[4]): 28672x8192 + 8192x28672 Q4_K, batch 1"}[w]
+
+
+# ------------------------------------------------------------------------------------------------ main
+def run_ours(args, rank, world, local_rank):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the Q4_K path has no CPU fallback")
+    import q4k_b200
+    lib = q4k_b200.load()
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if not lib.q4k_device_ok(local_rank):
+        raise SystemExit("bench.py: device is not compute capability 10.x (sm_100a build)")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    N = args.batch
+    sharded = args.workload == "ffn70b"
+    mats = ffn70b_matmuls() if sharded else tinyllama_token_matmuls()
+    row_range = (lambda M: (M * rank // world, M * (rank + 1) // world)) if sharded else None
+    ms = MatSet(torch, q4k_b200, mats, N, device, seed=1234 + (rank if sharded else 0), row_range=row_range)
+    total_bytes = sum(algo_bytes(M, K, N) for _, M, K in mats) * (1 if sharded else world)
+
+    gathered = None
+    if sharded and world > 1:
+        gathered = [torch.zeros((world, N, it["M"]), device=device) for it in ms.items]
+
+        def enqueue():
+            st = torch.cuda.current_stream().cuda_stream
+            for it, full in zip(ms.items, gathered):
+                rc = lib.q4k_mul_mat(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), it["x"].data_ptr(), N, it["K"] * 4,
+                                     it["dst"].data_ptr(), it["M"] * 4, ms.ws.data_ptr(), ms.ws.numel(), st)
+                assert rc == 0, rc
+                dist.all_gather_into_tensor(full, it["dst"])
+        step = enqueue
+        launches_per_step = None
+    else:
+        g = graph_of(torch, ms.enqueue_device)
+        step = g.replay
+    n0 = lib.q4k_kernel_launches()
+    ms.enqueue_device()
+    launches_per_step = lib.q4k_kernel_launches() - n0
+    torch.cuda.synchronize()
+
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ms_total = timed_steps(torch, step, args.steps, args.warmup, barrier)
+    # end to end: pinned host activations in, host results out, every step
+    ms.make_host()
+    if sharded and world > 1:
+        def step_host():
+            ms.enqueue_host()
+            for it, full in zip(ms.items, gathered):
+                dist.all_gather_into_tensor(full, it["dst"])
+            torch.cuda.current_stream().synchronize()
+    else:
+        def step_host():
+            ms.enqueue_host()
+            torch.cuda.current_stream().synchronize()
+    ms_e2e = timed_steps(torch, step_host, args.steps, args.warmup, barrier)
+    clk = clocks.stop() if rank == 0 else None
+
+    t = torch.tensor([ms_total, ms_e2e], device=device, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src, _ = measured_peaks()
+    per_step_ms = ms_total / args.steps
+    value = total_bytes / (per_step_ms * 1e-3) / 1e9
+    e2e_val = total_bytes / (ms_e2e / args.steps * 1e-3) / 1e9
+    # dominant kernel = the GEMV: per-launch algorithmic bytes / average launch slot inside the timed region
+    n_gemv = len(ms.items)
+    per_launch_bytes = ms.algo_bytes / n_gemv
+    per_launch_us = per_step_ms * 1e3 / n_gemv
+    achieved = per_launch_bytes / per_launch_us / 1e3
+    line = {"metric": "q4k_gemv_hbm_gbs", "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(per_step_ms, 5), "higher_is_better": True,
+            "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+            "dtype": "int8 x uint4 -> int32, f32 scales", "data": "synthetic (random valid block_q4_K bytes, N(0,1) activations)",
+            "config": {"workload": workload_name(args.workload), "batch": N, "mul_mats": n_gemv,
+                       "weight_bytes_per_step_per_gpu": ms.weight_bytes,
+                       "l2": f"no flush needed: each step streams {ms.weight_bytes >> 20} MiB of distinct weights per GPU (> 126 MiB L2)"
+                             if ms.weight_bytes > L2_BYTES else "WARNING: per-GPU weights fit in L2",
+                       "launch": "CUDA graph replay of the C-ABI launches" if gathered is None else "stream launches + NCCL all_gather",
+                       "parallelism": f"rowshard{world}" if sharded else f"replica{world}"},
+            "decode_tok_s": round(1e3 / per_step_ms, 1) if not sharded else None,
+            "pct_of_nominal_8TBs": round(100 * value / world / HBM_NOMINAL_GBS, 2),
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "kernel": "gemv_q4k_tma_kernel (+ quantize_q8_K_kernel in the same launch slot)",
+                         "bytes_per_launch": round(per_launch_bytes), "us_per_launch": round(per_launch_us, 3)},
+            "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": ms.h2d, "d2h_bytes_per_step": ms.d2h,
+                    "ms_per_step": round(ms_e2e / args.steps, 5),
+                    "decode_tok_s": round(1e3 / (ms_e2e / args.steps), 1) if not sharded else None},
+            "gpu_launches": int(launches_per_step * args.steps), "clocks": clk}
+    if world == 1 and not args.no_cpu:
+        try:
+            line["cpu_baseline"] = cpu_baseline_obj(mats, N, total_bytes)
+        except Exception as e:       # the baseline is a reported number, never a dependency of the GPU path
+            line["cpu_baseline"] = {"value": None, "unit": "GB/s", "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
+    if world == 1 and args.shapes:
+        line["shapes"] = gemv_shape_table(torch, q4k_b200, device,
+                                          [(5632, 2048, 1), (4096, 14336, 1), (14336, 4096, 1), (4096, 14336, 8),
+                                           (28672, 8192, 1), (8192, 28672, 1), (28672, 8192, 8)])
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=[None, "tinyllama-token", "ffn70b"])
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--shapes", action="store_true", help="add the per-shape GEMV table (C1/C4/C5)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.workload is None:
+        args.workload = "tinyllama-token" if max(world, args.gpus) == 1 else "ffn70b"
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -181,10 +181,10 @@ int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes,
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 
-int q4k_mul_mat_host(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
-                     const float *x_host, int64_t N, float *dst_host,
-                     void *x_stage_dev, float *dst_stage_dev,
-                     void *workspace_dev, size_t workspace_bytes, void *stream) {
+int q4k_mul_mat_host_async(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                           const float *x_host, int64_t N, float *dst_host,
+                           void *x_stage_dev, float *dst_stage_dev,
+                           void *workspace_dev, size_t workspace_bytes, void *stream) {
     if (M < 0 || N < 0 || K < 0) return Q4K_ERR_BAD_SHAPE;
     if (M == 0 || N == 0) return Q4K_OK;
     if (!x_host || !dst_host || !x_stage_dev || !dst_stage_dev) return Q4K_ERR_BAD_POINTER;
@@ -196,7 +196,17 @@ int q4k_mul_mat_host(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stri
                                dst_stage_dev, M * 4, workspace_dev, workspace_bytes, stream);
     if (rc != Q4K_OK) return rc;
     e = cudaMemcpyAsync(dst_host, dst_stage_dev, (size_t)N * M * 4, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+int q4k_mul_mat_host(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                     const float *x_host, int64_t N, float *dst_host,
+                     void *x_stage_dev, float *dst_stage_dev,
+                     void *workspace_dev, size_t workspace_bytes, void *stream) {
+    const int rc = q4k_mul_mat_host_async(w_dev, M, K, w_row_stride_bytes, x_host, N, dst_host, x_stage_dev, dst_stage_dev,
+                                          workspace_dev, workspace_bytes, stream);
+    if (rc != Q4K_OK || M <= 0 || N <= 0) return rc;
+    const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 

@@ -50,6 +50,7 @@ def load():
         L.q4k_vec_dot_q4_K_q8_K.argtypes = [i32, vp, sz, vp, sz, vp, sz, i32]
         L.q4k_debug_partials.argtypes = [vp, i64, i64, i64, i64, vp, i64, i64, vp, vp, vp, vp]
         L.q4k_mul_mat_host.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
+        L.q4k_mul_mat_host_async.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         _lib = L
     return _lib
 

@@ -91,6 +91,15 @@ int q4k_mul_mat_host(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stri
                      void *x_stage_dev, float *dst_stage_dev,
                      void *workspace_dev, size_t workspace_bytes, void *stream);
 
+/* same without the final synchronize: everything (H2D of x, quantize, mul_mat, D2H of dst) is queued on
+ * `stream`; the caller synchronizes the stream once per batch of calls.  This is what the backend plugin's
+ * set_tensor_async / graph_compute / get_tensor_async + synchronize sequence amounts to
+ * (L/ggml/src/ggml-backend-impl.h:95-106).  x_host / dst_host should be pinned. */
+int q4k_mul_mat_host_async(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                           const float *x_host, int64_t N, float *dst_host,
+                           void *x_stage_dev, float *dst_stage_dev,
+                           void *workspace_dev, size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

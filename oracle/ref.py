@@ -56,6 +56,9 @@ def libs():
         shim.ref_plugin_mul_mat_q4k.argtypes = [C.c_char_p, vp, i64, i64, vp, i64, vp, i32, C.POINTER(C.c_double)]
         shim.ref_plugin_mul_mat_q4k.restype = i32
         shim.ref_cpu_has_avx2.restype = i32
+        shim.ref_mul_mat_set_q4k.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), i64, i32, i32, i32,
+                                             C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        shim.ref_mul_mat_set_q4k.restype = i32
         # ggml-cpu's fp16->fp32 is a lookup table filled by ggml_cpu_init() (ggml-cpu.c:3526-3549);
         # the reference always reaches vec_dot through backend init, direct callers must do it themselves
         cpu.ggml_cpu_init()
@@ -162,6 +165,21 @@ def plugin_mul_mat(so_path: str, w: np.ndarray, x: np.ndarray, iters: int = 1):
     if rc != 0:
         raise RuntimeError(f"ref_plugin_mul_mat_q4k rc={rc}")
     return dst, secs[0], secs[1]
+
+
+def mul_mat_set(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, iters: int = 3):
+    """One ggml graph holding a Q4_K mul_mat per (M, K) in `shapes` (random valid weights made inside the
+    shim), computed on ggml_backend_cpu with n_threads.  Returns (best_seconds, mean_seconds, checksum)."""
+    shim = libs()[3]
+    n = len(shapes)
+    Ms = (C.c_int64 * n)(*[int(m) for m, _ in shapes])
+    Ks = (C.c_int64 * n)(*[int(k) for _, k in shapes])
+    secs = (C.c_double * 2)()
+    chk = C.c_double(0)
+    rc = shim.ref_mul_mat_set_q4k(n, Ms, Ks, N, n_threads, warmup, iters, secs, C.byref(chk))
+    if rc != 0:
+        raise RuntimeError(f"ref_mul_mat_set_q4k rc={rc}")
+    return secs[0], secs[1], chk.value
 
 
 def has_avx2() -> bool:

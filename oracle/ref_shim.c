@@ -118,3 +118,68 @@ int ref_plugin_mul_mat_q4k(const char *path, const void *w_q4k, int64_t M, int64
 
 int ref_cpu_has_avx2(void) { return ggml_cpu_has_avx2(); }
 int ref_n_backend_devices(void) { return (int)ggml_backend_dev_count(); }
+
+/* A whole set of independent Q4_K mul_mats in ONE graph (bench.py's reference arm: the Q4_K matmuls of one
+ * decode token).  Weights are filled with valid random block_q4_K bytes (xorshift; fp16 d = 2^-4,
+ * dmin = 2^-5 — throughput only, the parity tests use real quantized weights), activations with a
+ * deterministic ramp.  Times `iters` graph computes after `warmup`.  secs[0] = best, secs[1] = mean.
+ * checksum (optional) receives the sum of all outputs of the last compute. */
+int ref_mul_mat_set_q4k(int n_mats, const int64_t *Ms, const int64_t *Ks, int64_t N, int n_threads,
+                        int warmup, int iters, double *secs, double *checksum) {
+    ggml_backend_t cpu = ggml_backend_cpu_init();
+    if (!cpu) return -1;
+    ggml_backend_cpu_set_n_threads(cpu, n_threads);
+    struct ggml_init_params ip = { ggml_tensor_overhead() * (size_t)(3 * n_mats + 8) +
+                                   ggml_graph_overhead_custom((size_t)(4 * n_mats + 16), false), NULL, true };
+    struct ggml_context *ctx = ggml_init(ip);
+    if (!ctx) { ggml_backend_free(cpu); return -1; }
+    struct ggml_cgraph *gf = ggml_new_graph_custom(ctx, (size_t)(4 * n_mats + 16), false);
+    struct ggml_tensor **ws = calloc((size_t)n_mats, sizeof *ws), **xs = calloc((size_t)n_mats, sizeof *xs),
+                       **ys = calloc((size_t)n_mats, sizeof *ys);
+    for (int i = 0; i < n_mats; ++i) {
+        ws[i] = ggml_new_tensor_2d(ctx, GGML_TYPE_Q4_K, Ks[i], Ms[i]);
+        xs[i] = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, Ks[i], N);
+        ys[i] = ggml_mul_mat(ctx, ws[i], xs[i]);
+        ggml_build_forward_expand(gf, ys[i]);
+    }
+    int rc = 0;
+    ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors_from_buft(ctx, ggml_backend_cpu_buffer_type());
+    if (!buf) { rc = -2; goto done; }
+    uint64_t s = 0x9E3779B97F4A7C15ull;
+    for (int i = 0; i < n_mats; ++i) {
+        uint8_t *p = (uint8_t *)ws[i]->data;
+        const size_t nbytes = ggml_nbytes(ws[i]);
+        for (size_t o = 0; o + 8 <= nbytes; o += 8) {
+            s ^= s << 13; s ^= s >> 7; s ^= s << 17;
+            memcpy(p + o, &s, 8);
+        }
+        for (size_t o = 0; o < nbytes; o += 144) { p[o] = 0x00; p[o + 1] = 0x2c; p[o + 2] = 0x00; p[o + 3] = 0x28; }
+        float *x = (float *)xs[i]->data;
+        const int64_t ne = Ks[i] * N;
+        for (int64_t j = 0; j < ne; ++j) x[j] = (float)((j * 2654435761u) % 2001) * 1e-3f - 1.0f;
+    }
+    for (int i = 0; i < warmup; ++i) ggml_backend_graph_compute(cpu, gf);
+    double best = 1e30, total = 0;
+    for (int i = 0; i < iters; ++i) {
+        const double t0 = now_s();
+        if (ggml_backend_graph_compute(cpu, gf) != GGML_STATUS_SUCCESS) { rc = -3; break; }
+        const double dt = now_s() - t0;
+        total += dt;
+        if (dt < best) best = dt;
+    }
+    if (secs) { secs[0] = best; secs[1] = iters > 0 ? total / iters : 0; }
+    if (checksum) {
+        double c = 0;
+        for (int i = 0; i < n_mats; ++i) {
+            const float *y = (const float *)ys[i]->data;
+            for (int64_t j = 0; j < Ms[i] * N; ++j) c += y[j];
+        }
+        *checksum = c;
+    }
+done:
+    if (buf) ggml_backend_buffer_free(buf);
+    ggml_free(ctx);
+    free(ws); free(xs); free(ys);
+    ggml_backend_free(cpu);
+    return rc;
+}
