@@ -42,6 +42,7 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 // Q4K_GEMV_ORDER=fast selects the cheaper float association for every batch size; default is the
 // reference's AVX2 order (bit-identical fp32) wherever the GEMV stays HBM-bound with it.
+static int64_t g_fuse_limit = 32768;   // N*K floats up to which the quantizer is fused into the GEMV launch
 static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
 static bool gemv_exact_for(int N) {
     int &mode = g_order_mode;
@@ -80,6 +81,16 @@ int q4k_debug_set_gemv_order(int mode) {
 
 int q4k_debug_set_gemv_config(int cfg) {
     g_gemv_config = cfg;
+    return Q4K_OK;
+}
+
+int q4k_debug_set_fuse_limit(int64_t n_floats) {
+    g_fuse_limit = n_floats;
+    return Q4K_OK;
+}
+
+int q4k_debug_set_pdl(int on) {
+    g_gemv_pdl = on ? 1 : 0;
     return Q4K_OK;
 }
 
@@ -147,6 +158,19 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
     if (K > 0) {
         if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
         if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
+        // decode shapes: one launch — every CTA quantizes the (small) activations into its own shared memory
+        if (N <= Q4K_GEMV_MAX_N && N * K <= g_fuse_limit && g_gemv_config == 0) {
+            if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
+            const int64_t nb = K / Q4K_QK_K;
+            if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (dst_col_stride_bytes < M * 4 || (dst_col_stride_bytes & 3)) return Q4K_ERR_BAD_SHAPE;
+            const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M, K, w_row_stride_bytes, nullptr, x_dev, (int)N, x_row_stride_bytes,
+                                                          dst_dev, dst_col_stride_bytes, gemv_exact_for((int)N), 0,
+                                                          g_gemv_pdl != 0, (cudaStream_t)stream);
+            if (e == cudaSuccess) return Q4K_OK;
+            if (e != cudaErrorNotSupported) return cuda_fail(e);
+        }
         const int rc = q4k_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, stream);
         if (rc != Q4K_OK) return rc;
     }

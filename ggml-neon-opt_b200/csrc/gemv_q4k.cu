@@ -220,6 +220,7 @@ static cudaError_t launch_cfg(GemvParams p, cudaStream_t stream) {
 
 // development knob (q4k_debug_set_gemv_config): 0 = heuristic, 1.. = force one of the compiled shapes
 int g_gemv_config = 0;
+int g_gemv_pdl = 1;
 
 template <int N, bool EXACT>
 static cudaError_t launch_n(const GemvParams &p, cudaStream_t stream) {
@@ -259,9 +260,9 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                 float *dst, int64_t dst_col_stride_bytes, bool exact_order, cudaStream_t stream) {
     if (M == 0 || N == 0) return cudaSuccess;
     if (g_gemv_config == 0 || g_gemv_config >= 10) {      // production path: TMA-bulk staged kernel
-        const cudaError_t e = launch_gemv_q4k_q8k_tma(w, M, K, w_row_stride_bytes, xq, N, xq_row_stride_bytes, dst,
+        const cudaError_t e = launch_gemv_q4k_q8k_tma(w, M, K, w_row_stride_bytes, xq, nullptr, N, xq_row_stride_bytes, dst,
                                                       dst_col_stride_bytes, exact_order,
-                                                      g_gemv_config >= 10 ? g_gemv_config - 10 : 0, stream);
+                                                      g_gemv_config >= 10 ? g_gemv_config - 10 : 0, g_gemv_pdl != 0, stream);
         if (e != cudaErrorNotSupported) return e;
         // activations too large for one shared-memory residency: the K-tiled direct-load kernel below takes it
     }

@@ -1,26 +1,31 @@
 // gemv_q4k_tma.cu — decode GEMV (batch 1..8), TMA-bulk staged.  dst[n][m] = vec_dot(W row m, Q8_K(x row n)).
 // Replaces ggml_compute_forward_mul_mat_one_chunk's vec_dot loop (L/ggml/src/ggml-cpu/ggml-cpu.c:1115-1203)
-// + ggml_vec_dot_q4_K_q8_K (L/ggml/src/ggml-cpu/arch/x86/quants.c:1741-1823) for N <= 8.
+// + ggml_vec_dot_q4_K_q8_K (L/ggml/src/ggml-cpu/arch/x86/quants.c:1741-1823) for N <= 8, and — when the
+// activations are handed over as F32 — the quantize_row_q8_K pass in front of it (ggml-cpu.c:1267-1307,
+// L/ggml/src/ggml-quants.c:2555-2592) inside the same launch.
 //
 // HBM-bound by design; no tensor cores.  Every weight byte crosses HBM once, moved by the copy engine:
-//   * each warp owns a private ring of S stages; a stage holds a 4-row x 8-superblock tile of block_q4_K
-//     (4 x 1152 contiguous bytes) fetched by lane 0 with cp.async.bulk (UBLKCP) + mbarrier complete_tx.
-//     S-1 tiles (~4.6 KB each) are in flight per warp with no registers tied up.
-//   * one lane per superblock ("lane (r, b)": row r of the tile, superblock b): the 16 B header is unpacked
-//     once per superblock (no redundancy across lanes), nibbles come out of shared memory with conflict-free
-//     LDS.128 (144 B block stride = 36 words = 4 banks per lane step).
-//   * the Q8_K activations are re-laid out once per CTA: 272 B per block (256 qs + the 8 pair-summed bsums),
-//     68 words = 4 banks per block step, so eight lanes on eight different blocks never conflict and lanes
-//     on the same block broadcast.
+//   * each warp owns a private ring of S slots; a slot holds a 4-row x 8-superblock tile of block_q4_K
+//     (4 x 1152 contiguous bytes) fetched with cp.async.bulk (UBLKCP) + mbarrier complete_tx.
+//   * one lane per superblock ("lane (r, b)": row r of the tile, superblock b).  The lane pulls its 144 bytes
+//     out of shared memory into registers with nine conflict-free LDS.128 (144 B block stride = 36 words =
+//     4 banks per lane step), the warp hands the slot straight back to the copy engine, and the arithmetic
+//     runs from registers while the next tile is in flight.  The 16 B header is unpacked once per superblock.
+//   * the Q8_K activations live in shared memory once per CTA: 272 B per block (256 qs + the 8 pair-summed
+//     bsums), 68 words = 4 banks per block step, so eight lanes on eight blocks never conflict and the four
+//     rows of a tile broadcast.  They are either copied from a Q8_K workspace or quantized in place from F32
+//     (same arithmetic as quantize_q8k.cu, bit-exact).
 //   * rows are dealt to CTAs in balanced contiguous ranges; warps of a CTA pull 4-row groups from a
 //     shared-memory counter, so the tail inside an SM is one row group.
+//   * programmatic dependent launch: barrier init and the first weight tiles are issued BEFORE
+//     griddepcontrol.wait (weights never depend on the previous kernel), only the activations wait.
 //
 // Float order.  EXACT reproduces the reference's AVX2 accumulation bit for bit: the integer lane sums
 // sumi_t (t = 0..7: word t of every 32-byte nibble group) and the four min products of every superblock
-// are parked in a per-warp scratch, then lane (r, t) runs the reference's FMA chain over the superblocks
-// in order: acc_t = fma(d, (float)sumi_t, acc_t), acc_m = fma(dmin, (float)prod, acc_m); the final
-// horizontal adds follow hsum_float_8 / movehl / movehdup.  Without EXACT every lane folds its superblock
-// into one int and lanes are summed at the end (same integers; fp32 within 1e-5 of the reference).
+// are parked in a per-warp scratch (transposed, conflict-free), then lane (r, t) runs the reference's FMA
+// chain over the superblocks in order: acc_t = fma(d, (float)sumi_t, acc_t), acc_m = fma(dmin, (float)prod,
+// acc_m); the final horizontal adds follow hsum_float_8 / movehl / movehdup.  Without EXACT every lane folds
+// its superblock into one int and lanes are summed at the end (same integers; fp32 within 1e-5).
 //
 // The high nibbles are never shifted: dp4a.u32.s32 on (w & 0xf0f0f0f0) gives 16 x the high-nibble dot
 // product, the low side is multiplied by 16 x scale, and the (exact) >> 4 happens once per lane sum.
@@ -36,15 +41,17 @@ constexpr int TILE_SB = 8;
 constexpr int ROW_BYTES = TILE_SB * BLK_Q4K;        // 1152
 constexpr int STAGE_BYTES = TILE_ROWS * ROW_BYTES;  // 4608
 constexpr int Q8_STRIDE = 272;                      // 256 qs + 8 x int16 pair sums
-constexpr int SCR_WORDS = 32 * 20 + 32;             // per column scratch: 20 words per (r, b) + row skew
+constexpr int SCR_ROW = 136;                        // scratch words per (column, tile row); 136 % 32 == 8
+constexpr int SCR_WORDS = TILE_ROWS * SCR_ROW;      // per column
 constexpr int WARPS = 8;
 
 struct TmaGemvParams {
     const uint8_t *w;
     int64_t M, w_stride;
     int nb;
-    const uint8_t *xq;
-    int64_t xq_stride;
+    const uint8_t *xq;      // Q8_K activations, or
+    const float *xf;        // F32 activations (quantized inside the kernel) when xq == nullptr
+    int64_t x_stride;       // bytes between activation rows (of whichever is set)
     float *dst;
     int64_t dst_stride;
     int64_t n_groups;       // ceil(M / 4)
@@ -59,6 +66,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t done;
     do {
@@ -71,40 +81,70 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c) {
     int d;
     asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
     return d;
 }
+__device__ __forceinline__ uint4 lds128(const uint8_t *p) { return *reinterpret_cast<const uint4 *>(p); }
+
+// activations already Q8_K in global memory -> the CTA's shared-memory layout
+template <int N>
+__device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, float *d_s) {
+    const int tid = threadIdx.x, nt = blockDim.x, nb = p.nb;
+    for (int i = tid; i < N * nb * 64; i += nt) {
+        const int blk = i >> 6, wd = i & 63, n = blk / nb, b = blk - n * nb;
+        const uint8_t *src = p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K;
+        reinterpret_cast<uint32_t *>(q8_s + (size_t)blk * Q8_STRIDE)[wd] = (reinterpret_cast<const uint32_t *>(src + Q8K_QS))[wd];
+    }
+    for (int i = tid; i < N * nb * 8; i += nt) {
+        const int blk = i >> 3, k = i & 7, n = blk / nb, b = blk - n * nb;
+        const int16_t *bs = reinterpret_cast<const int16_t *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K + Q8K_BSUMS);
+        reinterpret_cast<int16_t *>(q8_s + (size_t)blk * Q8_STRIDE + 256)[k] = (int16_t)(bs[2 * k] + bs[2 * k + 1]);   // hadd_epi16
+    }
+    for (int i = tid; i < N * nb; i += nt) {
+        const int n = i / nb, b = i - n * nb;
+        d_s[i] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K);
+    }
+}
+
+// F32 activations -> Q8_K in shared memory: one warp per 256-block, the arithmetic of quantize_q8k.cu
+// (quantize_row_q8_K_ref, L/ggml/src/ggml-quants.c:2555-2592) through q4k::quantize_block_q8_K.
+template <int N>
+__device__ __forceinline__ void stage_f32(const TmaGemvParams &p, uint8_t *q8_s, float *d_s) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5, nb = p.nb;
+    for (int blk = warp; blk < N * nb; blk += nwarps) {
+        const int n = blk / nb, b = blk - n * nb;
+        const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(p.xf) + n * p.x_stride) + b * QK_K;
+        const float4 a = reinterpret_cast<const float4 *>(src)[lane];       // plain (coherent) loads: with PDL the
+        const float4 c = reinterpret_cast<const float4 *>(src)[32 + lane];  // producer kernel may still have been running when this one started
+        const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+        uint32_t w_lo, w_hi;
+        int s_lo, s_hi;
+        const float d = quantize_block_q8_K(v, lane, w_lo, w_hi, s_lo, s_hi);
+        uint8_t *dst = q8_s + (size_t)blk * Q8_STRIDE;
+        reinterpret_cast<uint32_t *>(dst)[lane] = w_lo;
+        reinterpret_cast<uint32_t *>(dst)[32 + lane] = w_hi;
+        // s_lo / s_hi hold the sums of 16-element groups l/4 and 8 + l/4; the pair sums are 32-element groups
+        s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 4);
+        s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 4);
+        if ((lane & 7) == 0) {
+            reinterpret_cast<int16_t *>(dst + 256)[lane >> 3] = (int16_t)s_lo;
+            reinterpret_cast<int16_t *>(dst + 256)[4 + (lane >> 3)] = (int16_t)s_hi;
+        }
+        if (lane == 0) d_s[blk] = d;
+    }
+}
 
 }  // namespace
 
 namespace {
 
-__device__ __forceinline__ uint4 lds128(const uint8_t *p) { return *reinterpret_cast<const uint4 *>(p); }
-
-template <int N>
-__device__ __forceinline__ void stage_activations(const TmaGemvParams &p, uint8_t *q8_s, float *d_s) {
-    const int tid = threadIdx.x, nt = blockDim.x, nb = p.nb;
-    for (int i = tid; i < N * nb * 64; i += nt) {
-        const int blk = i >> 6, wd = i & 63, n = blk / nb, b = blk - n * nb;
-        const uint8_t *src = p.xq + n * p.xq_stride + (int64_t)b * BLK_Q8K;
-        reinterpret_cast<uint32_t *>(q8_s + (size_t)blk * Q8_STRIDE)[wd] = __ldg(reinterpret_cast<const uint32_t *>(src + Q8K_QS) + wd);
-    }
-    for (int i = tid; i < N * nb * 8; i += nt) {
-        const int blk = i >> 3, k = i & 7, n = blk / nb, b = blk - n * nb;
-        const int16_t *bs = reinterpret_cast<const int16_t *>(p.xq + n * p.xq_stride + (int64_t)b * BLK_Q8K + Q8K_BSUMS);
-        reinterpret_cast<int16_t *>(q8_s + (size_t)blk * Q8_STRIDE + 256)[k] = (int16_t)(bs[2 * k] + bs[2 * k + 1]);   // hadd_epi16
-    }
-    for (int i = tid; i < N * nb; i += nt) {
-        const int n = i / nb, b = i - n * nb;
-        d_s[i] = *reinterpret_cast<const float *>(p.xq + n * p.xq_stride + (int64_t)b * BLK_Q8K);
-    }
-}
-
 template <int N, bool EXACT>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, 2)
 gemv_q4k_tma_kernel(const TmaGemvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int nb = p.nb, S = p.stages;
@@ -130,7 +170,6 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
         for (int s = 0; s < S; ++s) mbar_init(smem_u32(&bars[s]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    stage_activations<N>(p, q8_s, d_s);
     __syncthreads();
 
     // ---- producer state (warp-uniform) ----
@@ -150,7 +189,7 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
         if (exhausted) {
             if (lane == 0) {
                 meta[s] = make_int2(-1, 0);
-                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+                mbar_arrive(bar);
             }
             return;
         }
@@ -158,40 +197,56 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
         const uint32_t bytes = (uint32_t)nsb * BLK_Q4K;
         if (lane == 0) {
             meta[s] = make_int2((int)cur_rg, prod_ks);
-            fence_proxy_async();                      // our generic reads of this stage are done (after __syncwarp)
             mbar_expect_tx(bar, bytes * TILE_ROWS);
         }
         __syncwarp();
         if (lane < TILE_ROWS) {
             int64_t row = cur_rg * TILE_ROWS + lane;
             if (row >= p.M) row = p.M - 1;            // ragged last group: stay in bounds, result is not stored
+            fence_proxy_async();                      // the warp's generic reads of this slot are done (after __syncwarp)
             bulk_g2s(smem_u32(wbuf + (size_t)s * STAGE_BYTES + lane * ROW_BYTES),
                      p.w + row * p.w_stride + (int64_t)prod_ks * ROW_BYTES, bytes, bar);
         }
         ++prod_ks;
     };
 
+    // weights never depend on the previous kernel in the stream: get them moving before the dependency wait
     for (int s = 0; s < S; ++s) produce(s);
+    griddep_launch_dependents();
+    griddep_wait();
+    if (p.xq) stage_q8<N>(p, q8_s, d_s);
+    else stage_f32<N>(p, q8_s, d_s);
+    __syncthreads();
 
     float acc[N], accm[N];
 #pragma unroll
     for (int n = 0; n < N; ++n) { acc[n] = 0.0f; accm[n] = 0.0f; }
 
-    for (int it = 0;; ++it) {
-        const int s = it % S;
-        mbar_wait(smem_u32(&bars[s]), (uint32_t)((it / S) & 1));
+    int s = 0;
+    uint32_t parity = 0;
+    for (;;) {
+        mbar_wait(smem_u32(&bars[s]), parity);
         const int2 mt = meta[s];
         if (mt.x < 0) break;
         const int ks = mt.y;
         const int nsb = min(TILE_SB, nb - ks * TILE_SB);
-        const uint8_t *wst = wbuf + (size_t)s * STAGE_BYTES;
+        const bool active = b < nsb;
 
-        if (b < nsb) {
-            const uint8_t *blk = wst + r * ROW_BYTES + b * BLK_Q4K;
+        // the lane's superblock: shared memory -> registers, then the slot goes back to the copy engine
+        uint4 hdr, q[8];
+        {
+            const uint8_t *blk = wbuf + (size_t)s * STAGE_BYTES + r * ROW_BYTES + (active ? b : 0) * BLK_Q4K;
+            hdr = lds128(blk);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) q[i] = lds128(blk + 16 + 16 * i);
+        }
+        __syncwarp();
+        produce(s);
+
+        if (active) {
             const int kb = ks * TILE_SB + b;
-            const uint4 hdr = lds128(blk);
             const uint4 sm = unpack_scales_mins(hdr);
-            const float xd = header_d(hdr), xdm = header_dmin(hdr);
+            const float2 dd = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));   // {d, dmin}
             int sum16[N][EXACT ? 8 : 1];
 #pragma unroll
             for (int n = 0; n < N; ++n)
@@ -199,10 +254,10 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
                 for (int t = 0; t < (EXACT ? 8 : 1); ++t) sum16[n][t] = 0;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-                const uint4 qa = lds128(blk + 16 + 32 * g), qb = lds128(blk + 32 + 32 * g);
-                const uint32_t q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
-                const uint32_t scp = byte_pair(sm.x, sm.y, g);
-                const int sc_lo16 = (int)((scp & 0xffu) << 4), sc_hi = (int)(scp >> 8);
+                const uint32_t qw[8] = {q[2 * g].x, q[2 * g].y, q[2 * g].z, q[2 * g].w,
+                                        q[2 * g + 1].x, q[2 * g + 1].y, q[2 * g + 1].z, q[2 * g + 1].w};
+                const uint32_t scw = (g < 2 ? sm.x : sm.y) >> (16 * (g & 1));
+                const int sc_lo16 = (int)((scw & 0xffu) << 4), sc_hi = (int)((scw >> 8) & 0xffu);
 #pragma unroll
                 for (int n = 0; n < N; ++n) {
                     const uint8_t *yb = q8_s + (size_t)(n * nb + kb) * Q8_STRIDE + 64 * g;
@@ -212,16 +267,16 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
                     if (EXACT) {
 #pragma unroll
                         for (int t = 0; t < 8; ++t) {
-                            const int dl = __dp4a((int)(q[t] & 0x0f0f0f0fu), (int)ylo[t], 0);
-                            const int dh = dp4a_u8s8(q[t] & 0xf0f0f0f0u, yhi[t], 0);
+                            const int dl = __dp4a((int)(qw[t] & 0x0f0f0f0fu), (int)ylo[t], 0);
+                            const int dh = dp4a_u8s8(qw[t] & 0xf0f0f0f0u, yhi[t], 0);
                             sum16[n][t] += sc_lo16 * dl + sc_hi * dh;
                         }
                     } else {
                         int pl = 0, ph = 0;
 #pragma unroll
                         for (int t = 0; t < 8; ++t) {
-                            pl = __dp4a((int)(q[t] & 0x0f0f0f0fu), (int)ylo[t], pl);
-                            ph = dp4a_u8s8(q[t] & 0xf0f0f0f0u, yhi[t], ph);
+                            pl = __dp4a((int)(qw[t] & 0x0f0f0f0fu), (int)ylo[t], pl);
+                            ph = dp4a_u8s8(qw[t] & 0xf0f0f0f0u, yhi[t], ph);
                         }
                         sum16[n][0] += sc_lo16 * pl + sc_hi * ph;
                     }
@@ -229,21 +284,19 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
             }
 #pragma unroll
             for (int n = 0; n < N; ++n) {
-                const uint8_t *yblk = q8_s + (size_t)(n * nb + kb) * Q8_STRIDE;
-                const uint4 ps = lds128(yblk + 256);
+                const uint4 ps = lds128(q8_s + (size_t)(n * nb + kb) * Q8_STRIDE + 256);
                 const float yd = d_s[n * nb + kb];
-                const float dall = __fmul_rn(yd, xd), dmn = __fmul_rn(-yd, xdm);
-                const int p0 = __dp2a_lo((int)ps.x, (int)byte_pair(sm.z, sm.w, 0), 0);
-                const int p1 = __dp2a_lo((int)ps.y, (int)byte_pair(sm.z, sm.w, 1), 0);
-                const int p2 = __dp2a_lo((int)ps.z, (int)byte_pair(sm.z, sm.w, 2), 0);
-                const int p3 = __dp2a_lo((int)ps.w, (int)byte_pair(sm.z, sm.w, 3), 0);
+                const float dall = __fmul_rn(yd, dd.x), dmn = __fmul_rn(-yd, dd.y);
+                // _mm_madd_epi16(mins, hadd(bsums)): prod_i = m[2i] * ps[2i] + m[2i+1] * ps[2i+1]
+                const int p0 = __dp2a_lo((int)ps.x, (int)sm.z, 0), p1 = __dp2a_hi((int)ps.y, (int)sm.z, 0);
+                const int p2 = __dp2a_lo((int)ps.z, (int)sm.w, 0), p3 = __dp2a_hi((int)ps.w, (int)sm.w, 0);
                 if (EXACT) {
-                    int4 *dstw = reinterpret_cast<int4 *>(scratch + n * SCR_WORDS + (r * 8 + b) * 20 + r * 8);
-                    dstw[0] = make_int4(sum16[n][0] >> 4, sum16[n][1] >> 4, sum16[n][2] >> 4, sum16[n][3] >> 4);
-                    dstw[1] = make_int4(sum16[n][4 % (EXACT ? 8 : 1)] >> 4, sum16[n][5 % (EXACT ? 8 : 1)] >> 4,
-                                        sum16[n][6 % (EXACT ? 8 : 1)] >> 4, sum16[n][7 % (EXACT ? 8 : 1)] >> 4);
-                    dstw[2] = make_int4(p0, p1, p2, p3);
-                    dstw[3] = make_int4(__float_as_int(dall), __float_as_int(dmn), 0, 0);
+                    int *row = scratch + n * SCR_WORDS + r * SCR_ROW;
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) row[t * 8 + (t & 4) + b] = sum16[n][t % (EXACT ? 8 : 1)] >> 4;
+                    row[68 + b] = p0; row[76 + b] = p1; row[84 + b] = p2; row[92 + b] = p3;
+                    row[100 + b] = __float_as_int(dall);
+                    row[108 + b] = __float_as_int(dmn);
                 } else {
                     acc[n] = __fmaf_rn(dall, (float)(sum16[n][0] >> 4), acc[n]);
                     accm[n] = __fmaf_rn(dmn, (float)(p0 + p1 + p2 + p3), accm[n]);
@@ -255,11 +308,23 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
             // chain phase: lane (r, t = b) walks the superblocks of row r in order, as the AVX2 loop does
 #pragma unroll
             for (int n = 0; n < N; ++n) {
-                const int *row_scr = scratch + n * SCR_WORDS + r * 8 * 20 + r * 8;
-                for (int bb = 0; bb < nsb; ++bb) {
-                    const int *e = row_scr + bb * 20;
-                    acc[n] = __fmaf_rn(__int_as_float(e[12]), (float)e[b], acc[n]);
-                    accm[n] = __fmaf_rn(__int_as_float(e[13]), (float)e[8 + (b & 3)], accm[n]);
+                const int *row = scratch + n * SCR_WORDS + r * SCR_ROW;
+                const int4 s0 = *reinterpret_cast<const int4 *>(row + b * 8 + (b & 4));
+                const int4 s1 = *reinterpret_cast<const int4 *>(row + b * 8 + (b & 4) + 4);
+                const int4 m0 = *reinterpret_cast<const int4 *>(row + 68 + (b & 3) * 8);
+                const int4 m1 = *reinterpret_cast<const int4 *>(row + 68 + (b & 3) * 8 + 4);
+                const float4 da0 = *reinterpret_cast<const float4 *>(row + 100), da1 = *reinterpret_cast<const float4 *>(row + 104);
+                const float4 dm0 = *reinterpret_cast<const float4 *>(row + 108), dm1 = *reinterpret_cast<const float4 *>(row + 112);
+                const int sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+                const int mv[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+                const float da[8] = {da0.x, da0.y, da0.z, da0.w, da1.x, da1.y, da1.z, da1.w};
+                const float dm[8] = {dm0.x, dm0.y, dm0.z, dm0.w, dm1.x, dm1.y, dm1.z, dm1.w};
+#pragma unroll
+                for (int bb = 0; bb < 8; ++bb) {
+                    if (bb < nsb) {
+                        acc[n] = __fmaf_rn(da[bb], (float)sv[bb], acc[n]);
+                        accm[n] = __fmaf_rn(dm[bb], (float)mv[bb], accm[n]);
+                    }
                 }
             }
         }
@@ -285,8 +350,7 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
                 acc[n] = 0.0f; accm[n] = 0.0f;
             }
         }
-        __syncwarp();
-        produce(s);
+        if (++s == S) { s = 0; parity ^= 1u; }
     }
 }
 
@@ -307,18 +371,14 @@ size_t fixed_smem(int N, int nb, bool exact) {
 constexpr size_t PER_STAGE = (size_t)WARPS * (STAGE_BYTES + 16);
 
 template <int N, bool EXACT>
-cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, cudaStream_t stream) {
+cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
     auto kern = gemv_q4k_tma_kernel<N, EXACT>;
     const size_t fixed = fixed_smem(N, p.nb, EXACT);
-    if (fixed + 2 * PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
-    int stages = want_stages;
-    if (stages <= 0) {
-        // two CTAs per SM with 2-3 stages when the activations are small, else one CTA with up to 4
-        const size_t half = SMEM_MAX / 2 - 1024;
-        if (fixed + 2 * PER_STAGE <= half) stages = (fixed + 3 * PER_STAGE <= half) ? 3 : 2;
-        else stages = (int)((SMEM_MAX - fixed) / PER_STAGE) > 4 ? 4 : (int)((SMEM_MAX - fixed) / PER_STAGE);
-    }
-    while (stages > 2 && fixed + stages * PER_STAGE > SMEM_MAX) --stages;
+    if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
+    // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits
+    int stages = want_stages > 0 ? want_stages : 2;
+    while (stages > 1 && 2 * (fixed + stages * PER_STAGE + 1024) > SMEM_MAX) --stages;
+    if (fixed + stages * PER_STAGE > SMEM_MAX) stages = (int)((SMEM_MAX - fixed) / PER_STAGE);
     p.stages = stages;
     const size_t smem = fixed + stages * PER_STAGE;
     static bool attr_set = false;
@@ -327,46 +387,58 @@ cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, cudaStream_t stream) 
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    int per_sm = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, smem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorNotSupported;
+    int per_sm = (2 * (smem + 1024) <= SMEM_MAX) ? 2 : 1;
     int64_t grid = (int64_t)sm_count() * per_sm;
-    if (grid > p.n_groups) grid = p.n_groups;
-    kern<<<(unsigned)grid, WARPS * 32, smem, stream>>>(p);
+    if (grid > p.n_groups) grid = p.n_groups;        // small matrices: at least one 4-row group per CTA
+    if (grid < 1) grid = 1;
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(WARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 template <bool EXACT>
-cudaError_t launch_tma_e(int N, const TmaGemvParams &p, int stages, cudaStream_t st) {
+cudaError_t launch_tma_e(int N, const TmaGemvParams &p, int stages, bool pdl, cudaStream_t st) {
     switch (N) {
-        case 1: return launch_tma_n<1, EXACT>(p, stages, st);
-        case 2: return launch_tma_n<2, EXACT>(p, stages, st);
-        case 3: return launch_tma_n<3, EXACT>(p, stages, st);
-        case 4: return launch_tma_n<4, EXACT>(p, stages, st);
-        case 5: return launch_tma_n<5, EXACT>(p, stages, st);
-        case 6: return launch_tma_n<6, EXACT>(p, stages, st);
-        case 7: return launch_tma_n<7, EXACT>(p, stages, st);
-        case 8: return launch_tma_n<8, EXACT>(p, stages, st);
+        case 1: return launch_tma_n<1, EXACT>(p, stages, pdl, st);
+        case 2: return launch_tma_n<2, EXACT>(p, stages, pdl, st);
+        case 3: return launch_tma_n<3, EXACT>(p, stages, pdl, st);
+        case 4: return launch_tma_n<4, EXACT>(p, stages, pdl, st);
+        case 5: return launch_tma_n<5, EXACT>(p, stages, pdl, st);
+        case 6: return launch_tma_n<6, EXACT>(p, stages, pdl, st);
+        case 7: return launch_tma_n<7, EXACT>(p, stages, pdl, st);
+        case 8: return launch_tma_n<8, EXACT>(p, stages, pdl, st);
         default: return cudaErrorInvalidValue;
     }
 }
 
 }  // namespace
 
+// xq != nullptr: activations are Q8_K blocks (x_row_stride_bytes between rows); else xf: F32 rows, quantized
+// inside the kernel.  pdl: launch with programmatic stream serialization (the kernel waits for its
+// predecessor only before it touches the activations).
 cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
-                                    const void *xq, int N, int64_t xq_row_stride_bytes,
+                                    const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
-                                    cudaStream_t stream) {
+                                    bool pdl, cudaStream_t stream) {
     if (M == 0 || N == 0) return cudaSuccess;
     TmaGemvParams p;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
-    p.xq = (const uint8_t *)xq; p.xq_stride = xq_row_stride_bytes;
+    p.xq = (const uint8_t *)xq; p.xf = xf; p.x_stride = x_row_stride_bytes;
     p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
     p.n_groups = (M + TILE_ROWS - 1) / TILE_ROWS;
     p.stages = 0;
-    return exact_order ? launch_tma_e<true>(N, p, stages, stream) : launch_tma_e<false>(N, p, stages, stream);
+    return exact_order ? launch_tma_e<true>(N, p, stages, pdl, stream) : launch_tma_e<false>(N, p, stages, pdl, stream);
 }
 
 }  // namespace q4k

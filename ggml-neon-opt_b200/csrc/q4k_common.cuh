@@ -66,4 +66,53 @@ __device__ __forceinline__ int nearest_int(float f) {
     return (int)(__float_as_uint(shifted) & 0x7fffffu) - 0x400000;
 }
 
+// One 256-float block of quantize_row_q8_K_ref (L/ggml/src/ggml-quants.c:2555-2592) on one warp.  Lane l
+// holds floats [4l, 4l+4) and [128+4l, 128+4l+4) in v[0..3], v[4..7].  Every float operation is an explicit
+// single-rounding intrinsic (no FMA contraction possible):
+//   absmax : per-lane scan in index order (strict '>'), then a butterfly that prefers the larger |x| and, on
+//            ties, the smaller index == "first occurrence wins" of the scalar loop
+//   iscale : __fdiv_rn(-127, max)            d : __fdiv_rn(1, iscale)
+//   q      : min(127, nearest_int(__fmul_rn(iscale, x)))
+// Returns d; w_lo / w_hi = the lane's two packed int8x4 words (qs words l and 32 + l); s_lo / s_hi = bsums
+// of the 16-element groups l/4 and 8 + l/4 (valid in every lane of the group).  All-zero block: d = 0, q = 0
+// and zero bsums (the reference leaves bsums unwritten there, :2568-2573).
+__device__ __forceinline__ float quantize_block_q8_K(const float (&v)[8], int lane, uint32_t &w_lo, uint32_t &w_hi,
+                                                     int &s_lo, int &s_hi) {
+    float amax = 0.0f, smax = 0.0f;
+    int idx = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float ax = fabsf(v[i]);
+        if (ax > amax) { amax = ax; smax = v[i]; idx = (i < 4 ? 4 * lane + i : 128 + 4 * lane + (i - 4)); }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const float oa = __shfl_xor_sync(0xffffffffu, amax, off);
+        const float os = __shfl_xor_sync(0xffffffffu, smax, off);
+        const int   oi = __shfl_xor_sync(0xffffffffu, idx, off);
+        if (oa > amax || (oa == amax && oi < idx)) { amax = oa; smax = os; idx = oi; }
+    }
+    int q[8];
+    float d_out;
+    if (amax == 0.0f) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = 0;
+        d_out = 0.0f;
+    } else {
+        const float iscale = __fdiv_rn(-127.0f, smax);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = min(127, nearest_int(__fmul_rn(iscale, v[i])));
+        d_out = __fdiv_rn(1.0f, iscale);
+    }
+    w_lo = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
+    w_hi = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+    s_lo = q[0] + q[1] + q[2] + q[3];
+    s_hi = q[4] + q[5] + q[6] + q[7];
+    s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 1);
+    s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 1);
+    s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 2);
+    s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 2);
+    return d_out;
+}
+
 }  // namespace q4k

@@ -16,12 +16,13 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                 const void *xq, int N, int64_t xq_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, bool exact_order, cudaStream_t stream);
 
-// the TMA-bulk staged implementation (gemv_q4k_tma.cu); stages <= 0 = choose; cudaErrorNotSupported if the
-// Q8_K activations do not fit in shared memory
+// the TMA-bulk staged implementation (gemv_q4k_tma.cu).  Activations: xq (Q8_K blocks) or, when xq == nullptr,
+// xf (F32 rows, quantized inside the kernel).  stages <= 0 = choose; pdl = programmatic dependent launch.
+// cudaErrorNotSupported if the Q8_K activations do not fit in shared memory.
 cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
-                                    const void *xq, int N, int64_t xq_row_stride_bytes,
+                                    const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
-                                    cudaStream_t stream);
+                                    bool pdl, cudaStream_t stream);
 
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
@@ -33,6 +34,7 @@ cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride
                                   int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);
 
 extern int g_gemv_config;   // development knob, see gemv_q4k.cu
+extern int g_gemv_pdl;      // 1 = launch the GEMV with programmatic stream serialization (default)
 int sm_count();               // multiprocessors of the current device (cached)
 
 }  // namespace q4k

@@ -31,52 +31,16 @@ quantize_q8_K_kernel(const float *__restrict__ x, uint8_t *__restrict__ y, int64
     const float4 b = __ldg(reinterpret_cast<const float4 *>(src) + 32 + lane);
     const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 
-    // per-lane first-occurrence absmax over indices 4l..4l+3 then 128+4l..128+4l+3 (ascending)
-    float amax = 0.0f, smax = 0.0f;
-    int idx = 0x7fffffff;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const float ax = fabsf(v[i]);
-        if (ax > amax) { amax = ax; smax = v[i]; idx = (i < 4 ? 4 * lane + i : 128 + 4 * lane + (i - 4)); }
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        const float oa = __shfl_xor_sync(0xffffffffu, amax, off);
-        const float os = __shfl_xor_sync(0xffffffffu, smax, off);
-        const int   oi = __shfl_xor_sync(0xffffffffu, idx, off);
-        if (oa > amax || (oa == amax && oi < idx)) { amax = oa; smax = os; idx = oi; }
-    }
-
-    int q[8];
-    float d_out;
-    if (amax == 0.0f) {                       // :2568-2573 (we also zero the bsums, see q4k_b200.h)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) q[i] = 0;
-        d_out = 0.0f;
-    } else {
-        const float iscale = __fdiv_rn(-127.0f, smax);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) q[i] = min(127, nearest_int(__fmul_rn(iscale, v[i])));
-        d_out = __fdiv_rn(1.0f, iscale);
-    }
-
-    auto pack4 = [](int q0, int q1, int q2, int q3) -> uint32_t {
-        return (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
-    };
+    uint32_t w_lo, w_hi;
+    int s_lo, s_hi;
+    const float d_out = quantize_block_q8_K(v, lane, w_lo, w_hi, s_lo, s_hi);
     uint32_t *qs = reinterpret_cast<uint32_t *>(dst + Q8K_QS);
-    qs[lane]      = pack4(q[0], q[1], q[2], q[3]);
-    qs[32 + lane] = pack4(q[4], q[5], q[6], q[7]);
-
-    int s_lo = q[0] + q[1] + q[2] + q[3];     // group (4l)/16     = l/4
-    int s_hi = q[4] + q[5] + q[6] + q[7];     // group 8 + l/4
-    s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 1);
-    s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 1);
-    s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 2);
-    s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 2);
+    qs[lane]      = w_lo;
+    qs[32 + lane] = w_hi;
     int16_t *bsums = reinterpret_cast<int16_t *>(dst + Q8K_BSUMS);
     if ((lane & 3) == 0) {
-        bsums[lane >> 2]       = (int16_t)s_lo;
-        bsums[8 + (lane >> 2)] = (int16_t)s_hi;
+        bsums[lane >> 2]       = (int16_t)s_lo;     // group (4l)/16 = l/4
+        bsums[8 + (lane >> 2)] = (int16_t)s_hi;     // group 8 + l/4
     }
     if (lane == 0) *reinterpret_cast<float *>(dst) = d_out;
 }

@@ -83,6 +83,12 @@ int q4k_debug_set_gemv_order(int mode);
 /* development knob: 0 = launch heuristic, 1.. = force a compiled GEMV tile shape (gemv_q4k.cu) */
 int q4k_debug_set_gemv_config(int cfg);
 
+/* development knob: largest N*K (floats) for which q4k_mul_mat fuses quantize_row_q8_K into the GEMV launch
+ * (default 32768); 0 = always run the quantizer as its own kernel. */
+int q4k_debug_set_fuse_limit(int64_t n_floats);
+/* development knob: 1 (default) = GEMV launches use programmatic dependent launch, 0 = plain stream order */
+int q4k_debug_set_pdl(int on);
+
 /* host-buffer convenience used by the plugin's e2e path and bench.py's e2e leg: copies x (pinned or
  * pageable host) to the device, runs q4k_mul_mat, copies dst back.  Weights stay resident (w_dev).
  * Synchronous. */
