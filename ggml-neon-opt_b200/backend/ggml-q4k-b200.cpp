@@ -1,0 +1,459 @@
+// ggml-q4k-b200.cpp — out-of-tree ggml backend plugin ("Q4K_B200") for NVIDIA B200.
+//
+// Claims exactly one operation: GGML_OP_MUL_MAT with GGML_TYPE_Q4_K src0, F32 src1, F32 dst — the path
+// ggml_compute_forward_mul_mat -> quantize_row_q8_K -> ggml_vec_dot_q4_K_q8_K of the CPU backend
+// (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401).  Everything else stays on whichever backend the scheduler picks.
+// There is no fallback to ggml-cpu or ggml-cuda in here: a node this backend accepted either runs on the
+// sm_100a kernels behind include/q4k_b200.h or graph_compute returns GGML_STATUS_FAILED.
+//
+// Loaded through the reference's own mechanism: ggml_backend_load(path) / env GGML_BACKEND_PATH
+// (L/ggml/src/ggml-backend-reg.cpp:247-291, 603-607) -> ggml_backend_score() -> ggml_backend_init().
+// Implements the vtables of L/ggml/src/ggml-backend-impl.h (API version 2): reg_i (:198-208), device_i
+// (:140-184), buffer_type_i (:17-35), buffer_i (:41-58), backend_i (:90-126).  Shape of a one-op backend
+// follows the role ggml-blas plays in the tree (L/ggml/src/ggml-blas/ggml-blas.cpp:227-518); none of its code
+// is reused.
+//
+// This file is plain C++ (no CUDA headers): device memory, copies, streams and the kernels are reached
+// through the C ABI of libq4k_b200.so only.
+#include "ggml-backend-impl.h"
+#include "ggml-impl.h"
+#include "ggml.h"
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/q4k_b200.h"
+
+namespace {
+
+constexpr size_t Q4K_TENSOR_ALIGN = 128;    // every tensor starts 128-byte aligned: 16 B loads / bulk copies are safe
+
+struct reg_context;
+
+struct device_context {
+    int         cuda_device = 0;
+    std::string name;           // "Q4K_B200_0"
+    std::string description;    // "NVIDIA B200 (148 SMs)"
+    ggml_backend_buffer_type buft{};
+};
+
+struct buffer_context {
+    int    cuda_device;
+    void * base;
+};
+
+struct backend_context {
+    device_context * dev;
+    void *  stream    = nullptr;
+    void *  workspace = nullptr;     // Q8_K copy of src1: the analogue of params->wdata (ggml-cpu.c:1267-1307)
+    size_t  workspace_bytes = 0;
+};
+
+std::vector<ggml_backend_device> & devices() {
+    static std::vector<ggml_backend_device> d;
+    return d;
+}
+std::vector<device_context> & device_contexts() {
+    static std::vector<device_context> d;
+    return d;
+}
+
+// ------------------------------------------------------------------------------------------ buffer
+void buffer_free(ggml_backend_buffer_t buffer) {
+    auto * ctx = (buffer_context *) buffer->context;
+    q4k_mem_free(ctx->cuda_device, ctx->base);
+    delete ctx;
+}
+
+void * buffer_get_base(ggml_backend_buffer_t buffer) {
+    return ((buffer_context *) buffer->context)->base;
+}
+
+void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
+    auto * ctx = (buffer_context *) buffer->context;
+    if (q4k_mem_set(ctx->cuda_device, (char *) tensor->data + offset, value, size, nullptr) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: memset_tensor failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    auto * ctx = (buffer_context *) buffer->context;
+    if (q4k_mem_h2d(ctx->cuda_device, (char *) tensor->data + offset, data, size, nullptr) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: set_tensor failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    auto * ctx = (buffer_context *) buffer->context;
+    if (q4k_mem_d2h(ctx->cuda_device, data, (const char *) tensor->data + offset, size, nullptr) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: get_tensor failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+bool buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_tensor * dst) {
+    auto * ctx = (buffer_context *) buffer->context;
+    if (!src->buffer) return false;
+    if (ggml_backend_buffer_is_host(src->buffer)) {
+        return q4k_mem_h2d(ctx->cuda_device, dst->data, src->data, ggml_nbytes(src), nullptr) == Q4K_OK;
+    }
+    if (src->buffer->iface.get_base == buffer_get_base &&
+        ((buffer_context *) src->buffer->context)->cuda_device == ctx->cuda_device) {
+        return q4k_mem_d2d(ctx->cuda_device, dst->data, src->data, ggml_nbytes(src), nullptr) == Q4K_OK;
+    }
+    return false;       // the caller falls back to get_tensor + set_tensor through host memory
+}
+
+void buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    auto * ctx = (buffer_context *) buffer->context;
+    if (q4k_mem_set(ctx->cuda_device, ctx->base, value, buffer->size, nullptr) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: clear failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+const ggml_backend_buffer_i buffer_iface = {
+    /* .free_buffer   = */ buffer_free,
+    /* .get_base      = */ buffer_get_base,
+    /* .init_tensor   = */ nullptr,
+    /* .memset_tensor = */ buffer_memset_tensor,
+    /* .set_tensor    = */ buffer_set_tensor,
+    /* .get_tensor    = */ buffer_get_tensor,
+    /* .cpy_tensor    = */ buffer_cpy_tensor,
+    /* .clear         = */ buffer_clear,
+    /* .reset         = */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------ buffer type
+const char * buft_get_name(ggml_backend_buffer_type_t buft) {
+    return ((device_context *) buft->context)->name.c_str();
+}
+
+ggml_backend_buffer_t buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    auto * dev = (device_context *) buft->context;
+    void * base = q4k_mem_alloc(dev->cuda_device, size + Q4K_TENSOR_ALIGN);
+    if (!base) {
+        GGML_LOG_ERROR("Q4K_B200: failed to allocate %zu bytes on device %d (cudaError %d)\n", size, dev->cuda_device, q4k_last_cuda_error());
+        return nullptr;                                   // the caller treats NULL as out-of-memory
+    }
+    auto * ctx = new buffer_context{dev->cuda_device, base};
+    return ggml_backend_buffer_init(buft, buffer_iface, ctx, size);
+}
+
+size_t buft_get_alignment(ggml_backend_buffer_type_t) { return Q4K_TENSOR_ALIGN; }
+
+const ggml_backend_buffer_type_i buft_iface = {
+    /* .get_name       = */ buft_get_name,
+    /* .alloc_buffer   = */ buft_alloc_buffer,
+    /* .get_alignment  = */ buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ nullptr,
+    /* .is_host        = */ nullptr,
+};
+
+bool buft_is_ours(ggml_backend_buffer_type_t buft) { return buft && buft->iface.get_name == buft_get_name; }
+
+}  // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------------------------ backend (stream)
+const char * backend_get_name(ggml_backend_t) { return "Q4K_B200"; }
+
+void backend_free(ggml_backend_t backend) {
+    auto * ctx = (backend_context *) backend->context;
+    q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream);
+    q4k_mem_free(ctx->dev->cuda_device, ctx->workspace);
+    q4k_stream_destroy(ctx->dev->cuda_device, ctx->stream);
+    delete ctx;
+    delete backend;
+}
+
+void backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    auto * ctx = (backend_context *) backend->context;
+    if (q4k_mem_h2d(ctx->dev->cuda_device, (char *) tensor->data + offset, data, size, ctx->stream) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: set_tensor_async failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+void backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    auto * ctx = (backend_context *) backend->context;
+    if (q4k_mem_d2h(ctx->dev->cuda_device, data, (const char *) tensor->data + offset, size, ctx->stream) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: get_tensor_async failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+void backend_synchronize(ggml_backend_t backend) {
+    auto * ctx = (backend_context *) backend->context;
+    if (q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream) != Q4K_OK) {
+        GGML_ABORT("Q4K_B200: synchronize failed (cudaError %d)", q4k_last_cuda_error());
+    }
+}
+
+// the conditions under which this backend takes a MUL_MAT node (also the contract of supports_op)
+bool mul_mat_supported(const ggml_tensor * op) {
+    const ggml_tensor * src0 = op->src[0];
+    const ggml_tensor * src1 = op->src[1];
+    if (!src0 || !src1) return false;
+    if (src0->type != GGML_TYPE_Q4_K || src1->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (src0->ne[0] % Q4K_QK_K != 0 || src0->ne[0] != src1->ne[0]) return false;
+    // weights: whole block_q4_K rows, 16-byte aligned strides (144 = 9 x 16, so any stride made of rows is)
+    if (src0->nb[0] != Q4K_BLOCK_Q4K || src0->nb[1] < (size_t) (src0->ne[0] / Q4K_QK_K) * Q4K_BLOCK_Q4K) return false;
+    if ((src0->nb[1] | src0->nb[2] | src0->nb[3]) & 15) return false;
+    // activations: unit inner stride, 16-byte aligned row / batch strides (permuted src1 is declined)
+    if (src1->nb[0] != sizeof(float) || src1->nb[1] < (size_t) src1->ne[0] * sizeof(float)) return false;
+    if ((src1->nb[1] | src1->nb[2] | src1->nb[3]) & 15) return false;
+    // result: dense columns
+    if (op->nb[0] != sizeof(float) || op->nb[1] < (size_t) op->ne[0] * sizeof(float)) return false;
+    if ((op->nb[1] | op->nb[2] | op->nb[3]) & 3) return false;
+    // broadcast of src0 over dims 2 / 3 as in ggml_compute_forward_mul_mat (ggml-cpu.c:1142-1143)
+    if (src0->ne[2] == 0 || src0->ne[3] == 0) return false;
+    if (src1->ne[2] % src0->ne[2] != 0 || src1->ne[3] % src0->ne[3] != 0) return false;
+    // the weights must live in this backend's memory: tensor->data is a device pointer here
+    if (src0->buffer && !buft_is_ours(src0->buffer->buft)) return false;
+    return true;
+}
+
+ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
+    const ggml_tensor * src0 = node->src[0];
+    const ggml_tensor * src1 = node->src[1];
+    const int64_t K = src0->ne[0], M = src0->ne[1], N = src1->ne[1];
+    const int64_t ne02 = src0->ne[2], ne03 = src0->ne[3], ne12 = src1->ne[2], ne13 = src1->ne[3];
+    const int64_t r2 = ne12 / ne02, r3 = ne13 / ne03;
+    if (M == 0 || N == 0 || ne12 == 0 || ne13 == 0) return GGML_STATUS_SUCCESS;
+
+    const size_t need = q4k_mul_mat_workspace_bytes(K, N);
+    if (need > ctx->workspace_bytes) {
+        // grow-only scratch; in-flight kernels may still read the old one
+        if (q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream) != Q4K_OK) return GGML_STATUS_FAILED;
+        q4k_mem_free(ctx->dev->cuda_device, ctx->workspace);
+        ctx->workspace = q4k_mem_alloc(ctx->dev->cuda_device, need);
+        ctx->workspace_bytes = ctx->workspace ? need : 0;
+        if (!ctx->workspace) {
+            GGML_LOG_ERROR("Q4K_B200: cannot allocate %zu bytes of Q8_K workspace\n", need);
+            return GGML_STATUS_ALLOC_FAILED;
+        }
+    }
+    for (int64_t i13 = 0; i13 < ne13; ++i13) {
+        for (int64_t i12 = 0; i12 < ne12; ++i12) {
+            const int64_t i03 = i13 / r3, i02 = i12 / r2;
+            const char * w = (const char *) src0->data + i02 * src0->nb[2] + i03 * src0->nb[3];
+            const char * x = (const char *) src1->data + i12 * src1->nb[2] + i13 * src1->nb[3];
+            char * d = (char *) node->data + i12 * node->nb[2] + i13 * node->nb[3];
+            const int rc = q4k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
+                                       (float *) d, (int64_t) node->nb[1], ctx->workspace, ctx->workspace_bytes, ctx->stream);
+            if (rc != Q4K_OK) {
+                GGML_LOG_ERROR("Q4K_B200: q4k_mul_mat(%s) failed: rc=%d cudaError=%d\n", node->name, rc, q4k_last_cuda_error());
+                return GGML_STATUS_FAILED;
+            }
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    auto * ctx = (backend_context *) backend->context;
+    if (q4k_set_device(ctx->dev->cuda_device) != Q4K_OK) return GGML_STATUS_FAILED;
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        ggml_tensor * node = cgraph->nodes[i];
+        switch (node->op) {
+            case GGML_OP_MUL_MAT: {
+                if (!mul_mat_supported(node)) {
+                    GGML_ABORT("Q4K_B200: %s: MUL_MAT node outside the supports_op contract reached graph_compute", node->name);
+                }
+                const ggml_status st = compute_mul_mat(ctx, node);
+                if (st != GGML_STATUS_SUCCESS) return st;
+            } break;
+            case GGML_OP_NONE:
+            case GGML_OP_RESHAPE:
+            case GGML_OP_VIEW:
+            case GGML_OP_PERMUTE:
+            case GGML_OP_TRANSPOSE:
+                break;
+            default:
+                GGML_ABORT("Q4K_B200: unsupported op %s reached graph_compute", ggml_op_desc(node));
+        }
+    }
+    return GGML_STATUS_SUCCESS;         // asynchronous: results are complete after synchronize()
+}
+
+const ggml_backend_i backend_iface = {
+    /* .get_name           = */ backend_get_name,
+    /* .free               = */ backend_free,
+    /* .set_tensor_async   = */ backend_set_tensor_async,
+    /* .get_tensor_async   = */ backend_get_tensor_async,
+    /* .cpy_tensor_async   = */ nullptr,
+    /* .synchronize        = */ backend_synchronize,
+    /* .graph_plan_create  = */ nullptr,
+    /* .graph_plan_free    = */ nullptr,
+    /* .graph_plan_update  = */ nullptr,
+    /* .graph_plan_compute = */ nullptr,
+    /* .graph_compute      = */ backend_graph_compute,
+    /* .event_record       = */ nullptr,
+    /* .event_wait         = */ nullptr,
+    /* .graph_optimize     = */ nullptr,
+};
+
+ggml_guid_t backend_guid() {
+    static ggml_guid guid = {0x51, 0x34, 0x4b, 0x5f, 0x42, 0x32, 0x30, 0x30, 0x9a, 0x10, 0x0a, 0x73, 0x6d, 0x31, 0x30, 0x30};
+    return &guid;
+}
+
+}  // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------------------------ device
+const char * device_get_name(ggml_backend_dev_t dev) { return ((device_context *) dev->context)->name.c_str(); }
+const char * device_get_description(ggml_backend_dev_t dev) { return ((device_context *) dev->context)->description.c_str(); }
+
+void device_get_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    auto * ctx = (device_context *) dev->context;
+    size_t f = 0, t = 0;
+    q4k_device_info(ctx->cuda_device, nullptr, 0, &f, &t, nullptr);
+    *free = f;
+    *total = t;
+}
+
+enum ggml_backend_dev_type device_get_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+
+ggml_backend_buffer_type_t device_get_buffer_type(ggml_backend_dev_t dev) {
+    return &((device_context *) dev->context)->buft;
+}
+
+void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
+    props->name        = device_get_name(dev);
+    props->description = device_get_description(dev);
+    props->type        = device_get_type(dev);
+    device_get_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps = {
+        /* .async                = */ true,
+        /* .host_buffer          = */ false,
+        /* .buffer_from_host_ptr = */ false,
+        /* .events               = */ false,
+    };
+}
+
+ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char *) {
+    auto * dctx = (device_context *) dev->context;
+    void * stream = q4k_stream_create(dctx->cuda_device);
+    if (!stream) {
+        GGML_LOG_ERROR("Q4K_B200: cannot create a stream on device %d (cudaError %d)\n", dctx->cuda_device, q4k_last_cuda_error());
+        return nullptr;
+    }
+    auto * ctx = new backend_context;
+    ctx->dev = dctx;
+    ctx->stream = stream;
+    return new ggml_backend{
+        /* .guid    = */ backend_guid(),
+        /* .iface   = */ backend_iface,
+        /* .device  = */ dev,
+        /* .context = */ ctx,
+    };
+}
+
+bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    switch (op->op) {
+        // test-backend-ops asks about every tensor of the context, leaves and views included
+        // (L/tests/test-backend-ops.cpp:1152-1161); these are no-ops for a backend
+        case GGML_OP_NONE:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_VIEW:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT:
+            return mul_mat_supported(op);
+        default:
+            return false;
+    }
+}
+
+bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    return buft_is_ours(buft) && buft->context == dev->context;
+}
+
+const ggml_backend_device_i device_iface = {
+    /* .get_name             = */ device_get_name,
+    /* .get_description      = */ device_get_description,
+    /* .get_memory           = */ device_get_memory,
+    /* .get_type             = */ device_get_type,
+    /* .get_props            = */ device_get_props,
+    /* .init_backend         = */ device_init_backend,
+    /* .get_buffer_type      = */ device_get_buffer_type,
+    /* .get_host_buffer_type = */ nullptr,
+    /* .buffer_from_host_ptr = */ nullptr,
+    /* .supports_op          = */ device_supports_op,
+    /* .supports_buft        = */ device_supports_buft,
+    /* .offload_op           = */ nullptr,
+    /* .event_new            = */ nullptr,
+    /* .event_free           = */ nullptr,
+    /* .event_synchronize    = */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------ registry
+const char * reg_get_name(ggml_backend_reg_t) { return "Q4K_B200"; }
+size_t reg_get_device_count(ggml_backend_reg_t) { return devices().size(); }
+ggml_backend_dev_t reg_get_device(ggml_backend_reg_t, size_t index) {
+    GGML_ASSERT(index < devices().size());
+    return &devices()[index];
+}
+void * reg_get_proc_address(ggml_backend_reg_t, const char *) { return nullptr; }
+
+const ggml_backend_reg_i reg_iface = {
+    /* .get_name         = */ reg_get_name,
+    /* .get_device_count = */ reg_get_device_count,
+    /* .get_device       = */ reg_get_device,
+    /* .get_proc_address = */ reg_get_proc_address,
+};
+
+int count_sm100_devices() {
+    int n = 0;
+    const int total = q4k_device_count();
+    for (int d = 0; d < total; ++d) n += q4k_device_ok(d) ? 1 : 0;
+    return n;
+}
+
+ggml_backend_reg_t q4k_b200_reg() {
+    static ggml_backend_reg reg = {
+        /* .api_version = */ GGML_BACKEND_API_VERSION,
+        /* .iface       = */ reg_iface,
+        /* .context     = */ nullptr,
+    };
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const int total = q4k_device_count();
+        auto & dctx = device_contexts();
+        dctx.reserve(total);                    // pointers into these vectors are handed out: never reallocate
+        for (int d = 0; d < total; ++d) {
+            if (!q4k_device_ok(d)) continue;    // sm_100 only: the kernels are compiled for sm_100a and nothing else
+            char name[256] = "";
+            int sms = 0;
+            q4k_device_info(d, name, sizeof name, nullptr, nullptr, &sms);
+            device_context c;
+            c.cuda_device = d;
+            c.name = "Q4K_B200_" + std::to_string(dctx.size());
+            c.description = std::string(name) + " (" + std::to_string(sms) + " SMs, " + q4k_build_info() + ")";
+            dctx.push_back(c);
+        }
+        auto & devs = devices();
+        devs.reserve(dctx.size());
+        for (auto & c : dctx) {
+            devs.push_back(ggml_backend_device{device_iface, &reg, &c});
+            c.buft = ggml_backend_buffer_type{buft_iface, &devs.back(), &c};
+        }
+        GGML_LOG_INFO("Q4K_B200: %zu sm_100 device(s); claims MUL_MAT(Q4_K, F32) only\n", devs.size());
+    });
+    return &reg;
+}
+
+}  // namespace
+
+// DL entry points (L/ggml/src/ggml-backend-impl.h:214-251); declared here without GGML_BACKEND_DL so the file
+// builds the same way in or out of the reference tree
+extern "C" {
+__attribute__((visibility("default"))) ggml_backend_reg_t ggml_backend_init(void) { return q4k_b200_reg(); }
+__attribute__((visibility("default"))) int ggml_backend_score(void) { return count_sm100_devices() > 0 ? 100 : 0; }
+}

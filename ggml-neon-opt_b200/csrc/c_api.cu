@@ -37,6 +37,7 @@ static int cuda_fail(cudaError_t e) {
     t_last_cuda_error = (int)e;
     return Q4K_ERR_CUDA;
 }
+int note_cuda_error(cudaError_t e) { return cuda_fail(e); }
 
 static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

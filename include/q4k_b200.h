@@ -44,6 +44,25 @@ int         q4k_device_ok(int device);             /* 1 if `device` is compute c
 int         q4k_last_cuda_error(void);             /* last cudaError_t seen by this library, per thread */
 int64_t     q4k_kernel_launches(void);             /* kernels launched by this library so far (process-wide) */
 
+/* device memory / streams for host code above this ABI that is compiled without CUDA headers (the ggml backend
+ * plugin: buffer_type_i.alloc_buffer, buffer_i.set_tensor / get_tensor / memset_tensor / clear / cpy_tensor and
+ * backend_i.synchronize of L/ggml/src/ggml-backend-impl.h:17-126).  All act on `device`; copies with a NULL
+ * stream are synchronous, with a stream they are queued on it (host memory should be pinned then). */
+int     q4k_device_count(void);                                        /* number of CUDA devices (plain ordinals; check each with q4k_device_ok) */
+int     q4k_device_info(int device, char *name, size_t name_len, size_t *free_bytes, size_t *total_bytes, int *sm_count);
+void   *q4k_mem_alloc(int device, size_t bytes);                       /* NULL on failure (q4k_last_cuda_error) */
+int     q4k_mem_free(int device, void *ptr_dev);
+int     q4k_mem_set(int device, void *dst_dev, int value, size_t bytes, void *stream);
+int     q4k_mem_h2d(int device, void *dst_dev, const void *src_host, size_t bytes, void *stream);
+int     q4k_mem_d2h(int device, void *dst_host, const void *src_dev, size_t bytes, void *stream);
+int     q4k_mem_d2d(int device, void *dst_dev, const void *src_dev, size_t bytes, void *stream);
+void   *q4k_host_alloc_pinned(size_t bytes);                           /* page-locked host memory for async copies */
+int     q4k_host_free_pinned(void *ptr_host);
+void   *q4k_stream_create(int device);                                 /* cudaStream_t as void*; NULL on failure */
+int     q4k_stream_destroy(int device, void *stream);
+int     q4k_stream_synchronize(int device, void *stream);
+int     q4k_set_device(int device);                                    /* makes `device` current for the calling thread */
+
 /* replaces quantize_row_q8_K (L/ggml/src/ggml-quants.c:2555-2592, bound as from_float of Q8_K at
  * L/ggml/src/ggml-cpu/ggml-cpu.c:355-357) for `nrows` rows of k floats; row r is read at
  * x_dev + r*x_row_stride_bytes and written to y_dev + r*(k/256*292).  Bit-exact, except that bsums of

@@ -1,0 +1,67 @@
+"""The ggml backend plugin (ggml-neon-opt_b200/lib/libggml-q4k-b200.so) driven by the UNMODIFIED reference:
+loaded through ggml_backend_load / GGML_BACKEND_PATH (L/ggml/src/ggml-backend-reg.cpp:247-291, 603-607), run by
+the reference's own graph API and by its own per-op harness test-backend-ops (L/tests/test-backend-ops.cpp),
+which compares every case with the reference CPU backend (NMSE <= 5e-4 for MUL_MAT, :3300-3302)."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import make_acts, make_weights
+from oracle import port, ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PLUGIN = os.path.join(ROOT, "ggml-neon-opt_b200", "lib", "libggml-q4k-b200.so")
+TBO = os.path.join(ROOT, "oracle", "_ref", "test-backend-ops")
+
+needs_ref = pytest.mark.skipif(not (ref.available() and os.path.exists(PLUGIN)), reason="oracle/_ref or the plugin not built")
+
+
+@needs_ref
+def test_plugin_exports_dl_entry_points():
+    out = subprocess.check_output(["nm", "-D", "--defined-only", PLUGIN], text=True)
+    assert " T ggml_backend_init" in out and " T ggml_backend_score" in out
+
+
+@needs_ref
+def test_plugin_scores_zero_without_sm100_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    w, x = make_weights(4, 256), make_acts(1, 256, adversarial=False)
+    with pytest.raises(RuntimeError, match="rc=-10"):      # ggml_backend_load refuses a backend whose score is 0
+        ref.plugin_mul_mat(PLUGIN, w, x)
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (300, 1024, 3), (128, 512, 16)])
+def test_plugin_graph_matches_reference_cpu_backend(M, K, N):
+    w, x = make_weights(M, K), make_acts(N, K)
+    got, _, _ = ref.plugin_mul_mat(PLUGIN, w, x)
+    cpu, _, _ = ref.mul_mat(w, x, n_threads=4)
+    if N <= 2:
+        assert np.array_equal(got.view(np.uint32), cpu.view(np.uint32))       # same float order as the AVX2 vec_dot
+    else:
+        f64 = port.mul_mat_f64(w, x)
+        rms = np.sqrt((f64 ** 2).mean(axis=1, keepdims=True))
+        assert np.all(np.abs(got - cpu) <= 1e-5 * np.maximum(np.abs(cpu), rms))
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_reference_test_backend_ops_mul_mat():
+    env = dict(os.environ, GGML_BACKEND_PATH=PLUGIN)
+    p = subprocess.run([TBO, "test", "-o", "MUL_MAT", "-b", "Q4K_B200_0"], env=env, capture_output=True, text=True, timeout=900)
+    out = p.stdout + p.stderr
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    open(os.path.join(ROOT, "gpurun_out", "test_backend_ops_mul_mat.log"), "w").write(out)
+    clean = re.sub(r"\x1b\[[0-9;]*m", "", out)
+    q4k_ok = [l for l in clean.splitlines() if "type_a=q4_K" in l and l.rstrip().endswith("OK")]
+    fails = [l for l in clean.splitlines() if "FAIL" in l]
+    assert p.returncode == 0, clean[-2000:]
+    assert not fails, fails[:5]
+    assert len(q4k_ok) >= 9, clean[-2000:]          # at least the m=16, n=1..9, k=256 sweep ran on the GPU
+    assert re.search(r"Backend Q4K_B200: OK", clean)
