@@ -44,6 +44,7 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 // Q4K_GEMV_ORDER=fast selects the cheaper float association for every batch size; default is the
 // reference's AVX2 order (bit-identical fp32) wherever the GEMV stays HBM-bound with it.
 static int64_t g_fuse_limit = 32768;   // N*K floats up to which the quantizer is fused into the GEMV launch
+static int g_gemm_enabled = 1;          // 0: N > 8 takes the decode kernel eight columns at a time (development)
 static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
 static bool gemv_exact_for(int N) {
     int &mode = g_order_mode;
@@ -87,6 +88,11 @@ int q4k_debug_set_gemv_config(int cfg) {
 
 int q4k_debug_set_fuse_limit(int64_t n_floats) {
     g_fuse_limit = n_floats;
+    return Q4K_OK;
+}
+
+int q4k_debug_set_gemm(int on) {
+    g_gemm_enabled = on ? 1 : 0;
     return Q4K_OK;
 }
 
@@ -171,6 +177,17 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
                                                           g_gemv_pdl != 0, (cudaStream_t)stream);
             if (e == cudaSuccess) return Q4K_OK;
             if (e != cudaErrorNotSupported) return cuda_fail(e);
+        }
+        // prefill shapes: planar Q8 quantizer + tensor-core GEMM (tcgen05 kind::i8)
+        if (N > Q4K_GEMV_MAX_N && g_gemm_enabled) {
+            if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
+            const int64_t nb = K / Q4K_QK_K;
+            if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (dst_col_stride_bytes < M * 4 || (dst_col_stride_bytes & 3) || !aligned16(workspace_dev)) return Q4K_ERR_BAD_SHAPE;
+            const cudaError_t e = launch_gemm_q4k_f32(w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev,
+                                                      dst_col_stride_bytes, workspace_dev, (cudaStream_t)stream);
+            return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
         }
         const int rc = q4k_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, stream);
         if (rc != Q4K_OK) return rc;

@@ -1,14 +1,373 @@
-// gemm_q4k_tc.cu — prefill GEMM (N > 8) on tcgen05 kind::i8 with TMEM accumulators.
-// Placeholder until the tensor-core kernel lands: reports "not supported" so the C ABI takes the
-// GEMV-per-8-columns route (same GPU arithmetic, not a CPU fallback).
+// gemm_q4k_tc.cu — prefill GEMM (batch > 8) on the 5th-generation tensor cores: tcgen05.mma kind::i8, TMEM accumulators.
+// dst[n][m] = sum_blk  d_x[n,blk] * ( d_w[m,blk] * sumi[m,n,blk]  -  dmin_w[m,blk] * summ[m,n,blk] )
+// which is ggml_compute_forward_mul_mat for Q4_K x F32 at ne11 = N (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401) with
+// the integer stage of ggml_vec_dot_q4_K_q8_K (L/ggml/src/ggml-cpu/quants.c:575-611) kept EXACT:
+//   sumi = sum_j sc[j] * p[j]        p[j] = sum_{l<32} q4[32j+l] * q8[32j+l]
+//   summ = sum_j m[j]  * (sum of the 32 q8 of sub-block j)
+//
+// How the per-sub-block 6-bit scales get through an int8 tensor core exactly.  sc <= 63 and q4 <= 15, so
+// sc*q4 needs 10 bits.  Split the SCALE, not the product:  sc = 8*sh + sl  (sh, sl <= 7).  Then sh*q4 and
+// sl*q4 are <= 105 and fit a signed byte, a packed multiply of four nibble-bytes by sh never carries between
+// bytes, and   sumi = 8 * (A_hi . q8) + (A_lo . q8)   with A_hi = sh*q4, A_lo = sl*q4 accumulated over the
+// whole 256-wide superblock in two TMEM accumulators.  The mins ride the tensor core too: summ = A_m . q8 with
+// A_m[k] = m[sub-block of k] (<= 63), a third accumulator.  One TMEM drain per superblock instead of one per
+// 32-wide sub-block; the fp32 scales d_w*d_x, dmin_w*d_x are applied by the epilogue warps per superblock,
+// sequentially over superblocks (the NEON order of the reference; within 1e-5 of the AVX2 oracle).
+//
+// CTA = 128 weight rows x 128 activation columns, 13 warps, warp-specialised:
+//   warps 0-7   epilogue: thread <-> TMEM lane (= weight row); warps 0-3 own columns 0-63, warps 4-7 columns
+//               64-127.  tcgen05.ld 16 columns x 3 accumulators at a time, 64 fp32 results per thread in registers.
+//   warps 8-11  producers: thread <-> weight row: loads its block_q4_K bytes (16 B loads), unpacks scales,
+//               writes the three int8 A tiles of half a superblock (K = 128) into shared memory in the canonical
+//               K-major no-swizzle UMMA layout (8-row x 16-byte core matrices); thread <-> column for the B tile.
+//   warp 12     allocates TMEM; one elected lane issues the MMAs (M = 128, N = 64, K = 32) and commits to mbarriers.
+// Pipelines: shared-memory ring of 3 stages (64 KB each: A_hi, A_lo, A_m, B) producers -> MMA; the two column
+// halves of the accumulators alternate between the tensor core and their epilogue group (MMA of half 1 overlaps
+// the drain of half 0).
+//
+// Activations arrive "planar" (quantize_q8_planar below): int8 qs[N][K] + float d[nb][Nld] — the same numbers
+// quantize_row_q8_K produces (bit-exact, shared device function), laid out so that tiles load with 16-byte
+// accesses (block_q8_K's 292-byte stride is only 4-byte aligned).  bsums are not needed: the mins use the MMA.
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
 namespace q4k {
 
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 128;          // CTA tile; BK = K bytes per pipeline stage (half a superblock)
+constexpr int HALF_N = 64;                            // columns per accumulator half / per MMA
+constexpr int STAGES = 3;
+constexpr int TILE_BYTES = BM * BK;                   // 16 KB: one int8 operand tile of a stage
+constexpr int STAGE_BYTES_TC = 4 * TILE_BYTES;        // A_hi, A_lo, A_m, B
+constexpr int EPI_WARPS = 8, PROD_WARPS = 4;
+constexpr int GEMM_THREADS = (EPI_WARPS + PROD_WARPS + 1) * 32;   // 416
+constexpr int TMEM_COLS = 512;                        // 3 accumulators x 128 columns, rounded to a power of two
+constexpr uint32_t SBO_BYTES = 8 * BK;                // 1024: next 8-row group of core matrices
+constexpr uint32_t LBO_BYTES = 128;                   // next 16-byte K chunk (core matrices of a row group are contiguous)
+
+struct GemmParams {
+    const uint8_t *w;
+    int64_t M, w_stride;
+    int nb;
+    const int8_t *xq;       // planar int8 [N][K]
+    const float *xd;        // [nb][Nld]
+    int64_t N, Nld;
+    float *dst;
+    int64_t dst_stride;     // floats between dst columns
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// shared-memory matrix descriptor, K-major, SWIZZLE_NONE ("interleave"): 8-row x 16-byte core matrices,
+// LBO = byte distance between the two 16-byte K chunks of one MMA, SBO = byte distance between 8-row groups
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3ffffu) >> 4);                    // start address, bits [0,14)
+    d |= (uint64_t)(LBO_BYTES >> 4) << 16;                       // leading byte offset, bits [16,30)
+    d |= (uint64_t)(SBO_BYTES >> 4) << 32;                       // stride byte offset, bits [32,46)
+    d |= (uint64_t)1 << 46;                                      // descriptor version 1 (sm_100)
+    return d;                                                    // base offset 0, layout type 0 = no swizzle
+}
+
+// instruction descriptor for kind::i8: D = S32, A = B = signed 8-bit, both K-major, M = 128, N = 64
+__device__ __forceinline__ uint32_t umma_idesc_i8() {
+    uint32_t d = 0;
+    d |= 2u << 4;                   // c_format: S32
+    d |= 1u << 7;                   // a_format: signed 8-bit
+    d |= 1u << 10;                  // b_format: signed 8-bit
+    d |= (uint32_t)(HALF_N >> 3) << 17;
+    d |= (uint32_t)(BM >> 4) << 24;
+    return d;
+}
+
+__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on the mbarrier when every MMA issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+}  // namespace
+
+namespace {
+
+__device__ __forceinline__ uint4 ldg16(const void *p) { return *reinterpret_cast<const uint4 *>(p); }
+
+struct ProdRegs {
+    uint4 hdr;
+    uint4 q[4];     // 64 bytes of nibbles: two 64-element groups
+    uint4 y[8];     // 128 int8 activations of this thread's column
+};
+
+__device__ __forceinline__ void producer_load(const GemmParams &p, const uint8_t *wrow, const int8_t *xcol, int step, ProdRegs &r) {
+    const int kb = step >> 1, hh = step & 1;
+    const uint8_t *blk = wrow + (int64_t)kb * BLK_Q4K;
+    r.hdr = ldg16(blk);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.q[i] = ldg16(blk + 16 + 64 * hh + 16 * i);
+    const int8_t *xs = xcol + (int64_t)kb * QK_K + 128 * hh;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r.y[i] = ldg16(xs + 16 * i);
+}
+
+// one thread = one weight row (A tiles) and one activation column (B tile) of a pipeline stage
+__device__ __forceinline__ void producer_store(uint8_t *stage, int t, int hh, const ProdRegs &r) {
+    const uint4 sm = unpack_scales_mins(r.hdr);
+    const uint32_t scw = hh ? sm.y : sm.x, mw = hh ? sm.w : sm.z;
+    uint8_t *row_base = stage + (t >> 3) * SBO_BYTES + (t & 7) * 16;
+#pragma unroll
+    for (int gi = 0; gi < 2; ++gi) {
+        const uint32_t qw[8] = {r.q[2 * gi].x, r.q[2 * gi].y, r.q[2 * gi].z, r.q[2 * gi].w,
+                                r.q[2 * gi + 1].x, r.q[2 * gi + 1].y, r.q[2 * gi + 1].z, r.q[2 * gi + 1].w};
+#pragma unroll
+        for (int nib = 0; nib < 2; ++nib) {             // 0: low nibbles = sub-block 2g, 1: high nibbles = sub-block 2g + 1
+            const uint32_t sc = (scw >> (16 * gi + 8 * nib)) & 0xffu, mn = (mw >> (16 * gi + 8 * nib)) & 0xffu;
+            const uint32_t sh = sc >> 3, sl = sc & 7u, mrep = mn * 0x01010101u;
+            uint32_t v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = (nib ? (qw[i] >> 4) : qw[i]) & 0x0f0f0f0fu;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {               // two 16-element K chunks per sub-block
+                uint8_t *dst = row_base + (4 * gi + 2 * nib + c) * LBO_BYTES;
+                *reinterpret_cast<uint4 *>(dst) = make_uint4(v[4 * c] * sh, v[4 * c + 1] * sh, v[4 * c + 2] * sh, v[4 * c + 3] * sh);
+                *reinterpret_cast<uint4 *>(dst + TILE_BYTES) = make_uint4(v[4 * c] * sl, v[4 * c + 1] * sl, v[4 * c + 2] * sl, v[4 * c + 3] * sl);
+                *reinterpret_cast<uint4 *>(dst + 2 * TILE_BYTES) = make_uint4(mrep, mrep, mrep, mrep);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4 *>(row_base + 3 * TILE_BYTES + i * LBO_BYTES) = r.y[i];
+}
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_q4k_tc_kernel(const GemmParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    float *dx_s = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES_TC);            // [half][buffer][64]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES_TC + 1024);
+    uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 16);
+    const uint32_t bar0 = smem_addr(bars);
+    auto full_bar = [&](int s) { return bar0 + 8u * s; };
+    auto empty_bar = [&](int s) { return bar0 + 8u * (3 + s); };
+    auto tfull_bar = [&](int h) { return bar0 + 8u * (6 + h); };
+    auto tempty_bar = [&](int h) { return bar0 + 8u * (8 + h); };
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+    const int nb = p.nb, nsteps = 2 * nb;
+    const int64_t K = (int64_t)nb * QK_K;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), PROD_WARPS * 32); mbar_init(empty_bar(s), 1); }
+        for (int h = 0; h < 2; ++h) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), 4 * 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == EPI_WARPS + PROD_WARPS) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_ptr_s)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_ptr_s;
+
+    if (warp < EPI_WARPS) {
+        // ===================== epilogue: TMEM -> registers, per-superblock fp32 scales =====================
+        const int qd = warp & 3, h = warp >> 2, tg = threadIdx.x & 127;       // lane quadrant, column half, thread in group
+        const int64_t row = m0 + 32 * qd + lane;
+        const uint8_t *wrow = p.w + (row < p.M ? row : p.M - 1) * p.w_stride;
+        float *dx = dx_s + h * 128;
+        int64_t ncl = n0 + 64 * h + (tg & 63);
+        if (ncl >= p.N) ncl = p.N - 1;
+        float acc[HALF_N];
+#pragma unroll
+        for (int i = 0; i < HALF_N; ++i) acc[i] = 0.0f;
+        uint32_t dd_next = *reinterpret_cast<const uint32_t *>(wrow);
+        if (tg < 64) dx[tg] = p.xd[ncl];                                       // superblock 0 -> buffer 0
+        const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(HALF_N * h);
+        for (int kb = 0; kb < nb; ++kb) {
+            const uint32_t dd = dd_next;
+            if (kb + 1 < nb) dd_next = *reinterpret_cast<const uint32_t *>(wrow + (int64_t)(kb + 1) * BLK_Q4K);
+            mbar_wait(tfull_bar(h), (uint32_t)(kb & 1));
+            tc_fence_after();
+            asm volatile("bar.sync %0, 128;" ::"r"(1 + h) : "memory");        // everyone is done with superblock kb - 1
+            if (tg < 64 && kb + 1 < nb) dx[((kb + 1) & 1) * 64 + tg] = p.xd[(int64_t)(kb + 1) * p.Nld + ncl];
+            const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));   // {d, dmin} of this row's superblock
+            const float *dxk = dx + (kb & 1) * 64;
+#pragma unroll
+            for (int c4 = 0; c4 < HALF_N / 16; ++c4) {
+                uint32_t vh[16], vl[16], vm[16];
+                tmem_ld16(tbase + 16 * c4, vh);
+                tmem_ld16(tbase + 128 + 16 * c4, vl);
+                tmem_ld16(tbase + 256 + 16 * c4, vm);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int sumi = 8 * (int)vh[i] + (int)vl[i];
+                    float t = __fmul_rn(dw.x, (float)sumi);
+                    t = __fmaf_rn(-dw.y, (float)(int)vm[i], t);
+                    acc[16 * c4 + i] = __fmaf_rn(dxk[16 * c4 + i], t, acc[16 * c4 + i]);
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(tempty_bar(h));
+        }
+        if (row < p.M) {
+#pragma unroll
+            for (int c = 0; c < HALF_N; ++c) {
+                const int64_t n = n0 + 64 * h + c;
+                if (n < p.N) p.dst[n * p.dst_stride + row] = acc[c];
+            }
+        }
+    } else if (warp < EPI_WARPS + PROD_WARPS) {
+        // ===================== producers: Q4_K bytes -> three int8 A tiles; planar int8 activations -> B tile =====================
+        const int t = threadIdx.x - EPI_WARPS * 32;
+        const int64_t row = m0 + t < p.M ? m0 + t : p.M - 1, col = n0 + t < p.N ? n0 + t : p.N - 1;
+        const uint8_t *wrow = p.w + row * p.w_stride;
+        const int8_t *xcol = p.xq + col * K;
+        ProdRegs cur, nxt;
+        producer_load(p, wrow, xcol, 0, cur);
+        int s = 0;
+        uint32_t phase = 0;
+        for (int step = 0; step < nsteps; ++step) {
+            if (step + 1 < nsteps) producer_load(p, wrow, xcol, step + 1, nxt);
+            mbar_wait(empty_bar(s), phase ^ 1u);
+            producer_store(smem + (size_t)s * STAGE_BYTES_TC, t, step & 1, cur);
+            fence_async_smem();                    // generic-proxy stores -> visible to the tensor core's async proxy
+            mbar_arrive(full_bar(s));
+            cur = nxt;
+            if (++s == STAGES) { s = 0; phase ^= 1u; }
+        }
+    } else if (lane == 0) {
+        // ===================== MMA issuer (one thread) =====================
+        const uint32_t idesc = umma_idesc_i8();
+        const uint32_t stage0 = smem_addr(smem);
+        int s = 0;
+        uint32_t phase = 0;
+        for (int step = 0; step < nsteps; ++step) {
+            const int kb = step >> 1, hh = step & 1;
+            mbar_wait(full_bar(s), phase);
+            tc_fence_after();
+            const uint32_t sa = stage0 + (uint32_t)s * STAGE_BYTES_TC;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (hh == 0) {                     // new superblock: the previous one must have left this half of TMEM
+                    mbar_wait(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
+                    tc_fence_after();
+                }
+#pragma unroll
+                for (int o = 0; o < 3; ++o) {
+#pragma unroll
+                    for (int j = 0; j < BK / 32; ++j) {
+                        const uint64_t a_desc = umma_desc(sa + o * TILE_BYTES + j * 2 * LBO_BYTES);
+                        const uint64_t b_desc = umma_desc(sa + 3 * TILE_BYTES + h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES);
+                        umma_i8(tmem + o * 128 + h * HALF_N, a_desc, b_desc, idesc, (uint32_t)((hh | j) != 0));
+                    }
+                }
+                if (hh == 1) umma_commit(tfull_bar(h));     // superblock complete in this half -> its epilogue group
+            }
+            umma_commit(empty_bar(s));                      // stage consumed -> producers
+            if (++s == STAGES) { s = 0; phase ^= 1u; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == EPI_WARPS + PROD_WARPS) {
+        __syncwarp();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+    }
+}
+
+// F32 rows -> planar Q8: int8 qs[N][K] and float d[nb][Nld]; the arithmetic of quantize_row_q8_K (shared device
+// function, bit-exact), one warp per 256-block
+__global__ void __launch_bounds__(256)
+quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, float *__restrict__ d, int64_t nb_per_row,
+                          int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld) {
+    const int lane = threadIdx.x & 31;
+    const int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (blk >= nblocks_total) return;
+    const int64_t row = blk / nb_per_row, b = blk - row * nb_per_row;
+    const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + row * x_row_stride_bytes) + b * QK_K;
+    const float4 a = __ldg(reinterpret_cast<const float4 *>(src) + lane);
+    const float4 c = __ldg(reinterpret_cast<const float4 *>(src) + 32 + lane);
+    const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+    uint32_t w_lo, w_hi;
+    int s_lo, s_hi;
+    const float dq = quantize_block_q8_K(v, lane, w_lo, w_hi, s_lo, s_hi);
+    uint32_t *out = reinterpret_cast<uint32_t *>(qs + (row * nb_per_row + b) * QK_K);
+    out[lane] = w_lo;
+    out[32 + lane] = w_hi;
+    if (lane == 0) d[b * Nld + row] = dq;
+}
+
+}  // namespace
+
+// Q8_K-block activations (q4k_mul_mat_q8 with N > 8): no planar copy is available without a workspace; the caller
+// runs the decode kernel eight columns at a time (same GPU arithmetic)
 cudaError_t launch_gemm_q4k_q8k(const void *, int64_t, int64_t, int64_t, const void *, int64_t, int64_t,
                                 float *, int64_t, cudaStream_t) {
     return cudaErrorNotSupported;
+}
+
+// F32 activations: quantize to planar Q8 in `workspace` (N*K + nb*N*4 bytes <= q4k_mul_mat_workspace_bytes), then the
+// tensor-core GEMM.  Two launches.
+cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                                const float *x, int64_t N, int64_t x_row_stride_bytes,
+                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream) {
+    if (M == 0 || N == 0) return cudaSuccess;
+    const int64_t nb = K / QK_K;
+    int8_t *qs = reinterpret_cast<int8_t *>(workspace);
+    float *d = reinterpret_cast<float *>(qs + N * K);
+    const int64_t total = nb * N;
+    quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, nb, total, x_row_stride_bytes, N);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+
+    GemmParams p;
+    p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
+    p.xq = qs; p.xd = d; p.N = N; p.Nld = N;
+    p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
+    constexpr size_t smem = (size_t)STAGES * STAGE_BYTES_TC + 1024 + 256;
+    static bool attr_set = false;
+    if (!attr_set) {
+        e = cudaFuncSetAttribute(gemm_q4k_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM));     // column tiles of one row tile run together (L2)
+    gemm_q4k_tc_kernel<<<grid, GEMM_THREADS, smem, stream>>>(p);
+    count_launch();
+    return cudaGetLastError();
 }
 
 }  // namespace q4k

@@ -108,6 +108,9 @@ int q4k_debug_set_fuse_limit(int64_t n_floats);
 /* development knob: 1 (default) = GEMV launches use programmatic dependent launch, 0 = plain stream order */
 int q4k_debug_set_pdl(int on);
 
+/* development knob: 1 (default) = N > 8 runs the tcgen05 GEMM, 0 = the decode kernel eight columns at a time */
+int q4k_debug_set_gemm(int on);
+
 /* host-buffer convenience used by the plugin's e2e path and bench.py's e2e leg: copies x (pinned or
  * pageable host) to the device, runs q4k_mul_mat, copies dst back.  Weights stay resident (w_dev).
  * Synchronous. */

@@ -127,6 +127,38 @@ def test_back_to_back_pdl_launches_see_fresh_activations(q4k):
     assert np.array_equal(y3.cpu().numpy().view(np.uint32), r3.view(np.uint32))
 
 
+@pytest.mark.parametrize("M,K,N", [(128, 256, 16), (256, 2048, 128), (130, 512, 9), (300, 1024, 200), (64, 4096, 130), (512, 5632, 64)])
+def test_gemm_tensor_core_within_tolerance(q4k, M, K, N):
+    """N > 8 takes the tcgen05 kind::i8 GEMM (exact int32 sumi / summ per superblock in TMEM, fp32 scales in the
+    epilogue); fp32 results within 1e-5 of the AVX2-order oracle, ragged M / N tiles included."""
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(N, K)
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+
+
+def test_gemm_integer_stage_is_exact(q4k):
+    """With d = dmin = 1 in every weight block and activations that quantize to themselves (d_x = 1), the fp32 output
+    is exactly sumi - summ: any error in the tensor-core integer stage (scale split, min accumulator) shows."""
+    from oracle import port
+    rng = np.random.default_rng(5)
+    M, K, N = 128, 512, 32
+    w = rng.integers(0, 256, (M, K // 256, 144), dtype=np.uint8)
+    w[..., 0:2] = np.frombuffer(np.float16(1.0).tobytes(), np.uint8)
+    w[..., 2:4] = np.frombuffer(np.float16(1.0).tobytes(), np.uint8)
+    w = w.reshape(M, -1)
+    x = rng.integers(-127, 128, (N, K)).astype(np.float32)
+    x[:, ::256] = -127.0                                    # block max -> iscale = 1, d = 1
+    xq = port.quantize_q8_K(x)
+    want = np.zeros((N, M), np.int64)
+    for n in range(N):
+        for m in range(M):
+            _, si, sm = port.vec_dot_partials(w[m], xq[n])
+            want[n, m] = int(si.sum()) - int(sm.sum())
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert np.array_equal(got.astype(np.int64), want) and np.array_equal(got, want.astype(np.float32))
+
+
 def test_vec_dot_signature_bit_identical(q4k):
     import torch
     from oracle import port
