@@ -117,7 +117,14 @@ int q4k_quantize_q8_K(const float *x_dev, void *y_dev, int64_t k, int64_t nrows,
 
 size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
     if (K <= 0 || N <= 0 || K % Q4K_QK_K != 0) return 0;
-    return (size_t)N * (size_t)(K / Q4K_QK_K) * Q4K_BLOCK_Q8K;
+    const size_t nb = (size_t)(K / Q4K_QK_K);
+    size_t need = (size_t)N * nb * Q4K_BLOCK_Q8K;                        // block_q8_K rows (decode path)
+    if (N > Q4K_GEMV_MAX_N) {                                            // prefill path: int8 in whole 128-column tiles + scales
+        const size_t npad = ((size_t)N + 127) / 128 * 128;
+        const size_t gemm = npad * (size_t)K + nb * (size_t)N * 4;
+        if (gemm > need) need = gemm;
+    }
+    return need;
 }
 
 int q4k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,

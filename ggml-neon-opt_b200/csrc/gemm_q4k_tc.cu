@@ -37,11 +37,19 @@ namespace {
 
 constexpr int BM = 128, BN = 128, BK = 128;          // CTA tile; BK = K bytes per pipeline stage (half a superblock)
 constexpr int HALF_N = 64;                            // columns per accumulator half / per MMA
-constexpr int STAGES = 3;
+constexpr int A_STAGES = 2;                           // unpacked A tiles (A_hi, A_lo, A_m): producers -> MMA
+constexpr int B_SLOTS = 4;                            // activation tiles, written in place by cp.async
+constexpr int RAW_SLOTS = 3;                          // raw block_q4_K bytes of 128 rows x one superblock (coalesced cp.async)
+constexpr int PREFETCH = 3;                           // pipeline steps of global loads in flight per producer thread
 constexpr int TILE_BYTES = BM * BK;                   // 16 KB: one int8 operand tile of a stage
-constexpr int STAGE_BYTES_TC = 4 * TILE_BYTES;        // A_hi, A_lo, A_m, B
-constexpr int EPI_WARPS = 8, PROD_WARPS = 4;
-constexpr int GEMM_THREADS = (EPI_WARPS + PROD_WARPS + 1) * 32;   // 416
+constexpr int A_STAGE_BYTES = 3 * TILE_BYTES;         // A_hi, A_lo, A_m
+constexpr int RAW_ROW_BYTES = BLK_Q4K, RAW_SLOT_BYTES = BM * RAW_ROW_BYTES;
+constexpr int SMEM_A = 0, SMEM_B = SMEM_A + A_STAGES * A_STAGE_BYTES, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES;
+constexpr int SMEM_DX = SMEM_RAW + RAW_SLOTS * RAW_SLOT_BYTES, SMEM_BARS = SMEM_DX + 1024;
+constexpr int SMEM_TOTAL = SMEM_BARS + 256;
+constexpr int EPI_WARPS = 16, PROD_WARPS = 4;        // 4 epilogue groups of 4 warps (32 columns each), 2 groups per accumulator half
+constexpr int EPI_COLS = BN / (EPI_WARPS / 4);        // 32 columns per epilogue thread
+constexpr int GEMM_THREADS = (EPI_WARPS + PROD_WARPS + 1) * 32;   // 672
 constexpr int TMEM_COLS = 512;                        // 3 accumulators x 128 columns, rounded to a power of two
 constexpr uint32_t SBO_BYTES = 8 * BK;                // 1024: next 8-row group of core matrices
 constexpr uint32_t LBO_BYTES = 128;                   // next 16-byte K chunk (core matrices of a row group are contiguous)
@@ -50,7 +58,7 @@ struct GemmParams {
     const uint8_t *w;
     int64_t M, w_stride;
     int nb;
-    const int8_t *xq;       // planar int8 [N][K]
+    const int8_t *xq;       // int8 activations, pre-tiled: [column tile][superblock][half][16 KB canonical B tile]
     const float *xd;        // [nb][Nld]
     int64_t N, Nld;
     float *dst;
@@ -114,6 +122,11 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
                    "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                  : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr) : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 }  // namespace
@@ -122,32 +135,48 @@ namespace {
 
 __device__ __forceinline__ uint4 ldg16(const void *p) { return *reinterpret_cast<const uint4 *>(p); }
 
-struct ProdRegs {
-    uint4 hdr;
-    uint4 q[4];     // 64 bytes of nibbles: two 64-element groups
-    uint4 y[8];     // 128 int8 activations of this thread's column
-};
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__device__ __forceinline__ void producer_load(const GemmParams &p, const uint8_t *wrow, const int8_t *xcol, int step, ProdRegs &r) {
+// Global -> shared copies of one pipeline step, 16 bytes per cp.async, consecutive threads on consecutive chunks
+// (coalesced; the destination is linear in the chunk index for both operands):
+//   B tile of `step`      : 1024 chunks, the activations are stored pre-tiled in exactly the shared-memory order
+//   raw weights of `sb`   : 128 rows x 9 chunks (whole block_q4_K), issued together with the B tile of step 2*sb
+__device__ __forceinline__ void producer_issue(const GemmParams &p, uint32_t smem0, int t, int64_t m0, int64_t ntile, int step) {
     const int kb = step >> 1, hh = step & 1;
-    const uint8_t *blk = wrow + (int64_t)kb * BLK_Q4K;
-    r.hdr = ldg16(blk);
+    const int8_t *bsrc = p.xq + (((ntile * p.nb + kb) * 2 + hh) << 14) + 16 * t;
+    const uint32_t bdst = smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES + 16 * t;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) r.q[i] = ldg16(blk + 16 + 64 * hh + 16 * i);
-    const int8_t *xs = xcol + (int64_t)kb * QK_K + 128 * hh;
+    for (int i = 0; i < 8; ++i) cp_async16(bdst + i * 2048, bsrc + i * 2048);
+    if (hh == 0) {
+        const uint32_t raw = smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) r.y[i] = ldg16(xs + 16 * i);
+        for (int i = 0; i < 9; ++i) {
+            const int c = i * 128 + t, r = c / 9, ch = c - 9 * r;
+            int64_t row = m0 + r;
+            if (row >= p.M) row = p.M - 1;
+            cp_async16(raw + 16 * c, p.w + row * p.w_stride + (int64_t)kb * BLK_Q4K + 16 * ch);
+        }
+    }
 }
 
-// one thread = one weight row (A tiles) and one activation column (B tile) of a pipeline stage
-__device__ __forceinline__ void producer_store(uint8_t *stage, int t, int hh, const ProdRegs &r) {
-    const uint4 sm = unpack_scales_mins(r.hdr);
+// the thread's raw row (in shared memory) -> three int8 A tiles of the stage
+__device__ __forceinline__ void producer_unpack(uint8_t *a_stage, const uint8_t *raw, int t, int hh) {
+    const uint4 hdr = *reinterpret_cast<const uint4 *>(raw);
+    uint4 q[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) q[i] = *reinterpret_cast<const uint4 *>(raw + 16 + 64 * hh + 16 * i);
+    const uint4 sm = unpack_scales_mins(hdr);
     const uint32_t scw = hh ? sm.y : sm.x, mw = hh ? sm.w : sm.z;
-    uint8_t *row_base = stage + (t >> 3) * SBO_BYTES + (t & 7) * 16;
+    uint8_t *row_base = a_stage + (t >> 3) * SBO_BYTES + (t & 7) * 16;
 #pragma unroll
     for (int gi = 0; gi < 2; ++gi) {
-        const uint32_t qw[8] = {r.q[2 * gi].x, r.q[2 * gi].y, r.q[2 * gi].z, r.q[2 * gi].w,
-                                r.q[2 * gi + 1].x, r.q[2 * gi + 1].y, r.q[2 * gi + 1].z, r.q[2 * gi + 1].w};
+        const uint32_t qw[8] = {q[2 * gi].x, q[2 * gi].y, q[2 * gi].z, q[2 * gi].w,
+                                q[2 * gi + 1].x, q[2 * gi + 1].y, q[2 * gi + 1].z, q[2 * gi + 1].w};
 #pragma unroll
         for (int nib = 0; nib < 2; ++nib) {             // 0: low nibbles = sub-block 2g, 1: high nibbles = sub-block 2g + 1
             const uint32_t sc = (scw >> (16 * gi + 8 * nib)) & 0xffu, mn = (mw >> (16 * gi + 8 * nib)) & 0xffu;
@@ -164,21 +193,20 @@ __device__ __forceinline__ void producer_store(uint8_t *stage, int t, int hh, co
             }
         }
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4 *>(row_base + 3 * TILE_BYTES + i * LBO_BYTES) = r.y[i];
 }
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_q4k_tc_kernel(const GemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    float *dx_s = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES_TC);            // [half][buffer][64]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES_TC + 1024);
-    uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 16);
+    float *dx_s = reinterpret_cast<float *>(smem + SMEM_DX);            // [half][buffer][64]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BARS);
+    uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 24);
     const uint32_t bar0 = smem_addr(bars);
-    auto full_bar = [&](int s) { return bar0 + 8u * s; };
-    auto empty_bar = [&](int s) { return bar0 + 8u * (3 + s); };
-    auto tfull_bar = [&](int h) { return bar0 + 8u * (6 + h); };
-    auto tempty_bar = [&](int h) { return bar0 + 8u * (8 + h); };
+    auto full_bar = [&](int s) { return bar0 + 8u * s; };                  // [B_SLOTS]  producers -> MMA, one per pipeline step slot
+    auto emptya_bar = [&](int s) { return bar0 + 8u * (4 + s); };          // [A_STAGES] MMA -> producers
+    auto emptyb_bar = [&](int s) { return bar0 + 8u * (6 + s); };          // [B_SLOTS]  MMA -> producers
+    auto tfull_bar = [&](int h) { return bar0 + 8u * (10 + h); };
+    auto tempty_bar = [&](int h) { return bar0 + 8u * (12 + h); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
@@ -186,8 +214,9 @@ gemm_q4k_tc_kernel(const GemmParams p) {
     const int64_t K = (int64_t)nb * QK_K;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), PROD_WARPS * 32); mbar_init(empty_bar(s), 1); }
-        for (int h = 0; h < 2; ++h) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), 4 * 32); }
+        for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_WARPS * 32); mbar_init(emptyb_bar(s), 1); }
+        for (int s = 0; s < A_STAGES; ++s) mbar_init(emptya_bar(s), 1);
+        for (int h = 0; h < 2; ++h) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), (EPI_WARPS / 2) * 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == EPI_WARPS + PROD_WARPS) {
@@ -201,40 +230,46 @@ gemm_q4k_tc_kernel(const GemmParams p) {
 
     if (warp < EPI_WARPS) {
         // ===================== epilogue: TMEM -> registers, per-superblock fp32 scales =====================
-        const int qd = warp & 3, h = warp >> 2, tg = threadIdx.x & 127;       // lane quadrant, column half, thread in group
+        const int qd = warp & 3, grp = warp >> 2, h = grp >> 1;               // lane quadrant, column group (32 wide), accumulator half
+        const int th = threadIdx.x & 255;                                      // thread within the half (two groups)
         const int64_t row = m0 + 32 * qd + lane;
         const uint8_t *wrow = p.w + (row < p.M ? row : p.M - 1) * p.w_stride;
         float *dx = dx_s + h * 128;
-        int64_t ncl = n0 + 64 * h + (tg & 63);
+        int64_t ncl = n0 + HALF_N * h + (th & 63);
         if (ncl >= p.N) ncl = p.N - 1;
-        float acc[HALF_N];
+        float acc[EPI_COLS];
 #pragma unroll
-        for (int i = 0; i < HALF_N; ++i) acc[i] = 0.0f;
+        for (int i = 0; i < EPI_COLS; ++i) acc[i] = 0.0f;
         uint32_t dd_next = *reinterpret_cast<const uint32_t *>(wrow);
-        if (tg < 64) dx[tg] = p.xd[ncl];                                       // superblock 0 -> buffer 0
-        const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(HALF_N * h);
+        if (th < 64) dx[th] = p.xd[ncl];                                       // superblock 0 -> buffer 0
+        const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * grp);
+        const int cofs = EPI_COLS * (grp & 1);                                 // this group's columns inside the half
         for (int kb = 0; kb < nb; ++kb) {
             const uint32_t dd = dd_next;
             if (kb + 1 < nb) dd_next = *reinterpret_cast<const uint32_t *>(wrow + (int64_t)(kb + 1) * BLK_Q4K);
             mbar_wait(tfull_bar(h), (uint32_t)(kb & 1));
             tc_fence_after();
-            asm volatile("bar.sync %0, 128;" ::"r"(1 + h) : "memory");        // everyone is done with superblock kb - 1
-            if (tg < 64 && kb + 1 < nb) dx[((kb + 1) & 1) * 64 + tg] = p.xd[(int64_t)(kb + 1) * p.Nld + ncl];
+            asm volatile("bar.sync %0, 256;" ::"r"(1 + h) : "memory");        // everyone of this half is done with superblock kb - 1
+            if (th < 64 && kb + 1 < nb) dx[((kb + 1) & 1) * 64 + th] = p.xd[(int64_t)(kb + 1) * p.Nld + ncl];
             const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));   // {d, dmin} of this row's superblock
-            const float *dxk = dx + (kb & 1) * 64;
+            const float *dxk = dx + (kb & 1) * 64 + cofs;
+            uint32_t vh[2][8], vl[2][8], vm[2][8];
+            tmem_ld8(tbase, vh[0]); tmem_ld8(tbase + 128, vl[0]); tmem_ld8(tbase + 256, vm[0]);
 #pragma unroll
-            for (int c4 = 0; c4 < HALF_N / 16; ++c4) {
-                uint32_t vh[16], vl[16], vm[16];
-                tmem_ld16(tbase + 16 * c4, vh);
-                tmem_ld16(tbase + 128 + 16 * c4, vl);
-                tmem_ld16(tbase + 256 + 16 * c4, vm);
+            for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
+                const int cur = c8 & 1;
                 tmem_ld_wait();
+                if (c8 + 1 < EPI_COLS / 8) {                                   // next 8 columns in flight while these are scaled
+                    tmem_ld8(tbase + 8 * (c8 + 1), vh[cur ^ 1]);
+                    tmem_ld8(tbase + 128 + 8 * (c8 + 1), vl[cur ^ 1]);
+                    tmem_ld8(tbase + 256 + 8 * (c8 + 1), vm[cur ^ 1]);
+                }
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int sumi = 8 * (int)vh[i] + (int)vl[i];
+                for (int i = 0; i < 8; ++i) {
+                    const int sumi = ((int)vh[cur][i] << 3) + (int)vl[cur][i];
                     float t = __fmul_rn(dw.x, (float)sumi);
-                    t = __fmaf_rn(-dw.y, (float)(int)vm[i], t);
-                    acc[16 * c4 + i] = __fmaf_rn(dxk[16 * c4 + i], t, acc[16 * c4 + i]);
+                    t = __fmaf_rn(-dw.y, (float)(int)vm[cur][i], t);
+                    acc[8 * c8 + i] = __fmaf_rn(dxk[8 * c8 + i], t, acc[8 * c8 + i]);
                 }
             }
             tc_fence_before();
@@ -242,41 +277,47 @@ gemm_q4k_tc_kernel(const GemmParams p) {
         }
         if (row < p.M) {
 #pragma unroll
-            for (int c = 0; c < HALF_N; ++c) {
-                const int64_t n = n0 + 64 * h + c;
+            for (int c = 0; c < EPI_COLS; ++c) {
+                const int64_t n = n0 + EPI_COLS * grp + c;
                 if (n < p.N) p.dst[n * p.dst_stride + row] = acc[c];
             }
         }
     } else if (warp < EPI_WARPS + PROD_WARPS) {
         // ===================== producers: Q4_K bytes -> three int8 A tiles; planar int8 activations -> B tile =====================
         const int t = threadIdx.x - EPI_WARPS * 32;
-        const int64_t row = m0 + t < p.M ? m0 + t : p.M - 1, col = n0 + t < p.N ? n0 + t : p.N - 1;
-        const uint8_t *wrow = p.w + row * p.w_stride;
-        const int8_t *xcol = p.xq + col * K;
-        ProdRegs cur, nxt;
-        producer_load(p, wrow, xcol, 0, cur);
-        int s = 0;
-        uint32_t phase = 0;
+        const uint32_t smem0 = smem_addr(smem);
+        const int64_t ntile = blockIdx.x;
+#pragma unroll
+        for (int i = 0; i < PREFETCH; ++i) {             // fresh slots: nothing to wait for
+            if (i < nsteps) producer_issue(p, smem0, t, m0, ntile, i);
+            cp_async_commit();
+        }
         for (int step = 0; step < nsteps; ++step) {
-            if (step + 1 < nsteps) producer_load(p, wrow, xcol, step + 1, nxt);
-            mbar_wait(empty_bar(s), phase ^ 1u);
-            producer_store(smem + (size_t)s * STAGE_BYTES_TC, t, step & 1, cur);
-            fence_async_smem();                    // generic-proxy stores -> visible to the tensor core's async proxy
-            mbar_arrive(full_bar(s));
-            cur = nxt;
-            if (++s == STAGES) { s = 0; phase ^= 1u; }
+            cp_async_wait<PREFETCH - 1>();               // this thread's copies for `step` have landed ...
+            if ((step & 1) == 0) asm volatile("bar.sync 3, 128;" ::: "memory");   // ... and everybody else's: the raw rows are shared
+            const int a = step % A_STAGES;
+            mbar_wait(emptya_bar(a), (uint32_t)(((step / A_STAGES) & 1) ^ 1));
+            producer_unpack(smem + SMEM_A + a * A_STAGE_BYTES, smem + SMEM_RAW + ((step >> 1) % RAW_SLOTS) * RAW_SLOT_BYTES + t * RAW_ROW_BYTES,
+                            t, step & 1);
+            fence_async_smem();                          // generic-proxy writes (st.shared, cp.async) -> tensor core's async proxy
+            mbar_arrive(full_bar(step % B_SLOTS));
+            const int ahead = step + PREFETCH;
+            if (ahead < nsteps) {
+                // the B slot of step `ahead` was last read by the MMAs of step ahead - B_SLOTS
+                mbar_wait(emptyb_bar(ahead % B_SLOTS), (uint32_t)(((ahead / B_SLOTS) & 1) ^ 1));
+                producer_issue(p, smem0, t, m0, ntile, ahead);
+            }
+            cp_async_commit();
         }
     } else if (lane == 0) {
         // ===================== MMA issuer (one thread) =====================
         const uint32_t idesc = umma_idesc_i8();
         const uint32_t stage0 = smem_addr(smem);
-        int s = 0;
-        uint32_t phase = 0;
         for (int step = 0; step < nsteps; ++step) {
-            const int kb = step >> 1, hh = step & 1;
-            mbar_wait(full_bar(s), phase);
+            const int kb = step >> 1, hh = step & 1, a = step % A_STAGES, bslot = step % B_SLOTS;
+            mbar_wait(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));
             tc_fence_after();
-            const uint32_t sa = stage0 + (uint32_t)s * STAGE_BYTES_TC;
+            const uint32_t sa = stage0 + SMEM_A + (uint32_t)a * A_STAGE_BYTES, sb = stage0 + SMEM_B + (uint32_t)bslot * TILE_BYTES;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (hh == 0) {                     // new superblock: the previous one must have left this half of TMEM
@@ -288,14 +329,14 @@ gemm_q4k_tc_kernel(const GemmParams p) {
 #pragma unroll
                     for (int j = 0; j < BK / 32; ++j) {
                         const uint64_t a_desc = umma_desc(sa + o * TILE_BYTES + j * 2 * LBO_BYTES);
-                        const uint64_t b_desc = umma_desc(sa + 3 * TILE_BYTES + h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES);
+                        const uint64_t b_desc = umma_desc(sb + h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES);
                         umma_i8(tmem + o * 128 + h * HALF_N, a_desc, b_desc, idesc, (uint32_t)((hh | j) != 0));
                     }
                 }
                 if (hh == 1) umma_commit(tfull_bar(h));     // superblock complete in this half -> its epilogue group
             }
-            umma_commit(empty_bar(s));                      // stage consumed -> producers
-            if (++s == STAGES) { s = 0; phase ^= 1u; }
+            umma_commit(emptya_bar(a));                     // A stage and B slot consumed -> producers
+            umma_commit(emptyb_bar(bslot));
         }
     }
 
@@ -307,8 +348,10 @@ gemm_q4k_tc_kernel(const GemmParams p) {
     }
 }
 
-// F32 rows -> planar Q8: int8 qs[N][K] and float d[nb][Nld]; the arithmetic of quantize_row_q8_K (shared device
-// function, bit-exact), one warp per 256-block
+// F32 rows -> int8 activations in the GEMM's own tiled order + float d[nb][Nld]; the arithmetic of quantize_row_q8_K
+// (shared device function, bit-exact), one warp per 256-block.  Element k of column n, superblock b lands in
+//   tile (n / 128, b), half k / 128, then the canonical K-major core-matrix order of the shared-memory B tile:
+//   ((n % 128) / 8) * 1024 + ((k % 128) / 16) * 128 + (n % 8) * 16 + k % 16
 __global__ void __launch_bounds__(256)
 quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, float *__restrict__ d, int64_t nb_per_row,
                           int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld) {
@@ -323,9 +366,12 @@ quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, 
     uint32_t w_lo, w_hi;
     int s_lo, s_hi;
     const float dq = quantize_block_q8_K(v, lane, w_lo, w_hi, s_lo, s_hi);
-    uint32_t *out = reinterpret_cast<uint32_t *>(qs + (row * nb_per_row + b) * QK_K);
-    out[lane] = w_lo;
-    out[32 + lane] = w_hi;
+    const int64_t ntile = row >> 7, nl = row & 127;
+    int8_t *tile = qs + ((ntile * nb_per_row + b) << 15) + (nl >> 3) * 1024 + (nl & 7) * 16;
+    // lane l holds elements 4l..4l+3 (half 0) and 128+4l..128+4l+3 (half 1): chunk l / 4, bytes 4 * (l % 4)
+    const int off = (lane >> 2) * 128 + (lane & 3) * 4;
+    *reinterpret_cast<uint32_t *>(tile + off) = w_lo;
+    *reinterpret_cast<uint32_t *>(tile + 16384 + off) = w_hi;
     if (lane == 0) d[b * Nld + row] = dq;
 }
 
@@ -338,15 +384,16 @@ cudaError_t launch_gemm_q4k_q8k(const void *, int64_t, int64_t, int64_t, const v
     return cudaErrorNotSupported;
 }
 
-// F32 activations: quantize to planar Q8 in `workspace` (N*K + nb*N*4 bytes <= q4k_mul_mat_workspace_bytes), then the
+// F32 activations: quantize into `workspace` (roundup(N,128)*K + nb*N*4 bytes <= q4k_mul_mat_workspace_bytes), then the
 // tensor-core GEMM.  Two launches.
 cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream) {
     if (M == 0 || N == 0) return cudaSuccess;
     const int64_t nb = K / QK_K;
+    const int64_t Npad = (N + BN - 1) / BN * BN;          // whole column tiles; columns >= N hold stale bytes, never stored
     int8_t *qs = reinterpret_cast<int8_t *>(workspace);
-    float *d = reinterpret_cast<float *>(qs + N * K);
+    float *d = reinterpret_cast<float *>(qs + Npad * K);
     const int64_t total = nb * N;
     quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, nb, total, x_row_stride_bytes, N);
     count_launch();
@@ -357,7 +404,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
     p.xq = qs; p.xd = d; p.N = N; p.Nld = N;
     p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
-    constexpr size_t smem = (size_t)STAGES * STAGE_BYTES_TC + 1024 + 256;
+    constexpr size_t smem = SMEM_TOTAL;
     static bool attr_set = false;
     if (!attr_set) {
         e = cudaFuncSetAttribute(gemm_q4k_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
