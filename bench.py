@@ -209,6 +209,35 @@ def graph_of(torch, enqueue):
     return g
 
 
+def gemm_table(torch, q4k, device, peaks):
+    """Prefill (N = 512) figures: quantizer + tcgen05 kind::i8 GEMM through q4k_mul_mat.  int8 ops = 2*M*N*K
+    (op_flops of L/tests/test-backend-ops.cpp:3308-3311; the hi/lo/min split's extra MMA work is NOT counted)."""
+    out = {"shapes": []}
+    int8_nominal = 4500.0                                   # dense int8 = dense fp8 rate on B200 (B200_PROFILING.md: 4.5 PFLOP/s)
+    int8_from_bf16 = 2.0 * float(peaks.get("bf16_tflops", 0.0)) if peaks else 0.0
+
+    def run(mats, N, iters):
+        ms = MatSet(torch, q4k, mats, N, device, seed=5)
+        for _ in range(2):
+            ms.enqueue_device()
+        t = timed_steps(torch, ms.enqueue_device, iters, 1, lambda: None) / iters
+        ops = sum(2.0 * M * K * N for _, M, K in mats)
+        del ms
+        torch.cuda.empty_cache()
+        return t, ops
+
+    for M, K, N in [(4096, 14336, 512), (14336, 4096, 512), (4096, 14336, 32)]:
+        t, ops = run([("m", M, K)], N, 10)
+        out["shapes"].append({"M": M, "K": K, "N": N, "us": round(t * 1e3, 1), "tops": round(ops / t / 1e9, 1)})
+    t, ops = run(tinyllama_token_matmuls(), 512, 3)
+    tops = ops / t / 1e9
+    out["tinyllama_pp512"] = {"ms_per_pass": round(t, 3), "tops": round(tops, 1), "tok_s": round(512 / t * 1e3, 0),
+                              "int8_ops_per_pass": ops,
+                              "frac_of_nominal_int8_4500": round(tops / int8_nominal, 4),
+                              "frac_of_2x_measured_bf16": round(tops / int8_from_bf16, 4) if int8_from_bf16 else None}
+    return out
+
+
 def gemv_shape_table(torch, q4k, device, shapes, steps=20):
     """Per-shape GEMV figures (quantize + GEMV through q4k_mul_mat), rotating through > 2 x L2 of distinct
     weight copies so the bytes come from HBM.  Extra evidence; not the headline."""
@@ -313,23 +342,40 @@ def run_ours(args, rank, world, local_rank):
     N = args.batch
     sharded = args.workload == "ffn70b"
     mats = ffn70b_matmuls() if sharded else tinyllama_token_matmuls()
-    row_range = (lambda M: (M * rank // world, M * (rank + 1) // world)) if sharded else None
+    if sharded:
+        # distinct weight copies until every GPU streams > 2 x L2 per step: the bytes must come from HBM, not L2
+        per_gpu = sum(M * (K // 256) * 144 for _, M, K in mats) / world
+        copies = max(1, int(-(-2.2 * L2_BYTES // per_gpu)))
+        mats = [(f"{n}.{c}", M, K) for c in range(copies) for n, M, K in mats]
+    from q4k_b200.shard import shard_rows
+    row_range = (lambda M: shard_rows(M, world)[rank]) if sharded else None
     ms = MatSet(torch, q4k_b200, mats, N, device, seed=1234 + (rank if sharded else 0), row_range=row_range)
     total_bytes = sum(algo_bytes(M, K, N) for _, M, K in mats) * (1 if sharded else world)
 
     gathered = None
+    shards, gather_kind = None, None
     if sharded and world > 1:
-        gathered = [torch.zeros((world, N, it["M"]), device=device) for it in ms.items]
+        from q4k_b200.shard import RowShardedQ4K
+        gen = torch.Generator(device=device)
+        gen.manual_seed(777)                                   # activations are replicated: same numbers on every rank
+        shards = []
+        for it in ms.items:
+            it["x"] = torch.randn((N, it["K"]), device=device, generator=gen)
+            shards.append(RowShardedQ4K(it["w"], it["M_full"], it["K"], gather=args.gather))
+        gather_kind = shards[0].gather + (f" [{shards[0].peer_note}]" if shards[0].peer_note else "")
+        gathered = True
 
         def enqueue():
-            st = torch.cuda.current_stream().cuda_stream
-            for it, full in zip(ms.items, gathered):
-                rc = lib.q4k_mul_mat(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), it["x"].data_ptr(), N, it["K"] * 4,
-                                     it["dst"].data_ptr(), it["M"] * 4, ms.ws.data_ptr(), ms.ws.numel(), st)
-                assert rc == 0, rc
-                dist.all_gather_into_tensor(full, it["dst"])
+            for it, sh in zip(ms.items, shards):
+                it["full"] = sh.mul_mat(it["x"])
         step = enqueue
-        launches_per_step = None
+        if args.graph and shards[0].gather == "peer":        # NCCL collectives are left out of graph capture
+            try:                                               # the whole step (GEMVs + cross-GPU barriers) as one CUDA graph
+                step = graph_of(torch, enqueue).replay
+                gather_kind += ", CUDA graph"
+            except Exception as e:
+                torch.cuda.synchronize()
+                gather_kind += f", stream launches (graph capture failed: {type(e).__name__})"
     else:
         g = graph_of(torch, ms.enqueue_device)
         step = g.replay
@@ -345,10 +391,15 @@ def run_ours(args, rank, world, local_rank):
     # end to end: pinned host activations in, host results out, every step
     ms.make_host()
     if sharded and world > 1:
+        for it in ms.items:
+            it["x_host"] = it["x"].cpu().pin_memory()
+            it["full_host"] = torch.zeros((N, it["M_full"]), dtype=torch.float32).pin_memory()
+        ms.d2h = sum(it["full_host"].numel() * 4 for it in ms.items)
         def step_host():
-            ms.enqueue_host()
-            for it, full in zip(ms.items, gathered):
-                dist.all_gather_into_tensor(full, it["dst"])
+            for it, sh in zip(ms.items, shards):
+                it["x_stage"].copy_(it["x_host"], non_blocking=True)
+                full = sh.mul_mat(it["x_stage"])
+                it["full_host"].copy_(full, non_blocking=True)
             torch.cuda.current_stream().synchronize()
     else:
         def step_host():
@@ -383,7 +434,7 @@ def run_ours(args, rank, world, local_rank):
                        "weight_bytes_per_step_per_gpu": ms.weight_bytes,
                        "l2": f"no flush needed: each step streams {ms.weight_bytes >> 20} MiB of distinct weights per GPU (> 126 MiB L2)"
                              if ms.weight_bytes > L2_BYTES else "WARNING: per-GPU weights fit in L2",
-                       "launch": "CUDA graph replay of the C-ABI launches" if gathered is None else "stream launches + NCCL all_gather",
+                       "launch": "CUDA graph replay of the C-ABI launches" if gathered is None else f"gather={gather_kind}",
                        "parallelism": f"rowshard{world}" if sharded else f"replica{world}"},
             "decode_tok_s": round(1e3 / per_step_ms, 1) if not sharded else None,
             "pct_of_nominal_8TBs": round(100 * value / world / HBM_NOMINAL_GBS, 2),
@@ -401,6 +452,7 @@ def run_ours(args, rank, world, local_rank):
         except Exception as e:       # the baseline is a reported number, never a dependency of the GPU path
             line["cpu_baseline"] = {"value": None, "unit": "GB/s", "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
     if world == 1 and args.shapes:
+        line["prefill"] = gemm_table(torch, q4k_b200, device, measured_peaks()[2])
         line["shapes"] = gemv_shape_table(torch, q4k_b200, device,
                                           [(5632, 2048, 1), (4096, 14336, 1), (14336, 4096, 1), (4096, 14336, 8),
                                            (28672, 8192, 1), (8192, 28672, 1), (28672, 8192, 8)])
@@ -417,8 +469,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=[None, "tinyllama-token", "ffn70b"])
     ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--no-graph", dest="graph", action="store_false", help="sharded path: plain stream launches")
+    ap.add_argument("--gather", default="auto", choices=["auto", "nccl", "peer"], help="row-shard output exchange (N > 1 GPUs)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--shapes", action="store_true", help="add the per-shape GEMV table (C1/C4/C5)")
+    ap.add_argument("--shapes", action="store_true", default=True, help="add the per-shape GEMV table (C1/C4/C5) and the prefill GEMM figures")
+    ap.add_argument("--no-shapes", dest="shapes", action="store_false")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
@@ -429,6 +484,9 @@ def main():
         run_reference(args, rank)
     else:
         run_ours(args, rank, world, local_rank)
+        if world > 1:                       # symmetric-memory / NCCL teardown order at interpreter exit is not ours to debug
+            sys.stdout.flush()
+            os._exit(0)
 
 
 if __name__ == "__main__":

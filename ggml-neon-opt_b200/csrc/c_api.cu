@@ -203,6 +203,25 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
                           dst_dev, dst_col_stride_bytes, stream);
 }
 
+int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                      const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                      float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream) {
+    if (M_local < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0 || dst_row0 < 0) return Q4K_ERR_BAD_SHAPE;
+    if (N > Q4K_GEMV_MAX_N || n_peers < 1 || n_peers > 8) return Q4K_ERR_UNSUPPORTED;
+    if (M_local == 0 || N == 0) return Q4K_OK;
+    if (!w_dev || !x_dev || !dst_peers) return Q4K_ERR_BAD_POINTER;
+    for (int g = 0; g < n_peers; ++g) if (!dst_peers[g]) return Q4K_ERR_BAD_POINTER;
+    const int64_t nb = K / Q4K_QK_K;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (dst_col_stride_bytes < (dst_row0 + M_local) * 4 || (dst_col_stride_bytes & 3)) return Q4K_ERR_BAD_SHAPE;
+    const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M_local, K, w_row_stride_bytes, nullptr, x_dev, (int)N, x_row_stride_bytes,
+                                                  nullptr, dst_col_stride_bytes, gemv_exact_for((int)N), 0, g_gemv_pdl != 0,
+                                                  (cudaStream_t)stream, dst_peers, n_peers, dst_row0);
+    if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;     // activations too large for one shared-memory residency
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
 int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, size_t bx, const void *vy_dev, size_t by, int nrc) {
     (void)bs; (void)bx; (void)by;
     if (nrc != 1) return Q4K_ERR_UNSUPPORTED;      // the reference asserts nrc == 1 on x86 (arch/x86/quants.c:1743)

@@ -52,7 +52,9 @@ struct TmaGemvParams {
     const uint8_t *xq;      // Q8_K activations, or
     const float *xf;        // F32 activations (quantized inside the kernel) when xq == nullptr
     int64_t x_stride;       // bytes between activation rows (of whichever is set)
-    float *dst;
+    float *dst[8];          // output buffer of every peer GPU that gets a copy of the result (dst[0] = local)
+    int n_dst;
+    int64_t dst_row0;       // first row of this shard inside the (full) output column
     int64_t dst_stride;
     int64_t n_groups;       // ceil(M / 4)
     int stages;
@@ -346,7 +348,12 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
                     a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, 2));
                     a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, 4));
                 }
-                if (b == 0 && row < p.M) p.dst[(int64_t)n * p.dst_stride + row] = a;
+                if (b == 0 && row < p.M) {
+                    // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
+                    const int64_t o = (int64_t)n * p.dst_stride + p.dst_row0 + row;
+                    p.dst[0][o] = a;
+                    for (int g = 1; g < p.n_dst; ++g) p.dst[g][o] = a;
+                }
                 acc[n] = 0.0f; accm[n] = 0.0f;
             }
         }
@@ -430,12 +437,17 @@ cudaError_t launch_tma_e(int N, const TmaGemvParams &p, int stages, bool pdl, cu
 cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                     const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
-                                    bool pdl, cudaStream_t stream) {
+                                    bool pdl, cudaStream_t stream, float *const *peer_dst, int n_peers, int64_t dst_row0) {
     if (M == 0 || N == 0) return cudaSuccess;
+    if (n_peers > 8) return cudaErrorInvalidValue;
     TmaGemvParams p;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
     p.xq = (const uint8_t *)xq; p.xf = xf; p.x_stride = x_row_stride_bytes;
-    p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
+    for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
+    if (n_peers > 0) { for (int g = 0; g < n_peers; ++g) p.dst[g] = peer_dst[g]; p.n_dst = n_peers; }
+    else { p.dst[0] = dst; p.n_dst = 1; }
+    p.dst_row0 = dst_row0;
+    p.dst_stride = dst_col_stride_bytes / 4;
     p.n_groups = (M + TILE_ROWS - 1) / TILE_ROWS;
     p.stages = 0;
     return exact_order ? launch_tma_e<true>(N, p, stages, pdl, stream) : launch_tma_e<false>(N, p, stages, pdl, stream);

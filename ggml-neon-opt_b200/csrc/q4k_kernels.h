@@ -19,10 +19,13 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
 // the TMA-bulk staged implementation (gemv_q4k_tma.cu).  Activations: xq (Q8_K blocks) or, when xq == nullptr,
 // xf (F32 rows, quantized inside the kernel).  stages <= 0 = choose; pdl = programmatic dependent launch.
 // cudaErrorNotSupported if the Q8_K activations do not fit in shared memory.
+// peer_dst / n_peers / dst_row0: row-sharded multi-GPU — the result rows are stored at row offset dst_row0 into the
+// output buffer of every listed GPU (peer-mapped pointers; peer_dst[0] should be the local one).
 cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                     const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
-                                    bool pdl, cudaStream_t stream);
+                                    bool pdl, cudaStream_t stream,
+                                    float *const *peer_dst = nullptr, int n_peers = 0, int64_t dst_row0 = 0);
 
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,

@@ -51,6 +51,7 @@ def load():
         L.q4k_debug_partials.argtypes = [vp, i64, i64, i64, i64, vp, i64, i64, vp, vp, vp, vp]
         L.q4k_mul_mat_host.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_host_async.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
+        L.q4k_mul_mat_peers.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp]
         L.q4k_debug_set_fuse_limit.argtypes = [i64]
         L.q4k_debug_set_pdl.argtypes = [i32]
         L.q4k_debug_set_gemv_order.argtypes = [i32]

@@ -78,6 +78,16 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
                 float *dst_dev, int64_t dst_col_stride_bytes,
                 void *workspace_dev, size_t workspace_bytes, void *stream);
 
+/* row-sharded multi-GPU decode (N <= 8): this GPU owns weight rows [dst_row0, dst_row0 + M_local) of a larger matrix.
+ * Runs quantize + GEMV in ONE launch and stores every result at row dst_row0 + m of column n into the output buffer
+ * of EVERY GPU in dst_peers[0..n_peers) (device pointers valid on this GPU: its own buffer and NVLink peer-mapped
+ * ones, e.g. CUDA IPC / symmetric memory) — the all-gather of SURVEY.md §8e fused into the GEMV epilogue.  The
+ * caller orders the peers' reads after all ranks' launches (a cross-GPU barrier).  What it replaces in the
+ * reference: the dst-slice peer copies of ggml-cuda's row split (L/ggml/src/ggml-cuda/ggml-cuda.cu:1720). */
+int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                      const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                      float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream);
+
 /* same, src1 already Q8_K (vec_dot_type == src1->type branch, ggml-cpu.c:1267): N rows of K/256 blocks */
 int q4k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                    const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
