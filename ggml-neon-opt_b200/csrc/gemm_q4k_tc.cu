@@ -14,20 +14,22 @@
 // 32-wide sub-block; the fp32 scales d_w*d_x, dmin_w*d_x are applied by the epilogue warps per superblock,
 // sequentially over superblocks (the NEON order of the reference; within 1e-5 of the AVX2 oracle).
 //
-// CTA = 128 weight rows x 128 activation columns, 13 warps, warp-specialised:
-//   warps 0-7   epilogue: thread <-> TMEM lane (= weight row); warps 0-3 own columns 0-63, warps 4-7 columns
-//               64-127.  tcgen05.ld 16 columns x 3 accumulators at a time, 64 fp32 results per thread in registers.
-//   warps 8-11  producers: thread <-> weight row: loads its block_q4_K bytes (16 B loads), unpacks scales,
-//               writes the three int8 A tiles of half a superblock (K = 128) into shared memory in the canonical
-//               K-major no-swizzle UMMA layout (8-row x 16-byte core matrices); thread <-> column for the B tile.
-//   warp 12     allocates TMEM; one elected lane issues the MMAs (M = 128, N = 64, K = 32) and commits to mbarriers.
-// Pipelines: shared-memory ring of 3 stages (64 KB each: A_hi, A_lo, A_m, B) producers -> MMA; the two column
-// halves of the accumulators alternate between the tensor core and their epilogue group (MMA of half 1 overlaps
-// the drain of half 0).
+// CTA = 128 weight rows x 128 activation columns, 21 warps, warp-specialised:
+//   warps 0-15  epilogue: thread <-> TMEM lane (= weight row); group g = warp / 4 owns columns 32g..32g+31 (groups
+//               0,1 = accumulator half 0, groups 2,3 = half 1).  tcgen05.ld 8 columns x 3 accumulators at a time,
+//               double-buffered, 32 fp32 results per thread in registers.
+//   warps 16-19 producers: coalesced 16-byte cp.async of (a) whole block_q4_K rows of the tile's superblock into a raw
+//               ring and (b) the int8 activation tile, which is stored PRE-TILED in global memory in exactly the
+//               shared-memory order, straight into its B slot; then thread <-> weight row: unpack scales, write the
+//               three int8 A tiles of half a superblock (K = 128) in the canonical K-major no-swizzle UMMA layout
+//               (8-row x 16-byte core matrices).
+//   warp 20     allocates TMEM; one lane issues the MMAs (M = 128, N = 64, K = 32) and commits to mbarriers.
+// Pipelines: A stages (2 x 48 KB), B slots (4 x 16 KB), raw ring (3 x 18 KB), 3 steps of loads in flight; the two
+// column halves of the accumulators alternate between the tensor core and their epilogue groups (the MMAs of half 1
+// overlap the drain of half 0).
 //
-// Activations arrive "planar" (quantize_q8_planar below): int8 qs[N][K] + float d[nb][Nld] — the same numbers
-// quantize_row_q8_K produces (bit-exact, shared device function), laid out so that tiles load with 16-byte
-// accesses (block_q8_K's 292-byte stride is only 4-byte aligned).  bsums are not needed: the mins use the MMA.
+// Activations (quantize_q8_planar_kernel below): the same int8 / float d that quantize_row_q8_K produces (shared
+// device function, bit-exact), int8 in tile order + float d[nb][N].  bsums are not needed: the mins use the MMA.
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
