@@ -60,6 +60,19 @@ def tinyllama_token_matmuls():
     return mats
 
 
+def shared_input_ids(mats):
+    """input id per mul_mat: attn_q / attn_k / attn_v of a layer read the same attn_norm output and ffn_gate / ffn_up the
+    same ffn_norm output (L/src/models/llama.cpp build_attn / build_ffn inputs); every other mul_mat has its own input."""
+    ids, nxt, cur = [], -1, None
+    for name, _, _ in mats:
+        blk, _, leaf = name.rpartition(".")
+        fam = "qkv" if leaf in ("attn_q", "attn_k", "attn_v") else ("gu" if leaf in ("ffn_gate", "ffn_up") else leaf)
+        if (blk, fam) != cur or fam not in ("qkv", "gu"):
+            nxt, cur = nxt + 1, (blk, fam)
+        ids.append(nxt)
+    return ids
+
+
 def ffn70b_matmuls():
     return [("ffn_up_70b", 28672, 8192), ("ffn_down_70b", 8192, 28672)]
 
@@ -160,6 +173,23 @@ class MatSet:
                    it["dst"].data_ptr(), it["M"] * 4, ws, wsn, st)
             if rc != 0:
                 raise RuntimeError(f"q4k_mul_mat rc={rc} cuda={self.lib.q4k_last_cuda_error()}")
+
+    def make_plan(self):
+        """The whole step as one q4k_plan: packed inputs / outputs, shared activations, fused launches, one CUDA graph."""
+        t = self.torch
+        ids = shared_input_ids([(it["name"], it["M"], it["K"]) for it in self.items])
+        plan = self.q4k.GraphPlan(self.items[0]["w"].device.index)
+        for it, iid in zip(self.items, ids):
+            it["plan_index"], it["input_id"] = plan.add(it["w"], self.N, iid), iid
+        plan.finalize()
+        for it in self.items:
+            plan.input(it["input_id"]).copy_(it["x"])
+        self.plan = plan
+        self.plan_in_host = t.zeros(plan.input_bytes, dtype=t.uint8).pin_memory()
+        self.plan_out_host = t.zeros(plan.output_bytes, dtype=t.uint8).pin_memory()
+        self.plan_in_host.copy_(plan._in)
+        self.h2d, self.d2h = plan.input_bytes, plan.output_bytes
+        return plan
 
     def make_host(self):
         t = self.torch
@@ -353,7 +383,7 @@ def run_ours(args, rank, world, local_rank):
     total_bytes = sum(algo_bytes(M, K, N) for _, M, K in mats) * (1 if sharded else world)
 
     gathered = None
-    shards, gather_kind = None, None
+    shards, gather_kind, plan = None, None, None
     if sharded and world > 1:
         from q4k_b200.shard import RowShardedQ4K
         gen = torch.Generator(device=device)
@@ -376,11 +406,17 @@ def run_ours(args, rank, world, local_rank):
             except Exception as e:
                 torch.cuda.synchronize()
                 gather_kind += f", stream launches (graph capture failed: {type(e).__name__})"
+    elif args.plan:
+        plan = ms.make_plan()                                  # the library's own graph plan (q4k_plan_*)
+        step = plan.run
     else:
         g = graph_of(torch, ms.enqueue_device)
         step = g.replay
     n0 = lib.q4k_kernel_launches()
-    ms.enqueue_device()
+    if plan is not None:
+        plan.run()
+    else:
+        ms.enqueue_device()
     launches_per_step = lib.q4k_kernel_launches() - n0
     torch.cuda.synchronize()
 
@@ -389,7 +425,8 @@ def run_ours(args, rank, world, local_rank):
         clocks.start()
     ms_total = timed_steps(torch, step, args.steps, args.warmup, barrier)
     # end to end: pinned host activations in, host results out, every step
-    ms.make_host()
+    if plan is None:
+        ms.make_host()
     if sharded and world > 1:
         for it in ms.items:
             it["x_host"] = it["x"].cpu().pin_memory()
@@ -400,6 +437,10 @@ def run_ours(args, rank, world, local_rank):
                 it["x_stage"].copy_(it["x_host"], non_blocking=True)
                 full = sh.mul_mat(it["x_stage"])
                 it["full_host"].copy_(full, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+    elif plan is not None:
+        def step_host():                                       # ONE packed H2D, the graph, ONE packed D2H
+            plan.run_host(ms.plan_in_host, ms.plan_out_host)
             torch.cuda.current_stream().synchronize()
     else:
         def step_host():
@@ -422,7 +463,7 @@ def run_ours(args, rank, world, local_rank):
     value = total_bytes / (per_step_ms * 1e-3) / 1e9
     e2e_val = total_bytes / (ms_e2e / args.steps * 1e-3) / 1e9
     # dominant kernel = the GEMV: per-launch algorithmic bytes / average launch slot inside the timed region
-    n_gemv = len(ms.items)
+    n_gemv = int(launches_per_step) if plan is not None else len(ms.items)
     per_launch_bytes = ms.algo_bytes / n_gemv
     per_launch_us = per_step_ms * 1e3 / n_gemv
     achieved = per_launch_bytes / per_launch_us / 1e3
@@ -430,11 +471,14 @@ def run_ours(args, rank, world, local_rank):
             "warmup": args.warmup, "ms_per_step": round(per_step_ms, 5), "higher_is_better": True,
             "scaling": "strong" if sharded else "weak", "vs_baseline": None,
             "dtype": "int8 x uint4 -> int32, f32 scales", "data": "synthetic (random valid block_q4_K bytes, N(0,1) activations)",
-            "config": {"workload": workload_name(args.workload), "batch": N, "mul_mats": n_gemv,
+            "config": {"workload": workload_name(args.workload), "batch": N, "mul_mats": len(ms.items),
                        "weight_bytes_per_step_per_gpu": ms.weight_bytes,
                        "l2": f"no flush needed: each step streams {ms.weight_bytes >> 20} MiB of distinct weights per GPU (> 126 MiB L2)"
                              if ms.weight_bytes > L2_BYTES else "WARNING: per-GPU weights fit in L2",
-                       "launch": "CUDA graph replay of the C-ABI launches" if gathered is None else f"gather={gather_kind}",
+                       "launch": (f"q4k_plan_run: one CUDA graph of {int(launches_per_step)} launches (q/k/v and gate/up fused, shared activations)"
+                                  if plan is not None else "CUDA graph replay of the C-ABI launches") if gathered is None else f"gather={gather_kind}",
+                       "e2e_path": "q4k_plan_run_host: one packed H2D + graph + one packed D2H per step" if plan is not None
+                                   else "host buffers per mul_mat",
                        "parallelism": f"rowshard{world}" if sharded else f"replica{world}"},
             "decode_tok_s": round(1e3 / per_step_ms, 1) if not sharded else None,
             "pct_of_nominal_8TBs": round(100 * value / world / HBM_NOMINAL_GBS, 2),
@@ -471,6 +515,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="sharded path: plain stream launches")
     ap.add_argument("--gather", default="auto", choices=["auto", "nccl", "peer"], help="row-shard output exchange (N > 1 GPUs)")
+    ap.add_argument("--no-plan", dest="plan", action="store_false", help="single GPU: one q4k_mul_mat per launch instead of the graph plan")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--shapes", action="store_true", default=True, help="add the per-shape GEMV table (C1/C4/C5) and the prefill GEMM figures")
     ap.add_argument("--no-shapes", dest="shapes", action="store_false")

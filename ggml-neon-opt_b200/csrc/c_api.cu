@@ -20,6 +20,9 @@ static std::atomic<int64_t> g_launches{0};
 static thread_local int t_last_cuda_error = 0;
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+void add_launches(int64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int64_t launch_count() { return g_launches.load(std::memory_order_relaxed); }
+bool gemv_exact_policy(int N);
 
 int sm_count() {
     static int cached[64] = {0};
@@ -46,7 +49,9 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 static int64_t g_fuse_limit = 32768;   // N*K floats up to which the quantizer is fused into the GEMV launch
 static int g_gemm_enabled = 1;          // 0: N > 8 takes the decode kernel eight columns at a time (development)
 static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
-static bool gemv_exact_for(int N) {
+bool gemv_exact_policy(int N);
+static bool gemv_exact_for(int N) { return gemv_exact_policy(N); }
+bool gemv_exact_policy(int N) {
     int &mode = g_order_mode;
     if (mode < 0) {
         const char *e = getenv("Q4K_GEMV_ORDER");
@@ -219,6 +224,23 @@ int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_r
                                                   nullptr, dst_col_stride_bytes, gemv_exact_for((int)N), 0, g_gemv_pdl != 0,
                                                   (cudaStream_t)stream, dst_peers, n_peers, dst_row0);
     if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;     // activations too large for one shared-memory residency
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+int q4k_mul_mat_group(int n_mats, const void *const *w_dev, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                      const float *const *x_dev, int64_t N, int64_t x_row_stride_bytes, float *const *dst_dev, void *stream) {
+    if (n_mats < 1 || n_mats > 4 || N < 1 || N > Q4K_GEMV_MAX_N) return Q4K_ERR_UNSUPPORTED;
+    if (K <= 0 || K % Q4K_QK_K != 0 || !w_dev || !M || !x_dev || !dst_dev) return Q4K_ERR_BAD_SHAPE;
+    const int64_t nb = K / Q4K_QK_K;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15)) return Q4K_ERR_BAD_SHAPE;
+    if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15)) return Q4K_ERR_BAD_SHAPE;
+    for (int i = 0; i < n_mats; ++i) {
+        if (M[i] < 0) return Q4K_ERR_BAD_SHAPE;
+        if (!w_dev[i] || !x_dev[i] || !dst_dev[i] || !aligned16(w_dev[i]) || !aligned16(x_dev[i])) return Q4K_ERR_BAD_POINTER;
+    }
+    const cudaError_t e = launch_gemv_q4k_group(n_mats, w_dev, M, K, w_row_stride_bytes, x_dev, (int)N, x_row_stride_bytes, dst_dev,
+                                                gemv_exact_for((int)N), g_gemv_pdl != 0, (cudaStream_t)stream);
+    if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 

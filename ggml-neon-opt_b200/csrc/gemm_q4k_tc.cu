@@ -12,7 +12,7 @@
 // whole 256-wide superblock in two TMEM accumulators.  The mins ride the tensor core too: summ = A_m . q8 with
 // A_m[k] = m[sub-block of k] (<= 63), a third accumulator.  One TMEM drain per superblock instead of one per
 // 32-wide sub-block; the fp32 scales d_w*d_x, dmin_w*d_x are applied by the epilogue warps per superblock,
-// sequentially over superblocks (the NEON order of the reference; within 1e-5 of the AVX2 oracle).
+// sequentially over superblocks (the NEON order of the reference; within 1e-5 of the AVX2 order).
 //
 // CTA = 128 weight rows x 128 activation columns, 21 warps, warp-specialised:
 //   warps 0-15  epilogue: thread <-> TMEM lane (= weight row); group g = warp / 4 owns columns 32g..32g+31 (groups

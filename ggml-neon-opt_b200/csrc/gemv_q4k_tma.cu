@@ -56,8 +56,16 @@ struct TmaGemvParams {
     int n_dst;
     int64_t dst_row0;       // first row of this shard inside the (full) output column
     int64_t dst_stride;
-    int64_t n_groups;       // ceil(M / 4)
+    int64_t n_groups;       // total 4-row groups of the launch
     int stages;
+    // horizontally fused launch: up to 4 independent matrices with the same K and N (q/k/v, gate/up ...).  Row groups
+    // are numbered through all of them; gend[i] = groups of matrices 0..i.  nmat == 1 uses w / M / dst above.
+    int nmat, nx;
+    const uint8_t *wm[4];
+    int64_t Mm[4], gend[4];
+    float *dstm[4];
+    const float *xsrc[4];   // the nx distinct F32 activation buffers; xslot[i] = which one matrix i reads
+    int xslot[4];
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -118,9 +126,9 @@ __device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, 
 template <int N>
 __device__ __forceinline__ void stage_f32(const TmaGemvParams &p, uint8_t *q8_s, float *d_s) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5, nb = p.nb;
-    for (int blk = warp; blk < N * nb; blk += nwarps) {
-        const int n = blk / nb, b = blk - n * nb;
-        const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(p.xf) + n * p.x_stride) + b * QK_K;
+    for (int blk = warp; blk < p.nx * N * nb; blk += nwarps) {
+        const int xs = blk / (N * nb), rem = blk - xs * N * nb, n = rem / nb, b = rem - n * nb;
+        const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(p.xsrc[xs]) + n * p.x_stride) + b * QK_K;
         const float4 a = reinterpret_cast<const float4 *>(src)[lane];       // plain (coherent) loads: with PDL the
         const float4 c = reinterpret_cast<const float4 *>(src)[32 + lane];  // producer kernel may still have been running when this one started
         const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
@@ -154,8 +162,8 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
     const int r = lane >> 3, b = lane & 7;        // int phase: row r of the tile, superblock b; chain phase: (r, t = b)
 
     size_t off = 0;
-    uint8_t *q8_s = smem;                                  off += (size_t)N * nb * Q8_STRIDE;
-    float *d_s = reinterpret_cast<float *>(smem + off);    off += ((size_t)N * nb * 4 + 127) & ~(size_t)127;
+    uint8_t *q8_s = smem;                                  off += (size_t)p.nx * N * nb * Q8_STRIDE;
+    float *d_s = reinterpret_cast<float *>(smem + off);    off += ((size_t)p.nx * N * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
     uint8_t *wbuf = smem + off + (size_t)warp * S * STAGE_BYTES;   off += (size_t)WARPS * S * STAGE_BYTES;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + off) + warp * S;   off += (size_t)WARPS * S * 8;
@@ -203,11 +211,14 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
         }
         __syncwarp();
         if (lane < TILE_ROWS) {
-            int64_t row = cur_rg * TILE_ROWS + lane;
-            if (row >= p.M) row = p.M - 1;            // ragged last group: stay in bounds, result is not stored
+            int mat = 0;
+            int64_t lg = cur_rg;                      // row group inside its matrix
+            while (mat + 1 < p.nmat && cur_rg >= p.gend[mat]) { lg = cur_rg - p.gend[mat]; ++mat; }
+            int64_t row = lg * TILE_ROWS + lane;
+            if (row >= p.Mm[mat]) row = p.Mm[mat] - 1;   // ragged last group: stay in bounds, result is not stored
             fence_proxy_async();                      // the warp's generic reads of this slot are done (after __syncwarp)
             bulk_g2s(smem_u32(wbuf + (size_t)s * STAGE_BYTES + lane * ROW_BYTES),
-                     p.w + row * p.w_stride + (int64_t)prod_ks * ROW_BYTES, bytes, bar);
+                     p.wm[mat] + row * p.w_stride + (int64_t)prod_ks * ROW_BYTES, bytes, bar);
         }
         ++prod_ks;
     };
@@ -233,6 +244,9 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
         const int ks = mt.y;
         const int nsb = min(TILE_SB, nb - ks * TILE_SB);
         const bool active = b < nsb;
+        int mat = 0, lgrp = mt.x;
+        while (mat + 1 < p.nmat && mt.x >= (int)p.gend[mat]) { lgrp = mt.x - (int)p.gend[mat]; ++mat; }
+        const int abase = p.xslot[mat] * N;                 // first staged activation row of this matrix's input
 
         // the lane's superblock: shared memory -> registers, then the slot goes back to the copy engine
         uint4 hdr, q[8];
@@ -262,7 +276,7 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
                 const int sc_lo16 = (int)((scw & 0xffu) << 4), sc_hi = (int)((scw >> 8) & 0xffu);
 #pragma unroll
                 for (int n = 0; n < N; ++n) {
-                    const uint8_t *yb = q8_s + (size_t)(n * nb + kb) * Q8_STRIDE + 64 * g;
+                    const uint8_t *yb = q8_s + (size_t)((abase + n) * nb + kb) * Q8_STRIDE + 64 * g;
                     const uint4 y0 = lds128(yb), y1 = lds128(yb + 16), y2 = lds128(yb + 32), y3 = lds128(yb + 48);
                     const uint32_t ylo[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
                     const uint32_t yhi[8] = {y2.x, y2.y, y2.z, y2.w, y3.x, y3.y, y3.z, y3.w};
@@ -286,8 +300,8 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
             }
 #pragma unroll
             for (int n = 0; n < N; ++n) {
-                const uint4 ps = lds128(q8_s + (size_t)(n * nb + kb) * Q8_STRIDE + 256);
-                const float yd = d_s[n * nb + kb];
+                const uint4 ps = lds128(q8_s + (size_t)((abase + n) * nb + kb) * Q8_STRIDE + 256);
+                const float yd = d_s[(abase + n) * nb + kb];
                 const float dall = __fmul_rn(yd, dd.x), dmn = __fmul_rn(-yd, dd.y);
                 // _mm_madd_epi16(mins, hadd(bsums)): prod_i = m[2i] * ps[2i] + m[2i+1] * ps[2i+1]
                 const int p0 = __dp2a_lo((int)ps.x, (int)sm.z, 0), p1 = __dp2a_hi((int)ps.y, (int)sm.z, 0);
@@ -331,7 +345,7 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
             }
         }
         if (ks == ksteps - 1) {                              // row group finished: horizontal sums + store
-            const int64_t row = (int64_t)mt.x * TILE_ROWS + r;
+            const int64_t row = (int64_t)lgrp * TILE_ROWS + r;
 #pragma unroll
             for (int n = 0; n < N; ++n) {
                 float a = acc[n], m = accm[n];
@@ -348,11 +362,15 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
                     a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, 2));
                     a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, 4));
                 }
-                if (b == 0 && row < p.M) {
-                    // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
-                    const int64_t o = (int64_t)n * p.dst_stride + p.dst_row0 + row;
-                    p.dst[0][o] = a;
-                    for (int g = 1; g < p.n_dst; ++g) p.dst[g][o] = a;
+                if (b == 0 && row < p.Mm[mat]) {
+                    if (p.nmat == 1) {
+                        // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
+                        const int64_t o = (int64_t)n * p.dst_stride + p.dst_row0 + row;
+                        p.dst[0][o] = a;
+                        for (int g = 1; g < p.n_dst; ++g) p.dst[g][o] = a;
+                    } else {
+                        p.dstm[mat][(int64_t)n * p.Mm[mat] + row] = a;      // fused launches write dense [N][M_i] results
+                    }
                 }
                 acc[n] = 0.0f; accm[n] = 0.0f;
             }
@@ -367,9 +385,9 @@ namespace {
 
 constexpr size_t SMEM_MAX = 232448;      // 227 KB per CTA on sm_100
 
-size_t fixed_smem(int N, int nb, bool exact) {
-    size_t off = (size_t)N * nb * Q8_STRIDE;
-    off += ((size_t)N * nb * 4 + 127) & ~(size_t)127;
+size_t fixed_smem(int nrows, int nb, bool exact, int N) {    // nrows = staged activation rows (N per distinct input)
+    size_t off = (size_t)nrows * nb * Q8_STRIDE;
+    off += ((size_t)nrows * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
     off += 16;                                               // row-group counter
     if (exact) off += (size_t)WARPS * N * SCR_WORDS * 4;
@@ -380,7 +398,7 @@ constexpr size_t PER_STAGE = (size_t)WARPS * (STAGE_BYTES + 16);
 template <int N, bool EXACT>
 cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
     auto kern = gemv_q4k_tma_kernel<N, EXACT>;
-    const size_t fixed = fixed_smem(N, p.nb, EXACT);
+    const size_t fixed = fixed_smem(N * p.nx, p.nb, EXACT, N);
     if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
     // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits
     int stages = want_stages > 0 ? want_stages : 2;
@@ -450,7 +468,40 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.dst_stride = dst_col_stride_bytes / 4;
     p.n_groups = (M + TILE_ROWS - 1) / TILE_ROWS;
     p.stages = 0;
+    p.nmat = 1; p.nx = 1;
+    for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
+    p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
     return exact_order ? launch_tma_e<true>(N, p, stages, pdl, stream) : launch_tma_e<false>(N, p, stages, pdl, stream);
+}
+
+// Horizontally fused decode launch: nmat (<= 4) independent matrices with the same K and N in ONE launch; matrices
+// that read the same activations (q/k/v, gate/up) share one staged copy.  F32 activations only; results are dense
+// [N][M_i].  cudaErrorNotSupported when the staged activations do not fit.
+cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                                  const float *const *x, int N, int64_t x_row_stride_bytes, float *const *dst,
+                                  bool exact_order, bool pdl, cudaStream_t stream) {
+    if (nmat < 1 || nmat > 4) return cudaErrorInvalidValue;
+    TmaGemvParams p;
+    p.w = (const uint8_t *)w[0]; p.M = M[0]; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
+    p.xq = nullptr; p.xf = x[0]; p.x_stride = x_row_stride_bytes;
+    for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
+    p.dst[0] = dst[0]; p.n_dst = 1; p.dst_row0 = 0; p.dst_stride = M[0];
+    p.stages = 0; p.nmat = nmat; p.nx = 0;
+    int64_t groups = 0;
+    for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
+    for (int i = 0; i < nmat; ++i) {
+        p.wm[i] = (const uint8_t *)w[i]; p.Mm[i] = M[i]; p.dstm[i] = dst[i];
+        groups += (M[i] + TILE_ROWS - 1) / TILE_ROWS;
+        p.gend[i] = groups;
+        int slot = -1;
+        for (int j = 0; j < p.nx; ++j) if (p.xsrc[j] == x[i]) slot = j;
+        if (slot < 0) { slot = p.nx; p.xsrc[p.nx++] = x[i]; }
+        p.xslot[i] = slot;
+    }
+    p.n_groups = groups;
+    if (groups == 0 || N == 0) return cudaSuccess;
+    if (groups > 0x7fffffff) return cudaErrorInvalidValue;
+    return exact_order ? launch_tma_e<true>(N, p, 0, pdl, stream) : launch_tma_e<false>(N, p, 0, pdl, stream);
 }
 
 }  // namespace q4k

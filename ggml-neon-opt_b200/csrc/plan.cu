@@ -1,0 +1,193 @@
+// plan.cu — graph plans for the Q4_K mul_mat path (q4k_plan_* of include/q4k_b200.h).
+//
+// The reference's backend interface has optional graph plans (graph_plan_create / graph_plan_compute,
+// L/ggml/src/ggml-backend-impl.h:100-108): "compute graph with a plan".  This is that idea for a sequence of Q4_K
+// mul_mats: record once, replay as one CUDA graph.  What the plan adds over calling q4k_mul_mat in a loop:
+//   * the launches are captured with their programmatic-dependent-launch edges, so a replay costs one graph launch
+//     and the weight prefetch of kernel i + 1 overlaps the tail of kernel i;
+//   * consecutive mul_mats that read the same activations (q/k/v, gate/up) are fused into one launch;
+//   * inputs and outputs are packed into two device buffers, so a host caller does ONE H2D and ONE D2H per replay
+//     instead of one pair per mul_mat.
+#include "../../include/q4k_b200.h"
+
+#include <cstdio>
+#include <vector>
+
+#include "q4k_kernels.h"
+
+namespace q4k {
+int note_cuda_error(cudaError_t e);      // c_api.cu
+bool gemv_exact_policy(int N);           // c_api.cu
+}
+
+struct q4k_plan {
+    struct Item {
+        const void *w;
+        int64_t M, K, w_stride, N;
+        int input_id;
+        size_t out_off;
+    };
+    struct Input {
+        int id;
+        int64_t N, K;
+        size_t off;
+    };
+    int device = 0;
+    std::vector<Item> items;
+    std::vector<Input> inputs;
+    size_t in_bytes = 0, out_bytes = 0, ws_bytes = 0;
+    char *in_dev = nullptr, *out_dev = nullptr, *ws_dev = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches = 0;
+    bool finalized = false;
+
+    const Input *find_input(int id) const {
+        for (const auto &in : inputs) if (in.id == id) return &in;
+        return nullptr;
+    }
+};
+
+namespace {
+
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// enqueue every launch of the plan on `st` (used once, under stream capture)
+int enqueue_all(q4k_plan *p, cudaStream_t st) {
+    size_t i = 0;
+    while (i < p->items.size()) {
+        const q4k_plan::Item &a = p->items[i];
+        size_t j = i + 1;
+        if (a.N <= Q4K_GEMV_MAX_N) {
+            while (j < p->items.size() && j - i < 4 && p->items[j].input_id == a.input_id && p->items[j].K == a.K &&
+                   p->items[j].N == a.N && p->items[j].w_stride == a.w_stride) ++j;
+        }
+        const q4k_plan::Input *in = p->find_input(a.input_id);
+        const float *x = reinterpret_cast<const float *>(p->in_dev + in->off);
+        int rc = Q4K_ERR_UNSUPPORTED;
+        if (j - i > 1) {
+            const void *w[4];
+            int64_t M[4];
+            const float *xs[4];
+            float *dst[4];
+            for (size_t k = i; k < j; ++k) {
+                w[k - i] = p->items[k].w; M[k - i] = p->items[k].M; xs[k - i] = x;
+                dst[k - i] = reinterpret_cast<float *>(p->out_dev + p->items[k].out_off);
+            }
+            rc = q4k_mul_mat_group((int)(j - i), w, M, a.K, a.w_stride, xs, a.N, a.K * 4, dst, st);
+            if (rc != Q4K_OK && rc != Q4K_ERR_UNSUPPORTED) return rc;
+        }
+        if (rc == Q4K_ERR_UNSUPPORTED) {            // not fusable (or a single mul_mat): one q4k_mul_mat each
+            for (size_t k = i; k < j; ++k) {
+                const q4k_plan::Item &b = p->items[k];
+                rc = q4k_mul_mat(b.w, b.M, b.K, b.w_stride, x, b.N, b.K * 4, reinterpret_cast<float *>(p->out_dev + b.out_off), b.M * 4,
+                                 p->ws_dev, p->ws_bytes, st);
+                if (rc != Q4K_OK) return rc;
+            }
+        }
+        i = j;
+    }
+    return Q4K_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+q4k_plan *q4k_plan_create(int device) {
+    if (!q4k_device_ok(device)) return nullptr;
+    q4k_plan *p = new q4k_plan;
+    p->device = device;
+    return p;
+}
+
+int q4k_plan_add_mul_mat(q4k_plan *p, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N, int input_id) {
+    if (!p || p->finalized) return Q4K_ERR_UNSUPPORTED;
+    if (!w_dev) return Q4K_ERR_BAD_POINTER;
+    if (M <= 0 || N <= 0 || K <= 0 || K % Q4K_QK_K != 0 || w_row_stride_bytes < K / Q4K_QK_K * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15))
+        return Q4K_ERR_BAD_SHAPE;
+    const q4k_plan::Input *in = p->find_input(input_id);
+    if (in && (in->N != N || in->K != K)) return Q4K_ERR_BAD_SHAPE;        // one input_id = one [N][K] buffer
+    if (!in) {
+        p->inputs.push_back({input_id, N, K, p->in_bytes});
+        p->in_bytes += align256((size_t)N * K * 4);
+    }
+    p->items.push_back({w_dev, M, K, w_row_stride_bytes, N, input_id, p->out_bytes});
+    p->out_bytes += align256((size_t)N * M * 4);
+    const size_t ws = q4k_mul_mat_workspace_bytes(K, N);
+    if (ws > p->ws_bytes) p->ws_bytes = ws;
+    return (int)p->items.size() - 1;
+}
+
+int q4k_plan_finalize(q4k_plan *p) {
+    if (!p || p->finalized || p->items.empty()) return Q4K_ERR_UNSUPPORTED;
+    cudaError_t e = cudaSetDevice(p->device);
+    if (e != cudaSuccess) return q4k::note_cuda_error(e);
+    if ((e = cudaMalloc(&p->in_dev, p->in_bytes)) != cudaSuccess) return q4k::note_cuda_error(e);
+    if ((e = cudaMalloc(&p->out_dev, p->out_bytes)) != cudaSuccess) return q4k::note_cuda_error(e);
+    if ((e = cudaMalloc(&p->ws_dev, p->ws_bytes ? p->ws_bytes : 16)) != cudaSuccess) return q4k::note_cuda_error(e);
+    if ((e = cudaMemset(p->in_dev, 0, p->in_bytes)) != cudaSuccess) return q4k::note_cuda_error(e);
+    cudaStream_t cs = nullptr;
+    if ((e = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking)) != cudaSuccess) return q4k::note_cuda_error(e);
+    // one eager pass first: per-kernel attributes (dynamic shared memory opt-in) are set outside the capture
+    int rc = enqueue_all(p, cs);
+    if (rc == Q4K_OK && (e = cudaStreamSynchronize(cs)) != cudaSuccess) rc = q4k::note_cuda_error(e);
+    if (rc != Q4K_OK) { cudaStreamDestroy(cs); return rc; }
+    const int64_t before = q4k::launch_count();
+    if ((e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal)) != cudaSuccess) { cudaStreamDestroy(cs); return q4k::note_cuda_error(e); }
+    rc = enqueue_all(p, cs);
+    e = cudaStreamEndCapture(cs, &p->graph);
+    p->launches = q4k::launch_count() - before;
+    if (rc != Q4K_OK || e != cudaSuccess) { cudaStreamDestroy(cs); return rc != Q4K_OK ? rc : q4k::note_cuda_error(e); }
+    e = cudaGraphInstantiate(&p->exec, p->graph, 0);
+    cudaStreamDestroy(cs);
+    if (e != cudaSuccess) return q4k::note_cuda_error(e);
+    p->finalized = true;
+    return Q4K_OK;
+}
+
+size_t q4k_plan_input_bytes(const q4k_plan *p) { return p ? p->in_bytes : 0; }
+size_t q4k_plan_output_bytes(const q4k_plan *p) { return p ? p->out_bytes : 0; }
+int64_t q4k_plan_input_offset(const q4k_plan *p, int input_id) {
+    const q4k_plan::Input *in = p ? p->find_input(input_id) : nullptr;
+    return in ? (int64_t)in->off : -1;
+}
+int64_t q4k_plan_output_offset(const q4k_plan *p, int index) {
+    return (p && index >= 0 && (size_t)index < p->items.size()) ? (int64_t)p->items[index].out_off : -1;
+}
+void *q4k_plan_input_dev(q4k_plan *p) { return p ? p->in_dev : nullptr; }
+void *q4k_plan_output_dev(q4k_plan *p) { return p ? p->out_dev : nullptr; }
+int64_t q4k_plan_launches(const q4k_plan *p) { return p ? p->launches : 0; }
+
+int q4k_plan_run(q4k_plan *p, void *stream) {
+    if (!p || !p->finalized) return Q4K_ERR_UNSUPPORTED;
+    const cudaError_t e = cudaGraphLaunch(p->exec, (cudaStream_t)stream);
+    if (e != cudaSuccess) return q4k::note_cuda_error(e);
+    q4k::add_launches(p->launches);
+    return Q4K_OK;
+}
+
+int q4k_plan_run_host(q4k_plan *p, const void *in_host, void *out_host, void *stream) {
+    if (!p || !p->finalized) return Q4K_ERR_UNSUPPORTED;
+    if (!in_host || !out_host) return Q4K_ERR_BAD_POINTER;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemcpyAsync(p->in_dev, in_host, p->in_bytes, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return q4k::note_cuda_error(e);
+    const int rc = q4k_plan_run(p, stream);
+    if (rc != Q4K_OK) return rc;
+    e = cudaMemcpyAsync(out_host, p->out_dev, p->out_bytes, cudaMemcpyDeviceToHost, st);
+    return e == cudaSuccess ? Q4K_OK : q4k::note_cuda_error(e);
+}
+
+void q4k_plan_destroy(q4k_plan *p) {
+    if (!p) return;
+    cudaSetDevice(p->device);
+    if (p->exec) cudaGraphExecDestroy(p->exec);
+    if (p->graph) cudaGraphDestroy(p->graph);
+    cudaFree(p->in_dev);
+    cudaFree(p->out_dev);
+    cudaFree(p->ws_dev);
+    delete p;
+}
+
+}  // extern "C"

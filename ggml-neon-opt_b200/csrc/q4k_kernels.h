@@ -27,6 +27,11 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
                                     bool pdl, cudaStream_t stream,
                                     float *const *peer_dst = nullptr, int n_peers = 0, int64_t dst_row0 = 0);
 
+// up to 4 matrices (same K, N) in one launch; see gemv_q4k_tma.cu
+cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                                  const float *const *x, int N, int64_t x_row_stride_bytes, float *const *dst,
+                                  bool exact_order, bool pdl, cudaStream_t stream);
+
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, int64_t N, int64_t xq_row_stride_bytes,
@@ -43,6 +48,8 @@ cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride
 
 extern int g_gemv_config;   // development knob, see gemv_q4k.cu
 extern int g_gemv_pdl;      // 1 = launch the GEMV with programmatic stream serialization (default)
+void add_launches(int64_t n);  // launches replayed through a CUDA graph
+int64_t launch_count();
 int sm_count();               // multiprocessors of the current device (cached)
 
 }  // namespace q4k

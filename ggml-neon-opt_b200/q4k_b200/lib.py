@@ -52,6 +52,29 @@ def load():
         L.q4k_mul_mat_host.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_host_async.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_peers.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp]
+        L.q4k_mul_mat_group.argtypes = [i32, vp, vp, i64, i64, vp, i64, i64, vp, vp]
+        L.q4k_plan_create.argtypes = [i32]
+        L.q4k_plan_create.restype = vp
+        L.q4k_plan_add_mul_mat.argtypes = [vp, vp, i64, i64, i64, i64, i32]
+        L.q4k_plan_finalize.argtypes = [vp]
+        L.q4k_plan_input_bytes.argtypes = [vp]
+        L.q4k_plan_input_bytes.restype = sz
+        L.q4k_plan_output_bytes.argtypes = [vp]
+        L.q4k_plan_output_bytes.restype = sz
+        L.q4k_plan_input_offset.argtypes = [vp, i32]
+        L.q4k_plan_input_offset.restype = i64
+        L.q4k_plan_output_offset.argtypes = [vp, i32]
+        L.q4k_plan_output_offset.restype = i64
+        L.q4k_plan_input_dev.argtypes = [vp]
+        L.q4k_plan_input_dev.restype = vp
+        L.q4k_plan_output_dev.argtypes = [vp]
+        L.q4k_plan_output_dev.restype = vp
+        L.q4k_plan_launches.argtypes = [vp]
+        L.q4k_plan_launches.restype = i64
+        L.q4k_plan_run.argtypes = [vp, vp]
+        L.q4k_plan_run_host.argtypes = [vp, vp, vp, vp]
+        L.q4k_plan_destroy.argtypes = [vp]
+        L.q4k_plan_destroy.restype = None
         L.q4k_debug_set_fuse_limit.argtypes = [i64]
         L.q4k_debug_set_pdl.argtypes = [i32]
         L.q4k_debug_set_gemv_order.argtypes = [i32]
@@ -182,3 +205,112 @@ def mul_mat_host(w: torch.Tensor, x_host: torch.Tensor, dst_host: torch.Tensor, 
         _check("q4k_mul_mat_host", load().q4k_mul_mat_host(w.data_ptr(), plan.M, plan.K, w.stride(0), x_host.data_ptr(), plan.N,
                                                            dst_host.data_ptr(), plan.x_stage.data_ptr(), plan.dst_stage.data_ptr(),
                                                            plan.ws.data_ptr(), plan.ws.numel(), _stream()))
+
+
+def mul_mat_group(ws, xs, outs=None):
+    """Horizontally fused decode launch (q4k_mul_mat_group): up to 4 Q4_K matrices with the same K, F32 inputs xs[i]
+    [N, K] (N <= 8; the same tensor may repeat) -> list of float32 [N, M_i]."""
+    n = len(ws)
+    if n != len(xs) or not 1 <= n <= 4:
+        raise ValueError("1..4 matrices, one input each")
+    N, K = xs[0].shape
+    for w, x in zip(ws, xs):
+        _dev_u8(w, "w")
+        if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and tuple(x.shape) == (N, K)):
+            raise TypeError("xs: contiguous CUDA float32 [N, K], same shape for all")
+        if w.shape[1] != K // QK_K * Q4K_BLOCK or w.stride(0) != ws[0].stride(0):
+            raise ValueError("shape mismatch between w and x")
+    if outs is None:
+        outs = [torch.empty((N, w.shape[0]), dtype=torch.float32, device=w.device) for w in ws]
+    vpa, i64a = C.c_void_p * n, C.c_int64 * n
+    with torch.cuda.device(ws[0].device):
+        _check("q4k_mul_mat_group", load().q4k_mul_mat_group(n, vpa(*[w.data_ptr() for w in ws]), i64a(*[w.shape[0] for w in ws]), K,
+                                                             ws[0].stride(0), vpa(*[x.data_ptr() for x in xs]), N, K * 4,
+                                                             vpa(*[o.data_ptr() for o in outs]), _stream()))
+    return outs
+
+
+class GraphPlan:
+    """q4k_plan_*: a fixed sequence of Q4_K mul_mats recorded once and replayed as one CUDA graph, with inputs and
+    outputs packed into two device buffers (one H2D + one D2H per replay for a host caller).
+
+    add(w, N, input_id) -> index; finalize(); input(input_id) / output(index) are torch views of the plan's buffers."""
+
+    def __init__(self, device=0):
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self._L = load()
+        self._p = self._L.q4k_plan_create(self.device.index or 0)
+        if not self._p:
+            raise Q4KError("q4k_plan_create", -5, self._L.q4k_last_cuda_error())
+        self._keep, self._shapes, self._in_shapes = [], [], {}
+        self.finalized = False
+
+    def add(self, w: torch.Tensor, N: int, input_id: int) -> int:
+        _dev_u8(w, "w")
+        M, K = w.shape[0], w.shape[1] // Q4K_BLOCK * QK_K
+        rc = self._L.q4k_plan_add_mul_mat(self._p, w.data_ptr(), M, K, w.stride(0), N, input_id)
+        if rc < 0:
+            raise Q4KError("q4k_plan_add_mul_mat", rc, self._L.q4k_last_cuda_error())
+        self._keep.append(w)
+        self._shapes.append((N, M))
+        self._in_shapes[input_id] = (N, K)
+        return rc
+
+    def finalize(self):
+        with torch.cuda.device(self.device):
+            _check("q4k_plan_finalize", self._L.q4k_plan_finalize(self._p))
+        self.finalized = True
+        self.input_bytes = self._L.q4k_plan_input_bytes(self._p)
+        self.output_bytes = self._L.q4k_plan_output_bytes(self._p)
+        self.launches = self._L.q4k_plan_launches(self._p)
+        self._in = _wrap_device(self._L.q4k_plan_input_dev(self._p), self.input_bytes, self.device)
+        self._out = _wrap_device(self._L.q4k_plan_output_dev(self._p), self.output_bytes, self.device)
+        return self
+
+    def input_offset(self, input_id: int) -> int:
+        return self._L.q4k_plan_input_offset(self._p, input_id)
+
+    def output_offset(self, index: int) -> int:
+        return self._L.q4k_plan_output_offset(self._p, index)
+
+    def input(self, input_id: int) -> torch.Tensor:
+        N, K = self._in_shapes[input_id]
+        off = self.input_offset(input_id)
+        return self._in[off: off + N * K * 4].view(torch.float32).view(N, K)
+
+    def output(self, index: int) -> torch.Tensor:
+        N, M = self._shapes[index]
+        off = self.output_offset(index)
+        return self._out[off: off + N * M * 4].view(torch.float32).view(N, M)
+
+    def run(self):
+        with torch.cuda.device(self.device):
+            _check("q4k_plan_run", self._L.q4k_plan_run(self._p, _stream()))
+
+    def run_host(self, in_host: torch.Tensor, out_host: torch.Tensor):
+        """in_host / out_host: CPU uint8 tensors of input_bytes / output_bytes (pinned for async copies)."""
+        if in_host.numel() * in_host.element_size() != self.input_bytes or out_host.numel() * out_host.element_size() != self.output_bytes:
+            raise ValueError("host buffers must be exactly input_bytes / output_bytes")
+        with torch.cuda.device(self.device):
+            _check("q4k_plan_run_host", self._L.q4k_plan_run_host(self._p, in_host.data_ptr(), out_host.data_ptr(), _stream()))
+
+    def close(self):
+        if self._p:
+            self._in = self._out = None
+            self._L.q4k_plan_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _wrap_device(ptr: int, nbytes: int, device) -> torch.Tensor:
+    """A uint8 torch view of device memory owned by the library (no copy, no ownership)."""
+    class _Mem:
+        pass
+    m = _Mem()
+    m.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+    return torch.as_tensor(m, device=device)

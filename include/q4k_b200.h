@@ -88,6 +88,35 @@ int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_r
                       const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
                       float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream);
 
+/* horizontally fused decode launch: n_mats (<= 4) independent mul_mats with the same K and N (<= 8) in ONE kernel
+ * launch — e.g. attn_q / attn_k / attn_v or ffn_gate / ffn_up of one layer, which the reference runs as separate
+ * ggml_compute_forward_mul_mat nodes.  x_dev[i] may repeat: matrices reading the same activations share one quantized
+ * copy.  Results are dense: dst_dev[i] is [N][M[i]].  Q4K_ERR_UNSUPPORTED when the shapes do not fit one launch. */
+int q4k_mul_mat_group(int n_mats, const void *const *w_dev, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                      const float *const *x_dev, int64_t N, int64_t x_row_stride_bytes, float *const *dst_dev, void *stream);
+
+/* Graph plans — the backend_i.graph_plan_create / graph_plan_compute pair of L/ggml/src/ggml-backend-impl.h:100-108 for
+ * this path: a fixed sequence of Q4_K mul_mats (one decode token's worth, say) recorded once, replayed as ONE CUDA
+ * graph with programmatic-dependent-launch edges.  Inputs (F32 activations, one buffer per input_id) and outputs
+ * (dense [N][M] per mul_mat) are packed into two contiguous device buffers owned by the plan, so a host caller moves
+ * one block in and one block out per replay.  Consecutive mul_mats with the same input_id, K and N <= 8 are fused
+ * into one launch (q4k_mul_mat_group).  All functions return 0 / a negative Q4K_ERR_* code unless noted. */
+typedef struct q4k_plan q4k_plan;
+q4k_plan *q4k_plan_create(int device);                                   /* NULL on failure */
+int       q4k_plan_add_mul_mat(q4k_plan *plan, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                               int64_t N, int input_id);                 /* returns the mul_mat's index (>= 0) */
+int       q4k_plan_finalize(q4k_plan *plan);                             /* allocates staging, captures the graph */
+size_t    q4k_plan_input_bytes(const q4k_plan *plan);
+size_t    q4k_plan_output_bytes(const q4k_plan *plan);
+int64_t   q4k_plan_input_offset(const q4k_plan *plan, int input_id);     /* byte offset of [N][K] floats; -1 if unknown */
+int64_t   q4k_plan_output_offset(const q4k_plan *plan, int index);       /* byte offset of [N][M] floats */
+void     *q4k_plan_input_dev(q4k_plan *plan);
+void     *q4k_plan_output_dev(q4k_plan *plan);
+int64_t   q4k_plan_launches(const q4k_plan *plan);                       /* kernel launches per replay */
+int       q4k_plan_run(q4k_plan *plan, void *stream);                    /* inputs already in the plan's device buffer */
+int       q4k_plan_run_host(q4k_plan *plan, const void *in_host, void *out_host, void *stream);  /* H2D, replay, D2H; async */
+void      q4k_plan_destroy(q4k_plan *plan);
+
 /* same, src1 already Q8_K (vec_dot_type == src1->type branch, ggml-cpu.c:1267): N rows of K/256 blocks */
 int q4k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                    const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,

@@ -1,0 +1,131 @@
+"""GPU: horizontally fused launches (q4k_mul_mat_group) and graph plans (q4k_plan_*) give exactly the bytes the
+one-launch-per-mul_mat path gives, which test_gpu_parity.py pins against the oracle; one case is also checked against
+the oracle directly so this file stands on its own."""
+import numpy as np
+import pytest
+
+from conftest import make_acts, make_weights
+
+pytestmark = pytest.mark.gpu
+
+
+def t(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def bits(a):
+    return a.cpu().numpy().view(np.uint32)
+
+
+@pytest.mark.parametrize("Ms,K,N", [((2048, 256, 256), 2048, 1), ((5632, 5632), 2048, 1), ((37, 4, 129, 1), 512, 2),
+                                    ((64, 64), 4096, 8), ((300,), 1024, 3)])
+def test_group_shared_input_equals_separate_launches(q4k, Ms, K, N):
+    ws = [t(make_weights(M, K, seed=11 + i)) for i, M in enumerate(Ms)]
+    x = t(make_acts(N, K))
+    outs = q4k.mul_mat_group(ws, [x] * len(ws))
+    for w, o in zip(ws, outs):
+        assert np.array_equal(bits(o), bits(q4k.mul_mat(w, x)))
+
+
+def test_group_distinct_inputs(q4k):
+    K, N = 1024, 2
+    ws = [t(make_weights(M, K, seed=3 + i)) for i, M in enumerate((96, 40, 200))]
+    xs = [t(make_acts(N, K, seed=20 + i)) for i in range(3)]
+    xs[2] = xs[0]                                            # a repeat shares the staged copy
+    outs = q4k.mul_mat_group(ws, xs)
+    for w, x, o in zip(ws, xs, outs):
+        assert np.array_equal(bits(o), bits(q4k.mul_mat(w, x)))
+
+
+def test_group_against_oracle(q4k):
+    from oracle import port
+    K = 2048
+    wn = [make_weights(M, K, seed=5 + i) for i, M in enumerate((128, 36))]
+    xn = make_acts(1, K)
+    outs = q4k.mul_mat_group([t(w) for w in wn], [t(xn)] * 2)
+    for w, o in zip(wn, outs):
+        assert np.array_equal(bits(o), port.mul_mat(w, xn, port.ORDER_AVX2).view(np.uint32))
+
+
+def test_group_rejects_bad_arguments(q4k):
+    import torch
+    L = q4k.load()
+    assert L.q4k_mul_mat_group(0, None, None, 256, 144, None, 1, 1024, None, None) == -5
+    assert L.q4k_mul_mat_group(5, None, None, 256, 144, None, 1, 1024, None, None) == -5
+    assert L.q4k_mul_mat_group(1, None, None, 256, 144, None, 9, 1024, None, None) == -5     # N > 8: not a decode launch
+    assert L.q4k_mul_mat_group(1, None, None, 100, 144, None, 1, 400, None, None) == -1
+    del torch
+
+
+def _layer(q4k, N, seed=0):
+    """one transformer layer's Q4_K mul_mats the way the reference graph has them: q/k/v share an input, gate/up too"""
+    K, FF = 512, 1024
+    shapes = [("q", K, K, 0), ("k", 128, K, 0), ("v", 128, K, 0), ("o", K, K, 1), ("gate", FF, K, 2), ("up", FF, K, 2), ("down", K, FF, 3)]
+    ws = [t(make_weights(M, Kk, seed=seed + i)) for i, (_, M, Kk, _) in enumerate(shapes)]
+    return shapes, ws
+
+
+@pytest.mark.parametrize("N", [1, 4, 16])
+def test_plan_replay_equals_individual_mul_mats(q4k, N):
+    import torch
+    shapes, ws = _layer(q4k, N)
+    plan = q4k.GraphPlan(0)
+    idx = [plan.add(w, N, iid) for w, (_, _, _, iid) in zip(ws, shapes)]
+    plan.finalize()
+    assert idx == list(range(len(ws)))
+    if N <= 8:
+        assert plan.launches == 4                      # q+k+v, o, gate+up, down (quantizers fused in)
+    xs = {iid: t(make_acts(N, Kk, seed=40 + iid)) for _, _, Kk, iid in shapes}
+    for rep in range(2):                               # replays see fresh inputs
+        for iid, x in xs.items():
+            plan.input(iid).copy_(x + rep)
+        n0 = q4k.kernel_launches()
+        plan.run()
+        torch.cuda.synchronize()
+        assert q4k.kernel_launches() - n0 == plan.launches
+        for i, (w, (_, _, _, iid)) in enumerate(zip(ws, shapes)):
+            assert np.array_equal(bits(plan.output(i)), bits(q4k.mul_mat(w, xs[iid] + rep))), (rep, i)
+    plan.close()
+
+
+def test_plan_run_host_one_copy_each_way(q4k):
+    import torch
+    N = 1
+    shapes, ws = _layer(q4k, N, seed=9)
+    plan = q4k.GraphPlan(0)
+    for w, (_, _, _, iid) in zip(ws, shapes):
+        plan.add(w, N, iid)
+    plan.finalize()
+    hin = torch.zeros(plan.input_bytes, dtype=torch.uint8).pin_memory()
+    hout = torch.zeros(plan.output_bytes, dtype=torch.uint8).pin_memory()
+    xs = {}
+    for _, _, Kk, iid in shapes:
+        xs[iid] = make_acts(N, Kk, seed=70 + iid)
+        off = plan.input_offset(iid)
+        assert off >= 0 and off % 256 == 0
+        hin[off: off + N * Kk * 4] = torch.from_numpy(xs[iid].view(np.uint8).reshape(-1))
+    assert plan.input_offset(99) == -1 and plan.output_offset(len(ws)) == -1
+    plan.run_host(hin, hout)
+    torch.cuda.synchronize()
+    for i, (w, (_, M, _, iid)) in enumerate(zip(ws, shapes)):
+        off = plan.output_offset(i)
+        got = hout[off: off + N * M * 4].numpy().view(np.uint32).reshape(N, M)
+        assert np.array_equal(got, bits(q4k.mul_mat(w, t(xs[iid]))))
+    plan.close()
+
+
+def test_plan_argument_errors(q4k):
+    w = t(make_weights(8, 512))
+    plan = q4k.GraphPlan(0)
+    L = q4k.load()
+    assert L.q4k_plan_finalize(plan._p) == -5                       # empty plan
+    assert plan.add(w, 1, 0) == 0
+    with pytest.raises(q4k.Q4KError):
+        plan.add(w, 2, 0)                                           # same input_id, different N
+    assert L.q4k_plan_run(plan._p, None) == -5                      # not finalized
+    plan.finalize()
+    with pytest.raises(q4k.Q4KError):
+        plan.add(w, 1, 0)                                           # frozen
+    assert L.q4k_plan_run_host(plan._p, None, None, None) == -2
+    plan.close()
