@@ -484,7 +484,7 @@ def run_ours(args, rank, world, local_rank):
             "pct_of_nominal_8TBs": round(100 * value / world / HBM_NOMINAL_GBS, 2),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
-                         "kernel": "gemv_q4k_tma_kernel (+ quantize_q8_K_kernel in the same launch slot)",
+                         "kernel": "gemv_q4k_mma_kernel (Q8_K quantizer fused into the launch)",
                          "bytes_per_launch": round(per_launch_bytes), "us_per_launch": round(per_launch_us, 3)},
             "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": ms.h2d, "d2h_bytes_per_step": ms.d2h,
                     "ms_per_step": round(ms_e2e / args.steps, 5),

@@ -44,8 +44,10 @@ int note_cuda_error(cudaError_t e) { return cuda_fail(e); }
 
 static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Q4K_GEMV_ORDER=fast selects the cheaper float association for every batch size; default is the
-// reference's AVX2 order (bit-identical fp32) wherever the GEMV stays HBM-bound with it.
+// Float order of the decode path (N <= 8).  Default: the tensor-pipe kernel (gemv_q4k_mma.cu), exact integers and a fixed
+// launch-independent float association, within 1e-5 of the reference.  Q4K_GEMV_ORDER=exact (or
+// q4k_debug_set_gemv_order(1)) selects the kernel that reproduces the reference's AVX2 accumulation order bit for bit
+// (gemv_q4k_tma.cu) at ~10-25% less throughput on small matrices.
 static int64_t g_fuse_limit = 32768;   // N*K floats up to which the quantizer is fused into the GEMV launch
 static int g_gemm_enabled = 1;          // 0: N > 8 takes the decode kernel eight columns at a time (development)
 static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
@@ -57,9 +59,8 @@ bool gemv_exact_policy(int N) {
         const char *e = getenv("Q4K_GEMV_ORDER");
         mode = !e ? 0 : (!strcmp(e, "exact") ? 1 : (!strcmp(e, "fast") ? 2 : 0));
     }
-    if (mode == 1) return true;
-    if (mode == 2) return false;
-    return N <= 2;
+    (void)N;
+    return mode == 1;
 }
 
 }  // namespace q4k

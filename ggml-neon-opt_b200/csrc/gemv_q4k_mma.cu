@@ -1,0 +1,449 @@
+// gemv_q4k_mma.cu — decode GEMV (batch 1..8), integer dot products on the tensor pipe.
+// Replaces the vec_dot loop of ggml_compute_forward_mul_mat_one_chunk (L/ggml/src/ggml-cpu/ggml-cpu.c:1115-1203)
+// + ggml_vec_dot_q4_K_q8_K (L/ggml/src/ggml-cpu/arch/x86/quants.c:1741-1823) for N <= 8, with the
+// quantize_row_q8_K pass (ggml-cpu.c:1267-1307, L/ggml/src/ggml-quants.c:2555-2592) fused in front.
+//
+// Why a second decode kernel.  gemv_q4k_tma.cu does the 4-bit x 8-bit products with dp4a: ~590 issue slots per
+// superblock-lane, which puts a B200 SM at ~75% of its issue rate when HBM runs at peak — the kernel is as much
+// issue-bound as HBM-bound, and a launch whose tiles all land at once (a 2048-row projection) pays the whole
+// burst after the data has arrived.  Here the products go through mma.sync.m16n8k32 (u8 x s8 -> s32, IMMA.16832):
+// ~7 issue slots per superblock-row instead of ~18, for every batch size up to 8 at the same cost.  It is still an
+// HBM-bound streaming kernel — the tensor pipe runs at a few percent of its rate; it is used as a wide dot-product
+// unit, the matrix is never reshaped.  The integers are exact (same sumi / summ as the reference); the float stage
+// is the reference's per-superblock form  acc += (d*dy)*sumi,  accm += (-dmin*dy)*summ  with a fixed, launch-
+// independent association (below), within 1e-5 of ggml_vec_dot_q4_K_q8_K; the bit-identical AVX2 order remains
+// available from gemv_q4k_tma.cu (Q4K_GEMV_ORDER=exact).
+//
+// Work split.  A CTA tile is 16 weight rows (the MMA's m).  Eight consumer warps split K: in every round warp w
+// takes superblock 8*round + w of those 16 rows, so a 2048-column matrix is one round and a 2048-row matrix is
+// 128 tiles x 8 warps.  Warp 8 is the producer: per round it drops the 16 x 1152 contiguous bytes into a shared
+// memory slot with 16 bulk copies (UBLKCP) on an mbarrier; slots are recycled through a second mbarrier that the
+// consumer warps arrive on.  The slot's row pitch is 1152 + 16 (or + 32) bytes so that the fragment loads of the
+// eight row lanes hit distinct banks.
+//
+// Fragments, N == 1 ("columns are sub-blocks").  Lane (r = lane / 4, c = lane % 4) owns rows r and r + 8 and the
+// 32-byte nibble chunk c of the superblock, i.e. sub-blocks 2c (low nibbles) and 2c + 1 (high nibbles).  MMA t
+// (t = 0..7) multiplies word t of every chunk: the k index of the instruction is (chunk, nibble half, byte of the
+// word); the B operand carries the activation word (sub-block j, word t) in column j only, zeros elsewhere, so
+// after the eight MMAs  C[row][j] = dot(sub-block j of the row, activations of sub-block j)  for all eight j at
+// once.  The high-nibble operands are (w & 0xf0f0f0f0), 16 x the value: the lane folds  16*sc_lo*C_lo + sc_hi*C_hi
+// and shifts right by 4 (exact).  N >= 2 ("columns are batch columns"): one MMA per sub-block, k = the 32 bytes
+// of the sub-block, B column n = activations of batch column n.
+//
+// Float association (all N): every lane accumulates its own sub-block pair over the superblocks its warp owns, in
+// order; at the end of the tile the four chunk lanes are summed (xor 1, xor 2), then the eight warps' partials in
+// warp order.  Nothing depends on the grid, the ring depth or the batch size a column is computed in.
+#include <cstdlib>
+
+#include "gemv_stage.cuh"
+#include "q4k_kernels.h"
+
+namespace q4k {
+
+namespace {
+
+constexpr int MROWS = 16;                 // rows per CTA tile
+constexpr int KW = 8;                     // consumer warps = superblocks per round
+constexpr int MMA_THREADS = (KW + 2) * 32;  // 8 consumer warps, the producer warp, the reducer warp
+constexpr int PBUF = 4;                   // partial-sum buffers between the consumer warps and the reducer warp
+
+__device__ __forceinline__ void imma_16832(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint2 lds64(const uint8_t *p) { return *reinterpret_cast<const uint2 *>(p); }
+__device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
+
+template <int N> struct MmaCfg {
+    // shared-memory row pitch of a slot: N == 1 reads 16-byte pieces (quarter-warp = 2 rows x 4 chunks: pitch = 4 words
+    // mod 32), N >= 2 reads 8-byte pieces (half-warp = 4 rows x 4 pieces: pitch = 8 words mod 32)
+    static constexpr int PITCH = N == 1 ? ROW_BYTES + 16 : ROW_BYTES + 32;
+    static constexpr int SLOT = MROWS * PITCH;
+    static constexpr int NC = N == 1 ? 1 : 2;            // result columns held per lane and row
+};
+
+// ---- one superblock column of a slot, N == 1 ---------------------------------------------------------------------
+// acc[0] / accm[0]: row r, acc[1] / accm[1]: row r + 8 (partial over this lane's chunk)
+__device__ __forceinline__ void sb_step_n1(const uint8_t *slot_sb, const uint8_t *y0, const uint8_t *y1, const uint8_t *yblk, float yd,
+                                           int lane, float (&acc)[2], float (&accm)[2]) {
+    constexpr int PITCH = MmaCfg<1>::PITCH;
+    const int r = lane >> 2, c = lane & 3;
+    const uint8_t *p0 = slot_sb + r * PITCH, *p1 = p0 + 8 * PITCH;
+    const uint4 h0 = lds128(p0), h1 = lds128(p1);
+    const uint4 wa = lds128(p0 + 16 + 32 * c), wb = lds128(p0 + 32 + 32 * c);
+    const uint4 va = lds128(p1 + 16 + 32 * c), vb = lds128(p1 + 32 + 32 * c);
+    const uint4 ya = lds128(y0), yb = lds128(y0 + 16), za = lds128(y1), zb = lds128(y1 + 16);
+    const uint32_t w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+    const uint32_t v[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
+    const uint32_t b0[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+    const uint32_t b1[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+    int ce[4] = {0, 0, 0, 0}, co[4] = {0, 0, 0, 0};          // two accumulators: halves the dependent IMMA chain
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        if (t & 1) imma_16832(co, w[t] & 0x0f0f0f0fu, v[t] & 0x0f0f0f0fu, w[t] & 0xf0f0f0f0u, v[t] & 0xf0f0f0f0u, b0[t], b1[t]);
+        else       imma_16832(ce, w[t] & 0x0f0f0f0fu, v[t] & 0x0f0f0f0fu, w[t] & 0xf0f0f0f0u, v[t] & 0xf0f0f0f0u, b0[t], b1[t]);
+    }
+    // C: [0] = (row r, sub-block 2c), [1] = (row r, 2c + 1, x16), [2] / [3] = row r + 8
+    const uint4 u0 = unpack_scales_mins(h0), u1 = unpack_scales_mins(h1);
+    const int sh = 16 * (c & 1);
+    const uint32_t sc0 = ((c < 2 ? u0.x : u0.y) >> sh) & 0xffffu, sc1 = ((c < 2 ? u1.x : u1.y) >> sh) & 0xffffu;
+    const uint32_t mn0 = ((c < 2 ? u0.z : u0.w) >> sh) & 0xffffu, mn1 = ((c < 2 ? u1.z : u1.w) >> sh) & 0xffffu;
+    const int s0 = ((int)((sc0 & 0xffu) << 4) * (ce[0] + co[0]) + (int)(sc0 >> 8) * (ce[1] + co[1])) >> 4;
+    const int s1 = ((int)((sc1 & 0xffu) << 4) * (ce[2] + co[2]) + (int)(sc1 >> 8) * (ce[3] + co[3])) >> 4;
+    const int psw = *reinterpret_cast<const int *>(yblk + 256 + 4 * c);      // pair sums of sub-blocks 2c, 2c + 1
+    const int m0 = __dp2a_lo(psw, (int)mn0, 0), m1 = __dp2a_lo(psw, (int)mn1, 0);
+    const float2 dd0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));   // {d, dmin}
+    const float2 dd1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
+    acc[0] = __fmaf_rn(__fmul_rn(yd, dd0.x), (float)s0, acc[0]);
+    accm[0] = __fmaf_rn(__fmul_rn(-yd, dd0.y), (float)m0, accm[0]);
+    acc[1] = __fmaf_rn(__fmul_rn(yd, dd1.x), (float)s1, acc[1]);
+    accm[1] = __fmaf_rn(__fmul_rn(-yd, dd1.y), (float)m1, accm[1]);
+}
+
+// ---- one superblock column of a slot, 2 <= N <= 8 ------------------------------------------------------------------
+// acc[2 * i + k]: row r + 8 i, batch column 2c + k (complete sums: the MMA reduces over the whole sub-block)
+// ycol: this lane's B column (batch column lane / 4) block, or a zero block when lane / 4 >= N
+// ylo / yhi: the blocks of batch columns 2c and 2c + 1 (for the min products and dy), clamped to a valid column
+template <int N>
+__device__ __forceinline__ void sb_step_nn(const uint8_t *slot_sb, const uint8_t *ycol, const uint8_t *ylo, const uint8_t *yhi,
+                                           float yd_lo, float yd_hi, int lane, float (&acc)[4], float (&accm)[4]) {
+    constexpr int PITCH = MmaCfg<N>::PITCH;
+    const int r = lane >> 2, c = lane & 3;
+    const uint8_t *p0 = slot_sb + r * PITCH, *p1 = p0 + 8 * PITCH;
+    const uint4 h0 = lds128(p0), h1 = lds128(p1);
+    const uint4 u0 = unpack_scales_mins(h0), u1 = unpack_scales_mins(h1);
+    int s[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint2 w = lds64(p0 + 16 + 32 * g + 8 * c), v = lds64(p1 + 16 + 32 * g + 8 * c);
+        const uint2 bl = lds64(ycol + 64 * g + 8 * c), bh = lds64(ycol + 64 * g + 32 + 8 * c);
+        int cl[4] = {0, 0, 0, 0}, ch[4] = {0, 0, 0, 0};
+        imma_16832(cl, w.x & 0x0f0f0f0fu, v.x & 0x0f0f0f0fu, w.y & 0x0f0f0f0fu, v.y & 0x0f0f0f0fu, bl.x, bl.y);
+        imma_16832(ch, w.x & 0xf0f0f0f0u, v.x & 0xf0f0f0f0u, w.y & 0xf0f0f0f0u, v.y & 0xf0f0f0f0u, bh.x, bh.y);
+        const uint32_t q0 = (g < 2 ? u0.x : u0.y) >> (16 * (g & 1)), q1 = (g < 2 ? u1.x : u1.y) >> (16 * (g & 1));
+        const int lo0 = (int)((q0 & 0xffu) << 4), hi0 = (int)((q0 >> 8) & 0xffu);
+        const int lo1 = (int)((q1 & 0xffu) << 4), hi1 = (int)((q1 >> 8) & 0xffu);
+        s[0] += lo0 * cl[0] + hi0 * ch[0];
+        s[1] += lo0 * cl[1] + hi0 * ch[1];
+        s[2] += lo1 * cl[2] + hi1 * ch[2];
+        s[3] += lo1 * cl[3] + hi1 * ch[3];
+    }
+    const float2 dd0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));
+    const float2 dd1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
+    const uint4 pl = lds128(ylo + 256), ph = lds128(yhi + 256);       // the eight pair sums of each column
+    // summ = sum_j m[j] * ps[j]: four dp2a per (row, column)
+    const int ml0 = __dp2a_hi((int)pl.w, (int)u0.w, __dp2a_lo((int)pl.z, (int)u0.w, __dp2a_hi((int)pl.y, (int)u0.z, __dp2a_lo((int)pl.x, (int)u0.z, 0))));
+    const int mh0 = __dp2a_hi((int)ph.w, (int)u0.w, __dp2a_lo((int)ph.z, (int)u0.w, __dp2a_hi((int)ph.y, (int)u0.z, __dp2a_lo((int)ph.x, (int)u0.z, 0))));
+    const int ml1 = __dp2a_hi((int)pl.w, (int)u1.w, __dp2a_lo((int)pl.z, (int)u1.w, __dp2a_hi((int)pl.y, (int)u1.z, __dp2a_lo((int)pl.x, (int)u1.z, 0))));
+    const int mh1 = __dp2a_hi((int)ph.w, (int)u1.w, __dp2a_lo((int)ph.z, (int)u1.w, __dp2a_hi((int)ph.y, (int)u1.z, __dp2a_lo((int)ph.x, (int)u1.z, 0))));
+    acc[0] = __fmaf_rn(__fmul_rn(yd_lo, dd0.x), (float)(s[0] >> 4), acc[0]);
+    acc[1] = __fmaf_rn(__fmul_rn(yd_hi, dd0.x), (float)(s[1] >> 4), acc[1]);
+    acc[2] = __fmaf_rn(__fmul_rn(yd_lo, dd1.x), (float)(s[2] >> 4), acc[2]);
+    acc[3] = __fmaf_rn(__fmul_rn(yd_hi, dd1.x), (float)(s[3] >> 4), acc[3]);
+    accm[0] = __fmaf_rn(__fmul_rn(-yd_lo, dd0.y), (float)ml0, accm[0]);
+    accm[1] = __fmaf_rn(__fmul_rn(-yd_hi, dd0.y), (float)mh0, accm[1]);
+    accm[2] = __fmaf_rn(__fmul_rn(-yd_lo, dd1.y), (float)ml1, accm[2]);
+    accm[3] = __fmaf_rn(__fmul_rn(-yd_hi, dd1.y), (float)mh1, accm[3]);
+}
+
+
+template <int N>
+__global__ void __launch_bounds__(MMA_THREADS, 2)
+gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
+    using Cfg = MmaCfg<N>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int nb = p.nb, S = p.stages;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp == 0) { TICK(0); GTICK(10); }
+
+    size_t off = 0;
+    uint8_t *q8_s = smem;                                   off += (size_t)p.nx * N * nb * Q8_STRIDE;
+    uint8_t *zero_s = smem + off;                           off += Q8_STRIDE;
+    float *d_s = reinterpret_cast<float *>(smem + off);     off += ((size_t)p.nx * N * nb * 4 + 127) & ~(size_t)127;
+    off = (off + 127) & ~(size_t)127;
+    float *part_s = reinterpret_cast<float *>(smem + off);  off += (size_t)PBUF * KW * N * MROWS * 4;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + off);   off += (size_t)S * 8;
+    uint64_t *empty = reinterpret_cast<uint64_t *>(smem + off);  off += (size_t)S * 8;
+    uint64_t *pfull = reinterpret_cast<uint64_t *>(smem + off);  off += (size_t)PBUF * 8;
+    uint64_t *pempty = reinterpret_cast<uint64_t *>(smem + off); off += (size_t)PBUF * 8;
+    off = (off + 127) & ~(size_t)127;
+    uint8_t *slots = smem + off;
+
+    // balanced contiguous range of 16-row tiles for this CTA (n_groups counts tiles here)
+    const int64_t tstep = p.interleave ? gridDim.x : 1;
+    const int64_t t0 = p.interleave ? blockIdx.x : p.n_groups * blockIdx.x / gridDim.x;
+    const int64_t t1 = p.interleave ? p.n_groups : p.n_groups * (blockIdx.x + 1) / gridDim.x;
+    // tile -> (matrix, tile inside the matrix); mat only ever moves forward
+    auto locate = [&](int64_t tile, int &mat) -> int64_t {
+        while (mat + 1 < p.nmat && tile >= p.gend[mat]) ++mat;
+        return mat ? tile - p.gend[mat - 1] : tile;
+    };
+    const int rounds = (nb + KW - 1) / KW;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) { mbar_init(smem_u32(&full[s]), 1); mbar_init(smem_u32(&empty[s]), KW); }
+        for (int b = 0; b < PBUF; ++b) { mbar_init(smem_u32(&pfull[b]), KW); mbar_init(smem_u32(&pempty[b]), 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (threadIdx.x < Q8_STRIDE / 4) reinterpret_cast<uint32_t *>(zero_s)[threadIdx.x] = 0u;
+    __syncthreads();
+    griddep_launch_dependents();
+    if (warp == 0) TICK(1);
+
+    if (warp == KW) {
+        // ---- producer warp: weights never depend on the previous kernel in the stream, so it never waits for it ----
+        int s = 0;
+        uint32_t eparity = 1;                // parity of the phase BEFORE the first one: the first S waits fall through
+        int mat = 0;
+        for (int64_t tile = t0; tile < t1; tile += tstep) {
+            const int64_t lt = locate(tile, mat);
+            int64_t row = lt * MROWS + (lane & 15);
+            if (row >= p.Mm[mat]) row = p.Mm[mat] - 1;          // ragged last tile: stay in bounds, result is not stored
+            const uint8_t *src = p.wm[mat] + row * p.w_stride;
+            for (int rd = 0; rd < rounds; ++rd) {
+                mbar_wait(smem_u32(&empty[s]), eparity);
+                const uint32_t bytes = (uint32_t)min(KW, nb - rd * KW) * BLK_Q4K;
+                const uint32_t bar = smem_u32(&full[s]);
+                if (lane == 0) mbar_expect_tx(bar, bytes * MROWS);
+                __syncwarp();
+                if (lane < MROWS) {
+                    fence_proxy_async();
+                    bulk_g2s(smem_u32(slots + (size_t)s * Cfg::SLOT + lane * Cfg::PITCH), src + (int64_t)rd * ROW_BYTES, bytes, bar);
+                }
+                if (tile == t0 && rd == 0) TICK(9);
+                if (++s == S) { s = 0; eparity ^= 1u; }
+            }
+        }
+        return;
+    }
+
+    if (warp == KW + 1) {
+        // ---- reducer warp: sums the eight warps' partials of a tile in warp order and stores the result rows, so the
+        // consumer warps never meet at a CTA barrier and run on into the next tile ----
+        int mat = 0;
+        int b = 0;
+        uint32_t fparity = 0;
+        for (int64_t tile = t0; tile < t1; tile += tstep) {
+            const int64_t lt = locate(tile, mat);
+            const int64_t m_rows = p.Mm[mat];
+            mbar_wait(smem_u32(&pfull[b]), fparity);
+            for (int i = lane; i < N * MROWS; i += 32) {
+                const int col = i / MROWS, rr = i % MROWS;
+                const float *pp = part_s + (size_t)b * KW * N * MROWS + i;
+                float a = pp[0];
+#pragma unroll
+                for (int w = 1; w < KW; ++w) a = __fadd_rn(a, pp[(size_t)w * N * MROWS]);
+                const int64_t row = lt * MROWS + rr;
+                if (row < m_rows) {
+                    if (p.nmat == 1) {
+                        // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
+                        const int64_t o = (int64_t)col * p.dst_stride + p.dst_row0 + row;
+                        p.dst[0][o] = a;
+                        for (int g = 1; g < p.n_dst; ++g) p.dst[g][o] = a;
+                    } else {
+                        p.dstm[mat][(int64_t)col * m_rows + row] = a;     // fused launches write dense [N][M_i] results
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&pempty[b]));
+            if (++b == PBUF) { b = 0; fparity ^= 1u; }
+        }
+        return;
+    }
+
+    // ---- consumer warps: everything that does not depend on the activations happens before the dependency wait
+    // (parameter loads through the constant cache are ~50 cycles each and chain; the compiler would sink them) ----
+    const int r = lane >> 2, c = lane & 3;
+    StageF32<N> stage;
+    stage.prepare(p, KW * 32);
+    touch_params(p);
+    int mat = 0;
+    locate(t0, mat);
+    int abase = p.xslot[mat] * N;
+    const int nmat = p.nmat;
+    asm volatile("" : "+r"(mat), "+r"(abase));                              // materialised here, not after the wait
+    asm volatile("" ::"r"(nmat));
+    griddep_wait();
+    if (warp == 0) { TICK(2); GTICK(11); }
+    if (p.xq) stage_q8<N>(p, q8_s, d_s, KW * 32);
+    else stage.run(q8_s, d_s);
+    if (warp == 0) TICK(3);
+    named_bar_sync(1, KW * 32);
+    if (warp == 0) TICK(4);
+
+    int s = 0, buf = 0;
+    uint32_t parity = 0, pparity = 1;        // pparity: phase before the first one, the first PBUF waits fall through
+    for (int64_t tile = t0; tile < t1; tile += tstep) {
+        float acc[2 * Cfg::NC], accm[2 * Cfg::NC];
+#pragma unroll
+        for (int i = 0; i < 2 * Cfg::NC; ++i) { acc[i] = 0.0f; accm[i] = 0.0f; }
+
+        for (int rd = 0; rd < rounds; ++rd) {
+            if (warp == 0 && tile == t0 && rd == 0) TICK(14);
+            mbar_wait(smem_u32(&full[s]), parity);
+            if (warp == 0 && tile == t0 && rd == 0) TICK(5);
+            const int kb = rd * KW + warp;
+            if (kb < nb) {
+                const uint8_t *slot_sb = slots + (size_t)s * Cfg::SLOT + warp * BLK_Q4K;
+                if constexpr (N == 1) {
+                    const uint8_t *yblk = q8_s + (size_t)(abase * nb + kb) * Q8_STRIDE;
+                    const int j = r;                                     // this lane's B column = sub-block j
+                    const uint8_t *y0 = (j == 2 * c) ? yblk + 32 * j : zero_s;
+                    const uint8_t *y1 = (j == 2 * c + 1) ? yblk + 32 * j : zero_s;
+                    sb_step_n1(slot_sb, y0, y1, yblk, d_s[abase * nb + kb], lane, acc, accm);
+                } else {
+                    const int ncol = r;                                  // this lane's B column = batch column
+                    const uint8_t *ycol = ncol < N ? q8_s + (size_t)((abase + ncol) * nb + kb) * Q8_STRIDE : zero_s;
+                    const int nlo = min(2 * c, N - 1), nhi = min(2 * c + 1, N - 1);
+                    sb_step_nn<N>(slot_sb, ycol, q8_s + (size_t)((abase + nlo) * nb + kb) * Q8_STRIDE,
+                                  q8_s + (size_t)((abase + nhi) * nb + kb) * Q8_STRIDE,
+                                  d_s[(abase + nlo) * nb + kb], d_s[(abase + nhi) * nb + kb], lane, acc, accm);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&empty[s]));
+            if (++s == S) { s = 0; parity ^= 1u; }
+        }
+
+        if (warp == 0 && tile == t0) TICK(6);
+        // ---- tile epilogue: chunk lanes here, the eight warps in order in the reducer warp ----
+        mbar_wait(smem_u32(&pempty[buf]), pparity);
+        float *part = part_s + (size_t)buf * KW * N * MROWS + (size_t)warp * N * MROWS;
+        if constexpr (N == 1) {
+            float v0 = __fadd_rn(acc[0], accm[0]), v1 = __fadd_rn(acc[1], accm[1]);
+            v0 = __fadd_rn(v0, __shfl_xor_sync(0xffffffffu, v0, 1));
+            v1 = __fadd_rn(v1, __shfl_xor_sync(0xffffffffu, v1, 1));
+            v0 = __fadd_rn(v0, __shfl_xor_sync(0xffffffffu, v0, 2));
+            v1 = __fadd_rn(v1, __shfl_xor_sync(0xffffffffu, v1, 2));
+            if (c == 0) { part[r] = v0; part[r + 8] = v1; }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int col = 2 * c + k;
+                if (col < N) {
+                    part[col * MROWS + r] = __fadd_rn(acc[k], accm[k]);
+                    part[col * MROWS + r + 8] = __fadd_rn(acc[2 + k], accm[2 + k]);
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&pfull[buf]));
+        if (++buf == PBUF) { buf = 0; pparity ^= 1u; }
+        if (tile + tstep < t1) {                                           // the next tile's matrix
+            locate(tile + tstep, mat);
+            abase = p.xslot[mat] * N;
+        }
+        if (warp == 0 && tile + tstep >= t1) { TICK(7); GTICK(12); }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------- launch
+constexpr size_t MMA_SMEM_MAX = 232448;      // 227 KB per CTA on sm_100
+
+int mma_env(const char *name) {              // development knobs (tools/launch_chain.py); unset = 0
+    const char *e = getenv(name);
+    return e ? atoi(e) : 0;
+}
+
+size_t mma_fixed_smem(int nrows, int nb, int N, int S) {
+    size_t off = (size_t)nrows * nb * Q8_STRIDE + Q8_STRIDE;
+    off += ((size_t)nrows * nb * 4 + 127) & ~(size_t)127;
+    off = (off + 127) & ~(size_t)127;
+    off += (size_t)PBUF * KW * N * MROWS * 4 + (size_t)S * 16 + (size_t)PBUF * 16;
+    return ((off + 127) & ~(size_t)127) + 128;
+}
+
+template <int N>
+cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
+    auto kern = gemv_q4k_mma_kernel<N>;
+    const size_t slot = MmaCfg<N>::SLOT;
+    const size_t fixed = mma_fixed_smem(N * p.nx, p.nb, N, 8);
+    // two CTAs per SM with as deep a ring as fits (<= 5 slots: 2 x 5 x 18 KB in flight per SM is past the latency-
+    // bandwidth product); one CTA per SM when the staged activations are too large for that
+    int per_sm = 2;
+    int stages = fixed + 1024 < MMA_SMEM_MAX / 2 ? (int)((MMA_SMEM_MAX / 2 - 1024 - fixed) / slot) : 0;
+    if (stages < 2) {
+        per_sm = 1;
+        stages = fixed < MMA_SMEM_MAX ? (int)((MMA_SMEM_MAX - fixed) / slot) : 0;
+        if (stages < 2) return cudaErrorNotSupported;              // activations do not fit: caller tiles or falls back
+    }
+    if (stages > 5) stages = 5;
+    if (mma_env("Q4K_DBG_MMA_STAGES") > 0 && mma_env("Q4K_DBG_MMA_STAGES") < stages) stages = mma_env("Q4K_DBG_MMA_STAGES");
+    if (mma_env("Q4K_DBG_MMA_PER_SM") > 0) per_sm = min(per_sm, mma_env("Q4K_DBG_MMA_PER_SM"));
+    p.stages = stages;
+    p.interleave = mma_env("Q4K_DBG_MMA_CONTIG") > 0 ? 0 : 1;
+    const size_t smem = fixed + (size_t)stages * slot;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MMA_SMEM_MAX);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    int64_t grid = (int64_t)sm_count() * per_sm;
+    if (grid > p.n_groups) grid = p.n_groups;
+    if (grid < 1) grid = 1;
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(MMA_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
+    count_launch();
+    return e;
+}
+
+}  // namespace
+
+// One launch of the MMA decode kernel: nmat (1..4) matrices with the same K and N.  Activations: xq (Q8_K rows, nmat == 1
+// only) or xf[i] (F32, quantized in the kernel; equal pointers share one staged copy).  nmat == 1 stores at
+// dst[0] + dst_row0 with column stride dst_col_stride_bytes into every peer buffer; nmat > 1 stores dense [N][M_i].
+// cudaErrorNotSupported when the staged activations do not fit in shared memory.
+cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                                const void *xq, const float *const *xf, int N, int64_t x_row_stride_bytes,
+                                float *const *dst, int64_t dst_col_stride_bytes, float *const *peer_dst, int n_peers,
+                                int64_t dst_row0, bool pdl, cudaStream_t stream) {
+    if (nmat < 1 || nmat > 4 || N < 1 || N > 8 || n_peers > 8) return cudaErrorInvalidValue;
+    TmaGemvParams p;
+    p.w = (const uint8_t *)w[0]; p.M = M[0]; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
+    p.xq = (const uint8_t *)xq; p.xf = xf ? xf[0] : nullptr; p.x_stride = x_row_stride_bytes;
+    for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
+    if (n_peers > 0) { for (int g = 0; g < n_peers; ++g) p.dst[g] = peer_dst[g]; p.n_dst = n_peers; }
+    else { p.dst[0] = dst[0]; p.n_dst = 1; }
+    p.dst_row0 = dst_row0;
+    p.dst_stride = dst_col_stride_bytes > 0 ? dst_col_stride_bytes / 4 : M[0];      // 0 = dense [N][M]
+    p.stages = 0; p.nmat = nmat; p.nx = 0;
+    for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
+    int64_t tiles = 0;
+    for (int i = 0; i < nmat; ++i) {
+        p.wm[i] = (const uint8_t *)w[i]; p.Mm[i] = M[i]; p.dstm[i] = dst ? dst[i] : nullptr;
+        tiles += (M[i] + MROWS - 1) / MROWS;
+        p.gend[i] = tiles;
+        const float *xi = xf ? xf[i] : nullptr;
+        int slot = -1;
+        for (int j = 0; j < p.nx; ++j) if (p.xsrc[j] == xi) slot = j;
+        if (slot < 0) { slot = p.nx; p.xsrc[p.nx++] = xi; }
+        p.xslot[i] = slot;
+    }
+    p.n_groups = tiles;
+    if (tiles == 0) return cudaSuccess;
+    if (tiles > 0x7fffffff) return cudaErrorInvalidValue;
+    switch (N) {
+        case 1: return launch_mma_n<1>(p, pdl, stream);
+        case 2: return launch_mma_n<2>(p, pdl, stream);
+        case 3: return launch_mma_n<3>(p, pdl, stream);
+        case 4: return launch_mma_n<4>(p, pdl, stream);
+        case 5: return launch_mma_n<5>(p, pdl, stream);
+        case 6: return launch_mma_n<6>(p, pdl, stream);
+        case 7: return launch_mma_n<7>(p, pdl, stream);
+        default: return launch_mma_n<8>(p, pdl, stream);
+    }
+}
+
+}  // namespace q4k

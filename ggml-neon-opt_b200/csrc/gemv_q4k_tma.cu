@@ -29,133 +29,20 @@
 //
 // The high nibbles are never shifted: dp4a.u32.s32 on (w & 0xf0f0f0f0) gives 16 x the high-nibble dot
 // product, the low side is multiplied by 16 x scale, and the (exact) >> 4 happens once per lane sum.
+#include <cstdlib>
+
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
+
+#include "gemv_stage.cuh"
 
 namespace q4k {
 
 namespace {
 
-constexpr int TILE_ROWS = 4;
-constexpr int TILE_SB = 8;
-constexpr int ROW_BYTES = TILE_SB * BLK_Q4K;        // 1152
-constexpr int STAGE_BYTES = TILE_ROWS * ROW_BYTES;  // 4608
-constexpr int Q8_STRIDE = 272;                      // 256 qs + 8 x int16 pair sums
-constexpr int SCR_ROW = 136;                        // scratch words per (column, tile row); 136 % 32 == 8
-constexpr int SCR_WORDS = TILE_ROWS * SCR_ROW;      // per column
-constexpr int WARPS = 8;
-
-struct TmaGemvParams {
-    const uint8_t *w;
-    int64_t M, w_stride;
-    int nb;
-    const uint8_t *xq;      // Q8_K activations, or
-    const float *xf;        // F32 activations (quantized inside the kernel) when xq == nullptr
-    int64_t x_stride;       // bytes between activation rows (of whichever is set)
-    float *dst[8];          // output buffer of every peer GPU that gets a copy of the result (dst[0] = local)
-    int n_dst;
-    int64_t dst_row0;       // first row of this shard inside the (full) output column
-    int64_t dst_stride;
-    int64_t n_groups;       // total 4-row groups of the launch
-    int stages;
-    // horizontally fused launch: up to 4 independent matrices with the same K and N (q/k/v, gate/up ...).  Row groups
-    // are numbered through all of them; gend[i] = groups of matrices 0..i.  nmat == 1 uses w / M / dst above.
-    int nmat, nx;
-    const uint8_t *wm[4];
-    int64_t Mm[4], gend[4];
-    float *dstm[4];
-    const float *xsrc[4];   // the nx distinct F32 activation buffers; xslot[i] = which one matrix i reads
-    int xslot[4];
-};
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-
-__device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c) {
-    int d;
-    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ uint4 lds128(const uint8_t *p) { return *reinterpret_cast<const uint4 *>(p); }
-
-// activations already Q8_K in global memory -> the CTA's shared-memory layout
-template <int N>
-__device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, float *d_s) {
-    const int tid = threadIdx.x, nt = blockDim.x, nb = p.nb;
-    for (int i = tid; i < N * nb * 64; i += nt) {
-        const int blk = i >> 6, wd = i & 63, n = blk / nb, b = blk - n * nb;
-        const uint8_t *src = p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K;
-        reinterpret_cast<uint32_t *>(q8_s + (size_t)blk * Q8_STRIDE)[wd] = (reinterpret_cast<const uint32_t *>(src + Q8K_QS))[wd];
-    }
-    for (int i = tid; i < N * nb * 8; i += nt) {
-        const int blk = i >> 3, k = i & 7, n = blk / nb, b = blk - n * nb;
-        const int16_t *bs = reinterpret_cast<const int16_t *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K + Q8K_BSUMS);
-        reinterpret_cast<int16_t *>(q8_s + (size_t)blk * Q8_STRIDE + 256)[k] = (int16_t)(bs[2 * k] + bs[2 * k + 1]);   // hadd_epi16
-    }
-    for (int i = tid; i < N * nb; i += nt) {
-        const int n = i / nb, b = i - n * nb;
-        d_s[i] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K);
-    }
-}
-
-// F32 activations -> Q8_K in shared memory: one warp per 256-block, the arithmetic of quantize_q8k.cu
-// (quantize_row_q8_K_ref, L/ggml/src/ggml-quants.c:2555-2592) through q4k::quantize_block_q8_K.
-template <int N>
-__device__ __forceinline__ void stage_f32(const TmaGemvParams &p, uint8_t *q8_s, float *d_s) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5, nb = p.nb;
-    for (int blk = warp; blk < p.nx * N * nb; blk += nwarps) {
-        const int xs = blk / (N * nb), rem = blk - xs * N * nb, n = rem / nb, b = rem - n * nb;
-        const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(p.xsrc[xs]) + n * p.x_stride) + b * QK_K;
-        const float4 a = reinterpret_cast<const float4 *>(src)[lane];       // plain (coherent) loads: with PDL the
-        const float4 c = reinterpret_cast<const float4 *>(src)[32 + lane];  // producer kernel may still have been running when this one started
-        const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
-        uint32_t w_lo, w_hi;
-        int s_lo, s_hi;
-        const float d = quantize_block_q8_K(v, lane, w_lo, w_hi, s_lo, s_hi);
-        uint8_t *dst = q8_s + (size_t)blk * Q8_STRIDE;
-        reinterpret_cast<uint32_t *>(dst)[lane] = w_lo;
-        reinterpret_cast<uint32_t *>(dst)[32 + lane] = w_hi;
-        // s_lo / s_hi hold the sums of 16-element groups l/4 and 8 + l/4; the pair sums are 32-element groups
-        s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 4);
-        s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 4);
-        if ((lane & 7) == 0) {
-            reinterpret_cast<int16_t *>(dst + 256)[lane >> 3] = (int16_t)s_lo;
-            reinterpret_cast<int16_t *>(dst + 256)[4 + (lane >> 3)] = (int16_t)s_hi;
-        }
-        if (lane == 0) d_s[blk] = d;
-    }
-}
-
-}  // namespace
-
-namespace {
-
 template <int N, bool EXACT>
 __global__ void __launch_bounds__(WARPS * 32, 2)
-gemv_q4k_tma_kernel(const TmaGemvParams p) {
+gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int nb = p.nb, S = p.stages;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -226,9 +113,12 @@ gemv_q4k_tma_kernel(const TmaGemvParams p) {
     // weights never depend on the previous kernel in the stream: get them moving before the dependency wait
     for (int s = 0; s < S; ++s) produce(s);
     griddep_launch_dependents();
+    StageF32<N> stage;
+    stage.prepare(p, blockDim.x);
+    touch_params(p);
     griddep_wait();
     if (p.xq) stage_q8<N>(p, q8_s, d_s);
-    else stage_f32<N>(p, q8_s, d_s);
+    else stage.run(q8_s, d_s);
     __syncthreads();
 
     float acc[N], accm[N];
@@ -395,6 +285,11 @@ size_t fixed_smem(int nrows, int nb, bool exact, int N) {    // nrows = staged a
 }
 constexpr size_t PER_STAGE = (size_t)WARPS * (STAGE_BYTES + 16);
 
+int dbg_env(const char *name) {           // development knobs (tools/launch_chain.py); unset = 0
+    const char *e = getenv(name);
+    return e ? atoi(e) : 0;
+}
+
 template <int N, bool EXACT>
 cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
     auto kern = gemv_q4k_tma_kernel<N, EXACT>;
@@ -402,6 +297,7 @@ cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_
     if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
     // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits
     int stages = want_stages > 0 ? want_stages : 2;
+    if (dbg_env("Q4K_DBG_STAGES") > 0) stages = dbg_env("Q4K_DBG_STAGES");
     while (stages > 1 && 2 * (fixed + stages * PER_STAGE + 1024) > SMEM_MAX) --stages;
     if (fixed + stages * PER_STAGE > SMEM_MAX) stages = (int)((SMEM_MAX - fixed) / PER_STAGE);
     p.stages = stages;
@@ -413,6 +309,7 @@ cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_
         attr_set = true;
     }
     int per_sm = (2 * (smem + 1024) <= SMEM_MAX) ? 2 : 1;
+    if (dbg_env("Q4K_DBG_PER_SM") > 0) per_sm = dbg_env("Q4K_DBG_PER_SM");
     int64_t grid = (int64_t)sm_count() * per_sm;
     if (grid > p.n_groups) grid = p.n_groups;        // small matrices: at least one 4-row group per CTA
     if (grid < 1) grid = 1;
@@ -458,6 +355,15 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
                                     bool pdl, cudaStream_t stream, float *const *peer_dst, int n_peers, int64_t dst_row0) {
     if (M == 0 || N == 0) return cudaSuccess;
     if (n_peers > 8) return cudaErrorInvalidValue;
+    if (!exact_order && stages <= 0 && dbg_env("Q4K_DBG_MMA") >= 0) {      // tolerance order: the tensor-pipe kernel
+        const void *wv[1] = {w};
+        const int64_t Mv[1] = {M};
+        const float *xv[1] = {xf};
+        float *dv[1] = {dst};
+        const cudaError_t e = launch_gemv_q4k_mma(1, wv, Mv, K, w_row_stride_bytes, xq, xq ? nullptr : xv, N, x_row_stride_bytes, dv,
+                                                  dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream);
+        if (e != cudaErrorNotSupported) return e;
+    }
     TmaGemvParams p;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
     p.xq = (const uint8_t *)xq; p.xf = xf; p.x_stride = x_row_stride_bytes;
@@ -467,7 +373,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.dst_row0 = dst_row0;
     p.dst_stride = dst_col_stride_bytes / 4;
     p.n_groups = (M + TILE_ROWS - 1) / TILE_ROWS;
-    p.stages = 0;
+    p.stages = 0; p.interleave = 0;
     p.nmat = 1; p.nx = 1;
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
@@ -481,12 +387,17 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
                                   const float *const *x, int N, int64_t x_row_stride_bytes, float *const *dst,
                                   bool exact_order, bool pdl, cudaStream_t stream) {
     if (nmat < 1 || nmat > 4) return cudaErrorInvalidValue;
+    if (!exact_order && dbg_env("Q4K_DBG_MMA") >= 0) {
+        const cudaError_t e = launch_gemv_q4k_mma(nmat, w, M, K, w_row_stride_bytes, nullptr, x, N, x_row_stride_bytes, dst,
+                                                  0, nullptr, 0, 0, pdl, stream);
+        if (e != cudaErrorNotSupported) return e;
+    }
     TmaGemvParams p;
     p.w = (const uint8_t *)w[0]; p.M = M[0]; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
     p.xq = nullptr; p.xf = x[0]; p.x_stride = x_row_stride_bytes;
     for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
     p.dst[0] = dst[0]; p.n_dst = 1; p.dst_row0 = 0; p.dst_stride = M[0];
-    p.stages = 0; p.nmat = nmat; p.nx = 0;
+    p.stages = 0; p.interleave = 0; p.nmat = nmat; p.nx = 0;
     int64_t groups = 0;
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     for (int i = 0; i < nmat; ++i) {

@@ -1,0 +1,215 @@
+// gemv_stage.cuh — pieces shared by the decode kernels (gemv_q4k_tma.cu, gemv_q4k_mma.cu): launch parameters, the
+// mbarrier / bulk-copy / griddepcontrol PTX wrappers, and the staging of the activations in shared memory (Q8_K copied
+// from a workspace, or quantized in place from F32 with the arithmetic of quantize_q8k.cu).
+#pragma once
+
+#include "q4k_common.cuh"
+
+#ifdef Q4K_TIMING          // tools/micro/mma_ticks.cu: per-phase clock64 stamps of CTA 0 (development only)
+__device__ long long g_ticks[16];
+#define TICK(i) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { long long t_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_)); g_ticks[i] = t_; } } while (0)
+#define GTICK(i) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_ticks[i] = t_; } } while (0)
+#else
+#define TICK(i) do {} while (0)
+#define GTICK(i) do {} while (0)
+#endif
+
+namespace q4k {
+
+namespace {
+
+constexpr int TILE_ROWS = 4;
+constexpr int TILE_SB = 8;
+constexpr int ROW_BYTES = TILE_SB * BLK_Q4K;        // 1152
+constexpr int STAGE_BYTES = TILE_ROWS * ROW_BYTES;  // 4608
+constexpr int Q8_STRIDE = 272;                      // 256 qs + 8 x int16 pair sums
+constexpr int SCR_ROW = 136;                        // scratch words per (column, tile row); 136 % 32 == 8
+constexpr int SCR_WORDS = TILE_ROWS * SCR_ROW;      // per column
+constexpr int WARPS = 8;
+
+struct TmaGemvParams {
+    const uint8_t *w;
+    int64_t M, w_stride;
+    int nb;
+    const uint8_t *xq;      // Q8_K activations, or
+    const float *xf;        // F32 activations (quantized inside the kernel) when xq == nullptr
+    int64_t x_stride;       // bytes between activation rows (of whichever is set)
+    float *dst[8];          // output buffer of every peer GPU that gets a copy of the result (dst[0] = local)
+    int n_dst;
+    int64_t dst_row0;       // first row of this shard inside the (full) output column
+    int64_t dst_stride;
+    int64_t n_groups;       // total 4-row groups of the launch
+    int stages;
+    int interleave;         // gemv_q4k_mma.cu: 1 = tiles dealt round-robin to the CTAs (the grid sweeps memory front to back)
+    // horizontally fused launch: up to 4 independent matrices with the same K and N (q/k/v, gate/up ...).  Row groups
+    // are numbered through all of them; gend[i] = groups of matrices 0..i.  nmat == 1 uses w / M / dst above.
+    int nmat, nx;
+    const uint8_t *wm[4];
+    int64_t Mm[4], gend[4];
+    float *dstm[4];
+    const float *xsrc[4];   // the nx distinct F32 activation buffers; xslot[i] = which one matrix i reads
+    int xslot[4];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+#ifdef Q4K_TEST_WAIT
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+#else
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+#endif
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+__device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint4 lds128(const uint8_t *p) { return *reinterpret_cast<const uint4 *>(p); }
+
+// activations already Q8_K in global memory -> the CTA's shared-memory layout
+template <int N>
+__device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, float *d_s, int nt = 0) {
+    if (nt == 0) nt = blockDim.x;              // nt: the first nt threads of the CTA take part
+    const int tid = threadIdx.x, nb = p.nb;
+    for (int i = tid; i < N * nb * 64; i += nt) {
+        const int blk = i >> 6, wd = i & 63, n = blk / nb, b = blk - n * nb;
+        const uint8_t *src = p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K;
+        reinterpret_cast<uint32_t *>(q8_s + (size_t)blk * Q8_STRIDE)[wd] = (reinterpret_cast<const uint32_t *>(src + Q8K_QS))[wd];
+    }
+    for (int i = tid; i < N * nb * 8; i += nt) {
+        const int blk = i >> 3, k = i & 7, n = blk / nb, b = blk - n * nb;
+        const int16_t *bs = reinterpret_cast<const int16_t *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K + Q8K_BSUMS);
+        reinterpret_cast<int16_t *>(q8_s + (size_t)blk * Q8_STRIDE + 256)[k] = (int16_t)(bs[2 * k] + bs[2 * k + 1]);   // hadd_epi16
+    }
+    for (int i = tid; i < N * nb; i += nt) {
+        const int n = i / nb, b = i - n * nb;
+        d_s[i] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K);
+    }
+}
+
+// F32 activations -> Q8_K in shared memory: one warp per 256-block, the arithmetic of quantize_q8k.cu
+// (quantize_row_q8_K_ref, L/ggml/src/ggml-quants.c:2555-2592) through q4k::quantize_block_q8_K.
+// Two phases so that nothing but the loads and the arithmetic sits behind griddepcontrol.wait: prepare() reads the
+// launch parameters (first touch of a kernel's constant bank is a cache miss) and does the index arithmetic for the
+// warp's first STAGE_R blocks; run() issues all loads of a round trip before any arithmetic.
+constexpr int STAGE_R = 3;
+
+template <int N>
+struct StageF32 {
+    const float *src[STAGE_R];
+    int total, nwarps, nb;
+    const float *x0, *x1, *x2, *x3;      // the (up to four) distinct activation buffers; scalars, not an array: stays in registers
+    int64_t x_stride;
+
+    __device__ __forceinline__ const float *block_src(int blk) const {
+        const int xs = blk / (N * nb), rem = blk - xs * N * nb, n = rem / nb, b = rem - n * nb;
+        const float *x = xs == 0 ? x0 : (xs == 1 ? x1 : (xs == 2 ? x2 : x3));
+        return reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + n * x_stride) + b * QK_K;
+    }
+    __device__ __forceinline__ void prepare(const TmaGemvParams &p, int nt) {
+        nb = p.nb; nwarps = nt >> 5; total = p.nx * N * nb; x_stride = p.x_stride;
+        x0 = p.xsrc[0]; x1 = p.xsrc[1]; x2 = p.xsrc[2]; x3 = p.xsrc[3];
+        const int warp = threadIdx.x >> 5;
+#pragma unroll
+        for (int rr = 0; rr < STAGE_R; ++rr) {
+            const int blk = warp + rr * nwarps;
+            src[rr] = blk < total ? block_src(blk) : nullptr;
+        }
+    }
+    __device__ __forceinline__ void quantize_to(const float4 &a, const float4 &c, int blk, uint8_t *q8_s, float *d_s) const {
+        const int lane = threadIdx.x & 31;
+        const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+        uint32_t w_lo, w_hi;
+        int s_lo, s_hi;
+        const float d = quantize_block_q8_K<8>(v, lane, w_lo, w_hi, s_lo, s_hi);     // s_*: the 32-element pair sums
+        uint8_t *dst = q8_s + (size_t)blk * Q8_STRIDE;
+        reinterpret_cast<uint32_t *>(dst)[lane] = w_lo;
+        reinterpret_cast<uint32_t *>(dst)[32 + lane] = w_hi;
+        if ((lane & 7) == 0) {
+            reinterpret_cast<int16_t *>(dst + 256)[lane >> 3] = (int16_t)s_lo;
+            reinterpret_cast<int16_t *>(dst + 256)[4 + (lane >> 3)] = (int16_t)s_hi;
+        }
+        if (lane == 0) d_s[blk] = d;
+    }
+    __device__ __forceinline__ void run(uint8_t *q8_s, float *d_s) const {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        {   // the prepared blocks: nothing but loads and arithmetic (no index math: integer division by nb is ~100 instructions)
+            float4 a[STAGE_R], c[STAGE_R];
+#pragma unroll
+            for (int rr = 0; rr < STAGE_R; ++rr) {
+                if (src[rr]) {                                                        // warp-uniform
+                    a[rr] = reinterpret_cast<const float4 *>(src[rr])[lane];          // plain (coherent) loads: with PDL the producer
+                    c[rr] = reinterpret_cast<const float4 *>(src[rr])[32 + lane];     // kernel may still have been running at entry
+                }
+            }
+#ifdef Q4K_TIMING
+            if (warp == 0) { asm volatile("" ::"f"(a[0].x), "f"(c[0].x)); TICK(13); }
+#endif
+#pragma unroll
+            for (int rr = 0; rr < STAGE_R; ++rr)
+                if (src[rr]) quantize_to(a[rr], c[rr], warp + rr * nwarps, q8_s, d_s);
+        }
+        if (total > STAGE_R * nwarps) {                                               // long activations: the rest
+#pragma unroll 1
+            for (int base = warp + STAGE_R * nwarps; base < total; base += nwarps * STAGE_R) {
+                const float *sp[STAGE_R];
+                float4 a[STAGE_R], c[STAGE_R];
+#pragma unroll
+                for (int rr = 0; rr < STAGE_R; ++rr) {
+                    const int blk = base + rr * nwarps;
+                    sp[rr] = blk < total ? block_src(blk) : nullptr;
+                    if (sp[rr]) {
+                        a[rr] = reinterpret_cast<const float4 *>(sp[rr])[lane];
+                        c[rr] = reinterpret_cast<const float4 *>(sp[rr])[32 + lane];
+                    }
+                }
+#pragma unroll
+                for (int rr = 0; rr < STAGE_R; ++rr)
+                    if (sp[rr]) quantize_to(a[rr], c[rr], base + rr * nwarps, q8_s, d_s);
+            }
+        }
+    }
+};
+
+// Reads one field of every 64-byte piece of the launch parameters: the first access to a kernel's constant bank misses
+// the constant cache (~0.3 us); done before griddepcontrol.wait, the misses overlap the previous kernel.
+__device__ __forceinline__ void touch_params(const TmaGemvParams &p) {
+    asm volatile("" ::"l"(p.w), "l"(p.x_stride), "l"(p.dst[3]), "l"(p.dst[7]), "l"(p.dst_row0), "l"(p.dst_stride), "r"(p.nmat),
+                 "l"(p.wm[3]), "l"(p.Mm[3]), "l"(p.gend[3]), "l"(p.dstm[3]), "l"(p.xsrc[3]), "r"(p.xslot[3]));
+}
+
+template <int N>
+__device__ __forceinline__ void stage_f32(const TmaGemvParams &p, uint8_t *q8_s, float *d_s, int nt = 0) {
+    StageF32<N> st;
+    st.prepare(p, nt == 0 ? blockDim.x : nt);
+    st.run(q8_s, d_s);
+}
+
+}  // namespace
+
+}  // namespace q4k

@@ -69,37 +69,46 @@ __device__ __forceinline__ int nearest_int(float f) {
 // One 256-float block of quantize_row_q8_K_ref (L/ggml/src/ggml-quants.c:2555-2592) on one warp.  Lane l
 // holds floats [4l, 4l+4) and [128+4l, 128+4l+4) in v[0..3], v[4..7].  Every float operation is an explicit
 // single-rounding intrinsic (no FMA contraction possible):
-//   absmax : per-lane scan in index order (strict '>'), then a butterfly that prefers the larger |x| and, on
-//            ties, the smaller index == "first occurrence wins" of the scalar loop
+//   absmax : max of |x| as unsigned bit patterns (non-negative floats order like integers): per lane, then a
+//            five-step butterfly of single shuffles.  "First occurrence wins" of the scalar loop: elements of the
+//            first half (index 4l + i) precede all of the second half (128 + 4l + i) and are ordered by lane, so the
+//            winner is the lowest lane of a ballot over "my first-half maximum is the block maximum" (else of the
+//            same ballot for the second half); its sign comes from a parallel ballot.  (Measured on B200: REDUX /
+//            CREDUX reductions cost ~200 cycles each, the shuffle butterfly ~25 per step.)
 //   iscale : __fdiv_rn(-127, max)            d : __fdiv_rn(1, iscale)
 //   q      : min(127, nearest_int(__fmul_rn(iscale, x)))
-// Returns d; w_lo / w_hi = the lane's two packed int8x4 words (qs words l and 32 + l); s_lo / s_hi = bsums
-// of the 16-element groups l/4 and 8 + l/4 (valid in every lane of the group).  All-zero block: d = 0, q = 0
+// Returns d; w_lo / w_hi = the lane's two packed int8x4 words (qs words l and 32 + l); s_lo / s_hi = sums over the
+// GROUP-lane group of the lane (GROUP = 4: the bsums of the 16-element groups l/4 and 8 + l/4; GROUP = 8: the pair
+// sums bsums[2k] + bsums[2k+1] of 32 elements), valid in every lane of the group.  All-zero block: d = 0, q = 0
 // and zero bsums (the reference leaves bsums unwritten there, :2568-2573).
+template <int GROUP = 4>
 __device__ __forceinline__ float quantize_block_q8_K(const float (&v)[8], int lane, uint32_t &w_lo, uint32_t &w_hi,
                                                      int &s_lo, int &s_hi) {
-    float amax = 0.0f, smax = 0.0f;
-    int idx = 0x7fffffff;
+    (void)lane;
+    // per-lane maxima of the two halves, first occurrence inside the lane (strict '>' in index order)
+    uint32_t a_lo = 0u, a_hi = 0u;
+    bool n_lo = false, n_hi = false;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const float ax = fabsf(v[i]);
-        if (ax > amax) { amax = ax; smax = v[i]; idx = (i < 4 ? 4 * lane + i : 128 + 4 * lane + (i - 4)); }
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t lo = __float_as_uint(fabsf(v[i])), hi = __float_as_uint(fabsf(v[4 + i]));
+        const bool lo_ok = !(v[i] != v[i]), hi_ok = !(v[4 + i] != v[4 + i]);       // NaN never wins (amax < NaN is false)
+        if (lo_ok && lo > a_lo) { a_lo = lo; n_lo = v[i] < 0.0f; }
+        if (hi_ok && hi > a_hi) { a_hi = hi; n_hi = v[4 + i] < 0.0f; }
     }
+    uint32_t abits = max(a_lo, a_hi);
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        const float oa = __shfl_xor_sync(0xffffffffu, amax, off);
-        const float os = __shfl_xor_sync(0xffffffffu, smax, off);
-        const int   oi = __shfl_xor_sync(0xffffffffu, idx, off);
-        if (oa > amax || (oa == amax && oi < idx)) { amax = oa; smax = os; idx = oi; }
-    }
+    for (int off = 16; off > 0; off >>= 1) abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, off));
+    const unsigned in_lo = __ballot_sync(0xffffffffu, a_lo == abits), in_hi = __ballot_sync(0xffffffffu, a_hi == abits);
+    const unsigned neg_lo = __ballot_sync(0xffffffffu, n_lo), neg_hi = __ballot_sync(0xffffffffu, n_hi);
+    const bool neg = in_lo ? ((neg_lo >> (__ffs(in_lo) - 1)) & 1u) : ((neg_hi >> (__ffs(in_hi) - 1)) & 1u);
     int q[8];
     float d_out;
-    if (amax == 0.0f) {
+    if (abits == 0u) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) q[i] = 0;
         d_out = 0.0f;
     } else {
-        const float iscale = __fdiv_rn(-127.0f, smax);
+        const float iscale = __fdiv_rn(-127.0f, __uint_as_float(abits | (neg ? 0x80000000u : 0u)));
 #pragma unroll
         for (int i = 0; i < 8; ++i) q[i] = min(127, nearest_int(__fmul_rn(iscale, v[i])));
         d_out = __fdiv_rn(1.0f, iscale);
@@ -108,10 +117,11 @@ __device__ __forceinline__ float quantize_block_q8_K(const float (&v)[8], int la
     w_hi = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
     s_lo = q[0] + q[1] + q[2] + q[3];
     s_hi = q[4] + q[5] + q[6] + q[7];
-    s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 1);
-    s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 1);
-    s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 2);
-    s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 2);
+#pragma unroll
+    for (int off = 1; off < GROUP; off <<= 1) {
+        s_lo += __shfl_xor_sync(0xffffffffu, s_lo, off);
+        s_hi += __shfl_xor_sync(0xffffffffu, s_hi, off);
+    }
     return d_out;
 }
 

@@ -32,6 +32,12 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
                                   const float *const *x, int N, int64_t x_row_stride_bytes, float *const *dst,
                                   bool exact_order, bool pdl, cudaStream_t stream);
 
+// the tensor-pipe decode kernel (gemv_q4k_mma.cu): tolerance float order, N <= 8; see there for the arguments
+cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                                const void *xq, const float *const *xf, int N, int64_t x_row_stride_bytes,
+                                float *const *dst, int64_t dst_col_stride_bytes, float *const *peer_dst, int n_peers,
+                                int64_t dst_row0, bool pdl, cudaStream_t stream);
+
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, int64_t N, int64_t xq_row_stride_bytes,

@@ -135,8 +135,9 @@ int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes,
                        const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
                        int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev, void *stream);
 
-/* development knob: 0 = policy (default), 1 = always the reference's AVX2 float order, 2 = never.
- * Overrides the Q4K_GEMV_ORDER environment variable ("exact" / "fast"). */
+/* Float order of the decode path (N <= 8): 0 / 2 = default — exact integer sums, fixed launch-independent float
+ * association, results within 1e-5 of ggml_vec_dot_q4_K_q8_K; 1 = the reference's AVX2 accumulation order, fp32 results
+ * bit-identical to the x86 build (slower kernel).  Overrides the Q4K_GEMV_ORDER environment variable ("exact" / "fast"). */
 int q4k_debug_set_gemv_order(int mode);
 /* development knob: 0 = launch heuristic, 1.. = force a compiled GEMV tile shape (gemv_q4k.cu) */
 int q4k_debug_set_gemv_config(int cfg);

@@ -43,3 +43,12 @@ def q4k():
     import q4k_b200
     q4k_b200.load()        # raises if the CUDA library is missing: no fallback
     return q4k_b200
+
+
+@pytest.fixture()
+def exact_order(q4k):
+    """decode path in the reference's AVX2 float order (bit-identical fp32); the default order is tolerance-only"""
+    lib = q4k.load()
+    lib.q4k_debug_set_gemv_order(1)
+    yield lib
+    lib.q4k_debug_set_gemv_order(0)

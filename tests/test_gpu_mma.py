@@ -1,0 +1,73 @@
+"""GPU: the tensor-pipe decode kernel (gemv_q4k_mma.cu; float order "fast") against the oracle.  The integer stage must
+be exact (checked with weights / activations whose float stage is exact in any order); fp32 within 1e-5 (assert_close of
+test_gpu_parity.py: |got - ref| <= 1e-5 * max(|ref|, column rms))."""
+import numpy as np
+import pytest
+
+from conftest import make_acts, make_weights
+from test_gpu_parity import assert_close, t
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def fast_order(q4k):
+    lib = q4k.load()
+    lib.q4k_debug_set_gemv_order(2)
+    yield lib
+    lib.q4k_debug_set_gemv_order(0)
+
+
+@pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (2048, 5632, 1), (100, 512, 1), (1, 256, 1), (17, 2560, 1), (64, 14336, 1),
+                                   (257, 2048, 2), (300, 2048, 3), (129, 1024, 4), (77, 2048, 5), (40, 512, 6), (50, 768, 7),
+                                   (64, 4096, 8), (33, 5632, 8)])
+def test_mma_gemv_within_tolerance(q4k, fast_order, M, K, N):
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(N, K)
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+
+
+@pytest.mark.parametrize("N", [1, 2, 5, 8])
+def test_mma_gemv_integer_stage_is_exact(q4k, fast_order, N):
+    """d = dmin = 1 in every weight block, activations that quantize to themselves (d_x = 1), small scales: every float
+    operation of the kernel is exact, so the output is sumi - summ bit for bit whatever the accumulation order."""
+    from oracle import port
+    rng = np.random.default_rng(7 + N)
+    M, K = 100, 2560                                        # ragged tile (100 % 16) and ragged round (10 superblocks)
+    w = rng.integers(0, 256, (M, K // 256, 144), dtype=np.uint8)
+    w[..., 0:2] = np.frombuffer(np.float16(1.0).tobytes(), np.uint8)
+    w[..., 2:4] = np.frombuffer(np.float16(1.0).tobytes(), np.uint8)
+    w[..., 4:16] &= 0x33                                    # 6-bit scales / mins <= 3 (+ high bits <= 3 << 4): sums stay < 2^24
+    w = w.reshape(M, -1)
+    x = rng.integers(-20, 21, (N, K)).astype(np.float32)
+    x[:, ::256] = -127.0                                    # block max -> iscale = 1, d = 1
+    xq = port.quantize_q8_K(x)
+    want = np.zeros((N, M), np.int64)
+    for n in range(N):
+        for m in range(M):
+            _, si, sm = port.vec_dot_partials(w[m], xq[n])
+            want[n, m] = int(si.sum()) - int(sm.sum())
+    assert np.abs(want).max() < 2 ** 24
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert np.array_equal(got, want.astype(np.float32))
+
+
+@pytest.mark.parametrize("N", [1, 4])
+def test_mma_result_independent_of_launch_shape(q4k, fast_order, N):
+    """the same rows give the same bits alone, inside a fused group launch, and as the tail of a taller matrix"""
+    K = 2048
+    wa, wb = make_weights(96, K, seed=3), make_weights(40, K, seed=4)
+    x = t(make_acts(N, K))
+    a, b = q4k.mul_mat(t(wa), x), q4k.mul_mat(t(wb), x)
+    ga, gb = q4k.mul_mat_group([t(wa), t(wb)], [x, x])
+    tall = q4k.mul_mat(t(np.concatenate([wa, wb])), x)
+    for u, v in ((a, ga), (b, gb), (a, tall[:, :96]), (b, tall[:, 96:])):
+        assert np.array_equal(u.cpu().numpy().view(np.uint32), v.cpu().numpy().view(np.uint32))
+
+
+def test_mma_q8_input_equals_fused_f32(q4k, fast_order):
+    M, K, N = 200, 1024, 3
+    w, x = t(make_weights(M, K)), t(make_acts(N, K))
+    xq = q4k.quantize_q8_K(x)
+    assert np.array_equal(q4k.mul_mat_q8(w, xq).cpu().numpy().view(np.uint32), q4k.mul_mat(w, x).cpu().numpy().view(np.uint32))

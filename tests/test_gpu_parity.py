@@ -57,7 +57,7 @@ def test_int32_partials_bit_exact(q4k, M, K, N):
 
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (100, 512, 1), (257, 2048, 2), (64, 14336, 1), (1, 256, 1)])
-def test_gemv_bit_identical_to_avx2_reference_order(q4k, M, K, N):
+def test_gemv_bit_identical_to_avx2_reference_order(q4k, exact_order, M, K, N):
     from oracle import port
     w, x = make_weights(M, K), make_acts(N, K)
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
@@ -83,7 +83,7 @@ def test_mul_mat_large_batch(q4k, N):
 
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (2048, 5632, 1), (259, 2048, 2), (64, 8192, 4), (33, 1024, 8)])
-def test_fused_quantize_equals_two_kernel_path(q4k, M, K, N):
+def test_fused_quantize_equals_two_kernel_path(q4k, exact_order, M, K, N):
     """q4k_mul_mat fuses quantize_row_q8_K into the GEMV launch for decode shapes; the result must be bit-identical
     to quantize kernel + GEMV (and, for N <= 2, to the AVX2-order oracle), with and without PDL launches."""
     from oracle import port
@@ -109,7 +109,7 @@ def test_fused_quantize_equals_two_kernel_path(q4k, M, K, N):
         assert_close(fused, ref, port.mul_mat_f64(w, x))
 
 
-def test_back_to_back_pdl_launches_see_fresh_activations(q4k):
+def test_back_to_back_pdl_launches_see_fresh_activations(q4k, exact_order):
     """Chained mul_mats on one stream (each reads what the previous wrote) under programmatic dependent launch."""
     import torch
     from oracle import port

@@ -18,6 +18,15 @@ def bits(a):
     return a.cpu().numpy().view(np.uint32)
 
 
+@pytest.fixture(params=["default", "exact"], autouse=True)
+def order(request, q4k):
+    """every test here runs with both decode kernels: the default (tensor-pipe, tolerance order) and the AVX2-order one"""
+    lib = q4k.load()
+    lib.q4k_debug_set_gemv_order(1 if request.param == "exact" else 0)
+    yield request.param
+    lib.q4k_debug_set_gemv_order(0)
+
+
 @pytest.mark.parametrize("Ms,K,N", [((2048, 256, 256), 2048, 1), ((5632, 5632), 2048, 1), ((37, 4, 129, 1), 512, 2),
                                     ((64, 64), 4096, 8), ((300,), 1024, 3)])
 def test_group_shared_input_equals_separate_launches(q4k, Ms, K, N):
@@ -38,14 +47,19 @@ def test_group_distinct_inputs(q4k):
         assert np.array_equal(bits(o), bits(q4k.mul_mat(w, x)))
 
 
-def test_group_against_oracle(q4k):
+def test_group_against_oracle(q4k, order):
     from oracle import port
+    from test_gpu_parity import assert_close
     K = 2048
     wn = [make_weights(M, K, seed=5 + i) for i, M in enumerate((128, 36))]
     xn = make_acts(1, K)
     outs = q4k.mul_mat_group([t(w) for w in wn], [t(xn)] * 2)
     for w, o in zip(wn, outs):
-        assert np.array_equal(bits(o), port.mul_mat(w, xn, port.ORDER_AVX2).view(np.uint32))
+        ref = port.mul_mat(w, xn, port.ORDER_AVX2)
+        if order == "exact":
+            assert np.array_equal(bits(o), ref.view(np.uint32))
+        else:
+            assert_close(o.cpu().numpy(), ref, port.mul_mat_f64(w, xn))
 
 
 def test_group_rejects_bad_arguments(q4k):

@@ -39,15 +39,24 @@ def test_plugin_scores_zero_without_sm100_device():
 @pytest.mark.gpu
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (300, 1024, 3), (128, 512, 16)])
 def test_plugin_graph_matches_reference_cpu_backend(M, K, N):
+    import ctypes
     w, x = make_weights(M, K), make_acts(N, K)
-    got, _, _ = ref.plugin_mul_mat(PLUGIN, w, x)
     cpu, _, _ = ref.mul_mat(w, x, n_threads=4)
-    if N <= 2:
-        assert np.array_equal(got.view(np.uint32), cpu.view(np.uint32))       # same float order as the AVX2 vec_dot
-    else:
-        f64 = port.mul_mat_f64(w, x)
-        rms = np.sqrt((f64 ** 2).mean(axis=1, keepdims=True))
-        assert np.all(np.abs(got - cpu) <= 1e-5 * np.maximum(np.abs(cpu), rms))
+    f64 = port.mul_mat_f64(w, x)
+    rms = np.sqrt((f64 ** 2).mean(axis=1, keepdims=True))
+    got, _, _ = ref.plugin_mul_mat(PLUGIN, w, x)                              # default float order: within 1e-5
+    assert np.all(np.abs(got - cpu) <= 1e-5 * np.maximum(np.abs(cpu), rms))
+    if N <= 8:                                                               # AVX2-order decode kernel: bit-identical
+        lib = ctypes.CDLL(os.path.join(ROOT, "ggml-neon-opt_b200", "lib", "libq4k_b200.so"))   # the instance the plugin links
+        lib.q4k_debug_set_gemv_order(1)
+        try:
+            got, _, _ = ref.plugin_mul_mat(PLUGIN, w, x)
+        finally:
+            lib.q4k_debug_set_gemv_order(0)
+        if N <= 2:
+            assert np.array_equal(got.view(np.uint32), cpu.view(np.uint32))
+        else:
+            assert np.all(np.abs(got - cpu) <= 1e-5 * np.maximum(np.abs(cpu), rms))
 
 
 @needs_ref

@@ -1,0 +1,63 @@
+// Launch-chain floor on B200: microseconds per dependent launch inside a CUDA graph, with and without
+// programmatic dependent launch, for kernels that do (a) nothing, (b) a dependent global load + store,
+// (c) a load, a warp reduction and a __syncthreads (the shape of the GEMV's activation staging).
+#include <cstdio>
+#include <cuda_runtime.h>
+
+__global__ void k_empty(const float *x, float *y, int mode) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (mode >= 1) {
+        float v = x[threadIdx.x + (blockIdx.x & 7) * 256];
+        if (mode >= 2) {
+            for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+            __shared__ float s[8];
+            if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = v;
+            __syncthreads();
+            v = s[threadIdx.x & 7];
+        }
+        if (mode >= 3) {     // dependent shared-memory chain ~ the integer phase's latency
+            for (int i = 0; i < 200; ++i) v = __fmaf_rn(v, 1.0001f, 0.5f);
+        }
+        if (threadIdx.x == 0) y[blockIdx.x] = v;
+    }
+}
+
+static float run(int grid, int mode, bool pdl, int chain, int reps) {
+    float *x, *y;
+    cudaMalloc(&x, 1 << 20); cudaMalloc(&y, 1 << 20);
+    cudaMemset(x, 0, 1 << 20);
+    cudaStream_t st; cudaStreamCreate(&st);
+    cudaGraph_t g; cudaGraphExec_t ge;
+    cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal);
+    for (int i = 0; i < chain; ++i) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(256); cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+        cudaLaunchKernelEx(&cfg, k_empty, (const float *)x, y, mode);
+    }
+    cudaStreamEndCapture(st, &g);
+    cudaGraphInstantiate(&ge, g, 0);
+    cudaGraphLaunch(ge, st); cudaStreamSynchronize(st);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, st);
+    for (int r = 0; r < reps; ++r) cudaGraphLaunch(ge, st);
+    cudaEventRecord(e1, st);
+    cudaStreamSynchronize(st);
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    cudaGraphExecDestroy(ge); cudaGraphDestroy(g); cudaStreamDestroy(st); cudaFree(x); cudaFree(y);
+    return ms * 1e3f / (chain * reps);
+}
+
+int main() {
+    for (int pdl = 0; pdl < 2; ++pdl)
+        for (int grid : {1, 148, 296})
+            for (int mode = 0; mode < 4; ++mode)
+                printf("pdl=%d grid=%3d mode=%d  %.3f us/launch\n", pdl, grid, mode, run(grid, mode, pdl, 200, 20));
+    cudaError_t e = cudaDeviceSynchronize();
+    printf("status %s\n", cudaGetErrorString(e));
+    return 0;
+}
