@@ -39,6 +39,10 @@ sys.path.insert(0, os.path.join(ROOT, "ggml-neon-opt_b200"))
 L2_BYTES = 126 << 20
 HBM_NOMINAL_GBS = 8000.0           # BASELINE.json's stated denominator ("~8 TB/s")
 HBM_FALLBACK_GBS = 6650.0          # /opt/skills/guides/B200_PROFILING.md fallback if MEASURED_PEAKS.json is absent
+# dram__bytes_read.sum + dram__bytes_write.sum of one gemv_q4k_mma_kernel launch from the round's `ncu --set full` capture
+NCU_TRAFFIC = {"bytes": 6562304, "note": "ncu --set full of the 5632x2048 N=1 launch (profiles/r1_ncu_gemv_mma_c1_5632x2048.txt): "
+                                         "6562304 B DRAM read + 0 B write per launch vs 6518784 B algorithmic; the 28672x8192 launch reads "
+                                         "132.22 MB for 132.19 MB algorithmic (profiles/r1_ncu_gemv_mma_c5_28672x8192.txt)"}
 Q6K_LAYERS = {0, 1, 4, 7, 10, 13, 16, 19, 20, 21}   # use_more_bits(i, 22), L/src/llama-quant.cpp:185-187
 
 
@@ -483,7 +487,8 @@ def run_ours(args, rank, world, local_rank):
             "decode_tok_s": round(1e3 / per_step_ms, 1) if not sharded else None,
             "pct_of_nominal_8TBs": round(100 * value / world / HBM_NOMINAL_GBS, 2),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC["bytes"], "traffic_note": NCU_TRAFFIC["note"],
+                         "peak_source": peak_src,
                          "kernel": "gemv_q4k_mma_kernel (Q8_K quantizer fused into the launch)",
                          "bytes_per_launch": round(per_launch_bytes), "us_per_launch": round(per_launch_us, 3)},
             "e2e": {"value": round(e2e_val, 2), "unit": "GB/s", "h2d_bytes_per_step": ms.h2d, "d2h_bytes_per_step": ms.d2h,

@@ -5,15 +5,6 @@
 
 #include "q4k_common.cuh"
 
-#ifdef Q4K_TIMING          // tools/micro/mma_ticks.cu: per-phase clock64 stamps of CTA 0 (development only)
-__device__ long long g_ticks[16];
-#define TICK(i) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { long long t_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_)); g_ticks[i] = t_; } } while (0)
-#define GTICK(i) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_ticks[i] = t_; } } while (0)
-#else
-#define TICK(i) do {} while (0)
-#define GTICK(i) do {} while (0)
-#endif
-
 namespace q4k {
 
 namespace {

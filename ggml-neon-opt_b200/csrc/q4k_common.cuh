@@ -9,6 +9,18 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifdef Q4K_TIMING          // tools/micro/mma_ticks.cu: per-phase clock64 stamps of CTA 0 (development only)
+__device__ long long g_ticks[32];
+#define TICK(i) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { long long t_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_)); g_ticks[i] = t_; } } while (0)
+#define GTICK(i) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_ticks[i] = t_; } } while (0)
+// QT: stamp after the value `dep` exists (warp 0 of CTA 0)
+#define QT(i, dep) do { if (blockIdx.x == 0 && threadIdx.x < 32) { asm volatile("" ::"r"(dep)); TICK(i); } } while (0)
+#else
+#define TICK(i) do {} while (0)
+#define GTICK(i) do {} while (0)
+#define QT(i, dep) do {} while (0)
+#endif
+
 namespace q4k {
 
 constexpr int QK_K      = 256;
@@ -96,11 +108,14 @@ __device__ __forceinline__ float quantize_block_q8_K(const float (&v)[8], int la
         if (hi_ok && hi > a_hi) { a_hi = hi; n_hi = v[4 + i] < 0.0f; }
     }
     uint32_t abits = max(a_lo, a_hi);
+    QT(16, abits);
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, off));
+    QT(17, abits);
     const unsigned in_lo = __ballot_sync(0xffffffffu, a_lo == abits), in_hi = __ballot_sync(0xffffffffu, a_hi == abits);
     const unsigned neg_lo = __ballot_sync(0xffffffffu, n_lo), neg_hi = __ballot_sync(0xffffffffu, n_hi);
     const bool neg = in_lo ? ((neg_lo >> (__ffs(in_lo) - 1)) & 1u) : ((neg_hi >> (__ffs(in_hi) - 1)) & 1u);
+    QT(18, (unsigned)neg);
     int q[8];
     float d_out;
     if (abits == 0u) {
@@ -115,6 +130,7 @@ __device__ __forceinline__ float quantize_block_q8_K(const float (&v)[8], int la
     }
     w_lo = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
     w_hi = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+    QT(19, w_lo ^ w_hi);
     s_lo = q[0] + q[1] + q[2] + q[3];
     s_hi = q[4] + q[5] + q[6] + q[7];
 #pragma unroll
@@ -122,6 +138,7 @@ __device__ __forceinline__ float quantize_block_q8_K(const float (&v)[8], int la
         s_lo += __shfl_xor_sync(0xffffffffu, s_lo, off);
         s_hi += __shfl_xor_sync(0xffffffffu, s_hi, off);
     }
+    QT(20, (unsigned)(s_lo + s_hi) ^ __float_as_uint(d_out));
     return d_out;
 }
 

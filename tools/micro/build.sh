@@ -8,4 +8,5 @@ $NV -DQ4K_TIMING -DQ4K_TEST_WAIT -o $D/mma_ticks_tw $D/mma_ticks.cu
 $NV -o $D/quant_lat $D/quant_lat.cu
 $NV -o $D/pdl_floor $D/pdl_floor.cu
 $NV -o $D/imma_rate $D/imma_rate.cu
+$NV -o $D/stream_bulk $D/stream_bulk.cu
 ls -la $D | grep -v "\.cu$\|\.sh$"

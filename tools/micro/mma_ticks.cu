@@ -42,7 +42,7 @@ int main(int argc, char **argv) {
     for (int r = 0; r < 10; ++r) cudaGraphLaunch(ge, st);
     cudaEventRecord(e1, st); cudaStreamSynchronize(st);
     float ms; cudaEventElapsedTime(&ms, e0, e1);
-    long long t[16];
+    long long t[32];
     cudaMemcpyFromSymbol(t, ::g_ticks, sizeof(t));
     printf("M=%d K=%d: %.3f us/launch (%s)\n", M, K, ms * 1e3 / (chain * 10), cudaGetErrorString(cudaGetLastError()));
     const char *names[] = {"entry", "init+sync", "griddep_wait", "stage", "stage barrier", "first full wait", "compute tile 0", "last tile done", "epilogue barrier", "producer first issue"};
@@ -50,6 +50,8 @@ int main(int argc, char **argv) {
     printf("  %-20s at %6lld cycles\n", names[9], t[9] - t[0]);
     printf("  barrier -> before full wait %lld cycles, the wait itself %lld\n", t[14] - t[4], t[5] - t[14]);
     printf("  stage: loads landed at +%lld cycles after wait-return, quantize +%lld\n", t[13] - t[2], t[3] - t[13]);
+    printf("  quantize (warp 0, last block): lane scan +%lld, butterfly +%lld, ballots +%lld, fdiv/round/pack +%lld, sums+d +%lld, stores +%lld\n",
+           t[16] - t[13], t[17] - t[16], t[18] - t[17], t[19] - t[18], t[20] - t[19], t[3] - t[20]);
     printf("  globaltimer: entry->wait-return %lld ns, wait-return->end %lld ns\n", t[11] - t[10], t[12] - t[11]);
     return 0;
 }

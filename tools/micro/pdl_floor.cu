@@ -8,7 +8,7 @@ __global__ void k_empty(const float *x, float *y, int mode) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (mode >= 1) {
-        float v = x[threadIdx.x + (blockIdx.x & 7) * 256];
+        float v = x[(threadIdx.x & 255) + (blockIdx.x & 7) * 256];
         if (mode >= 2) {
             for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
             __shared__ float s[8];
@@ -23,7 +23,8 @@ __global__ void k_empty(const float *x, float *y, int mode) {
     }
 }
 
-static float run(int grid, int mode, bool pdl, int chain, int reps) {
+static float run(int grid, int mode, bool pdl, int chain, int reps, int threads = 256, int smem = 0) {
+    if (smem) cudaFuncSetAttribute(k_empty, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     float *x, *y;
     cudaMalloc(&x, 1 << 20); cudaMalloc(&y, 1 << 20);
     cudaMemset(x, 0, 1 << 20);
@@ -32,7 +33,7 @@ static float run(int grid, int mode, bool pdl, int chain, int reps) {
     cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal);
     for (int i = 0; i < chain; ++i) {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(256); cfg.stream = st;
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.stream = st; cfg.dynamicSmemBytes = smem;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -57,6 +58,10 @@ int main() {
         for (int grid : {1, 148, 296})
             for (int mode = 0; mode < 4; ++mode)
                 printf("pdl=%d grid=%3d mode=%d  %.3f us/launch\n", pdl, grid, mode, run(grid, mode, pdl, 200, 20));
+    for (int smem : {0, 40 << 10, 105 << 10, 200 << 10})
+        for (int threads : {256, 320})
+            for (int grid : {128, 296})
+                printf("pdl=1 grid=%3d threads=%d smem=%3dKB mode=2  %.3f us/launch\n", grid, threads, smem >> 10, run(grid, 2, true, 200, 20, threads, smem));
     cudaError_t e = cudaDeviceSynchronize();
     printf("status %s\n", cudaGetErrorString(e));
     return 0;
