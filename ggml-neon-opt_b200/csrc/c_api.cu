@@ -48,7 +48,7 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 // launch-independent float association, within 1e-5 of the reference.  Q4K_GEMV_ORDER=exact (or
 // q4k_debug_set_gemv_order(1)) selects the kernel that reproduces the reference's AVX2 accumulation order bit for bit
 // (gemv_q4k_tma.cu) at ~10-25% less throughput on small matrices.
-static int64_t g_fuse_limit = 32768;   // N*K floats up to which the quantizer is fused into the GEMV launch
+static int64_t g_fuse_limit = 16384;   // N*K floats up to which the quantizer is fused into the decode launch (measured: K = 28672 is faster with the separate quantizer)
 static int g_gemm_enabled = 1;          // 0: N > 8 takes the decode kernel eight columns at a time (development)
 static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
 bool gemv_exact_policy(int N);

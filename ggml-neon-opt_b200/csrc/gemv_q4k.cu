@@ -264,7 +264,16 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                                       dst_col_stride_bytes, exact_order,
                                                       g_gemv_config >= 10 ? g_gemv_config - 10 : 0, g_gemv_pdl != 0, stream);
         if (e != cudaErrorNotSupported) return e;
-        // activations too large for one shared-memory residency: the K-tiled direct-load kernel below takes it
+        // activations too large for one shared-memory residency (8 columns of K = 28672 ...): half the columns per launch —
+        // the weights stream twice, which still beats the K-tiled direct-load kernel below by an order of magnitude
+        if (N > 1) {
+            const int n0 = N / 2;
+            const cudaError_t e0 = launch_gemv_q4k_q8k(w, M, K, w_row_stride_bytes, xq, n0, xq_row_stride_bytes, dst, dst_col_stride_bytes,
+                                                       exact_order, stream);
+            if (e0 != cudaSuccess) return e0;
+            return launch_gemv_q4k_q8k(w, M, K, w_row_stride_bytes, (const uint8_t *)xq + (size_t)n0 * xq_row_stride_bytes, N - n0,
+                                       xq_row_stride_bytes, dst + (size_t)n0 * (dst_col_stride_bytes / 4), dst_col_stride_bytes, exact_order, stream);
+        }
     }
     GemvParams p;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);

@@ -33,6 +33,7 @@
 // Float association (all N): every lane accumulates its own sub-block pair over the superblocks its warp owns, in
 // order; at the end of the tile the four chunk lanes are summed (xor 1, xor 2), then the eight warps' partials in
 // warp order.  Nothing depends on the grid, the ring depth or the batch size a column is computed in.
+#include <algorithm>
 #include <cstdlib>
 
 #include "gemv_stage.cuh"
@@ -147,14 +148,49 @@ __device__ __forceinline__ void sb_step_nn(const uint8_t *slot_sb, const uint8_t
 }
 
 
-template <int N>
+// ---- cluster helpers (split-K: the CTAs of a cluster share one tile, CTA rank = K part) -------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_remote_f32(uint32_t raddr, float v) { asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(raddr), "f"(v) : "memory"); }
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t rbar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {      // observes arrivals from other CTAs
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+constexpr int SEG_ROUNDS = 4;             // rounds per segment: the unit of the float association along K (8192 columns)
+constexpr int XD = 2;                     // split-K: exchange buffers (tiles in flight between the parts and the leader)
+
+// MODE 0: K <= 8192 (one segment; the common decode shapes, everything about segments folds away), 1: several segments,
+// 2: several segments split over the CTAs of a cluster
+template <int N, int MODE>
 __global__ void __launch_bounds__(MMA_THREADS, 2)
 gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
+    constexpr bool SPLITK = MODE == 2;
     using Cfg = MmaCfg<N>;
+    constexpr int ITEMS = (N * MROWS + 31) / 32;          // results per reducer lane
     extern __shared__ __align__(128) uint8_t smem[];
-    const int nb = p.nb, S = p.stages;
+    const int nb = p.nb, S = p.stages, KP = SPLITK ? p.kparts : 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (warp == 0) { TICK(0); GTICK(10); }
+
+    // K split: segments of SEG_ROUNDS rounds; part `rank` of the cluster owns segments [seg0, seg1)
+    const int rounds = (nb + KW - 1) / KW, nseg = MODE == 0 ? 1 : (rounds + SEG_ROUNDS - 1) / SEG_ROUNDS;
+    const int rank = KP > 1 ? (int)cluster_ctarank() : 0;
+    const int seg0 = nseg * rank / KP, seg1 = nseg * (rank + 1) / KP;
+    const int pseg_max = (nseg + KP - 1) / KP;            // segments of the largest part
 
     size_t off = 0;
     uint8_t *q8_s = smem;                                   off += (size_t)p.nx * N * nb * Q8_STRIDE;
@@ -162,31 +198,36 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     float *d_s = reinterpret_cast<float *>(smem + off);     off += ((size_t)p.nx * N * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
     float *part_s = reinterpret_cast<float *>(smem + off);  off += (size_t)PBUF * KW * N * MROWS * 4;
+    float *xbuf = reinterpret_cast<float *>(smem + off);    off += KP > 1 ? (size_t)XD * (KP - 1) * pseg_max * N * MROWS * 4 : 0;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + off);   off += (size_t)S * 8;
     uint64_t *empty = reinterpret_cast<uint64_t *>(smem + off);  off += (size_t)S * 8;
     uint64_t *pfull = reinterpret_cast<uint64_t *>(smem + off);  off += (size_t)PBUF * 8;
     uint64_t *pempty = reinterpret_cast<uint64_t *>(smem + off); off += (size_t)PBUF * 8;
+    uint64_t *xfull = reinterpret_cast<uint64_t *>(smem + off);  off += (size_t)XD * 8;      // leader: a tile's remote parts have landed
+    uint64_t *xcredit = reinterpret_cast<uint64_t *>(smem + off); off += (size_t)XD * 8;    // parts: the leader has consumed the buffer
     off = (off + 127) & ~(size_t)127;
     uint8_t *slots = smem + off;
 
-    // balanced contiguous range of 16-row tiles for this CTA (n_groups counts tiles here)
-    const int64_t tstep = p.interleave ? gridDim.x : 1;
-    const int64_t t0 = p.interleave ? blockIdx.x : p.n_groups * blockIdx.x / gridDim.x;
-    const int64_t t1 = p.interleave ? p.n_groups : p.n_groups * (blockIdx.x + 1) / gridDim.x;
+    // tiles of this cluster (n_groups counts tiles): dealt round-robin so that the grid sweeps memory front to back
+    const int64_t ncl = gridDim.x / KP, cl = blockIdx.x / KP;
+    const int64_t tstep = p.interleave ? ncl : 1;
+    const int64_t t0 = p.interleave ? cl : p.n_groups * cl / ncl;
+    const int64_t t1 = p.interleave ? p.n_groups : p.n_groups * (cl + 1) / ncl;
     // tile -> (matrix, tile inside the matrix); mat only ever moves forward
     auto locate = [&](int64_t tile, int &mat) -> int64_t {
         while (mat + 1 < p.nmat && tile >= p.gend[mat]) ++mat;
         return mat ? tile - p.gend[mat - 1] : tile;
     };
-    const int rounds = (nb + KW - 1) / KW;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(smem_u32(&full[s]), 1); mbar_init(smem_u32(&empty[s]), KW); }
         for (int b = 0; b < PBUF; ++b) { mbar_init(smem_u32(&pfull[b]), KW); mbar_init(smem_u32(&pempty[b]), 1); }
+        for (int b = 0; b < XD; ++b) { mbar_init(smem_u32(&xfull[b]), KP > 1 ? KP - 1 : 1); mbar_init(smem_u32(&xcredit[b]), 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (threadIdx.x < Q8_STRIDE / 4) reinterpret_cast<uint32_t *>(zero_s)[threadIdx.x] = 0u;
     __syncthreads();
+    if (KP > 1) cluster_sync_all();          // every CTA's barriers exist before anyone arrives on them remotely
     griddep_launch_dependents();
     if (warp == 0) TICK(1);
 
@@ -195,12 +236,13 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
         int s = 0;
         uint32_t eparity = 1;                // parity of the phase BEFORE the first one: the first S waits fall through
         int mat = 0;
+        const int rd0 = seg0 * SEG_ROUNDS, rd1 = min(seg1 * SEG_ROUNDS, rounds);
         for (int64_t tile = t0; tile < t1; tile += tstep) {
             const int64_t lt = locate(tile, mat);
             int64_t row = lt * MROWS + (lane & 15);
             if (row >= p.Mm[mat]) row = p.Mm[mat] - 1;          // ragged last tile: stay in bounds, result is not stored
             const uint8_t *src = p.wm[mat] + row * p.w_stride;
-            for (int rd = 0; rd < rounds; ++rd) {
+            for (int rd = rd0; rd < rd1; ++rd) {
                 mbar_wait(smem_u32(&empty[s]), eparity);
                 const uint32_t bytes = (uint32_t)min(KW, nb - rd * KW) * BLK_Q4K;
                 const uint32_t bar = smem_u32(&full[s]);
@@ -210,7 +252,7 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
                     fence_proxy_async();
                     bulk_g2s(smem_u32(slots + (size_t)s * Cfg::SLOT + lane * Cfg::PITCH), src + (int64_t)rd * ROW_BYTES, bytes, bar);
                 }
-                if (tile == t0 && rd == 0) TICK(9);
+                if (tile == t0 && rd == rd0) TICK(9);
                 if (++s == S) { s = 0; eparity ^= 1u; }
             }
         }
@@ -218,36 +260,77 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     }
 
     if (warp == KW + 1) {
-        // ---- reducer warp: sums the eight warps' partials of a tile in warp order and stores the result rows, so the
-        // consumer warps never meet at a CTA barrier and run on into the next tile ----
-        int mat = 0;
-        int b = 0;
-        uint32_t fparity = 0;
+        // ---- reducer warp.  Per segment: the eight warps' partials in warp order.  Per tile: the segment sums in K order —
+        // its own in registers; with split-K the other parts' segment sums arrive in the leader's exchange buffer (DSMEM)
+        // and are added there in the same order, so the result does not depend on how K was split.
+        int mat = 0, b = 0, xs = 0;
+        uint32_t fparity = 0, xparity = 0, cparity = 1;
         for (int64_t tile = t0; tile < t1; tile += tstep) {
             const int64_t lt = locate(tile, mat);
             const int64_t m_rows = p.Mm[mat];
-            mbar_wait(smem_u32(&pfull[b]), fparity);
-            for (int i = lane; i < N * MROWS; i += 32) {
-                const int col = i / MROWS, rr = i % MROWS;
-                const float *pp = part_s + (size_t)b * KW * N * MROWS + i;
-                float a = pp[0];
+            float tot[ITEMS];
+            if (rank > 0) mbar_wait_cluster(smem_u32(&xcredit[xs]), cparity);     // the leader is done with this exchange buffer
+            for (int seg = seg0; seg < seg1; ++seg) {
+                mbar_wait(smem_u32(&pfull[b]), fparity);
 #pragma unroll
-                for (int w = 1; w < KW; ++w) a = __fadd_rn(a, pp[(size_t)w * N * MROWS]);
-                const int64_t row = lt * MROWS + rr;
-                if (row < m_rows) {
-                    if (p.nmat == 1) {
-                        // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
-                        const int64_t o = (int64_t)col * p.dst_stride + p.dst_row0 + row;
-                        p.dst[0][o] = a;
-                        for (int g = 1; g < p.n_dst; ++g) p.dst[g][o] = a;
-                    } else {
-                        p.dstm[mat][(int64_t)col * m_rows + row] = a;     // fused launches write dense [N][M_i] results
+                for (int it = 0; it < ITEMS; ++it) {
+                    const int i = lane + 32 * it;
+                    if (i < N * MROWS) {
+                        const float *pp = part_s + (size_t)b * KW * N * MROWS + i;
+                        float a = pp[0];
+#pragma unroll
+                        for (int w = 1; w < KW; ++w) a = __fadd_rn(a, pp[(size_t)w * N * MROWS]);
+                        if (rank == 0) tot[it] = seg == 0 ? a : __fadd_rn(tot[it], a);
+                        else st_remote_f32(mapa_shared(smem_u32(xbuf + (((size_t)xs * (KP - 1) + rank - 1) * pseg_max + (seg - seg0)) * N * MROWS + i), 0), a);
                     }
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&pempty[b]));
+                if (++b == PBUF) { b = 0; fparity ^= 1u; }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&pempty[b]));
-            if (++b == PBUF) { b = 0; fparity ^= 1u; }
+            if (tile == t0) TICK(21);
+            if (rank > 0) {
+                asm volatile("fence.acq_rel.cluster;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive_remote(mapa_shared(smem_u32(&xfull[xs]), 0));
+            } else {
+                if (KP > 1) {
+                    mbar_wait_cluster(smem_u32(&xfull[xs]), xparity);
+                    if (tile == t0) TICK(22);
+                    for (int g = 1; g < KP; ++g) {
+                        const int gs = nseg * (g + 1) / KP - nseg * g / KP;
+                        for (int sl = 0; sl < gs; ++sl) {
+#pragma unroll
+                            for (int it = 0; it < ITEMS; ++it) {
+                                const int i = lane + 32 * it;
+                                if (i < N * MROWS) tot[it] = __fadd_rn(tot[it], xbuf[(((size_t)xs * (KP - 1) + g - 1) * pseg_max + sl) * N * MROWS + i]);
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int it = 0; it < ITEMS; ++it) {
+                    const int i = lane + 32 * it;
+                    const int col = i / MROWS, rr = i % MROWS;
+                    const int64_t row = lt * MROWS + rr;
+                    if (i < N * MROWS && row < m_rows) {
+                        if (p.nmat == 1) {
+                            // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
+                            const int64_t o = (int64_t)col * p.dst_stride + p.dst_row0 + row;
+                            p.dst[0][o] = tot[it];
+                            for (int g = 1; g < p.n_dst; ++g) p.dst[g][o] = tot[it];
+                        } else {
+                            p.dstm[mat][(int64_t)col * m_rows + row] = tot[it];     // fused launches write dense [N][M_i] results
+                        }
+                    }
+                }
+                if (tile == t0) TICK(23);
+                if (KP > 1 && tile + XD * tstep < t1) {      // hand the buffer back (only if a part will use it again: it may have exited)
+                    __syncwarp();
+                    if (lane > 0 && lane < KP) mbar_arrive_remote(mapa_shared(smem_u32(&xcredit[xs]), lane));
+                }
+            }
+            if (++xs == XD) { xs = 0; xparity ^= 1u; cparity ^= 1u; }
         }
         return;
     }
@@ -255,8 +338,9 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     // ---- consumer warps: everything that does not depend on the activations happens before the dependency wait
     // (parameter loads through the constant cache are ~50 cycles each and chain; the compiler would sink them) ----
     const int r = lane >> 2, c = lane & 3;
+    const int kb0 = seg0 * SEG_ROUNDS * KW, kb1 = min(seg1 * SEG_ROUNDS * KW, nb);       // this part's superblocks
     StageF32<N> stage;
-    stage.prepare(p, KW * 32);
+    stage.prepare(p, KW * 32, kb0, kb1 - kb0);
     touch_params(p);
     int mat = 0;
     locate(t0, mat);
@@ -266,7 +350,7 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     asm volatile("" ::"r"(nmat));
     griddep_wait();
     if (warp == 0) { TICK(2); GTICK(11); }
-    if (p.xq) stage_q8<N>(p, q8_s, d_s, KW * 32);
+    if (p.xq) stage_q8<N>(p, q8_s, d_s, KW * 32, kb0, kb1 - kb0);
     else stage.run(q8_s, d_s);
     if (warp == 0) TICK(3);
     named_bar_sync(1, KW * 32);
@@ -275,61 +359,64 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     int s = 0, buf = 0;
     uint32_t parity = 0, pparity = 1;        // pparity: phase before the first one, the first PBUF waits fall through
     for (int64_t tile = t0; tile < t1; tile += tstep) {
-        float acc[2 * Cfg::NC], accm[2 * Cfg::NC];
+        for (int seg = seg0; seg < seg1; ++seg) {
+            float acc[2 * Cfg::NC], accm[2 * Cfg::NC];
 #pragma unroll
-        for (int i = 0; i < 2 * Cfg::NC; ++i) { acc[i] = 0.0f; accm[i] = 0.0f; }
+            for (int i = 0; i < 2 * Cfg::NC; ++i) { acc[i] = 0.0f; accm[i] = 0.0f; }
 
-        for (int rd = 0; rd < rounds; ++rd) {
-            if (warp == 0 && tile == t0 && rd == 0) TICK(14);
-            mbar_wait(smem_u32(&full[s]), parity);
-            if (warp == 0 && tile == t0 && rd == 0) TICK(5);
-            const int kb = rd * KW + warp;
-            if (kb < nb) {
-                const uint8_t *slot_sb = slots + (size_t)s * Cfg::SLOT + warp * BLK_Q4K;
-                if constexpr (N == 1) {
-                    const uint8_t *yblk = q8_s + (size_t)(abase * nb + kb) * Q8_STRIDE;
-                    const int j = r;                                     // this lane's B column = sub-block j
-                    const uint8_t *y0 = (j == 2 * c) ? yblk + 32 * j : zero_s;
-                    const uint8_t *y1 = (j == 2 * c + 1) ? yblk + 32 * j : zero_s;
-                    sb_step_n1(slot_sb, y0, y1, yblk, d_s[abase * nb + kb], lane, acc, accm);
-                } else {
-                    const int ncol = r;                                  // this lane's B column = batch column
-                    const uint8_t *ycol = ncol < N ? q8_s + (size_t)((abase + ncol) * nb + kb) * Q8_STRIDE : zero_s;
-                    const int nlo = min(2 * c, N - 1), nhi = min(2 * c + 1, N - 1);
-                    sb_step_nn<N>(slot_sb, ycol, q8_s + (size_t)((abase + nlo) * nb + kb) * Q8_STRIDE,
-                                  q8_s + (size_t)((abase + nhi) * nb + kb) * Q8_STRIDE,
-                                  d_s[(abase + nlo) * nb + kb], d_s[(abase + nhi) * nb + kb], lane, acc, accm);
+            const int rde = min((seg + 1) * SEG_ROUNDS, rounds);
+            for (int rd = seg * SEG_ROUNDS; rd < rde; ++rd) {
+                if (warp == 0 && tile == t0 && rd == seg0 * SEG_ROUNDS) TICK(14);
+                mbar_wait(smem_u32(&full[s]), parity);
+                if (warp == 0 && tile == t0 && rd == seg0 * SEG_ROUNDS) TICK(5);
+                const int kb = rd * KW + warp;
+                if (kb < nb) {
+                    const uint8_t *slot_sb = slots + (size_t)s * Cfg::SLOT + warp * BLK_Q4K;
+                    if constexpr (N == 1) {
+                        const uint8_t *yblk = q8_s + (size_t)(abase * nb + kb) * Q8_STRIDE;
+                        const int j = r;                                     // this lane's B column = sub-block j
+                        const uint8_t *y0 = (j == 2 * c) ? yblk + 32 * j : zero_s;
+                        const uint8_t *y1 = (j == 2 * c + 1) ? yblk + 32 * j : zero_s;
+                        sb_step_n1(slot_sb, y0, y1, yblk, d_s[abase * nb + kb], lane, acc, accm);
+                    } else {
+                        const int ncol = r;                                  // this lane's B column = batch column
+                        const uint8_t *ycol = ncol < N ? q8_s + (size_t)((abase + ncol) * nb + kb) * Q8_STRIDE : zero_s;
+                        const int nlo = min(2 * c, N - 1), nhi = min(2 * c + 1, N - 1);
+                        sb_step_nn<N>(slot_sb, ycol, q8_s + (size_t)((abase + nlo) * nb + kb) * Q8_STRIDE,
+                                      q8_s + (size_t)((abase + nhi) * nb + kb) * Q8_STRIDE,
+                                      d_s[(abase + nlo) * nb + kb], d_s[(abase + nhi) * nb + kb], lane, acc, accm);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&empty[s]));
+                if (++s == S) { s = 0; parity ^= 1u; }
+            }
+
+            if (warp == 0 && tile == t0 && seg == seg0) TICK(6);
+            // ---- segment epilogue: chunk lanes here, the eight warps in order in the reducer warp ----
+            mbar_wait(smem_u32(&pempty[buf]), pparity);
+            float *part = part_s + (size_t)buf * KW * N * MROWS + (size_t)warp * N * MROWS;
+            if constexpr (N == 1) {
+                float v0 = __fadd_rn(acc[0], accm[0]), v1 = __fadd_rn(acc[1], accm[1]);
+                v0 = __fadd_rn(v0, __shfl_xor_sync(0xffffffffu, v0, 1));
+                v1 = __fadd_rn(v1, __shfl_xor_sync(0xffffffffu, v1, 1));
+                v0 = __fadd_rn(v0, __shfl_xor_sync(0xffffffffu, v0, 2));
+                v1 = __fadd_rn(v1, __shfl_xor_sync(0xffffffffu, v1, 2));
+                if (c == 0) { part[r] = v0; part[r + 8] = v1; }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const int col = 2 * c + k;
+                    if (col < N) {
+                        part[col * MROWS + r] = __fadd_rn(acc[k], accm[k]);
+                        part[col * MROWS + r + 8] = __fadd_rn(acc[2 + k], accm[2 + k]);
+                    }
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&empty[s]));
-            if (++s == S) { s = 0; parity ^= 1u; }
+            if (lane == 0) mbar_arrive(smem_u32(&pfull[buf]));
+            if (++buf == PBUF) { buf = 0; pparity ^= 1u; }
         }
-
-        if (warp == 0 && tile == t0) TICK(6);
-        // ---- tile epilogue: chunk lanes here, the eight warps in order in the reducer warp ----
-        mbar_wait(smem_u32(&pempty[buf]), pparity);
-        float *part = part_s + (size_t)buf * KW * N * MROWS + (size_t)warp * N * MROWS;
-        if constexpr (N == 1) {
-            float v0 = __fadd_rn(acc[0], accm[0]), v1 = __fadd_rn(acc[1], accm[1]);
-            v0 = __fadd_rn(v0, __shfl_xor_sync(0xffffffffu, v0, 1));
-            v1 = __fadd_rn(v1, __shfl_xor_sync(0xffffffffu, v1, 1));
-            v0 = __fadd_rn(v0, __shfl_xor_sync(0xffffffffu, v0, 2));
-            v1 = __fadd_rn(v1, __shfl_xor_sync(0xffffffffu, v1, 2));
-            if (c == 0) { part[r] = v0; part[r + 8] = v1; }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                const int col = 2 * c + k;
-                if (col < N) {
-                    part[col * MROWS + r] = __fadd_rn(acc[k], accm[k]);
-                    part[col * MROWS + r + 8] = __fadd_rn(acc[2 + k], accm[2 + k]);
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&pfull[buf]));
-        if (++buf == PBUF) { buf = 0; pparity ^= 1u; }
         if (tile + tstep < t1) {                                           // the next tile's matrix
             locate(tile + tstep, mat);
             abase = p.xslot[mat] * N;
@@ -346,19 +433,49 @@ int mma_env(const char *name) {              // development knobs (tools/launch_
     return e ? atoi(e) : 0;
 }
 
-size_t mma_fixed_smem(int nrows, int nb, int N, int S) {
+size_t mma_fixed_smem(int nrows, int nb, int N, int S, int KP) {
+    const int rounds = (nb + KW - 1) / KW, nseg = (rounds + SEG_ROUNDS - 1) / SEG_ROUNDS, pseg_max = (nseg + KP - 1) / KP;
     size_t off = (size_t)nrows * nb * Q8_STRIDE + Q8_STRIDE;
     off += ((size_t)nrows * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
-    off += (size_t)PBUF * KW * N * MROWS * 4 + (size_t)S * 16 + (size_t)PBUF * 16;
+    off += (size_t)PBUF * KW * N * MROWS * 4 + (size_t)S * 16 + (size_t)PBUF * 16 + (size_t)XD * 16;
+    if (KP > 1) off += (size_t)XD * (KP - 1) * pseg_max * N * MROWS * 4;
     return ((off + 127) & ~(size_t)127) + 128;
+}
+
+// How many CTAs share a tile along K.  Split when one CTA per tile would leave SMs idle or would make every CTA quantize
+// a long activation vector by itself; the float result does not depend on the choice (segment order, see the kernel).
+int choose_kparts(int64_t tiles, int nb, int nrows /* staged activation rows */, int slots) {
+    const int forced = mma_env("Q4K_DBG_MMA_KPARTS");
+    const int rounds = (nb + KW - 1) / KW, nseg = (rounds + SEG_ROUNDS - 1) / SEG_ROUNDS;
+    if (forced > 0) return forced <= nseg ? forced : 1;
+    // Rough per-launch model in microseconds, fitted to profiles/r1_launch_chain_splitk.txt: every CTA quantizes the
+    // activations of its K part (0.45 us per 8 blocks), then walks its rounds (0.3 us each); two CTAs on one SM slow each
+    // other down.  Splitting only pays while all CTAs of the launch are resident at once (one wave).
+    int best = 1;
+    double best_t = 1e30;
+    for (int kp = 1; kp <= 4; kp *= 2) {
+        if (kp > nseg) break;
+        if (kp > 1 && tiles * kp > slots) break;
+        const bool two = std::min<int64_t>(tiles * kp, slots) > slots / 2;
+        const int prounds = std::min(rounds, (nseg + kp - 1) / kp * SEG_ROUNDS);
+        const int blocks = std::min(nb, prounds * KW) * nrows;
+        const double stage = 0.45 * ((blocks + KW - 1) / KW) * (two ? 1.6 : 1.0);
+        const double waves = (double)((tiles * kp + slots - 1) / slots);
+        const double t = stage + waves * prounds * 0.3 * (two ? 1.3 : 1.0) + (kp > 1 ? 0.5 : 0.0);
+        if (t < best_t - 1e-9) { best_t = t; best = kp; }
+    }
+    return best;
 }
 
 template <int N>
 cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
-    auto kern = gemv_q4k_mma_kernel<N>;
     const size_t slot = MmaCfg<N>::SLOT;
-    const size_t fixed = mma_fixed_smem(N * p.nx, p.nb, N, 8);
+    const int KP = choose_kparts(p.n_groups, p.nb, N * p.nx, sm_count() * 2);
+    p.kparts = KP;
+    const int mode = KP > 1 ? 2 : ((p.nb + KW - 1) / KW <= SEG_ROUNDS ? 0 : 1);
+    auto kern = mode == 2 ? gemv_q4k_mma_kernel<N, 2> : (mode == 1 ? gemv_q4k_mma_kernel<N, 1> : gemv_q4k_mma_kernel<N, 0>);
+    const size_t fixed = mma_fixed_smem(N * p.nx, p.nb, N, 8, KP);
     // two CTAs per SM with as deep a ring as fits (<= 5 slots: 2 x 5 x 18 KB in flight per SM is past the latency-
     // bandwidth product); one CTA per SM when the staged activations are too large for that
     int per_sm = 2;
@@ -374,26 +491,36 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
     p.stages = stages;
     p.interleave = mma_env("Q4K_DBG_MMA_CONTIG") > 0 ? 0 : 1;
     const size_t smem = fixed + (size_t)stages * slot;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[3] = {false, false, false};
+    if (!attr_set[mode]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MMA_SMEM_MAX);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        attr_set[mode] = true;
     }
     int64_t grid = (int64_t)sm_count() * per_sm;
-    if (grid > p.n_groups) grid = p.n_groups;
-    if (grid < 1) grid = 1;
+    if (grid > p.n_groups * KP) grid = p.n_groups * KP;
+    grid -= grid % KP;                               // whole clusters
+    if (grid < KP) grid = KP;
 
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(MMA_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (KP > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = KP; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = na;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
     return e;

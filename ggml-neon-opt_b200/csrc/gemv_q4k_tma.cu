@@ -373,7 +373,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.dst_row0 = dst_row0;
     p.dst_stride = dst_col_stride_bytes / 4;
     p.n_groups = (M + TILE_ROWS - 1) / TILE_ROWS;
-    p.stages = 0; p.interleave = 0;
+    p.stages = 0; p.interleave = 0; p.kparts = 1;
     p.nmat = 1; p.nx = 1;
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
@@ -397,7 +397,7 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
     p.xq = nullptr; p.xf = x[0]; p.x_stride = x_row_stride_bytes;
     for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
     p.dst[0] = dst[0]; p.n_dst = 1; p.dst_row0 = 0; p.dst_stride = M[0];
-    p.stages = 0; p.interleave = 0; p.nmat = nmat; p.nx = 0;
+    p.stages = 0; p.interleave = 0; p.kparts = 1; p.nmat = nmat; p.nx = 0;
     int64_t groups = 0;
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     for (int i = 0; i < nmat; ++i) {

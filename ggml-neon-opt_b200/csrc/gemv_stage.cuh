@@ -32,6 +32,7 @@ struct TmaGemvParams {
     int64_t n_groups;       // total 4-row groups of the launch
     int stages;
     int interleave;         // gemv_q4k_mma.cu: 1 = tiles dealt round-robin to the CTAs (the grid sweeps memory front to back)
+    int kparts;             // gemv_q4k_mma.cu: CTAs of a thread-block cluster that split K of one tile (1, 2 or 4)
     // horizontally fused launch: up to 4 independent matrices with the same K and N (q/k/v, gate/up ...).  Row groups
     // are numbered through all of them; gend[i] = groups of matrices 0..i.  nmat == 1 uses w / M / dst above.
     int nmat, nx;
@@ -82,24 +83,26 @@ __device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c) {
 }
 __device__ __forceinline__ uint4 lds128(const uint8_t *p) { return *reinterpret_cast<const uint4 *>(p); }
 
-// activations already Q8_K in global memory -> the CTA's shared-memory layout
+// activations already Q8_K in global memory -> the CTA's shared-memory layout.  [b0, b0 + nbw) = the window of
+// superblocks this CTA needs (the whole row unless the launch splits K); nbw = 0 means all.
 template <int N>
-__device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, float *d_s, int nt = 0) {
+__device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, float *d_s, int nt = 0, int b0 = 0, int nbw = 0) {
     if (nt == 0) nt = blockDim.x;              // nt: the first nt threads of the CTA take part
     const int tid = threadIdx.x, nb = p.nb;
-    for (int i = tid; i < N * nb * 64; i += nt) {
-        const int blk = i >> 6, wd = i & 63, n = blk / nb, b = blk - n * nb;
+    if (nbw == 0) nbw = nb;
+    for (int i = tid; i < N * nbw * 64; i += nt) {
+        const int e = i >> 6, wd = i & 63, n = e / nbw, b = b0 + e - n * nbw, blk = n * nb + b;
         const uint8_t *src = p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K;
         reinterpret_cast<uint32_t *>(q8_s + (size_t)blk * Q8_STRIDE)[wd] = (reinterpret_cast<const uint32_t *>(src + Q8K_QS))[wd];
     }
-    for (int i = tid; i < N * nb * 8; i += nt) {
-        const int blk = i >> 3, k = i & 7, n = blk / nb, b = blk - n * nb;
+    for (int i = tid; i < N * nbw * 8; i += nt) {
+        const int e = i >> 3, k = i & 7, n = e / nbw, b = b0 + e - n * nbw, blk = n * nb + b;
         const int16_t *bs = reinterpret_cast<const int16_t *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K + Q8K_BSUMS);
         reinterpret_cast<int16_t *>(q8_s + (size_t)blk * Q8_STRIDE + 256)[k] = (int16_t)(bs[2 * k] + bs[2 * k + 1]);   // hadd_epi16
     }
-    for (int i = tid; i < N * nb; i += nt) {
-        const int n = i / nb, b = i - n * nb;
-        d_s[i] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K);
+    for (int i = tid; i < N * nbw; i += nt) {
+        const int n = i / nbw, b = b0 + i - n * nbw;
+        d_s[n * nb + b] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K);
     }
 }
 
@@ -108,28 +111,34 @@ __device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, 
 // Two phases so that nothing but the loads and the arithmetic sits behind griddepcontrol.wait: prepare() reads the
 // launch parameters (first touch of a kernel's constant bank is a cache miss) and does the index arithmetic for the
 // warp's first STAGE_R blocks; run() issues all loads of a round trip before any arithmetic.
+// [b0, b0 + nbw): the window of superblocks this CTA needs (split-K launches stage only their part of K).
 constexpr int STAGE_R = 3;
 
 template <int N>
 struct StageF32 {
     const float *src[STAGE_R];
-    int total, nwarps, nb;
+    int slot[STAGE_R];                   // shared-memory block index of the prepared blocks
+    int total, nwarps, nb, b0, nbw;
     const float *x0, *x1, *x2, *x3;      // the (up to four) distinct activation buffers; scalars, not an array: stays in registers
     int64_t x_stride;
 
-    __device__ __forceinline__ const float *block_src(int blk) const {
-        const int xs = blk / (N * nb), rem = blk - xs * N * nb, n = rem / nb, b = rem - n * nb;
+    // e-th block of this CTA's window -> source pointer and shared-memory block index
+    __device__ __forceinline__ const float *block_src(int e, int &blk) const {
+        const int xs = e / (N * nbw), rem = e - xs * N * nbw, n = rem / nbw, b = b0 + rem - n * nbw;
         const float *x = xs == 0 ? x0 : (xs == 1 ? x1 : (xs == 2 ? x2 : x3));
+        blk = (xs * N + n) * nb + b;
         return reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + n * x_stride) + b * QK_K;
     }
-    __device__ __forceinline__ void prepare(const TmaGemvParams &p, int nt) {
-        nb = p.nb; nwarps = nt >> 5; total = p.nx * N * nb; x_stride = p.x_stride;
+    __device__ __forceinline__ void prepare(const TmaGemvParams &p, int nt, int win0 = 0, int win = 0) {
+        nb = p.nb; b0 = win0; nbw = win ? win : p.nb;
+        nwarps = nt >> 5; total = p.nx * N * nbw; x_stride = p.x_stride;
         x0 = p.xsrc[0]; x1 = p.xsrc[1]; x2 = p.xsrc[2]; x3 = p.xsrc[3];
         const int warp = threadIdx.x >> 5;
 #pragma unroll
         for (int rr = 0; rr < STAGE_R; ++rr) {
-            const int blk = warp + rr * nwarps;
-            src[rr] = blk < total ? block_src(blk) : nullptr;
+            const int e = warp + rr * nwarps;
+            slot[rr] = 0;
+            src[rr] = e < total ? block_src(e, slot[rr]) : nullptr;
         }
     }
     __device__ __forceinline__ void quantize_to(const float4 &a, const float4 &c, int blk, uint8_t *q8_s, float *d_s) const {
@@ -159,21 +168,23 @@ struct StageF32 {
                 }
             }
 #ifdef Q4K_TIMING
-            if (warp == 0) { asm volatile("" ::"f"(a[0].x), "f"(c[0].x)); TICK(13); }
+            if (warp == 0) TICK(13);
 #endif
 #pragma unroll
             for (int rr = 0; rr < STAGE_R; ++rr)
-                if (src[rr]) quantize_to(a[rr], c[rr], warp + rr * nwarps, q8_s, d_s);
+                if (src[rr]) quantize_to(a[rr], c[rr], slot[rr], q8_s, d_s);
         }
         if (total > STAGE_R * nwarps) {                                               // long activations: the rest
 #pragma unroll 1
             for (int base = warp + STAGE_R * nwarps; base < total; base += nwarps * STAGE_R) {
                 const float *sp[STAGE_R];
+                int sl[STAGE_R];
                 float4 a[STAGE_R], c[STAGE_R];
 #pragma unroll
                 for (int rr = 0; rr < STAGE_R; ++rr) {
-                    const int blk = base + rr * nwarps;
-                    sp[rr] = blk < total ? block_src(blk) : nullptr;
+                    const int e = base + rr * nwarps;
+                    sl[rr] = 0;
+                    sp[rr] = e < total ? block_src(e, sl[rr]) : nullptr;
                     if (sp[rr]) {
                         a[rr] = reinterpret_cast<const float4 *>(sp[rr])[lane];
                         c[rr] = reinterpret_cast<const float4 *>(sp[rr])[32 + lane];
@@ -181,24 +192,24 @@ struct StageF32 {
                 }
 #pragma unroll
                 for (int rr = 0; rr < STAGE_R; ++rr)
-                    if (sp[rr]) quantize_to(a[rr], c[rr], base + rr * nwarps, q8_s, d_s);
+                    if (sp[rr]) quantize_to(a[rr], c[rr], sl[rr], q8_s, d_s);
             }
         }
     }
 };
-
-// Reads one field of every 64-byte piece of the launch parameters: the first access to a kernel's constant bank misses
-// the constant cache (~0.3 us); done before griddepcontrol.wait, the misses overlap the previous kernel.
-__device__ __forceinline__ void touch_params(const TmaGemvParams &p) {
-    asm volatile("" ::"l"(p.w), "l"(p.x_stride), "l"(p.dst[3]), "l"(p.dst[7]), "l"(p.dst_row0), "l"(p.dst_stride), "r"(p.nmat),
-                 "l"(p.wm[3]), "l"(p.Mm[3]), "l"(p.gend[3]), "l"(p.dstm[3]), "l"(p.xsrc[3]), "r"(p.xslot[3]));
-}
 
 template <int N>
 __device__ __forceinline__ void stage_f32(const TmaGemvParams &p, uint8_t *q8_s, float *d_s, int nt = 0) {
     StageF32<N> st;
     st.prepare(p, nt == 0 ? blockDim.x : nt);
     st.run(q8_s, d_s);
+}
+
+// Reads one field of every 64-byte piece of the launch parameters: the first access to a kernel's constant bank misses
+// the constant cache (~0.3 us); done before griddepcontrol.wait, the misses overlap the previous kernel.
+__device__ __forceinline__ void touch_params(const TmaGemvParams &p) {
+    asm volatile("" ::"l"(p.w), "l"(p.x_stride), "l"(p.dst[3]), "l"(p.dst[7]), "l"(p.dst_row0), "l"(p.dst_stride), "r"(p.nmat),
+                 "l"(p.wm[3]), "l"(p.Mm[3]), "l"(p.gend[3]), "l"(p.dstm[3]), "l"(p.xsrc[3]), "r"(p.xslot[3]));
 }
 
 }  // namespace

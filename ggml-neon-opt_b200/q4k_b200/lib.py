@@ -13,7 +13,8 @@ import torch
 
 QK_K, Q4K_BLOCK, Q8K_BLOCK = 256, 144, 292
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.normpath(os.path.join(_HERE, "..", "lib", "libq4k_b200.so"))
+# Q4K_B200_LIB: another build of the same library (A/B comparisons of kernels on one GPU box); default = the in-tree build
+_LIB_PATH = os.environ.get("Q4K_B200_LIB") or os.path.normpath(os.path.join(_HERE, "..", "lib", "libq4k_b200.so"))
 _lib = None
 
 _ERR = {-1: "bad shape", -2: "bad pointer", -3: "workspace too small", -4: "CUDA error", -5: "unsupported"}

@@ -143,7 +143,7 @@ int q4k_debug_set_gemv_order(int mode);
 int q4k_debug_set_gemv_config(int cfg);
 
 /* development knob: largest N*K (floats) for which q4k_mul_mat fuses quantize_row_q8_K into the GEMV launch
- * (default 32768); 0 = always run the quantizer as its own kernel. */
+ * (default 16384); 0 = always run the quantizer as its own kernel. */
 int q4k_debug_set_fuse_limit(int64_t n_floats);
 /* development knob: 1 (default) = GEMV launches use programmatic dependent launch, 0 = plain stream order */
 int q4k_debug_set_pdl(int on);

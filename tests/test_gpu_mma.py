@@ -20,7 +20,7 @@ def fast_order(q4k):
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (2048, 5632, 1), (100, 512, 1), (1, 256, 1), (17, 2560, 1), (64, 14336, 1),
                                    (257, 2048, 2), (300, 2048, 3), (129, 1024, 4), (77, 2048, 5), (40, 512, 6), (50, 768, 7),
-                                   (64, 4096, 8), (33, 5632, 8)])
+                                   (64, 4096, 8), (33, 5632, 8), (32, 28672, 8), (20, 28672, 5)])
 def test_mma_gemv_within_tolerance(q4k, fast_order, M, K, N):
     from oracle import port
     w, x = make_weights(M, K), make_acts(N, K)
@@ -71,3 +71,25 @@ def test_mma_q8_input_equals_fused_f32(q4k, fast_order):
     w, x = t(make_weights(M, K)), t(make_acts(N, K))
     xq = q4k.quantize_q8_K(x)
     assert np.array_equal(q4k.mul_mat_q8(w, xq).cpu().numpy().view(np.uint32), q4k.mul_mat(w, x).cpu().numpy().view(np.uint32))
+
+
+@pytest.mark.parametrize("M,K,N", [(2048, 16384, 1), (100, 14336, 1), (48, 28672, 2), (300, 24576, 5), (33, 8448, 8)])
+def test_mma_split_k_does_not_change_the_bits(q4k, fast_order, M, K, N):
+    """K split over the CTAs of a cluster (1, 2 or 4 parts): the segment sums are added in the same order wherever they
+    were computed, so every split gives the same bits — and all of them are within tolerance of the oracle."""
+    import os
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(N, K)
+    wd, xd = t(w), t(x)
+    outs = {}
+    try:
+        for kp in (1, 2, 4):
+            os.environ["Q4K_DBG_MMA_KPARTS"] = str(kp)
+            outs[kp] = q4k.mul_mat(wd, xd).cpu().numpy()
+    finally:
+        os.environ.pop("Q4K_DBG_MMA_KPARTS", None)
+    policy = q4k.mul_mat(wd, xd).cpu().numpy()
+    assert_close(outs[1], port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    for kp in (2, 4):
+        assert np.array_equal(outs[kp].view(np.uint32), outs[1].view(np.uint32)), kp
+    assert np.array_equal(policy.view(np.uint32), outs[1].view(np.uint32))

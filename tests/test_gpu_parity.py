@@ -98,7 +98,7 @@ def test_fused_quantize_equals_two_kernel_path(q4k, exact_order, M, K, N):
         lib.q4k_debug_set_pdl(0)
         nopdl = q4k.mul_mat(wd, xd).cpu().numpy()
     finally:
-        lib.q4k_debug_set_fuse_limit(32768)
+        lib.q4k_debug_set_fuse_limit(16384)
         lib.q4k_debug_set_pdl(1)
     assert np.array_equal(two.view(np.uint32), fused.view(np.uint32))
     assert np.array_equal(two.view(np.uint32), nopdl.view(np.uint32))

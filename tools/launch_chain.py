@@ -21,9 +21,12 @@ def main():
     ap.add_argument("--n", type=int, default=1)
     ap.add_argument("--tag", default="")
     ap.add_argument("--order", type=int, default=0, help="0 policy, 1 exact, 2 fast")
+    ap.add_argument("--fuse-limit", type=int, default=-1, help="N*K floats up to which the quantizer is fused into the launch")
     a = ap.parse_args()
     lib = q4k_b200.load()
     lib.q4k_debug_set_gemv_order(a.order)
+    if a.fuse_limit >= 0:
+        lib.q4k_debug_set_fuse_limit(a.fuse_limit)
     N = a.n
     for spec in a.specs.split(","):
         ms, K = spec.split("x")

@@ -52,6 +52,8 @@ int main(int argc, char **argv) {
     printf("  stage: loads landed at +%lld cycles after wait-return, quantize +%lld\n", t[13] - t[2], t[3] - t[13]);
     printf("  quantize (warp 0, last block): lane scan +%lld, butterfly +%lld, ballots +%lld, fdiv/round/pack +%lld, sums+d +%lld, stores +%lld\n",
            t[16] - t[13], t[17] - t[16], t[18] - t[17], t[19] - t[18], t[20] - t[19], t[3] - t[20]);
+    printf("  reducer (first tile): own segments done at %lld, remote parts landed +%lld, stored +%lld (cycles after wait-return)\n",
+           t[21] - t[2], t[22] - t[21], t[23] - (t[22] > t[21] ? t[22] : t[21]));
     printf("  globaltimer: entry->wait-return %lld ns, wait-return->end %lld ns\n", t[11] - t[10], t[12] - t[11]);
     return 0;
 }

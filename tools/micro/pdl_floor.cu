@@ -23,7 +23,7 @@ __global__ void k_empty(const float *x, float *y, int mode) {
     }
 }
 
-static float run(int grid, int mode, bool pdl, int chain, int reps, int threads = 256, int smem = 0) {
+static float run(int grid, int mode, bool pdl, int chain, int reps, int threads = 256, int smem = 0, int cluster = 1) {
     if (smem) cudaFuncSetAttribute(k_empty, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     float *x, *y;
     cudaMalloc(&x, 1 << 20); cudaMalloc(&y, 1 << 20);
@@ -34,10 +34,11 @@ static float run(int grid, int mode, bool pdl, int chain, int reps, int threads 
     for (int i = 0; i < chain; ++i) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.stream = st; cfg.dynamicSmemBytes = smem;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+        cudaLaunchAttribute at[2];
+        int na = 0;
+        if (pdl) { at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[na].val.programmaticStreamSerializationAllowed = 1; ++na; }
+        if (cluster > 1) { at[na].id = cudaLaunchAttributeClusterDimension; at[na].val.clusterDim.x = cluster; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1; ++na; }
+        cfg.attrs = at; cfg.numAttrs = na;
         cudaLaunchKernelEx(&cfg, k_empty, (const float *)x, y, mode);
     }
     cudaStreamEndCapture(st, &g);
@@ -62,6 +63,10 @@ int main() {
         for (int threads : {256, 320})
             for (int grid : {128, 296})
                 printf("pdl=1 grid=%3d threads=%d smem=%3dKB mode=2  %.3f us/launch\n", grid, threads, smem >> 10, run(grid, 2, true, 200, 20, threads, smem));
+    for (int cluster : {1, 2, 4})
+        for (int grid : {128, 256})
+            for (int pdl = 0; pdl < 2; ++pdl)
+                printf("cluster=%d pdl=%d grid=%3d threads=320 smem=105KB mode=2  %.3f us/launch\n", cluster, pdl, grid, run(grid, 2, pdl, 200, 20, 320, 105 << 10, cluster));
     cudaError_t e = cudaDeviceSynchronize();
     printf("status %s\n", cudaGetErrorString(e));
     return 0;
