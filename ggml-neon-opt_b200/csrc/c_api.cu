@@ -209,9 +209,10 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
                           dst_dev, dst_col_stride_bytes, stream);
 }
 
-int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
-                      const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
-                      float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream) {
+int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                         float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,
+                         void *workspace_dev, size_t workspace_bytes, void *stream) {
     if (M_local < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0 || dst_row0 < 0) return Q4K_ERR_BAD_SHAPE;
     if (N > Q4K_GEMV_MAX_N || n_peers < 1 || n_peers > 8) return Q4K_ERR_UNSUPPORTED;
     if (M_local == 0 || N == 0) return Q4K_OK;
@@ -221,11 +222,27 @@ int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_r
     if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
     if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
     if (dst_col_stride_bytes < (dst_row0 + M_local) * 4 || (dst_col_stride_bytes & 3)) return Q4K_ERR_BAD_SHAPE;
-    const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M_local, K, w_row_stride_bytes, nullptr, x_dev, (int)N, x_row_stride_bytes,
+    const void *xq = nullptr;
+    int64_t xq_stride = x_row_stride_bytes;
+    if (N * K > g_fuse_limit && workspace_dev && workspace_bytes >= (size_t)(N * nb * Q4K_BLOCK_Q8K)) {
+        // long activations: quantize once in a kernel of its own instead of once per CTA (same rule as q4k_mul_mat)
+        const cudaError_t eq = launch_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, (cudaStream_t)stream);
+        if (eq != cudaSuccess) return cuda_fail(eq);
+        xq = workspace_dev;
+        xq_stride = nb * Q4K_BLOCK_Q8K;
+    }
+    const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M_local, K, w_row_stride_bytes, xq, xq ? nullptr : x_dev, (int)N, xq_stride,
                                                   nullptr, dst_col_stride_bytes, gemv_exact_for((int)N), 0, g_gemv_pdl != 0,
                                                   (cudaStream_t)stream, dst_peers, n_peers, dst_row0);
     if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;     // activations too large for one shared-memory residency
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
+int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                      const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                      float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream) {
+    return q4k_mul_mat_peers_ws(w_dev, M_local, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_peers, n_peers, dst_row0,
+                                dst_col_stride_bytes, nullptr, 0, stream);
 }
 
 int q4k_mul_mat_group(int n_mats, const void *const *w_dev, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,

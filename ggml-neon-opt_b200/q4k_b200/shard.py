@@ -8,8 +8,10 @@ output slices are exchanged:
   * `gather="nccl"`  one all_gather of [N, M/G] floats per GPU over NVLink/NVSwitch (torch.distributed, NCCL).
   * `gather="peer"`  no collective kernel at all: the GEMV epilogue stores every result straight into the output
                      buffer of EVERY peer through NVLink-mapped symmetric memory (q4k_mul_mat_peers), followed by
-                     one symmetric-memory barrier.  The payload is tiny (28672 x 4 B per token for the 70B FFN), so
-                     this removes the NCCL launch + protocol latency that dominates the baseline.
+                     one flag exchange (q4k_peer_signal_wait: a one-warp kernel, system-scope release / acquire on
+                     peer-mapped flags, device-side epoch so that it replays inside a CUDA graph).  The payload is
+                     tiny (28672 x 4 B per token for the 70B FFN), so this removes the NCCL launch + protocol
+                     latency that dominates the baseline.
 
 What the reference has instead: ggml-cuda's --split-mode row slices src0 rows by tensor_split, peer-copies src1 to
 each device and copies the dst slices back to the main device only (L/ggml/src/ggml-cuda/ggml-cuda.cu:774-787,
@@ -125,7 +127,15 @@ class RowShardedQ4K:
         self._peer_arr = [(C.c_void_p * self.world)(*[ptrs[r] + b * half for r in order]) for b in range(2)]
         self._flip = 0
         self._out.zero_()
+        # flags of the cross-GPU step: one uint32 per (rank, peer) in symmetric memory + a local call counter
+        self._flags = symm.empty((64,), dtype=torch.int32, device=dev)
+        self._fhdl = symm.rendezvous(self._flags, dist.group.WORLD.group_name if self.group is None else self.group.group_name)
+        self._flag_arr = (C.c_void_p * self.world)(*list(self._fhdl.buffer_ptrs))
+        self._flags.zero_()
+        self._epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)
         self._hdl.barrier(channel=0)
+        self._fhdl.barrier(channel=0)
 
     def mul_mat(self, x: torch.Tensor) -> torch.Tensor:
         """x: replicated F32 activations [N, K] (identical on every rank) -> [N, M] on every rank.  With the peer
@@ -137,11 +147,15 @@ class RowShardedQ4K:
             b = self._flip
             self._flip ^= 1
             if self.r1 > self.r0:
-                rc = lib.q4k_mul_mat_peers(self.w.data_ptr(), self.r1 - self.r0, self.K, self.w.stride(0), x.data_ptr(), N, x.stride(0) * 4,
-                                           self._peer_arr[b], self.world, self.r0, self.M * 4, st)
+                if self._ws is None or self._ws.numel() < self._lib.workspace_bytes(self.K, N):
+                    self._ws = torch.empty(max(self._lib.workspace_bytes(self.K, self.max_n), 16), dtype=torch.uint8, device=self.w.device)
+                rc = lib.q4k_mul_mat_peers_ws(self.w.data_ptr(), self.r1 - self.r0, self.K, self.w.stride(0), x.data_ptr(), N, x.stride(0) * 4,
+                                              self._peer_arr[b], self.world, self.r0, self.M * 4, self._ws.data_ptr(), self._ws.numel(), st)
                 if rc != 0:
-                    raise self._lib.Q4KError("q4k_mul_mat_peers", rc, lib.q4k_last_cuda_error())
-            self._hdl.barrier(channel=0)                 # every rank's stores have landed everywhere
+                    raise self._lib.Q4KError("q4k_mul_mat_peers_ws", rc, lib.q4k_last_cuda_error())
+            rc = lib.q4k_peer_signal_wait(self._flag_arr, self.world, self.rank, self._epoch.data_ptr(), st)   # every rank's stores have landed
+            if rc != 0:
+                raise self._lib.Q4KError("q4k_peer_signal_wait", rc, lib.q4k_last_cuda_error())
             return self._out[b, :N]
         local = self._lib.mul_mat(self.w, x) if self.r1 > self.r0 else x.new_empty((N, 0))
         return all_gather_rows(local, self.ranges, self.M, self.group)

@@ -88,6 +88,21 @@ int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_r
                       const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
                       float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream);
 
+/* q4k_mul_mat_peers with a Q8_K workspace (>= q4k_mul_mat_workspace_bytes(K, N)): long activation rows (N*K above the
+ * fuse limit) are quantized once by a kernel of their own instead of once per CTA, as q4k_mul_mat does. */
+int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                         float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,
+                         void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* the cross-GPU step after q4k_mul_mat_peers: "all ranks' result stores have landed everywhere".  flags_peers[r] = the
+ * peer-mapped pointer to rank r's flag buffer (world x uint32, zero-initialised once, same symmetric allocation on every
+ * rank), epoch_dev = a zero-initialised uint32 in this rank's device memory.  One small kernel: bumps the epoch, publishes
+ * it into every peer's flags (system-scope release), waits for every peer's epoch (system-scope acquire).  Every rank must
+ * call it the same number of times.  Graph-capturable; no host synchronisation.  Replaces the ncclAllGather / event +
+ * cudaMemcpyPeerAsync gather of a row split (L/ggml/src/ggml-cuda/ggml-cuda.cu:1720-1760). */
+int q4k_peer_signal_wait(void *const *flags_peers, int world, int rank, void *epoch_dev, void *stream);
+
 /* horizontally fused decode launch: n_mats (<= 4) independent mul_mats with the same K and N (<= 8) in ONE kernel
  * launch — e.g. attn_q / attn_k / attn_v or ffn_gate / ffn_up of one layer, which the reference runs as separate
  * ggml_compute_forward_mul_mat nodes.  x_dev[i] may repeat: matrices reading the same activations share one quantized
