@@ -453,6 +453,16 @@ def run_ours(args, rank, world, local_rank):
     ms_e2e = timed_steps(torch, step_host, args.steps, args.warmup, barrier)
     clk = clocks.stop() if rank == 0 else None
 
+    # strong-scaling anchor: the SAME workload, unsharded, on one GPU (every rank measures its own GPU; max over ranks)
+    same_1gpu = None
+    if sharded and world > 1:
+        full = MatSet(torch, q4k_b200, mats, N, device, seed=4321)
+        one_plan = full.make_plan()
+        ms_one = timed_steps(torch, one_plan.run, args.steps, args.warmup, barrier)
+        t1 = torch.tensor([ms_one], device=device, dtype=torch.float64)
+        dist.all_reduce(t1, op=dist.ReduceOp.MAX)
+        same_1gpu = float(t1[0]) / args.steps
+
     t = torch.tensor([ms_total, ms_e2e], device=device, dtype=torch.float64)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -495,6 +505,12 @@ def run_ours(args, rank, world, local_rank):
                     "ms_per_step": round(ms_e2e / args.steps, 5),
                     "decode_tok_s": round(1e3 / (ms_e2e / args.steps), 1) if not sharded else None},
             "gpu_launches": int(launches_per_step * args.steps), "clocks": clk}
+    if same_1gpu is not None:
+        v1 = total_bytes / (same_1gpu * 1e-3) / 1e9
+        line["same_workload_1gpu"] = {"value": round(v1, 2), "unit": "GB/s", "ms_per_step": round(same_1gpu, 5),
+                                      "speedup": round(value / v1, 3),
+                                      "note": "the same matrices unsharded on ONE GPU (q4k_plan_run), measured in this run; the N = 1 bench line "
+                                              "is a different workload (TinyLlama token), so compute strong-scaling efficiency from this field"}
     if world == 1 and not args.no_cpu:
         try:
             line["cpu_baseline"] = cpu_baseline_obj(mats, N, total_bytes)
