@@ -253,6 +253,47 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
     return GGML_STATUS_SUCCESS;
 }
 
+// A decode-shaped mul_mat that can share a launch with its neighbours: plain 2-D, batch <= 8, dense rows on both sides.
+bool groupable(const ggml_tensor * node) {
+    const ggml_tensor * src0 = node->src[0];
+    const ggml_tensor * src1 = node->src[1];
+    return src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src1->ne[1] >= 1 &&
+           src1->ne[1] <= Q4K_GEMV_MAX_N && src0->ne[1] > 0 && node->nb[1] == (size_t) src0->ne[1] * sizeof(float);
+}
+
+// Consecutive MUL_MAT nodes that read the same activations (attn_q / attn_k / attn_v, ffn_gate / ffn_up: separate
+// ggml_mul_mat nodes on one `cur` in the reference's llama graph) go out as ONE launch (q4k_mul_mat_group).
+// Returns the number of nodes consumed starting at cgraph->nodes[i] (0 = not fused, caller runs the node by itself).
+int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i) {
+    ggml_tensor * first = cgraph->nodes[i];
+    if (!groupable(first)) return 0;
+    const void * w[4];
+    int64_t M[4];
+    const float * x[4];
+    float * dst[4];
+    int n = 0, last = i;
+    for (int j = i; j < cgraph->n_nodes && n < 4; ++j) {
+        ggml_tensor * node = cgraph->nodes[j];
+        if (node->op == GGML_OP_NONE || node->op == GGML_OP_RESHAPE || node->op == GGML_OP_VIEW || node->op == GGML_OP_PERMUTE ||
+            node->op == GGML_OP_TRANSPOSE) continue;                          // no-ops in between do not break a group
+        if (node->op != GGML_OP_MUL_MAT || !mul_mat_supported(node) || !groupable(node)) break;
+        if (node->src[1] != first->src[1] || node->src[0]->ne[0] != first->src[0]->ne[0] || node->src[0]->nb[1] != first->src[0]->nb[1]) break;
+        w[n] = node->src[0]->data; M[n] = node->src[0]->ne[1]; x[n] = (const float *) node->src[1]->data; dst[n] = (float *) node->data;
+        ++n;
+        last = j;
+    }
+    if (n < 2) return 0;
+    const ggml_tensor * src1 = first->src[1];
+    const int rc = q4k_mul_mat_group(n, w, M, first->src[0]->ne[0], (int64_t) first->src[0]->nb[1], x, src1->ne[1], (int64_t) src1->nb[1], dst,
+                                     ctx->stream);
+    if (rc == Q4K_ERR_UNSUPPORTED) return 0;
+    if (rc != Q4K_OK) {
+        GGML_LOG_ERROR("Q4K_B200: q4k_mul_mat_group(%s ...) failed: rc=%d cudaError=%d\n", first->name, rc, q4k_last_cuda_error());
+        return -1;
+    }
+    return last - i + 1;
+}
+
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     auto * ctx = (backend_context *) backend->context;
     if (q4k_set_device(ctx->dev->cuda_device) != Q4K_OK) return GGML_STATUS_FAILED;
@@ -263,6 +304,9 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
                 if (!mul_mat_supported(node)) {
                     GGML_ABORT("Q4K_B200: %s: MUL_MAT node outside the supports_op contract reached graph_compute", node->name);
                 }
+                const int fused = try_fused_group(ctx, cgraph, i);
+                if (fused < 0) return GGML_STATUS_FAILED;
+                if (fused > 0) { i += fused - 1; break; }
                 const ggml_status st = compute_mul_mat(ctx, node);
                 if (st != GGML_STATUS_SUCCESS) return st;
             } break;

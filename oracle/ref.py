@@ -55,6 +55,8 @@ def libs():
         shim.ref_mul_mat_q4k.restype = i32
         shim.ref_plugin_mul_mat_q4k.argtypes = [C.c_char_p, vp, i64, i64, vp, i64, vp, i32, C.POINTER(C.c_double)]
         shim.ref_plugin_mul_mat_q4k.restype = i32
+        shim.ref_plugin_mul_mat_shared_q4k.argtypes = [C.c_char_p, i32, vp, C.POINTER(i64), i64, vp, i64, vp]
+        shim.ref_plugin_mul_mat_shared_q4k.restype = i32
         shim.ref_cpu_has_avx2.restype = i32
         shim.ref_mul_mat_set_q4k.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), i64, i32, i32, i32,
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -165,6 +167,22 @@ def plugin_mul_mat(so_path: str, w: np.ndarray, x: np.ndarray, iters: int = 1):
     if rc != 0:
         raise RuntimeError(f"ref_plugin_mul_mat_q4k rc={rc}")
     return dst, secs[0], secs[1]
+
+
+def plugin_mul_mat_shared(so_path: str, ws, x: np.ndarray):
+    """Several Q4_K matrices on ONE activation tensor (q/k/v of a layer) as one graph on our backend plugin."""
+    shim = libs()[3]
+    ws = [np.ascontiguousarray(w, dtype=np.uint8) for w in ws]
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    N, K = x.shape
+    n = len(ws)
+    outs = [np.zeros((N, w.shape[0]), np.float32) for w in ws]
+    rc = shim.ref_plugin_mul_mat_shared_q4k(so_path.encode(), n, (C.c_void_p * n)(*[w.ctypes.data for w in ws]),
+                                            (C.c_int64 * n)(*[w.shape[0] for w in ws]), K, _p(x), N,
+                                            (C.c_void_p * n)(*[o.ctypes.data for o in outs]))
+    if rc != 0:
+        raise RuntimeError(f"ref_plugin_mul_mat_shared_q4k rc={rc}")
+    return outs
 
 
 def mul_mat_set(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, iters: int = 3):

@@ -116,6 +116,50 @@ int ref_plugin_mul_mat_q4k(const char *path, const void *w_q4k, int64_t M, int64
     return rc;
 }
 
+/* n_mats Q4_K mul_mats on ONE activation tensor (attn_q / attn_k / attn_v of a layer: three ggml_mul_mat nodes on the same
+ * `cur`), as one graph on the plugin's first device.  w_q4k[i] is [Ms[i]][K/256*144], dst[i] receives [N][Ms[i]]. */
+int ref_plugin_mul_mat_shared_q4k(const char *path, int n_mats, const void *const *w_q4k, const int64_t *Ms, int64_t K,
+                                  const float *x, int64_t N, float *const *dst) {
+    static ggml_backend_reg_t reg = NULL;
+    if (!reg) reg = ggml_backend_load(path);
+    if (!reg) return -10;
+    if (ggml_backend_reg_dev_count(reg) < 1) return -11;
+    ggml_backend_dev_t dev = ggml_backend_reg_dev_get(reg, 0);
+    ggml_backend_t be = ggml_backend_dev_init(dev, NULL);
+    if (!be) return -13;
+    struct ggml_init_params ip = { ggml_tensor_overhead() * (size_t)(2 * n_mats + 8) + ggml_graph_overhead(), NULL, true };
+    struct ggml_context *ctx = ggml_init(ip);
+    if (!ctx) { ggml_backend_free(be); return -1; }
+    struct ggml_cgraph *gf = ggml_new_graph(ctx);
+    struct ggml_tensor *xs = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, K, N);
+    struct ggml_tensor *ws[8], *ys[8];
+    int rc = 0;
+    if (n_mats > 8) { rc = -1; goto out; }
+    for (int i = 0; i < n_mats; ++i) {
+        ws[i] = ggml_new_tensor_2d(ctx, GGML_TYPE_Q4_K, K, Ms[i]);
+        ys[i] = ggml_mul_mat(ctx, ws[i], xs);
+        ggml_build_forward_expand(gf, ys[i]);
+    }
+    {
+        ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors(ctx, be);
+        if (!buf) { rc = -2; goto out; }
+        for (int i = 0; i < n_mats; ++i) {
+            if (!ggml_backend_dev_supports_op(dev, ys[i])) { rc = -12; break; }
+            ggml_backend_tensor_set(ws[i], w_q4k[i], 0, ggml_nbytes(ws[i]));
+        }
+        if (!rc) {
+            ggml_backend_tensor_set(xs, x, 0, ggml_nbytes(xs));
+            if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -3;
+            for (int i = 0; i < n_mats && !rc; ++i) ggml_backend_tensor_get(ys[i], dst[i], 0, ggml_nbytes(ys[i]));
+        }
+        ggml_backend_buffer_free(buf);
+    }
+out:
+    ggml_free(ctx);
+    ggml_backend_free(be);
+    return rc;
+}
+
 int ref_cpu_has_avx2(void) { return ggml_cpu_has_avx2(); }
 int ref_n_backend_devices(void) { return (int)ggml_backend_dev_count(); }
 

@@ -61,6 +61,32 @@ def test_plugin_graph_matches_reference_cpu_backend(M, K, N):
 
 @needs_ref
 @pytest.mark.gpu
+@pytest.mark.parametrize("N", [1, 4, 16])
+def test_plugin_fuses_mul_mats_on_one_activation_tensor(N):
+    """q / k / v of a layer: three ggml_mul_mat nodes on one `cur`.  graph_compute sends them out as one launch
+    (q4k_mul_mat_group) for N <= 8 and one by one above; either way every result equals the single-node graph's bits."""
+    import ctypes
+    K = 1024
+    ws = [make_weights(M, K, seed=21 + i) for i, M in enumerate((512, 128, 96))]
+    x = make_acts(N, K)
+    lib = ctypes.CDLL(os.path.join(ROOT, "ggml-neon-opt_b200", "lib", "libq4k_b200.so"))
+    lib.q4k_kernel_launches.restype = ctypes.c_int64
+    n0 = lib.q4k_kernel_launches()
+    outs = ref.plugin_mul_mat_shared(PLUGIN, ws, x)
+    launches = lib.q4k_kernel_launches() - n0
+    if N <= 8:
+        assert launches == 1, launches
+    for w, o in zip(ws, outs):
+        alone, _, _ = ref.plugin_mul_mat(PLUGIN, w, x)
+        assert np.array_equal(o.view(np.uint32), alone.view(np.uint32))
+        cpu, _, _ = ref.mul_mat(w, x, n_threads=4)
+        f64 = port.mul_mat_f64(w, x)
+        rms = np.sqrt((f64 ** 2).mean(axis=1, keepdims=True))
+        assert np.all(np.abs(o - cpu) <= 1e-5 * np.maximum(np.abs(cpu), rms))
+
+
+@needs_ref
+@pytest.mark.gpu
 def test_reference_test_backend_ops_mul_mat():
     env = dict(os.environ, GGML_BACKEND_PATH=PLUGIN)
     p = subprocess.run([TBO, "test", "-o", "MUL_MAT", "-b", "Q4K_B200_0"], env=env, capture_output=True, text=True, timeout=900)
