@@ -125,9 +125,8 @@ size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
     if (K <= 0 || N <= 0 || K % Q4K_QK_K != 0) return 0;
     const size_t nb = (size_t)(K / Q4K_QK_K);
     size_t need = (size_t)N * nb * Q4K_BLOCK_Q8K;                        // block_q8_K rows (decode path)
-    if (N > Q4K_GEMV_MAX_N) {                                            // prefill path: int8 in whole 128-column tiles + scales
-        const size_t npad = ((size_t)N + 127) / 128 * 128;
-        const size_t gemm = npad * (size_t)K + nb * (size_t)N * 4;
+    if (N > Q4K_GEMV_MAX_N) {                                            // prefill path: int8 + mins tiles of whole 128-column tiles, scales
+        const size_t gemm = q4k::gemm_workspace_bytes(K, N);
         if (gemm > need) need = gemm;
     }
     return need;

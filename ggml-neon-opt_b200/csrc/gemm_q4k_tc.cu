@@ -1,35 +1,46 @@
-// gemm_q4k_tc.cu — prefill GEMM (batch > 8) on the 5th-generation tensor cores: tcgen05.mma kind::i8, TMEM accumulators.
+// gemm_q4k_tc.cu — prefill GEMM (batch > 8) on the 5th-generation tensor cores: tcgen05.mma, TMEM accumulators,
+// weights fed to the tensor core from TENSOR MEMORY (the A operand never touches shared memory).
 // dst[n][m] = sum_blk  d_x[n,blk] * ( d_w[m,blk] * sumi[m,n,blk]  -  dmin_w[m,blk] * summ[m,n,blk] )
 // which is ggml_compute_forward_mul_mat for Q4_K x F32 at ne11 = N (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401) with
 // the integer stage of ggml_vec_dot_q4_K_q8_K (L/ggml/src/ggml-cpu/quants.c:575-611) kept EXACT:
 //   sumi = sum_j sc[j] * p[j]        p[j] = sum_{l<32} q4[32j+l] * q8[32j+l]
-//   summ = sum_j m[j]  * (sum of the 32 q8 of sub-block j)
+//   summ = sum_j m[j]  * bs[j]       bs[j] = sum of the 32 q8 of sub-block j
 //
-// How the per-sub-block 6-bit scales get through an int8 tensor core exactly.  sc <= 63 and q4 <= 15, so
-// sc*q4 needs 10 bits.  Split the SCALE, not the product:  sc = 8*sh + sl  (sh, sl <= 7).  Then sh*q4 and
-// sl*q4 are <= 105 and fit a signed byte, a packed multiply of four nibble-bytes by sh never carries between
-// bytes, and   sumi = 8 * (A_hi . q8) + (A_lo . q8)   with A_hi = sh*q4, A_lo = sl*q4 accumulated over the
-// whole 256-wide superblock in two TMEM accumulators.  The mins ride the tensor core too: summ = A_m . q8 with
-// A_m[k] = m[sub-block of k] (<= 63), a third accumulator.  One TMEM drain per superblock instead of one per
-// 32-wide sub-block; the fp32 scales d_w*d_x, dmin_w*d_x are applied by the epilogue warps per superblock,
-// sequentially over superblocks (the NEON order of the reference; within 1e-5 of the AVX2 order).
+// sumi through an int8 tensor core, exactly.  sc <= 63 and q4 <= 15, so sc*q4 needs 10 bits.  Split the SCALE, not
+// the product:  sc = 8*sh + sl  (sh, sl <= 7).  Then sh*q4 and sl*q4 are <= 105 and fit a signed byte, a packed
+// multiply of four nibble-bytes by sh never carries between bytes, and  sumi = 8 * (A_hi . q8) + (A_lo . q8)  with
+// A_hi = sh*q4, A_lo = sl*q4 accumulated over the whole 256-wide superblock in two int32 TMEM accumulators
+// (kind::i8).
 //
-// CTA = 128 weight rows x 128 activation columns, 21 warps, warp-specialised:
-//   warps 0-15  epilogue: thread <-> TMEM lane (= weight row); group g = warp / 4 owns columns 32g..32g+31 (groups
-//               0,1 = accumulator half 0, groups 2,3 = half 1).  tcgen05.ld 8 columns x 3 accumulators at a time,
-//               double-buffered, 32 fp32 results per thread in registers.
-//   warps 16-19 producers: coalesced 16-byte cp.async of (a) whole block_q4_K rows of the tile's superblock into a raw
-//               ring and (b) the int8 activation tile, which is stored PRE-TILED in global memory in exactly the
-//               shared-memory order, straight into its B slot; then thread <-> weight row: unpack scales, write the
-//               three int8 A tiles of half a superblock (K = 128) in the canonical K-major no-swizzle UMMA layout
-//               (8-row x 16-byte core matrices).
-//   warp 20     allocates TMEM; one lane issues the MMAs (M = 128, N = 64, K = 32) and commits to mbarriers.
-// Pipelines: A stages (2 x 48 KB), B slots (4 x 16 KB), raw ring (3 x 18 KB), 3 steps of loads in flight; the two
-// column halves of the accumulators alternate between the tensor core and their epilogue groups (the MMAs of half 1
-// overlap the drain of half 0).
+// summ through ONE small MMA per superblock, exactly.  bs[j] is in [-4064, 4064]; write bs = 64*bh + bl with
+// bl = bs & 63, bh = bs >> 6 in [-64, 63].  Then  summ = sum_j (64 m[j]) * bh[j] + m[j] * bl[j]  is a K = 16 dot
+// product whose factors (<= 4032, 6 significant bits) are exact in fp16, whose products are < 2^18 and whose sum is
+// < 2^22: a kind::f16 MMA with an fp32 accumulator computes it without rounding.  The quantizer emits bh / bl.
+//
+// What bounds this kernel is shared-memory bandwidth and issue slots, not the tensor pipe (profiles/r1_gemm_trace_v4.txt:
+// with A in shared memory the MMAs alone read 144 KB per K = 128 step, 1150 cycles at 128 B/clk).  So:
+//   * A_hi / A_lo are written by the producer threads straight from registers into TMEM (tcgen05.st, thread <->
+//     TMEM lane <-> weight row) and read from there by the MMA ([a_tmem] operand form);
+//   * shared memory carries only the int8 activation tile (B), the raw Q4_K bytes and the tiny mins operands.
+//
+// CTA = 128 weight rows x 128 activation columns, 25 warps, warp-specialised:
+//   warps 0-15   epilogue: thread <-> TMEM lane (= weight row) of quadrant warp % 4; column group g = warp / 4 owns
+//                columns 16g..16g+15 of BOTH accumulator halves, so one half drains with all 16 warps while the
+//                tensor core works on the other.
+//   warps 16-23  producers: coalesced 16-byte cp.async of whole block_q4_K rows (raw ring), of the pre-tiled int8
+//                activation tile (straight into its B slot) and of the mins tile; then thread <-> weight row
+//                (quadrant = warp % 4) and K half (warp / 4): unpack scales, multiply nibbles, tcgen05.st.
+//   warp 24      allocates TMEM; one lane issues the MMAs (M = 128, N = 64, K = 32) and commits to mbarriers.
+// TMEM columns: [0,128) A_hi.q8, [128,256) A_lo.q8, [256,384) mins (fp32), [384,512) two A stages x (hi, lo) x 32.
+// The two 64-column halves of the accumulators alternate between the tensor core and the epilogue.
 //
 // Activations (quantize_q8_planar_kernel below): the same int8 / float d that quantize_row_q8_K produces (shared
-// device function, bit-exact), int8 in tile order + float d[nb][N].  bsums are not needed: the mins use the MMA.
+// device function, bit-exact), int8 in tile order + float d[nb][N] + the fp16 mins tile (bh | bl).
+#include <cstdlib>
+
+#include <cuda.h>
+#include <cuda_fp16.h>
+
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
@@ -37,31 +48,45 @@ namespace q4k {
 
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 128;          // CTA tile; BK = K bytes per pipeline stage (half a superblock)
+constexpr int BM = 128, BN = 128, BK = 128;          // CTA tile; BK = K bytes per pipeline step (half a superblock)
 constexpr int HALF_N = 64;                            // columns per accumulator half / per MMA
-constexpr int A_STAGES = 2;                           // unpacked A tiles (A_hi, A_lo, A_m): producers -> MMA
-constexpr int B_SLOTS = 4;                            // activation tiles, written in place by cp.async
-constexpr int RAW_SLOTS = 3;                          // raw block_q4_K bytes of 128 rows x one superblock (coalesced cp.async)
-constexpr int PREFETCH = 3;                           // pipeline steps of global loads in flight per producer thread
-constexpr int TILE_BYTES = BM * BK;                   // 16 KB: one int8 operand tile of a stage
-constexpr int A_STAGE_BYTES = 3 * TILE_BYTES;         // A_hi, A_lo, A_m
+constexpr int B_SLOTS = 6;                            // activation tiles, written in place by cp.async
+constexpr int RAW_SLOTS = 4;                          // raw block_q4_K bytes of 128 rows x one superblock
+constexpr int AM_SLOTS = 2, BMIN_SLOTS = 4;           // mins operands (per superblock): weights side, activation side
+constexpr int TILE_BYTES = BN * BK;                   // 16 KB: the int8 activation tile of a step
+constexpr int MIN_TILE_BYTES = 128 * 16 * 2;          // 4 KB: 128 rows (or columns) x 16 fp16
 constexpr int RAW_ROW_BYTES = BLK_Q4K, RAW_SLOT_BYTES = BM * RAW_ROW_BYTES;
-constexpr int SMEM_A = 0, SMEM_B = SMEM_A + A_STAGES * A_STAGE_BYTES, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES;
-constexpr int SMEM_DX = SMEM_RAW + RAW_SLOTS * RAW_SLOT_BYTES, SMEM_BARS = SMEM_DX + 1024;
+constexpr int EPI_WARPS = 16, PROD_WARPS = 8;
+constexpr int PROD_THREADS = PROD_WARPS * 32;
+constexpr int EPI_COLS = 16;                          // columns per epilogue thread per half
+constexpr int MMA_WARP = EPI_WARPS + PROD_WARPS, LOAD_WARP = MMA_WARP + 1;
+constexpr int GEMM_THREADS = (LOAD_WARP + 1) * 32;   // 832
+constexpr int SMEM_B = 0, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES, SMEM_AM = SMEM_RAW + RAW_SLOTS * RAW_SLOT_BYTES;
+constexpr int SMEM_BMIN = SMEM_AM + AM_SLOTS * MIN_TILE_BYTES, SMEM_DX = SMEM_BMIN + BMIN_SLOTS * MIN_TILE_BYTES;
+constexpr int SMEM_BARS = SMEM_DX + EPI_WARPS * 2 * 32 * 4;
 constexpr int SMEM_TOTAL = SMEM_BARS + 256;
-constexpr int EPI_WARPS = 16, PROD_WARPS = 4;        // 4 epilogue groups of 4 warps (32 columns each), 2 groups per accumulator half
-constexpr int EPI_COLS = BN / (EPI_WARPS / 4);        // 32 columns per epilogue thread
-constexpr int GEMM_THREADS = (EPI_WARPS + PROD_WARPS + 1) * 32;   // 672
-constexpr int TMEM_COLS = 512;                        // 3 accumulators x 128 columns, rounded to a power of two
-constexpr uint32_t SBO_BYTES = 8 * BK;                // 1024: next 8-row group of core matrices
-constexpr uint32_t LBO_BYTES = 128;                   // next 16-byte K chunk (core matrices of a row group are contiguous)
+constexpr int TMEM_COLS = 512;
+constexpr uint32_t TM_HI = 0, TM_LO = 128, TM_MIN = 256, TM_A = 384;   // TMEM column of each region
+constexpr uint32_t TM_A_STAGE = 64, TM_A_TILE = 32;  // columns per A stage (hi + lo) and per tile (128 bytes of K)
+constexpr uint32_t SBO_BYTES = 8 * BK;                // int8 B tile: next 8-column group of core matrices
+constexpr uint32_t LBO_BYTES = 128;                   // next 16-byte K chunk (core matrices of a group are contiguous)
+constexpr uint32_t MIN_SBO_BYTES = 256;               // mins tiles: 8 rows x (2 chunks x 16 bytes)
+
+#ifdef Q4K_GEMM_TRACE
+__device__ long long g_gemm_trace[16][256];
+#define TR(slot, idx) do { if (blockIdx.x == 0 && blockIdx.y == 0 && (idx) < 256) g_gemm_trace[slot][idx] = clock64(); } while (0)
+#else
+#define TR(slot, idx) do { } while (0)
+#endif
 
 struct GemmParams {
+    CUtensorMap wmap;       // the weights as a 2-D byte tensor [M][row stride], box = 128 rows x one block_q4_K (144 bytes)
     const uint8_t *w;
     int64_t M, w_stride;
     int nb;
     const int8_t *xq;       // int8 activations, pre-tiled: [column tile][superblock][half][16 KB canonical B tile]
     const float *xd;        // [nb][Nld]
+    const uint8_t *bmin;    // fp16 mins tiles: [column tile][superblock][4 KB canonical tile: 128 columns x (bh[8] | bl[8])]
     int64_t N, Nld;
     float *dst;
     int64_t dst_stride;     // floats between dst columns
@@ -82,35 +107,91 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     } while (!done);
 }
+// long waits (a whole pipeline stage): polling steals issue slots from the warps that work.  mode 1: hardware suspend
+// hint, mode 2: nanosleep backoff, 0: plain polling
+template <int MODE>
+__device__ __forceinline__ void mbar_wait_long(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    if (MODE == 1) {
+        do {
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(bar), "r"(parity), "r"(100000u) : "memory");
+        } while (!done);
+    } else if (MODE == 2) {
+        for (;;) {
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+            if (done) break;
+            __nanosleep(32);
+        }
+    } else {
+        mbar_wait(bar, parity);
+    }
+}
+#ifndef Q4K_GEMM_WAIT
+#define Q4K_GEMM_WAIT 1
+#endif
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+// packed fp32 pairs (sm_100): the same round-to-nearest results as two scalar operations, half the issue slots
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // shared-memory matrix descriptor, K-major, SWIZZLE_NONE ("interleave"): 8-row x 16-byte core matrices,
 // LBO = byte distance between the two 16-byte K chunks of one MMA, SBO = byte distance between 8-row groups
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t sbo_bytes) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3ffffu) >> 4);                    // start address, bits [0,14)
     d |= (uint64_t)(LBO_BYTES >> 4) << 16;                       // leading byte offset, bits [16,30)
-    d |= (uint64_t)(SBO_BYTES >> 4) << 32;                       // stride byte offset, bits [32,46)
+    d |= (uint64_t)(sbo_bytes >> 4) << 32;                       // stride byte offset, bits [32,46)
     d |= (uint64_t)1 << 46;                                      // descriptor version 1 (sm_100)
     return d;                                                    // base offset 0, layout type 0 = no swizzle
 }
 
-// instruction descriptor for kind::i8: D = S32, A = B = signed 8-bit, both K-major, M = 128, N = 64
-__device__ __forceinline__ uint32_t umma_idesc_i8() {
+// instruction descriptors, M = 128, N = 64, both operands K-major.  kind::i8: D = S32, A = B = signed 8-bit;
+// kind::f16: D = F32, A = B = F16
+__device__ __forceinline__ uint32_t umma_idesc(bool f16) {
     uint32_t d = 0;
-    d |= 2u << 4;                   // c_format: S32
-    d |= 1u << 7;                   // a_format: signed 8-bit
-    d |= 1u << 10;                  // b_format: signed 8-bit
+    d |= (f16 ? 1u : 2u) << 4;      // c_format: F32 / S32
+    if (!f16) {
+        d |= 1u << 7;               // a_format: signed 8-bit   (F16 = 0)
+        d |= 1u << 10;              // b_format: signed 8-bit
+    }
     d |= (uint32_t)(HALF_N >> 3) << 17;
     d |= (uint32_t)(BM >> 4) << 24;
     return d;
 }
 
-__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+// D[tmem] (+)= A[tmem] * B[smem]   — the A operand comes from tensor memory: lane = row, 4 int8 per 32-bit column
+__device__ __forceinline__ void umma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// D[tmem] = A[smem] * B[smem], fp16 operands, fp32 accumulator (the mins)
+__device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 // arrives on the mbarrier when every MMA issued so far by this thread has completed
@@ -130,98 +211,103 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
                  : "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-}  // namespace
-
-namespace {
-
-__device__ __forceinline__ uint4 ldg16(const void *p) { return *reinterpret_cast<const uint4 *>(p); }
-
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+// 16 consecutive 32-bit columns of the thread's TMEM lane
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// Global -> shared copies of one pipeline step, 16 bytes per cp.async, consecutive threads on consecutive chunks
-// (coalesced; the destination is linear in the chunk index for both operands):
-//   B tile of `step`      : 1024 chunks, the activations are stored pre-tiled in exactly the shared-memory order
-//   raw weights of `sb`   : 128 rows x 9 chunks (whole block_q4_K), issued together with the B tile of step 2*sb
-__device__ __forceinline__ void producer_issue(const GemmParams &p, uint32_t smem0, int t, int64_t m0, int64_t ntile, int step) {
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// TMA tile copy of a 2-D box global -> shared (coordinates: c0 = byte inside the row, c1 = row)
+__device__ __forceinline__ void tma_g2s_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+
+// Global -> shared copies of one pipeline step, issued by one lane of the loader warp:
+//   B tile of `step`        : one 16 KB bulk copy (the activations are stored pre-tiled in exactly the shared-memory order)
+//   mins tile of `sb`       : one 4 KB bulk copy                                          } with the B tile of step 2*sb
+//   raw weights of `sb`     : one TMA box, 128 rows x 144 bytes (rows past M read as zero) }
+__device__ __forceinline__ void loader_issue(const GemmParams &p, uint32_t smem0, uint32_t full, uint32_t rawfull, int m0, int64_t ntile, int step) {
     const int kb = step >> 1, hh = step & 1;
-    const int8_t *bsrc = p.xq + (((ntile * p.nb + kb) * 2 + hh) << 14) + 16 * t;
-    const uint32_t bdst = smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES + 16 * t;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) cp_async16(bdst + i * 2048, bsrc + i * 2048);
+    mbar_expect_tx(full, TILE_BYTES + (hh == 0 ? MIN_TILE_BYTES : 0));
+    bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + kb) * 2 + hh) << 14), TILE_BYTES, full);
     if (hh == 0) {
-        const uint32_t raw = smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES;
+        bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + kb) << 12), MIN_TILE_BYTES, full);
+        mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
+        tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, &p.wmap, kb * BLK_Q4K, m0, rawfull);
+    }
+}
+
+// the thread's 64 weights of this step (one 32-byte group of its raw row: low nibbles = sub-block 2j, high nibbles
+// = sub-block 2j + 1) -> 2 x 16 TMEM columns: A_hi = sh * q4, A_lo = sl * q4, K order = element order
+__device__ __forceinline__ void producer_unpack(uint32_t (&hi)[16], uint32_t (&lo)[16], const uint8_t *raw, const uint4 sm, int j) {
+    const uint4 qa = *reinterpret_cast<const uint4 *>(raw + 16 + 32 * j), qb = *reinterpret_cast<const uint4 *>(raw + 32 + 32 * j);
+    const uint32_t qw[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+    const uint32_t sc2 = byte_pair(sm.x, sm.y, j);
 #pragma unroll
-        for (int i = 0; i < 9; ++i) {
-            const int c = i * 128 + t, r = c / 9, ch = c - 9 * r;
-            int64_t row = m0 + r;
-            if (row >= p.M) row = p.M - 1;
-            cp_async16(raw + 16 * c, p.w + row * p.w_stride + (int64_t)kb * BLK_Q4K + 16 * ch);
+    for (int nib = 0; nib < 2; ++nib) {
+        const uint32_t sc = (sc2 >> (8 * nib)) & 0xffu, sh = sc >> 3, sl = sc & 7u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t v = (nib ? (qw[i] >> 4) : qw[i]) & 0x0f0f0f0fu;
+            hi[8 * nib + i] = v * sh;
+            lo[8 * nib + i] = v * sl;
         }
     }
 }
 
-// the thread's raw row (in shared memory) -> three int8 A tiles of the stage
-__device__ __forceinline__ void producer_unpack(uint8_t *a_stage, const uint8_t *raw, int t, int hh) {
-    const uint4 hdr = *reinterpret_cast<const uint4 *>(raw);
-    uint4 q[4];
+// the row's mins operand of a superblock: 64 * m[0..7] | m[0..7] as fp16, canonical K-major tile (SBO 256, LBO 128)
+__device__ __forceinline__ void producer_mins(uint8_t *am_tile, int row, const uint4 sm) {
+    const __half2 bias = __half2half2(__ushort_as_half((unsigned short)0x6400)), k64 = __half2half2(__ushort_as_half((unsigned short)0x5400));
+    uint32_t m1[4], m64[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) q[i] = *reinterpret_cast<const uint4 *>(raw + 16 + 64 * hh + 16 * i);
-    const uint4 sm = unpack_scales_mins(hdr);
-    const uint32_t scw = hh ? sm.y : sm.x, mw = hh ? sm.w : sm.z;
-    uint8_t *row_base = a_stage + (t >> 3) * SBO_BYTES + (t & 7) * 16;
-#pragma unroll
-    for (int gi = 0; gi < 2; ++gi) {
-        const uint32_t qw[8] = {q[2 * gi].x, q[2 * gi].y, q[2 * gi].z, q[2 * gi].w,
-                                q[2 * gi + 1].x, q[2 * gi + 1].y, q[2 * gi + 1].z, q[2 * gi + 1].w};
-#pragma unroll
-        for (int nib = 0; nib < 2; ++nib) {             // 0: low nibbles = sub-block 2g, 1: high nibbles = sub-block 2g + 1
-            const uint32_t sc = (scw >> (16 * gi + 8 * nib)) & 0xffu, mn = (mw >> (16 * gi + 8 * nib)) & 0xffu;
-            const uint32_t sh = sc >> 3, sl = sc & 7u, mrep = mn * 0x01010101u;
-            uint32_t v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = (nib ? (qw[i] >> 4) : qw[i]) & 0x0f0f0f0fu;
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {               // two 16-element K chunks per sub-block
-                uint8_t *dst = row_base + (4 * gi + 2 * nib + c) * LBO_BYTES;
-                *reinterpret_cast<uint4 *>(dst) = make_uint4(v[4 * c] * sh, v[4 * c + 1] * sh, v[4 * c + 2] * sh, v[4 * c + 3] * sh);
-                *reinterpret_cast<uint4 *>(dst + TILE_BYTES) = make_uint4(v[4 * c] * sl, v[4 * c + 1] * sl, v[4 * c + 2] * sl, v[4 * c + 3] * sl);
-                *reinterpret_cast<uint4 *>(dst + 2 * TILE_BYTES) = make_uint4(mrep, mrep, mrep, mrep);
-            }
-        }
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t src = i < 2 ? sm.z : sm.w;
+        const uint32_t pair = __byte_perm(src, 0u, (i & 1) ? 0x4342u : 0x4140u) | 0x64006400u;        // {1024 + m[2i], 1024 + m[2i+1]}
+        const __half2 h = __hsub2(*reinterpret_cast<const __half2 *>(&pair), bias);                   // exact
+        const __half2 h64 = __hmul2(h, k64);                                                          // exact (<= 4032, 6 bits)
+        m1[i] = *reinterpret_cast<const uint32_t *>(&h);
+        m64[i] = *reinterpret_cast<const uint32_t *>(&h64);
     }
+    uint8_t *dst = am_tile + (row >> 3) * MIN_SBO_BYTES + (row & 7) * 16;
+    *reinterpret_cast<uint4 *>(dst) = make_uint4(m64[0], m64[1], m64[2], m64[3]);
+    *reinterpret_cast<uint4 *>(dst + LBO_BYTES) = make_uint4(m1[0], m1[1], m1[2], m1[3]);
 }
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_q4k_tc_kernel(const GemmParams p) {
+gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    float *dx_s = reinterpret_cast<float *>(smem + SMEM_DX);            // [half][buffer][64]
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BARS);
     uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 24);
     const uint32_t bar0 = smem_addr(bars);
     auto full_bar = [&](int s) { return bar0 + 8u * s; };                  // [B_SLOTS]  producers -> MMA, one per pipeline step slot
-    auto emptya_bar = [&](int s) { return bar0 + 8u * (4 + s); };          // [A_STAGES] MMA -> producers
-    auto emptyb_bar = [&](int s) { return bar0 + 8u * (6 + s); };          // [B_SLOTS]  MMA -> producers
-    auto tfull_bar = [&](int h) { return bar0 + 8u * (10 + h); };
-    auto tempty_bar = [&](int h) { return bar0 + 8u * (12 + h); };
+    auto done_bar = [&](int s) { return bar0 + 8u * (B_SLOTS + s); };      // [B_SLOTS]  MMA -> producers: the step's MMAs have completed
+    auto tfull_bar = [&](int h) { return bar0 + 8u * (2 * B_SLOTS + h); };
+    auto tempty_bar = [&](int h) { return bar0 + 8u * (2 * B_SLOTS + 2 + h); };
+    auto rawfull_bar = [&](int s) { return bar0 + 8u * (2 * B_SLOTS + 4 + s); };   // [RAW_SLOTS] loader -> producers
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
     const int nb = p.nb, nsteps = 2 * nb;
-    const int64_t K = (int64_t)nb * QK_K;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_WARPS * 32); mbar_init(emptyb_bar(s), 1); }
-        for (int s = 0; s < A_STAGES; ++s) mbar_init(emptya_bar(s), 1);
-        for (int h = 0; h < 2; ++h) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), (EPI_WARPS / 2) * 32); }
+        for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_THREADS + 1); mbar_init(done_bar(s), 1); }
+        for (int s = 0; s < RAW_SLOTS; ++s) mbar_init(rawfull_bar(s), 1);
+        for (int h = 0; h < 2; ++h) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), EPI_WARPS * 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == EPI_WARPS + PROD_WARPS) {
+    if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_ptr_s)), "n"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -232,131 +318,178 @@ gemm_q4k_tc_kernel(const GemmParams p) {
 
     if (warp < EPI_WARPS) {
         // ===================== epilogue: TMEM -> registers, per-superblock fp32 scales =====================
-        const int qd = warp & 3, grp = warp >> 2, h = grp >> 1;               // lane quadrant, column group (32 wide), accumulator half
-        const int th = threadIdx.x & 255;                                      // thread within the half (two groups)
+        const int qd = warp & 3, g = warp >> 2;                               // lane quadrant, column group (16 wide, both halves)
         const int64_t row = m0 + 32 * qd + lane;
         const uint8_t *wrow = p.w + (row < p.M ? row : p.M - 1) * p.w_stride;
-        float *dx = dx_s + h * 128;
-        int64_t ncl = n0 + HALF_N * h + (th & 63);
+        float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 64;   // [buffer][half 0: 16 | half 1: 16], private to the warp
+        int64_t ncl = n0 + HALF_N * (lane >> 4) + EPI_COLS * g + (lane & 15); // the column whose d_x this lane fetches
         if (ncl >= p.N) ncl = p.N - 1;
-        float acc[EPI_COLS];
+        uint64_t acc[2][EPI_COLS / 2];                                        // fp32 pairs
 #pragma unroll
-        for (int i = 0; i < EPI_COLS; ++i) acc[i] = 0.0f;
+        for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
         uint32_t dd_next = *reinterpret_cast<const uint32_t *>(wrow);
-        if (th < 64) dx[th] = p.xd[ncl];                                       // superblock 0 -> buffer 0
-        const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * grp);
-        const int cofs = EPI_COLS * (grp & 1);                                 // this group's columns inside the half
+        dxw[lane] = p.xd[ncl];                                                // superblock 0 -> buffer 0
+        __syncwarp();
+        const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g);
         for (int kb = 0; kb < nb; ++kb) {
             const uint32_t dd = dd_next;
-            if (kb + 1 < nb) dd_next = *reinterpret_cast<const uint32_t *>(wrow + (int64_t)(kb + 1) * BLK_Q4K);
-            mbar_wait(tfull_bar(h), (uint32_t)(kb & 1));
-            tc_fence_after();
-            asm volatile("bar.sync %0, 256;" ::"r"(1 + h) : "memory");        // everyone of this half is done with superblock kb - 1
-            if (th < 64 && kb + 1 < nb) dx[((kb + 1) & 1) * 64 + th] = p.xd[(int64_t)(kb + 1) * p.Nld + ncl];
-            const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));   // {d, dmin} of this row's superblock
-            const float *dxk = dx + (kb & 1) * 64 + cofs;
-            uint32_t vh[2][8], vl[2][8], vm[2][8];
-            tmem_ld8(tbase, vh[0]); tmem_ld8(tbase + 128, vl[0]); tmem_ld8(tbase + 256, vm[0]);
-#pragma unroll
-            for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
-                const int cur = c8 & 1;
-                tmem_ld_wait();
-                if (c8 + 1 < EPI_COLS / 8) {                                   // next 8 columns in flight while these are scaled
-                    tmem_ld8(tbase + 8 * (c8 + 1), vh[cur ^ 1]);
-                    tmem_ld8(tbase + 128 + 8 * (c8 + 1), vl[cur ^ 1]);
-                    tmem_ld8(tbase + 256 + 8 * (c8 + 1), vm[cur ^ 1]);
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int sumi = ((int)vh[cur][i] << 3) + (int)vl[cur][i];
-                    float t = __fmul_rn(dw.x, (float)sumi);
-                    t = __fmaf_rn(-dw.y, (float)(int)vm[cur][i], t);
-                    acc[8 * c8 + i] = __fmaf_rn(dxk[8 * c8 + i], t, acc[8 * c8 + i]);
-                }
+            float dx_next = 0.0f;
+            if (kb + 1 < nb) {
+                dd_next = *reinterpret_cast<const uint32_t *>(wrow + (int64_t)(kb + 1) * BLK_Q4K);
+                dx_next = p.xd[(int64_t)(kb + 1) * p.Nld + ncl];
             }
-            tc_fence_before();
-            mbar_arrive(tempty_bar(h));
+            const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));   // {d, dmin} of this row's superblock
+            const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                mbar_wait_long<Q4K_GEMM_WAIT>(tfull_bar(h), (uint32_t)(kb & 1));
+                if (lane == 0 && g == 0 && qd == 0) TR(8 + 2 * h, kb);
+                tc_fence_after();
+                const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + (kb & 1) * 32 + 16 * h);
+#pragma unroll
+                for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
+                    uint32_t vh[8], vl[8], vm[8];
+                    const uint32_t ta = tbase + HALF_N * h + 8 * c8;
+                    tmem_ld8(ta + TM_HI, vh); tmem_ld8(ta + TM_LO, vl); tmem_ld8(ta + TM_MIN, vm);
+                    tmem_ld_wait();
+                    if (c8 == EPI_COLS / 8 - 1) {          // everything of this half is in registers: hand the columns back
+                        tc_fence_before();
+                        if (lane == 0 && g == 0 && qd == 0) TR(9 + 2 * h, kb);
+                        mbar_arrive(tempty_bar(h));
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
+                        const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
+                        uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
+                        t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
+                        acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
+                    }
+                }
+                if (lane == 0 && g == 0 && qd == 0) TR(12 + 2 * h, kb);
+            }
+            dxw[((kb + 1) & 1) * 32 + lane] = dx_next;                        // last read during superblock kb - 1
+            __syncwarp();
         }
         if (row < p.M) {
 #pragma unroll
-            for (int c = 0; c < EPI_COLS; ++c) {
-                const int64_t n = n0 + EPI_COLS * grp + c;
-                if (n < p.N) p.dst[n * p.dst_stride + row] = acc[c];
+            for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                for (int c = 0; c < EPI_COLS / 2; ++c) {
+                    const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 2 * c;
+                    float a0, a1;
+                    unpack2(acc[h][c], a0, a1);
+                    if (n < p.N) p.dst[n * p.dst_stride + row] = a0;
+                    if (n + 1 < p.N) p.dst[(n + 1) * p.dst_stride + row] = a1;
+                }
             }
         }
     } else if (warp < EPI_WARPS + PROD_WARPS) {
-        // ===================== producers: Q4_K bytes -> three int8 A tiles; planar int8 activations -> B tile =====================
-        const int t = threadIdx.x - EPI_WARPS * 32;
-        const uint32_t smem0 = smem_addr(smem);
-        const int64_t ntile = blockIdx.x;
-#pragma unroll
-        for (int i = 0; i < PREFETCH; ++i) {             // fresh slots: nothing to wait for
-            if (i < nsteps) producer_issue(p, smem0, t, m0, ntile, i);
-            cp_async_commit();
-        }
+        // ===================== producers: Q4_K bytes -> A_hi / A_lo in TMEM; activations -> B slot =====================
+        const int t = threadIdx.x - EPI_WARPS * 32, pw = t >> 5;
+        const int qd = pw & 3, khalf = pw >> 2, r = 32 * qd + lane;           // TMEM lane = weight row of the tile; which 64 of the 128 K
+        const uint32_t ta_base = tmem + ((uint32_t)(32 * qd) << 16) + TM_A + 16u * khalf;
+        uint4 sm = make_uint4(0, 0, 0, 0);
         for (int step = 0; step < nsteps; ++step) {
-            cp_async_wait<PREFETCH - 1>();               // this thread's copies for `step` have landed ...
-            if ((step & 1) == 0) asm volatile("bar.sync 3, 128;" ::: "memory");   // ... and everybody else's: the raw rows are shared
-            const int a = step % A_STAGES;
-            mbar_wait(emptya_bar(a), (uint32_t)(((step / A_STAGES) & 1) ^ 1));
-            producer_unpack(smem + SMEM_A + a * A_STAGE_BYTES, smem + SMEM_RAW + ((step >> 1) % RAW_SLOTS) * RAW_SLOT_BYTES + t * RAW_ROW_BYTES,
-                            t, step & 1);
-            fence_async_smem();                          // generic-proxy writes (st.shared, cp.async) -> tensor core's async proxy
-            mbar_arrive(full_bar(step % B_SLOTS));
-            const int ahead = step + PREFETCH;
-            if (ahead < nsteps) {
-                // the B slot of step `ahead` was last read by the MMAs of step ahead - B_SLOTS
-                mbar_wait(emptyb_bar(ahead % B_SLOTS), (uint32_t)(((ahead / B_SLOTS) & 1) ^ 1));
-                producer_issue(p, smem0, t, m0, ntile, ahead);
-            }
-            cp_async_commit();
-        }
-    } else if (lane == 0) {
-        // ===================== MMA issuer (one thread) =====================
-        const uint32_t idesc = umma_idesc_i8();
-        const uint32_t stage0 = smem_addr(smem);
-        for (int step = 0; step < nsteps; ++step) {
-            const int kb = step >> 1, hh = step & 1, a = step % A_STAGES, bslot = step % B_SLOTS;
-            mbar_wait(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));
+            const int kb = step >> 1, hh = step & 1;
+            if (hh == 0) mbar_wait_long<Q4K_GEMM_WAIT>(rawfull_bar(kb % RAW_SLOTS), (uint32_t)((kb / RAW_SLOTS) & 1));
+            if (t == 0) TR(0, step);
+            const uint8_t *raw = smem + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES + r * RAW_ROW_BYTES;
+            if (hh == 0) sm = unpack_scales_mins(*reinterpret_cast<const uint4 *>(raw));
+            uint32_t hi[16], lo[16];
+            producer_unpack(hi, lo, raw, sm, 2 * hh + khalf);
+            // A stage step % 2 was last read by the MMAs of step - 2
+            if (step >= 2) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar((step - 2) % B_SLOTS), (uint32_t)(((step - 2) / B_SLOTS) & 1));
+            if (t == 0) TR(1, step);
             tc_fence_after();
-            const uint32_t sa = stage0 + SMEM_A + (uint32_t)a * A_STAGE_BYTES, sb = stage0 + SMEM_B + (uint32_t)bslot * TILE_BYTES;
+            const uint32_t ta = ta_base + (uint32_t)(step & 1) * TM_A_STAGE;
+            tmem_st16(ta, hi);
+            tmem_st16(ta + TM_A_TILE, lo);
+            if (hh == 0 && khalf == 0) {
+                producer_mins(smem + SMEM_AM + (kb % AM_SLOTS) * MIN_TILE_BYTES, r, sm);
+                fence_async_smem();                      // generic-proxy st.shared -> the tensor core's async proxy
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(full_bar(step % B_SLOTS));
+            if (t == 0) TR(2, step);
+        }
+    } else if (warp == MMA_WARP) {
+        // ===================== MMA issuer: the whole warp runs the loop (uniform control flow keeps the descriptors in
+        // uniform registers), one elected lane issues =====================
+        const uint32_t idesc = umma_idesc(false), idesc_min = umma_idesc(true);
+        const uint32_t smem0 = smem_addr(smem);
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+        const uint64_t desc_hi = umma_desc(0, SBO_BYTES), desc_min_hi = umma_desc(0, MIN_SBO_BYTES);
+        // Per superblock: all 16 MMAs of column half 0 (both K steps), then all 16 of half 1.  A half's TMEM columns are
+        // drained by the epilogue while the tensor core works on the other half (a window of half a superblock).
+        for (int kb = 0; kb < nb; ++kb) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                if (hh == 0) {                     // new superblock: the previous one must have left this half of TMEM
-                    mbar_wait(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
-                    tc_fence_after();
-                }
 #pragma unroll
-                for (int o = 0; o < 3; ++o) {
-#pragma unroll
-                    for (int j = 0; j < BK / 32; ++j) {
-                        const uint64_t a_desc = umma_desc(sa + o * TILE_BYTES + j * 2 * LBO_BYTES);
-                        const uint64_t b_desc = umma_desc(sb + h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES);
-                        umma_i8(tmem + o * 128 + h * HALF_N, a_desc, b_desc, idesc, (uint32_t)((hh | j) != 0));
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int step = 2 * kb + hh, bslot = step % B_SLOTS;
+                    if (h == 0) {                  // the step's operands: A stage in TMEM, B slot in shared memory
+                        if (lane == 0) TR(4, step);
+                        mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));
+                        if (lane == 0) TR(5, step);
                     }
+                    if (hh == 0) {                 // new superblock: the previous one must have left this half of TMEM
+                        mbar_wait_long<Q4K_GEMM_WAIT>(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
+                        if (lane == 0) TR(6 + h, step);
+                    }
+                    tc_fence_after();
+                    const uint32_t ta = tm + TM_A + (uint32_t)(step & 1) * TM_A_STAGE;
+                    const uint64_t bd0 = desc_hi + (uint64_t)((smem0 + SMEM_B + (uint32_t)bslot * TILE_BYTES) >> 4);
+                    if (elect_one()) {
+#pragma unroll
+                        for (int o = 0; o < 2; ++o) {
+#pragma unroll
+                            for (int j = 0; j < BK / 32; ++j) {
+                                const uint64_t b_desc = bd0 + (uint64_t)((h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES) >> 4);
+                                umma_i8_ts(tm + (o ? TM_LO : TM_HI) + h * HALF_N, ta + o * TM_A_TILE + 8 * j, b_desc, idesc, (uint32_t)((hh | j) != 0));
+                            }
+                        }
+                        if (hh == 1) {             // the superblock's mins (K = 16, fp16), then this half is complete -> epilogue
+                            const uint64_t a_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_AM + (kb % AM_SLOTS) * MIN_TILE_BYTES) >> 4);
+                            const uint64_t b_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES + h * (HALF_N / 8) * MIN_SBO_BYTES) >> 4);
+                            umma_f16_ss(tm + TM_MIN + h * HALF_N, a_desc, b_desc, idesc_min, 0u);
+                            umma_commit(tfull_bar(h));
+                        }
+                        if (h == 1) umma_commit(done_bar(bslot));   // A stage and B slot consumed by both halves -> producers
+                    }
+                    __syncwarp();
                 }
-                if (hh == 1) umma_commit(tfull_bar(h));     // superblock complete in this half -> its epilogue group
             }
-            umma_commit(emptya_bar(a));                     // A stage and B slot consumed -> producers
-            umma_commit(emptyb_bar(bslot));
+        }
+    } else if (lane == 0) {
+        // ===================== loader (one thread): TMA copies, up to B_SLOTS steps ahead of the tensor core =====================
+        const uint32_t smem0 = smem_addr(smem);
+        for (int step = 0; step < nsteps; ++step) {
+            // slot reuse: the MMAs of step - B_SLOTS have completed, so its B slot is free; every producer had arrived for that
+            // step, so the raw slot of superblock step / 2 - RAW_SLOTS has been read; the mins slots likewise
+            if (step >= B_SLOTS) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar(step % B_SLOTS), (uint32_t)(((step - B_SLOTS) / B_SLOTS) & 1));
+            loader_issue(p, smem0, full_bar(step % B_SLOTS), rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, (int64_t)blockIdx.x, step);
         }
     }
 
     tc_fence_before();
     __syncthreads();
-    if (warp == EPI_WARPS + PROD_WARPS) {
+    if (warp == MMA_WARP) {
         __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
     }
 }
 
-// F32 rows -> int8 activations in the GEMM's own tiled order + float d[nb][Nld]; the arithmetic of quantize_row_q8_K
-// (shared device function, bit-exact), one warp per 256-block.  Element k of column n, superblock b lands in
+// F32 rows -> int8 activations in the GEMM's own tiled order + float d[nb][Nld] + the fp16 mins tile; the arithmetic
+// of quantize_row_q8_K (shared device function, bit-exact), one warp per 256-block.  Element k of column n,
+// superblock b lands in
 //   tile (n / 128, b), half k / 128, then the canonical K-major core-matrix order of the shared-memory B tile:
 //   ((n % 128) / 8) * 1024 + ((k % 128) / 16) * 128 + (n % 8) * 16 + k % 16
+// and the sums bs[j] of its eight 32-element sub-blocks, split bs = 64 * bh + bl (bl = bs & 63), land as fp16 in
+//   mins tile (n / 128, b):  ((n % 128) / 8) * 256 + {bh: 0, bl: 128} + (n % 8) * 16 + 2 * j
 __global__ void __launch_bounds__(256)
-quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, float *__restrict__ d, int64_t nb_per_row,
-                          int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld) {
+quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, float *__restrict__ d, uint8_t *__restrict__ bmin,
+                          int64_t nb_per_row, int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld) {
     const int lane = threadIdx.x & 31;
     const int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (blk >= nblocks_total) return;
@@ -367,7 +500,7 @@ quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, 
     const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
     uint32_t w_lo, w_hi;
     int s_lo, s_hi;
-    const float dq = quantize_block_q8_K(v, lane, w_lo, w_hi, s_lo, s_hi);
+    const float dq = quantize_block_q8_K<8>(v, lane, w_lo, w_hi, s_lo, s_hi);     // 8-lane sums = the 32-element sub-block sums
     const int64_t ntile = row >> 7, nl = row & 127;
     int8_t *tile = qs + ((ntile * nb_per_row + b) << 15) + (nl >> 3) * 1024 + (nl & 7) * 16;
     // lane l holds elements 4l..4l+3 (half 0) and 128+4l..128+4l+3 (half 1): chunk l / 4, bytes 4 * (l % 4)
@@ -375,6 +508,12 @@ quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, 
     *reinterpret_cast<uint32_t *>(tile + off) = w_lo;
     *reinterpret_cast<uint32_t *>(tile + 16384 + off) = w_hi;
     if (lane == 0) d[b * Nld + row] = dq;
+    if ((lane & 7) == 0) {                                  // sub-blocks lane / 8 (half 0) and 4 + lane / 8 (half 1)
+        __half *mt = reinterpret_cast<__half *>(bmin + ((ntile * nb_per_row + b) << 12) + (nl >> 3) * MIN_SBO_BYTES + (nl & 7) * 16);
+        const int j = lane >> 3;
+        mt[j] = __int2half_rn(s_lo >> 6);        mt[64 + j] = __int2half_rn(s_lo & 63);
+        mt[4 + j] = __int2half_rn(s_hi >> 6);    mt[64 + 4 + j] = __int2half_rn(s_hi & 63);
+    }
 }
 
 }  // namespace
@@ -386,25 +525,56 @@ cudaError_t launch_gemm_q4k_q8k(const void *, int64_t, int64_t, int64_t, const v
     return cudaErrorNotSupported;
 }
 
-// F32 activations: quantize into `workspace` (roundup(N,128)*K + nb*N*4 bytes <= q4k_mul_mat_workspace_bytes), then the
-// tensor-core GEMM.  Two launches.
+// workspace layout of the prefill path: int8 tiles | mins tiles | float d   (q4k_mul_mat_workspace_bytes adds them up)
+size_t gemm_workspace_bytes(int64_t K, int64_t N) {
+    const size_t nb = (size_t)(K / QK_K), ntiles = ((size_t)N + BN - 1) / BN;
+    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + nb * (size_t)N * 4;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+static cudaError_t make_weight_map(CUtensorMap *map, const void *w, int64_t M, int64_t nb, int64_t w_row_stride_bytes) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess) return e;
+        if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+        encode = (encode_fn)fn;
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)(nb * BLK_Q4K), (cuuint64_t)M};
+    const cuuint64_t strides[1] = {(cuuint64_t)w_row_stride_bytes};
+    const cuuint32_t box[2] = {(cuuint32_t)BLK_Q4K, (cuuint32_t)BM}, estr[2] = {1, 1};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(w), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+// F32 activations: quantize into `workspace` (gemm_workspace_bytes), then the tensor-core GEMM.  Two launches.
 cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream) {
     if (M == 0 || N == 0) return cudaSuccess;
     const int64_t nb = K / QK_K;
-    const int64_t Npad = (N + BN - 1) / BN * BN;          // whole column tiles; columns >= N hold stale bytes, never stored
+    const int64_t ntiles = (N + BN - 1) / BN;             // whole column tiles; columns >= N hold stale bytes, never stored
     int8_t *qs = reinterpret_cast<int8_t *>(workspace);
-    float *d = reinterpret_cast<float *>(qs + Npad * K);
+    uint8_t *bmin = reinterpret_cast<uint8_t *>(qs + ntiles * BN * K);
+    float *d = reinterpret_cast<float *>(bmin + ntiles * nb * MIN_TILE_BYTES);
     const int64_t total = nb * N;
-    quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, nb, total, x_row_stride_bytes, N);
+    quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, bmin, nb, total, x_row_stride_bytes, N);
     count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
 
     GemmParams p;
+    e = make_weight_map(&p.wmap, w, M, nb, w_row_stride_bytes);
+    if (e != cudaSuccess) return e;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
-    p.xq = qs; p.xd = d; p.N = N; p.Nld = N;
+    p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
     p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
     constexpr size_t smem = SMEM_TOTAL;
     static bool attr_set = false;
@@ -420,3 +590,9 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
 }
 
 }  // namespace q4k
+
+#ifdef Q4K_GEMM_TRACE
+extern "C" int q4k_debug_gemm_trace(long long *host) {
+    return (int)cudaMemcpyFromSymbol(host, q4k::g_gemm_trace, sizeof(long long) * 16 * 256);
+}
+#endif

@@ -43,7 +43,8 @@ cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                 const void *xq, int64_t N, int64_t xq_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, cudaStream_t stream);
 
-// F32 activations, N > 8: planar Q8 quantizer + tcgen05 GEMM; `workspace` >= q4k_mul_mat_workspace_bytes(K, N)
+// F32 activations, N > 8: planar Q8 quantizer + tcgen05 GEMM; `workspace` >= gemm_workspace_bytes(K, N)
+size_t gemm_workspace_bytes(int64_t K, int64_t N);
 cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream);

@@ -9,4 +9,5 @@ $NV -o $D/quant_lat $D/quant_lat.cu
 $NV -o $D/pdl_floor $D/pdl_floor.cu
 $NV -o $D/imma_rate $D/imma_rate.cu
 $NV -o $D/stream_bulk $D/stream_bulk.cu
+$NV -o $D/umma_rate $D/umma_rate.cu
 ls -la $D | grep -v "\.cu$\|\.sh$"
