@@ -17,6 +17,7 @@ LIB = os.path.join(HERE, "_build", "libq4k_oracle.so")
 QK_K = 256
 Q4K_BLOCK = 144
 Q8K_BLOCK = 292
+Q6K_BLOCK = 210
 ORDER_GENERIC, ORDER_AVX2, ORDER_NEON = 0, 1, 2
 
 _lib = None
@@ -24,7 +25,7 @@ _lib = None
 
 def build() -> str:
     """Compile the restatement with gcc (seconds).  Building the checker is not using it."""
-    src = [os.path.join(HERE, f) for f in ("q4k_oracle.c", "q4k_oracle.h")]
+    src = [os.path.join(HERE, f) for f in ("q4k_oracle.c", "q6k_oracle.c", "q4k_oracle.h")]
     if os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(s) for s in src):
         return LIB
     subprocess.check_call(["make", "-C", HERE, "oracle"], stdout=subprocess.DEVNULL)
@@ -56,6 +57,17 @@ def lib():
         L.ora_vec_dot_q4_K_q8_K_f64.restype = C.c_double
         L.ora_mul_mat_q4_K_f32.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, i32]
         L.ora_mul_mat_q4_K_f32.restype = i32
+        L.ora_quantize_row_q6_K.argtypes = [vp, vp, i64]
+        L.ora_dequantize_row_q6_K.argtypes = [vp, vp, i64]
+        L.ora_vec_dot_q6_partials.argtypes = [i32, vp, vp, vp, vp]
+        for name in ("generic", "avx2order"):
+            fn = getattr(L, f"ora_vec_dot_q6_K_q8_K_{name}")
+            fn.argtypes = [i32, f32p, C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, i32]
+            fn.restype = None
+        L.ora_vec_dot_q6_K_q8_K_f64.argtypes = [i32, vp, vp]
+        L.ora_vec_dot_q6_K_q8_K_f64.restype = C.c_double
+        L.ora_mul_mat_q6_K_f32.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, i32]
+        L.ora_mul_mat_q6_K_f32.restype = i32
         _lib = L
     return _lib
 
@@ -173,3 +185,83 @@ def mul_mat_f64(w: np.ndarray, x: np.ndarray) -> np.ndarray:
         for m in range(w.shape[0]):
             out[n, m] = vec_dot_f64(w[m], yq[n])
     return out
+
+
+# ---------------------------------------------------------------------------------------- Q6_K (q6k_oracle.c)
+def quantize_q6_K(x: np.ndarray) -> np.ndarray:
+    """x: float32 [M, K] -> uint8 [M, K/256*210] (quantize_row_q6_K_ref, L/ggml/src/ggml-quants.c:1692-1760)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    K = x.shape[-1]
+    assert K % QK_K == 0
+    rows = x.reshape(-1, K)
+    out = np.zeros((rows.shape[0], K // QK_K * Q6K_BLOCK), np.uint8)
+    for r in range(rows.shape[0]):
+        lib().ora_quantize_row_q6_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*x.shape[:-1], -1)
+
+
+def dequantize_q6_K(w: np.ndarray) -> np.ndarray:
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    rows = w.reshape(-1, w.shape[-1])
+    K = rows.shape[1] // Q6K_BLOCK * QK_K
+    out = np.empty((rows.shape[0], K), np.float32)
+    for r in range(rows.shape[0]):
+        lib().ora_dequantize_row_q6_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*w.shape[:-1], K)
+
+
+def vec_dot_q6_partials(wrow: np.ndarray, yrow: np.ndarray):
+    """-> (p[nb,16], sumi[nb]) int32: the exact integer stage of ggml_vec_dot_q6_K_q8_K."""
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q6K_BLOCK
+    assert yrow.size == nb * Q8K_BLOCK
+    p = np.zeros((nb, 16), np.int32)
+    si = np.zeros(nb, np.int32)
+    lib().ora_vec_dot_q6_partials(nb * QK_K, _p(wrow), _p(yrow), _p(p), _p(si))
+    return p, si
+
+
+def vec_dot_q6(wrow: np.ndarray, yrow: np.ndarray, order: int = ORDER_AVX2) -> np.float32:
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q6K_BLOCK
+    s = C.c_float(0)
+    name = "avx2order" if order == ORDER_AVX2 else "generic"
+    getattr(lib(), f"ora_vec_dot_q6_K_q8_K_{name}")(nb * QK_K, C.byref(s), 0, _p(wrow), 0, _p(yrow), 0, 1)
+    return np.float32(s.value)
+
+
+def mul_mat_q6(w: np.ndarray, x: np.ndarray, order: int = ORDER_AVX2) -> np.ndarray:
+    """w: uint8 [M, K/256*210]; x: float32 [N, K] -> float32 [N, M]."""
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    M = w.shape[0]
+    N, K = x.shape
+    assert w.shape[1] == K // QK_K * Q6K_BLOCK
+    dst = np.zeros((N, M), np.float32)
+    wdata = np.zeros(N * (K // QK_K) * Q8K_BLOCK, np.uint8)
+    rc = lib().ora_mul_mat_q6_K_f32(_p(w), M, K, w.shape[1], _p(x), N, K * 4, _p(dst), M * 4, _p(wdata), order)
+    if rc != 0:
+        raise ValueError(f"ora_mul_mat_q6_K_f32 rc={rc}")
+    return dst
+
+
+def mul_mat_q6_f64(w: np.ndarray, x: np.ndarray) -> np.ndarray:
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    yq = quantize_q8_K(x)
+    nb = w.shape[1] // Q6K_BLOCK
+    out = np.zeros((yq.shape[0], w.shape[0]), np.float64)
+    for n in range(yq.shape[0]):
+        for m in range(w.shape[0]):
+            out[n, m] = lib().ora_vec_dot_q6_K_q8_K_f64(nb * QK_K, _p(w[m]), _p(yq[n]))
+    return out
+
+
+def random_q6_K(rng, M: int, K: int) -> np.ndarray:
+    """Random VALID block_q6_K bytes (any ql / qh / scales bytes are valid; d is a finite fp16)."""
+    nb = K // QK_K
+    w = rng.integers(0, 256, (M, nb, Q6K_BLOCK), dtype=np.uint8)
+    d = (rng.uniform(0.0005, 0.01, (M, nb)) * rng.choice([-1.0, 1.0], (M, nb))).astype(np.float16)
+    w[:, :, 208:210] = d.view(np.uint8).reshape(M, nb, 2)
+    return w.reshape(M, nb * Q6K_BLOCK)

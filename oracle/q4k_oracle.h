@@ -38,6 +38,14 @@ typedef struct {
     int16_t bsums[ORA_QK_K / 16];
 } ora_block_q8_K;
 
+/* L/ggml/src/ggml-common.h:326-336 — 210 bytes */
+typedef struct {
+    uint8_t  ql[ORA_QK_K / 2];          /* low 4 bits of the 6-bit levels  */
+    uint8_t  qh[ORA_QK_K / 4];          /* high 2 bits                     */
+    int8_t   scales[ORA_QK_K / 16];     /* 16 signed 8-bit sub-block scales */
+    uint16_t d;                         /* fp16 super-block scale          */
+} ora_block_q6_K;
+
 /* float accumulation orders of the reference's variants */
 enum ora_float_order {
     ORA_ORDER_GENERIC = 0,   /* L/ggml/src/ggml-cpu/quants.c:550-623            */
@@ -70,6 +78,18 @@ int ora_mul_mat_q4_K_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stri
                          const float *x, int64_t N, int64_t x_row_stride_bytes,
                          float *dst, int64_t dst_col_stride_bytes,
                          void *wdata /* N * K/256 * 292 bytes */, int order);
+
+/* ---- Q6_K x Q8_K (q6k_oracle.c) ---- */
+void ora_quantize_row_q6_K(const float *x, void *y, int64_t k);       /* L/ggml/src/ggml-quants.c:1692-1760 */
+void ora_dequantize_row_q6_K(const void *x, float *y, int64_t k);     /* L/ggml/src/ggml-quants.c:1762-1791 */
+/* integer stage: p[nb*16] per-16 sub-block dot products (levels offset by -32), sumi[nb] = sum_j scales[j]*p[j] */
+void ora_vec_dot_q6_partials(int n, const void *vx, const void *vy, int32_t *p, int32_t *sumi);
+void ora_vec_dot_q6_K_q8_K_generic(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+void ora_vec_dot_q6_K_q8_K_avx2order(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+double ora_vec_dot_q6_K_q8_K_f64(int n, const void *vx, const void *vy);
+int ora_mul_mat_q6_K_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride,
+                         const float *x, int64_t N, int64_t x_row_stride_bytes,
+                         float *dst, int64_t dst_col_stride_bytes, void *wdata, int order);
 
 #ifdef __cplusplus
 }

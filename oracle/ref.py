@@ -51,6 +51,11 @@ def libs():
         for fn in (cpu.ggml_vec_dot_q4_K_q8_K, cpu.ggml_vec_dot_q4_K_q8_K_generic):
             fn.argtypes = [i32, C.POINTER(C.c_float), C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, i32]
             fn.restype = None
+        base.quantize_row_q6_K_ref.argtypes = [vp, vp, i64]
+        base.dequantize_row_q6_K.argtypes = [vp, vp, i64]
+        for fn in (cpu.ggml_vec_dot_q6_K_q8_K, cpu.ggml_vec_dot_q6_K_q8_K_generic):
+            fn.argtypes = [i32, C.POINTER(C.c_float), C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, i32]
+            fn.restype = None
         shim.ref_mul_mat_q4k.argtypes = [vp, i64, i64, vp, i64, vp, i32, i32, i32, C.POINTER(C.c_double)]
         shim.ref_mul_mat_q4k.restype = i32
         shim.ref_plugin_mul_mat_q4k.argtypes = [C.c_char_p, vp, i64, i64, vp, i64, vp, i32, C.POINTER(C.c_double)]
@@ -198,6 +203,44 @@ def mul_mat_set(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, iters: 
     if rc != 0:
         raise RuntimeError(f"ref_mul_mat_set_q4k rc={rc}")
     return secs[0], secs[1], chk.value
+
+
+Q6K_BLOCK = 210
+
+
+def quantize_q6_K(x: np.ndarray) -> np.ndarray:
+    """quantize_row_q6_K_ref per row (L/ggml/src/ggml-quants.c:1692-1760)."""
+    base = libs()[0]
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    K = x.shape[-1]
+    rows = x.reshape(-1, K)
+    out = np.zeros((rows.shape[0], K // QK_K * Q6K_BLOCK), np.uint8)
+    for r in range(rows.shape[0]):
+        base.quantize_row_q6_K_ref(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*x.shape[:-1], -1)
+
+
+def dequantize_q6_K(w: np.ndarray) -> np.ndarray:
+    base = libs()[0]
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    rows = w.reshape(-1, w.shape[-1])
+    K = rows.shape[1] // Q6K_BLOCK * QK_K
+    out = np.empty((rows.shape[0], K), np.float32)
+    for r in range(rows.shape[0]):
+        base.dequantize_row_q6_K(_p(rows[r]), _p(out[r]), K)
+    return out.reshape(*w.shape[:-1], K)
+
+
+def vec_dot_q6(wrow: np.ndarray, yrow: np.ndarray, generic: bool = False) -> np.float32:
+    """ggml_vec_dot_q6_K_q8_K — the __AVX2__ branch in this build (arch/x86/quants.c:2145-2218)."""
+    cpu = libs()[1]
+    wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
+    yrow = np.ascontiguousarray(yrow, dtype=np.uint8)
+    nb = wrow.size // Q6K_BLOCK
+    s = C.c_float(0)
+    fn = cpu.ggml_vec_dot_q6_K_q8_K_generic if generic else cpu.ggml_vec_dot_q6_K_q8_K
+    fn(nb * QK_K, C.byref(s), 0, _p(wrow), 0, _p(yrow), 0, 1)
+    return np.float32(s.value)
 
 
 def has_avx2() -> bool:

@@ -38,3 +38,12 @@ np.savez_compressed(os.path.join(os.path.dirname(__file__), "q4k_ref_vectors.npz
                     w=w, x=x, wq=wq, xq=xq, y_avx2=y_avx2, y_generic=y_generic, w_deq=ref.dequantize_q4_K(wq),
                     note=np.array("llama.cpp a3cb0474, ggml-base no -m flags, ggml-cpu -mavx2 -mfma -mf16c -mbmi2, gcc 13.3"))
 print("wrote", wq.shape, xq.shape, y_avx2.shape)
+
+# ---- Q6_K: same inputs through quantize_row_q6_K_ref / ggml_vec_dot_q6_K_q8_K
+w6 = ref.quantize_q6_K(w)
+y6_avx2 = np.array([[ref.vec_dot_q6(w6[m], xq[n]) for m in range(M)] for n in range(x.shape[0])], np.float32)
+y6_generic = np.array([[ref.vec_dot_q6(w6[m], xq[n], generic=True) for m in range(M)] for n in range(x.shape[0])], np.float32)
+np.savez_compressed(os.path.join(os.path.dirname(__file__), "q6k_ref_vectors.npz"),
+                    w=w, x=x, wq=w6, xq=xq, y_avx2=y6_avx2, y_generic=y6_generic, w_deq=ref.dequantize_q6_K(w6),
+                    note=np.array("llama.cpp a3cb0474, ggml-base no -m flags, ggml-cpu -mavx2 -mfma -mf16c -mbmi2, gcc 13.3"))
+print("wrote q6", w6.shape, y6_avx2.shape)
