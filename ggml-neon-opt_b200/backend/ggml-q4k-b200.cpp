@@ -2,7 +2,9 @@
 //
 // Claims exactly one operation: GGML_OP_MUL_MAT with GGML_TYPE_Q4_K src0, F32 src1, F32 dst — the path
 // ggml_compute_forward_mul_mat -> quantize_row_q8_K -> ggml_vec_dot_q4_K_q8_K of the CPU backend
-// (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401).  Everything else stays on whichever backend the scheduler picks.
+// (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401) — and, since Q4_K_M model files keep some matrices in it (SURVEY.md §8f
+// rank 1), the same operation with GGML_TYPE_Q6_K src0 (ggml_vec_dot_q6_K_q8_K).  Everything else stays on whichever
+// backend the scheduler picks.
 // There is no fallback to ggml-cpu or ggml-cuda in here: a node this backend accepted either runs on the
 // sm_100a kernels behind include/q4k_b200.h or graph_compute returns GGML_STATUS_FAILED.
 //
@@ -197,11 +199,18 @@ bool mul_mat_supported(const ggml_tensor * op) {
     const ggml_tensor * src0 = op->src[0];
     const ggml_tensor * src1 = op->src[1];
     if (!src0 || !src1) return false;
-    if (src0->type != GGML_TYPE_Q4_K || src1->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    const bool q6 = src0->type == GGML_TYPE_Q6_K;
+    if ((src0->type != GGML_TYPE_Q4_K && !q6) || src1->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
     if (src0->ne[0] % Q4K_QK_K != 0 || src0->ne[0] != src1->ne[0]) return false;
-    // weights: whole block_q4_K rows, 16-byte aligned strides (144 = 9 x 16, so any stride made of rows is)
-    if (src0->nb[0] != Q4K_BLOCK_Q4K || src0->nb[1] < (size_t) (src0->ne[0] / Q4K_QK_K) * Q4K_BLOCK_Q4K) return false;
-    if ((src0->nb[1] | src0->nb[2] | src0->nb[3]) & 15) return false;
+    if (q6) {
+        // weights: whole block_q6_K rows; 210-byte blocks are 2-byte aligned by nature, the kernel takes any even stride
+        if (src0->nb[0] != Q4K_BLOCK_Q6K || src0->nb[1] < (size_t) (src0->ne[0] / Q4K_QK_K) * Q4K_BLOCK_Q6K) return false;
+        if ((src0->nb[1] | src0->nb[2] | src0->nb[3]) & 1) return false;
+    } else {
+        // weights: whole block_q4_K rows, 16-byte aligned strides (144 = 9 x 16, so any stride made of rows is)
+        if (src0->nb[0] != Q4K_BLOCK_Q4K || src0->nb[1] < (size_t) (src0->ne[0] / Q4K_QK_K) * Q4K_BLOCK_Q4K) return false;
+        if ((src0->nb[1] | src0->nb[2] | src0->nb[3]) & 15) return false;
+    }
     // activations: unit inner stride, 16-byte aligned row / batch strides (permuted src1 is declined)
     if (src1->nb[0] != sizeof(float) || src1->nb[1] < (size_t) src1->ne[0] * sizeof(float)) return false;
     if ((src1->nb[1] | src1->nb[2] | src1->nb[3]) & 15) return false;
@@ -224,7 +233,8 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
     const int64_t r2 = ne12 / ne02, r3 = ne13 / ne03;
     if (M == 0 || N == 0 || ne12 == 0 || ne13 == 0) return GGML_STATUS_SUCCESS;
 
-    const size_t need = q4k_mul_mat_workspace_bytes(K, N);
+    const bool q6 = src0->type == GGML_TYPE_Q6_K;
+    const size_t need = q6 ? q6k_mul_mat_workspace_bytes(K, N) : q4k_mul_mat_workspace_bytes(K, N);
     if (need > ctx->workspace_bytes) {
         // grow-only scratch; in-flight kernels may still read the old one
         if (q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream) != Q4K_OK) return GGML_STATUS_FAILED;
@@ -242,10 +252,12 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
             const char * w = (const char *) src0->data + i02 * src0->nb[2] + i03 * src0->nb[3];
             const char * x = (const char *) src1->data + i12 * src1->nb[2] + i13 * src1->nb[3];
             char * d = (char *) node->data + i12 * node->nb[2] + i13 * node->nb[3];
-            const int rc = q4k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
-                                       (float *) d, (int64_t) node->nb[1], ctx->workspace, ctx->workspace_bytes, ctx->stream);
+            const int rc = q6 ? q6k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
+                                            (float *) d, (int64_t) node->nb[1], ctx->workspace, ctx->workspace_bytes, ctx->stream)
+                              : q4k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
+                                            (float *) d, (int64_t) node->nb[1], ctx->workspace, ctx->workspace_bytes, ctx->stream);
             if (rc != Q4K_OK) {
-                GGML_LOG_ERROR("Q4K_B200: q4k_mul_mat(%s) failed: rc=%d cudaError=%d\n", node->name, rc, q4k_last_cuda_error());
+                GGML_LOG_ERROR("Q4K_B200: %s(%s) failed: rc=%d cudaError=%d\n", q6 ? "q6k_mul_mat" : "q4k_mul_mat", node->name, rc, q4k_last_cuda_error());
                 return GGML_STATUS_FAILED;
             }
         }
@@ -257,7 +269,7 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
 bool groupable(const ggml_tensor * node) {
     const ggml_tensor * src0 = node->src[0];
     const ggml_tensor * src1 = node->src[1];
-    return src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src1->ne[1] >= 1 &&
+    return src0->type == GGML_TYPE_Q4_K && src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src1->ne[1] >= 1 &&
            src1->ne[1] <= Q4K_GEMV_MAX_N && src0->ne[1] > 0 && node->nb[1] == (size_t) src0->ne[1] * sizeof(float);
 }
 
@@ -488,7 +500,7 @@ ggml_backend_reg_t q4k_b200_reg() {
             devs.push_back(ggml_backend_device{device_iface, &reg, &c});
             c.buft = ggml_backend_buffer_type{buft_iface, &devs.back(), &c};
         }
-        GGML_LOG_INFO("Q4K_B200: %zu sm_100 device(s); claims MUL_MAT(Q4_K, F32) only\n", devs.size());
+        GGML_LOG_INFO("Q4K_B200: %zu sm_100 device(s); claims MUL_MAT(Q4_K | Q6_K, F32) only\n", devs.size());
     });
     return &reg;
 }

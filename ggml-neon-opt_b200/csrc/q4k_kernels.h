@@ -49,6 +49,11 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream);
 
+// Q6_K decode GEMV (gemv_q6k.cu), 1 <= N <= 8; dump != nullptr also writes the per-superblock integer sums
+cudaError_t launch_gemv_q6k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                            const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
+                            float *dst, int64_t dst_col_stride_bytes, int32_t *dump, bool pdl, cudaStream_t stream);
+
 cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
                                   const void *xq, int64_t N, int64_t xq_row_stride_bytes,
                                   int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);

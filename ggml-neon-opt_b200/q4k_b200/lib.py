@@ -12,6 +12,7 @@ import os
 import torch
 
 QK_K, Q4K_BLOCK, Q8K_BLOCK = 256, 144, 292
+Q6K_BLOCK = 210
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # Q4K_B200_LIB: another build of the same library (A/B comparisons of kernels on one GPU box); default = the in-tree build
 _LIB_PATH = os.environ.get("Q4K_B200_LIB") or os.path.normpath(os.path.join(_HERE, "..", "lib", "libq4k_b200.so"))
@@ -78,6 +79,11 @@ def load():
         L.q4k_plan_run_host.argtypes = [vp, vp, vp, vp]
         L.q4k_plan_destroy.argtypes = [vp]
         L.q4k_plan_destroy.restype = None
+        L.q6k_mul_mat_workspace_bytes.argtypes = [i64, i64]
+        L.q6k_mul_mat_workspace_bytes.restype = sz
+        L.q6k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
+        L.q6k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
+        L.q6k_debug_partials.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, vp, vp]
         L.q4k_debug_set_fuse_limit.argtypes = [i64]
         L.q4k_debug_set_pdl.argtypes = [i32]
         L.q4k_debug_set_gemv_order.argtypes = [i32]
@@ -189,6 +195,56 @@ def debug_partials(w: torch.Tensor, xq: torch.Tensor, row0: int = 0, nrows: int 
         _check("q4k_debug_partials", load().q4k_debug_partials(w.data_ptr(), nb * QK_K, w.stride(0), row0, nrows, xq.data_ptr(), N,
                                                                xq.stride(0), p.data_ptr(), si.data_ptr(), sm.data_ptr(), _stream()))
     return p, si, sm
+
+
+def mul_mat_q6k(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None,
+                workspace: torch.Tensor | None = None) -> torch.Tensor:
+    """ggml_mul_mat(Q6_K w [M, K/256*210], F32 x [N, K]) -> float32 [N, M]  (include/q4k_b200.h: q6k_mul_mat)."""
+    _dev_u8(w, "w")
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.is_contiguous()):
+        raise TypeError("x: expected a contiguous 2-D CUDA float32 tensor")
+    M, N, K = w.shape[0], x.shape[0], x.shape[1]
+    if K % QK_K or w.shape[1] != K // QK_K * Q6K_BLOCK:
+        raise ValueError("shape mismatch between w and x")
+    if out is None:
+        out = torch.empty((N, M), dtype=torch.float32, device=x.device)
+    if workspace is None:
+        workspace = torch.empty(max(load().q6k_mul_mat_workspace_bytes(K, N), 16), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        _check("q6k_mul_mat", load().q6k_mul_mat(w.data_ptr(), M, K, w.stride(0), x.data_ptr(), N, K * 4,
+                                                 out.data_ptr(), out.stride(0) * 4 if N > 1 else M * 4,
+                                                 workspace.data_ptr(), workspace.numel(), _stream()))
+    return out
+
+
+def mul_mat_q6k_q8(w: torch.Tensor, xq: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Same with src1 already Q8_K: xq uint8 [N, K/256*292]."""
+    _dev_u8(w, "w")
+    _dev_u8(xq, "xq")
+    M, N = w.shape[0], xq.shape[0]
+    nb = w.shape[1] // Q6K_BLOCK
+    if xq.shape[1] != nb * Q8K_BLOCK:
+        raise ValueError("shape mismatch between w and xq")
+    if out is None:
+        out = torch.empty((N, M), dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _check("q6k_mul_mat_q8", load().q6k_mul_mat_q8(w.data_ptr(), M, nb * QK_K, w.stride(0), xq.data_ptr(), N, xq.stride(0),
+                                                       out.data_ptr(), out.stride(0) * 4 if N > 1 else M * 4, _stream()))
+    return out
+
+
+def debug_partials_q6k(w: torch.Tensor, xq: torch.Tensor):
+    """-> (sumi int32 [N, M, nb], y float32 [N, M]) from the product kernel with its integer dump on."""
+    _dev_u8(w, "w")
+    _dev_u8(xq, "xq")
+    M, N = w.shape[0], xq.shape[0]
+    nb = w.shape[1] // Q6K_BLOCK
+    si = torch.zeros((N, M, nb), dtype=torch.int32, device=w.device)
+    y = torch.zeros((N, M), dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _check("q6k_debug_partials", load().q6k_debug_partials(w.data_ptr(), M, nb * QK_K, w.stride(0), xq.data_ptr(), N,
+                                                               xq.stride(0), si.data_ptr(), y.data_ptr(), _stream()))
+    return si, y
 
 
 class HostPlan:

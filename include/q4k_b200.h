@@ -26,6 +26,7 @@ extern "C" {
 #define Q4K_QK_K          256
 #define Q4K_BLOCK_Q4K     144
 #define Q4K_BLOCK_Q8K     292
+#define Q4K_BLOCK_Q6K     210    /* block_q6_K, L/ggml/src/ggml-common.h:326-336 */
 #define Q4K_GEMV_MAX_N    8      /* batch sizes served by the HBM-bound GEMV; larger N takes the GEMM */
 
 enum {
@@ -182,6 +183,30 @@ int q4k_mul_mat_host_async(const void *w_dev, int64_t M, int64_t K, int64_t w_ro
                            const float *x_host, int64_t N, float *dst_host,
                            void *x_stage_dev, float *dst_stage_dev,
                            void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* ---- Q6_K weights ----------------------------------------------------------------------
+ * TinyLlama Q4_K_M keeps attn_v / ffn_down of 10 layers and output.weight in Q6_K (L/src/llama-quant.cpp:228-230,
+ * 302-303, 358-364); these entries replace ggml_compute_forward_mul_mat for Q6_K src0 / F32 src1
+ * (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401 with type_traits_cpu[GGML_TYPE_Q6_K], :296-301: vec_dot =
+ * ggml_vec_dot_q6_K_q8_K, L/ggml/src/ggml-cpu/arch/x86/quants.c:2129-2218; vec_dot_type = Q8_K).
+ * Weights: M rows of K/256 block_q6_K (210 B each); w_dev and w_row_stride_bytes need only be even (210-byte blocks
+ * are 2-byte aligned by nature).  Every N is served by the HBM-bound decode kernel, eight columns per pass (there is no
+ * tensor-core Q6_K kernel yet).  Integer sums per superblock are exactly the reference's; fp32 within 1e-5. */
+size_t q6k_mul_mat_workspace_bytes(int64_t K, int64_t N);
+int q6k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                float *dst_dev, int64_t dst_col_stride_bytes,
+                void *workspace_dev, size_t workspace_bytes, void *stream);
+/* src1 already Q8_K */
+int q6k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                   const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
+                   float *dst_dev, int64_t dst_col_stride_bytes, void *stream);
+/* parity: runs the PRODUCT kernel with its integer dump switched on: sumi_dev[(n*M + m)*(K/256) + b] = the int32
+ * sum_j scales[j] * sum_l (q6 - 32) * q8 of superblock b (the reference's aux32 total, ggml-cpu/quants.c:740-752);
+ * dst_dev = dense [N][M] fp32 results. */
+int q6k_debug_partials(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                       const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
+                       int32_t *sumi_dev, float *dst_dev, void *stream);
 
 #ifdef __cplusplus
 }

@@ -9,7 +9,7 @@ LIB = os.path.join(ROOT, "ggml-neon-opt_b200", "lib", "libq4k_b200.so")
 
 def declared():
     src = open(os.path.join(ROOT, "include", "q4k_b200.h")).read()
-    return sorted(set(re.findall(r"\b(q4k_[a-z0-9_A-Z]+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b(q[46]k_[a-z0-9_A-Z]+)\s*\(", src)))
 
 
 def test_exports_match_header():
@@ -39,3 +39,12 @@ def test_product_path_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".c")):
                 txt = open(os.path.join(d, f)).read()
                 assert "oracle" not in txt.replace("the oracle", ""), os.path.join(d, f)
+
+
+def test_q6k_host_entries():
+    lib = ctypes.CDLL(LIB)
+    lib.q6k_mul_mat_workspace_bytes.restype = ctypes.c_size_t
+    lib.q6k_mul_mat_workspace_bytes.argtypes = [ctypes.c_int64, ctypes.c_int64]
+    assert lib.q6k_mul_mat_workspace_bytes(5632, 2) == 2 * 22 * 292
+    assert lib.q6k_mul_mat_workspace_bytes(100, 1) == 0
+    assert "q6k_mul_mat" in declared() and "q6k_debug_partials" in declared()
