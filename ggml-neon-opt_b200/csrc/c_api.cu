@@ -102,6 +102,11 @@ int q4k_debug_set_gemm(int on) {
     return Q4K_OK;
 }
 
+int q4k_debug_set_big_matrix_bytes(int64_t bytes) {
+    g_big_matrix_bytes = bytes;
+    return Q4K_OK;
+}
+
 int q4k_debug_set_pdl(int on) {
     g_gemv_pdl = on ? 1 : 0;
     return Q4K_OK;

@@ -15,8 +15,8 @@
 //     bsums), 68 words = 4 banks per block step, so eight lanes on eight blocks never conflict and the four
 //     rows of a tile broadcast.  They are either copied from a Q8_K workspace or quantized in place from F32
 //     (same arithmetic as quantize_q8k.cu, bit-exact).
-//   * rows are dealt to CTAs in balanced contiguous ranges; warps of a CTA pull 4-row groups from a
-//     shared-memory counter, so the tail inside an SM is one row group.
+//   * 4-row groups are dealt round-robin to the CTAs (the grid sweeps the matrix front to back); warps of a CTA pull
+//     their CTA's groups from a shared-memory counter, so the tail inside an SM is one row group.
 //   * programmatic dependent launch: barrier init and the first weight tiles are issued BEFORE
 //     griddepcontrol.wait (weights never depend on the previous kernel), only the activations wait.
 //
@@ -38,11 +38,20 @@
 
 namespace q4k {
 
+int64_t g_big_matrix_bytes = (int64_t)34 << 20;   // q4k_debug_set_big_matrix_bytes; <= 0: never (crossover measured: profiles/r1_big_sweep.txt)
+
 namespace {
 
-template <int N, bool EXACT>
+// ORD: 0 = fast (one int per lane and superblock), 1 = EXACT (the reference's AVX2 chain), 2 = the float association of
+// the tensor-pipe decode kernel (gemv_q4k_mma.cu, N == 1): per lane (= superblock class b of the eight of a round) four
+// chains over the 32-byte nibble chunks, summed (c0 + c1) + (c2 + c3) at the end of every 32-superblock segment, the
+// eight classes in order, the segments in K order — bit-identical to that kernel, so large matrices can take this
+// (copy-engine-bound, faster above ~34 MB) kernel without a row's bits depending on the size of its matrix.
+template <int N, int ORD>
 __global__ void __launch_bounds__(WARPS * 32, 2)
 gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
+    constexpr bool EXACT = ORD == 1, MMAORD = ORD == 2;
+    static_assert(!MMAORD || N == 1, "the tensor-pipe order is only instantiated for N == 1");
     extern __shared__ __align__(128) uint8_t smem[];
     const int nb = p.nb, S = p.stages;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -58,8 +67,8 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     int *counter = reinterpret_cast<int *>(smem + off);    off += 16;
     int *scratch = reinterpret_cast<int *>(smem + off) + (EXACT ? warp * N * SCR_WORDS : 0);
 
-    // balanced contiguous range of 4-row groups for this CTA
-    const int64_t g0 = p.n_groups * blockIdx.x / gridDim.x, g1 = p.n_groups * (blockIdx.x + 1) / gridDim.x;
+    // 4-row groups are dealt round-robin to the CTAs (group = blockIdx + k * gridDim): the grid sweeps the matrix front to
+    // back, which HBM likes better than 296 separate streams (measured on the tensor-pipe and the Q6_K kernels: +10-25%)
     const int ksteps = (nb + TILE_SB - 1) / TILE_SB;
 
     if (threadIdx.x == 0) *counter = 0;
@@ -78,9 +87,9 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
             int nxt = 0;
             if (lane == 0) nxt = atomicAdd(counter, 1);
             nxt = __shfl_sync(0xffffffffu, nxt, 0);
-            cur_rg = g0 + nxt;
+            cur_rg = (int64_t)blockIdx.x + (int64_t)nxt * gridDim.x;
             prod_ks = 0;
-            if (cur_rg >= g1) exhausted = true;
+            if (cur_rg >= p.n_groups) exhausted = true;
         }
         const uint32_t bar = smem_u32(&bars[s]);
         if (exhausted) {
@@ -124,6 +133,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     float acc[N], accm[N];
 #pragma unroll
     for (int n = 0; n < N; ++n) { acc[n] = 0.0f; accm[n] = 0.0f; }
+    float cacc[4] = {0.0f, 0.0f, 0.0f, 0.0f}, caccm[4] = {0.0f, 0.0f, 0.0f, 0.0f}, tot = 0.0f;   // MMAORD: chunk chains, tile total
 
     int s = 0;
     uint32_t parity = 0;
@@ -184,7 +194,12 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                             pl = __dp4a((int)(qw[t] & 0x0f0f0f0fu), (int)ylo[t], pl);
                             ph = dp4a_u8s8(qw[t] & 0xf0f0f0f0u, yhi[t], ph);
                         }
-                        sum16[n][0] += sc_lo16 * pl + sc_hi * ph;
+                        if (MMAORD) {
+                            const float dall = __fmul_rn(d_s[(abase + n) * nb + kb], dd.x);
+                            cacc[g] = __fmaf_rn(dall, (float)((sc_lo16 * pl + sc_hi * ph) >> 4), cacc[g]);
+                        } else {
+                            sum16[n][0] += sc_lo16 * pl + sc_hi * ph;
+                        }
                     }
                 }
             }
@@ -203,6 +218,11 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                     row[68 + b] = p0; row[76 + b] = p1; row[84 + b] = p2; row[92 + b] = p3;
                     row[100 + b] = __float_as_int(dall);
                     row[108 + b] = __float_as_int(dmn);
+                } else if (MMAORD) {
+                    caccm[0] = __fmaf_rn(dmn, (float)p0, caccm[0]);
+                    caccm[1] = __fmaf_rn(dmn, (float)p1, caccm[1]);
+                    caccm[2] = __fmaf_rn(dmn, (float)p2, caccm[2]);
+                    caccm[3] = __fmaf_rn(dmn, (float)p3, caccm[3]);
                 } else {
                     acc[n] = __fmaf_rn(dall, (float)(sum16[n][0] >> 4), acc[n]);
                     accm[n] = __fmaf_rn(dmn, (float)(p0 + p1 + p2 + p3), accm[n]);
@@ -234,6 +254,17 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                 }
             }
         }
+        if (MMAORD && ((ks & 3) == 3 || ks == ksteps - 1)) {     // end of a 32-superblock segment (gemv_q4k_mma.cu SEG_ROUNDS)
+            const float v01 = __fadd_rn(__fadd_rn(cacc[0], caccm[0]), __fadd_rn(cacc[1], caccm[1]));
+            const float v23 = __fadd_rn(__fadd_rn(cacc[2], caccm[2]), __fadd_rn(cacc[3], caccm[3]));
+            const float v = __fadd_rn(v01, v23);
+            float a = __shfl_sync(0xffffffffu, v, lane & ~7);
+#pragma unroll
+            for (int w = 1; w < 8; ++w) a = __fadd_rn(a, __shfl_sync(0xffffffffu, v, (lane & ~7) + w));
+            tot = (ks >> 2) == 0 ? a : __fadd_rn(tot, a);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { cacc[c] = 0.0f; caccm[c] = 0.0f; }
+        }
         if (ks == ksteps - 1) {                              // row group finished: horizontal sums + store
             const int64_t row = (int64_t)lgrp * TILE_ROWS + r;
 #pragma unroll
@@ -246,6 +277,8 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                     m = __fadd_rn(m, __shfl_xor_sync(0xffffffffu, m, 2));    // acc_m + movehl
                     m = __fadd_rn(m, __shfl_xor_sync(0xffffffffu, m, 1));    // + movehdup
                     a = __fadd_rn(a, m);
+                } else if (MMAORD) {
+                    a = tot;
                 } else {
                     a = __fadd_rn(a, m);
                     a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, 1));
@@ -290,9 +323,10 @@ int dbg_env(const char *name) {           // development knobs (tools/launch_cha
     return e ? atoi(e) : 0;
 }
 
-template <int N, bool EXACT>
+template <int N, int ORD>
 cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
-    auto kern = gemv_q4k_tma_kernel<N, EXACT>;
+    constexpr bool EXACT = ORD == 1;
+    auto kern = gemv_q4k_tma_kernel<N, ORD>;
     const size_t fixed = fixed_smem(N * p.nx, p.nb, EXACT, N);
     if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
     // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits
@@ -329,7 +363,7 @@ cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_
     return e;
 }
 
-template <bool EXACT>
+template <int EXACT>
 cudaError_t launch_tma_e(int N, const TmaGemvParams &p, int stages, bool pdl, cudaStream_t st) {
     switch (N) {
         case 1: return launch_tma_n<1, EXACT>(p, stages, pdl, st);
@@ -355,7 +389,12 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
                                     bool pdl, cudaStream_t stream, float *const *peer_dst, int n_peers, int64_t dst_row0) {
     if (M == 0 || N == 0) return cudaSuccess;
     if (n_peers > 8) return cudaErrorInvalidValue;
-    if (!exact_order && stages <= 0 && dbg_env("Q4K_DBG_MMA") >= 0) {      // tolerance order: the tensor-pipe kernel
+    // Large single-column launches: the lane-per-superblock kernel in the tensor-pipe kernel's float association (ORD 2,
+    // identical bits) — it runs at the bulk-copy ceiling where the 16-row tensor-pipe tiles do not (measured on B200:
+    // 28672x8192 24.1 vs 26.3 us, 8192x28672 29.3 vs 33.8 us, 8192x8192 10.3 vs 10.7 us; 4096x14336 14.7 vs 12.5 us, so
+    // matrices below 34 MiB stay on the tensor-pipe kernel — profiles/r1_big_sweep.txt).
+    const bool big = N == 1 && !exact_order && stages <= 0 && g_big_matrix_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= g_big_matrix_bytes;
+    if (!big && !exact_order && stages <= 0 && dbg_env("Q4K_DBG_MMA") >= 0) {      // tolerance order: the tensor-pipe kernel
         const void *wv[1] = {w};
         const int64_t Mv[1] = {M};
         const float *xv[1] = {xf};
@@ -377,7 +416,17 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.nmat = 1; p.nx = 1;
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
-    return exact_order ? launch_tma_e<true>(N, p, stages, pdl, stream) : launch_tma_e<false>(N, p, stages, pdl, stream);
+    if (big) {
+        const cudaError_t e = launch_tma_n<1, 2>(p, stages, pdl, stream);
+        if (e != cudaErrorNotSupported) return e;
+        const void *wv[1] = {w};                       // activations too long for this kernel's residency: the tensor-pipe kernel
+        const int64_t Mv[1] = {M};
+        const float *xv[1] = {xf};
+        float *dv[1] = {dst};
+        return launch_gemv_q4k_mma(1, wv, Mv, K, w_row_stride_bytes, xq, xq ? nullptr : xv, N, x_row_stride_bytes, dv,
+                                   dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream);
+    }
+    return exact_order ? launch_tma_e<1>(N, p, stages, pdl, stream) : launch_tma_e<0>(N, p, stages, pdl, stream);
 }
 
 // Horizontally fused decode launch: nmat (<= 4) independent matrices with the same K and N in ONE launch; matrices
@@ -412,7 +461,7 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
     p.n_groups = groups;
     if (groups == 0 || N == 0) return cudaSuccess;
     if (groups > 0x7fffffff) return cudaErrorInvalidValue;
-    return exact_order ? launch_tma_e<true>(N, p, 0, pdl, stream) : launch_tma_e<false>(N, p, 0, pdl, stream);
+    return exact_order ? launch_tma_e<1>(N, p, 0, pdl, stream) : launch_tma_e<0>(N, p, 0, pdl, stream);
 }
 
 }  // namespace q4k

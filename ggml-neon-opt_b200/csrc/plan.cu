@@ -26,6 +26,7 @@ struct q4k_plan {
         int64_t M, K, w_stride, N;
         int input_id;
         size_t out_off;
+        int q6;               // 1: block_q6_K weights (q6k_mul_mat), 0: block_q4_K
     };
     struct Input {
         int id;
@@ -58,8 +59,8 @@ int enqueue_all(q4k_plan *p, cudaStream_t st) {
     while (i < p->items.size()) {
         const q4k_plan::Item &a = p->items[i];
         size_t j = i + 1;
-        if (a.N <= Q4K_GEMV_MAX_N) {
-            while (j < p->items.size() && j - i < 4 && p->items[j].input_id == a.input_id && p->items[j].K == a.K &&
+        if (a.N <= Q4K_GEMV_MAX_N && !a.q6) {
+            while (j < p->items.size() && j - i < 4 && !p->items[j].q6 && p->items[j].input_id == a.input_id && p->items[j].K == a.K &&
                    p->items[j].N == a.N && p->items[j].w_stride == a.w_stride) ++j;
         }
         const q4k_plan::Input *in = p->find_input(a.input_id);
@@ -80,8 +81,10 @@ int enqueue_all(q4k_plan *p, cudaStream_t st) {
         if (rc == Q4K_ERR_UNSUPPORTED) {            // not fusable (or a single mul_mat): one q4k_mul_mat each
             for (size_t k = i; k < j; ++k) {
                 const q4k_plan::Item &b = p->items[k];
-                rc = q4k_mul_mat(b.w, b.M, b.K, b.w_stride, x, b.N, b.K * 4, reinterpret_cast<float *>(p->out_dev + b.out_off), b.M * 4,
-                                 p->ws_dev, p->ws_bytes, st);
+                rc = b.q6 ? q6k_mul_mat(b.w, b.M, b.K, b.w_stride, x, b.N, b.K * 4, reinterpret_cast<float *>(p->out_dev + b.out_off), b.M * 4,
+                                        p->ws_dev, p->ws_bytes, st)
+                          : q4k_mul_mat(b.w, b.M, b.K, b.w_stride, x, b.N, b.K * 4, reinterpret_cast<float *>(p->out_dev + b.out_off), b.M * 4,
+                                        p->ws_dev, p->ws_bytes, st);
                 if (rc != Q4K_OK) return rc;
             }
         }
@@ -101,10 +104,12 @@ q4k_plan *q4k_plan_create(int device) {
     return p;
 }
 
-int q4k_plan_add_mul_mat(q4k_plan *p, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N, int input_id) {
+static int plan_add(q4k_plan *p, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N, int input_id, int q6) {
     if (!p || p->finalized) return Q4K_ERR_UNSUPPORTED;
     if (!w_dev) return Q4K_ERR_BAD_POINTER;
-    if (M <= 0 || N <= 0 || K <= 0 || K % Q4K_QK_K != 0 || w_row_stride_bytes < K / Q4K_QK_K * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15))
+    if (M <= 0 || N <= 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (q6 ? (w_row_stride_bytes < K / Q4K_QK_K * Q4K_BLOCK_Q6K || (w_row_stride_bytes & 1))
+           : (w_row_stride_bytes < K / Q4K_QK_K * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15)))
         return Q4K_ERR_BAD_SHAPE;
     const q4k_plan::Input *in = p->find_input(input_id);
     if (in && (in->N != N || in->K != K)) return Q4K_ERR_BAD_SHAPE;        // one input_id = one [N][K] buffer
@@ -112,11 +117,19 @@ int q4k_plan_add_mul_mat(q4k_plan *p, const void *w_dev, int64_t M, int64_t K, i
         p->inputs.push_back({input_id, N, K, p->in_bytes});
         p->in_bytes += align256((size_t)N * K * 4);
     }
-    p->items.push_back({w_dev, M, K, w_row_stride_bytes, N, input_id, p->out_bytes});
+    p->items.push_back({w_dev, M, K, w_row_stride_bytes, N, input_id, p->out_bytes, q6});
     p->out_bytes += align256((size_t)N * M * 4);
-    const size_t ws = q4k_mul_mat_workspace_bytes(K, N);
+    const size_t ws = q6 ? q6k_mul_mat_workspace_bytes(K, N) : q4k_mul_mat_workspace_bytes(K, N);
     if (ws > p->ws_bytes) p->ws_bytes = ws;
     return (int)p->items.size() - 1;
+}
+
+int q4k_plan_add_mul_mat(q4k_plan *p, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N, int input_id) {
+    return plan_add(p, w_dev, M, K, w_row_stride_bytes, N, input_id, 0);
+}
+
+int q4k_plan_add_mul_mat_q6k(q4k_plan *p, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N, int input_id) {
+    return plan_add(p, w_dev, M, K, w_row_stride_bytes, N, input_id, 1);
 }
 
 int q4k_plan_finalize(q4k_plan *p) {

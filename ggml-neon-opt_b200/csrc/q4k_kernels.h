@@ -59,6 +59,7 @@ cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride
                                   int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);
 
 extern int g_gemv_config;   // development knob, see gemv_q4k.cu
+extern int64_t g_big_matrix_bytes;   // N == 1 launches with at least this many weight bytes take the bulk-copy kernel (gemv_q4k_tma.cu, ORD 2)
 extern int g_gemv_pdl;      // 1 = launch the GEMV with programmatic stream serialization (default)
 void add_launches(int64_t n);  // launches replayed through a CUDA graph
 int64_t launch_count();

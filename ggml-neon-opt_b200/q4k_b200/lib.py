@@ -60,6 +60,7 @@ def load():
         L.q4k_plan_create.argtypes = [i32]
         L.q4k_plan_create.restype = vp
         L.q4k_plan_add_mul_mat.argtypes = [vp, vp, i64, i64, i64, i64, i32]
+        L.q4k_plan_add_mul_mat_q6k.argtypes = [vp, vp, i64, i64, i64, i64, i32]
         L.q4k_plan_finalize.argtypes = [vp]
         L.q4k_plan_input_bytes.argtypes = [vp]
         L.q4k_plan_input_bytes.restype = sz
@@ -87,6 +88,7 @@ def load():
         L.q4k_debug_set_fuse_limit.argtypes = [i64]
         L.q4k_debug_set_pdl.argtypes = [i32]
         L.q4k_debug_set_gemv_order.argtypes = [i32]
+        L.q4k_debug_set_big_matrix_bytes.argtypes = [i64]
         L.q4k_debug_set_gemv_config.argtypes = [i32]
         _lib = L
     return _lib
@@ -304,10 +306,12 @@ class GraphPlan:
         self._keep, self._shapes, self._in_shapes = [], [], {}
         self.finalized = False
 
-    def add(self, w: torch.Tensor, N: int, input_id: int) -> int:
+    def add(self, w: torch.Tensor, N: int, input_id: int, q6k: bool = False) -> int:
+        """w: block_q4_K rows (or block_q6_K rows with q6k=True)."""
         _dev_u8(w, "w")
-        M, K = w.shape[0], w.shape[1] // Q4K_BLOCK * QK_K
-        rc = self._L.q4k_plan_add_mul_mat(self._p, w.data_ptr(), M, K, w.stride(0), N, input_id)
+        M, K = w.shape[0], w.shape[1] // (Q6K_BLOCK if q6k else Q4K_BLOCK) * QK_K
+        fn = self._L.q4k_plan_add_mul_mat_q6k if q6k else self._L.q4k_plan_add_mul_mat
+        rc = fn(self._p, w.data_ptr(), M, K, w.stride(0), N, input_id)
         if rc < 0:
             raise Q4KError("q4k_plan_add_mul_mat", rc, self._L.q4k_last_cuda_error())
         self._keep.append(w)

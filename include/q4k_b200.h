@@ -121,6 +121,8 @@ typedef struct q4k_plan q4k_plan;
 q4k_plan *q4k_plan_create(int device);                                   /* NULL on failure */
 int       q4k_plan_add_mul_mat(q4k_plan *plan, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                int64_t N, int input_id);                 /* returns the mul_mat's index (>= 0) */
+int       q4k_plan_add_mul_mat_q6k(q4k_plan *plan, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                                   int64_t N, int input_id);             /* same, block_q6_K weights (q6k_mul_mat) */
 int       q4k_plan_finalize(q4k_plan *plan);                             /* allocates staging, captures the graph */
 size_t    q4k_plan_input_bytes(const q4k_plan *plan);
 size_t    q4k_plan_output_bytes(const q4k_plan *plan);
@@ -163,6 +165,11 @@ int q4k_debug_set_gemv_config(int cfg);
 int q4k_debug_set_fuse_limit(int64_t n_floats);
 /* development knob: 1 (default) = GEMV launches use programmatic dependent launch, 0 = plain stream order */
 int q4k_debug_set_pdl(int on);
+
+/* development knob: single-column (N == 1) launches whose weights are at least this many bytes (default 34 MiB) run
+ * the lane-per-superblock bulk-copy kernel instead of the tensor-pipe kernel — same float association, identical bits,
+ * faster where the matrix is large enough to be bound by the copy engine; <= 0 = never. */
+int q4k_debug_set_big_matrix_bytes(int64_t bytes);
 
 /* development knob: 1 (default) = N > 8 runs the tcgen05 GEMM, 0 = the decode kernel eight columns at a time */
 int q4k_debug_set_gemm(int on);

@@ -66,6 +66,9 @@ def libs():
         shim.ref_mul_mat_set_q4k.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), i64, i32, i32, i32,
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]
         shim.ref_mul_mat_set_q4k.restype = i32
+        shim.ref_mul_mat_set_typed.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i32), i64, i32, i32, i32,
+                                               C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        shim.ref_mul_mat_set_typed.restype = i32
         # ggml-cpu's fp16->fp32 is a lookup table filled by ggml_cpu_init() (ggml-cpu.c:3526-3549);
         # the reference always reaches vec_dot through backend init, direct callers must do it themselves
         cpu.ggml_cpu_init()
@@ -206,6 +209,21 @@ def mul_mat_set(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, iters: 
 
 
 Q6K_BLOCK = 210
+
+
+def mul_mat_set_typed(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, iters: int = 3):
+    """mul_mat_set with a weight type per matrix: shapes = [(M, K, is_q6k)].  Returns (best_s, mean_s, checksum)."""
+    shim = libs()[3]
+    n = len(shapes)
+    Ms = (C.c_int64 * n)(*[int(s[0]) for s in shapes])
+    Ks = (C.c_int64 * n)(*[int(s[1]) for s in shapes])
+    q6 = (C.c_int * n)(*[int(bool(s[2])) for s in shapes])
+    secs = (C.c_double * 2)()
+    chk = C.c_double(0)
+    rc = shim.ref_mul_mat_set_typed(n, Ms, Ks, q6, N, n_threads, warmup, iters, secs, C.byref(chk))
+    if rc != 0:
+        raise RuntimeError(f"ref_mul_mat_set_typed rc={rc}")
+    return secs[0], secs[1], chk.value
 
 
 def quantize_q6_K(x: np.ndarray) -> np.ndarray:

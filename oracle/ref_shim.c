@@ -168,8 +168,10 @@ int ref_n_backend_devices(void) { return (int)ggml_backend_dev_count(); }
  * dmin = 2^-5 — throughput only, the parity tests use real quantized weights), activations with a
  * deterministic ramp.  Times `iters` graph computes after `warmup`.  secs[0] = best, secs[1] = mean.
  * checksum (optional) receives the sum of all outputs of the last compute. */
-int ref_mul_mat_set_q4k(int n_mats, const int64_t *Ms, const int64_t *Ks, int64_t N, int n_threads,
-                        int warmup, int iters, double *secs, double *checksum) {
+/* same with a weight type per matrix: q6[i] != 0 -> GGML_TYPE_Q6_K (random valid block_q6_K bytes, d = 2^-8), else Q4_K:
+ * the full Q4_K_M decode token */
+int ref_mul_mat_set_typed(int n_mats, const int64_t *Ms, const int64_t *Ks, const int *q6, int64_t N, int n_threads,
+                          int warmup, int iters, double *secs, double *checksum) {
     ggml_backend_t cpu = ggml_backend_cpu_init();
     if (!cpu) return -1;
     ggml_backend_cpu_set_n_threads(cpu, n_threads);
@@ -181,7 +183,7 @@ int ref_mul_mat_set_q4k(int n_mats, const int64_t *Ms, const int64_t *Ks, int64_
     struct ggml_tensor **ws = calloc((size_t)n_mats, sizeof *ws), **xs = calloc((size_t)n_mats, sizeof *xs),
                        **ys = calloc((size_t)n_mats, sizeof *ys);
     for (int i = 0; i < n_mats; ++i) {
-        ws[i] = ggml_new_tensor_2d(ctx, GGML_TYPE_Q4_K, Ks[i], Ms[i]);
+        ws[i] = ggml_new_tensor_2d(ctx, q6 && q6[i] ? GGML_TYPE_Q6_K : GGML_TYPE_Q4_K, Ks[i], Ms[i]);
         xs[i] = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, Ks[i], N);
         ys[i] = ggml_mul_mat(ctx, ws[i], xs[i]);
         ggml_build_forward_expand(gf, ys[i]);
@@ -197,7 +199,8 @@ int ref_mul_mat_set_q4k(int n_mats, const int64_t *Ms, const int64_t *Ks, int64_
             s ^= s << 13; s ^= s >> 7; s ^= s << 17;
             memcpy(p + o, &s, 8);
         }
-        for (size_t o = 0; o < nbytes; o += 144) { p[o] = 0x00; p[o + 1] = 0x2c; p[o + 2] = 0x00; p[o + 3] = 0x28; }
+        if (q6 && q6[i]) { for (size_t o = 0; o < nbytes; o += 210) { p[o + 208] = 0x00; p[o + 209] = 0x1c; } }
+        else { for (size_t o = 0; o < nbytes; o += 144) { p[o] = 0x00; p[o + 1] = 0x2c; p[o + 2] = 0x00; p[o + 3] = 0x28; } }
         float *x = (float *)xs[i]->data;
         const int64_t ne = Ks[i] * N;
         for (int64_t j = 0; j < ne; ++j) x[j] = (float)((j * 2654435761u) % 2001) * 1e-3f - 1.0f;
@@ -226,4 +229,9 @@ done:
     free(ws); free(xs); free(ys);
     ggml_backend_free(cpu);
     return rc;
+}
+
+int ref_mul_mat_set_q4k(int n_mats, const int64_t *Ms, const int64_t *Ks, int64_t N, int n_threads,
+                        int warmup, int iters, double *secs, double *checksum) {
+    return ref_mul_mat_set_typed(n_mats, Ms, Ks, NULL, N, n_threads, warmup, iters, secs, checksum);
 }

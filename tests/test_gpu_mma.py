@@ -93,3 +93,30 @@ def test_mma_split_k_does_not_change_the_bits(q4k, fast_order, M, K, N):
     for kp in (2, 4):
         assert np.array_equal(outs[kp].view(np.uint32), outs[1].view(np.uint32)), kp
     assert np.array_equal(policy.view(np.uint32), outs[1].view(np.uint32))
+
+
+@pytest.mark.parametrize("M,K", [(300, 2048), (64, 5632), (33, 2560), (16, 14336), (9, 28672), (5, 256), (130, 8192), (40, 8448)])
+def test_big_matrix_kernel_gives_the_tensor_pipe_kernels_bits(q4k, M, K):
+    """N == 1 launches above q4k_debug_set_big_matrix_bytes run the lane-per-superblock bulk-copy kernel in the tensor-pipe
+    kernel's float association (gemv_q4k_tma.cu ORD 2): same bits, so a row does not depend on the size of its matrix.
+    Shapes cover one / several 32-superblock segments, ragged rounds (K/256 % 8 != 0) and ragged row groups."""
+    import torch
+    from oracle import port
+    lib = q4k.load()
+    w, x = make_weights(M, K, seed=M), make_acts(1, K)
+    wd, xd = t(w), t(x)
+    xq = q4k.quantize_q8_K(xd)
+    try:
+        lib.q4k_debug_set_big_matrix_bytes(0)                 # never: the tensor-pipe kernel
+        a = q4k.mul_mat(wd, xd).cpu().numpy()
+        aq = q4k.mul_mat_q8(wd, xq).cpu().numpy()
+        lib.q4k_debug_set_big_matrix_bytes(1)                 # always: the bulk-copy kernel
+        n0 = q4k.kernel_launches()
+        b = q4k.mul_mat(wd, xd).cpu().numpy()
+        assert q4k.kernel_launches() - n0 in (1, 2)           # 2: activations above the fuse limit are quantized by their own kernel
+        bq = q4k.mul_mat_q8(wd, xq).cpu().numpy()
+    finally:
+        lib.q4k_debug_set_big_matrix_bytes(34 << 20)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert np.array_equal(a.view(np.uint32), aq.view(np.uint32)) and np.array_equal(a.view(np.uint32), bq.view(np.uint32))
+    assert_close(b, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))

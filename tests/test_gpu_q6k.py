@@ -120,3 +120,27 @@ def test_bad_arguments(q4k):
     out = torch.zeros((1, 4), device="cuda")
     assert L.q6k_mul_mat(w.data_ptr() + 1, 4, 512, 420, x.data_ptr(), 1, 2048, out.data_ptr(), 16, 0, 0, 0) == -1   # odd pointer
     assert L.q6k_mul_mat(w.data_ptr(), 4, 500, 420, x.data_ptr(), 1, 2048, out.data_ptr(), 16, 0, 0, 0) == -1        # K % 256
+
+
+def test_plan_mixes_q4k_and_q6k(q4k):
+    """a graph plan holding Q4_K and Q6_K mul_mats (one Q4_K_M layer: q/k on Q4_K, v on Q6_K, all on one input) replays
+    to the same bits as the direct calls"""
+    import torch
+    from conftest import make_weights
+    K, N = 2048, 1
+    wq, wk = t(make_weights(256, K, seed=1)), t(make_weights(64, K, seed=2))
+    wv = t(make_q6(64, K, real=False))
+    wd = t(make_q6(128, 5632, seed=5, real=False))
+    x, x2 = t(make_acts(N, K)), t(make_acts(N, 5632))
+    plan = q4k.GraphPlan()
+    i0, i1 = plan.add(wq, N, 0), plan.add(wk, N, 0)
+    i2 = plan.add(wv, N, 0, q6k=True)
+    i3 = plan.add(wd, N, 1, q6k=True)
+    plan.finalize()
+    plan.input(0).copy_(x)
+    plan.input(1).copy_(x2)
+    for _ in range(2):
+        plan.run()
+    torch.cuda.synchronize()
+    for idx, ref in ((i0, q4k.mul_mat(wq, x)), (i1, q4k.mul_mat(wk, x)), (i2, q4k.mul_mat_q6k(wv, x)), (i3, q4k.mul_mat_q6k(wd, x2))):
+        assert torch.equal(plan.output(idx).view(torch.int32), ref.view(torch.int32))
