@@ -292,6 +292,98 @@ def gemv_shape_table(torch, q4k, device, shapes, steps=20):
     return out
 
 
+def tinyllama_full_token_matmuls():
+    """(name, M, K, is_q6k) of EVERY weight mul_mat of one TinyLlama-1.1B Q4_K_M decode token in graph order: the 134 Q4_K
+    ones plus attn_v / ffn_down of Q6K_LAYERS and output.weight in Q6_K (L/src/llama-quant.cpp:228-230, 302-303, 358-364)."""
+    mats = []
+    for il in range(22):
+        q6 = il in Q6K_LAYERS
+        mats += [(f"blk.{il}.attn_q", 2048, 2048, False), (f"blk.{il}.attn_k", 256, 2048, False), (f"blk.{il}.attn_v", 256, 2048, q6),
+                 (f"blk.{il}.attn_output", 2048, 2048, False), (f"blk.{il}.ffn_gate", 5632, 2048, False),
+                 (f"blk.{il}.ffn_up", 5632, 2048, False), (f"blk.{il}.ffn_down", 2048, 5632, q6)]
+    mats.append(("output", 32000, 2048, True))
+    return mats
+
+
+def rand_q6k(torch, M, K, device, gen):
+    """Random VALID block_q6_K bytes (any ql / qh / scales bytes are valid), d = 2^-8: throughput-only weights."""
+    nb = K // 256
+    w = torch.randint(0, 256, (M, nb, 210), dtype=torch.uint8, device=device, generator=gen)
+    w[..., 208] = 0x00
+    w[..., 209] = 0x1c
+    return w.view(M, nb * 210)
+
+
+def full_token_extra(torch, q4k, device, steps, no_cpu):
+    """the whole Q4_K_M token (Q4_K + Q6_K mul_mats, 155 of them) as ONE q4k_plan on the GPU, and the
+    same set on the reference's CPU backend.  Extra evidence next to the headline (which stays the 134 Q4_K mul_mats)."""
+    mats = tinyllama_full_token_matmuls()
+    gen = torch.Generator(device=device)
+    gen.manual_seed(77)
+    ids = shared_input_ids([(n, M, K) for n, M, K, _ in mats])
+    plan = q4k.GraphPlan(torch.device(device).index or 0)
+    keep, nbytes = [], 0
+    for (name, M, K, q6), iid in zip(mats, ids):
+        w = (rand_q6k if q6 else rand_q4k)(torch, M, K, device, gen)
+        keep.append(w)
+        plan.add(w, 1, iid, q6k=q6)
+        nbytes += w.numel() + K * 4 + M * 4
+    plan.finalize()
+    for iid in set(ids):
+        plan.input(iid).normal_(generator=gen)
+    ms = timed_steps(torch, plan.run, steps, 5, lambda: None) / steps
+    in_host = torch.zeros(plan.input_bytes, dtype=torch.uint8).pin_memory()
+    out_host = torch.zeros(plan.output_bytes, dtype=torch.uint8).pin_memory()
+    in_host.copy_(plan._in)
+
+    def step_host():
+        plan.run_host(in_host, out_host)
+        torch.cuda.current_stream().synchronize()
+    ms_host = timed_steps(torch, step_host, steps, 5, lambda: None) / steps
+    out = {"workload": "tinyllama-1.1b-q4_k_m decode token, every weight mul_mat: 134 Q4_K + 21 Q6_K (attn_v / ffn_down of 10 layers, output.weight)",
+           "mul_mats": len(mats), "launches_per_step": int(plan.launches), "algorithmic_bytes": nbytes,
+           "ms_per_step": round(ms, 5), "gbs": round(nbytes / ms / 1e6, 1), "decode_tok_s": round(1e3 / ms, 1),
+           "e2e": {"ms_per_step": round(ms_host, 5), "gbs": round(nbytes / ms_host / 1e6, 1), "decode_tok_s": round(1e3 / ms_host, 1),
+                   "h2d_bytes_per_step": plan.input_bytes, "d2h_bytes_per_step": plan.output_bytes}}
+    if not no_cpu:
+        try:
+            from oracle import ref
+            threads = host_threads()
+            _, mean, _ = ref.mul_mat_set_typed([(M, K, q6) for _, M, K, q6 in mats], 1, threads, 1, 10)
+            out["cpu_reference"] = {"ms_per_step": round(mean * 1e3, 3), "gbs": round(nbytes / mean / 1e9, 2), "decode_tok_s": round(1 / mean, 1),
+                                    "cores": threads, "path": "ggml_backend_cpu: ggml_vec_dot_q4_K_q8_K / ggml_vec_dot_q6_K_q8_K (AVX2), 10 iterations"}
+        except Exception as e:
+            out["cpu_reference"] = {"unavailable": str(e)}
+    del plan, keep
+    torch.cuda.empty_cache()
+    return out
+
+
+def q6k_shape_table(torch, q4k, device, shapes, steps=20):
+    """Per-shape Q6_K decode figures (q6k_mul_mat: quantizer fused), weight copies rotated through > 2 x L2."""
+    out = []
+    gen = torch.Generator(device=device)
+    gen.manual_seed(5)
+    for M, K, N in shapes:
+        wbytes = M * (K // 256) * 210
+        copies = max(2, (2 * L2_BYTES + wbytes) // wbytes + 1)
+        ws = [rand_q6k(torch, M, K, device, gen) for _ in range(copies)]
+        x = torch.randn((N, K), device=device, generator=gen)
+        dst = torch.empty((N, M), device=device)
+        wsb = torch.empty(max(16, N * (K // 256) * 292), dtype=torch.uint8, device=device)
+
+        def enqueue():
+            for w in ws:
+                q4k.mul_mat_q6k(w, x, dst, wsb)
+        g = graph_of(torch, enqueue)
+        t = timed_steps(torch, g.replay, steps, 2, lambda: None) / (steps * copies)
+        out.append({"M": M, "K": K, "N": N, "us": round(t * 1e3, 3), "gbs": round((wbytes + N * K * 4 + M * N * 4) / t / 1e6, 1),
+                    "weight_copies": copies})
+        del ws, g
+        torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ reference arm
 def host_threads():
     try:
@@ -521,6 +613,8 @@ def run_ours(args, rank, world, local_rank):
         line["shapes"] = gemv_shape_table(torch, q4k_b200, device,
                                           [(5632, 2048, 1), (4096, 14336, 1), (14336, 4096, 1), (4096, 14336, 8),
                                            (28672, 8192, 1), (8192, 28672, 1), (28672, 8192, 8)])
+        line["full_q4_k_m_token"] = full_token_extra(torch, q4k_b200, device, args.steps, args.no_cpu)
+        line["q6k_shapes"] = q6k_shape_table(torch, q4k_b200, device, [(2048, 5632, 1), (32000, 2048, 1), (14336, 4096, 1), (28672, 8192, 1)])
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

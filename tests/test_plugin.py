@@ -99,4 +99,6 @@ def test_reference_test_backend_ops_mul_mat():
     assert p.returncode == 0, clean[-2000:]
     assert not fails, fails[:5]
     assert len(q4k_ok) >= 9, clean[-2000:]          # at least the m=16, n=1..9, k=256 sweep ran on the GPU
+    q6k_ok = [l for l in clean.splitlines() if "type_a=q6_K" in l and l.rstrip().endswith("OK")]
+    assert len(q6k_ok) >= 9, clean[-2000:]          # the plugin claims MUL_MAT(Q6_K) too
     assert re.search(r"Backend Q4K_B200: OK", clean)
