@@ -36,6 +36,7 @@
 //
 // Activations (quantize_q8_planar_kernel below): the same int8 / float d that quantize_row_q8_K produces (shared
 // device function, bit-exact), int8 in tile order + float d[nb][N] + the fp16 mins tile (bh | bl).
+#include <algorithm>
 #include <cstdlib>
 
 #include <cuda.h>
@@ -71,6 +72,7 @@ constexpr uint32_t TM_A_STAGE = 64, TM_A_TILE = 32;  // columns per A stage (hi 
 constexpr uint32_t SBO_BYTES = 8 * BK;                // int8 B tile: next 8-column group of core matrices
 constexpr uint32_t LBO_BYTES = 128;                   // next 16-byte K chunk (core matrices of a group are contiguous)
 constexpr uint32_t MIN_SBO_BYTES = 256;               // mins tiles: 8 rows x (2 chunks x 16 bytes)
+constexpr size_t FLAG_BYTES = 1024;                   // split-K turnstiles at the end of the workspace (<= 148 tiles x 4 bytes)
 
 #ifdef Q4K_GEMM_TRACE
 __device__ long long g_gemm_trace[16][256];
@@ -90,6 +92,8 @@ struct GemmParams {
     int64_t N, Nld;
     float *dst;
     int64_t dst_stride;     // floats between dst columns
+    int ksplit;             // CTAs along K per output tile (gridDim.z); 1 = the tile's CTA owns all of K
+    int *flags;             // ksplit > 1: one zero-initialised turnstile word per output tile
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -238,14 +242,15 @@ __device__ __forceinline__ void tma_g2s_2d(uint32_t dst, const CUtensorMap *map,
 //   B tile of `step`        : one 16 KB bulk copy (the activations are stored pre-tiled in exactly the shared-memory order)
 //   mins tile of `sb`       : one 4 KB bulk copy                                          } with the B tile of step 2*sb
 //   raw weights of `sb`     : one TMA box, 128 rows x 144 bytes (rows past M read as zero) }
-__device__ __forceinline__ void loader_issue(const GemmParams &p, uint32_t smem0, uint32_t full, uint32_t rawfull, int m0, int64_t ntile, int step) {
-    const int kb = step >> 1, hh = step & 1;
+// `step` counts from the CTA's first superblock kb0 (split-K); slots are indexed by the local step / superblock.
+__device__ __forceinline__ void loader_issue(const GemmParams &p, uint32_t smem0, uint32_t full, uint32_t rawfull, int m0, int64_t ntile, int step, int kb0) {
+    const int kb = step >> 1, hh = step & 1, gkb = kb0 + kb;
     mbar_expect_tx(full, TILE_BYTES + (hh == 0 ? MIN_TILE_BYTES : 0));
-    bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + kb) * 2 + hh) << 14), TILE_BYTES, full);
+    bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + gkb) * 2 + hh) << 14), TILE_BYTES, full);
     if (hh == 0) {
-        bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + kb) << 12), MIN_TILE_BYTES, full);
+        bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + gkb) << 12), MIN_TILE_BYTES, full);
         mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
-        tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, &p.wmap, kb * BLK_Q4K, m0, rawfull);
+        tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, &p.wmap, gkb * BLK_Q4K, m0, rawfull);
     }
 }
 
@@ -299,7 +304,9 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
-    const int nb = p.nb, nsteps = 2 * nb;
+    // split-K: CTA z of a tile owns superblocks [kb0, kb0 + nb) (balanced contiguous parts)
+    const int kb0 = (int)((int64_t)p.nb * blockIdx.z / p.ksplit);
+    const int nb = (int)((int64_t)p.nb * (blockIdx.z + 1) / p.ksplit) - kb0, nsteps = 2 * nb;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_THREADS + 1); mbar_init(done_bar(s), 1); }
@@ -327,8 +334,10 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         uint64_t acc[2][EPI_COLS / 2];                                        // fp32 pairs
 #pragma unroll
         for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
+        wrow += (int64_t)kb0 * BLK_Q4K;
+        const float *xdk = p.xd + (int64_t)kb0 * p.Nld;
         uint32_t dd_next = *reinterpret_cast<const uint32_t *>(wrow);
-        dxw[lane] = p.xd[ncl];                                                // superblock 0 -> buffer 0
+        dxw[lane] = xdk[ncl];                                                 // superblock 0 -> buffer 0
         __syncwarp();
         const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g);
         for (int kb = 0; kb < nb; ++kb) {
@@ -336,7 +345,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             float dx_next = 0.0f;
             if (kb + 1 < nb) {
                 dd_next = *reinterpret_cast<const uint32_t *>(wrow + (int64_t)(kb + 1) * BLK_Q4K);
-                dx_next = p.xd[(int64_t)(kb + 1) * p.Nld + ncl];
+                dx_next = xdk[(int64_t)(kb + 1) * p.Nld + ncl];
             }
             const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));   // {d, dmin} of this row's superblock
             const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
@@ -370,9 +379,35 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             dxw[((kb + 1) & 1) * 32 + lane] = dx_next;                        // last read during superblock kb - 1
             __syncwarp();
         }
+        // split-K: the parts of a tile add their sums in K order through a turnstile (part z waits until z - 1 has stored),
+        // so the float result is one fixed association.  All CTAs of a split launch are co-resident (the launcher only
+        // splits while tiles x parts <= SMs), so the wait cannot deadlock.
+        const int z = blockIdx.z;
+        int *flag = p.ksplit > 1 ? p.flags + (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+        if (z > 0) {
+            if (lane == 0) {
+                int seen;
+                do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory"); } while (seen != z);
+            }
+            __syncwarp();
+        }
         if (row < p.M) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
+                if (z > 0) {     // the earlier parts' sums: all loads of a half first (independent: one L2 round trip), then the adds
+                    float prev[EPI_COLS];
+#pragma unroll
+                    for (int c = 0; c < EPI_COLS; ++c) {
+                        const int64_t n = n0 + HALF_N * h + EPI_COLS * g + c;
+                        prev[c] = n < p.N ? __ldcg(p.dst + n * p.dst_stride + row) : 0.0f;
+                    }
+#pragma unroll
+                    for (int c = 0; c < EPI_COLS / 2; ++c) {
+                        float a0, a1;
+                        unpack2(acc[h][c], a0, a1);
+                        acc[h][c] = pack2(__fadd_rn(prev[2 * c], a0), __fadd_rn(prev[2 * c + 1], a1));
+                    }
+                }
 #pragma unroll
                 for (int c = 0; c < EPI_COLS / 2; ++c) {
                     const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 2 * c;
@@ -382,6 +417,11 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                     if (n + 1 < p.N) p.dst[(n + 1) * p.dst_stride + row] = a1;
                 }
             }
+        }
+        if (p.ksplit > 1 && z + 1 < p.ksplit) {
+            __threadfence();
+            asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // all 16 epilogue warps have stored
+            if (threadIdx.x == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(flag), "r"(z + 1) : "memory");
         }
     } else if (warp < EPI_WARPS + PROD_WARPS) {
         // ===================== producers: Q4_K bytes -> A_hi / A_lo in TMEM; activations -> B slot =====================
@@ -468,7 +508,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             // slot reuse: the MMAs of step - B_SLOTS have completed, so its B slot is free; every producer had arrived for that
             // step, so the raw slot of superblock step / 2 - RAW_SLOTS has been read; the mins slots likewise
             if (step >= B_SLOTS) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar(step % B_SLOTS), (uint32_t)(((step - B_SLOTS) / B_SLOTS) & 1));
-            loader_issue(p, smem0, full_bar(step % B_SLOTS), rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, (int64_t)blockIdx.x, step);
+            loader_issue(p, smem0, full_bar(step % B_SLOTS), rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, (int64_t)blockIdx.x, step, kb0);
         }
     }
 
@@ -489,7 +529,8 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
 //   mins tile (n / 128, b):  ((n % 128) / 8) * 256 + {bh: 0, bl: 128} + (n % 8) * 16 + 2 * j
 __global__ void __launch_bounds__(256)
 quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, float *__restrict__ d, uint8_t *__restrict__ bmin,
-                          int64_t nb_per_row, int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld) {
+                          int64_t nb_per_row, int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld, int *flags) {
+    if (flags && blockIdx.x == 0) flags[threadIdx.x] = 0;        // the split-K turnstiles of the GEMM that follows (FLAG_BYTES = 256 words)
     const int lane = threadIdx.x & 31;
     const int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (blk >= nblocks_total) return;
@@ -528,7 +569,25 @@ cudaError_t launch_gemm_q4k_q8k(const void *, int64_t, int64_t, int64_t, const v
 // workspace layout of the prefill path: int8 tiles | mins tiles | float d   (q4k_mul_mat_workspace_bytes adds them up)
 size_t gemm_workspace_bytes(int64_t K, int64_t N) {
     const size_t nb = (size_t)(K / QK_K), ntiles = ((size_t)N + BN - 1) / BN;
-    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + nb * (size_t)N * 4;
+    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + ((nb * (size_t)N * 4 + 255) & ~(size_t)255) + FLAG_BYTES;
+}
+
+// How many CTAs share one output tile along K.  A launch with fewer tiles than SMs leaves the rest idle (the 32 tiles of
+// 4096 x 14336 x 32).  Measured on B200 (profiles/r1_gemm_split_k.txt): a part costs ~1.5 us per superblock, a turnstile
+// hand-off ~10 superblocks' worth (stores, fence, flag, the next part's L2 reads), so splitting pays only for long K:
+// minimise nb / s + 10 (s - 1) while all CTAs stay co-resident.  4096 x 14336 x 32: 80.7 -> 55 us at s = 2; the
+// 8- and 22-superblock TinyLlama matrices stay unsplit (28.7 vs 23.0 us at 2048 x 2048 x 512).
+static int choose_ksplit(int64_t tiles, int64_t nb) {
+    if (const char *e = getenv("Q4K_DBG_GEMM_KSPLIT")) { const int v = atoi(e); if (v >= 1) return (int)std::min<int64_t>(v, nb); }
+    const int sms = sm_count();
+    int best = 1;
+    double best_cost = (double)nb;
+    for (int s = 2; s <= 4; ++s) {
+        if (tiles * s > sms || nb / s < 4) break;
+        const double cost = (double)((nb + s - 1) / s) + 10.0 * (s - 1);
+        if (cost < best_cost - 2.0) { best_cost = cost; best = s; }
+    }
+    return best;
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
@@ -564,8 +623,12 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     int8_t *qs = reinterpret_cast<int8_t *>(workspace);
     uint8_t *bmin = reinterpret_cast<uint8_t *>(qs + ntiles * BN * K);
     float *d = reinterpret_cast<float *>(bmin + ntiles * nb * MIN_TILE_BYTES);
+    int *flags = reinterpret_cast<int *>(reinterpret_cast<char *>(d) + ((nb * (size_t)N * 4 + 255) & ~(size_t)255));
+    const int64_t mtiles = (M + BM - 1) / BM;
+    const int ksplit = choose_ksplit(ntiles * mtiles, nb);
     const int64_t total = nb * N;
-    quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, bmin, nb, total, x_row_stride_bytes, N);
+    quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, bmin, nb, total, x_row_stride_bytes, N,
+                                                                               ksplit > 1 ? flags : nullptr);
     count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
@@ -576,6 +639,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
     p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
     p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
+    p.ksplit = ksplit; p.flags = flags;
     constexpr size_t smem = SMEM_TOTAL;
     static bool attr_set = false;
     if (!attr_set) {
@@ -583,7 +647,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    const dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM));     // column tiles of one row tile run together (L2)
+    const dim3 grid((unsigned)ntiles, (unsigned)mtiles, (unsigned)ksplit);              // column tiles of one row tile run together (L2)
     gemm_q4k_tc_kernel<<<grid, GEMM_THREADS, smem, stream>>>(p);
     count_launch();
     return cudaGetLastError();

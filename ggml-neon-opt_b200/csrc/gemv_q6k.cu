@@ -63,6 +63,16 @@ struct Q6Params {
 };
 
 __device__ __forceinline__ int sx8(uint32_t w, int i) { return (int)(int8_t)(w >> (8 * i)); }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ unsigned short lds16(uint32_t a) {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+    return v;
+}
 
 template <int N, bool DUMP>
 __global__ void __launch_bounds__(Q6_WARPS * 32, 2)
@@ -135,6 +145,7 @@ gemv_q6k_kernel(const __grid_constant__ Q6Params p) {
             fence_proxy_async();                      // the warp's generic accesses of this slot are done (after __syncwarp)
             if (len) bulk_g2s(smem_u32(dstp), a, len, bar);
         }
+        __syncwarp();                                 // the tail bytes stored by lanes 0..3 are visible to the lanes that read them
         ++prod_ks;
     };
 
@@ -195,19 +206,19 @@ gemv_q6k_kernel(const __grid_constant__ Q6Params p) {
         {
             const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(p.w + rowc * p.w_stride + (int64_t)ks * Q6_PIECE) & 15u);
             const uint8_t *blk = wbuf + (size_t)s * Q6_SLOT + r * Q6_ROWP + shift + (active ? b : 0) * BLK_Q6K;
-            const uint32_t *al = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(blk) & ~(uintptr_t)3);
-            const uint32_t fs = ((uint32_t)reinterpret_cast<uintptr_t>(blk) & 3u) * 8u;     // 0 or 16
-            uint32_t prev = al[0];
+            const uint32_t sa = smem_u32(blk), al = sa & ~3u;          // explicit ld.shared: the address arithmetic hides the state space
+            const uint32_t fs = (sa & 3u) * 8u;                        // 0 or 16
+            uint32_t prev = lds32(al);
 #pragma unroll
             for (int j = 0; j < 52; ++j) {
-                const uint32_t next = al[j + 1];
+                const uint32_t next = lds32(al + 4 * (j + 1));
                 const uint32_t v = __funnelshift_r(prev, next, fs);
                 if (j < 32) ql[j] = v;
                 else if (j < 48) qh[j - 32] = v;
                 else scw[j - 48] = v;
                 prev = next;
             }
-            dw = __half2float(*reinterpret_cast<const __half *>(blk + 208));
+            dw = __half2float(__ushort_as_half(lds16(sa + 208)));
         }
         __syncwarp();
         produce(s);

@@ -159,6 +159,34 @@ def test_gemm_integer_stage_is_exact(q4k):
     assert np.array_equal(got.astype(np.int64), want) and np.array_equal(got, want.astype(np.float32))
 
 
+@pytest.mark.parametrize("ksplit", [1, 2, 3, 8])
+def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit, monkeypatch):
+    """Launches with fewer tiles than SMs split K over several CTAs per tile (turnstile epilogue: parts add in K order).
+    Same exact-float construction as above at K = 2048: any lost / doubled superblock or a race in the turnstile shows as a
+    wrong integer; two runs give identical bits."""
+    from oracle import port
+    monkeypatch.setenv("Q4K_DBG_GEMM_KSPLIT", str(ksplit))
+    rng = np.random.default_rng(11)
+    M, K, N = 200, 2048, 40
+    w = rng.integers(0, 256, (M, K // 256, 144), dtype=np.uint8)
+    w[..., 0:2] = np.frombuffer(np.float16(1.0).tobytes(), np.uint8)
+    w[..., 2:4] = np.frombuffer(np.float16(1.0).tobytes(), np.uint8)
+    w = w.reshape(M, -1)
+    x = rng.integers(-127, 128, (N, K)).astype(np.float32)
+    x[:, ::256] = -127.0
+    xq = port.quantize_q8_K(x)
+    want = np.zeros((N, M), np.int64)
+    for n in range(N):
+        for m in range(M):
+            _, si, sm = port.vec_dot_partials(w[m], xq[n])
+            want[n, m] = int(si.sum()) - int(sm.sum())
+    assert np.abs(want).max() < 2 ** 24
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    again = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    assert np.array_equal(got, want.astype(np.float32))
+    assert np.array_equal(got.view(np.uint32), again.view(np.uint32))
+
+
 def test_vec_dot_signature_bit_identical(q4k):
     import torch
     from oracle import port
