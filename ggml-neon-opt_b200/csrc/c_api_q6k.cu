@@ -2,6 +2,8 @@
 // Argument validation, column tiling, error mapping.  No CPU fallback: if the kernel cannot run, the call fails.
 #include "../../include/q4k_b200.h"
 
+#include <cstdlib>
+
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
@@ -88,7 +90,9 @@ int q6k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
     const int64_t nb = K / Q4K_QK_K;
     if (check_w(w_dev, nb, w_row_stride_bytes)) return Q4K_ERR_BAD_SHAPE;
     if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
-    if (N <= Q4K_GEMV_MAX_N && N * K <= Q6K_FUSE_LIMIT) {        // decode: quantizer fused into the launch
+    int64_t fuse_limit = Q6K_FUSE_LIMIT;
+    if (const char *e = getenv("Q6K_DBG_FUSE_LIMIT")) fuse_limit = atoll(e);      // development knob (tools/fuse_sweep.py)
+    if (N <= Q4K_GEMV_MAX_N && N * K <= fuse_limit) {             // decode: quantizer fused into the launch
         const int rc = run_columns(w_dev, M, K, w_row_stride_bytes, nullptr, x_dev, N, x_row_stride_bytes, dst_dev,
                                    dst_col_stride_bytes, nullptr, st);
         if (rc != Q4K_ERR_UNSUPPORTED) return rc;

@@ -393,7 +393,10 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     // identical bits) — it runs at the bulk-copy ceiling where the 16-row tensor-pipe tiles do not (measured on B200:
     // 28672x8192 24.1 vs 26.3 us, 8192x28672 29.3 vs 33.8 us, 8192x8192 10.3 vs 10.7 us; 4096x14336 14.7 vs 12.5 us, so
     // matrices below 34 MiB stay on the tensor-pipe kernel — profiles/r1_big_sweep.txt).
-    const bool big = N == 1 && !exact_order && stages <= 0 && g_big_matrix_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= g_big_matrix_bytes;
+    // (long K with few rows — a 4096 x 28672 shard — stays on the tensor-pipe kernel, whose cluster split-K wins there:
+    // 20.6 vs 22.4 us, profiles/r1_shard_ab_2gpu.txt; the threshold 1 = "always" of the tests skips the row rule)
+    const bool big = N == 1 && !exact_order && stages <= 0 && g_big_matrix_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= g_big_matrix_bytes &&
+                     (M >= 8192 || g_big_matrix_bytes == 1);
     if (!big && !exact_order && stages <= 0 && dbg_env("Q4K_DBG_MMA") >= 0) {      // tolerance order: the tensor-pipe kernel
         const void *wv[1] = {w};
         const int64_t Mv[1] = {M};

@@ -19,6 +19,8 @@ dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 import torch.distributed._symmetric_memory as symm  # noqa: E402
 lib = q4k_b200.load()
+if os.environ.get("BIG_BYTES"):            # A/B: threshold of the big-matrix kernel (0 = always the tensor-pipe kernel)
+    lib.q4k_debug_set_big_matrix_bytes(int(os.environ["BIG_BYTES"]))
 gname = dist.group.WORLD.group_name
 
 
