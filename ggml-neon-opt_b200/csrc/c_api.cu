@@ -49,6 +49,7 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 // q4k_debug_set_gemv_order(1)) selects the kernel that reproduces the reference's AVX2 accumulation order bit for bit
 // (gemv_q4k_tma.cu) at ~10-25% less throughput on small matrices.
 static int64_t g_fuse_limit = 16384;   // N*K floats up to which the quantizer is fused into the decode launch (measured: K = 28672 is faster with the separate quantizer)
+constexpr int64_t Q4K_GEMV_GEMM_MIN_N = 12;   // largest N served by passes of the decode kernel when the GEMM is available
 static int g_gemm_enabled = 1;          // 0: N > 8 takes the decode kernel eight columns at a time (development)
 static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
 bool gemv_exact_policy(int N);
@@ -195,8 +196,10 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
             if (e == cudaSuccess) return Q4K_OK;
             if (e != cudaErrorNotSupported) return cuda_fail(e);
         }
-        // prefill shapes: planar Q8 quantizer + tensor-core GEMM (tcgen05 kind::i8)
-        if (N > Q4K_GEMV_MAX_N && g_gemm_enabled) {
+        // prefill shapes: planar Q8 quantizer + tensor-core GEMM (tcgen05 kind::i8).  Its time does not depend on N up to a
+        // 128-column tile, so 9..12 columns are cheaper as two passes of the decode kernel (the second pass finds the
+        // weights in L2): measured at six shapes, profiles/r1_midn_sweep.txt (4096x14336 N = 9: 39 vs 49 us)
+        if (N > Q4K_GEMV_GEMM_MIN_N && g_gemm_enabled) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
             const int64_t nb = K / Q4K_QK_K;
             if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;

@@ -135,6 +135,17 @@ __device__ __forceinline__ void mbar_wait_long(uint32_t bar, uint32_t parity) {
 #ifndef Q4K_GEMM_WAIT
 #define Q4K_GEMM_WAIT 1
 #endif
+// the two waits of the accumulator hand-off (tensor core <-> epilogue) are on the critical path: a suspended wait wakes up
+// ~300 cycles after the arrive (measured), plain polling does not
+#ifndef Q4K_GEMM_WAIT_TFULL
+#define Q4K_GEMM_WAIT_TFULL 1
+#endif
+#ifndef Q4K_GEMM_WAIT_TEMPTY
+#define Q4K_GEMM_WAIT_TEMPTY 1
+#endif
+#ifndef Q4K_GEMM_DRAIN
+#define Q4K_GEMM_DRAIN 0
+#endif
 __device__ __forceinline__ uint64_t pack2(float a, float b) {
     uint64_t r;
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
@@ -245,8 +256,13 @@ __device__ __forceinline__ void tma_g2s_2d(uint32_t dst, const CUtensorMap *map,
 // `step` counts from the CTA's first superblock kb0 (split-K); slots are indexed by the local step / superblock.
 __device__ __forceinline__ void loader_issue(const GemmParams &p, uint32_t smem0, uint32_t full, uint32_t rawfull, int m0, int64_t ntile, int step, int kb0) {
     const int kb = step >> 1, hh = step & 1, gkb = kb0 + kb;
-    mbar_expect_tx(full, TILE_BYTES + (hh == 0 ? MIN_TILE_BYTES : 0));
-    bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + gkb) * 2 + hh) << 14), TILE_BYTES, full);
+#ifdef Q4K_GEMM_DBG_NOB            // timing experiment only (wrong results): the B tile is copied for the first steps only
+    const bool copy_b = step < B_SLOTS;
+#else
+    const bool copy_b = true;
+#endif
+    mbar_expect_tx(full, (copy_b ? TILE_BYTES : 0) + (hh == 0 ? MIN_TILE_BYTES : 0));
+    if (copy_b) bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + gkb) * 2 + hh) << 14), TILE_BYTES, full);
     if (hh == 0) {
         bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + gkb) << 12), MIN_TILE_BYTES, full);
         mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
@@ -351,16 +367,22 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                mbar_wait_long<Q4K_GEMM_WAIT>(tfull_bar(h), (uint32_t)(kb & 1));
+                mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (uint32_t)(kb & 1));
                 if (lane == 0 && g == 0 && qd == 0) TR(8 + 2 * h, kb);
                 tc_fence_after();
                 const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + (kb & 1) * 32 + 16 * h);
+#if Q4K_GEMM_DRAIN == 0
 #pragma unroll
                 for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
                     uint32_t vh[8], vl[8], vm[8];
                     const uint32_t ta = tbase + HALF_N * h + 8 * c8;
+#ifdef Q4K_GEMM_DBG_NOLD          // timing experiment only (wrong results): no tcgen05.ld traffic
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { vh[i] = kb + i; vl[i] = kb; vm[i] = 0; }
+#else
                     tmem_ld8(ta + TM_HI, vh); tmem_ld8(ta + TM_LO, vl); tmem_ld8(ta + TM_MIN, vm);
                     tmem_ld_wait();
+#endif
                     if (c8 == EPI_COLS / 8 - 1) {          // everything of this half is in registers: hand the columns back
                         tc_fence_before();
                         if (lane == 0 && g == 0 && qd == 0) TR(9 + 2 * h, kb);
@@ -374,6 +396,32 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                         acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
                     }
                 }
+#else
+                // The hand-back of this half's TMEM columns is on the kernel's critical path (the tensor core cannot start
+                // the next superblock's half before it: profiles/r1_gemm_trace_v5.txt), so: every load first, arithmetic
+                // after the arrive.  hi / lo are folded to sumi before the mins are loaded (register budget: 78).
+                const uint32_t ta = tbase + HALF_N * h;
+                int si[EPI_COLS];
+                {
+                    uint32_t vh[EPI_COLS], vl[EPI_COLS];
+                    tmem_ld16(ta + TM_HI, vh); tmem_ld16(ta + TM_LO, vl);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < EPI_COLS; ++i) si[i] = ((int)vh[i] << 3) + (int)vl[i];
+                }
+                uint32_t vm[EPI_COLS];
+                tmem_ld16(ta + TM_MIN, vm);
+                tmem_ld_wait();
+                tc_fence_before();
+                if (lane == 0 && g == 0 && qd == 0) TR(9 + 2 * h, kb);
+                mbar_arrive(tempty_bar(h));
+#pragma unroll
+                for (int i = 0; i < EPI_COLS / 2; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
+                    uint64_t t = mul2(d2, pack2((float)si[2 * i], (float)si[2 * i + 1]));
+                    t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
+                    acc[h][i] = fma2(dxk[i], t, acc[h][i]);
+                }
+#endif
                 if (lane == 0 && g == 0 && qd == 0) TR(12 + 2 * h, kb);
             }
             dxw[((kb + 1) & 1) * 32 + lane] = dx_next;                        // last read during superblock kb - 1
@@ -442,8 +490,13 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             if (t == 0) TR(1, step);
             tc_fence_after();
             const uint32_t ta = ta_base + (uint32_t)(step & 1) * TM_A_STAGE;
+#ifdef Q4K_GEMM_DBG_NOST           // timing experiment only (wrong results): no tcgen05.st traffic after the first steps
+            if (step < 2)
+#endif
+            {
             tmem_st16(ta, hi);
             tmem_st16(ta + TM_A_TILE, lo);
+            }
             if (hh == 0 && khalf == 0) {
                 producer_mins(smem + SMEM_AM + (kb % AM_SLOTS) * MIN_TILE_BYTES, r, sm);
                 fence_async_smem();                      // generic-proxy st.shared -> the tensor core's async proxy
@@ -474,7 +527,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                         if (lane == 0) TR(5, step);
                     }
                     if (hh == 0) {                 // new superblock: the previous one must have left this half of TMEM
-                        mbar_wait_long<Q4K_GEMM_WAIT>(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
+                        mbar_wait_long<Q4K_GEMM_WAIT_TEMPTY>(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
                         if (lane == 0) TR(6 + h, step);
                     }
                     tc_fence_after();
