@@ -164,22 +164,37 @@ gemv_q6k_kernel(const __grid_constant__ Q6Params p) {
             d_s[i] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)kb * BLK_Q8K);
         }
     } else {
-        for (int e = warp; e < N * nb; e += Q6_WARPS) {
-            const int n = e / nb, kb = e - n * nb;
-            const float4 *src = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(p.xf) + n * p.x_stride) + kb * 64;
-            const float4 f0 = src[lane], f1 = src[32 + lane];
-            const float v[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
-            uint32_t w_lo, w_hi;
-            int s_lo, s_hi;
-            const float d = quantize_block_q8_K<4>(v, lane, w_lo, w_hi, s_lo, s_hi);
-            uint8_t *dq = q8_s + (size_t)e * Q6_Q8P;
-            reinterpret_cast<uint32_t *>(dq)[lane] = w_lo;
-            reinterpret_cast<uint32_t *>(dq)[32 + lane] = w_hi;
-            if ((lane & 3) == 0) {
-                reinterpret_cast<int16_t *>(dq + 256)[lane >> 2] = (int16_t)s_lo;
-                reinterpret_cast<int16_t *>(dq + 256)[8 + (lane >> 2)] = (int16_t)s_hi;
+        // three blocks per warp in flight: all loads of a round trip before any arithmetic (the quantizer is ~1000 dependent cycles)
+        for (int e0 = warp; e0 < N * nb; e0 += 3 * Q6_WARPS) {
+            float4 f0[3], f1[3];
+#pragma unroll
+            for (int rr = 0; rr < 3; ++rr) {
+                const int e = e0 + rr * Q6_WARPS;
+                if (e < N * nb) {                                            // warp-uniform
+                    const int n = e / nb, kb = e - n * nb;
+                    const float4 *src = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(p.xf) + n * p.x_stride) + kb * 64;
+                    f0[rr] = src[lane];
+                    f1[rr] = src[32 + lane];
+                }
             }
-            if (lane == 0) d_s[e] = d;
+#pragma unroll
+            for (int rr = 0; rr < 3; ++rr) {
+                const int e = e0 + rr * Q6_WARPS;
+                if (e < N * nb) {
+                    const float v[8] = {f0[rr].x, f0[rr].y, f0[rr].z, f0[rr].w, f1[rr].x, f1[rr].y, f1[rr].z, f1[rr].w};
+                    uint32_t w_lo, w_hi;
+                    int s_lo, s_hi;
+                    const float d = quantize_block_q8_K<4>(v, lane, w_lo, w_hi, s_lo, s_hi);
+                    uint8_t *dq = q8_s + (size_t)e * Q6_Q8P;
+                    reinterpret_cast<uint32_t *>(dq)[lane] = w_lo;
+                    reinterpret_cast<uint32_t *>(dq)[32 + lane] = w_hi;
+                    if ((lane & 3) == 0) {
+                        reinterpret_cast<int16_t *>(dq + 256)[lane >> 2] = (int16_t)s_lo;
+                        reinterpret_cast<int16_t *>(dq + 256)[8 + (lane >> 2)] = (int16_t)s_hi;
+                    }
+                    if (lane == 0) d_s[e] = d;
+                }
+            }
         }
     }
     __syncthreads();
