@@ -193,7 +193,7 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     const int pseg_max = (nseg + KP - 1) / KP;            // segments of the largest part
 
     size_t off = 0;
-    uint8_t *q8_s = smem;                                   off += (size_t)p.nx * N * nb * Q8_STRIDE;
+    uint8_t *q8_s = smem;                                   off += (size_t)p.nx * N * q8_row_bytes(nb);
     uint8_t *zero_s = smem + off;                           off += Q8_STRIDE;
     float *d_s = reinterpret_cast<float *>(smem + off);     off += ((size_t)p.nx * N * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
@@ -373,17 +373,17 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
                 if (kb < nb) {
                     const uint8_t *slot_sb = slots + (size_t)s * Cfg::SLOT + warp * BLK_Q4K;
                     if constexpr (N == 1) {
-                        const uint8_t *yblk = q8_s + (size_t)(abase * nb + kb) * Q8_STRIDE;
+                        const uint8_t *yblk = q8_s + q8_off(abase, kb, nb);
                         const int j = r;                                     // this lane's B column = sub-block j
                         const uint8_t *y0 = (j == 2 * c) ? yblk + 32 * j : zero_s;
                         const uint8_t *y1 = (j == 2 * c + 1) ? yblk + 32 * j : zero_s;
                         sb_step_n1(slot_sb, y0, y1, yblk, d_s[abase * nb + kb], lane, acc, accm);
                     } else {
                         const int ncol = r;                                  // this lane's B column = batch column
-                        const uint8_t *ycol = ncol < N ? q8_s + (size_t)((abase + ncol) * nb + kb) * Q8_STRIDE : zero_s;
+                        const uint8_t *ycol = ncol < N ? q8_s + q8_off(abase + ncol, kb, nb) : zero_s;
                         const int nlo = min(2 * c, N - 1), nhi = min(2 * c + 1, N - 1);
-                        sb_step_nn<N>(slot_sb, ycol, q8_s + (size_t)((abase + nlo) * nb + kb) * Q8_STRIDE,
-                                      q8_s + (size_t)((abase + nhi) * nb + kb) * Q8_STRIDE,
+                        sb_step_nn<N>(slot_sb, ycol, q8_s + q8_off(abase + nlo, kb, nb),
+                                      q8_s + q8_off(abase + nhi, kb, nb),
                                       d_s[(abase + nlo) * nb + kb], d_s[(abase + nhi) * nb + kb], lane, acc, accm);
                     }
                 }
@@ -435,7 +435,7 @@ int mma_env(const char *name) {              // development knobs (tools/launch_
 
 size_t mma_fixed_smem(int nrows, int nb, int N, int S, int KP) {
     const int rounds = (nb + KW - 1) / KW, nseg = (rounds + SEG_ROUNDS - 1) / SEG_ROUNDS, pseg_max = (nseg + KP - 1) / KP;
-    size_t off = (size_t)nrows * nb * Q8_STRIDE + Q8_STRIDE;
+    size_t off = (size_t)nrows * q8_row_bytes(nb) + Q8_STRIDE;
     off += ((size_t)nrows * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
     off += (size_t)PBUF * KW * N * MROWS * 4 + (size_t)S * 16 + (size_t)PBUF * 16 + (size_t)XD * 16;

@@ -58,7 +58,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     const int r = lane >> 3, b = lane & 7;        // int phase: row r of the tile, superblock b; chain phase: (r, t = b)
 
     size_t off = 0;
-    uint8_t *q8_s = smem;                                  off += (size_t)p.nx * N * nb * Q8_STRIDE;
+    uint8_t *q8_s = smem;                                  off += (size_t)p.nx * N * q8_row_bytes(nb);
     float *d_s = reinterpret_cast<float *>(smem + off);    off += ((size_t)p.nx * N * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
     uint8_t *wbuf = smem + off + (size_t)warp * S * STAGE_BYTES;   off += (size_t)WARPS * S * STAGE_BYTES;
@@ -176,7 +176,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                 const int sc_lo16 = (int)((scw & 0xffu) << 4), sc_hi = (int)((scw >> 8) & 0xffu);
 #pragma unroll
                 for (int n = 0; n < N; ++n) {
-                    const uint8_t *yb = q8_s + (size_t)((abase + n) * nb + kb) * Q8_STRIDE + 64 * g;
+                    const uint8_t *yb = q8_s + q8_off(abase + n, kb, nb) + 64 * g;
                     const uint4 y0 = lds128(yb), y1 = lds128(yb + 16), y2 = lds128(yb + 32), y3 = lds128(yb + 48);
                     const uint32_t ylo[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
                     const uint32_t yhi[8] = {y2.x, y2.y, y2.z, y2.w, y3.x, y3.y, y3.z, y3.w};
@@ -205,7 +205,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
             }
 #pragma unroll
             for (int n = 0; n < N; ++n) {
-                const uint4 ps = lds128(q8_s + (size_t)((abase + n) * nb + kb) * Q8_STRIDE + 256);
+                const uint4 ps = lds128(q8_s + q8_off(abase + n, kb, nb) + 256);
                 const float yd = d_s[(abase + n) * nb + kb];
                 const float dall = __fmul_rn(yd, dd.x), dmn = __fmul_rn(-yd, dd.y);
                 // _mm_madd_epi16(mins, hadd(bsums)): prod_i = m[2i] * ps[2i] + m[2i+1] * ps[2i+1]
@@ -309,7 +309,7 @@ namespace {
 constexpr size_t SMEM_MAX = 232448;      // 227 KB per CTA on sm_100
 
 size_t fixed_smem(int nrows, int nb, bool exact, int N) {    // nrows = staged activation rows (N per distinct input)
-    size_t off = (size_t)nrows * nb * Q8_STRIDE;
+    size_t off = (size_t)nrows * q8_row_bytes(nb);
     off += ((size_t)nrows * nb * 4 + 127) & ~(size_t)127;
     off = (off + 127) & ~(size_t)127;
     off += 16;                                               // row-group counter

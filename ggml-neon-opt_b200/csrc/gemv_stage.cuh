@@ -14,6 +14,12 @@ constexpr int TILE_SB = 8;
 constexpr int ROW_BYTES = TILE_SB * BLK_Q4K;        // 1152
 constexpr int STAGE_BYTES = TILE_ROWS * ROW_BYTES;  // 4608
 constexpr int Q8_STRIDE = 272;                      // 256 qs + 8 x int16 pair sums
+// Staged activations: row (= batch column, per distinct input) `row` is nb blocks of Q8_STRIDE bytes plus a pad that
+// makes the row pitch 8 words mod 32.  Without it the pitch of the usual K (nb = 8, 16, 32, 56, 112) is 0 mod 32 banks
+// and the B-fragment loads of the tensor-pipe kernel (lane / 4 = batch column) are 4-way bank conflicts: 62% of the
+// shared-memory wavefronts of an N = 8 launch (profiles/r1_ncu_gemv_mma_n8_c5.txt).
+__host__ __device__ __forceinline__ int q8_row_bytes(int nb) { return nb * Q8_STRIDE + 4 * ((8 - (nb * (Q8_STRIDE / 4)) % 32 + 32) % 32); }
+__host__ __device__ __forceinline__ size_t q8_off(int row, int kb, int nb) { return (size_t)row * q8_row_bytes(nb) + (size_t)kb * Q8_STRIDE; }
 constexpr int SCR_ROW = 136;                        // scratch words per (column, tile row); 136 % 32 == 8
 constexpr int SCR_WORDS = TILE_ROWS * SCR_ROW;      // per column
 constexpr int WARPS = 8;
@@ -88,21 +94,43 @@ __device__ __forceinline__ uint4 lds128(const uint8_t *p) { return *reinterpret_
 template <int N>
 __device__ __forceinline__ void stage_q8(const TmaGemvParams &p, uint8_t *q8_s, float *d_s, int nt = 0, int b0 = 0, int nbw = 0) {
     if (nt == 0) nt = blockDim.x;              // nt: the first nt threads of the CTA take part
-    const int tid = threadIdx.x, nb = p.nb;
+    const int nb = p.nb, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = nt >> 5;
     if (nbw == 0) nbw = nb;
-    for (int i = tid; i < N * nbw * 64; i += nt) {
-        const int e = i >> 6, wd = i & 63, n = e / nbw, b = b0 + e - n * nbw, blk = n * nb + b;
-        const uint8_t *src = p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K;
-        reinterpret_cast<uint32_t *>(q8_s + (size_t)blk * Q8_STRIDE)[wd] = (reinterpret_cast<const uint32_t *>(src + Q8K_QS))[wd];
-    }
-    for (int i = tid; i < N * nbw * 8; i += nt) {
-        const int e = i >> 3, k = i & 7, n = e / nbw, b = b0 + e - n * nbw, blk = n * nb + b;
-        const int16_t *bs = reinterpret_cast<const int16_t *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K + Q8K_BSUMS);
-        reinterpret_cast<int16_t *>(q8_s + (size_t)blk * Q8_STRIDE + 256)[k] = (int16_t)(bs[2 * k] + bs[2 * k + 1]);   // hadd_epi16
-    }
-    for (int i = tid; i < N * nbw; i += nt) {
-        const int n = i / nbw, b = b0 + i - n * nbw;
-        d_s[n * nb + b] = *reinterpret_cast<const float *>(p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K);
+    if (warp >= nwarps) return;
+    // one warp per block, four blocks in flight per warp (all loads of a round trip first): a word-per-thread loop with
+    // an integer division per word spent 30% of an N = 8 launch here (profiles/r1_ncu_gemv_mma_n8_c5.txt)
+    constexpr int R = 4;
+    const int total = N * nbw;
+    for (int e0 = warp; e0 < total; e0 += R * nwarps) {
+        uint32_t a[R], c[R], bw[R];
+        float dd[R];
+        int blk[R], boff[R];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr) {
+            const int e = e0 + rr * nwarps;
+            blk[rr] = -1;
+            if (e < total) {                                                   // warp-uniform
+                const int n = e / nbw, b = b0 + e - n * nbw;
+                blk[rr] = n * nb + b;
+                boff[rr] = (int)q8_off(n, b, nb);
+                const uint8_t *src = p.xq + n * p.x_stride + (int64_t)b * BLK_Q8K;
+                const uint32_t *qs = reinterpret_cast<const uint32_t *>(src + Q8K_QS);
+                a[rr] = qs[lane];
+                c[rr] = qs[32 + lane];
+                bw[rr] = lane < 8 ? reinterpret_cast<const uint32_t *>(src + Q8K_BSUMS)[lane] : 0u;   // bsums 2l, 2l + 1
+                dd[rr] = lane == 8 ? *reinterpret_cast<const float *>(src) : 0.0f;
+            }
+        }
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr) {
+            if (blk[rr] >= 0) {
+                uint8_t *dst = q8_s + boff[rr];
+                reinterpret_cast<uint32_t *>(dst)[lane] = a[rr];
+                reinterpret_cast<uint32_t *>(dst)[32 + lane] = c[rr];
+                if (lane < 8) reinterpret_cast<int16_t *>(dst + 256)[lane] = (int16_t)((int16_t)(bw[rr] & 0xffffu) + (int16_t)(bw[rr] >> 16));   // hadd_epi16
+                if (lane == 8) d_s[blk[rr]] = dd[rr];
+            }
+        }
     }
 }
 
@@ -117,16 +145,18 @@ constexpr int STAGE_R = 3;
 template <int N>
 struct StageF32 {
     const float *src[STAGE_R];
-    int slot[STAGE_R];                   // shared-memory block index of the prepared blocks
+    int slot[STAGE_R];                   // shared-memory block index of the prepared blocks (d_s), its byte offset in boff
+    int boff[STAGE_R];
     int total, nwarps, nb, b0, nbw;
     const float *x0, *x1, *x2, *x3;      // the (up to four) distinct activation buffers; scalars, not an array: stays in registers
     int64_t x_stride;
 
     // e-th block of this CTA's window -> source pointer and shared-memory block index
-    __device__ __forceinline__ const float *block_src(int e, int &blk) const {
+    __device__ __forceinline__ const float *block_src(int e, int &blk, int &off) const {
         const int xs = e / (N * nbw), rem = e - xs * N * nbw, n = rem / nbw, b = b0 + rem - n * nbw;
         const float *x = xs == 0 ? x0 : (xs == 1 ? x1 : (xs == 2 ? x2 : x3));
         blk = (xs * N + n) * nb + b;
+        off = (int)q8_off(xs * N + n, b, nb);
         return reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + n * x_stride) + b * QK_K;
     }
     __device__ __forceinline__ void prepare(const TmaGemvParams &p, int nt, int win0 = 0, int win = 0) {
@@ -137,17 +167,17 @@ struct StageF32 {
 #pragma unroll
         for (int rr = 0; rr < STAGE_R; ++rr) {
             const int e = warp + rr * nwarps;
-            slot[rr] = 0;
-            src[rr] = e < total ? block_src(e, slot[rr]) : nullptr;
+            slot[rr] = 0; boff[rr] = 0;
+            src[rr] = e < total ? block_src(e, slot[rr], boff[rr]) : nullptr;
         }
     }
-    __device__ __forceinline__ void quantize_to(const float4 &a, const float4 &c, int blk, uint8_t *q8_s, float *d_s) const {
+    __device__ __forceinline__ void quantize_to(const float4 &a, const float4 &c, int blk, int off, uint8_t *q8_s, float *d_s) const {
         const int lane = threadIdx.x & 31;
         const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
         uint32_t w_lo, w_hi;
         int s_lo, s_hi;
         const float d = quantize_block_q8_K<8>(v, lane, w_lo, w_hi, s_lo, s_hi);     // s_*: the 32-element pair sums
-        uint8_t *dst = q8_s + (size_t)blk * Q8_STRIDE;
+        uint8_t *dst = q8_s + off;
         reinterpret_cast<uint32_t *>(dst)[lane] = w_lo;
         reinterpret_cast<uint32_t *>(dst)[32 + lane] = w_hi;
         if ((lane & 7) == 0) {
@@ -172,19 +202,19 @@ struct StageF32 {
 #endif
 #pragma unroll
             for (int rr = 0; rr < STAGE_R; ++rr)
-                if (src[rr]) quantize_to(a[rr], c[rr], slot[rr], q8_s, d_s);
+                if (src[rr]) quantize_to(a[rr], c[rr], slot[rr], boff[rr], q8_s, d_s);
         }
         if (total > STAGE_R * nwarps) {                                               // long activations: the rest
 #pragma unroll 1
             for (int base = warp + STAGE_R * nwarps; base < total; base += nwarps * STAGE_R) {
                 const float *sp[STAGE_R];
-                int sl[STAGE_R];
+                int sl[STAGE_R], so[STAGE_R];
                 float4 a[STAGE_R], c[STAGE_R];
 #pragma unroll
                 for (int rr = 0; rr < STAGE_R; ++rr) {
                     const int e = base + rr * nwarps;
-                    sl[rr] = 0;
-                    sp[rr] = e < total ? block_src(e, sl[rr]) : nullptr;
+                    sl[rr] = 0; so[rr] = 0;
+                    sp[rr] = e < total ? block_src(e, sl[rr], so[rr]) : nullptr;
                     if (sp[rr]) {
                         a[rr] = reinterpret_cast<const float4 *>(sp[rr])[lane];
                         c[rr] = reinterpret_cast<const float4 *>(sp[rr])[32 + lane];
@@ -192,7 +222,7 @@ struct StageF32 {
                 }
 #pragma unroll
                 for (int rr = 0; rr < STAGE_R; ++rr)
-                    if (sp[rr]) quantize_to(a[rr], c[rr], sl[rr], q8_s, d_s);
+                    if (sp[rr]) quantize_to(a[rr], c[rr], sl[rr], so[rr], q8_s, d_s);
             }
         }
     }
