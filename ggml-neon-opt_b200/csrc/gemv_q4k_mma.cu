@@ -456,7 +456,10 @@ int choose_kparts(int64_t tiles, int nb, int nrows /* staged activation rows */,
     double best_t = 1e30;
     for (int kp = 1; kp <= 4; kp *= 2) {
         if (kp > nseg) break;
-        if (kp > 1 && tiles * kp > slots) break;
+        // beyond one wave only a 2-way split for batches (>= 4 staged rows): halving the activations a CTA stages is worth more
+        // than the second wave there (measured: 4096 x 14336 N = 8 30.1 -> 25.8 us, 8192 x 28672 N = 4 62 -> 57 us; no gain
+        // at N <= 2 — profiles/r1_batch_kparts.txt)
+        if (kp > 1 && tiles * kp > slots && !(kp == 2 && nrows >= 4)) break;
         const bool two = std::min<int64_t>(tiles * kp, slots) > slots / 2;
         const int prounds = std::min(rounds, (nseg + kp - 1) / kp * SEG_ROUNDS);
         const int blocks = std::min(nb, prounds * KW) * nrows;

@@ -11,7 +11,9 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 import q4k_b200  # noqa: E402
 from gemv_sweep import graph_time_us, rand_q4k  # noqa: E402
 
-for M, K in [(5632, 2048), (4096, 14336), (14336, 4096), (28672, 8192), (8192, 28672)]:
+import os as _os
+SHAPES = [tuple(map(int, s.split("x"))) for s in _os.environ.get("SHAPES", "5632x2048,4096x14336,14336x4096,28672x8192,8192x28672").split(",")]
+for M, K in SHAPES:
     wbytes = M * (K // 256) * 144
     copies = max(2, (320 << 20) // wbytes + 1)
     w = rand_q4k(M, K, copies)
