@@ -245,6 +245,31 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 
+int q4k_mul_mat_peers_sync(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                           const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                           float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,
+                           void *workspace_dev, size_t workspace_bytes,
+                           void *const *flags_peers, int world, int rank, void *epoch_dev, void *done_dev, void *stream) {
+    if (world < 1 || world > 8 || rank < 0 || rank >= world) return Q4K_ERR_BAD_SHAPE;
+    if (!flags_peers || !epoch_dev || !done_dev) return Q4K_ERR_BAD_POINTER;
+    PeerSyncReq req;
+    for (int r = 0; r < 8; ++r) req.flags[r] = nullptr;
+    for (int r = 0; r < world; ++r) {
+        if (!flags_peers[r]) return Q4K_ERR_BAD_POINTER;
+        req.flags[r] = static_cast<uint32_t *>(flags_peers[r]);
+    }
+    req.epoch = static_cast<uint32_t *>(epoch_dev); req.done = static_cast<uint32_t *>(done_dev);
+    req.world = world; req.rank = rank; req.taken = false;
+    t_sync_req = &req;
+    const int rc = q4k_mul_mat_peers_ws(w_dev, M_local, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_peers, n_peers, dst_row0,
+                                        dst_col_stride_bytes, workspace_dev, workspace_bytes, stream);
+    t_sync_req = nullptr;
+    if (rc != Q4K_OK) return rc;
+    // no kernel carried the request (this rank owns no rows): the exchange runs as its own kernel
+    if (!req.taken) return q4k_peer_signal_wait(flags_peers, world, rank, epoch_dev, stream);
+    return Q4K_OK;
+}
+
 int q4k_mul_mat_peers(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
                       const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
                       float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes, void *stream) {

@@ -332,6 +332,7 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
             }
             if (++xs == XD) { xs = 0; xparity ^= 1u; cparity ^= 1u; }
         }
+        if (p.sync_world > 0) peer_sync_tail(p, lane);        // row-sharded multi-GPU: the cross-GPU step, fused
         return;
     }
 
@@ -526,6 +527,7 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
     cfg.numAttrs = na;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
+    if (e == cudaSuccess && p.sync_world > 0 && t_sync_req) t_sync_req->taken = true;
     return e;
 }
 
@@ -549,6 +551,7 @@ cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M
     p.dst_row0 = dst_row0;
     p.dst_stride = dst_col_stride_bytes > 0 ? dst_col_stride_bytes / 4 : M[0];      // 0 = dense [N][M]
     p.stages = 0; p.nmat = nmat; p.nx = 0;
+    fill_sync(p, nmat == 1 ? n_peers : 0);
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     int64_t tiles = 0;
     for (int i = 0; i < nmat; ++i) {

@@ -38,6 +38,8 @@
 
 namespace q4k {
 
+thread_local PeerSyncReq *t_sync_req = nullptr;
+
 int64_t g_big_matrix_bytes = (int64_t)34 << 20;   // q4k_debug_set_big_matrix_bytes; <= 0: never (crossover measured: profiles/r1_big_sweep.txt)
 
 namespace {
@@ -71,7 +73,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     // back, which HBM likes better than 296 separate streams (measured on the tensor-pipe and the Q6_K kernels: +10-25%)
     const int ksteps = (nb + TILE_SB - 1) / TILE_SB;
 
-    if (threadIdx.x == 0) *counter = 0;
+    if (threadIdx.x == 0) { counter[0] = 0; counter[1] = 0; }     // [0] row groups handed out, [1] warps that have finished (fused peer sync)
     if (lane == 0) {
         for (int s = 0; s < S; ++s) mbar_init(smem_u32(&bars[s]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -300,6 +302,17 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
         }
         if (++s == S) { s = 0; parity ^= 1u; }
     }
+    if (p.sync_world > 0) {          // row-sharded multi-GPU: the cross-GPU step, fused; the CTA's last warp carries it
+        __syncwarp();
+        int lastw = 0;
+        if (lane == 0) {
+            __threadfence_block();                                       // this warp's stores before its arrival (CTA scope: cheap)
+            lastw = atomicAdd(&counter[1], 1) == WARPS - 1;
+            __threadfence_block();
+        }
+        lastw = __shfl_sync(0xffffffffu, lastw, 0);
+        if (lastw) peer_sync_tail(p, lane);
+    }
 }
 
 }  // namespace
@@ -360,6 +373,7 @@ cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_
     cfg.numAttrs = pdl ? 1 : 0;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
+    if (e == cudaSuccess && p.sync_world > 0 && t_sync_req) t_sync_req->taken = true;
     return e;
 }
 
@@ -417,6 +431,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.n_groups = (M + TILE_ROWS - 1) / TILE_ROWS;
     p.stages = 0; p.interleave = 0; p.kparts = 1;
     p.nmat = 1; p.nx = 1;
+    fill_sync(p, n_peers);
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
     if (big) {
@@ -450,6 +465,7 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
     for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
     p.dst[0] = dst[0]; p.n_dst = 1; p.dst_row0 = 0; p.dst_stride = M[0];
     p.stages = 0; p.interleave = 0; p.kparts = 1; p.nmat = nmat; p.nx = 0;
+    fill_sync(p, 0);
     int64_t groups = 0;
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     for (int i = 0; i < nmat; ++i) {

@@ -4,6 +4,7 @@
 #pragma once
 
 #include "q4k_common.cuh"
+#include "q4k_kernels.h"
 
 namespace q4k {
 
@@ -47,7 +48,22 @@ struct TmaGemvParams {
     float *dstm[4];
     const float *xsrc[4];   // the nx distinct F32 activation buffers; xslot[i] = which one matrix i reads
     int xslot[4];
+    // fused cross-GPU step of the row-sharded path (q4k_mul_mat_peers_sync): sync_world > 0 = the last CTA of the launch
+    // publishes this rank's epoch into every peer's flag row and waits for theirs (peer_sync_tail)
+    uint32_t *sync_flags[8];
+    uint32_t *sync_epoch, *sync_done;
+    int sync_world, sync_rank;
 };
+
+inline void fill_sync(TmaGemvParams &p, int n_peers) {
+    for (int r = 0; r < 8; ++r) p.sync_flags[r] = nullptr;
+    p.sync_epoch = p.sync_done = nullptr; p.sync_world = 0; p.sync_rank = 0;
+    if (t_sync_req && !t_sync_req->taken && n_peers > 0) {
+        for (int r = 0; r < 8; ++r) p.sync_flags[r] = t_sync_req->flags[r];
+        p.sync_epoch = t_sync_req->epoch; p.sync_done = t_sync_req->done;
+        p.sync_world = t_sync_req->world; p.sync_rank = t_sync_req->rank;
+    }
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -233,6 +249,45 @@ __device__ __forceinline__ void stage_f32(const TmaGemvParams &p, uint8_t *q8_s,
     StageF32<N> st;
     st.prepare(p, nt == 0 ? blockDim.x : nt);
     st.run(q8_s, d_s);
+}
+
+// The cross-GPU step fused into the decode launch (what q4k_peer_signal_wait does in a kernel of its own, peer_sync.cu).
+// Called by ONE full warp per CTA after all of the CTA's result stores (to every peer, over NVLink) have been issued and
+// fenced.  The last CTA of the grid to arrive bumps the device-side epoch, publishes it with a system-scope release store
+// into every peer's flag row and spins until every peer's epoch has arrived here: when the kernel completes, every rank's
+// rows have landed in this rank's output buffer.  Saves the dependent launch of the separate signal kernel (~2.5 us).
+__device__ __forceinline__ void peer_sync_tail(const TmaGemvParams &p, int lane) {
+    // One GPU-scope fence per CTA in front of its arrival; the ONE system-scope fence + release is the last CTA's (causality
+    // is transitive: stores -> warp / CTA synchronisation -> this fence -> arrival -> the last CTA's fence.sys -> flag).
+    // System-scope fences in every CTA (or worse, every lane) wait for the NVLink acknowledgements 296 times over and cost
+    // 8-13 us per launch (profiles/r1_shard_timing_fused_2gpu.txt).
+    __syncwarp();
+    int last = 0;
+    if (lane == 0) {
+        __threadfence();
+        last = atomicAdd(p.sync_done, 1u) == gridDim.x - 1u;
+    }
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    uint32_t e = 0;
+    if (lane == 0) {
+        __threadfence_system();                                // acquire side of the other CTAs' arrivals
+        *p.sync_done = 0u;                                     // everybody has arrived: ready for the next launch
+        e = *p.sync_epoch + 1u;
+        *p.sync_epoch = e;
+    }
+    __syncwarp();
+    e = __shfl_sync(0xffffffffu, e, 0);
+    if (lane < p.sync_world && lane != p.sync_rank) {
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.sync_flags[lane] + p.sync_rank), "r"(e) : "memory");
+        const uint32_t *mine = p.sync_flags[p.sync_rank] + lane;
+        uint32_t seen;
+        do {
+            asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+        } while ((int32_t)(seen - e) < 0);                     // wrap-safe "seen >= e"
+    }
+    __syncwarp();
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
 
 // Reads one field of every 64-byte piece of the launch parameters: the first access to a kernel's constant bank misses

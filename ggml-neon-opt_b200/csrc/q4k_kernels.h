@@ -58,6 +58,16 @@ cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride
                                   const void *xq, int64_t N, int64_t xq_row_stride_bytes,
                                   int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);
 
+// request handed from the C ABI (q4k_mul_mat_peers_sync) to whichever launcher ends up launching the single decode kernel
+// of the call: the kernel's last CTA then performs the cross-GPU flag exchange itself (gemv_stage.cuh peer_sync_tail)
+struct PeerSyncReq {
+    uint32_t *flags[8];     // every rank's flag row (peer-mapped), indexed by rank
+    uint32_t *epoch, *done; // this rank's call counter and CTA arrival counter (device memory, zero-initialised)
+    int world, rank;
+    bool taken;             // set by the launcher once a kernel carrying the request has been launched
+};
+extern thread_local PeerSyncReq *t_sync_req;
+
 extern int g_gemv_config;   // development knob, see gemv_q4k.cu
 extern int64_t g_big_matrix_bytes;   // N == 1 launches with at least this many weight bytes take the bulk-copy kernel (gemv_q4k_tma.cu, ORD 2)
 extern int g_gemv_pdl;      // 1 = launch the GEMV with programmatic stream serialization (default)

@@ -56,6 +56,7 @@ def load():
         L.q4k_mul_mat_peers.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp]
         L.q4k_peer_signal_wait.argtypes = [vp, i32, i32, vp, vp]
         L.q4k_mul_mat_peers_ws.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp, sz, vp]
+        L.q4k_mul_mat_peers_sync.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp, sz, vp, i32, i32, vp, vp, vp]
         L.q4k_mul_mat_group.argtypes = [i32, vp, vp, i64, i64, vp, i64, i64, vp, vp]
         L.q4k_plan_create.argtypes = [i32]
         L.q4k_plan_create.restype = vp

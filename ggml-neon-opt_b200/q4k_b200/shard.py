@@ -23,6 +23,8 @@ with world_size-2 gloo on CPU tensors in tests/test_shard.py.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -133,6 +135,12 @@ class RowShardedQ4K:
         self._flag_arr = (C.c_void_p * self.world)(*list(self._fhdl.buffer_ptrs))
         self._flags.zero_()
         self._epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._done = torch.zeros(1, dtype=torch.int32, device=dev)           # CTA arrival counter of the fused cross-GPU step
+        # Q4K_SHARD_FUSED_SYNC=1: the flag exchange fused into the decode launch (q4k_mul_mat_peers_sync) instead of the one-warp
+        # kernel of its own.  Bit-equal, but measured SLOWER on B200 (2 GPUs: 25.3 vs 20.9 us per call at 14336x8192 per rank,
+        # profiles/r1_shard_timing_fused_2gpu.txt): a fence in front of every CTA's arrival waits for that CTA's NVLink
+        # stores, while the kernel boundary + a programmatically pre-launched one-warp kernel costs 5 us in all.  Off by default.
+        self.fused_sync = os.environ.get("Q4K_SHARD_FUSED_SYNC", "0") == "1"
         torch.cuda.synchronize(dev)
         self._hdl.barrier(channel=0)
         self._fhdl.barrier(channel=0)
@@ -146,9 +154,17 @@ class RowShardedQ4K:
         if self.gather == "peer" and N <= self.max_n:
             b = self._flip
             self._flip ^= 1
+            if self._ws is None or self._ws.numel() < self._lib.workspace_bytes(self.K, N):
+                self._ws = torch.empty(max(self._lib.workspace_bytes(self.K, self.max_n), 16), dtype=torch.uint8, device=self.w.device)
+            if self.fused_sync:
+                # compute + all-gather (peer stores) + cross-GPU flag exchange in ONE launch
+                rc = lib.q4k_mul_mat_peers_sync(self.w.data_ptr(), self.r1 - self.r0, self.K, self.w.stride(0), x.data_ptr(), N, x.stride(0) * 4,
+                                                self._peer_arr[b], self.world, self.r0, self.M * 4, self._ws.data_ptr(), self._ws.numel(),
+                                                self._flag_arr, self.world, self.rank, self._epoch.data_ptr(), self._done.data_ptr(), st)
+                if rc != 0:
+                    raise self._lib.Q4KError("q4k_mul_mat_peers_sync", rc, lib.q4k_last_cuda_error())
+                return self._out[b, :N]
             if self.r1 > self.r0:
-                if self._ws is None or self._ws.numel() < self._lib.workspace_bytes(self.K, N):
-                    self._ws = torch.empty(max(self._lib.workspace_bytes(self.K, self.max_n), 16), dtype=torch.uint8, device=self.w.device)
                 rc = lib.q4k_mul_mat_peers_ws(self.w.data_ptr(), self.r1 - self.r0, self.K, self.w.stride(0), x.data_ptr(), N, x.stride(0) * 4,
                                               self._peer_arr[b], self.world, self.r0, self.M * 4, self._ws.data_ptr(), self._ws.numel(), st)
                 if rc != 0:

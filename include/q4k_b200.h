@@ -96,6 +96,18 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
                          float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,
                          void *workspace_dev, size_t workspace_bytes, void *stream);
 
+/* q4k_mul_mat_peers_ws + the cross-GPU step in ONE kernel: the decode kernel's last CTA publishes this rank's epoch into
+ * every peer's flag row and waits for theirs, so when the launch completes every rank's rows have landed in this rank's
+ * buffer — compute, all-gather and barrier in one launch.  Measured on B200 it is SLOWER than q4k_mul_mat_peers_ws followed by
+ * q4k_peer_signal_wait (2 GPUs, 14336x8192 per rank: 25.3 vs 20.9 us per call): kept as an option, not the default.  flags_peers
+ * / world / rank / epoch_dev as for q4k_peer_signal_wait; done_dev = one more zero-initialised uint32 in this rank's
+ * device memory (CTA arrival counter).  Falls back to a separate q4k_peer_signal_wait launch when this rank owns no rows. */
+int q4k_mul_mat_peers_sync(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                           const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                           float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,
+                           void *workspace_dev, size_t workspace_bytes,
+                           void *const *flags_peers, int world, int rank, void *epoch_dev, void *done_dev, void *stream);
+
 /* the cross-GPU step after q4k_mul_mat_peers: "all ranks' result stores have landed everywhere".  flags_peers[r] = the
  * peer-mapped pointer to rank r's flag buffer (world x uint32, zero-initialised once, same symmetric allocation on every
  * rank), epoch_dev = a zero-initialised uint32 in this rank's device memory.  One small kernel: bumps the epoch, publishes

@@ -80,10 +80,16 @@ for (M, K) in [(28672, 8192), (8192, 28672)]:
         f_peers(i)
         assert lib.q4k_peer_signal_wait(farr, world, rank, epoch.data_ptr(), st()) == 0
 
+    done = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def f_fused(i):        # compute + peer stores + flag exchange in ONE launch
+        assert lib.q4k_mul_mat_peers_sync(w[i % copies].data_ptr(), m, K, nb * 144, x.data_ptr(), 1, K * 4, parr[i & 1], world, r0, M * 4,
+                                          ws.data_ptr(), ws.numel(), farr, world, rank, epoch.data_ptr(), done.data_ptr(), st()) == 0
+
     def f_sig(i):
         assert lib.q4k_peer_signal_wait(farr, world, rank, epoch.data_ptr(), st()) == 0
 
-    res = dict(local=timed(f_local), peers_kernel_local_dst=timed(f_one), peers_no_sync=timed(f_peers), peers_and_signal=timed(f_full), signal_only=timed(f_sig))
+    res = dict(local=timed(f_local), peers_kernel_local_dst=timed(f_one), peers_no_sync=timed(f_peers), peers_and_signal=timed(f_full), fused_sync=timed(f_fused), signal_only=timed(f_sig))
     if rank == 0:
         print(f"M={M} K={K} world={world} rows/rank={m}: " + ", ".join(f"{k} {v:.2f} us" for k, v in res.items()), flush=True)
     dist.barrier()
