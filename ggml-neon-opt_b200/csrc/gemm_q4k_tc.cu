@@ -254,7 +254,13 @@ __device__ __forceinline__ void tma_g2s_2d(uint32_t dst, const CUtensorMap *map,
 //   mins tile of `sb`       : one 4 KB bulk copy                                          } with the B tile of step 2*sb
 //   raw weights of `sb`     : one TMA box, 128 rows x 144 bytes (rows past M read as zero) }
 // `step` counts from the CTA's first superblock kb0 (split-K); slots are indexed by the local step / superblock.
-__device__ __forceinline__ void loader_issue(const GemmParams &p, uint32_t smem0, uint32_t full, uint32_t rawfull, int m0, int64_t ntile, int step, int kb0) {
+// The raw weights do not depend on the quantizer kernel in front of this one (programmatic dependent launch), the B and
+// mins tiles do: the loader issues the first raw boxes before griddepcontrol.wait.
+__device__ __forceinline__ void loader_issue_raw(const GemmParams &p, uint32_t smem0, uint32_t rawfull, int m0, int kb, int kb0) {
+    mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
+    tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, &p.wmap, (kb0 + kb) * BLK_Q4K, m0, rawfull);
+}
+__device__ __forceinline__ void loader_issue_act(const GemmParams &p, uint32_t smem0, uint32_t full, int64_t ntile, int step, int kb0) {
     const int kb = step >> 1, hh = step & 1, gkb = kb0 + kb;
 #ifdef Q4K_GEMM_DBG_NOB            // timing experiment only (wrong results): the B tile is copied for the first steps only
     const bool copy_b = step < B_SLOTS;
@@ -263,11 +269,7 @@ __device__ __forceinline__ void loader_issue(const GemmParams &p, uint32_t smem0
 #endif
     mbar_expect_tx(full, (copy_b ? TILE_BYTES : 0) + (hh == 0 ? MIN_TILE_BYTES : 0));
     if (copy_b) bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + gkb) * 2 + hh) << 14), TILE_BYTES, full);
-    if (hh == 0) {
-        bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + gkb) << 12), MIN_TILE_BYTES, full);
-        mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
-        tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, &p.wmap, gkb * BLK_Q4K, m0, rawfull);
-    }
+    if (hh == 0) bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + gkb) << 12), MIN_TILE_BYTES, full);
 }
 
 // the thread's 64 weights of this step (one 32-byte group of its raw row: low nibbles = sub-block 2j, high nibbles
@@ -320,6 +322,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     // split-K: CTA z of a tile owns superblocks [kb0, kb0 + nb) (balanced contiguous parts)
     const int kb0 = (int)((int64_t)p.nb * blockIdx.z / p.ksplit);
     const int nb = (int)((int64_t)p.nb * (blockIdx.z + 1) / p.ksplit) - kb0, nsteps = 2 * nb;
@@ -353,6 +356,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         wrow += (int64_t)kb0 * BLK_Q4K;
         const float *xdk = p.xd + (int64_t)kb0 * p.Nld;
         uint32_t dd_next = *reinterpret_cast<const uint32_t *>(wrow);
+        asm volatile("griddepcontrol.wait;" ::: "memory");      // xd is written by the quantizer kernel in front of this one
         dxw[lane] = xdk[ncl];                                                 // superblock 0 -> buffer 0
         __syncwarp();
         const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g);
@@ -557,11 +561,15 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     } else if (lane == 0) {
         // ===================== loader (one thread): TMA copies, up to B_SLOTS steps ahead of the tensor core =====================
         const uint32_t smem0 = smem_addr(smem);
+        const int pre = min(nb, RAW_SLOTS);                     // raw boxes that can go out before the quantizer has finished
+        for (int kb = 0; kb < pre; ++kb) loader_issue_raw(p, smem0, rawfull_bar(kb % RAW_SLOTS), (int)m0, kb, kb0);
+        asm volatile("griddepcontrol.wait;" ::: "memory");      // the activation tiles come from the kernel in front of this one
         for (int step = 0; step < nsteps; ++step) {
             // slot reuse: the MMAs of step - B_SLOTS have completed, so its B slot is free; every producer had arrived for that
             // step, so the raw slot of superblock step / 2 - RAW_SLOTS has been read; the mins slots likewise
             if (step >= B_SLOTS) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar(step % B_SLOTS), (uint32_t)(((step - B_SLOTS) / B_SLOTS) & 1));
-            loader_issue(p, smem0, full_bar(step % B_SLOTS), rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, (int64_t)blockIdx.x, step, kb0);
+            if ((step & 1) == 0 && (step >> 1) >= pre) loader_issue_raw(p, smem0, rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, step >> 1, kb0);
+            loader_issue_act(p, smem0, full_bar(step % B_SLOTS), (int64_t)blockIdx.x, step, kb0);
         }
     }
 
@@ -583,6 +591,10 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
 __global__ void __launch_bounds__(256)
 quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, float *__restrict__ d, uint8_t *__restrict__ bmin,
                           int64_t nb_per_row, int64_t nblocks_total, int64_t x_row_stride_bytes, int64_t Nld, int *flags) {
+    // programmatic dependent launch on both sides: this kernel overwrites the workspace the GEMM in front of it may still be
+    // reading, so everything waits for that; the GEMM behind it may start its prologue (barriers, TMEM, raw weights) now
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (flags && blockIdx.x == 0) flags[threadIdx.x] = 0;        // the split-K turnstiles of the GEMM that follows (FLAG_BYTES = 256 words)
     const int lane = threadIdx.x & 31;
     const int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -680,11 +692,22 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     const int64_t mtiles = (M + BM - 1) / BM;
     const int ksplit = choose_ksplit(ntiles * mtiles, nb);
     const int64_t total = nb * N;
-    quantize_q8_planar_kernel<<<(unsigned)((total + 7) / 8), 256, 0, stream>>>(x, qs, d, bmin, nb, total, x_row_stride_bytes, N,
-                                                                               ksplit > 1 ? flags : nullptr);
-    count_launch();
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    cudaLaunchAttribute pdl_attr[1];
+    pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaError_t e;
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)((total + 7) / 8));
+        cfg.blockDim = dim3(256);
+        cfg.stream = stream;
+        cfg.attrs = pdl_attr;
+        cfg.numAttrs = g_gemv_pdl ? 1 : 0;
+        int *qflags = ksplit > 1 ? flags : nullptr;
+        e = cudaLaunchKernelEx(&cfg, quantize_q8_planar_kernel, x, qs, d, bmin, nb, total, x_row_stride_bytes, N, qflags);
+        count_launch();
+        if (e != cudaSuccess) return e;
+    }
 
     GemmParams p;
     e = make_weight_map(&p.wmap, w, M, nb, w_row_stride_bytes);
@@ -701,9 +724,16 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
         attr_set = true;
     }
     const dim3 grid((unsigned)ntiles, (unsigned)mtiles, (unsigned)ksplit);              // column tiles of one row tile run together (L2)
-    gemm_q4k_tc_kernel<<<grid, GEMM_THREADS, smem, stream>>>(p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cfg.attrs = pdl_attr;
+    cfg.numAttrs = g_gemv_pdl ? 1 : 0;
+    e = cudaLaunchKernelEx(&cfg, gemm_q4k_tc_kernel, p);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 }  // namespace q4k

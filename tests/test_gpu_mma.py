@@ -120,3 +120,39 @@ def test_big_matrix_kernel_gives_the_tensor_pipe_kernels_bits(q4k, M, K):
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
     assert np.array_equal(a.view(np.uint32), aq.view(np.uint32)) and np.array_equal(a.view(np.uint32), bq.view(np.uint32))
     assert_close(b, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+
+
+@pytest.mark.parametrize("big", [0, 1])
+def test_fused_peer_sync_single_rank(q4k, big):
+    """q4k_mul_mat_peers_sync with world = 1: the decode kernel carries the cross-GPU step (last CTA: epoch bump, flag
+    publish / wait over zero peers).  Results equal q4k_mul_mat bit for bit, the epoch counts the calls, the CTA arrival
+    counter is back at zero — on both decode kernels (big = 1 forces the bulk-copy kernel).  The real exchange runs in
+    tools/shard_check.py on 2 / 4 / 8 GPUs."""
+    import ctypes as C
+    import torch
+    lib = q4k.load()
+    M, K = 300, 2048
+    w, x = t(make_weights(M, K, seed=3)), t(make_acts(1, K))
+    want = q4k.mul_mat(w, x)
+    out = torch.zeros((1, M), device="cuda")
+    flags = torch.zeros(64, dtype=torch.int32, device="cuda")
+    epoch = torch.zeros(1, dtype=torch.int32, device="cuda")
+    done = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ws = torch.empty(max(q4k.workspace_bytes(K, 1), 16), dtype=torch.uint8, device="cuda")
+    peers = (C.c_void_p * 1)(out.data_ptr())
+    farr = (C.c_void_p * 1)(flags.data_ptr())
+    st = torch.cuda.current_stream().cuda_stream
+    try:
+        lib.q4k_debug_set_big_matrix_bytes(1 if big else 0)
+        for i in range(3):
+            out.zero_()
+            n0 = q4k.kernel_launches()
+            rc = lib.q4k_mul_mat_peers_sync(w.data_ptr(), M, K, w.stride(0), x.data_ptr(), 1, K * 4, peers, 1, 0, M * 4,
+                                            ws.data_ptr(), ws.numel(), farr, 1, 0, epoch.data_ptr(), done.data_ptr(), st)
+            assert rc == 0
+            assert q4k.kernel_launches() == n0 + 1                      # one launch: no separate signal kernel
+            torch.cuda.synchronize()
+            assert torch.equal(out.view(torch.int32), want.view(torch.int32))
+            assert int(epoch.item()) == i + 1 and int(done.item()) == 0
+    finally:
+        lib.q4k_debug_set_big_matrix_bytes(34 << 20)
