@@ -326,6 +326,9 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     // split-K: CTA z of a tile owns superblocks [kb0, kb0 + nb) (balanced contiguous parts)
     const int kb0 = (int)((int64_t)p.nb * blockIdx.z / p.ksplit);
     const int nb = (int)((int64_t)p.nb * (blockIdx.z + 1) / p.ksplit) - kb0, nsteps = 2 * nb;
+    // column halves of this tile that hold real columns: a tile with <= 64 of them (N <= 64, or the ragged last tile) runs
+    // half the MMAs and half the epilogue
+    const int nh = n0 + HALF_N < p.N ? 2 : 1;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_THREADS + 1); mbar_init(done_bar(s), 1); }
@@ -371,6 +374,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
+                if (h >= nh) break;
                 mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (uint32_t)(kb & 1));
                 if (lane == 0 && g == 0 && qd == 0) TR(8 + 2 * h, kb);
                 tc_fence_after();
@@ -446,6 +450,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         if (row < p.M) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
+                if (h >= nh) break;
                 if (z > 0) {     // the earlier parts' sums: all loads of a half first (independent: one L2 round trip), then the adds
                     float prev[EPI_COLS];
 #pragma unroll
@@ -522,6 +527,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         for (int kb = 0; kb < nb; ++kb) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
+                if (h >= nh) break;
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     const int step = 2 * kb + hh, bslot = step % B_SLOTS;
@@ -552,7 +558,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                             umma_f16_ss(tm + TM_MIN + h * HALF_N, a_desc, b_desc, idesc_min, 0u);
                             umma_commit(tfull_bar(h));
                         }
-                        if (h == 1) umma_commit(done_bar(bslot));   // A stage and B slot consumed by both halves -> producers
+                        if (h == nh - 1) umma_commit(done_bar(bslot));   // A stage and B slot consumed by every half -> producers
                     }
                     __syncwarp();
                 }
