@@ -42,6 +42,18 @@ struct q4k_plan {
     cudaGraphExec_t exec = nullptr;
     int64_t launches = 0;
     bool finalized = false;
+    // host-buffer replay (q4k_plan_run_host) as a copy / compute pipeline: the items cut into parts, one CUDA graph per part;
+    // part p's inputs go up and part p - 1's results come down on a side stream while part p computes
+    struct Part {
+        size_t begin, end;                 // items [begin, end)
+        size_t in_off, in_len, out_off, out_len;
+        cudaGraph_t graph;
+        cudaGraphExec_t exec;
+    };
+    std::vector<Part> parts;
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_join = nullptr;
+    std::vector<cudaEvent_t> ev_in, ev_out;
 
     const Input *find_input(int id) const {
         for (const auto &in : inputs) if (in.id == id) return &in;
@@ -53,14 +65,14 @@ namespace {
 
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
-// enqueue every launch of the plan on `st` (used once, under stream capture)
-int enqueue_all(q4k_plan *p, cudaStream_t st) {
-    size_t i = 0;
-    while (i < p->items.size()) {
+// enqueue the launches of items [begin, end) on `st` (used under stream capture)
+int enqueue_range(q4k_plan *p, cudaStream_t st, size_t begin, size_t end) {
+    size_t i = begin;
+    while (i < end) {
         const q4k_plan::Item &a = p->items[i];
         size_t j = i + 1;
         if (a.N <= Q4K_GEMV_MAX_N && !a.q6) {
-            while (j < p->items.size() && j - i < 4 && !p->items[j].q6 && p->items[j].input_id == a.input_id && p->items[j].K == a.K &&
+            while (j < end && j - i < 4 && !p->items[j].q6 && p->items[j].input_id == a.input_id && p->items[j].K == a.K &&
                    p->items[j].N == a.N && p->items[j].w_stride == a.w_stride) ++j;
         }
         const q4k_plan::Input *in = p->find_input(a.input_id);
@@ -89,6 +101,66 @@ int enqueue_all(q4k_plan *p, cudaStream_t st) {
             }
         }
         i = j;
+    }
+    return Q4K_OK;
+}
+
+int enqueue_all(q4k_plan *p, cudaStream_t st) { return enqueue_range(p, st, 0, p->items.size()); }
+
+// Cut the items into up to `want` parts of about equal result bytes, only where the input changes (a fused group is never
+// split), capture one graph per part and note the byte ranges of the packed buffers each part owns: results are packed in
+// item order, inputs in order of first use, so both are contiguous per part.
+int build_parts(q4k_plan *p, cudaStream_t cs, int want) {
+    const size_t n = p->items.size();
+    if (n < 8 || want < 2) return Q4K_OK;
+    // four parts of about equal result bytes (a small first / last part — less exposed copy — measured no better: the host
+    // then cannot enqueue the second graph before the first has finished)
+    static const double frac[4] = {0.25, 0.5, 0.75, 2.0};
+    (void)want;
+    std::vector<size_t> cuts{0};
+    size_t acc = 0;
+    for (size_t i = 0; i < n; ++i) {
+        if (i > 0 && p->items[i].input_id != p->items[i - 1].input_id && cuts.size() <= 4 &&
+            (double)acc >= frac[cuts.size() - 1] * (double)p->out_bytes) cuts.push_back(i);
+        acc += ((size_t)p->items[i].N * p->items[i].M * 4 + 255) & ~(size_t)255;
+    }
+    cuts.push_back(n);
+    if (cuts.size() < 3) return Q4K_OK;
+    std::vector<char> seen(p->inputs.size(), 0);
+    for (size_t c = 0; c + 1 < cuts.size(); ++c) {
+        q4k_plan::Part part{};
+        part.begin = cuts[c]; part.end = cuts[c + 1];
+        part.out_off = p->items[part.begin].out_off;
+        part.out_len = (part.end < n ? p->items[part.end].out_off : p->out_bytes) - part.out_off;
+        size_t lo = (size_t)-1, hi = 0;
+        for (size_t i = part.begin; i < part.end; ++i) {
+            for (size_t k = 0; k < p->inputs.size(); ++k) {
+                if (p->inputs[k].id != p->items[i].input_id || seen[k]) continue;
+                seen[k] = 1;
+                const size_t o = p->inputs[k].off, e = o + (((size_t)p->inputs[k].N * p->inputs[k].K * 4 + 255) & ~(size_t)255);
+                if (o < lo) lo = o;
+                if (e > hi) hi = e;
+            }
+        }
+        part.in_off = lo == (size_t)-1 ? 0 : lo;
+        part.in_len = lo == (size_t)-1 ? 0 : hi - lo;
+        cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+        if (e != cudaSuccess) return q4k::note_cuda_error(e);
+        const int rc = enqueue_range(p, cs, part.begin, part.end);
+        e = cudaStreamEndCapture(cs, &part.graph);
+        if (rc != Q4K_OK || e != cudaSuccess) return rc != Q4K_OK ? rc : q4k::note_cuda_error(e);
+        if ((e = cudaGraphInstantiate(&part.exec, part.graph, 0)) != cudaSuccess) return q4k::note_cuda_error(e);
+        p->parts.push_back(part);
+    }
+    cudaError_t e = cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return q4k::note_cuda_error(e);
+    cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
+    p->ev_in.resize(p->parts.size());
+    p->ev_out.resize(p->parts.size());
+    for (size_t c = 0; c < p->parts.size(); ++c) {
+        cudaEventCreateWithFlags(&p->ev_in[c], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&p->ev_out[c], cudaEventDisableTiming);
     }
     return Q4K_OK;
 }
@@ -153,8 +225,12 @@ int q4k_plan_finalize(q4k_plan *p) {
     p->launches = q4k::launch_count() - before;
     if (rc != Q4K_OK || e != cudaSuccess) { cudaStreamDestroy(cs); return rc != Q4K_OK ? rc : q4k::note_cuda_error(e); }
     e = cudaGraphInstantiate(&p->exec, p->graph, 0);
+    if (e != cudaSuccess) { cudaStreamDestroy(cs); return q4k::note_cuda_error(e); }
+    const int before_parts = (int)q4k::launch_count();
+    rc = build_parts(p, cs, 4);
+    (void)before_parts;
     cudaStreamDestroy(cs);
-    if (e != cudaSuccess) return q4k::note_cuda_error(e);
+    if (rc != Q4K_OK) return rc;
     p->finalized = true;
     return Q4K_OK;
 }
@@ -184,12 +260,47 @@ int q4k_plan_run_host(q4k_plan *p, const void *in_host, void *out_host, void *st
     if (!p || !p->finalized) return Q4K_ERR_UNSUPPORTED;
     if (!in_host || !out_host) return Q4K_ERR_BAD_POINTER;
     cudaStream_t st = (cudaStream_t)stream;
-    cudaError_t e = cudaMemcpyAsync(p->in_dev, in_host, p->in_bytes, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return q4k::note_cuda_error(e);
-    const int rc = q4k_plan_run(p, stream);
-    if (rc != Q4K_OK) return rc;
-    e = cudaMemcpyAsync(out_host, p->out_dev, p->out_bytes, cudaMemcpyDeviceToHost, st);
-    return e == cudaSuccess ? Q4K_OK : q4k::note_cuda_error(e);
+    cudaError_t e;
+    if (p->parts.empty()) {                  // short plans: one copy in, the graph, one copy out
+        e = cudaMemcpyAsync(p->in_dev, in_host, p->in_bytes, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return q4k::note_cuda_error(e);
+        const int rc = q4k_plan_run(p, stream);
+        if (rc != Q4K_OK) return rc;
+        e = cudaMemcpyAsync(out_host, p->out_dev, p->out_bytes, cudaMemcpyDeviceToHost, st);
+        return e == cudaSuccess ? Q4K_OK : q4k::note_cuda_error(e);
+    }
+    // Copy / compute pipeline.  Caller's stream: inputs of part 0, graph 0, graph 1 ...; side stream: the inputs of parts
+    // 1.. right away, then the results of each part as soon as its graph has finished — the copy engines run under the
+    // kernels, only the first upload and the last download stay exposed.  The caller's stream joins the side stream at the end.
+    const char *in = static_cast<const char *>(in_host);
+    char *out = static_cast<char *>(out_host);
+    const size_t np = p->parts.size();
+#define Q4K_TRY(call) do { e = (call); if (e != cudaSuccess) return q4k::note_cuda_error(e); } while (0)
+    Q4K_TRY(cudaEventRecord(p->ev_start, st));                               // orders the side stream after the caller's earlier work
+    if (p->parts[0].in_len) Q4K_TRY(cudaMemcpyAsync(p->in_dev + p->parts[0].in_off, in + p->parts[0].in_off, p->parts[0].in_len, cudaMemcpyHostToDevice, st));
+    Q4K_TRY(cudaGraphLaunch(p->parts[0].exec, st));
+    Q4K_TRY(cudaEventRecord(p->ev_out[0], st));
+    Q4K_TRY(cudaStreamWaitEvent(p->side, p->ev_start, 0));
+    for (size_t c = 1; c < np; ++c) {
+        const q4k_plan::Part &pt = p->parts[c];
+        if (pt.in_len) Q4K_TRY(cudaMemcpyAsync(p->in_dev + pt.in_off, in + pt.in_off, pt.in_len, cudaMemcpyHostToDevice, p->side));
+        Q4K_TRY(cudaEventRecord(p->ev_in[c], p->side));
+    }
+    for (size_t c = 1; c < np; ++c) {
+        Q4K_TRY(cudaStreamWaitEvent(st, p->ev_in[c], 0));
+        Q4K_TRY(cudaGraphLaunch(p->parts[c].exec, st));
+        Q4K_TRY(cudaEventRecord(p->ev_out[c], st));
+    }
+    for (size_t c = 0; c < np; ++c) {
+        const q4k_plan::Part &pt = p->parts[c];
+        Q4K_TRY(cudaStreamWaitEvent(p->side, p->ev_out[c], 0));
+        Q4K_TRY(cudaMemcpyAsync(out + pt.out_off, p->out_dev + pt.out_off, pt.out_len, cudaMemcpyDeviceToHost, p->side));
+    }
+    Q4K_TRY(cudaEventRecord(p->ev_join, p->side));
+    Q4K_TRY(cudaStreamWaitEvent(st, p->ev_join, 0));
+#undef Q4K_TRY
+    q4k::add_launches(p->launches);
+    return Q4K_OK;
 }
 
 void q4k_plan_destroy(q4k_plan *p) {
@@ -197,6 +308,12 @@ void q4k_plan_destroy(q4k_plan *p) {
     cudaSetDevice(p->device);
     if (p->exec) cudaGraphExecDestroy(p->exec);
     if (p->graph) cudaGraphDestroy(p->graph);
+    for (auto &pt : p->parts) { if (pt.exec) cudaGraphExecDestroy(pt.exec); if (pt.graph) cudaGraphDestroy(pt.graph); }
+    for (auto ev : p->ev_in) if (ev) cudaEventDestroy(ev);
+    for (auto ev : p->ev_out) if (ev) cudaEventDestroy(ev);
+    if (p->ev_start) cudaEventDestroy(p->ev_start);
+    if (p->ev_join) cudaEventDestroy(p->ev_join);
+    if (p->side) cudaStreamDestroy(p->side);
     cudaFree(p->in_dev);
     cudaFree(p->out_dev);
     cudaFree(p->ws_dev);
