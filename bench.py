@@ -535,7 +535,7 @@ def run_ours(args, rank, world, local_rank):
                 it["full_host"].copy_(full, non_blocking=True)
             torch.cuda.current_stream().synchronize()
     elif plan is not None:
-        def step_host():                                       # ONE packed H2D, the graph, ONE packed D2H
+        def step_host():                                       # packed H2D, the graph(s), packed D2H (pipelined inside q4k_plan_run_host)
             plan.run_host(ms.plan_in_host, ms.plan_out_host)
             torch.cuda.current_stream().synchronize()
     else:
@@ -583,7 +583,7 @@ def run_ours(args, rank, world, local_rank):
                              if ms.weight_bytes > L2_BYTES else "WARNING: per-GPU weights fit in L2",
                        "launch": (f"q4k_plan_run: one CUDA graph of {int(launches_per_step)} launches (q/k/v and gate/up fused, shared activations)"
                                   if plan is not None else "CUDA graph replay of the C-ABI launches") if gathered is None else f"gather={gather_kind}",
-                       "e2e_path": "q4k_plan_run_host: one packed H2D + graph + one packed D2H per step" if plan is not None
+                       "e2e_path": "q4k_plan_run_host: packed pinned inputs up, four graphs, packed results down; copies pipelined under the kernels on a side stream" if plan is not None
                                    else "host buffers per mul_mat",
                        "parallelism": f"rowshard{world}" if sharded else f"replica{world}"},
             "decode_tok_s": round(1e3 / per_step_ms, 1) if not sharded else None,
