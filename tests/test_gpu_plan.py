@@ -129,6 +129,41 @@ def test_plan_run_host_one_copy_each_way(q4k):
     plan.close()
 
 
+def test_plan_run_host_pipeline_multi_layer(q4k):
+    """Plans of >= 8 mul_mats replay from host buffers as a copy / compute pipeline (four graphs; the inputs of the later parts
+    and every part's results move on a side stream).  Three layers, fresh inputs on every replay: every result equals the
+    individual q4k_mul_mat bit for bit, also when replays are queued back to back without a synchronize in between."""
+    import torch
+    N, layers = 1, 3
+    plan = q4k.GraphPlan(0)
+    items = []                                            # (weights, global input id, K, M)
+    for il in range(layers):
+        shapes, ws = _layer(q4k, N, seed=100 * il)
+        for w, (_, M, Kk, iid) in zip(ws, shapes):
+            gid = 4 * il + iid
+            plan.add(w, N, gid)
+            items.append((w, gid, Kk, M))
+    plan.finalize()
+    hin = [torch.zeros(plan.input_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    hout = [torch.zeros(plan.output_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    xs = [{}, {}]
+    for rep in range(2):
+        for _, gid, Kk, _ in items:
+            if gid not in xs[rep]:
+                xs[rep][gid] = make_acts(N, Kk, seed=500 + 37 * rep + gid)
+                off = plan.input_offset(gid)
+                hin[rep][off: off + N * Kk * 4] = torch.from_numpy(xs[rep][gid].view(np.uint8).reshape(-1))
+    plan.run_host(hin[0], hout[0])
+    plan.run_host(hin[1], hout[1])                        # queued behind the first replay: must not overwrite inputs in use
+    torch.cuda.synchronize()
+    for rep in range(2):
+        for i, (w, gid, _, M) in enumerate(items):
+            off = plan.output_offset(i)
+            got = hout[rep][off: off + N * M * 4].numpy().view(np.uint32).reshape(N, M)
+            assert np.array_equal(got, bits(q4k.mul_mat(w, t(xs[rep][gid])))), (rep, i)
+    plan.close()
+
+
 def test_plan_argument_errors(q4k):
     w = t(make_weights(8, 512))
     plan = q4k.GraphPlan(0)
