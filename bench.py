@@ -157,12 +157,18 @@ class MatSet:
         gen = torch.Generator(device=device)
         gen.manual_seed(seed)
         self.items = []
-        for name, M, K in mats:
+        ids = shared_input_ids(mats)
+        for (name, M, K), iid in zip(mats, ids):
             r0, r1 = (0, M) if row_range is None else row_range(M)
             w = rand_q4k(torch, r1 - r0, K, device, gen)
             x = torch.randn((N, K), device=device, generator=gen)
+            # prefill: mul_mats of one layer that read the same tensor (q/k/v, gate/up) get the same activations, so the second
+            # and third reuse the quantized copy (q4k_mul_mat_reuse — what the plugin's graph_compute does)
+            shared = N > 12 and self.items and self.items[-1]["iid"] == iid and self.items[-1]["K"] == K
+            if shared:
+                x = self.items[-1]["x"]
             dst = torch.zeros((N, r1 - r0), device=device)
-            self.items.append(dict(name=name, M=r1 - r0, K=K, M_full=M, w=w, x=x, dst=dst))
+            self.items.append(dict(name=name, M=r1 - r0, K=K, M_full=M, w=w, x=x, dst=dst, iid=iid, reuse=bool(shared)))
         kmax = max(K for _, _, K in mats)
         self.ws = torch.empty(max(q4k.workspace_bytes(kmax, N), 16), dtype=torch.uint8, device=device)
         self.algo_bytes = sum(algo_bytes(it["M"], it["K"], N) for it in self.items)
@@ -173,8 +179,11 @@ class MatSet:
         st = self.torch.cuda.current_stream().cuda_stream
         ws, wsn, N, f = self.ws.data_ptr(), self.ws.numel(), self.N, self.lib.q4k_mul_mat
         for it in self.items:
-            rc = f(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), it["x"].data_ptr(), N, it["K"] * 4,
-                   it["dst"].data_ptr(), it["M"] * 4, ws, wsn, st)
+            if it["reuse"]:
+                rc = self.lib.q4k_mul_mat_reuse(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), N, it["dst"].data_ptr(), it["M"] * 4, ws, wsn, st)
+            else:
+                rc = f(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), it["x"].data_ptr(), N, it["K"] * 4,
+                       it["dst"].data_ptr(), it["M"] * 4, ws, wsn, st)
             if rc != 0:
                 raise RuntimeError(f"q4k_mul_mat rc={rc} cuda={self.lib.q4k_last_cuda_error()}")
 

@@ -225,7 +225,7 @@ bool mul_mat_supported(const ggml_tensor * op) {
     return true;
 }
 
-ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
+ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node, bool reuse_quantized) {
     const ggml_tensor * src0 = node->src[0];
     const ggml_tensor * src1 = node->src[1];
     const int64_t K = src0->ne[0], M = src0->ne[1], N = src1->ne[1];
@@ -252,7 +252,13 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node) {
             const char * w = (const char *) src0->data + i02 * src0->nb[2] + i03 * src0->nb[3];
             const char * x = (const char *) src1->data + i12 * src1->nb[2] + i13 * src1->nb[3];
             char * d = (char *) node->data + i12 * node->nb[2] + i13 * node->nb[3];
-            const int rc = q6 ? q6k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
+            int rc = Q4K_ERR_UNSUPPORTED;
+            if (reuse_quantized && !q6) {      // the node in front quantized this src1 into the workspace: GEMM only
+                rc = q4k_mul_mat_reuse(w, M, K, (int64_t) src0->nb[1], N, (float *) d, (int64_t) node->nb[1], ctx->workspace,
+                                       ctx->workspace_bytes, ctx->stream);
+            }
+            if (rc == Q4K_ERR_UNSUPPORTED)
+            rc = q6 ? q6k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
                                             (float *) d, (int64_t) node->nb[1], ctx->workspace, ctx->workspace_bytes, ctx->stream)
                               : q4k_mul_mat(w, M, K, (int64_t) src0->nb[1], (const float *) x, N, (int64_t) src1->nb[1],
                                             (float *) d, (int64_t) node->nb[1], ctx->workspace, ctx->workspace_bytes, ctx->stream);
@@ -309,6 +315,8 @@ int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i) {
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     auto * ctx = (backend_context *) backend->context;
     if (q4k_set_device(ctx->dev->cuda_device) != Q4K_OK) return GGML_STATUS_FAILED;
+    const ggml_tensor * last_quantized = nullptr;      // src1 whose prefill-quantized copy is in the workspace right now
+    const void * last_quantized_data = nullptr;
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
         switch (node->op) {
@@ -318,9 +326,15 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
                 }
                 const int fused = try_fused_group(ctx, cgraph, i);
                 if (fused < 0) return GGML_STATUS_FAILED;
-                if (fused > 0) { i += fused - 1; break; }
-                const ggml_status st = compute_mul_mat(ctx, node);
+                if (fused > 0) { i += fused - 1; last_quantized = nullptr; break; }
+                // consecutive prefill mul_mats on one src1 (q/k/v, gate/up) share the quantized copy of the activations
+                const ggml_tensor * s0 = node->src[0], * s1 = node->src[1];
+                const bool plain2d = s0->ne[2] == 1 && s0->ne[3] == 1 && s1->ne[2] == 1 && s1->ne[3] == 1;
+                const bool reuse = plain2d && s0->type == GGML_TYPE_Q4_K && last_quantized == s1 && last_quantized_data == s1->data;
+                const ggml_status st = compute_mul_mat(ctx, node, reuse);
                 if (st != GGML_STATUS_SUCCESS) return st;
+                if (plain2d && s0->type == GGML_TYPE_Q4_K) { last_quantized = s1; last_quantized_data = s1->data; }
+                else { last_quantized = nullptr; last_quantized_data = nullptr; }
             } break;
             case GGML_OP_NONE:
             case GGML_OP_RESHAPE:

@@ -245,6 +245,21 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 
+int q4k_mul_mat_reuse(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N,
+                      float *dst_dev, int64_t dst_col_stride_bytes, void *workspace_dev, size_t workspace_bytes, void *stream) {
+    if (M < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (N <= Q4K_GEMV_GEMM_MIN_N || !g_gemm_enabled) return Q4K_ERR_UNSUPPORTED;     // decode shapes quantize inside their launch
+    if (M == 0) return Q4K_OK;
+    if (!w_dev || !dst_dev || !workspace_dev) return Q4K_ERR_BAD_POINTER;
+    if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
+    const int64_t nb = K / Q4K_QK_K;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (dst_col_stride_bytes < M * 4 || (dst_col_stride_bytes & 3) || !aligned16(workspace_dev)) return Q4K_ERR_BAD_SHAPE;
+    const cudaError_t e = launch_gemm_q4k_f32(w_dev, M, K, w_row_stride_bytes, nullptr, N, 0, dst_dev, dst_col_stride_bytes,
+                                              workspace_dev, (cudaStream_t)stream);
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
 int q4k_mul_mat_peers_sync(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
                            const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
                            float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,

@@ -685,6 +685,7 @@ static cudaError_t make_weight_map(CUtensorMap *map, const void *w, int64_t M, i
 }
 
 // F32 activations: quantize into `workspace` (gemm_workspace_bytes), then the tensor-core GEMM.  Two launches.
+// x == nullptr: the quantized copy in `workspace` is reused (q4k_mul_mat_reuse) — one launch.
 cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream) {
@@ -702,7 +703,11 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
     cudaError_t e;
-    {
+    if (!x) {
+        // the workspace already holds the quantized copy of these activations (the mul_mat in front of this one read the same
+        // src1: q/k/v, gate/up): only the split-K turnstiles have to be reset
+        if (ksplit > 1 && (e = cudaMemsetAsync(flags, 0, FLAG_BYTES, stream)) != cudaSuccess) return e;
+    } else {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)((total + 7) / 8));
         cfg.blockDim = dim3(256);

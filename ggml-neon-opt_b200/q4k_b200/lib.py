@@ -48,6 +48,7 @@ def load():
         L.q4k_mul_mat_workspace_bytes.argtypes = [i64, i64]
         L.q4k_mul_mat_workspace_bytes.restype = sz
         L.q4k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
+        L.q4k_mul_mat_reuse.argtypes = [vp, i64, i64, i64, i64, vp, i64, vp, sz, vp]
         L.q4k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q4k_vec_dot_q4_K_q8_K.argtypes = [i32, vp, sz, vp, sz, vp, sz, i32]
         L.q4k_debug_partials.argtypes = [vp, i64, i64, i64, i64, vp, i64, i64, vp, vp, vp, vp]

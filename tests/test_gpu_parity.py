@@ -187,6 +187,27 @@ def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit, monk
     assert np.array_equal(got.view(np.uint32), again.view(np.uint32))
 
 
+@pytest.mark.parametrize("N,K", [(16, 512), (130, 2048), (40, 4096)])
+def test_prefill_reuses_the_quantized_activations(q4k, N, K):
+    """q/k/v of a layer are three mul_mats on one src1: q4k_mul_mat_reuse runs the GEMM on the quantized copy the first call
+    left in the workspace (one launch instead of two) and gives the bits of a full q4k_mul_mat; N <= 12 is declined."""
+    import torch
+    lib = q4k.load()
+    w1, w2 = t(make_weights(256, K, seed=1)), t(make_weights(96, K, seed=2))
+    x = t(make_acts(N, K))
+    ws = torch.empty(q4k.workspace_bytes(K, N), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    want = q4k.mul_mat(w2, x, workspace=ws.clone())
+    q4k.mul_mat(w1, x, workspace=ws)                        # leaves the quantized copy of x in ws
+    got = torch.zeros((N, 96), device="cuda")
+    n0 = q4k.kernel_launches()
+    assert lib.q4k_mul_mat_reuse(w2.data_ptr(), 96, K, w2.stride(0), N, got.data_ptr(), 96 * 4, ws.data_ptr(), ws.numel(), st) == 0
+    assert q4k.kernel_launches() == n0 + 1
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+    assert lib.q4k_mul_mat_reuse(w2.data_ptr(), 96, K, w2.stride(0), 8, got.data_ptr(), 96 * 4, ws.data_ptr(), ws.numel(), st) == -5
+
+
 def test_vec_dot_signature_bit_identical(q4k):
     import torch
     from oracle import port
