@@ -460,7 +460,9 @@ int choose_kparts(int64_t tiles, int nb, int nrows /* staged activation rows */,
         // beyond one wave only a 2-way split for batches (>= 4 staged rows): halving the activations a CTA stages is worth more
         // than the second wave there (measured: 4096 x 14336 N = 8 30.1 -> 25.8 us, 8192 x 28672 N = 4 62 -> 57 us; no gain
         // at N <= 2 — profiles/r1_batch_kparts.txt)
-        if (kp > 1 && tiles * kp > slots && !(kp == 2 && nrows >= 4)) break;
+        // ... and for one column of a long fused-quantizer K (56..64 superblocks: every CTA would quantize all of them):
+        // 4096 x 14336 N = 1 12.7 -> 11.8 us (profiles/r1_n1_kparts.txt)
+        if (kp > 1 && tiles * kp > slots && !(kp == 2 && (nrows >= 4 || (nrows * nb >= 56 && nb <= 64)))) break;
         const bool two = std::min<int64_t>(tiles * kp, slots) > slots / 2;
         const int prounds = std::min(rounds, (nseg + kp - 1) / kp * SEG_ROUNDS);
         const int blocks = std::min(nb, prounds * KW) * nrows;
