@@ -20,6 +20,11 @@ constexpr int QUANT_WARPS = 8;
 __global__ void __launch_bounds__(QUANT_WARPS * 32)
 quantize_q8_K_kernel(const float *__restrict__ x, uint8_t *__restrict__ y, int64_t nb_per_row,
                      int64_t nblocks_total, int64_t x_row_stride_bytes) {
+    // programmatic dependent launch on both sides: the decode kernel behind this one may start its prologue (barriers, the
+    // first weight tiles — they do not depend on the activations) right away; this kernel waits for the one in front of it
+    // before it reads x or overwrites the workspace that kernel may still be reading
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int lane = threadIdx.x & 31;
     const int64_t blk = (int64_t)blockIdx.x * QUANT_WARPS + (threadIdx.x >> 5);
     if (blk >= nblocks_total) return;
@@ -51,9 +56,18 @@ cudaError_t launch_quantize_q8_K(const float *x, void *y, int64_t k, int64_t nro
     const int64_t total = nb_per_row * nrows;
     if (total == 0) return cudaSuccess;
     const int64_t grid = (total + QUANT_WARPS - 1) / QUANT_WARPS;
-    quantize_q8_K_kernel<<<(unsigned)grid, QUANT_WARPS * 32, 0, stream>>>(x, (uint8_t *)y, nb_per_row, total, x_row_stride_bytes);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(QUANT_WARPS * 32);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_gemv_pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, quantize_q8_K_kernel, x, (uint8_t *)y, nb_per_row, total, x_row_stride_bytes);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 }  // namespace q4k
