@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "knobs.h"
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
@@ -48,20 +49,12 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 // launch-independent float association, within 1e-5 of the reference.  Q4K_GEMV_ORDER=exact (or
 // q4k_debug_set_gemv_order(1)) selects the kernel that reproduces the reference's AVX2 accumulation order bit for bit
 // (gemv_q4k_tma.cu) at ~10-25% less throughput on small matrices.
-static int64_t g_fuse_limit = 16384;   // N*K floats up to which the quantizer is fused into the decode launch (measured: K = 28672 is faster with the separate quantizer)
 constexpr int64_t Q4K_GEMV_GEMM_MIN_N = 12;   // largest N served by passes of the decode kernel when the GEMM is available
-static int g_gemm_enabled = 1;          // 0: N > 8 takes the decode kernel eight columns at a time (development)
-static int g_order_mode = -1;     // 0 = policy, 1 = always exact, 2 = never
 bool gemv_exact_policy(int N);
 static bool gemv_exact_for(int N) { return gemv_exact_policy(N); }
 bool gemv_exact_policy(int N) {
-    int &mode = g_order_mode;
-    if (mode < 0) {
-        const char *e = getenv("Q4K_GEMV_ORDER");
-        mode = !e ? 0 : (!strcmp(e, "exact") ? 1 : (!strcmp(e, "fast") ? 2 : 0));
-    }
     (void)N;
-    return mode == 1;
+    return knobs().order_mode == 1;
 }
 
 }  // namespace q4k
@@ -80,37 +73,6 @@ int q4k_device_ok(int device) {
     int major = 0;
     if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device) != cudaSuccess) return 0;
     return major == 10;
-}
-
-int q4k_debug_set_gemv_order(int mode) {
-    if (mode < 0 || mode > 2) return Q4K_ERR_UNSUPPORTED;
-    g_order_mode = mode;
-    return Q4K_OK;
-}
-
-int q4k_debug_set_gemv_config(int cfg) {
-    g_gemv_config = cfg;
-    return Q4K_OK;
-}
-
-int q4k_debug_set_fuse_limit(int64_t n_floats) {
-    g_fuse_limit = n_floats;
-    return Q4K_OK;
-}
-
-int q4k_debug_set_gemm(int on) {
-    g_gemm_enabled = on ? 1 : 0;
-    return Q4K_OK;
-}
-
-int q4k_debug_set_big_matrix_bytes(int64_t bytes) {
-    g_big_matrix_bytes = bytes;
-    return Q4K_OK;
-}
-
-int q4k_debug_set_pdl(int on) {
-    g_gemv_pdl = on ? 1 : 0;
-    return Q4K_OK;
 }
 
 int q4k_last_cuda_error(void) { return t_last_cuda_error; }
@@ -184,7 +146,7 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
         if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
         if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
         // decode shapes: one launch — every CTA quantizes the (small) activations into its own shared memory
-        if (N <= Q4K_GEMV_MAX_N && N * K <= g_fuse_limit && g_gemv_config == 0) {
+        if (N <= Q4K_GEMV_MAX_N && N * K <= knobs().fuse_limit && knobs().gemv_config == 0) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
             const int64_t nb = K / Q4K_QK_K;
             if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
@@ -192,14 +154,14 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
             if (dst_col_stride_bytes < M * 4 || (dst_col_stride_bytes & 3)) return Q4K_ERR_BAD_SHAPE;
             const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M, K, w_row_stride_bytes, nullptr, x_dev, (int)N, x_row_stride_bytes,
                                                           dst_dev, dst_col_stride_bytes, gemv_exact_for((int)N), 0,
-                                                          g_gemv_pdl != 0, (cudaStream_t)stream);
+                                                          knobs().pdl != 0, (cudaStream_t)stream);
             if (e == cudaSuccess) return Q4K_OK;
             if (e != cudaErrorNotSupported) return cuda_fail(e);
         }
         // prefill shapes: planar Q8 quantizer + tensor-core GEMM (tcgen05 kind::i8).  Its time does not depend on N up to a
         // 128-column tile, so 9..12 columns are cheaper as two passes of the decode kernel (the second pass finds the
         // weights in L2): measured at six shapes, profiles/r1_midn_sweep.txt (4096x14336 N = 9: 39 vs 49 us)
-        if (N > Q4K_GEMV_GEMM_MIN_N && g_gemm_enabled) {
+        if (N > Q4K_GEMV_GEMM_MIN_N && knobs().gemm_enabled) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
             const int64_t nb = K / Q4K_QK_K;
             if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
@@ -231,7 +193,7 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
     if (dst_col_stride_bytes < (dst_row0 + M_local) * 4 || (dst_col_stride_bytes & 3)) return Q4K_ERR_BAD_SHAPE;
     const void *xq = nullptr;
     int64_t xq_stride = x_row_stride_bytes;
-    if (N * K > g_fuse_limit && workspace_dev && workspace_bytes >= (size_t)(N * nb * Q4K_BLOCK_Q8K)) {
+    if (N * K > knobs().fuse_limit && workspace_dev && workspace_bytes >= (size_t)(N * nb * Q4K_BLOCK_Q8K)) {
         // long activations: quantize once in a kernel of its own instead of once per CTA (same rule as q4k_mul_mat)
         const cudaError_t eq = launch_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, (cudaStream_t)stream);
         if (eq != cudaSuccess) return cuda_fail(eq);
@@ -239,7 +201,7 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
         xq_stride = nb * Q4K_BLOCK_Q8K;
     }
     const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M_local, K, w_row_stride_bytes, xq, xq ? nullptr : x_dev, (int)N, xq_stride,
-                                                  nullptr, dst_col_stride_bytes, gemv_exact_for((int)N), 0, g_gemv_pdl != 0,
+                                                  nullptr, dst_col_stride_bytes, gemv_exact_for((int)N), 0, knobs().pdl != 0,
                                                   (cudaStream_t)stream, dst_peers, n_peers, dst_row0);
     if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;     // activations too large for one shared-memory residency
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
@@ -248,7 +210,7 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
 int q4k_mul_mat_reuse(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N,
                       float *dst_dev, int64_t dst_col_stride_bytes, void *workspace_dev, size_t workspace_bytes, void *stream) {
     if (M < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
-    if (N <= Q4K_GEMV_GEMM_MIN_N || !g_gemm_enabled) return Q4K_ERR_UNSUPPORTED;     // decode shapes quantize inside their launch
+    if (N <= Q4K_GEMV_GEMM_MIN_N || !knobs().gemm_enabled) return Q4K_ERR_UNSUPPORTED;     // decode shapes quantize inside their launch
     if (M == 0) return Q4K_OK;
     if (!w_dev || !dst_dev || !workspace_dev) return Q4K_ERR_BAD_POINTER;
     if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
@@ -304,7 +266,7 @@ int q4k_mul_mat_group(int n_mats, const void *const *w_dev, const int64_t *M, in
         if (!w_dev[i] || !x_dev[i] || !dst_dev[i] || !aligned16(w_dev[i]) || !aligned16(x_dev[i])) return Q4K_ERR_BAD_POINTER;
     }
     const cudaError_t e = launch_gemv_q4k_group(n_mats, w_dev, M, K, w_row_stride_bytes, x_dev, (int)N, x_row_stride_bytes, dst_dev,
-                                                gemv_exact_for((int)N), g_gemv_pdl != 0, (cudaStream_t)stream);
+                                                gemv_exact_for((int)N), knobs().pdl != 0, (cudaStream_t)stream);
     if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }

@@ -14,7 +14,6 @@ using namespace q4k;
 
 namespace {
 
-constexpr int64_t Q6K_FUSE_LIMIT = 32768;      // N*K floats up to which quantize_row_q8_K runs inside the GEMV launch
 
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
@@ -34,7 +33,7 @@ int run_columns(const void *w, int64_t M, int64_t K, int64_t w_stride, const voi
                                               xq ? (const char *)xq + n0 * x_stride : nullptr,
                                               xf ? (const float *)((const char *)xf + n0 * x_stride) : nullptr, nn, x_stride,
                                               (float *)((char *)dst + n0 * dst_stride), dst_stride,
-                                              dump ? dump + n0 * M * nb : nullptr, g_gemv_pdl != 0, st);
+                                              dump ? dump + n0 * M * nb : nullptr, knobs().pdl != 0, st);
         if (e == cudaErrorNotSupported && nn > 1) { step = nn / 2; continue; }
         if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;
         if (e != cudaSuccess) return note_cuda_error(e);
@@ -90,8 +89,7 @@ int q6k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
     const int64_t nb = K / Q4K_QK_K;
     if (check_w(w_dev, nb, w_row_stride_bytes)) return Q4K_ERR_BAD_SHAPE;
     if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
-    int64_t fuse_limit = Q6K_FUSE_LIMIT;
-    if (const char *e = getenv("Q6K_DBG_FUSE_LIMIT")) fuse_limit = atoll(e);      // development knob (tools/fuse_sweep.py)
+    const int64_t fuse_limit = knobs().q6k_fuse_limit;                          // default 32768 (tools/fuse_sweep.py)
     if (N <= Q4K_GEMV_MAX_N && N * K <= fuse_limit) {             // decode: quantizer fused into the launch
         const int rc = run_columns(w_dev, M, K, w_row_stride_bytes, nullptr, x_dev, N, x_row_stride_bytes, dst_dev,
                                    dst_col_stride_bytes, nullptr, st);

@@ -607,8 +607,9 @@ quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, 
     if (blk >= nblocks_total) return;
     const int64_t row = blk / nb_per_row, b = blk - row * nb_per_row;
     const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + row * x_row_stride_bytes) + b * QK_K;
-    const float4 a = __ldg(reinterpret_cast<const float4 *>(src) + lane);
-    const float4 c = __ldg(reinterpret_cast<const float4 *>(src) + 32 + lane);
+    // plain (coherent) loads: under programmatic dependent launch the kernel that produces x may still have been running at entry
+    const float4 a = reinterpret_cast<const float4 *>(src)[lane];
+    const float4 c = reinterpret_cast<const float4 *>(src)[32 + lane];
     const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
     uint32_t w_lo, w_hi;
     int s_lo, s_hi;
@@ -649,7 +650,7 @@ size_t gemm_workspace_bytes(int64_t K, int64_t N) {
 // minimise nb / s + 10 (s - 1) while all CTAs stay co-resident.  4096 x 14336 x 32: 80.7 -> 55 us at s = 2; the
 // 8- and 22-superblock TinyLlama matrices stay unsplit (28.7 vs 23.0 us at 2048 x 2048 x 512).
 static int choose_ksplit(int64_t tiles, int64_t nb) {
-    if (const char *e = getenv("Q4K_DBG_GEMM_KSPLIT")) { const int v = atoi(e); if (v >= 1) return (int)std::min<int64_t>(v, nb); }
+    if (knobs().gemm_ksplit >= 1) return (int)std::min<int64_t>(knobs().gemm_ksplit, nb);      // development / test knob
     const int sms = sm_count();
     int best = 1;
     double best_cost = (double)nb;
@@ -713,7 +714,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
         cfg.blockDim = dim3(256);
         cfg.stream = stream;
         cfg.attrs = pdl_attr;
-        cfg.numAttrs = g_gemv_pdl ? 1 : 0;
+        cfg.numAttrs = knobs().pdl ? 1 : 0;
         int *qflags = ksplit > 1 ? flags : nullptr;
         e = cudaLaunchKernelEx(&cfg, quantize_q8_planar_kernel, x, qs, d, bmin, nb, total, x_row_stride_bytes, N, qflags);
         count_launch();
@@ -728,12 +729,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
     p.ksplit = ksplit; p.flags = flags;
     constexpr size_t smem = SMEM_TOTAL;
-    static bool attr_set = false;
-    if (!attr_set) {
-        e = cudaFuncSetAttribute(gemm_q4k_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if ((e = ensure_max_dynamic_smem((const void *)gemm_q4k_tc_kernel, (int)smem)) != cudaSuccess) return e;
     const dim3 grid((unsigned)ntiles, (unsigned)mtiles, (unsigned)ksplit);              // column tiles of one row tile run together (L2)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
@@ -741,7 +737,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cfg.attrs = pdl_attr;
-    cfg.numAttrs = g_gemv_pdl ? 1 : 0;
+    cfg.numAttrs = knobs().pdl ? 1 : 0;
     e = cudaLaunchKernelEx(&cfg, gemm_q4k_tc_kernel, p);
     count_launch();
     return e;

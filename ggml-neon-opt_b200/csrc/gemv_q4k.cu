@@ -199,12 +199,7 @@ static cudaError_t launch_cfg(GemvParams p, cudaStream_t stream) {
     p.kt = (int)(p.nb < kt_fit ? p.nb : kt_fit);
     p.n_ktiles = (p.nb + p.kt - 1) / p.kt;
     const size_t smem = gemv_smem_bytes(N, p.kt);
-    static bool attr_set = false;        // per template instance
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BUDGET);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)SMEM_BUDGET)) return ea;
     constexpr int ROWS_PER_CTA = (THREADS / 32) * 4 * R;
     p.n_row_tiles = (p.M + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
     int per_sm = 1;
@@ -218,14 +213,11 @@ static cudaError_t launch_cfg(GemvParams p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
-// development knob (q4k_debug_set_gemv_config): 0 = heuristic, 1.. = force one of the compiled shapes
-int g_gemv_config = 0;
-int g_gemv_pdl = 1;
 
 template <int N, bool EXACT>
 static cudaError_t launch_n(const GemvParams &p, cudaStream_t stream) {
     if (N > 4) return launch_cfg<N, EXACT, 1, 2, 128>(p, stream);
-    switch (g_gemv_config) {
+    switch (knobs().gemv_config) {
         case 1: return launch_cfg<N, EXACT, 1, 4, 128>(p, stream);
         case 2: return launch_cfg<N, EXACT, 2, 2, 256>(p, stream);
         case 3: return launch_cfg<N, EXACT, 1, 8, 128>(p, stream);
@@ -259,10 +251,11 @@ cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
                                 const void *xq, int N, int64_t xq_row_stride_bytes,
                                 float *dst, int64_t dst_col_stride_bytes, bool exact_order, cudaStream_t stream) {
     if (M == 0 || N == 0) return cudaSuccess;
+    const int g_gemv_config = knobs().gemv_config;
     if (g_gemv_config == 0 || g_gemv_config >= 10) {      // production path: TMA-bulk staged kernel
         const cudaError_t e = launch_gemv_q4k_q8k_tma(w, M, K, w_row_stride_bytes, xq, nullptr, N, xq_row_stride_bytes, dst,
                                                       dst_col_stride_bytes, exact_order,
-                                                      g_gemv_config >= 10 ? g_gemv_config - 10 : 0, g_gemv_pdl != 0, stream);
+                                                      g_gemv_config >= 10 ? g_gemv_config - 10 : 0, knobs().pdl != 0, stream);
         if (e != cudaErrorNotSupported) return e;
         // activations too large for one shared-memory residency (8 columns of K = 28672 ...): half the columns per launch —
         // the weights stream twice, which still beats the K-tiled direct-load kernel below by an order of magnitude

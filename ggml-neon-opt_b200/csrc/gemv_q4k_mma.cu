@@ -429,11 +429,6 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
 // ---------------------------------------------------------------------------------------------------- launch
 constexpr size_t MMA_SMEM_MAX = 232448;      // 227 KB per CTA on sm_100
 
-int mma_env(const char *name) {              // development knobs (tools/launch_chain.py); unset = 0
-    const char *e = getenv(name);
-    return e ? atoi(e) : 0;
-}
-
 size_t mma_fixed_smem(int nrows, int nb, int N, int S, int KP) {
     const int rounds = (nb + KW - 1) / KW, nseg = (rounds + SEG_ROUNDS - 1) / SEG_ROUNDS, pseg_max = (nseg + KP - 1) / KP;
     size_t off = (size_t)nrows * q8_row_bytes(nb) + Q8_STRIDE;
@@ -447,7 +442,7 @@ size_t mma_fixed_smem(int nrows, int nb, int N, int S, int KP) {
 // How many CTAs share a tile along K.  Split when one CTA per tile would leave SMs idle or would make every CTA quantize
 // a long activation vector by itself; the float result does not depend on the choice (segment order, see the kernel).
 int choose_kparts(int64_t tiles, int nb, int nrows /* staged activation rows */, int slots) {
-    const int forced = mma_env("Q4K_DBG_MMA_KPARTS");
+    const int forced = knobs().mma_kparts;
     const int rounds = (nb + KW - 1) / KW, nseg = (rounds + SEG_ROUNDS - 1) / SEG_ROUNDS;
     if (forced > 0) return forced <= nseg ? forced : 1;
     // Rough per-launch model in microseconds, fitted to profiles/r1_launch_chain_splitk.txt: every CTA quantizes the
@@ -492,17 +487,12 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
         if (stages < 2) return cudaErrorNotSupported;              // activations do not fit: caller tiles or falls back
     }
     if (stages > 5) stages = 5;
-    if (mma_env("Q4K_DBG_MMA_STAGES") > 0 && mma_env("Q4K_DBG_MMA_STAGES") < stages) stages = mma_env("Q4K_DBG_MMA_STAGES");
-    if (mma_env("Q4K_DBG_MMA_PER_SM") > 0) per_sm = min(per_sm, mma_env("Q4K_DBG_MMA_PER_SM"));
+    if (knobs().mma_stages > 0 && knobs().mma_stages < stages) stages = knobs().mma_stages;
+    if (knobs().mma_per_sm > 0) per_sm = min(per_sm, knobs().mma_per_sm);
     p.stages = stages;
-    p.interleave = mma_env("Q4K_DBG_MMA_CONTIG") > 0 ? 0 : 1;
+    p.interleave = knobs().mma_contig > 0 ? 0 : 1;
     const size_t smem = fixed + (size_t)stages * slot;
-    static bool attr_set[3] = {false, false, false};
-    if (!attr_set[mode]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MMA_SMEM_MAX);
-        if (e != cudaSuccess) return e;
-        attr_set[mode] = true;
-    }
+    if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)MMA_SMEM_MAX)) return ea;
     int64_t grid = (int64_t)sm_count() * per_sm;
     if (grid > p.n_groups * KP) grid = p.n_groups * KP;
     grid -= grid % KP;                               // whole clusters

@@ -40,8 +40,6 @@ namespace q4k {
 
 thread_local PeerSyncReq *t_sync_req = nullptr;
 
-int64_t g_big_matrix_bytes = (int64_t)34 << 20;   // q4k_debug_set_big_matrix_bytes; <= 0: never (crossover measured: profiles/r1_big_sweep.txt)
-
 namespace {
 
 // ORD: 0 = fast (one int per lane and superblock), 1 = EXACT (the reference's AVX2 chain), 2 = the float association of
@@ -331,11 +329,6 @@ size_t fixed_smem(int nrows, int nb, bool exact, int N) {    // nrows = staged a
 }
 constexpr size_t PER_STAGE = (size_t)WARPS * (STAGE_BYTES + 16);
 
-int dbg_env(const char *name) {           // development knobs (tools/launch_chain.py); unset = 0
-    const char *e = getenv(name);
-    return e ? atoi(e) : 0;
-}
-
 template <int N, int ORD>
 cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
     constexpr bool EXACT = ORD == 1;
@@ -344,19 +337,14 @@ cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_
     if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
     // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits
     int stages = want_stages > 0 ? want_stages : 2;
-    if (dbg_env("Q4K_DBG_STAGES") > 0) stages = dbg_env("Q4K_DBG_STAGES");
+    if (knobs().tma_stages > 0) stages = knobs().tma_stages;
     while (stages > 1 && 2 * (fixed + stages * PER_STAGE + 1024) > SMEM_MAX) --stages;
     if (fixed + stages * PER_STAGE > SMEM_MAX) stages = (int)((SMEM_MAX - fixed) / PER_STAGE);
     p.stages = stages;
     const size_t smem = fixed + stages * PER_STAGE;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)SMEM_MAX)) return ea;
     int per_sm = (2 * (smem + 1024) <= SMEM_MAX) ? 2 : 1;
-    if (dbg_env("Q4K_DBG_PER_SM") > 0) per_sm = dbg_env("Q4K_DBG_PER_SM");
+    if (knobs().tma_per_sm > 0) per_sm = knobs().tma_per_sm;
     int64_t grid = (int64_t)sm_count() * per_sm;
     if (grid > p.n_groups) grid = p.n_groups;        // small matrices: at least one 4-row group per CTA
     if (grid < 1) grid = 1;
@@ -409,9 +397,10 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     // matrices below 34 MiB stay on the tensor-pipe kernel — profiles/r1_big_sweep.txt).
     // (long K with few rows — a 4096 x 28672 shard — stays on the tensor-pipe kernel, whose cluster split-K wins there:
     // 20.6 vs 22.4 us, profiles/r1_shard_ab_2gpu.txt; the threshold 1 = "always" of the tests skips the row rule)
-    const bool big = N == 1 && !exact_order && stages <= 0 && g_big_matrix_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= g_big_matrix_bytes &&
-                     (M >= 8192 || g_big_matrix_bytes == 1);
-    if (!big && !exact_order && stages <= 0 && dbg_env("Q4K_DBG_MMA") >= 0) {      // tolerance order: the tensor-pipe kernel
+    const int64_t big_bytes = knobs().big_matrix_bytes;
+    const bool big = N == 1 && !exact_order && stages <= 0 && big_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= big_bytes &&
+                     (M >= 8192 || big_bytes == 1);
+    if (!big && !exact_order && stages <= 0 && !knobs().mma_off) {      // tolerance order: the tensor-pipe kernel
         const void *wv[1] = {w};
         const int64_t Mv[1] = {M};
         const float *xv[1] = {xf};
@@ -454,7 +443,7 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
                                   const float *const *x, int N, int64_t x_row_stride_bytes, float *const *dst,
                                   bool exact_order, bool pdl, cudaStream_t stream) {
     if (nmat < 1 || nmat > 4) return cudaErrorInvalidValue;
-    if (!exact_order && dbg_env("Q4K_DBG_MMA") >= 0) {
+    if (!exact_order && !knobs().mma_off) {
         const cudaError_t e = launch_gemv_q4k_mma(nmat, w, M, K, w_row_stride_bytes, nullptr, x, N, x_row_stride_bytes, dst,
                                                   0, nullptr, 0, 0, pdl, stream);
         if (e != cudaErrorNotSupported) return e;

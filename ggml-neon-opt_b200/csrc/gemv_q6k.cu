@@ -314,17 +314,12 @@ cudaError_t launch_q6_n(Q6Params p, bool pdl, cudaStream_t stream) {
     const size_t fixed = fixed_smem_q6(N, p.nb);
     if (fixed + PER_STAGE_Q6 > SMEM_MAX_Q6) return cudaErrorNotSupported;        // activations do not fit: caller tiles
     int stages = 2;
-    if (const char *e = getenv("Q6K_DBG_STAGES")) stages = atoi(e) > 0 ? atoi(e) : stages;
+    if (knobs().q6k_stages > 0) stages = knobs().q6k_stages;
     while (stages > 1 && 2 * (fixed + stages * PER_STAGE_Q6 + 1024) > SMEM_MAX_Q6) --stages;
     if (fixed + stages * PER_STAGE_Q6 > SMEM_MAX_Q6) stages = (int)((SMEM_MAX_Q6 - fixed) / PER_STAGE_Q6);
     p.stages = stages;
     const size_t smem = fixed + stages * PER_STAGE_Q6;
-    static bool attr_set = false;
-    if (!attr_set) {
-        const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX_Q6);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)SMEM_MAX_Q6)) return ea;
     const int per_sm = (2 * (smem + 1024) <= SMEM_MAX_Q6) ? 2 : 1;
     int64_t grid = (int64_t)sm_count() * per_sm;
     if (grid > p.n_groups) grid = p.n_groups;

@@ -1,0 +1,37 @@
+// knobs.h — development / test settings of the library, and per-device kernel attributes.
+//
+// Nothing here is process-global mutable state: the defaults are read from the environment ONCE (first use, then
+// immutable); q4k_debug_set* change the CALLING THREAD's copy only.  A ggml backend instance is driven by one thread at a
+// time (SURVEY.md §8b "Threading"), the plugin never calls a setter, so two backend instances / llama contexts cannot change
+// each other's numerics, and no launch path calls getenv.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace q4k {
+
+struct Knobs {
+    int     order_mode;         // Q4K_GEMV_ORDER: 0 = default (tolerance order), 1 = the reference's AVX2 order bit for bit, 2 = never exact
+    int64_t fuse_limit;         // N*K floats up to which quantize_row_q8_K runs inside the decode launch
+    int     gemm_enabled;       // 0: N > 8 takes the decode kernel eight columns at a time
+    int64_t big_matrix_bytes;   // N == 1 launches with at least this many weight bytes take the bulk-copy kernel (ORD 2)
+    int     pdl;                // 1 = programmatic dependent launch
+    int     gemv_config;        // gemv_q4k.cu tile shapes (development)
+    int     mma_off;            // Q4K_DBG_MMA < 0: never the tensor-pipe decode kernel
+    int     mma_kparts, mma_stages, mma_per_sm, mma_contig;   // gemv_q4k_mma.cu launch shape (0 = choose)
+    int     tma_stages, tma_per_sm;                            // gemv_q4k_tma.cu
+    int     gemm_ksplit;        // gemm_q4k_tc.cu: CTAs along K per tile (0 = choose)
+    int     midn_max;           // largest N served by the batched tensor-pipe decode kernel (gemv_q4k_wide.cu); 0 = off
+    int64_t q6k_fuse_limit;
+    int     q6k_stages;
+};
+
+Knobs &knobs();                  // the calling thread's settings (initialised from the process defaults)
+void reset_knobs();              // back to the process defaults (this thread)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: remembered per (device, kernel), so a
+// process that drives several GPUs (the plugin registers one device per sm_100 GPU) sets it on each of them.
+cudaError_t ensure_max_dynamic_smem(const void *kernel, int bytes);
+
+}  // namespace q4k

@@ -77,7 +77,7 @@ extern "C" int q4k_peer_signal_wait(void *const *flags_peers, int world, int ran
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = q4k::g_gemv_pdl ? 1 : 0;
+    cfg.numAttrs = q4k::knobs().pdl ? 1 : 0;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, q4k::peer_signal_wait_kernel, p);
     q4k::count_launch();
     return e == cudaSuccess ? Q4K_OK : q4k::note_cuda_error(e);

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "knobs.h"
+
 namespace q4k {
 
 void count_launch();          // bumps the process-wide kernel launch counter (q4k_kernel_launches)
@@ -68,9 +70,6 @@ struct PeerSyncReq {
 };
 extern thread_local PeerSyncReq *t_sync_req;
 
-extern int g_gemv_config;   // development knob, see gemv_q4k.cu
-extern int64_t g_big_matrix_bytes;   // N == 1 launches with at least this many weight bytes take the bulk-copy kernel (gemv_q4k_tma.cu, ORD 2)
-extern int g_gemv_pdl;      // 1 = launch the GEMV with programmatic stream serialization (default)
 void add_launches(int64_t n);  // launches replayed through a CUDA graph
 int64_t launch_count();
 int sm_count();               // multiprocessors of the current device (cached)

@@ -32,8 +32,10 @@ quantize_q8_K_kernel(const float *__restrict__ x, uint8_t *__restrict__ y, int64
     const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + row * x_row_stride_bytes) + col * QK_K;
     uint8_t *dst = y + blk * BLK_Q8K;   // rows are packed: row stride = nb_per_row * 292
 
-    const float4 a = __ldg(reinterpret_cast<const float4 *>(src) + lane);
-    const float4 b = __ldg(reinterpret_cast<const float4 *>(src) + 32 + lane);
+    // plain (coherent) loads, not ld.global.nc: under programmatic dependent launch this kernel's lifetime overlaps the kernel
+    // that produces x (peer GPUs storing over NVLink included)
+    const float4 a = reinterpret_cast<const float4 *>(src)[lane];
+    const float4 b = reinterpret_cast<const float4 *>(src)[32 + lane];
     const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 
     uint32_t w_lo, w_hi;
@@ -64,7 +66,7 @@ cudaError_t launch_quantize_q8_K(const float *x, void *y, int64_t k, int64_t nro
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = g_gemv_pdl ? 1 : 0;
+    cfg.numAttrs = knobs().pdl ? 1 : 0;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, quantize_q8_K_kernel, x, (uint8_t *)y, nb_per_row, total, x_row_stride_bytes);
     count_launch();
     return e;

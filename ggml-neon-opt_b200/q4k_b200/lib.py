@@ -87,6 +87,8 @@ def load():
         L.q6k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
         L.q6k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q6k_debug_partials.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, vp, vp]
+        L.q4k_debug_set.argtypes = [C.c_char_p, i64]
+        L.q4k_debug_reset.restype = None
         L.q4k_debug_set_fuse_limit.argtypes = [i64]
         L.q4k_debug_set_pdl.argtypes = [i32]
         L.q4k_debug_set_gemv_order.argtypes = [i32]
@@ -120,6 +122,15 @@ def build_info() -> str:
 
 def kernel_launches() -> int:
     return load().q4k_kernel_launches()
+
+
+def debug_set(name: str, value: int) -> None:
+    """Development / test knob of the calling thread (q4k_debug_set of include/q4k_b200.h); 0 = the launch heuristic chooses."""
+    _check("q4k_debug_set", load().q4k_debug_set(name.encode(), int(value)))
+
+
+def debug_reset() -> None:
+    load().q4k_debug_reset()
 
 
 def workspace_bytes(K: int, N: int) -> int:

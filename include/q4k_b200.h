@@ -172,6 +172,16 @@ int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes,
                        const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
                        int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev, void *stream);
 
+/* Development / test knobs.  None of them is process-global mutable state: the defaults are read from the environment once
+ * (Q4K_GEMV_ORDER, Q4K_DBG_*), and every setter below changes the CALLING THREAD's copy only, so backend instances driven by
+ * different threads cannot change each other's numerics (SURVEY.md §8b "Threading"); the ggml plugin never calls a setter.
+ * q4k_debug_set(name, value): "gemv_order", "fuse_limit", "gemm", "big_matrix_bytes", "pdl", "gemv_config", "mma_off",
+ * "mma_kparts", "mma_stages", "mma_per_sm", "mma_contig", "tma_stages", "tma_per_sm", "gemm_ksplit", "midn_max",
+ * "q6k_fuse_limit", "q6k_stages" (0 = the launch heuristic chooses); Q4K_ERR_UNSUPPORTED for an unknown name.
+ * q4k_debug_reset(): this thread back to the process defaults. */
+int  q4k_debug_set(const char *name, int64_t value);
+void q4k_debug_reset(void);
+
 /* Float order of the decode path (N <= 8): 0 / 2 = default — exact integer sums, fixed launch-independent float
  * association, results within 1e-5 of ggml_vec_dot_q4_K_q8_K; 1 = the reference's AVX2 accumulation order, fp32 results
  * bit-identical to the x86 build (slower kernel).  Overrides the Q4K_GEMV_ORDER environment variable ("exact" / "fast"). */

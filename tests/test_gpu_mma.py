@@ -77,17 +77,16 @@ def test_mma_q8_input_equals_fused_f32(q4k, fast_order):
 def test_mma_split_k_does_not_change_the_bits(q4k, fast_order, M, K, N):
     """K split over the CTAs of a cluster (1, 2 or 4 parts): the segment sums are added in the same order wherever they
     were computed, so every split gives the same bits — and all of them are within tolerance of the oracle."""
-    import os
     from oracle import port
     w, x = make_weights(M, K), make_acts(N, K)
     wd, xd = t(w), t(x)
     outs = {}
     try:
         for kp in (1, 2, 4):
-            os.environ["Q4K_DBG_MMA_KPARTS"] = str(kp)
+            q4k.debug_set("mma_kparts", kp)
             outs[kp] = q4k.mul_mat(wd, xd).cpu().numpy()
     finally:
-        os.environ.pop("Q4K_DBG_MMA_KPARTS", None)
+        q4k.debug_set("mma_kparts", 0)
     policy = q4k.mul_mat(wd, xd).cpu().numpy()
     assert_close(outs[1], port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
     for kp in (2, 4):

@@ -160,12 +160,12 @@ def test_gemm_integer_stage_is_exact(q4k):
 
 
 @pytest.mark.parametrize("ksplit", [1, 2, 3, 8])
-def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit, monkeypatch):
+def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit):
     """Launches with fewer tiles than SMs split K over several CTAs per tile (turnstile epilogue: parts add in K order).
     Same exact-float construction as above at K = 2048: any lost / doubled superblock or a race in the turnstile shows as a
     wrong integer; two runs give identical bits."""
     from oracle import port
-    monkeypatch.setenv("Q4K_DBG_GEMM_KSPLIT", str(ksplit))
+    q4k.debug_set("gemm_ksplit", ksplit)
     rng = np.random.default_rng(11)
     M, K, N = 200, 2048, 40
     w = rng.integers(0, 256, (M, K // 256, 144), dtype=np.uint8)
@@ -181,8 +181,11 @@ def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit, monk
             _, si, sm = port.vec_dot_partials(w[m], xq[n])
             want[n, m] = int(si.sum()) - int(sm.sum())
     assert np.abs(want).max() < 2 ** 24
-    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
-    again = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    try:
+        got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+        again = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    finally:
+        q4k.debug_set("gemm_ksplit", 0)
     assert np.array_equal(got, want.astype(np.float32))
     assert np.array_equal(got.view(np.uint32), again.view(np.uint32))
 

@@ -26,12 +26,12 @@ for q6 in (False, True):
         res = {}
         for name, lim in (("fused", 1 << 30), ("separate", 0)):
             if q6:
-                os.environ["Q6K_DBG_FUSE_LIMIT"] = str(lim)
+                q4k_b200.debug_set("q6k_fuse_limit", lim)
             else:
                 lib.q4k_debug_set_fuse_limit(lim)
             us = graph_time_us(lambda i: f(w[i % copies], x, dst, ws), per_graph=max(copies, 20))
             res[name] = round(us, 2)
         lib.q4k_debug_set_fuse_limit(16384)
-        os.environ.pop("Q6K_DBG_FUSE_LIMIT", None)
+        q4k_b200.debug_set("q6k_fuse_limit", 32768)
         print(dict(type="q6_K" if q6 else "q4_K", M=M, K=K, **res, best_gbs=round((wbytes + K * 4 + M * 4) / min(res.values()) / 1e3, 1)), flush=True)
         del w
