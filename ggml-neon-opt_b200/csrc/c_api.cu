@@ -287,15 +287,51 @@ int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, si
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 
-int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
-                       const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
-                       int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev, void *stream) {
-    if (K <= 0 || K % Q4K_QK_K != 0 || row0 < 0 || nrows < 0 || N < 0) return Q4K_ERR_BAD_SHAPE;
-    if (nrows == 0 || N == 0) return Q4K_OK;
-    if (!w_dev || !xq_dev || !p_dev || !sumi_dev || !summ_dev || !aligned16(w_dev) || (w_row_stride_bytes & 15)) return Q4K_ERR_BAD_POINTER;
-    cudaError_t e = launch_debug_partials(w_dev, K, w_row_stride_bytes, row0, nrows, xq_dev, N, xq_row_stride_bytes,
-                                          p_dev, sumi_dev, summ_dev, (cudaStream_t)stream);
-    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                     const float *x_dev, int64_t N, int64_t x_row_stride_bytes, float *dst_dev,
+                     int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev,
+                     void *workspace_dev, size_t workspace_bytes, void *stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (kernel < Q4K_DUMP_DISPATCH || kernel > Q4K_DUMP_GEMM) return Q4K_ERR_UNSUPPORTED;
+    if (!w_dev || !x_dev || !dst_dev || !sumi_dev || !summ_dev) return Q4K_ERR_BAD_POINTER;
+    const int64_t nb = K / Q4K_QK_K;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
+    if (!workspace_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
+    cudaStream_t st = (cudaStream_t)stream;
+    // which product kernel: the one q4k_mul_mat would launch for this shape, unless the caller names one
+    const bool gemm = kernel == Q4K_DUMP_GEMM || (kernel == Q4K_DUMP_DISPATCH && N > Q4K_GEMV_GEMM_MIN_N && knobs().gemm_enabled);
+    if (gemm) {
+        if (N <= Q4K_GEMV_MAX_N) return Q4K_ERR_UNSUPPORTED;
+        const IntDump d{nullptr, sumi_dev, summ_dev};
+        const cudaError_t e = launch_gemm_q4k_f32(w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev, M * 4,
+                                                  workspace_dev, st, &d);
+        return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+    }
+    if (!p_dev) return Q4K_ERR_BAD_POINTER;
+    const bool exact = kernel == Q4K_DUMP_BULK_EXACT || (kernel == Q4K_DUMP_DISPATCH && gemv_exact_for((int)N));
+    const int which = kernel == Q4K_DUMP_DISPATCH ? 0 : (kernel == Q4K_DUMP_TENSOR_PIPE ? 1 : (kernel == Q4K_DUMP_BIG ? 3 : 2));
+    int64_t step = Q4K_GEMV_MAX_N;
+    for (int64_t n0 = 0; n0 < N;) {
+        const int nn = (int)((N - n0) < step ? (N - n0) : step);
+        const IntDump d{p_dev + n0 * M * nb * 8, sumi_dev + n0 * M * nb, summ_dev + n0 * M * nb};
+        const float *xs = (const float *)((const char *)x_dev + n0 * x_row_stride_bytes);
+        const void *xq = nullptr;
+        int64_t xstride = x_row_stride_bytes;
+        if ((int64_t)nn * K > knobs().fuse_limit) {             // as q4k_mul_mat: long activations go through the standalone quantizer
+            const cudaError_t eq = launch_quantize_q8_K(xs, workspace_dev, K, nn, x_row_stride_bytes, st);
+            if (eq != cudaSuccess) return cuda_fail(eq);
+            xq = workspace_dev; xs = nullptr; xstride = nb * Q4K_BLOCK_Q8K;
+        }
+        const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M, K, w_row_stride_bytes, xq, xs, nn, xstride, dst_dev + n0 * M, M * 4,
+                                                      exact, 0, knobs().pdl != 0, st, nullptr, 0, 0, &d, which);
+        if (e == cudaErrorNotSupported && nn > 1) { step = nn / 2; continue; }     // activations too long for one residency: fewer columns
+        if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;
+        if (e != cudaSuccess) return cuda_fail(e);
+        n0 += nn;
+    }
+    return Q4K_OK;
 }
 
 int q4k_mul_mat_host_async(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,

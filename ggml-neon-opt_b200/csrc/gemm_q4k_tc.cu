@@ -94,6 +94,7 @@ struct GemmParams {
     int64_t dst_stride;     // floats between dst columns
     int ksplit;             // CTAs along K per output tile (gridDim.z); 1 = the tile's CTA owns all of K
     int *flags;             // ksplit > 1: one zero-initialised turnstile word per output tile
+    int32_t *dump_sumi, *dump_summ;   // DUMP instantiation (parity): [(n*M + m)*nb + b] = the integers the epilogue read from TMEM
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -308,6 +309,8 @@ __device__ __forceinline__ void producer_mins(uint8_t *am_tile, int row, const u
     *reinterpret_cast<uint4 *>(dst + LBO_BYTES) = make_uint4(m1[0], m1[1], m1[2], m1[3]);
 }
 
+// DUMP: parity instantiation — the same code; the epilogue also writes out every superblock's sumi (= 8 hi + lo) and summ
+template <bool DUMP>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -399,6 +402,17 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
                         const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
+                        if constexpr (DUMP) {
+                            const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 8 * c8 + 2 * i;
+                            if (row < p.M && n < p.N) {
+                                p.dump_sumi[(n * p.M + row) * p.nb + kb0 + kb] = s0;
+                                p.dump_summ[(n * p.M + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
+                            }
+                            if (row < p.M && n + 1 < p.N) {
+                                p.dump_sumi[((n + 1) * p.M + row) * p.nb + kb0 + kb] = s1;
+                                p.dump_summ[((n + 1) * p.M + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
+                            }
+                        }
                         uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
                         t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
                         acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
@@ -689,7 +703,8 @@ static cudaError_t make_weight_map(CUtensorMap *map, const void *w, int64_t M, i
 // x == nullptr: the quantized copy in `workspace` is reused (q4k_mul_mat_reuse) — one launch.
 cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
-                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream) {
+                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream,
+                                const IntDump *dump) {
     if (M == 0 || N == 0) return cudaSuccess;
     const int64_t nb = K / QK_K;
     const int64_t ntiles = (N + BN - 1) / BN;             // whole column tiles; columns >= N hold stale bytes, never stored
@@ -728,8 +743,10 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
     p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
     p.ksplit = ksplit; p.flags = flags;
+    p.dump_sumi = dump ? dump->sumi : nullptr; p.dump_summ = dump ? dump->summ : nullptr;
+    auto kern = dump ? gemm_q4k_tc_kernel<true> : gemm_q4k_tc_kernel<false>;
     constexpr size_t smem = SMEM_TOTAL;
-    if ((e = ensure_max_dynamic_smem((const void *)gemm_q4k_tc_kernel, (int)smem)) != cudaSuccess) return e;
+    if ((e = ensure_max_dynamic_smem((const void *)kern, (int)smem)) != cudaSuccess) return e;
     const dim3 grid((unsigned)ntiles, (unsigned)mtiles, (unsigned)ksplit);              // column tiles of one row tile run together (L2)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
@@ -738,7 +755,7 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     cfg.stream = stream;
     cfg.attrs = pdl_attr;
     cfg.numAttrs = knobs().pdl ? 1 : 0;
-    e = cudaLaunchKernelEx(&cfg, gemm_q4k_tc_kernel, p);
+    e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
     return e;
 }

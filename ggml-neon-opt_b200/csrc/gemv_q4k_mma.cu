@@ -65,8 +65,16 @@ template <int N> struct MmaCfg {
 
 // ---- one superblock column of a slot, N == 1 ---------------------------------------------------------------------
 // acc[0] / accm[0]: row r, acc[1] / accm[1]: row r + 8 (partial over this lane's chunk)
+// dump (DUMP instantiations only): the integers of this (tile, superblock) go out as the kernel computed them
+struct DumpAt {
+    int32_t *p, *sumi, *summ;
+    int64_t row0, M;          // first row of the tile, rows of the matrix
+    int kb, nb;
+};
+
+template <bool DUMP>
 __device__ __forceinline__ void sb_step_n1(const uint8_t *slot_sb, const uint8_t *y0, const uint8_t *y1, const uint8_t *yblk, float yd,
-                                           int lane, float (&acc)[2], float (&accm)[2]) {
+                                           int lane, float (&acc)[2], float (&accm)[2], const DumpAt &da) {
     constexpr int PITCH = MmaCfg<1>::PITCH;
     const int r = lane >> 2, c = lane & 3;
     const uint8_t *p0 = slot_sb + r * PITCH, *p1 = p0 + 8 * PITCH;
@@ -93,6 +101,22 @@ __device__ __forceinline__ void sb_step_n1(const uint8_t *slot_sb, const uint8_t
     const int s1 = ((int)((sc1 & 0xffu) << 4) * (ce[2] + co[2]) + (int)(sc1 >> 8) * (ce[3] + co[3])) >> 4;
     const int psw = *reinterpret_cast<const int *>(yblk + 256 + 4 * c);      // pair sums of sub-blocks 2c, 2c + 1
     const int m0 = __dp2a_lo(psw, (int)mn0, 0), m1 = __dp2a_lo(psw, (int)mn1, 0);
+    if constexpr (DUMP) {
+        // C[row][j] IS p[j]: lane (r, c) holds sub-blocks 2c (exact) and 2c + 1 (x16) of rows r and r + 8
+        const int64_t r0 = da.row0 + r, r1 = r0 + 8;
+        if (r0 < da.M) { int32_t *o = da.p + ((r0 * da.nb) + da.kb) * 8 + 2 * c; o[0] = ce[0] + co[0]; o[1] = (ce[1] + co[1]) >> 4; }
+        if (r1 < da.M) { int32_t *o = da.p + ((r1 * da.nb) + da.kb) * 8 + 2 * c; o[0] = ce[2] + co[2]; o[1] = (ce[3] + co[3]) >> 4; }
+        int t0 = s0, t1 = s1, u0 = m0, u1 = m1;               // the four chunk lanes of a row add up to sumi / summ
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            t0 += __shfl_xor_sync(0xffffffffu, t0, o); t1 += __shfl_xor_sync(0xffffffffu, t1, o);
+            u0 += __shfl_xor_sync(0xffffffffu, u0, o); u1 += __shfl_xor_sync(0xffffffffu, u1, o);
+        }
+        if (c == 0) {
+            if (r0 < da.M) { da.sumi[r0 * da.nb + da.kb] = t0; da.summ[r0 * da.nb + da.kb] = u0; }
+            if (r1 < da.M) { da.sumi[r1 * da.nb + da.kb] = t1; da.summ[r1 * da.nb + da.kb] = u1; }
+        }
+    }
     const float2 dd0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));   // {d, dmin}
     const float2 dd1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
     acc[0] = __fmaf_rn(__fmul_rn(yd, dd0.x), (float)s0, acc[0]);
@@ -105,9 +129,9 @@ __device__ __forceinline__ void sb_step_n1(const uint8_t *slot_sb, const uint8_t
 // acc[2 * i + k]: row r + 8 i, batch column 2c + k (complete sums: the MMA reduces over the whole sub-block)
 // ycol: this lane's B column (batch column lane / 4) block, or a zero block when lane / 4 >= N
 // ylo / yhi: the blocks of batch columns 2c and 2c + 1 (for the min products and dy), clamped to a valid column
-template <int N>
+template <int N, bool DUMP>
 __device__ __forceinline__ void sb_step_nn(const uint8_t *slot_sb, const uint8_t *ycol, const uint8_t *ylo, const uint8_t *yhi,
-                                           float yd_lo, float yd_hi, int lane, float (&acc)[4], float (&accm)[4]) {
+                                           float yd_lo, float yd_hi, int lane, float (&acc)[4], float (&accm)[4], const DumpAt &da) {
     constexpr int PITCH = MmaCfg<N>::PITCH;
     const int r = lane >> 2, c = lane & 3;
     const uint8_t *p0 = slot_sb + r * PITCH, *p1 = p0 + 8 * PITCH;
@@ -128,6 +152,17 @@ __device__ __forceinline__ void sb_step_nn(const uint8_t *slot_sb, const uint8_t
         s[1] += lo0 * cl[1] + hi0 * ch[1];
         s[2] += lo1 * cl[2] + hi1 * ch[2];
         s[3] += lo1 * cl[3] + hi1 * ch[3];
+        if constexpr (DUMP) {      // C[row][column] of this MMA pair IS p[2g] (and 16 x p[2g + 1]) of that (row, batch column)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int64_t row = da.row0 + r + 8 * (i >> 1);
+                const int col = 2 * c + (i & 1);
+                if (row < da.M && col < N) {
+                    int32_t *o = da.p + (((int64_t)col * da.M + row) * da.nb + da.kb) * 8 + 2 * g;
+                    o[0] = cl[i]; o[1] = ch[i] >> 4;
+                }
+            }
+        }
     }
     const float2 dd0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));
     const float2 dd1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
@@ -137,6 +172,18 @@ __device__ __forceinline__ void sb_step_nn(const uint8_t *slot_sb, const uint8_t
     const int mh0 = __dp2a_hi((int)ph.w, (int)u0.w, __dp2a_lo((int)ph.z, (int)u0.w, __dp2a_hi((int)ph.y, (int)u0.z, __dp2a_lo((int)ph.x, (int)u0.z, 0))));
     const int ml1 = __dp2a_hi((int)pl.w, (int)u1.w, __dp2a_lo((int)pl.z, (int)u1.w, __dp2a_hi((int)pl.y, (int)u1.z, __dp2a_lo((int)pl.x, (int)u1.z, 0))));
     const int mh1 = __dp2a_hi((int)ph.w, (int)u1.w, __dp2a_lo((int)ph.z, (int)u1.w, __dp2a_hi((int)ph.y, (int)u1.z, __dp2a_lo((int)ph.x, (int)u1.z, 0))));
+    if constexpr (DUMP) {
+        const int si[4] = {s[0] >> 4, s[1] >> 4, s[2] >> 4, s[3] >> 4}, sm[4] = {ml0, mh0, ml1, mh1};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t row = da.row0 + r + 8 * (i >> 1);
+            const int col = 2 * c + (i & 1);
+            if (row < da.M && col < N) {
+                da.sumi[((int64_t)col * da.M + row) * da.nb + da.kb] = si[i];
+                da.summ[((int64_t)col * da.M + row) * da.nb + da.kb] = sm[i];
+            }
+        }
+    }
     acc[0] = __fmaf_rn(__fmul_rn(yd_lo, dd0.x), (float)(s[0] >> 4), acc[0]);
     acc[1] = __fmaf_rn(__fmul_rn(yd_hi, dd0.x), (float)(s[1] >> 4), acc[1]);
     acc[2] = __fmaf_rn(__fmul_rn(yd_lo, dd1.x), (float)(s[2] >> 4), acc[2]);
@@ -175,7 +222,8 @@ constexpr int XD = 2;                     // split-K: exchange buffers (tiles in
 
 // MODE 0: K <= 8192 (one segment; the common decode shapes, everything about segments folds away), 1: several segments,
 // 2: several segments split over the CTAs of a cluster
-template <int N, int MODE>
+// DUMP: parity instantiation — the same code, and the integers it computed are also written out (q4k_mul_mat_dump)
+template <int N, int MODE, bool DUMP = false>
 __global__ void __launch_bounds__(MMA_THREADS, 2)
 gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     constexpr bool SPLITK = MODE == 2;
@@ -360,6 +408,12 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
     int s = 0, buf = 0;
     uint32_t parity = 0, pparity = 1;        // pparity: phase before the first one, the first PBUF waits fall through
     for (int64_t tile = t0; tile < t1; tile += tstep) {
+        DumpAt da{};
+        if constexpr (DUMP) {
+            int dmat = 0;
+            da.p = p.dump_p; da.sumi = p.dump_sumi; da.summ = p.dump_summ;
+            da.row0 = locate(tile, dmat) * MROWS; da.M = p.Mm[0]; da.nb = nb; da.kb = 0;
+        }
         for (int seg = seg0; seg < seg1; ++seg) {
             float acc[2 * Cfg::NC], accm[2 * Cfg::NC];
 #pragma unroll
@@ -372,20 +426,21 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
                 if (warp == 0 && tile == t0 && rd == seg0 * SEG_ROUNDS) TICK(5);
                 const int kb = rd * KW + warp;
                 if (kb < nb) {
+                    if constexpr (DUMP) da.kb = kb;
                     const uint8_t *slot_sb = slots + (size_t)s * Cfg::SLOT + warp * BLK_Q4K;
                     if constexpr (N == 1) {
                         const uint8_t *yblk = q8_s + q8_off(abase, kb, nb);
                         const int j = r;                                     // this lane's B column = sub-block j
                         const uint8_t *y0 = (j == 2 * c) ? yblk + 32 * j : zero_s;
                         const uint8_t *y1 = (j == 2 * c + 1) ? yblk + 32 * j : zero_s;
-                        sb_step_n1(slot_sb, y0, y1, yblk, d_s[abase * nb + kb], lane, acc, accm);
+                        sb_step_n1<DUMP>(slot_sb, y0, y1, yblk, d_s[abase * nb + kb], lane, acc, accm, da);
                     } else {
                         const int ncol = r;                                  // this lane's B column = batch column
                         const uint8_t *ycol = ncol < N ? q8_s + q8_off(abase + ncol, kb, nb) : zero_s;
                         const int nlo = min(2 * c, N - 1), nhi = min(2 * c + 1, N - 1);
-                        sb_step_nn<N>(slot_sb, ycol, q8_s + q8_off(abase + nlo, kb, nb),
-                                      q8_s + q8_off(abase + nhi, kb, nb),
-                                      d_s[(abase + nlo) * nb + kb], d_s[(abase + nhi) * nb + kb], lane, acc, accm);
+                        sb_step_nn<N, DUMP>(slot_sb, ycol, q8_s + q8_off(abase + nlo, kb, nb),
+                                            q8_s + q8_off(abase + nhi, kb, nb),
+                                            d_s[(abase + nlo) * nb + kb], d_s[(abase + nhi) * nb + kb], lane, acc, accm, da);
                     }
                 }
                 __syncwarp();
@@ -472,10 +527,12 @@ int choose_kparts(int64_t tiles, int nb, int nrows /* staged activation rows */,
 template <int N>
 cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
     const size_t slot = MmaCfg<N>::SLOT;
-    const int KP = choose_kparts(p.n_groups, p.nb, N * p.nx, sm_count() * 2);
+    const bool dump = p.dump_p != nullptr;
+    const int KP = dump ? 1 : choose_kparts(p.n_groups, p.nb, N * p.nx, sm_count() * 2);   // a split part runs the same per-superblock code
     p.kparts = KP;
     const int mode = KP > 1 ? 2 : ((p.nb + KW - 1) / KW <= SEG_ROUNDS ? 0 : 1);
     auto kern = mode == 2 ? gemv_q4k_mma_kernel<N, 2> : (mode == 1 ? gemv_q4k_mma_kernel<N, 1> : gemv_q4k_mma_kernel<N, 0>);
+    if (dump) kern = mode == 1 ? gemv_q4k_mma_kernel<N, 1, true> : gemv_q4k_mma_kernel<N, 0, true>;
     const size_t fixed = mma_fixed_smem(N * p.nx, p.nb, N, 8, KP);
     // two CTAs per SM with as deep a ring as fits (<= 5 slots: 2 x 5 x 18 KB in flight per SM is past the latency-
     // bandwidth product); one CTA per SM when the staged activations are too large for that
@@ -532,8 +589,9 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
 cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, const float *const *xf, int N, int64_t x_row_stride_bytes,
                                 float *const *dst, int64_t dst_col_stride_bytes, float *const *peer_dst, int n_peers,
-                                int64_t dst_row0, bool pdl, cudaStream_t stream) {
+                                int64_t dst_row0, bool pdl, cudaStream_t stream, const IntDump *dump) {
     if (nmat < 1 || nmat > 4 || N < 1 || N > 8 || n_peers > 8) return cudaErrorInvalidValue;
+    if (dump && nmat != 1) return cudaErrorInvalidValue;
     TmaGemvParams p;
     p.w = (const uint8_t *)w[0]; p.M = M[0]; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
     p.xq = (const uint8_t *)xq; p.xf = xf ? xf[0] : nullptr; p.x_stride = x_row_stride_bytes;
@@ -544,6 +602,7 @@ cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M
     p.dst_stride = dst_col_stride_bytes > 0 ? dst_col_stride_bytes / 4 : M[0];      // 0 = dense [N][M]
     p.stages = 0; p.nmat = nmat; p.nx = 0;
     fill_sync(p, nmat == 1 ? n_peers : 0);
+    if (dump) { p.dump_p = dump->p; p.dump_sumi = dump->sumi; p.dump_summ = dump->summ; }
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     int64_t tiles = 0;
     for (int i = 0; i < nmat; ++i) {

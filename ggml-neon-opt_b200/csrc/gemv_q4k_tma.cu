@@ -47,7 +47,8 @@ namespace {
 // chains over the 32-byte nibble chunks, summed (c0 + c1) + (c2 + c3) at the end of every 32-superblock segment, the
 // eight classes in order, the segments in K order — bit-identical to that kernel, so large matrices can take this
 // (copy-engine-bound, faster above ~34 MB) kernel without a row's bits depending on the size of its matrix.
-template <int N, int ORD>
+// DUMP: parity instantiation — the same code, and the integers it computed are also written out (q4k_mul_mat_dump)
+template <int N, int ORD, bool DUMP = false>
 __global__ void __launch_bounds__(WARPS * 32, 2)
 gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     constexpr bool EXACT = ORD == 1, MMAORD = ORD == 2;
@@ -164,10 +165,13 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
             const uint4 sm = unpack_scales_mins(hdr);
             const float2 dd = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));   // {d, dmin}
             int sum16[N][EXACT ? 8 : 1];
+            int dsumi[N];                                   // DUMP only: the superblock's sumi as this kernel's integers give it
 #pragma unroll
-            for (int n = 0; n < N; ++n)
+            for (int n = 0; n < N; ++n) {
+                dsumi[n] = 0;
 #pragma unroll
                 for (int t = 0; t < (EXACT ? 8 : 1); ++t) sum16[n][t] = 0;
+            }
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
                 const uint32_t qw[8] = {q[2 * g].x, q[2 * g].y, q[2 * g].z, q[2 * g].w,
@@ -181,11 +185,18 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                     const uint32_t ylo[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
                     const uint32_t yhi[8] = {y2.x, y2.y, y2.z, y2.w, y3.x, y3.y, y3.z, y3.w};
                     if (EXACT) {
+                        int dpl = 0, dph = 0;
 #pragma unroll
                         for (int t = 0; t < 8; ++t) {
                             const int dl = __dp4a((int)(qw[t] & 0x0f0f0f0fu), (int)ylo[t], 0);
                             const int dh = dp4a_u8s8(qw[t] & 0xf0f0f0f0u, yhi[t], 0);
                             sum16[n][t] += sc_lo16 * dl + sc_hi * dh;
+                            if constexpr (DUMP) { dpl += dl; dph += dh; }
+                        }
+                        if constexpr (DUMP) {
+                            int32_t *o = p.dump_p + ((((int64_t)n * p.Mm[0] + (int64_t)lgrp * TILE_ROWS + r) * nb) + kb) * 8 + 2 * g;
+                            if ((int64_t)lgrp * TILE_ROWS + r < p.Mm[0]) { o[0] = dpl; o[1] = dph >> 4; }
+                            dsumi[n] += (sc_lo16 * dpl + sc_hi * dph) >> 4;
                         }
                     } else {
                         int pl = 0, ph = 0;
@@ -193,6 +204,11 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                         for (int t = 0; t < 8; ++t) {
                             pl = __dp4a((int)(qw[t] & 0x0f0f0f0fu), (int)ylo[t], pl);
                             ph = dp4a_u8s8(qw[t] & 0xf0f0f0f0u, yhi[t], ph);
+                        }
+                        if constexpr (DUMP) {
+                            int32_t *o = p.dump_p + ((((int64_t)n * p.Mm[0] + (int64_t)lgrp * TILE_ROWS + r) * nb) + kb) * 8 + 2 * g;
+                            if ((int64_t)lgrp * TILE_ROWS + r < p.Mm[0]) { o[0] = pl; o[1] = ph >> 4; }
+                            dsumi[n] += (sc_lo16 * pl + sc_hi * ph) >> 4;
                         }
                         if (MMAORD) {
                             const float dall = __fmul_rn(d_s[(abase + n) * nb + kb], dd.x);
@@ -211,6 +227,13 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                 // _mm_madd_epi16(mins, hadd(bsums)): prod_i = m[2i] * ps[2i] + m[2i+1] * ps[2i+1]
                 const int p0 = __dp2a_lo((int)ps.x, (int)sm.z, 0), p1 = __dp2a_hi((int)ps.y, (int)sm.z, 0);
                 const int p2 = __dp2a_lo((int)ps.z, (int)sm.w, 0), p3 = __dp2a_hi((int)ps.w, (int)sm.w, 0);
+                if constexpr (DUMP) {
+                    const int64_t drow = (int64_t)lgrp * TILE_ROWS + r;
+                    if (drow < p.Mm[0]) {
+                        p.dump_sumi[((int64_t)n * p.Mm[0] + drow) * nb + kb] = dsumi[n];
+                        p.dump_summ[((int64_t)n * p.Mm[0] + drow) * nb + kb] = p0 + p1 + p2 + p3;
+                    }
+                }
                 if (EXACT) {
                     int *row = scratch + n * SCR_WORDS + r * SCR_ROW;
 #pragma unroll
@@ -332,7 +355,7 @@ constexpr size_t PER_STAGE = (size_t)WARPS * (STAGE_BYTES + 16);
 template <int N, int ORD>
 cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
     constexpr bool EXACT = ORD == 1;
-    auto kern = gemv_q4k_tma_kernel<N, ORD>;
+    auto kern = p.dump_p ? gemv_q4k_tma_kernel<N, ORD, true> : gemv_q4k_tma_kernel<N, ORD>;
     const size_t fixed = fixed_smem(N * p.nx, p.nb, EXACT, N);
     if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
     // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits
@@ -388,9 +411,14 @@ cudaError_t launch_tma_e(int N, const TmaGemvParams &p, int stages, bool pdl, cu
 cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                     const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
-                                    bool pdl, cudaStream_t stream, float *const *peer_dst, int n_peers, int64_t dst_row0) {
+                                    bool pdl, cudaStream_t stream, float *const *peer_dst, int n_peers, int64_t dst_row0,
+                                    const IntDump *dump, int dump_kernel) {
+    // dump != nullptr (parity): dump_kernel picks the product kernel whose integers are wanted — 0 = whatever the dispatch
+    // below picks, 1 = the tensor-pipe kernel, 2 = the bulk-copy kernel in the order `exact_order` says, 3 = the bulk-copy
+    // kernel in the tensor-pipe float association (the large-matrix launch, N == 1)
     if (M == 0 || N == 0) return cudaSuccess;
     if (n_peers > 8) return cudaErrorInvalidValue;
+    if (dump && dump_kernel == 3 && N != 1) return cudaErrorInvalidValue;
     // Large single-column launches: the lane-per-superblock kernel in the tensor-pipe kernel's float association (ORD 2,
     // identical bits) — it runs at the bulk-copy ceiling where the 16-row tensor-pipe tiles do not (measured on B200:
     // 28672x8192 24.1 vs 26.3 us, 8192x28672 29.3 vs 33.8 us, 8192x8192 10.3 vs 10.7 us; 4096x14336 14.7 vs 12.5 us, so
@@ -398,16 +426,20 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     // (long K with few rows — a 4096 x 28672 shard — stays on the tensor-pipe kernel, whose cluster split-K wins there:
     // 20.6 vs 22.4 us, profiles/r1_shard_ab_2gpu.txt; the threshold 1 = "always" of the tests skips the row rule)
     const int64_t big_bytes = knobs().big_matrix_bytes;
-    const bool big = N == 1 && !exact_order && stages <= 0 && big_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= big_bytes &&
-                     (M >= 8192 || big_bytes == 1);
-    if (!big && !exact_order && stages <= 0 && !knobs().mma_off) {      // tolerance order: the tensor-pipe kernel
+    bool big = N == 1 && !exact_order && stages <= 0 && big_bytes > 0 && M * (K / QK_K) * BLK_Q4K >= big_bytes &&
+               (M >= 8192 || big_bytes == 1);
+    bool mma = !big && !exact_order && stages <= 0 && !knobs().mma_off;
+    if (dump && dump_kernel == 1) { big = false; mma = true; }
+    if (dump && dump_kernel == 2) { big = false; mma = false; }
+    if (dump && dump_kernel == 3) { big = true; mma = false; }
+    if (mma) {      // tolerance order: the tensor-pipe kernel
         const void *wv[1] = {w};
         const int64_t Mv[1] = {M};
         const float *xv[1] = {xf};
         float *dv[1] = {dst};
         const cudaError_t e = launch_gemv_q4k_mma(1, wv, Mv, K, w_row_stride_bytes, xq, xq ? nullptr : xv, N, x_row_stride_bytes, dv,
-                                                  dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream);
-        if (e != cudaErrorNotSupported) return e;
+                                                  dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream, dump);
+        if (e != cudaErrorNotSupported || dump) return e;
     }
     TmaGemvParams p;
     p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)(K / QK_K);
@@ -421,11 +453,12 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.stages = 0; p.interleave = 0; p.kparts = 1;
     p.nmat = 1; p.nx = 1;
     fill_sync(p, n_peers);
+    if (dump) { p.dump_p = dump->p; p.dump_sumi = dump->sumi; p.dump_summ = dump->summ; }
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
     if (big) {
         const cudaError_t e = launch_tma_n<1, 2>(p, stages, pdl, stream);
-        if (e != cudaErrorNotSupported) return e;
+        if (e != cudaErrorNotSupported || dump) return e;
         const void *wv[1] = {w};                       // activations too long for this kernel's residency: the tensor-pipe kernel
         const int64_t Mv[1] = {M};
         const float *xv[1] = {xf};

@@ -53,9 +53,14 @@ struct TmaGemvParams {
     uint32_t *sync_flags[8];
     uint32_t *sync_epoch, *sync_done;
     int sync_world, sync_rank;
+    // parity tooling (DUMP instantiations of the product kernels, nmat == 1): the integer stage of every (column n, row m,
+    // superblock b) as the kernel computed it — p[((n*M + m)*nb + b)*8 + j] = the sub-block dot products, sumi / summ
+    // [(n*M + m)*nb + b] (L/ggml/src/ggml-cpu/quants.c:575-611: aux32 -> sumi, and the mins sum)
+    int32_t *dump_p, *dump_sumi, *dump_summ;
 };
 
 inline void fill_sync(TmaGemvParams &p, int n_peers) {
+    p.dump_p = p.dump_sumi = p.dump_summ = nullptr;
     for (int r = 0; r < 8; ++r) p.sync_flags[r] = nullptr;
     p.sync_epoch = p.sync_done = nullptr; p.sync_world = 0; p.sync_rank = 0;
     if (t_sync_req && !t_sync_req->taken && n_peers > 0) {

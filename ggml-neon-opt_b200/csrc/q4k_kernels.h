@@ -10,6 +10,10 @@ namespace q4k {
 
 void count_launch();          // bumps the process-wide kernel launch counter (q4k_kernel_launches)
 
+// parity tooling: where a DUMP instantiation of a product kernel writes the integers it computed
+// (p[((n*M + m)*nb + b)*8 + j], sumi / summ[(n*M + m)*nb + b]; p may be null for the GEMM, which never forms p[j])
+struct IntDump { int32_t *p, *sumi, *summ; };
+
 cudaError_t launch_quantize_q8_K(const float *x, void *y, int64_t k, int64_t nrows, int64_t x_row_stride_bytes,
                                  cudaStream_t stream);
 
@@ -27,7 +31,8 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
                                     const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
                                     bool pdl, cudaStream_t stream,
-                                    float *const *peer_dst = nullptr, int n_peers = 0, int64_t dst_row0 = 0);
+                                    float *const *peer_dst = nullptr, int n_peers = 0, int64_t dst_row0 = 0,
+                                    const IntDump *dump = nullptr, int dump_kernel = 0);
 
 // up to 4 matrices (same K, N) in one launch; see gemv_q4k_tma.cu
 cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
@@ -38,7 +43,7 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
 cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, const float *const *xf, int N, int64_t x_row_stride_bytes,
                                 float *const *dst, int64_t dst_col_stride_bytes, float *const *peer_dst, int n_peers,
-                                int64_t dst_row0, bool pdl, cudaStream_t stream);
+                                int64_t dst_row0, bool pdl, cudaStream_t stream, const IntDump *dump = nullptr);
 
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
@@ -49,16 +54,13 @@ cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_r
 size_t gemm_workspace_bytes(int64_t K, int64_t N);
 cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                                 const float *x, int64_t N, int64_t x_row_stride_bytes,
-                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream);
+                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream,
+                                const IntDump *dump = nullptr);
 
 // Q6_K decode GEMV (gemv_q6k.cu), 1 <= N <= 8; dump != nullptr also writes the per-superblock integer sums
 cudaError_t launch_gemv_q6k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                             const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                             float *dst, int64_t dst_col_stride_bytes, int32_t *dump, bool pdl, cudaStream_t stream);
-
-cudaError_t launch_debug_partials(const void *w, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
-                                  const void *xq, int64_t N, int64_t xq_row_stride_bytes,
-                                  int32_t *p, int32_t *sumi, int32_t *summ, cudaStream_t stream);
 
 // request handed from the C ABI (q4k_mul_mat_peers_sync) to whichever launcher ends up launching the single decode kernel
 // of the call: the kernel's last CTA then performs the cross-GPU flag exchange itself (gemv_stage.cuh peer_sync_tail)

@@ -51,7 +51,7 @@ def load():
         L.q4k_mul_mat_reuse.argtypes = [vp, i64, i64, i64, i64, vp, i64, vp, sz, vp]
         L.q4k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q4k_vec_dot_q4_K_q8_K.argtypes = [i32, vp, sz, vp, sz, vp, sz, i32]
-        L.q4k_debug_partials.argtypes = [vp, i64, i64, i64, i64, vp, i64, i64, vp, vp, vp, vp]
+        L.q4k_mul_mat_dump.argtypes = [i32, vp, i64, i64, i64, vp, i64, i64, vp, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_host.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_host_async.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_peers.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp]
@@ -196,20 +196,28 @@ def vec_dot_q4_K_q8_K(n: int, s: torch.Tensor, bs: int, vx: torch.Tensor, bx: in
         _check("q4k_vec_dot_q4_K_q8_K", load().q4k_vec_dot_q4_K_q8_K(n, s.data_ptr(), bs, vx.data_ptr(), bx, vy.data_ptr(), by, nrc))
 
 
-def debug_partials(w: torch.Tensor, xq: torch.Tensor, row0: int = 0, nrows: int | None = None):
-    """-> (p [N, nrows, nb, 8], sumi [N, nrows, nb], summ [N, nrows, nb]) int32."""
+DUMP_DISPATCH, DUMP_TENSOR_PIPE, DUMP_BULK, DUMP_BULK_EXACT, DUMP_BIG, DUMP_GEMM = range(6)
+
+
+def mul_mat_dump(w: torch.Tensor, x: torch.Tensor, kernel: int = DUMP_DISPATCH):
+    """q4k_mul_mat through the DUMP instantiation of a PRODUCT kernel (q4k_mul_mat_dump).
+    -> (dst [N, M] f32, p [N, M, nb, 8] int32 or None for the GEMM, sumi [N, M, nb], summ [N, M, nb]).
+    The integer buffers are pre-filled with a sentinel, so anything the kernel did not write shows up."""
     _dev_u8(w, "w")
-    _dev_u8(xq, "xq")
-    nb = w.shape[1] // Q4K_BLOCK
-    nrows = w.shape[0] - row0 if nrows is None else nrows
-    N = xq.shape[0]
-    p = torch.zeros((N, nrows, nb, 8), dtype=torch.int32, device=w.device)
-    si = torch.zeros((N, nrows, nb), dtype=torch.int32, device=w.device)
-    sm = torch.zeros((N, nrows, nb), dtype=torch.int32, device=w.device)
+    M, nb = w.shape[0], w.shape[1] // Q4K_BLOCK
+    N, K = x.shape
+    SENT = -0x7f7f7f7f
+    gemm = kernel == DUMP_GEMM or (kernel == DUMP_DISPATCH and N > 12)
+    p = None if gemm else torch.full((N, M, nb, 8), SENT, dtype=torch.int32, device=w.device)
+    si = torch.full((N, M, nb), SENT, dtype=torch.int32, device=w.device)
+    sm = torch.full((N, M, nb), SENT, dtype=torch.int32, device=w.device)
+    dst = torch.empty((N, M), dtype=torch.float32, device=w.device)
+    ws = torch.empty(max(workspace_bytes(K, N), 16), dtype=torch.uint8, device=w.device)
     with torch.cuda.device(w.device):
-        _check("q4k_debug_partials", load().q4k_debug_partials(w.data_ptr(), nb * QK_K, w.stride(0), row0, nrows, xq.data_ptr(), N,
-                                                               xq.stride(0), p.data_ptr(), si.data_ptr(), sm.data_ptr(), _stream()))
-    return p, si, sm
+        _check("q4k_mul_mat_dump", load().q4k_mul_mat_dump(kernel, w.data_ptr(), M, K, w.stride(0), x.data_ptr(), N, x.stride(0) * 4, dst.data_ptr(),
+                                                           p.data_ptr() if p is not None else 0, si.data_ptr(), sm.data_ptr(),
+                                                           ws.data_ptr(), ws.numel(), _stream()))
+    return dst, p, si, sm
 
 
 def mul_mat_q6k(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None,

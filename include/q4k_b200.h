@@ -166,11 +166,26 @@ int q4k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride
 int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, size_t bx,
                           const void *vy_dev, size_t by, int nrc);
 
-/* debug / parity: integer stage of the dot product for rows [row0,row0+nrows) x all N columns:
- * p[(n*nrows + r)*nb*8 + b*8 + j], sumi[(n*nrows + r)*nb + b], summ[...] as int32. */
-int q4k_debug_partials(const void *w_dev, int64_t K, int64_t w_row_stride_bytes, int64_t row0, int64_t nrows,
-                       const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
-                       int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev, void *stream);
+/* debug / parity: q4k_mul_mat through a DUMP instantiation of the PRODUCT kernel itself — the same
+ * code, compiled with a flag that also writes out the integers it computed (the generic reference materialises them:
+ * L/ggml/src/ggml-cpu/quants.c:575-611, aux32 -> sumi, and the mins sum):
+ *   p_dev   [((n*M + m)*nb + b)*8 + j]  int32  dot product of sub-block j of superblock b (row m, column n)
+ *   sumi_dev[(n*M + m)*nb + b]          int32  sum_j sc[j] * p[j]
+ *   summ_dev[(n*M + m)*nb + b]          int32  sum_j m[j] * bsum32[j]
+ * dst_dev = dense [N][M] fp32 results of the same launch.  `kernel` picks the product kernel: */
+enum {
+    Q4K_DUMP_DISPATCH    = 0,    /* whatever q4k_mul_mat launches for this shape (decode kernel, or the GEMM for N > 12) */
+    Q4K_DUMP_TENSOR_PIPE = 1,    /* gemv_q4k_mma_kernel (the default decode kernel; p[j] are its MMA C fragments) */
+    Q4K_DUMP_BULK        = 2,    /* gemv_q4k_tma_kernel, default float order */
+    Q4K_DUMP_BULK_EXACT  = 3,    /* gemv_q4k_tma_kernel in the reference's AVX2 order */
+    Q4K_DUMP_BIG         = 4,    /* gemv_q4k_tma_kernel in the tensor-pipe association: the large-matrix launch, N == 1 */
+    Q4K_DUMP_GEMM        = 5,    /* gemm_q4k_tc_kernel: sumi = 8 hi + lo and summ as the epilogue reads them from TMEM; p_dev unused
+                                  * (the tensor core never forms p[j]: the scales are folded into the A operand), N > 8 */
+};
+int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                     const float *x_dev, int64_t N, int64_t x_row_stride_bytes, float *dst_dev,
+                     int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev,
+                     void *workspace_dev, size_t workspace_bytes, void *stream);
 
 /* Development / test knobs.  None of them is process-global mutable state: the defaults are read from the environment once
  * (Q4K_GEMV_ORDER, Q4K_DBG_*), and every setter below changes the CALLING THREAD's copy only, so backend instances driven by

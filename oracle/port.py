@@ -144,6 +144,32 @@ def vec_dot_partials(wrow: np.ndarray, yrow: np.ndarray):
     return p, si, sm
 
 
+def partials_matrix(w: np.ndarray, xq: np.ndarray):
+    """The integer stage for every (column n, row m, superblock b) at once, in numpy (int64 arithmetic, int32 results):
+    -> (p [N, M, nb, 8], sumi [N, M, nb], summ [N, M, nb]).  Same definitions as vec_dot_partials — the generic reference's
+    aux32 / sumi / mins sum (L/ggml/src/ggml-cpu/quants.c:575-611) with get_scale_min_k4 (L/ggml/src/ggml-quants.c:703-710)."""
+    w = np.ascontiguousarray(w, dtype=np.uint8)
+    xq = np.ascontiguousarray(xq, dtype=np.uint8)
+    M, nb = w.shape[0], w.shape[1] // Q4K_BLOCK
+    N = xq.shape[0]
+    blk = w.reshape(M, nb, Q4K_BLOCK)
+    s12 = blk[:, :, 4:16].astype(np.int64)
+    sc = np.empty((M, nb, 8), np.int64); mn = np.empty((M, nb, 8), np.int64)
+    sc[..., :4] = s12[..., 0:4] & 63
+    mn[..., :4] = s12[..., 4:8] & 63
+    sc[..., 4:] = (s12[..., 8:12] & 15) | ((s12[..., 0:4] >> 6) << 4)
+    mn[..., 4:] = (s12[..., 8:12] >> 4) | ((s12[..., 4:8] >> 6) << 4)
+    qs = blk[:, :, 16:].reshape(M, nb, 4, 32)
+    q4 = np.stack([qs & 15, qs >> 4], axis=3).reshape(M, nb, 8, 32).astype(np.int32)      # sub-block 2g = low nibbles, 2g + 1 = high
+    yb = xq.reshape(N, nb, Q8K_BLOCK)
+    q8 = yb[:, :, 4:260].view(np.int8).reshape(N, nb, 8, 32).astype(np.int32)
+    bs = yb[:, :, 260:292].copy().view(np.int16).reshape(N, nb, 8, 2).astype(np.int64).sum(3)   # bsums pairs = 32-element sums
+    pj = np.einsum("mbjl,nbjl->nmbj", q4, q8, dtype=np.int64)
+    sumi = (pj * sc[None]).sum(3)
+    summ = np.einsum("mbj,nbj->nmb", mn, bs)
+    return pj.astype(np.int32), sumi.astype(np.int32), summ.astype(np.int32)
+
+
 def vec_dot(wrow: np.ndarray, yrow: np.ndarray, order: int = ORDER_AVX2) -> np.float32:
     wrow = np.ascontiguousarray(wrow, dtype=np.uint8)
     yrow = np.ascontiguousarray(yrow, dtype=np.uint8)

@@ -5,6 +5,7 @@ import numpy as np
 import pytest
 
 from conftest import make_acts, make_weights
+from parity_util import check
 from test_gpu_parity import assert_close, t
 
 pytestmark = pytest.mark.gpu
@@ -25,7 +26,7 @@ def test_mma_gemv_within_tolerance(q4k, fast_order, M, K, N):
     from oracle import port
     w, x = make_weights(M, K), make_acts(N, K)
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
-    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    check(f"tensor-pipe decode {M}x{K} N={N}", got, w, x)
 
 
 @pytest.mark.parametrize("N", [1, 2, 5, 8])
@@ -88,7 +89,7 @@ def test_mma_split_k_does_not_change_the_bits(q4k, fast_order, M, K, N):
     finally:
         q4k.debug_set("mma_kparts", 0)
     policy = q4k.mul_mat(wd, xd).cpu().numpy()
-    assert_close(outs[1], port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    check(f"tensor-pipe decode split-K {M}x{K} N={N}", outs[1], w, x)
     for kp in (2, 4):
         assert np.array_equal(outs[kp].view(np.uint32), outs[1].view(np.uint32)), kp
     assert np.array_equal(policy.view(np.uint32), outs[1].view(np.uint32))
@@ -118,7 +119,7 @@ def test_big_matrix_kernel_gives_the_tensor_pipe_kernels_bits(q4k, M, K):
         lib.q4k_debug_set_big_matrix_bytes(34 << 20)
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
     assert np.array_equal(a.view(np.uint32), aq.view(np.uint32)) and np.array_equal(a.view(np.uint32), bq.view(np.uint32))
-    assert_close(b, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    check(f"large-matrix decode {M}x{K}", b, w, x)
 
 
 @pytest.mark.parametrize("big", [0, 1])

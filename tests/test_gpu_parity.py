@@ -1,10 +1,12 @@
 """GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
-Bit-exact for Q8_K bytes and the int32 partial sums; fp32 outputs bit-identical to the AVX2-order
-oracle where the kernel runs the exact order, else within 1e-5 (tolerance defined in `assert_close`)."""
+Bit-exact for Q8_K bytes and the int32 partial sums (dumped by the PRODUCT kernels); fp32 outputs bit-identical to the
+AVX2-order oracle where the kernel runs the exact order, else judged by tests/parity_util.py (literal 1e-5 relative statistic,
+no worse than the reference's own variant spread, scaled 1e-5 bound)."""
 import numpy as np
 import pytest
 
 from conftest import make_acts, make_weights
+from parity_util import check, log, rel_err, TOL
 
 pytestmark = pytest.mark.gpu
 
@@ -14,10 +16,11 @@ def t(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
 
-def assert_close(got, ref, f64, tol=1e-5):
-    """|got - ref| <= tol * max(|ref|, rms of the column).  Pure elementwise-relative is not meaningful
-    for outputs that are the difference of two large sums: the reference's own variants (generic / AVX2 /
-    NEON order) differ from each other by up to ~7e-5 elementwise on such elements."""
+def assert_close(got, ref, f64, tol=TOL, name="q6k"):
+    """The scaled bound alone, |got - ref| <= tol * max(|ref|, rms of the column), with the literal statistic printed — for the
+    comparisons that have no generic-order companion at hand (Q6_K, plans).  Q4_K comparisons use parity_util.check."""
+    r = rel_err(got, ref)
+    log(name, {"n": int(got.size), "max_rel_vs_avx2": float(r.max(initial=0.0)), "n_above_1e-5_vs_avx2": int((r > tol).sum())})
     rms = np.sqrt((f64 ** 2).mean(axis=1, keepdims=True))
     bound = tol * np.maximum(np.abs(ref), rms)
     bad = np.abs(got.astype(np.float64) - ref.astype(np.float64)) > bound
@@ -44,16 +47,46 @@ def test_quantize_q8k_denormals_and_ties(q4k):
     assert np.array_equal(got, port.quantize_q8_K(x))
 
 
-@pytest.mark.parametrize("M,K,N", [(33, 512, 1), (64, 2048, 2), (40, 1024, 5), (16, 4096, 8)])
-def test_int32_partials_bit_exact(q4k, M, K, N):
+DECODE_KERNELS = ["DUMP_DISPATCH", "DUMP_TENSOR_PIPE", "DUMP_BULK", "DUMP_BULK_EXACT"]
+
+
+@pytest.mark.parametrize("kernel", DECODE_KERNELS)
+@pytest.mark.parametrize("M,K,N", [(33, 512, 1), (64, 2048, 2), (40, 1024, 5), (16, 4096, 8), (100, 2048, 1), (50, 14336, 1), (21, 8448, 3), (37, 28672, 1)])
+def test_int32_partials_bit_exact_from_the_product_decode_kernels(q4k, kernel, M, K, N):
+    """Per-sub-block p[j], sumi and summ of EVERY (column, row, superblock), written by the DUMP instantiation of the product
+    kernel itself (same code, the MMA C fragments / dp4a sums it really computed), against the generic reference's integers
+    (L/ggml/src/ggml-cpu/quants.c:575-611); the fp32 results of that launch equal the plain launch's bit for bit."""
     from oracle import port
-    w = make_weights(M, K)
-    xq = port.quantize_q8_K(make_acts(N, K))
-    p, si, sm = [a.cpu().numpy() for a in q4k.debug_partials(t(w), t(xq))]
-    for n in range(N):
-        for m in range(M):
-            rp, rsi, rsm = port.vec_dot_partials(w[m], xq[n])
-            assert np.array_equal(p[n, m], rp) and np.array_equal(si[n, m], rsi) and np.array_equal(sm[n, m], rsm)
+    w, x = make_weights(M, K), make_acts(N, K)
+    rp, rsi, rsm = port.partials_matrix(w, port.quantize_q8_K(x))
+    dst, p, si, sm = q4k.mul_mat_dump(t(w), t(x), getattr(q4k, kernel))
+    assert np.array_equal(p.cpu().numpy(), rp)
+    assert np.array_equal(si.cpu().numpy(), rsi)
+    assert np.array_equal(sm.cpu().numpy(), rsm)
+    if kernel == "DUMP_DISPATCH":
+        assert np.array_equal(dst.cpu().numpy().view(np.uint32), q4k.mul_mat(t(w), t(x)).cpu().numpy().view(np.uint32))
+
+
+@pytest.mark.parametrize("M,K", [(33, 512), (70, 8192), (20, 28672)])
+def test_int32_partials_bit_exact_from_the_large_matrix_kernel(q4k, M, K):
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(1, K)
+    rp, rsi, rsm = port.partials_matrix(w, port.quantize_q8_K(x))
+    dst, p, si, sm = q4k.mul_mat_dump(t(w), t(x), q4k.DUMP_BIG)
+    assert np.array_equal(p.cpu().numpy(), rp) and np.array_equal(si.cpu().numpy(), rsi) and np.array_equal(sm.cpu().numpy(), rsm)
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 512, 16), (200, 2048, 40), (130, 1024, 130), (64, 14336, 32), (300, 4096, 9)])
+def test_int32_sums_bit_exact_from_the_gemm_epilogue(q4k, M, K, N):
+    """The prefill GEMM never forms p[j] (the scales ride in the A operand), but its epilogue reads sumi = 8 hi + lo and summ
+    of every (row, column, superblock) out of TMEM: the DUMP instantiation writes exactly those integers."""
+    from oracle import port
+    w, x = make_weights(M, K), make_acts(N, K)
+    _, rsi, rsm = port.partials_matrix(w, port.quantize_q8_K(x))
+    dst, p, si, sm = q4k.mul_mat_dump(t(w), t(x), q4k.DUMP_GEMM)
+    assert p is None
+    assert np.array_equal(si.cpu().numpy(), rsi) and np.array_equal(sm.cpu().numpy(), rsm)
+    assert np.array_equal(dst.cpu().numpy().view(np.uint32), q4k.mul_mat(t(w), t(x)).cpu().numpy().view(np.uint32))
 
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (100, 512, 1), (257, 2048, 2), (64, 14336, 1), (1, 256, 1)])
@@ -70,7 +103,7 @@ def test_gemv_batch_within_tolerance(q4k, M, K, N):
     from oracle import port
     w, x = make_weights(M, K), make_acts(N, K)
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
-    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    check(f"gemv {M}x{K} N={N}", got, w, x)
 
 
 @pytest.mark.parametrize("N", [9, 32, 100])
@@ -79,7 +112,7 @@ def test_mul_mat_large_batch(q4k, N):
     M, K = 128, 1024
     w, x = make_weights(M, K), make_acts(N, K)
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
-    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    check(f"mul_mat {M}x{K} N={N}", got, w, x)
 
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (2048, 5632, 1), (259, 2048, 2), (64, 8192, 4), (33, 1024, 8)])
@@ -106,7 +139,7 @@ def test_fused_quantize_equals_two_kernel_path(q4k, exact_order, M, K, N):
     if N <= 2:
         assert np.array_equal(fused.view(np.uint32), ref.view(np.uint32))
     else:
-        assert_close(fused, ref, port.mul_mat_f64(w, x))
+        check(f"fused {M}x{K} N={N}", fused, w, x)
 
 
 def test_back_to_back_pdl_launches_see_fresh_activations(q4k, exact_order):
@@ -134,7 +167,7 @@ def test_gemm_tensor_core_within_tolerance(q4k, M, K, N):
     from oracle import port
     w, x = make_weights(M, K), make_acts(N, K)
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
-    assert_close(got, port.mul_mat(w, x, port.ORDER_AVX2), port.mul_mat_f64(w, x))
+    check(f"gemm {M}x{K} N={N}", got, w, x)
 
 
 def test_gemm_integer_stage_is_exact(q4k):
