@@ -48,11 +48,33 @@ struct buffer_context {
     void * base;
 };
 
+// A launch sequence captured once and replayed (CUDA graph with programmatic-dependent-launch edges).  `sig` identifies
+// what was captured: every launching node's device pointers, shapes and strides.  ggml rebuilds the tensor structs of a graph
+// for every token, but ggml-alloc hands the same addresses to the same topology, so a decode loop hits the cache.
+struct graph_cache {
+    std::vector<uint64_t> sig;
+    q4k_graph * graph = nullptr;
+    uint64_t ws_generation = 0;      // the captured launches hold the workspace pointer of this generation
+    int seen = 0;                    // computes of `sig` so far (capture happens on the second: a graph seen once may never return)
+    bool failed = false;             // capture of `sig` failed once: stay on plain launches
+    ~graph_cache() { q4k_graph_destroy(graph); }
+};
+
 struct backend_context {
     device_context * dev;
     void *  stream    = nullptr;
     void *  workspace = nullptr;     // Q8_K copy of src1: the analogue of params->wdata (ggml-cpu.c:1267-1307)
     size_t  workspace_bytes = 0;
+    uint64_t ws_generation = 1;      // bumped whenever the workspace is reallocated (invalidates captured launches)
+    bool capturing = false;
+    graph_cache cache;               // graph_compute's own cache; graph plans carry theirs
+};
+
+// backend_i.graph_plan_create's result (L/ggml/src/ggml-backend-impl.h:100-108): the node list + its captured launches
+struct graph_plan {
+    std::vector<ggml_tensor *> nodes;
+    ggml_cgraph cgraph{};
+    graph_cache cache;
 };
 
 std::vector<ggml_backend_device> & devices() {
@@ -236,15 +258,8 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node, bool reus
     const bool q6 = src0->type == GGML_TYPE_Q6_K;
     const size_t need = q6 ? q6k_mul_mat_workspace_bytes(K, N) : q4k_mul_mat_workspace_bytes(K, N);
     if (need > ctx->workspace_bytes) {
-        // grow-only scratch; in-flight kernels may still read the old one
-        if (q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream) != Q4K_OK) return GGML_STATUS_FAILED;
-        q4k_mem_free(ctx->dev->cuda_device, ctx->workspace);
-        ctx->workspace = q4k_mem_alloc(ctx->dev->cuda_device, need);
-        ctx->workspace_bytes = ctx->workspace ? need : 0;
-        if (!ctx->workspace) {
-            GGML_LOG_ERROR("Q4K_B200: cannot allocate %zu bytes of Q8_K workspace\n", need);
-            return GGML_STATUS_ALLOC_FAILED;
-        }
+        GGML_LOG_ERROR("Q4K_B200: %s: workspace was not sized before the launches (need %zu, have %zu)\n", node->name, need, ctx->workspace_bytes);
+        return GGML_STATUS_FAILED;
     }
     for (int64_t i13 = 0; i13 < ne13; ++i13) {
         for (int64_t i12 = 0; i12 < ne12; ++i12) {
@@ -312,9 +327,58 @@ int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i) {
     return last - i + 1;
 }
 
-ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
-    auto * ctx = (backend_context *) backend->context;
-    if (q4k_set_device(ctx->dev->cuda_device) != Q4K_OK) return GGML_STATUS_FAILED;
+bool is_noop(const ggml_tensor * node) {
+    return node->op == GGML_OP_NONE || node->op == GGML_OP_RESHAPE || node->op == GGML_OP_VIEW || node->op == GGML_OP_PERMUTE ||
+           node->op == GGML_OP_TRANSPOSE;
+}
+
+// Q8_K scratch for the largest mul_mat of the graph, sized BEFORE any launch (no allocation, no synchronize between launches:
+// the launch sequence may be under stream capture).  Grow-only; growing invalidates captured launches (they hold the pointer).
+ggml_status ensure_workspace(backend_context * ctx, const ggml_cgraph * cgraph) {
+    size_t need = 0;
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        const ggml_tensor * node = cgraph->nodes[i];
+        if (node->op != GGML_OP_MUL_MAT || !node->src[0] || !node->src[1]) continue;
+        const int64_t K = node->src[0]->ne[0], N = node->src[1]->ne[1];
+        const size_t n = node->src[0]->type == GGML_TYPE_Q6_K ? q6k_mul_mat_workspace_bytes(K, N) : q4k_mul_mat_workspace_bytes(K, N);
+        if (n > need) need = n;
+    }
+    if (need <= ctx->workspace_bytes) return GGML_STATUS_SUCCESS;
+    // in-flight kernels may still read the old one
+    if (q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream) != Q4K_OK) return GGML_STATUS_FAILED;
+    q4k_mem_free(ctx->dev->cuda_device, ctx->workspace);
+    ctx->workspace = q4k_mem_alloc(ctx->dev->cuda_device, need);
+    ctx->workspace_bytes = ctx->workspace ? need : 0;
+    ++ctx->ws_generation;
+    if (!ctx->workspace) {
+        GGML_LOG_ERROR("Q4K_B200: cannot allocate %zu bytes of Q8_K workspace\n", need);
+        return GGML_STATUS_ALLOC_FAILED;
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+// What a captured launch sequence depends on: per launching node the op, types, device pointers, shapes and strides.
+void graph_signature(const ggml_cgraph * cgraph, std::vector<uint64_t> & sig, int & launching) {
+    sig.clear();
+    launching = 0;
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        const ggml_tensor * node = cgraph->nodes[i];
+        if (is_noop(node)) continue;
+        ++launching;
+        const ggml_tensor * t[3] = {node, node->src[0], node->src[1]};
+        sig.push_back((uint64_t) node->op);
+        for (const ggml_tensor * x : t) {
+            if (!x) { sig.push_back(0); continue; }
+            sig.push_back((uint64_t) (uintptr_t) x->data);
+            sig.push_back((uint64_t) x->type);
+            for (int d = 0; d < GGML_MAX_DIMS; ++d) { sig.push_back((uint64_t) x->ne[d]); sig.push_back((uint64_t) x->nb[d]); }
+        }
+        // consecutive prefill mul_mats share the quantized activations only if they name the SAME src1 tensor
+        sig.push_back(i > 0 && cgraph->nodes[i - 1]->src[1] == node->src[1] ? 1u : 0u);
+    }
+}
+
+ggml_status enqueue_nodes(backend_context * ctx, ggml_cgraph * cgraph) {
     const ggml_tensor * last_quantized = nullptr;      // src1 whose prefill-quantized copy is in the workspace right now
     const void * last_quantized_data = nullptr;
     for (int i = 0; i < cgraph->n_nodes; ++i) {
@@ -346,7 +410,78 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
                 GGML_ABORT("Q4K_B200: unsupported op %s reached graph_compute", ggml_op_desc(node));
         }
     }
-    return GGML_STATUS_SUCCESS;         // asynchronous: results are complete after synchronize()
+    return GGML_STATUS_SUCCESS;
+}
+
+// Runs the graph through `cache`: plain launches the first time a launch sequence is seen, captured into a CUDA graph the
+// second time (78 dependent launches of a decode token cost one graph launch after that), replayed from then on.
+ggml_status compute_cached(backend_context * ctx, ggml_cgraph * cgraph, graph_cache & cache) {
+    if (q4k_set_device(ctx->dev->cuda_device) != Q4K_OK) return GGML_STATUS_FAILED;
+    const ggml_status ws = ensure_workspace(ctx, cgraph);
+    if (ws != GGML_STATUS_SUCCESS) return ws;
+    static thread_local std::vector<uint64_t> sig;
+    int launching = 0;
+    graph_signature(cgraph, sig, launching);
+    if (launching < 2) return enqueue_nodes(ctx, cgraph);                    // nothing to amortise
+    const bool same = sig == cache.sig;
+    if (same && cache.graph && cache.ws_generation == ctx->ws_generation) {
+        if (q4k_graph_launch(cache.graph, ctx->stream) == Q4K_OK) return GGML_STATUS_SUCCESS;
+        GGML_LOG_ERROR("Q4K_B200: graph launch failed (cudaError %d)\n", q4k_last_cuda_error());
+        return GGML_STATUS_FAILED;
+    }
+    if (!same) {
+        q4k_graph_destroy(cache.graph);
+        cache.graph = nullptr; cache.sig = sig; cache.seen = 0; cache.failed = false;
+    } else if (cache.graph) {                                                // same launches, stale workspace pointer
+        q4k_graph_destroy(cache.graph);
+        cache.graph = nullptr;
+    }
+    if (++cache.seen < 2 || cache.failed) return enqueue_nodes(ctx, cgraph);
+    if (q4k_graph_begin_capture(ctx->stream) != Q4K_OK) { cache.failed = true; return enqueue_nodes(ctx, cgraph); }
+    const ggml_status st = enqueue_nodes(ctx, cgraph);
+    q4k_graph * g = nullptr;
+    const int rc = q4k_graph_end_capture(ctx->stream, st == GGML_STATUS_SUCCESS, &g);
+    if (st != GGML_STATUS_SUCCESS || rc != Q4K_OK || !g) {
+        cache.failed = true;                                                 // e.g. a launch that cannot be captured: plain launches
+        return st != GGML_STATUS_SUCCESS ? st : enqueue_nodes(ctx, cgraph);
+    }
+    cache.graph = g;
+    cache.ws_generation = ctx->ws_generation;
+    return q4k_graph_launch(g, ctx->stream) == Q4K_OK ? GGML_STATUS_SUCCESS : GGML_STATUS_FAILED;
+}
+
+ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    auto * ctx = (backend_context *) backend->context;
+    return compute_cached(ctx, cgraph, ctx->cache);      // asynchronous: results are complete after synchronize()
+}
+
+// backend_i.graph_plan_* (L/ggml/src/ggml-backend-impl.h:100-108; the CPU backend's: L/ggml/src/ggml-cpu/ggml-cpu.cpp:128-165)
+ggml_backend_graph_plan_t backend_graph_plan_create(ggml_backend_t, const ggml_cgraph * cgraph) {
+    auto * plan = new graph_plan;
+    plan->nodes.assign(cgraph->nodes, cgraph->nodes + cgraph->n_nodes);
+    plan->cgraph = *cgraph;
+    plan->cgraph.nodes = plan->nodes.data();
+    return plan;
+}
+
+void backend_graph_plan_free(ggml_backend_t backend, ggml_backend_graph_plan_t plan) {
+    auto * ctx = (backend_context *) backend->context;
+    q4k_stream_synchronize(ctx->dev->cuda_device, ctx->stream);
+    delete (graph_plan *) plan;
+}
+
+void backend_graph_plan_update(ggml_backend_t, ggml_backend_graph_plan_t plan_, const ggml_cgraph * cgraph) {
+    auto * plan = (graph_plan *) plan_;
+    plan->nodes.assign(cgraph->nodes, cgraph->nodes + cgraph->n_nodes);
+    plan->cgraph = *cgraph;
+    plan->cgraph.nodes = plan->nodes.data();              // the cache notices by itself if the launches changed
+}
+
+ggml_status backend_graph_plan_compute(ggml_backend_t backend, ggml_backend_graph_plan_t plan_) {
+    auto * ctx = (backend_context *) backend->context;
+    auto * plan = (graph_plan *) plan_;
+    // first compute: plain launches (kernel modules load, per-kernel attributes are set); second: captured; then replayed
+    return compute_cached(ctx, &plan->cgraph, plan->cache);
 }
 
 const ggml_backend_i backend_iface = {
@@ -356,10 +491,10 @@ const ggml_backend_i backend_iface = {
     /* .get_tensor_async   = */ backend_get_tensor_async,
     /* .cpy_tensor_async   = */ nullptr,
     /* .synchronize        = */ backend_synchronize,
-    /* .graph_plan_create  = */ nullptr,
-    /* .graph_plan_free    = */ nullptr,
-    /* .graph_plan_update  = */ nullptr,
-    /* .graph_plan_compute = */ nullptr,
+    /* .graph_plan_create  = */ backend_graph_plan_create,
+    /* .graph_plan_free    = */ backend_graph_plan_free,
+    /* .graph_plan_update  = */ backend_graph_plan_update,
+    /* .graph_plan_compute = */ backend_graph_plan_compute,
     /* .graph_compute      = */ backend_graph_compute,
     /* .event_record       = */ nullptr,
     /* .event_wait         = */ nullptr,

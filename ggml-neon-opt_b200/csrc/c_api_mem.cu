@@ -129,4 +129,44 @@ int q4k_stream_synchronize(int device, void *stream) {
     return Q4K_OK;
 }
 
+// ---- captured launch sequences (backend_i.graph_plan_* and the plugin's cached graph_compute) ------------------------
+struct q4k_graph {
+    cudaGraphExec_t exec;
+    int64_t launches;       // kernels of this library inside the graph (for q4k_kernel_launches)
+};
+static thread_local int64_t t_capture_launches0 = 0;
+
+int q4k_graph_begin_capture(void *stream) {
+    if (!stream) return Q4K_ERR_BAD_POINTER;           // the legacy default stream cannot be captured
+    t_capture_launches0 = q4k::launch_count();
+    Q4K_TRY(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+    return Q4K_OK;
+}
+
+int q4k_graph_end_capture(void *stream, int keep, q4k_graph **graph_out) {
+    cudaGraph_t g = nullptr;
+    const cudaError_t e = cudaStreamEndCapture((cudaStream_t)stream, &g);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); if (g) cudaGraphDestroy(g); return note_cuda_error(e); }
+    if (!keep || !graph_out) { if (g) cudaGraphDestroy(g); return Q4K_OK; }      // the caller abandons the capture (a launch failed)
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ei = cudaGraphInstantiate(&exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) { (void)cudaGetLastError(); return note_cuda_error(ei); }
+    *graph_out = new q4k_graph{exec, q4k::launch_count() - t_capture_launches0};
+    return Q4K_OK;
+}
+
+int q4k_graph_launch(q4k_graph *graph, void *stream) {
+    if (!graph) return Q4K_ERR_BAD_POINTER;
+    Q4K_TRY(cudaGraphLaunch(graph->exec, (cudaStream_t)stream));
+    q4k::add_launches(graph->launches);
+    return Q4K_OK;
+}
+
+void q4k_graph_destroy(q4k_graph *graph) {
+    if (!graph) return;
+    cudaGraphExecDestroy(graph->exec);
+    delete graph;
+}
+
 }  // extern "C"

@@ -64,6 +64,16 @@ int     q4k_stream_destroy(int device, void *stream);
 int     q4k_stream_synchronize(int device, void *stream);
 int     q4k_set_device(int device);                                    /* makes `device` current for the calling thread */
 
+/* Captured launch sequences: what backend_i.graph_plan_create / graph_plan_compute (L/ggml/src/ggml-backend-impl.h:100-108)
+ * and the plugin's cached graph_compute are made of.  Between begin and end every q4k_* launch on `stream` is recorded (CUDA
+ * stream capture, programmatic-dependent-launch edges included) instead of executed; end instantiates the graph (keep = 0:
+ * abandon it), launch replays it on a stream.  Nothing may synchronize or allocate between begin and end. */
+typedef struct q4k_graph q4k_graph;
+int  q4k_graph_begin_capture(void *stream);
+int  q4k_graph_end_capture(void *stream, int keep, q4k_graph **graph_out);
+int  q4k_graph_launch(q4k_graph *graph, void *stream);
+void q4k_graph_destroy(q4k_graph *graph);
+
 /* replaces quantize_row_q8_K (L/ggml/src/ggml-quants.c:2555-2592, bound as from_float of Q8_K at
  * L/ggml/src/ggml-cpu/ggml-cpu.c:355-357) for `nrows` rows of k floats; row r is read at
  * x_dev + r*x_row_stride_bytes and written to y_dev + r*(k/256*292).  Bit-exact, except that bsums of

@@ -86,7 +86,9 @@ def test_int32_sums_bit_exact_from_the_gemm_epilogue(q4k, M, K, N):
     dst, p, si, sm = q4k.mul_mat_dump(t(w), t(x), q4k.DUMP_GEMM)
     assert p is None
     assert np.array_equal(si.cpu().numpy(), rsi) and np.array_equal(sm.cpu().numpy(), rsm)
-    assert np.array_equal(dst.cpu().numpy().view(np.uint32), q4k.mul_mat(t(w), t(x)).cpu().numpy().view(np.uint32))
+    if N > 12:                                              # q4k_mul_mat serves N <= 12 with the decode kernel: other float order
+        assert np.array_equal(dst.cpu().numpy().view(np.uint32), q4k.mul_mat(t(w), t(x)).cpu().numpy().view(np.uint32))
+    check(f"gemm (dump instantiation) {M}x{K} N={N}", dst.cpu().numpy(), w, x)
 
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (100, 512, 1), (257, 2048, 2), (64, 14336, 1), (1, 256, 1)])
