@@ -41,6 +41,7 @@ struct device_context {
     std::string name;           // "Q4K_B200_0"
     std::string description;    // "NVIDIA B200 (148 SMs)"
     ggml_backend_buffer_type buft{};
+    ggml_backend_buffer_type host_buft{};   // page-locked host memory: what set_tensor_async / get_tensor_async copy from / to at full speed
 };
 
 struct buffer_context {
@@ -178,6 +179,35 @@ const ggml_backend_buffer_type_i buft_iface = {
 };
 
 bool buft_is_ours(ggml_backend_buffer_type_t buft) { return buft && buft->iface.get_name == buft_get_name; }
+
+// ------------------------------------------------------------------------------------------ host (pinned) buffer type
+// device_i.get_host_buffer_type (L/ggml/src/ggml-backend-impl.h:158): an ordinary CPU buffer whose pages are locked, so the
+// asynchronous copies of the backend run at PCIe speed and really are asynchronous.  The buffer itself is the reference's own CPU
+// buffer (ggml_backend_cpu_buffer_from_ptr); only the allocation and the free are ours.
+const char * host_buft_get_name(ggml_backend_buffer_type_t) { return "Q4K_B200_Host"; }
+
+void host_buffer_free(ggml_backend_buffer_t buffer) { q4k_host_free_pinned(buffer->context); }
+
+ggml_backend_buffer_t host_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    void * ptr = q4k_host_alloc_pinned(size);
+    if (!ptr) return nullptr;                                  // the caller falls back to a pageable CPU buffer
+    ggml_backend_buffer_t buffer = ggml_backend_cpu_buffer_from_ptr(ptr, size);
+    buffer->buft = buft;
+    buffer->iface.free_buffer = host_buffer_free;
+    return buffer;
+}
+
+size_t host_buft_get_alignment(ggml_backend_buffer_type_t) { return Q4K_TENSOR_ALIGN; }
+bool host_buft_is_host(ggml_backend_buffer_type_t) { return true; }
+
+const ggml_backend_buffer_type_i host_buft_iface = {
+    /* .get_name       = */ host_buft_get_name,
+    /* .alloc_buffer   = */ host_buft_alloc_buffer,
+    /* .get_alignment  = */ host_buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ nullptr,
+    /* .is_host        = */ host_buft_is_host,
+};
 
 }  // namespace
 
@@ -528,6 +558,10 @@ ggml_backend_buffer_type_t device_get_buffer_type(ggml_backend_dev_t dev) {
     return &((device_context *) dev->context)->buft;
 }
 
+ggml_backend_buffer_type_t device_get_host_buffer_type(ggml_backend_dev_t dev) {
+    return &((device_context *) dev->context)->host_buft;
+}
+
 void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
     props->name        = device_get_name(dev);
     props->description = device_get_description(dev);
@@ -535,7 +569,7 @@ void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
     device_get_memory(dev, &props->memory_free, &props->memory_total);
     props->caps = {
         /* .async                = */ true,
-        /* .host_buffer          = */ false,
+        /* .host_buffer          = */ true,
         /* .buffer_from_host_ptr = */ false,
         /* .events               = */ false,
     };
@@ -588,7 +622,7 @@ const ggml_backend_device_i device_iface = {
     /* .get_props            = */ device_get_props,
     /* .init_backend         = */ device_init_backend,
     /* .get_buffer_type      = */ device_get_buffer_type,
-    /* .get_host_buffer_type = */ nullptr,
+    /* .get_host_buffer_type = */ device_get_host_buffer_type,
     /* .buffer_from_host_ptr = */ nullptr,
     /* .supports_op          = */ device_supports_op,
     /* .supports_buft        = */ device_supports_buft,
@@ -648,6 +682,7 @@ ggml_backend_reg_t q4k_b200_reg() {
         for (auto & c : dctx) {
             devs.push_back(ggml_backend_device{device_iface, &reg, &c});
             c.buft = ggml_backend_buffer_type{buft_iface, &devs.back(), &c};
+            c.host_buft = ggml_backend_buffer_type{host_buft_iface, &devs.back(), &c};
         }
         GGML_LOG_INFO("Q4K_B200: %zu sm_100 device(s); claims MUL_MAT(Q4_K | Q6_K, F32) only\n", devs.size());
     });

@@ -97,10 +97,15 @@ class RowShardedQ4K:
         self.gather = "nccl"
         self.peer_note = ""
         self._ws = None
+        # The peer exchange alternates between two result buffers, chosen on the HOST per call.  A CUDA graph bakes the choice in,
+        # so a captured sequence must contain an EVEN number of calls of this object (then replays keep alternating and the
+        # "buffer (i + 1) % 2 is free after the exchange of call i" argument of _init_peer holds across replays too).
+        self.needs_even_capture = False
         if gather in ("auto", "peer") and self.world > 1:
             try:
                 self._init_peer()
                 self.gather = "peer"
+                self.needs_even_capture = True
             except Exception as e:                       # no P2P / symmetric memory on this box: NCCL does the exchange
                 if gather == "peer":
                     raise

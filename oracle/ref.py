@@ -69,6 +69,9 @@ def libs():
         shim.ref_mul_mat_set_typed.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i32), i64, i32, i32, i32,
                                                C.POINTER(C.c_double), C.POINTER(C.c_double)]
         shim.ref_mul_mat_set_typed.restype = i32
+        shim.ref_mul_mat_set_ex.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i32), i64, i32, i32, i32, i32,
+                                            C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        shim.ref_mul_mat_set_ex.restype = i32
         # ggml-cpu's fp16->fp32 is a lookup table filled by ggml_cpu_init() (ggml-cpu.c:3526-3549);
         # the reference always reaches vec_dot through backend init, direct callers must do it themselves
         cpu.ggml_cpu_init()
@@ -224,6 +227,58 @@ def mul_mat_set_typed(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, i
     if rc != 0:
         raise RuntimeError(f"ref_mul_mat_set_typed rc={rc}")
     return secs[0], secs[1], chk.value
+
+
+def mul_mat_set_ex(shapes, N: int = 1, n_threads: int = 1, warmup: int = 1, iters: int = 3, repack: bool = False):
+    """mul_mat_set_typed with the weights optionally in the CPU backend's CPU_REPACK buffer type — what llama-bench runs by default
+    on an AVX2 host (L/ggml/src/ggml-cpu/repack.cpp:1844-1849: block_q4_Kx8 + ggml_gemv/gemm_q4_K_8x8_q8_K).
+    shapes = [(M, K, is_q6k)].  Returns (best_s, mean_s, checksum)."""
+    shim = libs()[3]
+    n = len(shapes)
+    Ms = (C.c_int64 * n)(*[int(s[0]) for s in shapes])
+    Ks = (C.c_int64 * n)(*[int(s[1]) for s in shapes])
+    q6 = (C.c_int * n)(*[int(bool(s[2])) if len(s) > 2 else 0 for s in shapes])
+    secs = (C.c_double * 2)()
+    chk = C.c_double(0)
+    rc = shim.ref_mul_mat_set_ex(n, Ms, Ks, q6, N, n_threads, warmup, iters, int(repack), secs, C.byref(chk))
+    if rc != 0:
+        raise RuntimeError(f"ref_mul_mat_set_ex rc={rc}")
+    return secs[0], secs[1], chk.value
+
+
+def direct_q4k(m_sample: int, K: int, N: int = 1, warmup: int = 1, iters: int = 3):
+    """BASELINE.md §5 timing (i): quantize_row_q8_K + a loop of ggml_vec_dot_q4_K_q8_K over `m_sample` rows, ONE thread, through the
+    reference's type-traits table.  Returns (best_s, mean_s, checksum) per pass over the sample."""
+    shim = libs()[3]
+    secs = (C.c_double * 2)()
+    chk = C.c_double(0)
+    shim.ref_direct_q4k.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    rc = shim.ref_direct_q4k(m_sample, K, N, warmup, iters, secs, C.byref(chk))
+    if rc != 0:
+        raise RuntimeError(f"ref_direct_q4k rc={rc}")
+    return secs[0], secs[1], chk.value
+
+
+def plugin_graph_set(so_path: str, shapes, input_ids, N: int = 1, use_plan: bool = False, warmup: int = 3, iters: int = 20):
+    """The whole mul_mat set as ONE ggml graph on the backend plugin, driven through the reference's public backend API per step
+    (tensor_set_async -> graph_compute_async | graph_plan_compute -> tensor_get_async -> synchronize), wall-clock.
+    shapes = [(M, K, is_q6k)].  Returns dict(best_s, mean_s, checksum, h2d_bytes, d2h_bytes, pinned)."""
+    shim = libs()[3]
+    n = len(shapes)
+    Ms = (C.c_int64 * n)(*[int(s[0]) for s in shapes])
+    Ks = (C.c_int64 * n)(*[int(s[1]) for s in shapes])
+    q6 = (C.c_int * n)(*[int(bool(s[2])) if len(s) > 2 else 0 for s in shapes])
+    ids = (C.c_int * n)(*[int(i) for i in input_ids])
+    secs = (C.c_double * 2)()
+    chk = C.c_double(0)
+    h2d, d2h, pinned = C.c_int64(0), C.c_int64(0), C.c_int(0)
+    shim.ref_plugin_graph_set.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    rc = shim.ref_plugin_graph_set(so_path.encode(), n, Ms, Ks, q6, ids, N, int(use_plan), warmup, iters, secs, C.byref(chk),
+                                   C.byref(h2d), C.byref(d2h), C.byref(pinned))
+    if rc != 0:
+        raise RuntimeError(f"ref_plugin_graph_set rc={rc}")
+    return {"best_s": secs[0], "mean_s": secs[1], "checksum": chk.value, "h2d_bytes": h2d.value, "d2h_bytes": d2h.value, "pinned": bool(pinned.value)}
 
 
 def quantize_q6_K(x: np.ndarray) -> np.ndarray:

@@ -170,37 +170,77 @@ int ref_n_backend_devices(void) { return (int)ggml_backend_dev_count(); }
  * checksum (optional) receives the sum of all outputs of the last compute. */
 /* same with a weight type per matrix: q6[i] != 0 -> GGML_TYPE_Q6_K (random valid block_q6_K bytes, d = 2^-8), else Q4_K:
  * the full Q4_K_M decode token */
-int ref_mul_mat_set_typed(int n_mats, const int64_t *Ms, const int64_t *Ks, const int *q6, int64_t N, int n_threads,
-                          int warmup, int iters, double *secs, double *checksum) {
+/* random valid block bytes (xorshift; Q4_K: fp16 d = 2^-4, dmin = 2^-5; Q6_K: d = 2^-8) */
+static void fill_random_blocks(uint8_t *p, size_t nbytes, int q6, uint64_t *state) {
+    uint64_t s = *state;
+    for (size_t o = 0; o + 8 <= nbytes; o += 8) {
+        s ^= s << 13; s ^= s >> 7; s ^= s << 17;
+        memcpy(p + o, &s, 8);
+    }
+    if (q6) { for (size_t o = 0; o < nbytes; o += 210) { p[o + 208] = 0x00; p[o + 209] = 0x1c; } }
+    else { for (size_t o = 0; o < nbytes; o += 144) { p[o] = 0x00; p[o + 1] = 0x2c; p[o + 2] = 0x00; p[o + 3] = 0x28; } }
+    *state = s;
+}
+
+/* the CPU backend's CPU_REPACK extra buffer type (what llama's loader puts Q4_K weights in on an AVX2 host:
+ * L/ggml/src/ggml-cpu/repack.cpp:1844-1849 -> ggml_gemv/gemm_q4_K_8x8_q8_K), reached the way llama does: through the
+ * registry's "ggml_backend_dev_get_extra_bufts" proc address (L/ggml/src/ggml-cpu/ggml-cpu.cpp:624-632) */
+static ggml_backend_buffer_type_t cpu_repack_buft(ggml_backend_t cpu) {
+    ggml_backend_dev_t dev = ggml_backend_get_device(cpu);
+    ggml_backend_reg_t reg = ggml_backend_dev_backend_reg(dev);
+    typedef ggml_backend_buffer_type_t *(*get_extra_t)(ggml_backend_dev_t);
+    get_extra_t fn = (get_extra_t)ggml_backend_reg_get_proc_address(reg, "ggml_backend_dev_get_extra_bufts");
+    if (!fn) return NULL;
+    for (ggml_backend_buffer_type_t *b = fn(dev); b && *b; ++b)
+        if (strstr(ggml_backend_buft_name(*b), "REPACK")) return *b;
+    return NULL;
+}
+
+/* repack != 0: the weights live in the CPU_REPACK buffer type (repacked to block_q4_Kx8 by its set_tensor), as llama-bench runs
+ * them by default on an AVX2 host; Q6_K has no repack format on AVX2 and stays plain.  -20: no repack buffer type in this build. */
+int ref_mul_mat_set_ex(int n_mats, const int64_t *Ms, const int64_t *Ks, const int *q6, int64_t N, int n_threads,
+                       int warmup, int iters, int repack, double *secs, double *checksum) {
     ggml_backend_t cpu = ggml_backend_cpu_init();
     if (!cpu) return -1;
     ggml_backend_cpu_set_n_threads(cpu, n_threads);
     struct ggml_init_params ip = { ggml_tensor_overhead() * (size_t)(3 * n_mats + 8) +
                                    ggml_graph_overhead_custom((size_t)(4 * n_mats + 16), false), NULL, true };
-    struct ggml_context *ctx = ggml_init(ip);
-    if (!ctx) { ggml_backend_free(cpu); return -1; }
+    struct ggml_init_params ipw = { ggml_tensor_overhead() * (size_t)(n_mats + 8), NULL, true };
+    struct ggml_context *ctx = ggml_init(ip), *wctx = ggml_init(ipw);
+    if (!ctx || !wctx) { ggml_backend_free(cpu); return -1; }
     struct ggml_cgraph *gf = ggml_new_graph_custom(ctx, (size_t)(4 * n_mats + 16), false);
     struct ggml_tensor **ws = calloc((size_t)n_mats, sizeof *ws), **xs = calloc((size_t)n_mats, sizeof *xs),
                        **ys = calloc((size_t)n_mats, sizeof *ys);
     for (int i = 0; i < n_mats; ++i) {
-        ws[i] = ggml_new_tensor_2d(ctx, q6 && q6[i] ? GGML_TYPE_Q6_K : GGML_TYPE_Q4_K, Ks[i], Ms[i]);
+        /* repacked weights sit in their own context / buffer; everything else in a plain CPU buffer */
+        ws[i] = ggml_new_tensor_2d(repack && !(q6 && q6[i]) ? wctx : ctx, q6 && q6[i] ? GGML_TYPE_Q6_K : GGML_TYPE_Q4_K, Ks[i], Ms[i]);
         xs[i] = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, Ks[i], N);
         ys[i] = ggml_mul_mat(ctx, ws[i], xs[i]);
         ggml_build_forward_expand(gf, ys[i]);
     }
     int rc = 0;
+    ggml_backend_buffer_t wbuf = NULL;
     ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors_from_buft(ctx, ggml_backend_cpu_buffer_type());
     if (!buf) { rc = -2; goto done; }
+    if (repack) {
+        ggml_backend_buffer_type_t rb = cpu_repack_buft(cpu);
+        if (!rb) { rc = -20; goto done; }
+        wbuf = ggml_backend_alloc_ctx_tensors_from_buft(wctx, rb);
+        if (!wbuf) { rc = -2; goto done; }
+    }
     uint64_t s = 0x9E3779B97F4A7C15ull;
     for (int i = 0; i < n_mats; ++i) {
-        uint8_t *p = (uint8_t *)ws[i]->data;
         const size_t nbytes = ggml_nbytes(ws[i]);
-        for (size_t o = 0; o + 8 <= nbytes; o += 8) {
-            s ^= s << 13; s ^= s >> 7; s ^= s << 17;
-            memcpy(p + o, &s, 8);
+        const int is6 = q6 && q6[i];
+        if (repack && !is6) {                      /* through set_tensor: that is where the repack happens */
+            uint8_t *tmp = malloc(nbytes);
+            if (!tmp) { rc = -1; goto done; }
+            fill_random_blocks(tmp, nbytes, 0, &s);
+            ggml_backend_tensor_set(ws[i], tmp, 0, nbytes);
+            free(tmp);
+        } else {
+            fill_random_blocks((uint8_t *)ws[i]->data, nbytes, is6, &s);
         }
-        if (q6 && q6[i]) { for (size_t o = 0; o < nbytes; o += 210) { p[o + 208] = 0x00; p[o + 209] = 0x1c; } }
-        else { for (size_t o = 0; o < nbytes; o += 144) { p[o] = 0x00; p[o + 1] = 0x2c; p[o + 2] = 0x00; p[o + 3] = 0x28; } }
         float *x = (float *)xs[i]->data;
         const int64_t ne = Ks[i] * N;
         for (int64_t j = 0; j < ne; ++j) x[j] = (float)((j * 2654435761u) % 2001) * 1e-3f - 1.0f;
@@ -225,13 +265,157 @@ int ref_mul_mat_set_typed(int n_mats, const int64_t *Ms, const int64_t *Ks, cons
     }
 done:
     if (buf) ggml_backend_buffer_free(buf);
+    if (wbuf) ggml_backend_buffer_free(wbuf);
     ggml_free(ctx);
+    ggml_free(wctx);
     free(ws); free(xs); free(ys);
     ggml_backend_free(cpu);
     return rc;
 }
 
+int ref_mul_mat_set_typed(int n_mats, const int64_t *Ms, const int64_t *Ks, const int *q6, int64_t N, int n_threads,
+                          int warmup, int iters, double *secs, double *checksum) {
+    return ref_mul_mat_set_ex(n_mats, Ms, Ks, q6, N, n_threads, warmup, iters, 0, secs, checksum);
+}
+
+/* BASELINE.md §5 timing (i), "direct": quantize_row_q8_K of the N activation rows + one ggml_vec_dot_q4_K_q8_K per (row, column)
+ * on ONE thread, through the reference's own type-traits table (L/ggml/src/ggml-cpu/ggml-cpu.c:274-283, 355-357) — the loop
+ * ggml_compute_forward_mul_mat_one_chunk runs, without the threadpool.  Only rows [0, m_sample) are computed (bounded CPU
+ * time); weights random valid blocks.  secs[0] = best, secs[1] = mean seconds per pass over the sample. */
+int ref_direct_q4k(int64_t m_sample, int64_t K, int64_t N, int warmup, int iters, double *secs, double *checksum) {
+    const struct ggml_type_traits_cpu *tq4 = ggml_get_type_traits_cpu(GGML_TYPE_Q4_K), *tq8 = ggml_get_type_traits_cpu(GGML_TYPE_Q8_K);
+    if (!tq4 || !tq4->vec_dot || !tq8 || !tq8->from_float || tq4->vec_dot_type != GGML_TYPE_Q8_K) return -1;
+    const size_t wrow = ggml_row_size(GGML_TYPE_Q4_K, K), yrow = ggml_row_size(GGML_TYPE_Q8_K, K);
+    uint8_t *w = malloc(wrow * (size_t)m_sample), *y = malloc(yrow * (size_t)N);
+    float *x = malloc(sizeof(float) * (size_t)(K * N)), *dst = malloc(sizeof(float) * (size_t)(m_sample * N));
+    if (!w || !y || !x || !dst) { free(w); free(y); free(x); free(dst); return -1; }
+    uint64_t s = 0x9E3779B97F4A7C15ull;
+    fill_random_blocks(w, wrow * (size_t)m_sample, 0, &s);
+    for (int64_t j = 0; j < K * N; ++j) x[j] = (float)((j * 2654435761u) % 2001) * 1e-3f - 1.0f;
+    double best = 1e30, total = 0;
+    for (int it = 0; it < warmup + iters; ++it) {
+        const double t0 = now_s();
+        for (int64_t n = 0; n < N; ++n) tq8->from_float(x + n * K, y + (size_t)n * yrow, K);
+        for (int64_t n = 0; n < N; ++n)
+            for (int64_t m = 0; m < m_sample; ++m)
+                tq4->vec_dot((int)K, dst + n * m_sample + m, 0, w + (size_t)m * wrow, 0, y + (size_t)n * yrow, 0, 1);
+        const double dt = now_s() - t0;
+        if (it >= warmup) { total += dt; if (dt < best) best = dt; }
+    }
+    if (secs) { secs[0] = best; secs[1] = iters > 0 ? total / iters : 0; }
+    if (checksum) { double c = 0; for (int64_t j = 0; j < m_sample * N; ++j) c += dst[j]; *checksum = c; }
+    free(w); free(y); free(x); free(dst);
+    return 0;
+}
+
 int ref_mul_mat_set_q4k(int n_mats, const int64_t *Ms, const int64_t *Ks, int64_t N, int n_threads,
                         int warmup, int iters, double *secs, double *checksum) {
     return ref_mul_mat_set_typed(n_mats, Ms, Ks, NULL, N, n_threads, warmup, iters, secs, checksum);
+}
+
+/* bench.py's `e2e_plugin` leg: a whole set of mul_mats (the Q4_K_M decode token) as ONE ggml graph on the backend plugin's first
+ * device, driven the way a ggml host drives a backend — per step: ggml_backend_tensor_set_async of the step's activations from
+ * (pinned, if the device offers a host buffer type) host memory, ggml_backend_graph_compute_async (or graph_plan_compute when
+ * use_plan != 0 and the backend implements plans), ggml_backend_tensor_get_async of the results, ggml_backend_synchronize.
+ * Wall-clock per step.  Inputs are 2-D views of ONE packed F32 tensor and every mul_mat's dst is placed (view_src / view_offs)
+ * inside ONE packed result tensor, so a step moves one block up and one block down — the same traffic pattern as
+ * q4k_plan_run_host.  input_ids[i]: mul_mats with equal ids read the same activations (q/k/v, gate/up).
+ * Returns 0 or: -10 load failed, -11 no device, -12 supports_op says no, -13 init failed. */
+int ref_plugin_graph_set(const char *path, int n_mats, const int64_t *Ms, const int64_t *Ks, const int *q6, const int *input_ids,
+                         int64_t N, int use_plan, int warmup, int iters, double *secs, double *checksum,
+                         int64_t *h2d_bytes, int64_t *d2h_bytes, int *pinned) {
+    static ggml_backend_reg_t reg = NULL;
+    if (!reg) reg = ggml_backend_load(path);
+    if (!reg) return -10;
+    if (ggml_backend_reg_dev_count(reg) < 1) return -11;
+    ggml_backend_dev_t dev = ggml_backend_reg_dev_get(reg, 0);
+    ggml_backend_t be = ggml_backend_dev_init(dev, NULL);
+    if (!be) return -13;
+    int rc = 0;
+    struct ggml_init_params ipw = { ggml_tensor_overhead() * (size_t)(n_mats + 8), NULL, true };
+    struct ggml_init_params ip = { ggml_tensor_overhead() * (size_t)(3 * n_mats + 16) +
+                                   ggml_graph_overhead_custom((size_t)(4 * n_mats + 16), false), NULL, true };
+    struct ggml_context *wctx = ggml_init(ipw), *ctx = ggml_init(ip);
+    struct ggml_tensor **ws = calloc((size_t)n_mats, sizeof *ws), **ys = calloc((size_t)n_mats, sizeof *ys);
+    struct ggml_tensor **xv = calloc((size_t)n_mats, sizeof *xv);
+    int64_t *in_off = calloc((size_t)n_mats, sizeof *in_off);
+    ggml_backend_buffer_t wbuf = NULL, buf = NULL, hbuf = NULL;
+    ggml_backend_graph_plan_t plan = NULL;
+    float *host_in = NULL, *host_out = NULL;
+    if (!wctx || !ctx || !ws || !ys || !xv || !in_off) { rc = -1; goto out; }
+
+    /* packed layout: one [N][K] block per distinct input id, one [N][M] block per mul_mat, blocks 256-byte aligned */
+    int64_t in_floats = 0, out_floats = 0;
+    for (int i = 0; i < n_mats; ++i) {
+        int first = i;
+        for (int j = 0; j < i; ++j) if (input_ids[j] == input_ids[i]) { first = j; break; }
+        if (first == i) { in_off[i] = in_floats; in_floats += (N * Ks[i] + 63) / 64 * 64; }
+        else in_off[i] = -1 - first;
+    }
+    for (int i = 0; i < n_mats; ++i) out_floats += (N * Ms[i] + 63) / 64 * 64;
+    struct ggml_tensor *X = ggml_new_tensor_1d(ctx, GGML_TYPE_F32, in_floats);
+    struct ggml_tensor *Y = ggml_new_tensor_1d(ctx, GGML_TYPE_F32, out_floats);
+    struct ggml_cgraph *gf = ggml_new_graph_custom(ctx, (size_t)(4 * n_mats + 16), false);
+    int64_t yo = 0;
+    for (int i = 0; i < n_mats; ++i) {
+        ws[i] = ggml_new_tensor_2d(wctx, q6 && q6[i] ? GGML_TYPE_Q6_K : GGML_TYPE_Q4_K, Ks[i], Ms[i]);
+        xv[i] = in_off[i] >= 0 ? ggml_view_2d(ctx, X, Ks[i], N, (size_t)Ks[i] * 4, (size_t)in_off[i] * 4) : xv[-1 - in_off[i]];
+        ys[i] = ggml_mul_mat(ctx, ws[i], xv[i]);
+        ys[i]->view_src = Y;                               /* dst placed inside the packed result tensor */
+        ys[i]->view_offs = (size_t)yo * 4;
+        yo += (N * Ms[i] + 63) / 64 * 64;
+        ggml_build_forward_expand(gf, ys[i]);
+    }
+    wbuf = ggml_backend_alloc_ctx_tensors(wctx, be);
+    buf = ggml_backend_alloc_ctx_tensors(ctx, be);
+    if (!wbuf || !buf) { rc = -2; goto out; }
+    for (int i = 0; i < n_mats; ++i) if (!ggml_backend_dev_supports_op(dev, ys[i])) { rc = -12; goto out; }
+    {   /* weights: random valid blocks, uploaded through the buffer's set_tensor */
+        uint64_t s = 0x9E3779B97F4A7C15ull;
+        for (int i = 0; i < n_mats; ++i) {
+            const size_t nbytes = ggml_nbytes(ws[i]);
+            uint8_t *tmp = malloc(nbytes);
+            if (!tmp) { rc = -1; goto out; }
+            fill_random_blocks(tmp, nbytes, q6 && q6[i], &s);
+            ggml_backend_tensor_set(ws[i], tmp, 0, nbytes);
+            free(tmp);
+        }
+    }
+    {   /* host staging: the device's host (pinned) buffer type when it has one */
+        const size_t hb = (size_t)(in_floats + out_floats) * 4;
+        ggml_backend_buffer_type_t hbt = ggml_backend_dev_host_buffer_type(dev);
+        if (hbt) hbuf = ggml_backend_buft_alloc_buffer(hbt, hb);
+        if (pinned) *pinned = hbuf != NULL;
+        host_in = hbuf ? (float *)ggml_backend_buffer_get_base(hbuf) : malloc(hb);
+        if (!host_in) { rc = -1; goto out; }
+        host_out = host_in + in_floats;
+        for (int64_t j = 0; j < in_floats; ++j) host_in[j] = (float)((j * 2654435761u) % 2001) * 1e-3f - 1.0f;
+        memset(host_out, 0, (size_t)out_floats * 4);
+    }
+    if (use_plan) plan = ggml_backend_graph_plan_create(be, gf);       /* NULL-safe below: backends without plans */
+    double best = 1e30, total = 0;
+    for (int it = 0; it < warmup + iters; ++it) {
+        const double t0 = now_s();
+        ggml_backend_tensor_set_async(be, X, host_in, 0, (size_t)in_floats * 4);
+        const enum ggml_status st = plan ? ggml_backend_graph_plan_compute(be, plan) : ggml_backend_graph_compute_async(be, gf);
+        if (st != GGML_STATUS_SUCCESS) { rc = -3; break; }
+        ggml_backend_tensor_get_async(be, Y, host_out, 0, (size_t)out_floats * 4);
+        ggml_backend_synchronize(be);
+        const double dt = now_s() - t0;
+        if (it >= warmup) { total += dt; if (dt < best) best = dt; }
+    }
+    if (secs) { secs[0] = best; secs[1] = iters > 0 ? total / iters : 0; }
+    if (checksum) { double c = 0; for (int64_t j = 0; j < out_floats; ++j) c += host_out[j]; *checksum = c; }
+    if (h2d_bytes) *h2d_bytes = in_floats * 4;
+    if (d2h_bytes) *d2h_bytes = out_floats * 4;
+out:
+    if (plan) ggml_backend_graph_plan_free(be, plan);
+    if (hbuf) ggml_backend_buffer_free(hbuf); else free(host_in);
+    if (buf) ggml_backend_buffer_free(buf);
+    if (wbuf) ggml_backend_buffer_free(wbuf);
+    if (ctx) ggml_free(ctx);
+    if (wctx) ggml_free(wctx);
+    free(ws); free(ys); free(xv); free(in_off);
+    ggml_backend_free(be);
+    return rc;
 }
