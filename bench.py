@@ -722,7 +722,7 @@ def run_ours(args, rank, world, local_rank):
         parity_ok, parity = parity_before_timing(torch, ms.items, results, N, world, rank, dist)
         del results
         step, one_step, steps_per_call = enqueue, enqueue, 1
-        if args.graph and shards[0].gather == "peer":        # NCCL collectives are left out of graph capture
+        if args.graph and shards[0].gather in ("ll", "peer"):        # NCCL collectives are left out of graph capture
             try:                                               # the whole step (GEMVs + cross-GPU exchange) as one CUDA graph
                 if shards[0].needs_even_capture:               # two steps per graph: the host-chosen result buffers keep alternating
                     step, steps_per_call = graph_of(torch, lambda: (enqueue(), enqueue())).replay, 2
@@ -766,7 +766,10 @@ def run_ours(args, rank, world, local_rank):
         for _ in range(k % steps_per_call):
             one_step()
     ms_total = timed_region(torch, lambda: k_steps(args.steps), lambda: k_steps(args.warmup + args.warmup % steps_per_call), barrier)
-    per_step_ms0 = ms_total / steps_timed
+    t0 = torch.tensor([ms_total], device=device, dtype=torch.float64)
+    if dist is not None:                                       # every rank must replay the SAME number of steps below
+        dist.all_reduce(t0, op=dist.ReduceOp.MAX)
+    per_step_ms0 = float(t0[0]) / steps_timed
     sus_n, sus_ms = sustained(torch, step, 0.5, per_step_ms0 * steps_per_call, barrier)
     # end to end: pinned host activations in, host results out, every step
     if sharded and world > 1:
@@ -891,7 +894,7 @@ def main():
     ap.add_argument("--workload", default="ffn70b", choices=["tinyllama-token", "ffn70b"])
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="sharded path: plain stream launches")
-    ap.add_argument("--gather", default="auto", choices=["auto", "nccl", "peer"], help="row-shard output exchange (N > 1 GPUs)")
+    ap.add_argument("--gather", default="auto", choices=["auto", "nccl", "ll", "peer"], help="row-shard output exchange (N > 1 GPUs)")
     ap.add_argument("--no-plan", dest="plan", action="store_false", help="single GPU: one q4k_mul_mat per launch instead of the graph plan")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU legs")
     ap.add_argument("--shapes", action="store_true", default=True, help="add the decode_token object, the per-shape tables and the prefill figures")

@@ -207,6 +207,52 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 
+size_t q4k_ll_buffer_bytes(int64_t M_full, int64_t n_max) {
+    if (M_full <= 0 || n_max <= 0) return 0;
+    return (size_t)2 * (size_t)n_max * (size_t)M_full * 8;
+}
+
+int q4k_mul_mat_peers_ll(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                         void *const *ll_peers, int world, int rank, int64_t M_full, int64_t n_max, int64_t dst_row0,
+                         float *dst_dev, int64_t dst_col_stride_bytes, void *cnt_dev,
+                         void *workspace_dev, size_t workspace_bytes, void *stream) {
+    if (M_local < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0 || dst_row0 < 0 || M_full < dst_row0 + M_local) return Q4K_ERR_BAD_SHAPE;
+    if (N > Q4K_GEMV_MAX_N || N > n_max || world < 1 || world > 8 || rank < 0 || rank >= world) return Q4K_ERR_UNSUPPORTED;
+    if (N == 0) return Q4K_OK;
+    if (!ll_peers || !dst_dev || !cnt_dev || (M_local > 0 && (!w_dev || !x_dev))) return Q4K_ERR_BAD_POINTER;
+    if (dst_col_stride_bytes < M_full * 4 || (dst_col_stride_bytes & 3) || (reinterpret_cast<uintptr_t>(cnt_dev) & 7u)) return Q4K_ERR_BAD_SHAPE;
+    LLExchange ll;
+    for (int r = 0; r < 8; ++r) ll.peers[r] = nullptr;
+    for (int r = 0; r < world; ++r) {
+        if (!ll_peers[r] || (reinterpret_cast<uintptr_t>(ll_peers[r]) & 7u)) return Q4K_ERR_BAD_POINTER;
+        ll.peers[r] = ll_peers[r];
+    }
+    ll.local = ll_peers[rank]; ll.half_pairs = n_max * M_full; ll.M_full = M_full;
+    ll.cnt = static_cast<uint32_t *>(cnt_dev); ll.dst = dst_dev; ll.dst_stride = dst_col_stride_bytes / 4; ll.world = world;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (M_local == 0) {                        // nothing to compute here: gather everybody else's rows
+        const cudaError_t e = launch_ll_gather(ll, (int)N, knobs().pdl != 0, st);
+        return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+    }
+    const int64_t nb = K / Q4K_QK_K;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+    const void *xq = nullptr;
+    int64_t xq_stride = x_row_stride_bytes;
+    if (N * K > knobs().fuse_limit && workspace_dev && workspace_bytes >= (size_t)(N * nb * Q4K_BLOCK_Q8K)) {
+        const cudaError_t eq = launch_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, st);
+        if (eq != cudaSuccess) return cuda_fail(eq);
+        xq = workspace_dev;
+        xq_stride = nb * Q4K_BLOCK_Q8K;
+    }
+    const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M_local, K, w_row_stride_bytes, xq, xq ? nullptr : x_dev, (int)N, xq_stride,
+                                                  nullptr, 0, gemv_exact_for((int)N), 0, knobs().pdl != 0, st, nullptr, 0, dst_row0,
+                                                  nullptr, 0, &ll);
+    if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;     // activations too large for one shared-memory residency
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
 int q4k_mul_mat_reuse(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N,
                       float *dst_dev, int64_t dst_col_stride_bytes, void *workspace_dev, size_t workspace_bytes, void *stream) {
     if (M < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;

@@ -313,6 +313,8 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
         // and are added there in the same order, so the result does not depend on how K was split.
         int mat = 0, b = 0, xs = 0;
         uint32_t fparity = 0, xparity = 0, cparity = 1;
+        uint32_t ll_ep = 0;
+        if (p.ll_world > 0) { griddep_wait(); ll_ep = ll_epoch(p); }
         for (int64_t tile = t0; tile < t1; tile += tstep) {
             const int64_t lt = locate(tile, mat);
             const int64_t m_rows = p.Mm[mat];
@@ -362,7 +364,9 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
                     const int col = i / MROWS, rr = i % MROWS;
                     const int64_t row = lt * MROWS + rr;
                     if (i < N * MROWS && row < m_rows) {
-                        if (p.nmat == 1) {
+                        if (p.ll_world > 0) {
+                            ll_store(p, ll_ep, col, p.dst_row0 + row, tot[it]);      // {value, epoch} pairs into every rank's LL buffer
+                        } else if (p.nmat == 1) {
                             // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
                             const int64_t o = (int64_t)col * p.dst_stride + p.dst_row0 + row;
                             p.dst[0][o] = tot[it];
@@ -381,6 +385,7 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
             if (++xs == XD) { xs = 0; xparity ^= 1u; cparity ^= 1u; }
         }
         if (p.sync_world > 0) peer_sync_tail(p, lane);        // row-sharded multi-GPU: the cross-GPU step, fused
+        if (p.ll_world > 0 && rank == 0) ll_tail(p, N, ll_ep, cl, ncl, lane, 32);     // the leaders of the clusters share the gather
         return;
     }
 
@@ -589,7 +594,7 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
 cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, const float *const *xf, int N, int64_t x_row_stride_bytes,
                                 float *const *dst, int64_t dst_col_stride_bytes, float *const *peer_dst, int n_peers,
-                                int64_t dst_row0, bool pdl, cudaStream_t stream, const IntDump *dump) {
+                                int64_t dst_row0, bool pdl, cudaStream_t stream, const IntDump *dump, const LLExchange *ll) {
     if (nmat < 1 || nmat > 4 || N < 1 || N > 8 || n_peers > 8) return cudaErrorInvalidValue;
     if (dump && nmat != 1) return cudaErrorInvalidValue;
     TmaGemvParams p;
@@ -597,11 +602,13 @@ cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M
     p.xq = (const uint8_t *)xq; p.xf = xf ? xf[0] : nullptr; p.x_stride = x_row_stride_bytes;
     for (int g = 0; g < 8; ++g) p.dst[g] = nullptr;
     if (n_peers > 0) { for (int g = 0; g < n_peers; ++g) p.dst[g] = peer_dst[g]; p.n_dst = n_peers; }
-    else { p.dst[0] = dst[0]; p.n_dst = 1; }
+    else { p.dst[0] = dst ? dst[0] : nullptr; p.n_dst = 1; }
     p.dst_row0 = dst_row0;
     p.dst_stride = dst_col_stride_bytes > 0 ? dst_col_stride_bytes / 4 : M[0];      // 0 = dense [N][M]
     p.stages = 0; p.nmat = nmat; p.nx = 0;
     fill_sync(p, nmat == 1 ? n_peers : 0);
+    if (ll && nmat != 1) return cudaErrorInvalidValue;
+    fill_ll(p, ll);
     if (dump) { p.dump_p = dump->p; p.dump_sumi = dump->sumi; p.dump_summ = dump->summ; }
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     int64_t tiles = 0;

@@ -127,6 +127,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     stage.prepare(p, blockDim.x);
     touch_params(p);
     griddep_wait();
+    const uint32_t ll_ep = p.ll_world > 0 ? ll_epoch(p) : 0u;     // every warp reads it before the barrier below, i.e. before this CTA can arrive
     if (p.xq) stage_q8<N>(p, q8_s, d_s);
     else stage.run(q8_s, d_s);
     __syncthreads();
@@ -309,7 +310,9 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
                     a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, 4));
                 }
                 if (b == 0 && row < p.Mm[mat]) {
-                    if (p.nmat == 1) {
+                    if (p.ll_world > 0) {
+                        ll_store(p, ll_ep, n, p.dst_row0 + row, a);              // {value, epoch} pairs into every rank's LL buffer
+                    } else if (p.nmat == 1) {
                         // row-sharded multi-GPU: the epilogue IS the all-gather — one store per peer over NVLink
                         const int64_t o = (int64_t)n * p.dst_stride + p.dst_row0 + row;
                         p.dst[0][o] = a;
@@ -323,6 +326,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
         }
         if (++s == S) { s = 0; parity ^= 1u; }
     }
+    if (p.ll_world > 0 && warp == 0) ll_tail(p, N, ll_ep, blockIdx.x, gridDim.x, lane, 32);
     if (p.sync_world > 0) {          // row-sharded multi-GPU: the cross-GPU step, fused; the CTA's last warp carries it
         __syncwarp();
         int lastw = 0;
@@ -412,7 +416,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
                                     const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
                                     bool pdl, cudaStream_t stream, float *const *peer_dst, int n_peers, int64_t dst_row0,
-                                    const IntDump *dump, int dump_kernel) {
+                                    const IntDump *dump, int dump_kernel, const LLExchange *ll) {
     // dump != nullptr (parity): dump_kernel picks the product kernel whose integers are wanted — 0 = whatever the dispatch
     // below picks, 1 = the tensor-pipe kernel, 2 = the bulk-copy kernel in the order `exact_order` says, 3 = the bulk-copy
     // kernel in the tensor-pipe float association (the large-matrix launch, N == 1)
@@ -438,7 +442,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
         const float *xv[1] = {xf};
         float *dv[1] = {dst};
         const cudaError_t e = launch_gemv_q4k_mma(1, wv, Mv, K, w_row_stride_bytes, xq, xq ? nullptr : xv, N, x_row_stride_bytes, dv,
-                                                  dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream, dump);
+                                                  dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream, dump, ll);
         if (e != cudaErrorNotSupported || dump) return e;
     }
     TmaGemvParams p;
@@ -453,6 +457,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
     p.stages = 0; p.interleave = 0; p.kparts = 1;
     p.nmat = 1; p.nx = 1;
     fill_sync(p, n_peers);
+    fill_ll(p, ll);
     if (dump) { p.dump_p = dump->p; p.dump_sumi = dump->sumi; p.dump_summ = dump->summ; }
     for (int i = 0; i < 4; ++i) { p.wm[i] = nullptr; p.Mm[i] = 0; p.gend[i] = 0; p.dstm[i] = nullptr; p.xsrc[i] = nullptr; p.xslot[i] = 0; }
     p.wm[0] = p.w; p.Mm[0] = M; p.gend[0] = p.n_groups; p.xsrc[0] = xf;
@@ -464,9 +469,36 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
         const float *xv[1] = {xf};
         float *dv[1] = {dst};
         return launch_gemv_q4k_mma(1, wv, Mv, K, w_row_stride_bytes, xq, xq ? nullptr : xv, N, x_row_stride_bytes, dv,
-                                   dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream);
+                                   dst_col_stride_bytes, peer_dst, n_peers, dst_row0, pdl, stream, nullptr, ll);
     }
     return exact_order ? launch_tma_e<1>(N, p, stages, pdl, stream) : launch_tma_e<0>(N, p, stages, pdl, stream);
+}
+
+namespace {
+// the tail of an LL exchange alone (a rank that owns no rows of the matrix still gathers everybody else's)
+__global__ void __launch_bounds__(32) ll_gather_kernel(const __grid_constant__ TmaGemvParams p, int N) {
+    griddep_launch_dependents();
+    griddep_wait();
+    ll_tail(p, N, ll_epoch(p), blockIdx.x, gridDim.x, threadIdx.x, 32);
+}
+}  // namespace
+
+cudaError_t launch_ll_gather(const LLExchange &ll, int N, bool pdl, cudaStream_t stream) {
+    TmaGemvParams p = {};
+    fill_sync(p, 0);
+    fill_ll(p, &ll);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)sm_count());
+    cfg.blockDim = dim3(32);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, ll_gather_kernel, p, N);
+    count_launch();
+    return e;
 }
 
 // Horizontally fused decode launch: nmat (<= 4) independent matrices with the same K and N in ONE launch; matrices

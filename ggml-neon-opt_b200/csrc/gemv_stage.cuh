@@ -57,10 +57,28 @@ struct TmaGemvParams {
     // superblock b) as the kernel computed it — p[((n*M + m)*nb + b)*8 + j] = the sub-block dot products, sumi / summ
     // [(n*M + m)*nb + b] (L/ggml/src/ggml-cpu/quants.c:575-611: aux32 -> sumi, and the mins sum)
     int32_t *dump_p, *dump_sumi, *dump_summ;
+    // LL exchange (q4k_kernels.h LLExchange): ll_world > 0 = results go out as {value, epoch} pairs to every rank's LL buffer
+    uint2 *ll_peers[8];
+    const uint2 *ll_local;
+    int64_t ll_half, ll_M, ll_dst_stride;
+    uint32_t *ll_cnt;
+    float *ll_dst;
+    int ll_world;
 };
+
+inline void fill_ll(TmaGemvParams &p, const LLExchange *ll) {
+    for (int r = 0; r < 8; ++r) p.ll_peers[r] = nullptr;
+    p.ll_local = nullptr; p.ll_half = p.ll_M = p.ll_dst_stride = 0; p.ll_cnt = nullptr; p.ll_dst = nullptr; p.ll_world = 0;
+    if (!ll) return;
+    for (int r = 0; r < ll->world; ++r) p.ll_peers[r] = static_cast<uint2 *>(ll->peers[r]);
+    p.ll_local = static_cast<const uint2 *>(ll->local);
+    p.ll_half = ll->half_pairs; p.ll_M = ll->M_full; p.ll_dst_stride = ll->dst_stride;
+    p.ll_cnt = ll->cnt; p.ll_dst = ll->dst; p.ll_world = ll->world;
+}
 
 inline void fill_sync(TmaGemvParams &p, int n_peers) {
     p.dump_p = p.dump_sumi = p.dump_summ = nullptr;
+    fill_ll(p, nullptr);
     for (int r = 0; r < 8; ++r) p.sync_flags[r] = nullptr;
     p.sync_epoch = p.sync_done = nullptr; p.sync_world = 0; p.sync_rank = 0;
     if (t_sync_req && !t_sync_req->taken && n_peers > 0) {
@@ -293,6 +311,47 @@ __device__ __forceinline__ void peer_sync_tail(const TmaGemvParams &p, int lane)
     }
     __syncwarp();
     asm volatile("fence.acq_rel.sys;" ::: "memory");
+}
+
+// ---- LL exchange -------------------------------------------------------------------------------------------------------
+// epoch of this call: one more than the calls this object has completed (read after griddepcontrol.wait: the previous call's
+// last CTA wrote it)
+__device__ __forceinline__ uint32_t ll_epoch(const TmaGemvParams &p) {
+    uint32_t c;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(p.ll_cnt) : "memory");
+    return c + 1u;
+}
+// one result -> every rank's LL buffer.  The value and its epoch travel in ONE 8-byte store (atomic over NVLink), so the
+// receiver needs no fence: a pair whose epoch matches carries the value.
+__device__ __forceinline__ void ll_store(const TmaGemvParams &p, uint32_t ep, int64_t col, int64_t row_full, float v) {
+    const int64_t i = (int64_t)(ep & 1u) * p.ll_half + col * p.ll_M + row_full;
+    for (int g = 0; g < p.ll_world; ++g)
+        asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p.ll_peers[g] + i), "r"(__float_as_uint(v)), "r"(ep) : "memory");
+}
+// The tail: `nlanes` threads of ONE warp-sized group per CTA (lane = 0..nlanes-1) take slice `part` of `nparts` of the gathered
+// [N][M_full] vector, wait for each pair of this call to arrive in the rank's own LL buffer (whoever computes it: another
+// rank over NVLink, or a CTA of this launch) and write it out as a plain float.  The last CTA to finish publishes the call
+// counter.  Every CTA of the launch is resident (persistent grid), so nobody waits for a CTA that cannot run.
+__device__ __forceinline__ void ll_tail(const TmaGemvParams &p, int N, uint32_t ep, int64_t part, int64_t nparts, int lane, int nlanes) {
+    const int64_t total = (int64_t)N * p.ll_M;
+    const int64_t i0 = total * part / nparts, i1 = total * (part + 1) / nparts;
+    const uint2 *src = p.ll_local + (int64_t)(ep & 1u) * p.ll_half;
+    for (int64_t i = i0 + lane; i < i1; i += nlanes) {
+        uint32_t v, e;
+        do {
+            asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(src + i) : "memory");
+        } while (e != ep);
+        const int64_t col = i / p.ll_M, row = i - col * p.ll_M;
+        p.ll_dst[col * p.ll_dst_stride + row] = __uint_as_float(v);
+    }
+    __syncwarp();
+    if (lane == 0) {
+        const uint32_t old = atomicAdd(p.ll_cnt + 1, 1u);
+        if (old == (uint32_t)nparts - 1u) {            // every CTA has read cnt[0] (it read it before it arrived): publish the new count
+            p.ll_cnt[1] = 0u;
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.ll_cnt), "r"(ep) : "memory");
+        }
+    }
 }
 
 // Reads one field of every 64-byte piece of the launch parameters: the first access to a kernel's constant bank misses

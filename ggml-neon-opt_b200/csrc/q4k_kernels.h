@@ -14,6 +14,23 @@ void count_launch();          // bumps the process-wide kernel launch counter (q
 // (p[((n*M + m)*nb + b)*8 + j], sumi / summ[(n*M + m)*nb + b]; p may be null for the GEMM, which never forms p[j])
 struct IntDump { int32_t *p, *sumi, *summ; };
 
+// LL exchange of the row-sharded multi-GPU path (q4k_mul_mat_peers_ll): every result leaves the kernel as an 8-byte
+// {value, epoch} pair, stored (one atomic 8-byte NVLink store, no fence) into the LL buffer of EVERY rank; the tail of the same
+// launch polls this rank's own LL buffer until every rank's pairs of THIS call have arrived and writes them out as plain floats.
+// One launch = compute + all-gather + completion: no flag kernel, no system-scope fence.
+// LL buffer of a rank: [2 halves][n_max columns][M_full rows] pairs; the call's epoch = cnt[0] + 1 (device-side, so a CUDA
+// graph can replay the launch), the half it uses = epoch & 1; cnt[1] = CTA arrival counter (the last CTA publishes cnt[0]).
+struct LLExchange {
+    void *peers[8];          // every rank's LL buffer as mapped on THIS GPU (own one included), indexed by rank
+    void *local;             // this rank's own LL buffer
+    int64_t half_pairs;      // pairs per half = n_max * M_full
+    int64_t M_full;          // rows of the full matrix
+    uint32_t *cnt;           // two zero-initialised words in this rank's device memory
+    float *dst;              // plain F32 result [N][dst_stride] in this rank's memory, complete when the launch completes
+    int64_t dst_stride;      // floats between columns
+    int world;
+};
+
 cudaError_t launch_quantize_q8_K(const float *x, void *y, int64_t k, int64_t nrows, int64_t x_row_stride_bytes,
                                  cudaStream_t stream);
 
@@ -32,7 +49,7 @@ cudaError_t launch_gemv_q4k_q8k_tma(const void *w, int64_t M, int64_t K, int64_t
                                     float *dst, int64_t dst_col_stride_bytes, bool exact_order, int stages,
                                     bool pdl, cudaStream_t stream,
                                     float *const *peer_dst = nullptr, int n_peers = 0, int64_t dst_row0 = 0,
-                                    const IntDump *dump = nullptr, int dump_kernel = 0);
+                                    const IntDump *dump = nullptr, int dump_kernel = 0, const LLExchange *ll = nullptr);
 
 // up to 4 matrices (same K, N) in one launch; see gemv_q4k_tma.cu
 cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
@@ -43,7 +60,11 @@ cudaError_t launch_gemv_q4k_group(int nmat, const void *const *w, const int64_t 
 cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
                                 const void *xq, const float *const *xf, int N, int64_t x_row_stride_bytes,
                                 float *const *dst, int64_t dst_col_stride_bytes, float *const *peer_dst, int n_peers,
-                                int64_t dst_row0, bool pdl, cudaStream_t stream, const IntDump *dump = nullptr);
+                                int64_t dst_row0, bool pdl, cudaStream_t stream, const IntDump *dump = nullptr,
+                                const LLExchange *ll = nullptr);
+
+// the tail of an LL exchange as a kernel of its own: for a rank that owns no rows of a matrix (its launch has nothing to compute)
+cudaError_t launch_ll_gather(const LLExchange &ll, int N, bool pdl, cudaStream_t stream);
 
 // GEMM on tcgen05 (N > 8).  Returns cudaErrorNotSupported when the shape cannot take the tensor path.
 cudaError_t launch_gemm_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,

@@ -56,6 +56,9 @@ def load():
         L.q4k_mul_mat_host_async.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp, vp, vp, sz, vp]
         L.q4k_mul_mat_peers.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp]
         L.q4k_peer_signal_wait.argtypes = [vp, i32, i32, vp, vp]
+        L.q4k_mul_mat_peers_ll.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i32, i64, i64, i64, vp, i64, vp, vp, sz, vp]
+        L.q4k_ll_buffer_bytes.argtypes = [i64, i64]
+        L.q4k_ll_buffer_bytes.restype = sz
         L.q4k_mul_mat_peers_ws.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp, sz, vp]
         L.q4k_mul_mat_peers_sync.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp, sz, vp, i32, i32, vp, vp, vp]
         L.q4k_mul_mat_group.argtypes = [i32, vp, vp, i64, i64, vp, i64, i64, vp, vp]

@@ -6,7 +6,13 @@ plugin's set_tensor), activations are replicated, every GPU runs quantize + GEMV
 output slices are exchanged:
 
   * `gather="nccl"`  one all_gather of [N, M/G] floats per GPU over NVLink/NVSwitch (torch.distributed, NCCL).
-  * `gather="peer"`  no collective kernel at all: the GEMV epilogue stores every result straight into the output
+  * `gather="ll"`    (default when symmetric memory is available) compute + all-gather + completion in ONE launch
+                     (q4k_mul_mat_peers_ll): the kernel's epilogue stores every result as an 8-byte {value, epoch} pair into the
+                     LL buffer of EVERY rank (one atomic NVLink store each, no fence), and the tail of the same launch polls its
+                     own LL buffer until this call's pairs have arrived from everybody and writes them out as plain floats.
+                     No flag kernel; the epoch and the buffer half come from a device-side call counter, so a CUDA graph
+                     replays it with no constraint on how many calls were captured.
+  * `gather="peer"`  (round 1, kept for A/B) no collective kernel at all: the GEMV epilogue stores every result straight into the output
                      buffer of EVERY peer through NVLink-mapped symmetric memory (q4k_mul_mat_peers), followed by
                      one flag exchange (q4k_peer_signal_wait: a one-warp kernel, system-scope release / acquire on
                      peer-mapped flags, device-side epoch so that it replays inside a CUDA graph).  The payload is
@@ -78,8 +84,10 @@ class RowShardedQ4K:
     """One rank's row slice of a Q4_K matrix [M, K] + the exchange that rebuilds the full [N, M] result on every rank.
 
     w_local : uint8 CUDA tensor [m_local, K/256*144] — rows ranges[rank] of the full matrix.
-    gather  : "nccl" (all_gather of the slices) or "peer" (GEMV epilogue stores into every rank's buffer; needs
-              torch symmetric memory over NVLink P2P; N <= 8).  "auto" tries peer and falls back to nccl."""
+    gather  : "nccl" (all_gather of the slices), "ll" (one launch: LL pairs into every rank's buffer + in-kernel gather; needs
+              torch symmetric memory over NVLink P2P; N <= 8) or "peer" (round 1: plain peer stores + a flag kernel).
+              "auto" tries ll and falls back to nccl.  The result of the ll / peer modes is a view of a buffer that the next
+              call (ll) / the call after the next (peer) of this object overwrites."""
 
     def __init__(self, w_local: torch.Tensor, M: int, K: int, group=None, gather: str = "auto", max_n: int = 8, granule: int = 4):
         from . import lib as _lib
@@ -101,15 +109,18 @@ class RowShardedQ4K:
         # so a captured sequence must contain an EVEN number of calls of this object (then replays keep alternating and the
         # "buffer (i + 1) % 2 is free after the exchange of call i" argument of _init_peer holds across replays too).
         self.needs_even_capture = False
-        if gather in ("auto", "peer") and self.world > 1:
+        if gather in ("auto", "ll") and self.world > 1:
             try:
-                self._init_peer()
-                self.gather = "peer"
-                self.needs_even_capture = True
+                self._init_ll()
+                self.gather = "ll"
             except Exception as e:                       # no P2P / symmetric memory on this box: NCCL does the exchange
-                if gather == "peer":
+                if gather == "ll":
                     raise
-                self.peer_note = f"peer gather unavailable ({type(e).__name__}: {e}); using nccl"
+                self.peer_note = f"LL exchange unavailable ({type(e).__name__}: {e}); using nccl"
+        elif gather == "peer" and self.world > 1:
+            self._init_peer()
+            self.gather = "peer"
+            self.needs_even_capture = True
 
     @classmethod
     def from_full(cls, w_full: torch.Tensor, K: int, device, group=None, **kw):
@@ -118,6 +129,21 @@ class RowShardedQ4K:
         world, rank = dist.get_world_size(group), dist.get_rank(group)
         r0, r1 = shard_rows(M, world, kw.get("granule", 4))[rank]
         return cls(w_full[r0:r1].contiguous().to(device), M, K, group=group, **kw)
+
+    def _init_ll(self):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm
+        dev = self.w.device
+        gname = dist.group.WORLD.group_name if self.group is None else self.group.group_name
+        # LL buffer: [2 halves][max_n][M] pairs of {float value, uint32 epoch} = one int64 each, zero-initialised (epoch 0 = never)
+        self._ll = symm.empty((2, self.max_n, self.M), dtype=torch.int64, device=dev)
+        self._ll_hdl = symm.rendezvous(self._ll, gname)
+        self._ll.zero_()
+        self._ll_arr = (C.c_void_p * self.world)(*list(self._ll_hdl.buffer_ptrs))       # indexed by rank
+        self._cnt = torch.zeros(2, dtype=torch.int32, device=dev)                       # call counter, CTA arrivals
+        self._dst = torch.zeros((self.max_n, self.M), dtype=torch.float32, device=dev)  # plain result, complete when the launch is
+        torch.cuda.synchronize(dev)
+        self._ll_hdl.barrier(channel=0)
 
     def _init_peer(self):
         import ctypes as C
@@ -156,6 +182,15 @@ class RowShardedQ4K:
         N = x.shape[0]
         lib = self._lib.load()
         st = torch.cuda.current_stream().cuda_stream
+        if self.gather == "ll" and N <= self.max_n:
+            if self._ws is None:
+                self._ws = torch.empty(max(self._lib.workspace_bytes(self.K, self.max_n), 16), dtype=torch.uint8, device=self.w.device)
+            rc = lib.q4k_mul_mat_peers_ll(self.w.data_ptr(), self.r1 - self.r0, self.K, self.w.stride(0), x.data_ptr(), N, x.stride(0) * 4,
+                                          self._ll_arr, self.world, self.rank, self.M, self.max_n, self.r0,
+                                          self._dst.data_ptr(), self.M * 4, self._cnt.data_ptr(), self._ws.data_ptr(), self._ws.numel(), st)
+            if rc != 0:
+                raise self._lib.Q4KError("q4k_mul_mat_peers_ll", rc, lib.q4k_last_cuda_error())
+            return self._dst[:N]
         if self.gather == "peer" and N <= self.max_n:
             b = self._flip
             self._flip ^= 1

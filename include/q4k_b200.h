@@ -113,6 +113,25 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
                          float *const *dst_peers, int n_peers, int64_t dst_row0, int64_t dst_col_stride_bytes,
                          void *workspace_dev, size_t workspace_bytes, void *stream);
 
+/* Row-sharded multi-GPU decode with the LL exchange — compute, all-gather and completion in ONE launch, without a flag kernel
+ * and without a system-scope fence.  Every result leaves the kernel as an 8-byte {value, epoch} pair stored (one atomic NVLink
+ * store) into the LL buffer of EVERY rank; the tail of the same launch polls this rank's own LL buffer until the pairs of this
+ * call have arrived from everybody and writes them to dst_dev as plain floats: when the launch completes, dst_dev (this
+ * GPU's memory, N columns of M_full rows at dst_col_stride_bytes) holds the full result.  What it replaces in the reference:
+ * the event + cudaMemcpyPeerAsync gather of a row split (L/ggml/src/ggml-cuda/ggml-cuda.cu:1720-1760).
+ *   ll_peers[r]  rank r's LL buffer as mapped on this GPU (q4k_ll_buffer_bytes(M_full, n_max) bytes, zero-initialised once,
+ *                the same allocation on every rank: [2 halves][n_max][M_full] pairs);
+ *   cnt_dev      two zero-initialised uint32 in this rank's memory (call counter, CTA arrivals).  The epoch of a call and the
+ *                half it uses are derived from the counter ON THE DEVICE, so the launch can be captured into a CUDA graph and
+ *                replayed; every rank must make the same sequence of calls on its copy of the object.
+ * A rank with M_local == 0 still calls (it only gathers).  N <= 8. */
+size_t q4k_ll_buffer_bytes(int64_t M_full, int64_t n_max);
+int q4k_mul_mat_peers_ll(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
+                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                         void *const *ll_peers, int world, int rank, int64_t M_full, int64_t n_max, int64_t dst_row0,
+                         float *dst_dev, int64_t dst_col_stride_bytes, void *cnt_dev,
+                         void *workspace_dev, size_t workspace_bytes, void *stream);
+
 /* q4k_mul_mat_peers_ws + the cross-GPU step in ONE kernel: the decode kernel's last CTA publishes this rank's epoch into
  * every peer's flag row and waits for theirs, so when the launch completes every rank's rows have landed in this rank's
  * buffer — compute, all-gather and barrier in one launch.  Measured on B200 it is SLOWER than q4k_mul_mat_peers_ws followed by
