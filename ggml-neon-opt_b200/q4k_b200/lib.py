@@ -18,7 +18,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.environ.get("Q4K_B200_LIB") or os.path.normpath(os.path.join(_HERE, "..", "lib", "libq4k_b200.so"))
 _lib = None
 
-_ERR = {-1: "bad shape", -2: "bad pointer", -3: "workspace too small", -4: "CUDA error", -5: "unsupported"}
+_ERR = {-1: "bad shape", -2: "bad pointer", -3: "workspace too small", -4: "CUDA error", -5: "unsupported",
+        -6: "beyond the static scratch limit of q4k_mul_mat_noalloc"}
 
 
 class Q4KError(RuntimeError):
@@ -48,6 +49,7 @@ def load():
         L.q4k_mul_mat_workspace_bytes.argtypes = [i64, i64]
         L.q4k_mul_mat_workspace_bytes.restype = sz
         L.q4k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
+        L.q4k_mul_mat_noalloc.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q4k_mul_mat_reuse.argtypes = [vp, i64, i64, i64, i64, vp, i64, vp, sz, vp]
         L.q4k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q4k_vec_dot_q4_K_q8_K.argtypes = [i32, vp, sz, vp, sz, vp, sz, i32]

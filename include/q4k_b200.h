@@ -36,6 +36,7 @@ enum {
     Q4K_ERR_WORKSPACE    = -3,   /* workspace smaller than q4k_mul_mat_workspace_bytes() */
     Q4K_ERR_CUDA         = -4,   /* a CUDA runtime call failed; q4k_last_cuda_error() has the code */
     Q4K_ERR_UNSUPPORTED  = -5,   /* nrc not in {1}, device is not sm_100 ... */
+    Q4K_ERR_STATIC_LIMIT = -6,   /* q4k_mul_mat_noalloc: the shape needs more scratch than the library's static array holds */
 };
 
 /* library / device ------------------------------------------------------------------------------- */
@@ -88,6 +89,21 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
                 const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
                 float *dst_dev, int64_t dst_col_stride_bytes,
                 void *workspace_dev, size_t workspace_bytes, void *stream);
+
+/* q4k_mul_mat for callers that CANNOT allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc): the same decode mul_mat (N <= 8) with the Q8_K scratch in a static device array inside the library
+ * instead of a caller-supplied workspace.  No counterpart in the reference.
+ *   - calls no cudaMalloc / cudaFree / allocating library routine; inputs and outputs are still the caller's;
+ *   - limit: N <= 8 and N * K/256 * 292 <= Q4K_NOALLOC_SCRATCH_BYTES (1 MiB: K up to 114688 at N = 8), else
+ *     Q4K_ERR_STATIC_LIMIT; every GPU that loads the library holds the 1 MiB until the process exits;
+ *   - runs on the CURRENT device; results are bit-identical to q4k_mul_mat on the same inputs;
+ *   - all calls on a device share the one array, which keeps the last call's contents (nothing in it needs to start at zero:
+ *     the quantizer overwrites every block the decode kernel reads).  Calls that OVERLAP on the GPU (two streams, two threads
+ *     on one device) race on it: serialise them, or use q4k_mul_mat with your own workspace. */
+#define Q4K_NOALLOC_SCRATCH_BYTES (1 << 20)
+int q4k_mul_mat_noalloc(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                        const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
+                        float *dst_dev, int64_t dst_col_stride_bytes, void *stream);
 
 /* prefill (N > 12): the mul_mat in front of this one (same stream, same workspace) read the SAME activations — attn_q /
  * attn_k / attn_v or ffn_gate / ffn_up of a layer, separate ggml_mul_mat nodes on one src1 in the reference's graph — so their
