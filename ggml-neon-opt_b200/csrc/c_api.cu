@@ -209,7 +209,7 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
 
 size_t q4k_ll_buffer_bytes(int64_t M_full, int64_t n_max) {
     if (M_full <= 0 || n_max <= 0) return 0;
-    return (size_t)2 * (size_t)n_max * (size_t)M_full * 8;
+    return (size_t)2 * (size_t)n_max * (size_t)M_full * 8 + 2 * 8 * 8;       // data pairs + presence pairs
 }
 
 int q4k_mul_mat_peers_ll(const void *w_dev, int64_t M_local, int64_t K, int64_t w_row_stride_bytes,
@@ -229,7 +229,7 @@ int q4k_mul_mat_peers_ll(const void *w_dev, int64_t M_local, int64_t K, int64_t 
         ll.peers[r] = ll_peers[r];
     }
     ll.local = ll_peers[rank]; ll.half_pairs = n_max * M_full; ll.M_full = M_full;
-    ll.cnt = static_cast<uint32_t *>(cnt_dev); ll.dst = dst_dev; ll.dst_stride = dst_col_stride_bytes / 4; ll.world = world;
+    ll.cnt = static_cast<uint32_t *>(cnt_dev); ll.dst = dst_dev; ll.dst_stride = dst_col_stride_bytes / 4; ll.world = world; ll.rank = rank;
     cudaStream_t st = (cudaStream_t)stream;
     if (M_local == 0) {                        // nothing to compute here: gather everybody else's rows
         const cudaError_t e = launch_ll_gather(ll, (int)N, knobs().pdl != 0, st);

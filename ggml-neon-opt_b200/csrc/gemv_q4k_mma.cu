@@ -314,7 +314,7 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
         int mat = 0, b = 0, xs = 0;
         uint32_t fparity = 0, xparity = 0, cparity = 1;
         uint32_t ll_ep = 0;
-        if (p.ll_world > 0) { griddep_wait(); ll_ep = ll_epoch(p); }
+        if (p.ll_world > 0) { griddep_wait(); ll_ep = ll_epoch(p); if (blockIdx.x == 0) ll_presence(p, ll_ep, lane); }
         for (int64_t tile = t0; tile < t1; tile += tstep) {
             const int64_t lt = locate(tile, mat);
             const int64_t m_rows = p.Mm[mat];

@@ -128,6 +128,7 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
     touch_params(p);
     griddep_wait();
     const uint32_t ll_ep = p.ll_world > 0 ? ll_epoch(p) : 0u;     // every warp reads it before the barrier below, i.e. before this CTA can arrive
+    if (p.ll_world > 0 && blockIdx.x == 0 && warp == 0) ll_presence(p, ll_ep, lane);
     if (p.xq) stage_q8<N>(p, q8_s, d_s);
     else stage.run(q8_s, d_s);
     __syncthreads();
@@ -479,7 +480,9 @@ namespace {
 __global__ void __launch_bounds__(32) ll_gather_kernel(const __grid_constant__ TmaGemvParams p, int N) {
     griddep_launch_dependents();
     griddep_wait();
-    ll_tail(p, N, ll_epoch(p), blockIdx.x, gridDim.x, threadIdx.x, 32);
+    const uint32_t ep = ll_epoch(p);
+    if (blockIdx.x == 0) ll_presence(p, ep, threadIdx.x);
+    ll_tail(p, N, ep, blockIdx.x, gridDim.x, threadIdx.x, 32);
 }
 }  // namespace
 

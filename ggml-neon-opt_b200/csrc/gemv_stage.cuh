@@ -63,17 +63,17 @@ struct TmaGemvParams {
     int64_t ll_half, ll_M, ll_dst_stride;
     uint32_t *ll_cnt;
     float *ll_dst;
-    int ll_world;
+    int ll_world, ll_rank;
 };
 
 inline void fill_ll(TmaGemvParams &p, const LLExchange *ll) {
     for (int r = 0; r < 8; ++r) p.ll_peers[r] = nullptr;
-    p.ll_local = nullptr; p.ll_half = p.ll_M = p.ll_dst_stride = 0; p.ll_cnt = nullptr; p.ll_dst = nullptr; p.ll_world = 0;
+    p.ll_local = nullptr; p.ll_half = p.ll_M = p.ll_dst_stride = 0; p.ll_cnt = nullptr; p.ll_dst = nullptr; p.ll_world = 0; p.ll_rank = 0;
     if (!ll) return;
     for (int r = 0; r < ll->world; ++r) p.ll_peers[r] = static_cast<uint2 *>(ll->peers[r]);
     p.ll_local = static_cast<const uint2 *>(ll->local);
     p.ll_half = ll->half_pairs; p.ll_M = ll->M_full; p.ll_dst_stride = ll->dst_stride;
-    p.ll_cnt = ll->cnt; p.ll_dst = ll->dst; p.ll_world = ll->world;
+    p.ll_cnt = ll->cnt; p.ll_dst = ll->dst; p.ll_world = ll->world; p.ll_rank = ll->rank;
 }
 
 inline void fill_sync(TmaGemvParams &p, int n_peers) {
@@ -328,6 +328,14 @@ __device__ __forceinline__ void ll_store(const TmaGemvParams &p, uint32_t ep, in
     for (int g = 0; g < p.ll_world; ++g)
         asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p.ll_peers[g] + i), "r"(__float_as_uint(v)), "r"(ep) : "memory");
 }
+// "this rank has started call ep" -> every rank (ONE warp of the launch, after it has read the epoch, i.e. after this rank's
+// previous call has completed): see the back-pressure note at LLExchange
+__device__ __forceinline__ void ll_presence(const TmaGemvParams &p, uint32_t ep, int lane) {
+    if (lane < p.ll_world) {
+        uint2 *slot = p.ll_peers[lane] + 2 * p.ll_half + (int64_t)(ep & 1u) * 8 + p.ll_rank;
+        asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(slot), "r"(0u), "r"(ep) : "memory");
+    }
+}
 // The tail: `nlanes` threads of ONE warp-sized group per CTA (lane = 0..nlanes-1) take slice `part` of `nparts` of the gathered
 // [N][M_full] vector, wait for each pair of this call to arrive in the rank's own LL buffer (whoever computes it: another
 // rank over NVLink, or a CTA of this launch) and write it out as a plain float.  The last CTA to finish publishes the call
@@ -336,6 +344,13 @@ __device__ __forceinline__ void ll_tail(const TmaGemvParams &p, int N, uint32_t 
     const int64_t total = (int64_t)N * p.ll_M;
     const int64_t i0 = total * part / nparts, i1 = total * (part + 1) / nparts;
     const uint2 *src = p.ll_local + (int64_t)(ep & 1u) * p.ll_half;
+    if (part == 0 && lane < p.ll_world) {          // every rank has started this call (= has finished reading the call before)
+        const uint2 *slot = p.ll_local + 2 * p.ll_half + (int64_t)(ep & 1u) * 8 + lane;
+        uint32_t v, e;
+        do {
+            asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(slot) : "memory");
+        } while (e != ep);
+    }
     for (int64_t i = i0 + lane; i < i1; i += nlanes) {
         uint32_t v, e;
         do {

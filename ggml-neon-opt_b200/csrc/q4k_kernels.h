@@ -18,7 +18,11 @@ struct IntDump { int32_t *p, *sumi, *summ; };
 // {value, epoch} pair, stored (one atomic 8-byte NVLink store, no fence) into the LL buffer of EVERY rank; the tail of the same
 // launch polls this rank's own LL buffer until every rank's pairs of THIS call have arrived and writes them out as plain floats.
 // One launch = compute + all-gather + completion: no flag kernel, no system-scope fence.
-// LL buffer of a rank: [2 halves][n_max columns][M_full rows] pairs; the call's epoch = cnt[0] + 1 (device-side, so a CUDA
+// Back-pressure: a rank may overwrite half h with call k + 2 only after EVERY rank has finished reading call k out of it.  Data
+// pairs give that for ranks that own rows (a rank's call-(k+1) pairs leave after its call k has completed, and everybody's
+// call k + 1 waits for them); a rank that owns NO rows sends nothing, so every rank also sends one "presence" pair per call
+// ({0, epoch} into slot [half][rank] behind the data) and every tail waits for all of them.
+// LL buffer of a rank: [2 halves][n_max columns][M_full rows] pairs + [2 halves][8] presence pairs; the call's epoch = cnt[0] + 1 (device-side, so a CUDA
 // graph can replay the launch), the half it uses = epoch & 1; cnt[1] = CTA arrival counter (the last CTA publishes cnt[0]).
 struct LLExchange {
     void *peers[8];          // every rank's LL buffer as mapped on THIS GPU (own one included), indexed by rank
@@ -28,7 +32,7 @@ struct LLExchange {
     uint32_t *cnt;           // two zero-initialised words in this rank's device memory
     float *dst;              // plain F32 result [N][dst_stride] in this rank's memory, complete when the launch completes
     int64_t dst_stride;      // floats between columns
-    int world;
+    int world, rank;
 };
 
 cudaError_t launch_quantize_q8_K(const float *x, void *y, int64_t k, int64_t nrows, int64_t x_row_stride_bytes,

@@ -136,7 +136,8 @@ class RowShardedQ4K:
         dev = self.w.device
         gname = dist.group.WORLD.group_name if self.group is None else self.group.group_name
         # LL buffer: [2 halves][max_n][M] pairs of {float value, uint32 epoch} = one int64 each, zero-initialised (epoch 0 = never)
-        self._ll = symm.empty((2, self.max_n, self.M), dtype=torch.int64, device=dev)
+        nbytes = self._lib.load().q4k_ll_buffer_bytes(self.M, self.max_n)                  # data pairs + presence pairs
+        self._ll = symm.empty((nbytes // 8,), dtype=torch.int64, device=dev)
         self._ll_hdl = symm.rendezvous(self._ll, gname)
         self._ll.zero_()
         self._ll_arr = (C.c_void_p * self.world)(*list(self._ll_hdl.buffer_ptrs))       # indexed by rank

@@ -136,7 +136,7 @@ int q4k_mul_mat_peers_ws(const void *w_dev, int64_t M_local, int64_t K, int64_t 
  * GPU's memory, N columns of M_full rows at dst_col_stride_bytes) holds the full result.  What it replaces in the reference:
  * the event + cudaMemcpyPeerAsync gather of a row split (L/ggml/src/ggml-cuda/ggml-cuda.cu:1720-1760).
  *   ll_peers[r]  rank r's LL buffer as mapped on this GPU (q4k_ll_buffer_bytes(M_full, n_max) bytes, zero-initialised once,
- *                the same allocation on every rank: [2 halves][n_max][M_full] pairs);
+ *                the same allocation on every rank: [2 halves][n_max][M_full] data pairs + [2][8] presence pairs);
  *   cnt_dev      two zero-initialised uint32 in this rank's memory (call counter, CTA arrivals).  The epoch of a call and the
  *                half it uses are derived from the counter ON THE DEVICE, so the launch can be captured into a CUDA graph and
  *                replayed; every rank must make the same sequence of calls on its copy of the object.
