@@ -21,8 +21,10 @@
 #include "ggml-impl.h"
 #include "ggml.h"
 
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -324,26 +326,57 @@ bool groupable(const ggml_tensor * node) {
            src1->ne[1] <= Q4K_GEMV_MAX_N && src0->ne[1] > 0 && node->nb[1] == (size_t) src0->ne[1] * sizeof(float);
 }
 
-// Consecutive MUL_MAT nodes that read the same activations (attn_q / attn_k / attn_v, ffn_gate / ffn_up: separate
-// ggml_mul_mat nodes on one `cur` in the reference's llama graph) go out as ONE launch (q4k_mul_mat_group).
-// Returns the number of nodes consumed starting at cgraph->nodes[i] (0 = not fused, caller runs the node by itself).
-int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i) {
+bool is_noop(const ggml_tensor * node);
+
+// byte ranges of two tensors overlap (views carry their own data pointer; ggml_nbytes covers strided extents)
+bool overlaps(const ggml_tensor * a, const ggml_tensor * b) {
+    if (!a || !b || !a->data || !b->data) return false;
+    const char * a0 = (const char *) a->data, * b0 = (const char *) b->data;
+    return a0 < b0 + ggml_nbytes(b) && b0 < a0 + ggml_nbytes(a);
+}
+
+// May mul_mat node `h` run BEFORE the launching node `b` that precedes it in graph order?  (ggml-alloc reuses the memory of dead
+// tensors for later nodes, so "no data dependency" has to be checked on addresses, not on the graph.)
+bool can_hoist_over(const ggml_tensor * h, const ggml_tensor * b) {
+    if (overlaps(h, b)) return false;                                        // b's result would land on h's
+    for (int k = 0; k < GGML_MAX_SRC; ++k) {
+        if (overlaps(h, b->src[k])) return false;                            // h's result would land on something b still reads
+        if (overlaps(h->src[k], b)) return false;                            // h reads what b writes: a true dependency
+    }
+    return true;
+}
+
+// MUL_MAT nodes that read the same activations (attn_q / attn_k / attn_v, ffn_gate / ffn_up: separate ggml_mul_mat nodes on
+// one `cur` in the reference's llama graph) go out as ONE launch (q4k_mul_mat_group).  The members need not be adjacent: the
+// llama graph puts rope(q) between attn_q and attn_k (L/src/llama-graph.cpp build_attn: q_cur, k_cur, v_cur are expanded one
+// after the other); a later member is pulled in front of such nodes when no byte range says otherwise (can_hoist_over).
+// Marks every consumed node in `done`; returns the number of mul_mats fused (0 = not fused, -1 = launch failed).
+int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i, std::vector<char> & done) {
     ggml_tensor * first = cgraph->nodes[i];
     if (!groupable(first)) return 0;
     const void * w[4];
     int64_t M[4];
     const float * x[4];
     float * dst[4];
-    int n = 0, last = i;
-    for (int j = i; j < cgraph->n_nodes && n < 4; ++j) {
+    int idx[4];
+    int n = 0;
+    std::vector<const ggml_tensor *> skipped;                                 // launching nodes between the members
+    for (int j = i; j < cgraph->n_nodes && n < 4 && j < i + 12; ++j) {
         ggml_tensor * node = cgraph->nodes[j];
-        if (node->op == GGML_OP_NONE || node->op == GGML_OP_RESHAPE || node->op == GGML_OP_VIEW || node->op == GGML_OP_PERMUTE ||
-            node->op == GGML_OP_TRANSPOSE) continue;                          // no-ops in between do not break a group
-        if (node->op != GGML_OP_MUL_MAT || !mul_mat_supported(node) || !groupable(node)) break;
-        if (node->src[1] != first->src[1] || node->src[0]->ne[0] != first->src[0]->ne[0] || node->src[0]->nb[1] != first->src[0]->nb[1]) break;
+        if (is_noop(node) || done[j]) continue;
+        const bool member = node->op == GGML_OP_MUL_MAT && mul_mat_supported(node) && groupable(node) && node->src[1] == first->src[1] &&
+                            node->src[0]->ne[0] == first->src[0]->ne[0] && node->src[0]->nb[1] == first->src[0]->nb[1];
+        bool ok = member;
+        for (size_t k = 0; ok && k < skipped.size(); ++k) ok = can_hoist_over(node, skipped[k]);
+        for (int k = 0; ok && k < n; ++k) ok = !overlaps(node, cgraph->nodes[idx[k]]);     // two members never share a result range
+        if (!ok) {
+            if (node->op == GGML_OP_MUL_MAT) break;                           // a mul_mat that cannot join ends the search
+            skipped.push_back(node);
+            continue;
+        }
         w[n] = node->src[0]->data; M[n] = node->src[0]->ne[1]; x[n] = (const float *) node->src[1]->data; dst[n] = (float *) node->data;
+        idx[n] = j;
         ++n;
-        last = j;
     }
     if (n < 2) return 0;
     const ggml_tensor * src1 = first->src[1];
@@ -354,7 +387,136 @@ int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i) {
         GGML_LOG_ERROR("Q4K_B200: q4k_mul_mat_group(%s ...) failed: rc=%d cudaError=%d\n", first->name, rc, q4k_last_cuda_error());
         return -1;
     }
-    return last - i + 1;
+    for (int k = 0; k < n; ++k) done[idx[k]] = 1;
+    return n;
+}
+
+// ---- the cheap F32 ops around the mul_mats (kernels: csrc/ops.cu) -------------------------------
+bool f32_rows(const ggml_tensor * t) {       // F32, dense dim 0, 4-byte-multiple strides
+    return t && t->type == GGML_TYPE_F32 && t->nb[0] == sizeof(float) && !((t->nb[1] | t->nb[2] | t->nb[3]) & 3);
+}
+
+bool rms_norm_supported(const ggml_tensor * op) {
+    return f32_rows(op->src[0]) && f32_rows(op) && ggml_are_same_shape(op->src[0], op) && ggml_nrows(op) <= 0x7fffffff;
+}
+
+bool binary_supported(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    return f32_rows(a) && f32_rows(b) && f32_rows(op) && ggml_are_same_shape(a, op) && ggml_can_repeat(b, a) && ggml_nrows(op) <= 65535;
+}
+
+bool glu_supported(const ggml_tensor * op) {
+    const ggml_tensor * g = op->src[0], * u = op->src[1];
+    if (ggml_get_glu_op(op) != GGML_GLU_OP_SWIGLU || !u) return false;                 // split form only (what build_ffn emits)
+    return f32_rows(g) && f32_rows(u) && f32_rows(op) && ggml_is_contiguous_1(g) && ggml_is_contiguous_1(u) && ggml_is_contiguous_1(op) &&
+           ggml_are_same_shape(g, u) && op->ne[0] == g->ne[0] && ggml_nrows(op) == ggml_nrows(g) && ggml_nrows(op) <= 65535;
+}
+
+bool get_rows_supported(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * ids = op->src[1];
+    return f32_rows(a) && f32_rows(op) && ids && ids->type == GGML_TYPE_I32 && ggml_is_contiguous(ids) && a->ne[2] == 1 && a->ne[3] == 1 &&
+           ids->ne[1] == 1 && ids->ne[2] == 1 && ids->ne[3] == 1 && ids->ne[0] <= 65535;
+}
+
+bool rope_supported(const ggml_tensor * op) {
+    const ggml_tensor * x = op->src[0], * pos = op->src[1], * ff = op->src[2];
+    const int32_t * prm = (const int32_t *) op->op_params;
+    const int n_dims = prm[1], mode = prm[2];
+    if (mode != GGML_ROPE_TYPE_NORMAL && mode != GGML_ROPE_TYPE_NEOX) return false;            // no mrope / vision
+    if (!f32_rows(x) || !f32_rows(op) || !ggml_are_same_shape(x, op) || !pos || pos->type != GGML_TYPE_I32 || !ggml_is_contiguous(pos)) return false;
+    if (pos->ne[0] != x->ne[2] || (x->ne[0] & 1) || n_dims <= 0 || (n_dims & 1) || n_dims > x->ne[0]) return false;
+    if (ff && (ff->type != GGML_TYPE_F32 || !ggml_is_contiguous(ff) || ff->ne[0] < n_dims / 2)) return false;
+    return x->ne[1] <= 65535 && x->ne[2] * x->ne[3] <= 65535;
+}
+
+ggml_status op_failed(const char * what, const ggml_tensor * node, int rc) {
+    GGML_LOG_ERROR("Q4K_B200: %s(%s) failed: rc=%d cudaError=%d\n", what, node->name, rc, q4k_last_cuda_error());
+    return GGML_STATUS_FAILED;
+}
+
+// RMS_NORM, optionally with the residual ADD in front of it (`add`: its result is still written — the residual stream needs it)
+// and the MUL by the norm weight behind it (`mul`) in the same launch
+ggml_status compute_rms_norm(backend_context * ctx, const ggml_tensor * add, const ggml_tensor * norm, const ggml_tensor * mul) {
+    const ggml_tensor * x = add ? add->src[0] : norm->src[0];
+    const ggml_tensor * res = add ? add->src[1] : nullptr;
+    const ggml_tensor * out = mul ? mul : norm;
+    const ggml_tensor * w = mul ? (mul->src[0] == norm ? mul->src[1] : mul->src[0]) : nullptr;
+    float eps;
+    memcpy(&eps, norm->op_params, sizeof(float));
+    const int64_t x_nb[3] = {(int64_t) x->nb[1], (int64_t) x->nb[2], (int64_t) x->nb[3]};
+    const int64_t y_nb[3] = {(int64_t) out->nb[1], (int64_t) out->nb[2], (int64_t) out->nb[3]};
+    int64_t r_nb[3] = {0, 0, 0}, s_nb[3] = {0, 0, 0};
+    if (add) {
+        for (int d = 0; d < 3; ++d) { r_nb[d] = (int64_t) res->nb[d + 1]; s_nb[d] = (int64_t) add->nb[d + 1]; }
+    }
+    const int rc = q4k_op_rms_norm((const float *) x->data, x_nb, res ? (const float *) res->data : nullptr, r_nb, w ? (const float *) w->data : nullptr,
+                                   (float *) out->data, y_nb, add ? (float *) add->data : nullptr, s_nb, norm->ne, eps, ctx->stream);
+    return rc == Q4K_OK ? GGML_STATUS_SUCCESS : op_failed("q4k_op_rms_norm", norm, rc);
+}
+
+// how many nodes from cgraph->nodes[i] go into one q4k_op_rms_norm launch: [ADD] RMS_NORM [MUL by a broadcast weight row]
+int norm_chain(const ggml_cgraph * cgraph, int i, const ggml_tensor *& add, const ggml_tensor *& norm, const ggml_tensor *& mul) {
+    add = norm = mul = nullptr;
+    int j = i;
+    const ggml_tensor * n0 = cgraph->nodes[j];
+    if (n0->op == GGML_OP_ADD) {
+        if (j + 1 >= cgraph->n_nodes || !binary_supported(n0) || !ggml_are_same_shape(n0->src[0], n0->src[1])) return 0;
+        const ggml_tensor * n1 = cgraph->nodes[j + 1];
+        if (n1->op != GGML_OP_RMS_NORM || n1->src[0] != n0 || !rms_norm_supported(n1)) return 0;
+        add = n0;
+        ++j;
+    }
+    if (cgraph->nodes[j]->op != GGML_OP_RMS_NORM || !rms_norm_supported(cgraph->nodes[j])) return 0;
+    norm = cgraph->nodes[j];
+    if (j + 1 < cgraph->n_nodes && ggml_can_fuse(cgraph, j, {GGML_OP_RMS_NORM, GGML_OP_MUL})) {
+        const ggml_tensor * m = cgraph->nodes[j + 1];
+        const ggml_tensor * w = m->src[0] == norm ? m->src[1] : m->src[0];
+        if (binary_supported(m) && w != norm && f32_rows(w) && w->ne[0] == norm->ne[0] && ggml_nrows(w) == 1) { mul = m; ++j; }
+    }
+    return j - i + 1;
+}
+
+ggml_status compute_binary(backend_context * ctx, const ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0], * b = node->src[1];
+    const int64_t a_nb[3] = {(int64_t) a->nb[1], (int64_t) a->nb[2], (int64_t) a->nb[3]};
+    const int64_t b_nb[3] = {(int64_t) b->nb[1], (int64_t) b->nb[2], (int64_t) b->nb[3]};
+    const int64_t d_nb[3] = {(int64_t) node->nb[1], (int64_t) node->nb[2], (int64_t) node->nb[3]};
+    const int rc = q4k_op_binary(node->op == GGML_OP_ADD ? Q4K_OP_ADD : Q4K_OP_MUL, (const float *) a->data, a->ne, a_nb, (const float *) b->data, b->ne,
+                                 b_nb, (float *) node->data, d_nb, ctx->stream);
+    return rc == Q4K_OK ? GGML_STATUS_SUCCESS : op_failed("q4k_op_binary", node, rc);
+}
+
+ggml_status compute_glu(backend_context * ctx, const ggml_tensor * node) {
+    const ggml_tensor * g = node->src[0], * u = node->src[1];
+    const int rc = q4k_op_swiglu((const float *) g->data, (int64_t) g->nb[1], (const float *) u->data, (int64_t) u->nb[1], (float *) node->data,
+                                 (int64_t) node->nb[1], node->ne[0], ggml_nrows(node), ctx->stream);
+    return rc == Q4K_OK ? GGML_STATUS_SUCCESS : op_failed("q4k_op_swiglu", node, rc);
+}
+
+ggml_status compute_get_rows(backend_context * ctx, const ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0], * ids = node->src[1];
+    const int rc = q4k_op_get_rows_f32((const float *) a->data, (int64_t) a->nb[1], a->ne[1], (const int32_t *) ids->data, ids->ne[0],
+                                       (float *) node->data, (int64_t) node->nb[1], node->ne[0], ctx->stream);
+    return rc == Q4K_OK ? GGML_STATUS_SUCCESS : op_failed("q4k_op_get_rows_f32", node, rc);
+}
+
+ggml_status compute_rope(backend_context * ctx, const ggml_tensor * node) {
+    const ggml_tensor * x = node->src[0], * pos = node->src[1], * ff = node->src[2];
+    const int32_t * prm = (const int32_t *) node->op_params;
+    const int n_dims = prm[1], mode = prm[2], n_ctx_orig = prm[4];
+    float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+    memcpy(&freq_base, prm + 5, 4); memcpy(&freq_scale, prm + 6, 4); memcpy(&ext_factor, prm + 7, 4);
+    memcpy(&attn_factor, prm + 8, 4); memcpy(&beta_fast, prm + 9, 4); memcpy(&beta_slow, prm + 10, 4);
+    // the two host-side derivations of ggml_compute_forward_rope_f32 (ops.cpp:5584-5587), with the reference's own libm / helper
+    const float theta_scale = powf(freq_base, -2.0f / n_dims);
+    float corr_dims[2];
+    ggml_rope_yarn_corr_dims(n_dims, n_ctx_orig, freq_base, beta_fast, beta_slow, corr_dims);
+    const int64_t x_nb[3] = {(int64_t) x->nb[1], (int64_t) x->nb[2], (int64_t) x->nb[3]};
+    const int64_t d_nb[3] = {(int64_t) node->nb[1], (int64_t) node->nb[2], (int64_t) node->nb[3]};
+    const int rc = q4k_op_rope((const float *) x->data, x_nb, (const int32_t *) pos->data, ff ? (const float *) ff->data : nullptr, (float *) node->data,
+                               d_nb, x->ne, n_dims, mode == GGML_ROPE_TYPE_NEOX, theta_scale, freq_scale, ext_factor, attn_factor, corr_dims[0],
+                               corr_dims[1], ctx->stream);
+    return rc == Q4K_OK ? GGML_STATUS_SUCCESS : op_failed("q4k_op_rope", node, rc);
 }
 
 bool is_noop(const ggml_tensor * node) {
@@ -395,8 +557,9 @@ void graph_signature(const ggml_cgraph * cgraph, std::vector<uint64_t> & sig, in
         const ggml_tensor * node = cgraph->nodes[i];
         if (is_noop(node)) continue;
         ++launching;
-        const ggml_tensor * t[3] = {node, node->src[0], node->src[1]};
-        sig.push_back((uint64_t) node->op);
+        const ggml_tensor * t[4] = {node, node->src[0], node->src[1], node->src[2]};
+        sig.push_back((uint64_t) node->op | ((uint64_t) (uint32_t) node->op_params[0] << 32));      // op_params[0]: eps of RMS_NORM, the GLU kind
+        if (node->op == GGML_OP_ROPE) for (int k = 1; k < 11; ++k) sig.push_back((uint64_t) (uint32_t) node->op_params[k]);
         for (const ggml_tensor * x : t) {
             if (!x) { sig.push_back(0); continue; }
             sig.push_back((uint64_t) (uintptr_t) x->data);
@@ -411,16 +574,18 @@ void graph_signature(const ggml_cgraph * cgraph, std::vector<uint64_t> & sig, in
 ggml_status enqueue_nodes(backend_context * ctx, ggml_cgraph * cgraph) {
     const ggml_tensor * last_quantized = nullptr;      // src1 whose prefill-quantized copy is in the workspace right now
     const void * last_quantized_data = nullptr;
+    std::vector<char> done(cgraph->n_nodes, 0);         // mul_mats that already went out with an earlier node's group launch
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
+        if (done[i]) continue;
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
                 if (!mul_mat_supported(node)) {
                     GGML_ABORT("Q4K_B200: %s: MUL_MAT node outside the supports_op contract reached graph_compute", node->name);
                 }
-                const int fused = try_fused_group(ctx, cgraph, i);
+                const int fused = try_fused_group(ctx, cgraph, i, done);
                 if (fused < 0) return GGML_STATUS_FAILED;
-                if (fused > 0) { i += fused - 1; last_quantized = nullptr; break; }
+                if (fused > 0) { last_quantized = nullptr; break; }
                 // consecutive prefill mul_mats on one src1 (q/k/v, gate/up) share the quantized copy of the activations
                 const ggml_tensor * s0 = node->src[0], * s1 = node->src[1];
                 const bool plain2d = s0->ne[2] == 1 && s0->ne[3] == 1 && s1->ne[2] == 1 && s1->ne[3] == 1;
@@ -429,6 +594,44 @@ ggml_status enqueue_nodes(backend_context * ctx, ggml_cgraph * cgraph) {
                 if (st != GGML_STATUS_SUCCESS) return st;
                 if (plain2d && s0->type == GGML_TYPE_Q4_K) { last_quantized = s1; last_quantized_data = s1->data; }
                 else { last_quantized = nullptr; last_quantized_data = nullptr; }
+            } break;
+            case GGML_OP_ADD:
+            case GGML_OP_RMS_NORM: {
+                const ggml_tensor * add, * norm, * mul;
+                const int n = norm_chain(cgraph, i, add, norm, mul);       // [ADD] RMS_NORM [MUL] in one launch
+                last_quantized = nullptr;
+                if (n > 0) {
+                    const ggml_status st = compute_rms_norm(ctx, add, norm, mul);
+                    if (st != GGML_STATUS_SUCCESS) return st;
+                    i += n - 1;
+                    break;
+                }
+                if (node->op == GGML_OP_RMS_NORM) GGML_ABORT("Q4K_B200: %s: RMS_NORM node outside the supports_op contract", node->name);
+            }
+            [[fallthrough]];      // a plain ADD
+            case GGML_OP_MUL: {
+                if (!binary_supported(node)) GGML_ABORT("Q4K_B200: %s: %s node outside the supports_op contract", node->name, ggml_op_name(node->op));
+                last_quantized = nullptr;
+                const ggml_status st = compute_binary(ctx, node);
+                if (st != GGML_STATUS_SUCCESS) return st;
+            } break;
+            case GGML_OP_GLU: {
+                if (!glu_supported(node)) GGML_ABORT("Q4K_B200: %s: GLU node outside the supports_op contract", node->name);
+                last_quantized = nullptr;
+                const ggml_status st = compute_glu(ctx, node);
+                if (st != GGML_STATUS_SUCCESS) return st;
+            } break;
+            case GGML_OP_ROPE: {
+                if (!rope_supported(node)) GGML_ABORT("Q4K_B200: %s: ROPE node outside the supports_op contract", node->name);
+                last_quantized = nullptr;
+                const ggml_status st = compute_rope(ctx, node);
+                if (st != GGML_STATUS_SUCCESS) return st;
+            } break;
+            case GGML_OP_GET_ROWS: {
+                if (!get_rows_supported(node)) GGML_ABORT("Q4K_B200: %s: GET_ROWS node outside the supports_op contract", node->name);
+                last_quantized = nullptr;
+                const ggml_status st = compute_get_rows(ctx, node);
+                if (st != GGML_STATUS_SUCCESS) return st;
             } break;
             case GGML_OP_NONE:
             case GGML_OP_RESHAPE:
@@ -593,6 +796,11 @@ ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char *) {
     };
 }
 
+bool cheap_ops_enabled() {
+    static const bool on = [] { const char * e = getenv("Q4K_B200_CHEAP_OPS"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
     switch (op->op) {
         // test-backend-ops asks about every tensor of the context, leaves and views included
@@ -605,6 +813,18 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
             return true;
         case GGML_OP_MUL_MAT:
             return mul_mat_supported(op);
+        // the cheap ops of a decoder layer (Q4K_B200_CHEAP_OPS=0 leaves them to the CPU backend)
+        case GGML_OP_RMS_NORM:
+            return cheap_ops_enabled() && rms_norm_supported(op);
+        case GGML_OP_ADD:
+        case GGML_OP_MUL:
+            return cheap_ops_enabled() && binary_supported(op);
+        case GGML_OP_GLU:
+            return cheap_ops_enabled() && glu_supported(op);
+        case GGML_OP_GET_ROWS:
+            return cheap_ops_enabled() && get_rows_supported(op);
+        case GGML_OP_ROPE:
+            return cheap_ops_enabled() && rope_supported(op);
         default:
             return false;
     }
@@ -684,7 +904,8 @@ ggml_backend_reg_t q4k_b200_reg() {
             c.buft = ggml_backend_buffer_type{buft_iface, &devs.back(), &c};
             c.host_buft = ggml_backend_buffer_type{host_buft_iface, &devs.back(), &c};
         }
-        GGML_LOG_INFO("Q4K_B200: %zu sm_100 device(s); claims MUL_MAT(Q4_K | Q6_K, F32) only\n", devs.size());
+        GGML_LOG_INFO("Q4K_B200: %zu sm_100 device(s); claims MUL_MAT(Q4_K | Q6_K, F32)%s\n", devs.size(),
+                      cheap_ops_enabled() ? " and the F32 ops around it (RMS_NORM, ADD, MUL, GLU/SWIGLU, GET_ROWS, ROPE)" : " only");
     });
     return &reg;
 }

@@ -96,6 +96,8 @@ size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
     if (N > Q4K_GEMV_MAX_N) {                                            // prefill path: int8 + mins tiles of whole 128-column tiles, scales
         const size_t gemm = q4k::gemm_workspace_bytes(K, N);
         if (gemm > need) need = gemm;
+        const size_t wide = q4k::wide_workspace_bytes(K, N);             // batched decode kernel: staged Q8_K, padded to 8 columns
+        if (wide > need) need = wide;
     }
     return need;
 }
@@ -155,6 +157,19 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
             const cudaError_t e = launch_gemv_q4k_q8k_tma(w_dev, M, K, w_row_stride_bytes, nullptr, x_dev, (int)N, x_row_stride_bytes,
                                                           dst_dev, dst_col_stride_bytes, gemv_exact_for((int)N), 0,
                                                           knobs().pdl != 0, (cudaStream_t)stream);
+            if (e == cudaSuccess) return Q4K_OK;
+            if (e != cudaErrorNotSupported) return cuda_fail(e);
+        }
+        // batches between the decode kernel and the GEMM (8 < N <= midn_max): the batched tensor-pipe decode kernel — the
+        // weights stream once per 32 columns, the activations stream through shared memory next to them (gemv_q4k_wide.cu)
+        if (N > Q4K_GEMV_MAX_N && N <= knobs().midn_max) {
+            if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
+            const int64_t nb = K / Q4K_QK_K;
+            if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (dst_col_stride_bytes < M * 4 || (dst_col_stride_bytes & 3) || !aligned16(workspace_dev)) return Q4K_ERR_BAD_SHAPE;
+            const cudaError_t e = launch_gemv_q4k_wide(w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev,
+                                                       dst_col_stride_bytes, workspace_dev, knobs().pdl != 0, (cudaStream_t)stream);
             if (e == cudaSuccess) return Q4K_OK;
             if (e != cudaErrorNotSupported) return cuda_fail(e);
         }
@@ -256,7 +271,7 @@ int q4k_mul_mat_peers_ll(const void *w_dev, int64_t M_local, int64_t K, int64_t 
 int q4k_mul_mat_reuse(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N,
                       float *dst_dev, int64_t dst_col_stride_bytes, void *workspace_dev, size_t workspace_bytes, void *stream) {
     if (M < 0 || N < 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
-    if (N <= Q4K_GEMV_GEMM_MIN_N || !knobs().gemm_enabled) return Q4K_ERR_UNSUPPORTED;     // decode shapes quantize inside their launch
+    if (N <= Q4K_GEMV_GEMM_MIN_N || N <= knobs().midn_max || !knobs().gemm_enabled) return Q4K_ERR_UNSUPPORTED;     // decode shapes quantize inside their launch
     if (M == 0) return Q4K_OK;
     if (!w_dev || !dst_dev || !workspace_dev) return Q4K_ERR_BAD_POINTER;
     if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
@@ -338,7 +353,7 @@ int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_
                      int32_t *p_dev, int32_t *sumi_dev, int32_t *summ_dev,
                      void *workspace_dev, size_t workspace_bytes, void *stream) {
     if (M <= 0 || N <= 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
-    if (kernel < Q4K_DUMP_DISPATCH || kernel > Q4K_DUMP_GEMM) return Q4K_ERR_UNSUPPORTED;
+    if (kernel < Q4K_DUMP_DISPATCH || kernel > Q4K_DUMP_WIDE) return Q4K_ERR_UNSUPPORTED;
     if (!w_dev || !x_dev || !dst_dev || !sumi_dev || !summ_dev) return Q4K_ERR_BAD_POINTER;
     const int64_t nb = K / Q4K_QK_K;
     if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
@@ -347,6 +362,15 @@ int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_
     if (!workspace_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
     cudaStream_t st = (cudaStream_t)stream;
     // which product kernel: the one q4k_mul_mat would launch for this shape, unless the caller names one
+    const bool wide = kernel == Q4K_DUMP_WIDE || (kernel == Q4K_DUMP_DISPATCH && N > Q4K_GEMV_MAX_N && N <= knobs().midn_max);
+    if (wide) {
+        if (!p_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
+        const IntDump d{p_dev, sumi_dev, summ_dev};
+        const cudaError_t e = launch_gemv_q4k_wide(w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev, M * 4, workspace_dev,
+                                                   knobs().pdl != 0, st, &d);
+        if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;
+        return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+    }
     const bool gemm = kernel == Q4K_DUMP_GEMM || (kernel == Q4K_DUMP_DISPATCH && N > Q4K_GEMV_GEMM_MIN_N && knobs().gemm_enabled);
     if (gemm) {
         if (N <= Q4K_GEMV_MAX_N) return Q4K_ERR_UNSUPPORTED;

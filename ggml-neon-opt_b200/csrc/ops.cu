@@ -4,6 +4,7 @@
 //   ADD / MUL  apply_binary_op<op_add / op_mul>    L/ggml/src/ggml-cpu/binary-ops.cpp:52-120 (src1 broadcast over rows / dims)
 //   GLU        ggml_compute_forward_swiglu_f32     L/ggml/src/ggml-cpu/ops.cpp:2934-2990 (split form: silu(gate) * up)
 //   GET_ROWS   ggml_compute_forward_get_rows_f32   L/ggml/src/ggml-cpu/ops.cpp:4626-4660
+//   ROPE       ggml_compute_forward_rope_f32       L/ggml/src/ggml-cpu/ops.cpp:5436-5475, 5534-5700 (NORMAL and NEOX modes)
 // All HBM / latency-bound elementwise or row kernels (a decode token moves a few KB through each); they exist for the launch
 // chain, not for throughput: every kernel takes part in programmatic dependent launch like the decode kernels, so a captured
 // layer is one dependency chain without host gaps.
@@ -127,6 +128,51 @@ get_rows_kernel(const float *__restrict__ src, const int32_t *__restrict__ ids, 
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += (int64_t)gridDim.x * blockDim.x) dr[i] = sr[i];
 }
 
+// ROPE, modes NORMAL (pairs (2i, 2i+1)) and NEOX (pairs (i, i + n_dims/2)).  One thread per pair.  theta follows the reference's
+// cache loop exactly: theta = (float)pos, multiplied by theta_scale once per preceding pair (sequential float products), so the
+// angle has the reference's bits; cosf / sinf are CUDA's (<= 2 ulp), the rotation may contract to FMAs as gcc's does.
+struct RopeArgs {
+    const float *x;
+    const int32_t *pos;
+    const float *ff;
+    float *d;
+    int64_t ne0, ne1, ne2, ne3, xb1, xb2, xb3, db1, db2, db3;
+    int n_dims, neox;
+    float theta_scale, freq_scale, ext_factor, attn_factor, corr_lo, corr_hi;
+};
+
+__global__ void __launch_bounds__(128) rope_kernel(const __grid_constant__ RopeArgs p) {
+    pdl_enter();
+    const int64_t pair = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;          // pair index inside the row (ne0 / 2 pairs)
+    if (2 * pair >= p.ne0) return;
+    const int64_t i1 = blockIdx.y, i23 = blockIdx.z, i2 = i23 % p.ne2, i3 = i23 / p.ne2;
+    const float *xr = reinterpret_cast<const float *>(reinterpret_cast<const char *>(p.x) + i1 * p.xb1 + i2 * p.xb2 + i3 * p.xb3);
+    float *dr = reinterpret_cast<float *>(reinterpret_cast<char *>(p.d) + i1 * p.db1 + i2 * p.db2 + i3 * p.db3);
+    const int64_t i0 = 2 * pair;
+    if (i0 >= p.n_dims) {                          // channels beyond the rotated ones are copied
+        dr[i0] = xr[i0];
+        dr[i0 + 1] = xr[i0 + 1];
+        return;
+    }
+    float theta = (float)(int64_t)p.pos[i2];
+    for (int64_t k = 0; k < pair; ++k) theta = __fmul_rn(theta, p.theta_scale);
+    const float ff = p.ff ? p.ff[pair] : 1.0f;
+    const float theta_extrap = __fdiv_rn(theta, ff);
+    const float theta_interp = __fmul_rn(p.freq_scale, theta_extrap);
+    float th = theta_interp, mscale = p.attn_factor;
+    if (p.ext_factor != 0.0f) {
+        const float y = ((float)(i0 / 2) - p.corr_lo) / fmaxf(0.001f, p.corr_hi - p.corr_lo);
+        const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
+        th = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
+        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+    }
+    const float c = cosf(th) * mscale, sn = sinf(th) * mscale;
+    const int64_t a = p.neox ? pair : i0, b = p.neox ? pair + p.n_dims / 2 : i0 + 1;
+    const float x0 = xr[a], x1 = xr[b];
+    dr[a] = x0 * c - x1 * sn;
+    dr[b] = x0 * sn + x1 * c;
+}
+
 template <typename... KArgs, typename... Args>
 int launch(void (*kern)(KArgs...), dim3 grid, dim3 block, void *stream, Args... args) {
     cudaLaunchConfig_t cfg = {};
@@ -203,6 +249,21 @@ int q4k_op_get_rows_f32(const float *src_dev, int64_t src_row_stride_bytes, int6
     const unsigned gx = (unsigned)((nc + 255) / 256 > 64 ? 64 : (nc + 255) / 256);
     return launch(get_rows_kernel, dim3(gx, (unsigned)n_ids), dim3(256), stream, src_dev, ids_dev, dst_dev, nc, nrows_src, src_row_stride_bytes,
                   dst_row_stride_bytes);
+}
+
+int q4k_op_rope(const float *x_dev, const int64_t *x_nb, const int32_t *pos_dev, const float *freq_factors_dev, float *dst_dev,
+                const int64_t *dst_nb, const int64_t *ne, int n_dims, int neox, float theta_scale, float freq_scale, float ext_factor,
+                float attn_factor, float corr_lo, float corr_hi, void *stream) {
+    if (!ne || ne[0] < 0 || ne[1] < 0 || ne[2] < 0 || ne[3] < 0 || (ne[0] & 1) || n_dims < 0 || (n_dims & 1) || n_dims > ne[0]) return Q4K_ERR_BAD_SHAPE;
+    if (ne[0] == 0 || ne[1] == 0 || ne[2] == 0 || ne[3] == 0) return Q4K_OK;
+    if (!x_dev || !pos_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
+    if (!strides_ok(x_nb) || !strides_ok(dst_nb)) return Q4K_ERR_BAD_SHAPE;
+    if (ne[1] > 65535 || ne[2] * ne[3] > 65535) return Q4K_ERR_UNSUPPORTED;
+    RopeArgs p{x_dev, pos_dev, freq_factors_dev, dst_dev, ne[0], ne[1], ne[2], ne[3], x_nb[0], x_nb[1], x_nb[2], dst_nb[0], dst_nb[1], dst_nb[2],
+               n_dims, neox, theta_scale, freq_scale, ext_factor, attn_factor, corr_lo, corr_hi};
+    const int64_t pairs = ne[0] / 2;
+    const int threads = pairs >= 128 ? 128 : (int)((pairs + 31) / 32 * 32);
+    return launch(rope_kernel, dim3((unsigned)((pairs + threads - 1) / threads), (unsigned)ne[1], (unsigned)(ne[2] * ne[3])), dim3(threads), stream, p);
 }
 
 }  // extern "C"

@@ -82,6 +82,14 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
                                 float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream,
                                 const IntDump *dump = nullptr);
 
+// batched decode on the tensor pipe (gemv_q4k_wide.cu): F32 activations, 8 < N; quantizes into `workspace`
+// (wide_workspace_bytes) in its own staged layout and streams weights once per group of up to WIDE_MAX_COLS columns
+constexpr int WIDE_MAX_COLS = 32;
+size_t wide_workspace_bytes(int64_t K, int64_t N);
+cudaError_t launch_gemv_q4k_wide(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x, int64_t N,
+                                 int64_t x_row_stride_bytes, float *dst, int64_t dst_col_stride_bytes, void *workspace, bool pdl,
+                                 cudaStream_t stream, const IntDump *dump = nullptr);
+
 // Q6_K decode GEMV (gemv_q6k.cu), 1 <= N <= 8; dump != nullptr also writes the per-superblock integer sums
 cudaError_t launch_gemv_q6k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                             const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,

@@ -92,6 +92,12 @@ def load():
         L.q6k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
         L.q6k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q6k_debug_partials.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, vp, vp]
+        L.q4k_op_rms_norm.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_float, vp]
+        L.q4k_op_binary.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.q4k_op_swiglu.argtypes = [vp, i64, vp, i64, vp, i64, i64, i64, vp]
+        L.q4k_op_get_rows_f32.argtypes = [vp, i64, i64, vp, i64, vp, i64, i64, vp]
+        f32 = C.c_float
+        L.q4k_op_rope.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, f32, f32, f32, f32, f32, vp]
         L.q4k_debug_set.argtypes = [C.c_char_p, i64]
         L.q4k_debug_reset.restype = None
         L.q4k_debug_set_fuse_limit.argtypes = [i64]
@@ -273,6 +279,93 @@ def debug_partials_q6k(w: torch.Tensor, xq: torch.Tensor):
         _check("q6k_debug_partials", load().q6k_debug_partials(w.data_ptr(), M, nb * QK_K, w.stride(0), xq.data_ptr(), N,
                                                                xq.stride(0), si.data_ptr(), y.data_ptr(), _stream()))
     return si, y
+
+
+# ---- the cheap F32 ops around the mul_mats (include/q4k_b200.h: q4k_op_*).  Tensors are torch CUDA float32 with ggml's dim
+# order REVERSED (torch shape [ne3, ne2, ne1, ne0], last dim dense), up to 4-D; strides may be arbitrary in the outer dims.
+def _ggml_ne_nb(t: torch.Tensor):
+    if not (t.is_cuda and t.dtype == torch.float32 and 1 <= t.dim() <= 4 and t.stride(-1) == 1):
+        raise TypeError("expected a CUDA float32 tensor of 1..4 dims with a dense last dim")
+    shape = [1] * (4 - t.dim()) + list(t.shape)
+    stride = [0] * (4 - t.dim()) + list(t.stride())
+    ne = (C.c_int64 * 4)(shape[3], shape[2], shape[1], shape[0])
+    nb = (C.c_int64 * 3)(stride[2] * 4, stride[1] * 4, stride[0] * 4)
+    return ne, nb
+
+
+def op_rms_norm(x: torch.Tensor, eps: float, weight: torch.Tensor | None = None, residual: torch.Tensor | None = None,
+                want_sum: bool = False):
+    """GGML_OP_RMS_NORM per row of x; optional fused residual add in front (x + residual; want_sum also returns it) and
+    multiply by a weight row behind.  -> y, or (y, x + residual)."""
+    ne, x_nb = _ggml_ne_nb(x)
+    y = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    _, y_nb = _ggml_ne_nb(y)
+    r_nb = s_nb = None
+    ssum = None
+    if residual is not None:
+        if residual.shape != x.shape:
+            raise ValueError("residual must have the shape of x")
+        _, r_nb = _ggml_ne_nb(residual)
+        if want_sum:
+            ssum = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+            _, s_nb = _ggml_ne_nb(ssum)
+    if weight is not None and not (weight.is_cuda and weight.dtype == torch.float32 and weight.is_contiguous() and weight.numel() == x.shape[-1]):
+        raise TypeError("weight: expected a contiguous CUDA float32 row of x.shape[-1] elements")
+    with torch.cuda.device(x.device):
+        _check("q4k_op_rms_norm", load().q4k_op_rms_norm(x.data_ptr(), x_nb, residual.data_ptr() if residual is not None else None, r_nb,
+                                                         weight.data_ptr() if weight is not None else None, y.data_ptr(), y_nb,
+                                                         ssum.data_ptr() if ssum is not None else None, s_nb, ne, eps, _stream()))
+    return (y, ssum) if want_sum else y
+
+
+def op_binary(op: str, a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """GGML_OP_ADD / GGML_OP_MUL with b repeated over a (ggml_can_repeat)."""
+    a_ne, a_nb = _ggml_ne_nb(a)
+    b_ne, b_nb = _ggml_ne_nb(b)
+    d = torch.empty(a.shape, dtype=torch.float32, device=a.device)
+    _, d_nb = _ggml_ne_nb(d)
+    with torch.cuda.device(a.device):
+        _check("q4k_op_binary", load().q4k_op_binary({"add": 0, "mul": 1}[op], a.data_ptr(), a_ne, a_nb, b.data_ptr(), b_ne, b_nb,
+                                                     d.data_ptr(), d_nb, _stream()))
+    return d
+
+
+def op_swiglu(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    """GGML_OP_GLU / SWIGLU, split form: silu(gate) * up, 2-D [rows, nc] with a dense last dim."""
+    if gate.shape != up.shape or gate.dim() != 2 or gate.stride(1) != 1 or up.stride(1) != 1:
+        raise ValueError("gate / up: expected two 2-D tensors of one shape with dense rows")
+    d = torch.empty(gate.shape, dtype=torch.float32, device=gate.device)
+    with torch.cuda.device(gate.device):
+        _check("q4k_op_swiglu", load().q4k_op_swiglu(gate.data_ptr(), gate.stride(0) * 4, up.data_ptr(), up.stride(0) * 4, d.data_ptr(),
+                                                     d.stride(0) * 4, gate.shape[1], gate.shape[0], _stream()))
+    return d
+
+
+def op_get_rows(src: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
+    """GGML_OP_GET_ROWS: F32 rows of src [rows, nc] picked by int32 ids."""
+    if src.dim() != 2 or src.stride(1) != 1 or ids.dtype != torch.int32 or not ids.is_contiguous():
+        raise ValueError("src: 2-D float32 with dense rows; ids: contiguous int32")
+    d = torch.empty((ids.numel(), src.shape[1]), dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        _check("q4k_op_get_rows_f32", load().q4k_op_get_rows_f32(src.data_ptr(), src.stride(0) * 4, src.shape[0], ids.data_ptr(), ids.numel(),
+                                                                 d.data_ptr(), d.stride(0) * 4, src.shape[1], _stream()))
+    return d
+
+
+def op_rope(x: torch.Tensor, pos: torch.Tensor, n_dims: int, theta_scale: float, neox: bool = False, freq_scale: float = 1.0,
+            ext_factor: float = 0.0, attn_factor: float = 1.0, corr_dims=(0.0, 0.0), freq_factors: torch.Tensor | None = None) -> torch.Tensor:
+    """GGML_OP_ROPE (NORMAL / NEOX): x float32 [tokens, heads, head_dim] (or 4-D with a leading batch), pos int32 [tokens];
+    theta_scale = powf(freq_base, -2.0f / n_dims) and the YaRN correction dims come from the caller (include/q4k_b200.h)."""
+    ne, x_nb = _ggml_ne_nb(x)
+    if pos.dtype != torch.int32 or not pos.is_contiguous() or pos.numel() != ne[2]:
+        raise ValueError("pos: contiguous int32, one per token")
+    d = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    _, d_nb = _ggml_ne_nb(d)
+    with torch.cuda.device(x.device):
+        _check("q4k_op_rope", load().q4k_op_rope(x.data_ptr(), x_nb, pos.data_ptr(), freq_factors.data_ptr() if freq_factors is not None else None,
+                                                 d.data_ptr(), d_nb, ne, n_dims, int(neox), theta_scale, freq_scale, ext_factor, attn_factor,
+                                                 corr_dims[0], corr_dims[1], _stream()))
+    return d
 
 
 class HostPlan:

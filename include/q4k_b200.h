@@ -224,6 +224,7 @@ enum {
     Q4K_DUMP_BULK        = 2,    /* gemv_q4k_tma_kernel, default float order */
     Q4K_DUMP_BULK_EXACT  = 3,    /* gemv_q4k_tma_kernel in the reference's AVX2 order */
     Q4K_DUMP_BIG         = 4,    /* gemv_q4k_tma_kernel in the tensor-pipe association: the large-matrix launch, N == 1 */
+    Q4K_DUMP_WIDE        = 6,    /* gemv_q4k_wide_kernel: the batched decode kernel (8 < N <= 64 by default; any N here, 32 columns per launch) */
     Q4K_DUMP_GEMM        = 5,    /* gemm_q4k_tc_kernel: sumi = 8 hi + lo and summ as the epilogue reads them from TMEM; p_dev unused
                                   * (the tensor core never forms p[j]: the scales are folded into the A operand), N > 8 */
 };
@@ -303,6 +304,41 @@ int q6k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride
 int q6k_debug_partials(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                        const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
                        int32_t *sumi_dev, float *dst_dev, void *stream);
+
+/* ---- adjacent cheap ops of a decoder layer ----------------------------------------------
+ * The F32 ops between the weight mul_mats of the reference's llama graph (build_norm / build_ffn / the residual adds,
+ * L/src/llama-graph.cpp), so that the plugin keeps a norm -> mul_mat -> glu -> mul_mat -> add chain on the device and the
+ * scheduler (L/ggml/src/ggml-backend.cpp:776-827) stops cutting the graph around every mul_mat.  Tensors are ggml's: dim 0 is
+ * dense (4-byte elements), *_nb = byte strides of dims 1, 2, 3 (multiples of 4), ne = the four extents.  csrc/ops.cu. */
+enum { Q4K_OP_ADD = 0, Q4K_OP_MUL = 1 };
+/* GGML_OP_RMS_NORM, ggml_compute_forward_rms_norm_f32 (L/ggml/src/ggml-cpu/ops.cpp:3517-3570): y = x / sqrt(mean(x^2) + eps)
+ * per row.  Optional fusions of the nodes around it in the llama graph (each NULL = off; results equal the separate ops bit for
+ * bit, they are the same IEEE operations in the same order):
+ *   res_dev: x := x + res first (the residual GGML_OP_ADD in front of the norm); sum_dev (optional) receives x + res;
+ *   w_dev:   y := y * w, w = ne[0] floats broadcast over the rows (the GGML_OP_MUL by the norm weight behind the norm). */
+int q4k_op_rms_norm(const float *x_dev, const int64_t *x_nb, const float *res_dev, const int64_t *res_nb, const float *w_dev,
+                    float *y_dev, const int64_t *y_nb, float *sum_dev, const int64_t *sum_nb, const int64_t *ne, float eps, void *stream);
+/* GGML_OP_ADD / GGML_OP_MUL, all F32: apply_binary_op (L/ggml/src/ggml-cpu/binary-ops.cpp:52-120); b is repeated over a
+ * (ggml_can_repeat(b, a): every extent of a is a multiple of b's), dst has a's shape.  Bit-identical to the reference. */
+int q4k_op_binary(int op, const float *a_dev, const int64_t *a_ne, const int64_t *a_nb, const float *b_dev, const int64_t *b_ne,
+                  const int64_t *b_nb, float *dst_dev, const int64_t *dst_nb, void *stream);
+/* GGML_OP_GLU / GGML_GLU_OP_SWIGLU, split form (ggml_swiglu_split: src0 = gate, src1 = up),
+ * ggml_compute_forward_swiglu_f32 (L/ggml/src/ggml-cpu/ops.cpp:2934-2990): dst = silu(gate) * up, silu(x) = x / (1 + expf(-x))
+ * (L/ggml/src/ggml-cpu/vec.h:957).  ~1e-6 relative against the reference's AVX2 polynomial expf. */
+int q4k_op_swiglu(const float *gate_dev, int64_t gate_row_stride_bytes, const float *up_dev, int64_t up_row_stride_bytes,
+                  float *dst_dev, int64_t dst_row_stride_bytes, int64_t nc, int64_t nrows, void *stream);
+/* GGML_OP_GET_ROWS, F32 rows by I32 ids: ggml_compute_forward_get_rows_f32 (L/ggml/src/ggml-cpu/ops.cpp:4626-4660) */
+int q4k_op_get_rows_f32(const float *src_dev, int64_t src_row_stride_bytes, int64_t nrows_src, const int32_t *ids_dev, int64_t n_ids,
+                        float *dst_dev, int64_t dst_row_stride_bytes, int64_t nc, void *stream);
+/* GGML_OP_ROPE, F32, modes NORMAL (neox = 0: pairs (2i, 2i+1)) and NEOX (pairs (i, i + n_dims/2)); no mrope / vision:
+ * ggml_compute_forward_rope_f32 + ggml_rope_cache_init + rope_yarn (L/ggml/src/ggml-cpu/ops.cpp:5436-5475, 5534-5700).
+ * x / dst: ne = [head_dim, heads, tokens, batch]; pos_dev: int32 per token; freq_factors_dev: optional n_dims/2 floats.
+ * The caller hands over what the reference derives on the host: theta_scale = powf(freq_base, -2.0f / n_dims) and the YaRN
+ * correction dims (ggml_rope_yarn_corr_dims, L/ggml/src/ggml.c:4122-4135).  The angle is built with the reference's own
+ * sequence of float products; agreement with the reference is a few ulp of the rotated values (cosf / sinf, FMA contraction). */
+int q4k_op_rope(const float *x_dev, const int64_t *x_nb, const int32_t *pos_dev, const float *freq_factors_dev, float *dst_dev,
+                const int64_t *dst_nb, const int64_t *ne, int n_dims, int neox, float theta_scale, float freq_scale, float ext_factor,
+                float attn_factor, float corr_lo, float corr_hi, void *stream);
 
 #ifdef __cplusplus
 }

@@ -291,3 +291,58 @@ def random_q6_K(rng, M: int, K: int) -> np.ndarray:
     d = (rng.uniform(0.0005, 0.01, (M, nb)) * rng.choice([-1.0, 1.0], (M, nb))).astype(np.float16)
     w[:, :, 208:210] = d.view(np.uint8).reshape(M, nb, 2)
     return w.reshape(M, nb * Q6K_BLOCK)
+
+
+# ---- the cheap F32 ops around the mul_mats -------------------------------------------------------
+def rms_norm(x: np.ndarray, eps: float) -> np.ndarray:
+    """ggml_compute_forward_rms_norm_f32 (L/ggml/src/ggml-cpu/ops.cpp:3517-3570): squares rounded to float, summed in double
+    in element order, mean and 1/sqrtf(mean + eps) in float, y = x * scale."""
+    x = np.ascontiguousarray(x, np.float32)
+    sq = (x * x).astype(np.float32).astype(np.float64)
+    tot = np.zeros(x.shape[:-1], np.float64)
+    for i in range(x.shape[-1]):                      # sequential, as the reference's loop
+        tot += sq[..., i]
+    mean = (tot / x.shape[-1]).astype(np.float32)
+    scale = (np.float32(1.0) / np.sqrt((mean + np.float32(eps)).astype(np.float32))).astype(np.float32)
+    return (x * scale[..., None]).astype(np.float32)
+
+
+def swiglu(gate: np.ndarray, up: np.ndarray) -> np.ndarray:
+    """ggml_compute_forward_swiglu_f32, split form (L/ggml/src/ggml-cpu/ops.cpp:2934-2990): silu(gate) * up with
+    silu(x) = x / (1 + expf(-x)) (vec.h:957).  expf here is numpy's float32 exp; the reference's AVX2 path uses a polynomial
+    (ggml_v_expf): agreement ~1e-6 relative, not bit-exact."""
+    g = np.ascontiguousarray(gate, np.float32)
+    with np.errstate(over="ignore"):                  # exp(90) = inf in float32: x / inf = -0, as expf gives the reference
+        silu = (g / (np.float32(1.0) + np.exp(-g).astype(np.float32))).astype(np.float32)
+    return (silu * np.ascontiguousarray(up, np.float32)).astype(np.float32)
+
+
+def rope_theta_scale(freq_base: float, n_dims: int) -> np.float32:
+    """powf(freq_base, -2.0f / n_dims) with the C library's powf, as ggml_compute_forward_rope_f32 derives it (ops.cpp:5584)."""
+    import ctypes
+    libm = ctypes.CDLL("libm.so.6")
+    libm.powf.restype = ctypes.c_float
+    libm.powf.argtypes = [ctypes.c_float, ctypes.c_float]
+    return np.float32(libm.powf(np.float32(freq_base), np.float32(-2.0) / np.float32(n_dims)))
+
+
+def rope(x: np.ndarray, pos: np.ndarray, n_dims: int, neox: bool = False, freq_base: float = 10000.0, freq_scale: float = 1.0,
+         attn_factor: float = 1.0) -> np.ndarray:
+    """ggml_compute_forward_rope_f32 with ext_factor = 0 (L/ggml/src/ggml-cpu/ops.cpp:5436-5475, 5534-5700).
+    x: float32 [tokens, heads, ne0].  theta is the reference's running float product; cos / sin in float64 rounded to float32
+    (libm's cosf / sinf are within an ulp of that), the rotation in float32 without contraction."""
+    x = np.ascontiguousarray(x, np.float32)
+    y = x.copy()
+    ts = rope_theta_scale(freq_base, n_dims)
+    for t in range(x.shape[0]):
+        theta = np.float32(pos[t])
+        for i0 in range(0, n_dims, 2):
+            th = np.float32(np.float32(freq_scale) * theta)
+            c = np.float32(np.float32(np.cos(np.float64(th))) * np.float32(attn_factor))
+            s = np.float32(np.float32(np.sin(np.float64(th))) * np.float32(attn_factor))
+            a, b = (i0 // 2, i0 // 2 + n_dims // 2) if neox else (i0, i0 + 1)
+            x0, x1 = x[t, :, a], x[t, :, b]
+            y[t, :, a] = (x0 * c).astype(np.float32) - (x1 * s).astype(np.float32)
+            y[t, :, b] = (x0 * s).astype(np.float32) + (x1 * c).astype(np.float32)
+            theta = np.float32(theta * ts)
+    return y

@@ -72,6 +72,11 @@ def libs():
         shim.ref_mul_mat_set_ex.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i32), i64, i32, i32, i32, i32,
                                             C.POINTER(C.c_double), C.POINTER(C.c_double)]
         shim.ref_mul_mat_set_ex.restype = i32
+        shim.ref_cheap_ops.argtypes = [vp, vp, vp, vp, vp, i64, i64, C.c_float, i32, vp, vp, vp]
+        shim.ref_cheap_ops.restype = i32
+        f32 = C.c_float
+        shim.ref_rope.argtypes = [vp, vp, i64, i64, i64, i32, i32, i32, f32, f32, f32, f32, f32, f32, i32, vp]
+        shim.ref_rope.restype = i32
         # ggml-cpu's fp16->fp32 is a lookup table filled by ggml_cpu_init() (ggml-cpu.c:3526-3549);
         # the reference always reaches vec_dot through backend init, direct callers must do it themselves
         cpu.ggml_cpu_init()
@@ -318,3 +323,32 @@ def vec_dot_q6(wrow: np.ndarray, yrow: np.ndarray, generic: bool = False) -> np.
 
 def has_avx2() -> bool:
     return bool(libs()[3].ref_cpu_has_avx2())
+
+
+def cheap_ops(x: np.ndarray, res: np.ndarray, w: np.ndarray, g: np.ndarray, u: np.ndarray, eps: float, n_threads: int = 2):
+    """The reference's own ADD -> RMS_NORM -> MUL and SWIGLU(split) on ggml_backend_cpu (oracle/ref_shim.c: ref_cheap_ops).
+    x, res, g, u: float32 [rows, ne0]; w: [ne0].  -> (x + res, rms_norm(x + res) * w, silu(g) * u)."""
+    *_, shim = libs()
+    x, res, g, u = (np.ascontiguousarray(a, np.float32) for a in (x, res, g, u))
+    w = np.ascontiguousarray(w, np.float32)
+    ys, yn, yg = (np.empty_like(x) for _ in range(3))
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    rc = shim.ref_cheap_ops(p(x), p(res), p(w), p(g), p(u), x.shape[1], x.shape[0], eps, n_threads, p(ys), p(yn), p(yg))
+    if rc != 0:
+        raise RuntimeError(f"ref_cheap_ops failed: {rc}")
+    return ys, yn, yg
+
+
+def rope(x: np.ndarray, pos: np.ndarray, n_dims: int, mode: int = 0, freq_base: float = 10000.0, freq_scale: float = 1.0,
+         ext_factor: float = 0.0, attn_factor: float = 1.0, n_ctx_orig: int = 2048, beta_fast: float = 32.0, beta_slow: float = 1.0,
+         n_threads: int = 2) -> np.ndarray:
+    """The reference's ggml_rope_ext on ggml_backend_cpu (oracle/ref_shim.c: ref_rope).  x: float32 [tokens, heads, ne0]."""
+    *_, shim = libs()
+    x = np.ascontiguousarray(x, np.float32)
+    pos = np.ascontiguousarray(pos, np.int32)
+    y = np.empty_like(x)
+    rc = shim.ref_rope(x.ctypes.data_as(C.c_void_p), pos.ctypes.data_as(C.c_void_p), x.shape[2], x.shape[1], x.shape[0], n_dims, mode, n_ctx_orig,
+                       freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow, n_threads, y.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise RuntimeError(f"ref_rope failed: {rc}")
+    return y

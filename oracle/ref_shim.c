@@ -419,3 +419,70 @@ out:
     ggml_backend_free(be);
     return rc;
 }
+
+/* The cheap F32 ops between the mul_mats of a decoder layer on ggml_backend_cpu, as the reference's llama graph strings them
+ * together (build_norm / build_ffn): sum = add(x, res); y = mul(rms_norm(sum, eps), w); glu = swiglu_split(g, u).
+ * x, res, g, u: [nrows][ne0] floats, w: [ne0].  Pins oracle/port.py's restatements (and the GPU kernels behind them). */
+int ref_cheap_ops(const float *x, const float *res, const float *w, const float *g, const float *u, int64_t ne0, int64_t nrows, float eps,
+                  int n_threads, float *y_sum, float *y_norm, float *y_glu) {
+    ggml_backend_t cpu = ggml_backend_cpu_init();
+    if (!cpu) return -1;
+    ggml_backend_cpu_set_n_threads(cpu, n_threads);
+    struct ggml_init_params ip = { ggml_tensor_overhead() * 16 + ggml_graph_overhead(), NULL, true };
+    struct ggml_context *ctx = ggml_init(ip);
+    if (!ctx) { ggml_backend_free(cpu); return -1; }
+    struct ggml_tensor *tx = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, ne0, nrows), *tr = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, ne0, nrows);
+    struct ggml_tensor *tw = ggml_new_tensor_1d(ctx, GGML_TYPE_F32, ne0);
+    struct ggml_tensor *tg = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, ne0, nrows), *tu = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, ne0, nrows);
+    struct ggml_tensor *sum = ggml_add(ctx, tx, tr);
+    struct ggml_tensor *nrm = ggml_mul(ctx, ggml_rms_norm(ctx, sum, eps), tw);
+    struct ggml_tensor *glu = ggml_swiglu_split(ctx, tg, tu);
+    struct ggml_cgraph *gf = ggml_new_graph(ctx);
+    ggml_build_forward_expand(gf, nrm);
+    ggml_build_forward_expand(gf, glu);
+    ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors(ctx, cpu);
+    int rc = -2;
+    if (buf) {
+        const size_t nbytes = (size_t)ne0 * (size_t)nrows * sizeof(float);
+        ggml_backend_tensor_set(tx, x, 0, nbytes); ggml_backend_tensor_set(tr, res, 0, nbytes);
+        ggml_backend_tensor_set(tw, w, 0, (size_t)ne0 * sizeof(float));
+        ggml_backend_tensor_set(tg, g, 0, nbytes); ggml_backend_tensor_set(tu, u, 0, nbytes);
+        rc = ggml_backend_graph_compute(cpu, gf) == GGML_STATUS_SUCCESS ? 0 : -3;
+        if (rc == 0) {
+            ggml_backend_tensor_get(sum, y_sum, 0, nbytes); ggml_backend_tensor_get(nrm, y_norm, 0, nbytes);
+            ggml_backend_tensor_get(glu, y_glu, 0, nbytes);
+        }
+        ggml_backend_buffer_free(buf);
+    }
+    ggml_free(ctx);
+    ggml_backend_free(cpu);
+    return rc;
+}
+
+/* ggml_rope_ext on ggml_backend_cpu: x [n_tokens][n_heads][ne0] floats, pos [n_tokens]; mode 0 = NORMAL, 2 = NEOX. */
+int ref_rope(const float *x, const int32_t *pos, int64_t ne0, int64_t n_heads, int64_t n_tokens, int n_dims, int mode, int n_ctx_orig,
+             float freq_base, float freq_scale, float ext_factor, float attn_factor, float beta_fast, float beta_slow, int n_threads, float *y) {
+    ggml_backend_t cpu = ggml_backend_cpu_init();
+    if (!cpu) return -1;
+    ggml_backend_cpu_set_n_threads(cpu, n_threads);
+    struct ggml_init_params ip = { ggml_tensor_overhead() * 8 + ggml_graph_overhead(), NULL, true };
+    struct ggml_context *ctx = ggml_init(ip);
+    if (!ctx) { ggml_backend_free(cpu); return -1; }
+    struct ggml_tensor *tx = ggml_new_tensor_3d(ctx, GGML_TYPE_F32, ne0, n_heads, n_tokens);
+    struct ggml_tensor *tp = ggml_new_tensor_1d(ctx, GGML_TYPE_I32, n_tokens);
+    struct ggml_tensor *ty = ggml_rope_ext(ctx, tx, tp, NULL, n_dims, mode, n_ctx_orig, freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow);
+    struct ggml_cgraph *gf = ggml_new_graph(ctx);
+    ggml_build_forward_expand(gf, ty);
+    ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors(ctx, cpu);
+    int rc = -2;
+    if (buf) {
+        ggml_backend_tensor_set(tx, x, 0, ggml_nbytes(tx));
+        ggml_backend_tensor_set(tp, pos, 0, ggml_nbytes(tp));
+        rc = ggml_backend_graph_compute(cpu, gf) == GGML_STATUS_SUCCESS ? 0 : -3;
+        if (rc == 0) ggml_backend_tensor_get(ty, y, 0, ggml_nbytes(ty));
+        ggml_backend_buffer_free(buf);
+    }
+    ggml_free(ctx);
+    ggml_backend_free(cpu);
+    return rc;
+}

@@ -47,3 +47,24 @@ np.savez_compressed(os.path.join(os.path.dirname(__file__), "q6k_ref_vectors.npz
                     w=w, x=x, wq=w6, xq=xq, y_avx2=y6_avx2, y_generic=y6_generic, w_deq=ref.dequantize_q6_K(w6),
                     note=np.array("llama.cpp a3cb0474, ggml-base no -m flags, ggml-cpu -mavx2 -mfma -mf16c -mbmi2, gcc 13.3"))
 print("wrote q6", w6.shape, y6_avx2.shape)
+
+from oracle.port import rope_theta_scale as port_theta_scale  # noqa: E402
+
+# ---- the cheap F32 ops of a decoder layer: ADD -> RMS_NORM -> MUL and SWIGLU on ggml_backend_cpu
+r2 = np.random.default_rng(20261105)
+rows, ne0 = 5, 2048
+ox, ores = r2.standard_normal((rows, ne0)).astype(np.float32), r2.standard_normal((rows, ne0)).astype(np.float32)
+ox[1] *= 1e-4; ores[1] *= 1e-4          # tiny row: eps dominates the mean
+ox[2] *= 300.0                          # large row
+ow = r2.uniform(0.5, 1.5, ne0).astype(np.float32)
+og, ou = (r2.standard_normal((rows, ne0)) * 4).astype(np.float32), r2.standard_normal((rows, ne0)).astype(np.float32)
+og[3, :64] = np.linspace(-90, 90, 64, dtype=np.float32)       # silu tails: expf overflow / underflow side
+ys, yn, yg = ref.cheap_ops(ox, ores, ow, og, ou, 1e-5)
+# ROPE as the llama graph calls it (head_dim 64, freq_base 10000, NORMAL mode) and the NEOX pairing; positions up to the context end
+rx = r2.standard_normal((6, 4, 64)).astype(np.float32)
+rpos = np.array([0, 1, 17, 127, 511, 2047], np.int32)
+np.savez_compressed(os.path.join(os.path.dirname(__file__), "ops_ref_vectors.npz"), x=ox, res=ores, w=ow, g=og, u=ou, eps=np.float32(1e-5),
+                    y_sum=ys, y_norm=yn, y_glu=yg, rope_x=rx, rope_pos=rpos, rope_theta_scale=port_theta_scale(10000.0, 64),
+                    rope_y_normal=ref.rope(rx, rpos, 64, 0), rope_y_neox=ref.rope(rx, rpos, 64, 2),
+                    note=np.array("llama.cpp a3cb0474 ggml_backend_cpu: add, rms_norm, mul, swiglu_split; ggml-cpu -mavx2 -mfma -mf16c -mbmi2"))
+print("wrote ops", ys.shape)
