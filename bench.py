@@ -236,7 +236,7 @@ class MatSet:
             x = torch.randn((N, K), device=device, generator=gen)
             # prefill: mul_mats of one layer that read the same tensor (q/k/v, gate/up) get the same activations, so the second
             # and third reuse the quantized copy (q4k_mul_mat_reuse — what the plugin's graph_compute does)
-            shared = N > 12 and self.items and self.items[-1]["iid"] == iid and self.items[-1]["K"] == K
+            shared = N > 64 and self.items and self.items[-1]["iid"] == iid and self.items[-1]["K"] == K
             if shared:
                 x = self.items[-1]["x"]
             dst = torch.zeros((N, r1 - r0), device=device)

@@ -147,8 +147,9 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
     if (K > 0) {
         if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
         if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
+        const bool wide = N >= knobs().wide_min && N <= knobs().midn_max;
         // decode shapes: one launch — every CTA quantizes the (small) activations into its own shared memory
-        if (N <= Q4K_GEMV_MAX_N && N * K <= knobs().fuse_limit && knobs().gemv_config == 0) {
+        if (!wide && N <= Q4K_GEMV_MAX_N && N * K <= knobs().fuse_limit && knobs().gemv_config == 0) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
             const int64_t nb = K / Q4K_QK_K;
             if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
@@ -162,7 +163,7 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
         }
         // batches between the decode kernel and the GEMM (8 < N <= midn_max): the batched tensor-pipe decode kernel — the
         // weights stream once per 32 columns, the activations stream through shared memory next to them (gemv_q4k_wide.cu)
-        if (N > Q4K_GEMV_MAX_N && N <= knobs().midn_max) {
+        if (wide) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
             const int64_t nb = K / Q4K_QK_K;
             if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
@@ -362,7 +363,7 @@ int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_
     if (!workspace_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
     cudaStream_t st = (cudaStream_t)stream;
     // which product kernel: the one q4k_mul_mat would launch for this shape, unless the caller names one
-    const bool wide = kernel == Q4K_DUMP_WIDE || (kernel == Q4K_DUMP_DISPATCH && N > Q4K_GEMV_MAX_N && N <= knobs().midn_max);
+    const bool wide = kernel == Q4K_DUMP_WIDE || (kernel == Q4K_DUMP_DISPATCH && N >= knobs().wide_min && N <= knobs().midn_max);
     if (wide) {
         if (!p_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
         const IntDump d{p_dev, sumi_dev, summ_dev};

@@ -9,8 +9,12 @@
 //
 // Design.  The activations are quantized once per call (quantize_q8_K_wide_kernel: the arithmetic of quantize_q8k.cu, written
 // in the kernel's own staged layout) and then STREAM through shared memory next to the weights:
-//   * a round is 4 superblocks of K.  Per round the producer warp drops two weight slots (two 16-row tiles x 4 superblocks,
-//     16 bulk copies of 576 B each) and one activation stage (N_pad bulk copies of 4 x 288 B, one per column) on mbarriers.
+//   * a round is 4 superblocks of K.  Per round the producer issues THREE copies on mbarriers: two TMA boxes (one per tile
+//     slot: 16 rows x 608 B of raw block_q4_K through a 2-D tensor map over the weight matrix — the 32 bytes beyond the
+//     round's 576 are the row padding the fragment loads need, rows past M and bytes past the row read as zero) and one bulk
+//     copy of the round's activation stage, which the quantizer has laid out in global memory as the exact shared-memory
+//     image.  (Measured: an SM retires one bulk copy per ~80 cycles whatever its size — 48 copies of 576-1152 B per round held
+//     the first version of this kernel to 2.1 TB/s of weights alone.)
 //   * eight consumer warps = 4 superblocks x 2 tiles: warp w takes superblock w % 4 of tile slot w / 4.  A warp-step is
 //     mma.sync.m16n8k32 (u8 x s8 -> s32) over NT = N_pad / 8 column tiles with the A fragments (weights) loaded once: the
 //     "columns are batch columns" form of gemv_q4k_mma.cu, C[row][column] = the sub-block dot product p[j].
@@ -26,6 +30,8 @@
 // accm += (-dmin * dy) * summ;  the result is the four superblock classes' (acc + accm) added in class order.  Independent of
 // grid, ring depths and of N.  Within 1e-5 of ggml_vec_dot_q4_K_q8_K (tests/test_gpu_wide.py).
 #include <algorithm>
+
+#include <cuda.h>
 
 #include "gemv_stage.cuh"
 #include "q4k_kernels.h"
@@ -47,21 +53,27 @@ constexpr int WSLOT = WROWS * WPITCH;           // 9728 B
 constexpr size_t WIDE_SMEM_MAX = 232448;
 
 struct WideParams {
+    CUtensorMap wmap;           // the weights as a 2-D tensor of 8-byte elements [M][row bytes / 8], box = 16 rows x 608 B
     const uint8_t *w;
     int64_t M, w_stride;
     int nb;
-    const uint8_t *xs;          // staged activations: [n_pad][nb] blocks of XBLK bytes
+    const uint8_t *xs;          // staged activations: [rounds][n_pad] column pieces of APITCH bytes (4 blocks of XBLK + pad) = the stage images
     float *dst;
     int64_t dst_stride;         // floats between result columns
     int N, n_pad;
     int64_t tiles, passes;      // 16-row tiles, tile pairs
     int ast, wst;               // ring depths: activation stages, weight rounds (TSLOTS slots each)
+    int dbg;                    // development (knob wide_dbg): 1 = no activation copies, 2 = no arithmetic, 4 = no weight copies — wrong results, timing only
     int32_t *dump_p, *dump_sumi, *dump_summ;
 };
 
 __device__ __forceinline__ void imma(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void tma_box_g2s(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
 __device__ __forceinline__ uint2 lds64w(const uint8_t *p) { return *reinterpret_cast<const uint2 *>(p); }
 __device__ __forceinline__ void bar_sync_named(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
@@ -103,43 +115,50 @@ gemv_q4k_wide_kernel(const __grid_constant__ WideParams p) {
 
     if (warp == CW) {
         // ---- producer warp ----
-        const int ts = lane >> 4, rl = lane & 15;              // lane -> (tile slot, row of the tile) for the weight copies
-        auto issue_w = [&](int64_t q) {
-            const int64_t pass = blockIdx.x + (q / rounds) * gridDim.x;
-            const int rd = (int)(q % rounds), slot = (int)(q % WST);
-            const uint32_t ph = (uint32_t)((q / WST) & 1);
-            mbar_wait(smem_u32(&wempty[slot * TSLOTS + ts]), ph ^ 1u);
-            const uint32_t bytes = (uint32_t)min(RSB, nb - rd * RSB) * BLK_Q4K;
-            const uint32_t bar = smem_u32(&wfull[slot * TSLOTS + ts]);
-            if (rl == 0) mbar_expect_tx(bar, bytes * WROWS);
-            __syncwarp();
-            int64_t row = (pass * TSLOTS + ts) * WROWS + rl;
-            if (row >= p.M) row = p.M - 1;                     // ragged last tile / odd tile count: stay in bounds, not stored
-            fence_proxy_async();
-            bulk_g2s(smem_u32(w_s + (size_t)(slot * TSLOTS + ts) * WSLOT + rl * WPITCH),
-                     p.w + row * p.w_stride + (int64_t)rd * RSB * BLK_Q4K, bytes, bar);
+        // running state of the two copy sequences (no 64-bit divisions by run-time values on the issue path)
+        struct Seq { int64_t pass; int rd, slot; uint32_t ph; };
+        Seq sw{(int64_t)blockIdx.x, 0, 0, 0u}, sa{(int64_t)blockIdx.x, 0, 0, 0u};
+        auto advance = [&](Seq &s, int depth) {
+            if (++s.rd == rounds) { s.rd = 0; s.pass += gridDim.x; }
+            if (++s.slot == depth) { s.slot = 0; s.ph ^= 1u; }
         };
-        auto issue_a = [&](int64_t q) {
-            const int rd = (int)(q % rounds), st = (int)(q % AST);
-            const uint32_t ph = (uint32_t)((q / AST) & 1);
-            mbar_wait(smem_u32(&aempty[st]), ph ^ 1u);
-            const uint32_t bytes = (uint32_t)min(RSB, nb - rd * RSB) * XBLK;
-            const uint32_t bar = smem_u32(&afull[st]);
-            if (lane == 0) mbar_expect_tx(bar, bytes * (uint32_t)p.n_pad);
-            __syncwarp();
-            if (lane < p.n_pad) {
-                fence_proxy_async();
-                bulk_g2s(smem_u32(act_s + (size_t)st * astage + lane * APITCH),
-                         p.xs + ((int64_t)lane * nb + (int64_t)rd * RSB) * XBLK, bytes, bar);
+        auto issue_w = [&]() {                                 // lanes 0 and 1: one TMA box each (tile slots 0 and 1)
+            if (lane < TSLOTS) {
+                const int ts = lane;
+                mbar_wait(smem_u32(&wempty[sw.slot * TSLOTS + ts]), sw.ph ^ 1u);
+                const uint32_t bar = smem_u32(&wfull[sw.slot * TSLOTS + ts]);
+                if (p.dbg & 4) mbar_arrive(bar);
+                else {
+                    mbar_expect_tx(bar, WSLOT);
+                    fence_proxy_async();
+                    tma_box_g2s(smem_u32(w_s + (size_t)(sw.slot * TSLOTS + ts) * WSLOT), &p.wmap, sw.rd * (RSB * BLK_Q4K / 8),
+                                (int)((sw.pass * TSLOTS + ts) * WROWS), bar);
+                }
             }
+            advance(sw, WST);
+        };
+        auto issue_a = [&]() {
+            if (lane == 0) {
+                mbar_wait(smem_u32(&aempty[sa.slot]), sa.ph ^ 1u);
+                const uint32_t bar = smem_u32(&afull[sa.slot]);
+                if (p.dbg & 1) mbar_arrive(bar);
+                else {
+                    mbar_expect_tx(bar, (uint32_t)astage);
+                    fence_proxy_async();
+                    bulk_g2s(smem_u32(act_s + (size_t)sa.slot * astage), p.xs + (size_t)sa.rd * astage, (uint32_t)astage, bar);
+                }
+            }
+            advance(sa, AST);
         };
         // weights never depend on the previous kernel in the stream (the quantizer): the first WST rounds go out before the wait
-        const int64_t pre = total < WST ? total : WST;
-        for (int64_t q = 0; q < pre; ++q) issue_w(q);
+        // (both rings refill on the same event — round q consumed — so the loop waits in consumption order: a wait for a
+        // later round in front of a copy for an earlier one would cut that ring's lookahead to one round)
+        for (int64_t q = 0; q < WST && q < total; ++q) issue_w();
         griddep_wait();
+        for (int64_t q = 0; q < AST && q < total; ++q) issue_a();
         for (int64_t q = 0; q < total; ++q) {
-            issue_a(q);
-            if (q + WST < total) issue_w(q + WST);
+            if (q + AST < total) issue_a();
+            if (q + WST < total) issue_w();
         }
         return;
     }
@@ -147,7 +166,8 @@ gemv_q4k_wide_kernel(const __grid_constant__ WideParams p) {
     // ---- consumer warps ----
     const int sb = warp & (RSB - 1), ts = warp >> 2;
     const int r = lane >> 2, c = lane & 3;
-    int64_t q = 0;
+    int ast = 0, wsr = 0;                                       // ring positions and their phases, advanced once per round
+    uint32_t aph = 0u, wph = 0u;
     for (int64_t ip = 0; ip < my_passes; ++ip) {
         const int64_t pass = blockIdx.x + ip * gridDim.x;
         const int64_t tile = pass * TSLOTS + ts;
@@ -158,12 +178,12 @@ gemv_q4k_wide_kernel(const __grid_constant__ WideParams p) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) { acc[t][i] = 0.0f; accm[t][i] = 0.0f; }
 
-        for (int rd = 0; rd < rounds; ++rd, ++q) {
-            const int ast = (int)(q % AST), wsl = (int)(q % WST) * TSLOTS + ts;
-            mbar_wait(smem_u32(&afull[ast]), (uint32_t)((q / AST) & 1));
-            mbar_wait(smem_u32(&wfull[wsl]), (uint32_t)((q / WST) & 1));
+        for (int rd = 0; rd < rounds; ++rd) {
+            const int wsl = wsr * TSLOTS + ts;
+            mbar_wait(smem_u32(&afull[ast]), aph);
+            mbar_wait(smem_u32(&wfull[wsl]), wph);
             const int kb = rd * RSB + sb;
-            if (kb < nb && tile_ok) {
+            if (kb < nb && tile_ok && !(p.dbg & 2)) {
                 const uint8_t *p0 = w_s + (size_t)wsl * WSLOT + r * WPITCH + sb * BLK_Q4K, *p1 = p0 + 8 * WPITCH;
                 const uint8_t *ya = act_s + (size_t)ast * astage + sb * XBLK;
                 const uint4 h0 = lds128(p0), h1 = lds128(p1);
@@ -236,6 +256,8 @@ gemv_q4k_wide_kernel(const __grid_constant__ WideParams p) {
             }
             __syncwarp();
             if (lane == 0) { mbar_arrive(smem_u32(&aempty[ast])); mbar_arrive(smem_u32(&wempty[wsl])); }
+            if (++ast == AST) { ast = 0; aph ^= 1u; }
+            if (++wsr == WST) { wsr = 0; wph ^= 1u; }
         }
 
         // ---- end of the pass: the four superblock classes of each tile meet, in class order ----
@@ -264,8 +286,9 @@ gemv_q4k_wide_kernel(const __grid_constant__ WideParams p) {
     }
 }
 
-// Q8_K quantizer into the staged layout: one warp per (column, superblock); columns >= N (padding up to a multiple of 8) are
-// written as zero blocks.  Same arithmetic as quantize_q8k.cu (quantize_block_q8_K: explicit single-rounding intrinsics).
+// Q8_K quantizer into the staged layout — the shared-memory image of every round's activation stage, one after the other:
+// [round][column] pieces of APITCH bytes (the round's 4 blocks of the column + 32 B of bank padding).  One warp per
+// (column, superblock); columns >= N (padding up to a multiple of 8) are written as zero blocks.  Same arithmetic as quantize_q8k.cu (quantize_block_q8_K: explicit single-rounding intrinsics).
 __global__ void __launch_bounds__(256)
 quantize_q8_K_wide_kernel(const float *__restrict__ x, uint8_t *__restrict__ xs, int nb, int N, int n_pad, int64_t x_row_stride_bytes) {
     griddep_launch_dependents();
@@ -274,7 +297,7 @@ quantize_q8_K_wide_kernel(const float *__restrict__ x, uint8_t *__restrict__ xs,
     const int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (blk >= (int64_t)n_pad * nb) return;
     const int64_t col = blk / nb, b = blk - col * nb;
-    uint8_t *dst = xs + blk * XBLK;
+    uint8_t *dst = xs + ((b / RSB) * n_pad + col) * APITCH + (b % RSB) * XBLK;      // round b / 4, column col, block b % 4 of the piece
     uint32_t w_lo = 0u, w_hi = 0u;
     int s_lo = 0, s_hi = 0;
     float d = 0.0f;
@@ -329,8 +352,34 @@ cudaError_t launch_wide_nt(WideParams p, bool pdl, cudaStream_t stream) {
 
 size_t wide_workspace_bytes(int64_t K, int64_t N) {
     const int64_t cols = std::min<int64_t>(N, WIDE_MAX_COLS);
-    return (size_t)((cols + 7) / 8 * 8) * (size_t)(K / QK_K) * XBLK;
+    const int64_t rounds = (K / QK_K + RSB - 1) / RSB;
+    return (size_t)((cols + 7) / 8 * 8) * (size_t)rounds * APITCH;
 }
+
+namespace {
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+cudaError_t make_wide_weight_map(CUtensorMap *map, const void *w, int64_t M, int64_t nb, int64_t w_row_stride_bytes) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess) return e;
+        if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+        encode = (encode_fn)fn;
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)(nb * BLK_Q4K / 8), (cuuint64_t)M};
+    const cuuint64_t strides[1] = {(cuuint64_t)w_row_stride_bytes};
+    const cuuint32_t box[2] = {(cuuint32_t)(WPITCH / 8), (cuuint32_t)WROWS}, estr[2] = {1, 1};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_INT64, 2, const_cast<void *>(w), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+}  // namespace
 
 // F32 activations, 8 < N: quantizer (staged layout) + the batched decode kernel, column groups of up to 32.
 // dump: parity instantiation (p may be null).  cudaErrorNotSupported when a group's rings do not fit shared memory.
@@ -358,6 +407,7 @@ cudaError_t launch_gemv_q4k_wide(const void *w, int64_t M, int64_t K, int64_t w_
             if (eq != cudaSuccess) return eq;
         }
         WideParams p;
+        if (const cudaError_t em = make_wide_weight_map(&p.wmap, w, M, nb, w_row_stride_bytes)) return em;
         p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = nb;
         p.xs = (const uint8_t *)workspace;
         p.dst = reinterpret_cast<float *>(reinterpret_cast<char *>(dst) + n0 * dst_col_stride_bytes);
@@ -366,6 +416,7 @@ cudaError_t launch_gemv_q4k_wide(const void *w, int64_t M, int64_t K, int64_t w_
         p.tiles = (M + WROWS - 1) / WROWS;
         p.passes = (p.tiles + TSLOTS - 1) / TSLOTS;
         p.ast = p.wst = 0;
+        p.dbg = knobs().wide_dbg;
         p.dump_p = dump ? dump->p + n0 * M * nb * 8 : nullptr;
         p.dump_sumi = dump ? dump->sumi + n0 * M * nb : nullptr;
         p.dump_summ = dump ? dump->summ + n0 * M * nb : nullptr;

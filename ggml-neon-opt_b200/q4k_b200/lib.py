@@ -207,7 +207,8 @@ def vec_dot_q4_K_q8_K(n: int, s: torch.Tensor, bs: int, vx: torch.Tensor, bx: in
         _check("q4k_vec_dot_q4_K_q8_K", load().q4k_vec_dot_q4_K_q8_K(n, s.data_ptr(), bs, vx.data_ptr(), bx, vy.data_ptr(), by, nrc))
 
 
-DUMP_DISPATCH, DUMP_TENSOR_PIPE, DUMP_BULK, DUMP_BULK_EXACT, DUMP_BIG, DUMP_GEMM = range(6)
+DUMP_DISPATCH, DUMP_TENSOR_PIPE, DUMP_BULK, DUMP_BULK_EXACT, DUMP_BIG, DUMP_GEMM, DUMP_WIDE = range(7)
+MIDN_MAX = 64          # largest N the batched decode kernel serves by default (knob midn_max); the GEMM takes over above
 
 
 def mul_mat_dump(w: torch.Tensor, x: torch.Tensor, kernel: int = DUMP_DISPATCH):
@@ -218,7 +219,7 @@ def mul_mat_dump(w: torch.Tensor, x: torch.Tensor, kernel: int = DUMP_DISPATCH):
     M, nb = w.shape[0], w.shape[1] // Q4K_BLOCK
     N, K = x.shape
     SENT = -0x7f7f7f7f
-    gemm = kernel == DUMP_GEMM or (kernel == DUMP_DISPATCH and N > 12)
+    gemm = kernel == DUMP_GEMM or (kernel == DUMP_DISPATCH and N > MIDN_MAX)
     p = None if gemm else torch.full((N, M, nb, 8), SENT, dtype=torch.int32, device=w.device)
     si = torch.full((N, M, nb), SENT, dtype=torch.int32, device=w.device)
     sm = torch.full((N, M, nb), SENT, dtype=torch.int32, device=w.device)

@@ -76,8 +76,16 @@ def test_int32_partials_bit_exact_from_the_large_matrix_kernel(q4k, M, K):
     assert np.array_equal(p.cpu().numpy(), rp) and np.array_equal(si.cpu().numpy(), rsi) and np.array_equal(sm.cpu().numpy(), rsm)
 
 
+@pytest.fixture()
+def gemm_path(q4k):
+    """8 < N <= 64 through the tcgen05 GEMM (as for N > 64) instead of the batched decode kernel (tests/test_gpu_wide.py)"""
+    q4k.debug_set("midn_max", 0)
+    yield
+    q4k.debug_set("midn_max", 64)
+
+
 @pytest.mark.parametrize("M,K,N", [(128, 512, 16), (200, 2048, 40), (130, 1024, 130), (64, 14336, 32), (300, 4096, 9)])
-def test_int32_sums_bit_exact_from_the_gemm_epilogue(q4k, M, K, N):
+def test_int32_sums_bit_exact_from_the_gemm_epilogue(q4k, gemm_path, M, K, N):
     """The prefill GEMM never forms p[j] (the scales ride in the A operand), but its epilogue reads sumi = 8 hi + lo and summ
     of every (row, column, superblock) out of TMEM: the DUMP instantiation writes exactly those integers."""
     from oracle import port
@@ -163,7 +171,7 @@ def test_back_to_back_pdl_launches_see_fresh_activations(q4k, exact_order):
 
 
 @pytest.mark.parametrize("M,K,N", [(128, 256, 16), (256, 2048, 128), (130, 512, 9), (300, 1024, 200), (64, 4096, 130), (512, 5632, 64)])
-def test_gemm_tensor_core_within_tolerance(q4k, M, K, N):
+def test_gemm_tensor_core_within_tolerance(q4k, gemm_path, M, K, N):
     """N > 8 takes the tcgen05 kind::i8 GEMM (exact int32 sumi / summ per superblock in TMEM, fp32 scales in the
     epilogue); fp32 results within 1e-5 of the AVX2-order oracle, ragged M / N tiles included."""
     from oracle import port
@@ -172,7 +180,7 @@ def test_gemm_tensor_core_within_tolerance(q4k, M, K, N):
     check(f"gemm {M}x{K} N={N}", got, w, x)
 
 
-def test_gemm_integer_stage_is_exact(q4k):
+def test_gemm_integer_stage_is_exact(q4k, gemm_path):
     """With d = dmin = 1 in every weight block and activations that quantize to themselves (d_x = 1), the fp32 output
     is exactly sumi - summ: any error in the tensor-core integer stage (scale split, min accumulator) shows."""
     from oracle import port
@@ -195,7 +203,7 @@ def test_gemm_integer_stage_is_exact(q4k):
 
 
 @pytest.mark.parametrize("ksplit", [1, 2, 3, 8])
-def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit):
+def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, gemm_path, ksplit):
     """Launches with fewer tiles than SMs split K over several CTAs per tile (turnstile epilogue: parts add in K order).
     Same exact-float construction as above at K = 2048: any lost / doubled superblock or a race in the turnstile shows as a
     wrong integer; two runs give identical bits."""
@@ -226,7 +234,7 @@ def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, ksplit):
 
 
 @pytest.mark.parametrize("N,K", [(16, 512), (130, 2048), (40, 4096)])
-def test_prefill_reuses_the_quantized_activations(q4k, N, K):
+def test_prefill_reuses_the_quantized_activations(q4k, gemm_path, N, K):
     """q/k/v of a layer are three mul_mats on one src1: q4k_mul_mat_reuse runs the GEMM on the quantized copy the first call
     left in the workspace (one launch instead of two) and gives the bits of a full q4k_mul_mat; N <= 12 is declined."""
     import torch
