@@ -96,7 +96,10 @@ size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
     if (N > Q4K_GEMV_MAX_N) {                                            // prefill path: int8 + mins tiles of whole 128-column tiles, scales
         const size_t gemm = q4k::gemm_workspace_bytes(K, N);
         if (gemm > need) need = gemm;
-        const size_t wide = q4k::wide_workspace_bytes(K, N);             // batched decode kernel: staged Q8_K, padded to 8 columns
+
+    }
+    if (N >= knobs().wide_min && N <= knobs().midn_max) {                // batched decode kernel: staged Q8_K, padded to 8 columns
+        const size_t wide = q4k::wide_workspace_bytes(K, N);
         if (wide > need) need = wide;
     }
     return need;
@@ -147,7 +150,8 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
     if (K > 0) {
         if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
         if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
-        const bool wide = N >= knobs().wide_min && N <= knobs().midn_max;
+        // (the bit-exact AVX2 order, when asked for, exists only in the decode kernel)
+        const bool wide = N >= knobs().wide_min && N <= knobs().midn_max && !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N));
         // decode shapes: one launch — every CTA quantizes the (small) activations into its own shared memory
         if (!wide && N <= Q4K_GEMV_MAX_N && N * K <= knobs().fuse_limit && knobs().gemv_config == 0) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
@@ -363,7 +367,8 @@ int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_
     if (!workspace_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
     cudaStream_t st = (cudaStream_t)stream;
     // which product kernel: the one q4k_mul_mat would launch for this shape, unless the caller names one
-    const bool wide = kernel == Q4K_DUMP_WIDE || (kernel == Q4K_DUMP_DISPATCH && N >= knobs().wide_min && N <= knobs().midn_max);
+    const bool wide = kernel == Q4K_DUMP_WIDE || (kernel == Q4K_DUMP_DISPATCH && N >= knobs().wide_min && N <= knobs().midn_max &&
+                                                  !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N)));
     if (wide) {
         if (!p_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
         const IntDump d{p_dev, sumi_dev, summ_dev};

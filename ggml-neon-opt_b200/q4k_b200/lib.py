@@ -208,7 +208,7 @@ def vec_dot_q4_K_q8_K(n: int, s: torch.Tensor, bs: int, vx: torch.Tensor, bx: in
 
 
 DUMP_DISPATCH, DUMP_TENSOR_PIPE, DUMP_BULK, DUMP_BULK_EXACT, DUMP_BIG, DUMP_GEMM, DUMP_WIDE = range(7)
-MIDN_MAX = 64          # largest N the batched decode kernel serves by default (knob midn_max); the GEMM takes over above
+MIDN_MAX = 32          # largest N the batched decode kernel serves by default (knob midn_max); the GEMM takes over above
 
 
 def mul_mat_dump(w: torch.Tensor, x: torch.Tensor, kernel: int = DUMP_DISPATCH):

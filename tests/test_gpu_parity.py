@@ -81,7 +81,7 @@ def gemm_path(q4k):
     """8 < N <= 64 through the tcgen05 GEMM (as for N > 64) instead of the batched decode kernel (tests/test_gpu_wide.py)"""
     q4k.debug_set("midn_max", 0)
     yield
-    q4k.debug_set("midn_max", 64)
+    q4k.debug_set("midn_max", 32)
 
 
 @pytest.mark.parametrize("M,K,N", [(128, 512, 16), (200, 2048, 40), (130, 1024, 130), (64, 14336, 32), (300, 4096, 9)])

@@ -23,8 +23,10 @@ def order(request, q4k):
     """every test here runs with both decode kernels: the default (tensor-pipe, tolerance order) and the AVX2-order one"""
     lib = q4k.load()
     lib.q4k_debug_set_gemv_order(1 if request.param == "exact" else 0)
+    q4k.debug_set("wide_min", 9)        # N = 3..8 stay on the decode kernels here: q4k_mul_mat alone would hand them to gemv_q4k_wide.cu
     yield request.param
     lib.q4k_debug_set_gemv_order(0)
+    q4k.debug_set("wide_min", 3)
 
 
 @pytest.mark.parametrize("Ms,K,N", [((2048, 256, 256), 2048, 1), ((5632, 5632), 2048, 1), ((37, 4, 129, 1), 512, 2),
@@ -177,4 +179,29 @@ def test_plan_argument_errors(q4k):
     with pytest.raises(q4k.Q4KError):
         plan.add(w, 1, 0)                                           # frozen
     assert L.q4k_plan_run_host(plan._p, None, None, None) == -2
+    plan.close()
+
+
+def test_plan_default_dispatch_batch_4(q4k, order):
+    """default knobs at N = 4: q/k/v and gate/up go out as group launches of the decode kernel, o and down through the batched
+    decode kernel (quantizer + kernel): 2 + 2 * 2 launches; every output within 1e-5 of the oracle."""
+    import torch
+    from parity_util import check
+    if order == "exact":
+        pytest.skip("the AVX2-order mode keeps N <= 8 on the decode kernel")
+    q4k.debug_set("wide_min", 3)
+    N = 4
+    shapes, ws = _layer(q4k, N, seed=3)
+    plan = q4k.GraphPlan(0)
+    for w, (_, _, _, iid) in zip(ws, shapes):
+        plan.add(w, N, iid)
+    plan.finalize()
+    assert plan.launches == 6
+    xs = {iid: make_acts(N, Kk, seed=70 + iid) for _, _, Kk, iid in shapes}
+    for iid, x in xs.items():
+        plan.input(iid).copy_(t(x))
+    plan.run()
+    torch.cuda.synchronize()
+    for i, (w, (name, _, _, iid)) in enumerate(zip(ws, shapes)):
+        check(f"plan N=4 {name}", plan.output(i).cpu().numpy(), w.cpu().numpy(), xs[iid])
     plan.close()

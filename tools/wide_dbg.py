@@ -13,7 +13,7 @@ for M, K in [(28672, 8192), (4096, 14336)]:
     w = rand_q4k(M, K, copies)
     for N in (4, 16, 32):
         x = torch.randn((N, K), device="cuda"); dst = torch.empty((N, M), device="cuda")
-        ws = torch.empty(q4k_b200.workspace_bytes(K, N), dtype=torch.uint8, device="cuda")
+        ws = torch.empty(max(q4k_b200.workspace_bytes(K, N), q4k_b200.workspace_bytes(K, 9)), dtype=torch.uint8, device="cuda")
         res = {}
         for dbg in (0, 1, 2, 3, 4, 6, 7):
             q4k_b200.debug_set("wide_dbg", dbg)

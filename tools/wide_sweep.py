@@ -27,14 +27,14 @@ for M, K in shapes:
     for N in ns:
         x = torch.randn((N, K), device="cuda")
         dst = torch.empty((N, M), device="cuda")
-        ws = torch.empty(q4k_b200.workspace_bytes(K, N), dtype=torch.uint8, device="cuda")
+        ws = torch.empty(max(q4k_b200.workspace_bytes(K, N), q4k_b200.workspace_bytes(K, 9)), dtype=torch.uint8, device="cuda")
         res = {}
         for name, midn, wmin in (("wide", 64, 1), ("before", 0, 9)):      # N <= 8: "before" = the decode kernel (gemv_q4k_mma.cu)
             q4k_b200.debug_set("midn_max", midn)
             q4k_b200.debug_set("wide_min", wmin)
             res[name] = round(graph_time_us(lambda i: q4k_b200.mul_mat(w[i % copies], x, dst, ws), per_graph=max(copies, 10), replays=5), 1)
         q4k_b200.debug_set("midn_max", 64)
-        q4k_b200.debug_set("wide_min", 9)
+        q4k_b200.debug_set("wide_min", 3)
         algo = wbytes + N * K * 4 + M * N * 4
         gbs = algo / res["wide"] / 1e3
         print(json.dumps(dict(M=M, K=K, N=N, us_wide=res["wide"], us_before=res["before"], gbs=round(gbs, 1), frac_measured=round(gbs / PEAK, 3))), flush=True)
