@@ -102,6 +102,19 @@ gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
         }
         const int nsb = min(TILE_SB, nb - prod_ks * TILE_SB);
         const uint32_t bytes = (uint32_t)nsb * BLK_Q4K;
+        if (p.use_tma) {                               // one tensor copy per tile: 4 rows x 1152 B (zeros past the row end / past M)
+            if (lane == 0) {
+                int mat = 0;
+                int64_t lg = cur_rg;
+                while (mat + 1 < p.nmat && cur_rg >= p.gend[mat]) { lg = cur_rg - p.gend[mat]; ++mat; }
+                meta[s] = make_int2((int)cur_rg, prod_ks);
+                mbar_expect_tx(bar, STAGE_BYTES);
+                fence_proxy_async();                  // the warp's generic reads of this slot are done (callers sync the warp first)
+                tma_box_g2s(smem_u32(wbuf + (size_t)s * STAGE_BYTES), &p.wmap[mat], prod_ks * (ROW_BYTES / 8), (int)(lg * TILE_ROWS), bar);
+            }
+            ++prod_ks;
+            return;
+        }
         if (lane == 0) {
             meta[s] = make_int2((int)cur_rg, prod_ks);
             mbar_expect_tx(bar, bytes * TILE_ROWS);
@@ -361,6 +374,7 @@ template <int N, int ORD>
 cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
     constexpr bool EXACT = ORD == 1;
     auto kern = p.dump_p ? gemv_q4k_tma_kernel<N, ORD, true> : gemv_q4k_tma_kernel<N, ORD>;
+    fill_weight_maps(p, ROW_BYTES, TILE_ROWS);
     const size_t fixed = fixed_smem(N * p.nx, p.nb, EXACT, N);
     if (fixed + PER_STAGE > SMEM_MAX) return cudaErrorNotSupported;      // activations do not fit: caller tiles
     // resident CTAs per SM: as many as registers allow (launch bounds: 2), each with a 2-slot ring when it fits

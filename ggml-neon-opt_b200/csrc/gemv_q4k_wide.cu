@@ -72,10 +72,6 @@ __device__ __forceinline__ void imma(int (&c)[4], uint32_t a0, uint32_t a1, uint
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
-__device__ __forceinline__ void tma_box_g2s(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
 __device__ __forceinline__ uint2 lds64w(const uint8_t *p) { return *reinterpret_cast<const uint2 *>(p); }
 __device__ __forceinline__ void bar_sync_named(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
@@ -332,29 +328,6 @@ cudaError_t launch_wide_cfg(WideParams p, bool pdl, cudaStream_t stream) {
     return e;
 }
 
-// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
-cudaError_t make_wide_weight_map(CUtensorMap *map, const void *w, int64_t M, int64_t nb, int64_t w_row_stride_bytes) {
-    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-    static encode_fn encode = nullptr;
-    if (!encode) {
-        void *fn = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
-        if (e != cudaSuccess) return e;
-        if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
-        encode = (encode_fn)fn;
-    }
-    const cuuint64_t dims[2] = {(cuuint64_t)(nb * BLK_Q4K / 8), (cuuint64_t)M};
-    const cuuint64_t strides[1] = {(cuuint64_t)w_row_stride_bytes};
-    const cuuint32_t box[2] = {(cuuint32_t)(WPITCH / 8), (cuuint32_t)WROWS}, estr[2] = {1, 1};
-    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_INT64, 2, const_cast<void *>(w), dims, strides, box, estr,
-                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
-}
-
 }  // namespace
 
 size_t wide_workspace_bytes(int64_t K, int64_t N) {
@@ -371,7 +344,7 @@ cudaError_t launch_gemv_q4k_wide(const void *w, int64_t M, int64_t K, int64_t w_
     if (M <= 0 || N <= 0) return cudaSuccess;
     const int nb = (int)(K / QK_K);
     WideParams p;
-    if (const cudaError_t em = make_wide_weight_map(&p.wmap, w, M, nb, w_row_stride_bytes)) return em;
+    if (!make_row_box_map(&p.wmap, w, M, (int64_t)nb * BLK_Q4K, w_row_stride_bytes, WPITCH, WROWS)) return cudaErrorNotSupported;
     for (int64_t n0 = 0; n0 < N; n0 += WIDE_MAX_COLS) {
         const int nn = (int)std::min<int64_t>(WIDE_MAX_COLS, N - n0);
         // 17..24 columns run as 32 (zero columns): measured no slower than a ragged second half, and one shape less

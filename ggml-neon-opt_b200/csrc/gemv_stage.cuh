@@ -3,6 +3,8 @@
 // from a workspace, or quantized in place from F32 with the arithmetic of quantize_q8k.cu).
 #pragma once
 
+#include <cuda.h>
+
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
@@ -26,6 +28,11 @@ constexpr int SCR_WORDS = TILE_ROWS * SCR_ROW;      // per column
 constexpr int WARPS = 8;
 
 struct TmaGemvParams {
+    // the weight matrices as 2-D tensors of 8-byte elements [M][row bytes / 8] (make_row_box_map): ONE tensor copy fetches a
+    // whole tile (rows x row piece) where the bulk-copy path needs one copy per row — an SM retires a copy of either kind every
+    // ~60-80 cycles, which is what capped the row-piece kernels at ~5.7 TB/s (profiles/r1_micro_stream_bulk.txt, r2_wide_sweep*)
+    CUtensorMap wmap[4];
+    int use_tma;            // 1 = wmap[] are valid and the kernel fetches tiles through them
     const uint8_t *w;
     int64_t M, w_stride;
     int nb;
@@ -76,6 +83,45 @@ inline void fill_ll(TmaGemvParams &p, const LLExchange *ll) {
     p.ll_cnt = ll->cnt; p.ll_dst = ll->dst; p.ll_world = ll->world; p.ll_rank = ll->rank;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda): rows of `row_bytes`
+// (a multiple of 8) at `w_row_stride_bytes`, box = box_rows x box_bytes.  false = not available: the caller keeps bulk copies.
+inline bool make_row_box_map(CUtensorMap *map, const void *w, int64_t M, int64_t row_bytes, int64_t w_row_stride_bytes, int box_bytes,
+                             int box_rows) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+            encode = (encode_fn)fn;
+        tried = true;
+    }
+    if (!encode || M <= 0 || M > 0x7fffffff || (row_bytes & 7) || (box_bytes & 15) || box_bytes / 8 > 256 || box_rows > 256) return false;
+    if ((reinterpret_cast<uintptr_t>(w) & 15) || (w_row_stride_bytes & 15)) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)(row_bytes / 8), (cuuint64_t)M};
+    const cuuint64_t strides[1] = {(cuuint64_t)w_row_stride_bytes};
+    const cuuint32_t box[2] = {(cuuint32_t)(box_bytes / 8), (cuuint32_t)box_rows}, estr[2] = {1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_INT64, 2, const_cast<void *>(w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// tensor maps for the nmat matrices of a launch (p.wm / p.Mm / p.w_stride / p.nb must be set); leaves use_tma = 0 on any failure
+inline void fill_weight_maps(TmaGemvParams &p, int box_bytes, int box_rows) {
+    p.use_tma = 0;
+    // Measured (profiles/r2_tma_box_*.txt): worth 1-2% on launches that stream tens of MB (28672 x 8192: 24.41 -> 24.08 us), nothing
+    // or slightly negative on small ones (the first tensor copy also fetches its descriptor: 5632 x 2048 3.73 -> 3.81 us).
+    // tma_boxes: 0 = never, 1 = launches of at least 24 MiB of weights, 2 = always
+    int64_t bytes = 0;
+    for (int i = 0; i < p.nmat; ++i) bytes += p.Mm[i] * (int64_t)p.nb * BLK_Q4K;
+    if (knobs().tma_boxes == 0 || (knobs().tma_boxes == 1 && bytes < ((int64_t)24 << 20))) return;
+    for (int i = 0; i < p.nmat; ++i)
+        if (!make_row_box_map(&p.wmap[i], p.wm[i], p.Mm[i], (int64_t)p.nb * BLK_Q4K, p.w_stride, box_bytes, box_rows)) return;
+    p.use_tma = 1;
+}
+
 inline void fill_sync(TmaGemvParams &p, int n_peers) {
     p.dump_p = p.dump_sumi = p.dump_summ = nullptr;
     fill_ll(p, nullptr);
@@ -116,6 +162,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// TMA tile copy of a 2-D box global -> shared; c0 = first 8-byte element inside the row, c1 = first row.  Elements outside the
+// tensor (past the end of a row, rows past M) arrive as zeros and still count towards the barrier's byte count.
+__device__ __forceinline__ void tma_box_g2s(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

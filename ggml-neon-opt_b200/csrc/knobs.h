@@ -23,6 +23,7 @@ struct Knobs {
     int     tma_stages, tma_per_sm;                            // gemv_q4k_tma.cu
     int     gemm_ksplit;        // gemm_q4k_tc.cu: CTAs along K per tile (0 = choose)
     int     wide_min;           // smallest N q4k_mul_mat hands to the batched decode kernel (gemv_q4k_wide.cu); below it: gemv_q4k_mma.cu
+    int     tma_boxes;          // 1 = the decode kernels fetch weight tiles with TMA tensor copies (one per tile), 0 = one bulk copy per row
     int     wide_dbg;           // gemv_q4k_wide.cu timing experiments (results are wrong when set)
     int     midn_max;           // largest N served by the batched tensor-pipe decode kernel (gemv_q4k_wide.cu); 0 = off
     int64_t q6k_fuse_limit;
