@@ -98,6 +98,7 @@ size_t q4k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
         if (gemm > need) need = gemm;
 
     }
+    if (N == 1 && q4k::n1s_workspace_bytes(K) > need) need = q4k::n1s_workspace_bytes(K);      // streamed single-column kernel: whole rounds of staged blocks
     if (N >= knobs().wide_min && N <= knobs().midn_max) {                // batched decode kernel: staged Q8_K, padded to 8 columns
         const size_t wide = q4k::wide_workspace_bytes(K, N);
         if (wide > need) need = wide;
@@ -152,6 +153,23 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
         if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
         // (the bit-exact AVX2 order, when asked for, exists only in the decode kernel)
         const bool wide = N >= knobs().wide_min && N <= knobs().midn_max && !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N));
+        // one column of a matrix that streams tens of MB or has a long K: quantize once, stream the activations next to the weights
+        // (gemv_q4k_n1s.cu; the bits of the decode kernel below)
+        // Measured (profiles/r2_n1s_sweep.txt): wins where K is long and there are enough tiles for every SM — 4096 x 14336
+        // 11.85 -> 9.45 us, 4096 x 28672 18.3 -> 14.5, 8192 x 28672 27.6 -> 26.7; loses on short K (14336 x 4096 9.1 -> 9.7) and on
+        // few rows (1024 x 28672: 32 tile pairs for 148 SMs).
+        if (N == 1 && !gemv_exact_for(1) && knobs().gemv_config == 0 && !knobs().mma_off &&
+            ((K >= knobs().n1s_min_k && M >= 2048) ||
+             (knobs().n1s_min_bytes > 0 && M * (K / Q4K_QK_K) * Q4K_BLOCK_Q4K >= knobs().n1s_min_bytes))) {
+            if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;
+            const int64_t nb = K / Q4K_QK_K;
+            if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
+            if (!aligned16(x_dev) || !aligned16(workspace_dev)) return Q4K_ERR_BAD_SHAPE;
+            const cudaError_t e = launch_gemv_q4k_n1s(w_dev, M, K, w_row_stride_bytes, x_dev, dst_dev, workspace_dev, knobs().pdl != 0,
+                                                      (cudaStream_t)stream);
+            if (e == cudaSuccess) return Q4K_OK;
+            if (e != cudaErrorNotSupported) return cuda_fail(e);
+        }
         // decode shapes: one launch — every CTA quantizes the (small) activations into its own shared memory
         if (!wide && N <= Q4K_GEMV_MAX_N && N * K <= knobs().fuse_limit && knobs().gemv_config == 0) {
             if (!w_dev || !x_dev || !dst_dev) return Q4K_ERR_BAD_POINTER;

@@ -90,6 +90,12 @@ cudaError_t launch_gemv_q4k_wide(const void *w, int64_t M, int64_t K, int64_t w_
                                  int64_t x_row_stride_bytes, float *dst, int64_t dst_col_stride_bytes, void *workspace, bool pdl,
                                  cudaStream_t stream, const IntDump *dump = nullptr);
 
+// streamed single-column decode (gemv_q4k_n1s.cu): F32 activation row, quantized into `workspace` (n1s_workspace_bytes) and
+// streamed next to the weights; same bits as gemv_q4k_mma.cu at N == 1
+size_t n1s_workspace_bytes(int64_t K);
+cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x, float *dst,
+                                void *workspace, bool pdl, cudaStream_t stream);
+
 // Q6_K decode GEMV (gemv_q6k.cu), 1 <= N <= 8; dump != nullptr also writes the per-superblock integer sums
 cudaError_t launch_gemv_q6k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                             const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
