@@ -218,18 +218,6 @@ gemv_q4k_mma_kernel(const __grid_constant__ TmaGemvParams p) {
                 mbar_wait(smem_u32(&empty[s]), eparity);
                 const uint32_t bytes = (uint32_t)min(KW, nb - rd * KW) * BLK_Q4K;
                 const uint32_t bar = smem_u32(&full[s]);
-                if (p.use_tma) {
-                    // one tensor copy per slot: 16 rows x PITCH bytes (the pad bytes are the next round's first bytes; past the
-                    // row end and past M the box reads zeros)
-                    if (lane == 0) {
-                        mbar_expect_tx(bar, Cfg::SLOT);
-                        fence_proxy_async();
-                        tma_box_g2s(smem_u32(slots + (size_t)s * Cfg::SLOT), &p.wmap[mat], rd * (ROW_BYTES / 8), (int)(lt * MROWS), bar);
-                    }
-                    if (tile == t0 && rd == rd0) TICK(9);
-                    if (++s == S) { s = 0; eparity ^= 1u; }
-                    continue;
-                }
                 if (lane == 0) mbar_expect_tx(bar, bytes * MROWS);
                 __syncwarp();
                 if (lane < MROWS) {
@@ -488,7 +476,6 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
     if (knobs().mma_stages > 0 && knobs().mma_stages < stages) stages = knobs().mma_stages;
     if (knobs().mma_per_sm > 0) per_sm = min(per_sm, knobs().mma_per_sm);
     p.stages = stages;
-    fill_weight_maps(p, MmaCfg<N>::PITCH, MROWS);
     p.interleave = knobs().mma_contig > 0 ? 0 : 1;
     const size_t smem = fixed + (size_t)stages * slot;
     if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)MMA_SMEM_MAX)) return ea;
@@ -542,7 +529,7 @@ cudaError_t launch_gemv_q4k_mma(int nmat, const void *const *w, const int64_t *M
     else { p.dst[0] = dst ? dst[0] : nullptr; p.n_dst = 1; }
     p.dst_row0 = dst_row0;
     p.dst_stride = dst_col_stride_bytes > 0 ? dst_col_stride_bytes / 4 : M[0];      // 0 = dense [N][M]
-    p.stages = 0; p.nmat = nmat; p.nx = 0; p.use_tma = 0;
+    p.stages = 0; p.nmat = nmat; p.nx = 0;
     fill_sync(p, nmat == 1 ? n_peers : 0);
     if (ll && nmat != 1) return cudaErrorInvalidValue;
     fill_ll(p, ll);

@@ -50,7 +50,7 @@ namespace {
 // DUMP: parity instantiation — the same code, and the integers it computed are also written out (q4k_mul_mat_dump)
 template <int N, int ORD, bool DUMP = false>
 __global__ void __launch_bounds__(WARPS * 32, 2)
-gemv_q4k_tma_kernel(const __grid_constant__ TmaGemvParams p) {
+gemv_q4k_tma_kernel(const __grid_constant__ TmaBoxParams p) {
     constexpr bool EXACT = ORD == 1, MMAORD = ORD == 2;
     static_assert(!MMAORD || N == 1, "the tensor-pipe order is only instantiated for N == 1");
     extern __shared__ __align__(128) uint8_t smem[];
@@ -371,7 +371,9 @@ size_t fixed_smem(int nrows, int nb, bool exact, int N) {    // nrows = staged a
 constexpr size_t PER_STAGE = (size_t)WARPS * (STAGE_BYTES + 16);
 
 template <int N, int ORD>
-cudaError_t launch_tma_n(TmaGemvParams p, int want_stages, bool pdl, cudaStream_t stream) {
+cudaError_t launch_tma_n(const TmaGemvParams &base, int want_stages, bool pdl, cudaStream_t stream) {
+    TmaBoxParams p;
+    static_cast<TmaGemvParams &>(p) = base;
     constexpr bool EXACT = ORD == 1;
     auto kern = p.dump_p ? gemv_q4k_tma_kernel<N, ORD, true> : gemv_q4k_tma_kernel<N, ORD>;
     fill_weight_maps(p, ROW_BYTES, TILE_ROWS);

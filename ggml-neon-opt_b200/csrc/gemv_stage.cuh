@@ -28,11 +28,6 @@ constexpr int SCR_WORDS = TILE_ROWS * SCR_ROW;      // per column
 constexpr int WARPS = 8;
 
 struct TmaGemvParams {
-    // the weight matrices as 2-D tensors of 8-byte elements [M][row bytes / 8] (make_row_box_map): ONE tensor copy fetches a
-    // whole tile (rows x row piece) where the bulk-copy path needs one copy per row — an SM retires a copy of either kind every
-    // ~60-80 cycles, which is what capped the row-piece kernels at ~5.7 TB/s (profiles/r1_micro_stream_bulk.txt, r2_wide_sweep*)
-    CUtensorMap wmap[4];
-    int use_tma;            // 1 = wmap[] are valid and the kernel fetches tiles through them
     const uint8_t *w;
     int64_t M, w_stride;
     int nb;
@@ -73,6 +68,14 @@ struct TmaGemvParams {
     int ll_world, ll_rank;
 };
 
+// gemv_q4k_tma.cu's parameters: + the weight matrices as 2-D tensors of 8-byte elements [M][row bytes / 8] (make_row_box_map):
+// ONE tensor copy fetches a whole tile (rows x row piece) where the bulk-copy path needs one copy per row.  (Kept out of the
+// struct the tensor-pipe decode kernel takes: 520 more parameter bytes cost its 3.7 us launches 4%.)
+struct TmaBoxParams : TmaGemvParams {
+    CUtensorMap wmap[4];
+    int use_tma;            // 1 = wmap[] are valid and the kernel fetches tiles through them
+};
+
 inline void fill_ll(TmaGemvParams &p, const LLExchange *ll) {
     for (int r = 0; r < 8; ++r) p.ll_peers[r] = nullptr;
     p.ll_local = nullptr; p.ll_half = p.ll_M = p.ll_dst_stride = 0; p.ll_cnt = nullptr; p.ll_dst = nullptr; p.ll_world = 0; p.ll_rank = 0;
@@ -109,7 +112,7 @@ inline bool make_row_box_map(CUtensorMap *map, const void *w, int64_t M, int64_t
 }
 
 // tensor maps for the nmat matrices of a launch (p.wm / p.Mm / p.w_stride / p.nb must be set); leaves use_tma = 0 on any failure
-inline void fill_weight_maps(TmaGemvParams &p, int box_bytes, int box_rows) {
+inline void fill_weight_maps(TmaBoxParams &p, int box_bytes, int box_rows) {
     p.use_tma = 0;
     // Measured (profiles/r2_tma_box_*.txt): worth 1-2% on launches that stream tens of MB (28672 x 8192: 24.41 -> 24.08 us), nothing
     // or slightly negative on small ones (the first tensor copy also fetches its descriptor: 5632 x 2048 3.73 -> 3.81 us).
