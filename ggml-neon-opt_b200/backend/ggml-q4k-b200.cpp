@@ -211,6 +211,111 @@ const ggml_backend_buffer_type_i host_buft_iface = {
     /* .is_host        = */ host_buft_is_host,
 };
 
+// ------------------------------------------------------------------------------------------ split (row-sharded) buffer type
+// --split-mode row: L/src/llama-model.cpp:375-401 asks the registry for "ggml_backend_split_buffer_type" and puts the matmul
+// weights of a layer into the buffer type it returns.  The shape follows ggml-cuda's (L/ggml/src/ggml-cuda/ggml-cuda.cu:795-1050):
+// the buffer has no memory of its own (fake base address), init_tensor deals the tensor's rows to the devices
+// (q4k_split_create), set_tensor / get_tensor scatter / gather, and MUL_MAT on such a tensor runs every device's shard with the
+// result rows stored straight into the main device's dst (q4k_split_mul_mat).  Everything below the vtable is the C ABI.
+struct split_buft_context {
+    int main_device = 0;                 // index into devices()
+    std::vector<float> fractions;        // one share per registered device (all zero = equal)
+    std::string name;
+};
+
+struct split_buffer_context {
+    std::vector<q4k_split *> splits;     // one per tensor, owned
+    ~split_buffer_context() { for (auto * s : splits) q4k_split_destroy(s); }
+};
+
+const char * split_buft_get_name(ggml_backend_buffer_type_t buft) { return ((split_buft_context *) buft->context)->name.c_str(); }
+bool buft_is_split(ggml_backend_buffer_type_t buft) { return buft && buft->iface.get_name == split_buft_get_name; }
+bool tensor_is_split(const ggml_tensor * t) { return t && t->buffer && buft_is_split(t->buffer->buft); }
+
+void split_buffer_free(ggml_backend_buffer_t buffer) { delete (split_buffer_context *) buffer->context; }
+void * split_buffer_get_base(ggml_backend_buffer_t) { return (void *) 0x1000; }      // never dereferenced: tensors carry their shards in ->extra
+
+ggml_status split_buffer_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor) {
+    GGML_ASSERT(tensor->view_src == nullptr && "views of split tensors are not supported");
+    GGML_ASSERT(ggml_is_contiguous(tensor) && "split buffers hold contiguous tensors only");
+    auto * ctx = (split_buffer_context *) buffer->context;
+    auto * bctx = (split_buft_context *) buffer->buft->context;
+    std::vector<int> devs;
+    for (auto & d : device_contexts()) devs.push_back(d.cuda_device);
+    // 16-row granule: the decode kernels' tile, so every shard starts on a tile boundary
+    q4k_split * sp = q4k_split_create(devs.data(), (int) devs.size(), bctx->fractions.data(), ggml_nrows(tensor),
+                                      (int64_t) ggml_row_size(tensor->type, tensor->ne[0]), 16);
+    if (!sp) {
+        GGML_LOG_ERROR("Q4K_B200: cannot allocate the shards of %s (cudaError %d)\n", tensor->name, q4k_last_cuda_error());
+        return GGML_STATUS_ALLOC_FAILED;
+    }
+    ctx->splits.push_back(sp);
+    tensor->extra = sp;
+    return GGML_STATUS_SUCCESS;
+}
+
+void split_buffer_set_tensor(ggml_backend_buffer_t, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    if (q4k_split_set((q4k_split *) tensor->extra, data, offset, size) != Q4K_OK)
+        GGML_ABORT("Q4K_B200: set_tensor on split tensor %s failed (cudaError %d)", tensor->name, q4k_last_cuda_error());
+}
+
+void split_buffer_get_tensor(ggml_backend_buffer_t, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    if (q4k_split_get((q4k_split *) tensor->extra, data, offset, size) != Q4K_OK)
+        GGML_ABORT("Q4K_B200: get_tensor on split tensor %s failed (cudaError %d)", tensor->name, q4k_last_cuda_error());
+}
+
+void split_buffer_clear(ggml_backend_buffer_t, uint8_t) {}
+
+const ggml_backend_buffer_i split_buffer_iface = {
+    /* .free_buffer   = */ split_buffer_free,
+    /* .get_base      = */ split_buffer_get_base,
+    /* .init_tensor   = */ split_buffer_init_tensor,
+    /* .memset_tensor = */ nullptr,
+    /* .set_tensor    = */ split_buffer_set_tensor,
+    /* .get_tensor    = */ split_buffer_get_tensor,
+    /* .cpy_tensor    = */ nullptr,
+    /* .clear         = */ split_buffer_clear,
+    /* .reset         = */ nullptr,
+};
+
+ggml_backend_buffer_t split_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    return ggml_backend_buffer_init(buft, split_buffer_iface, new split_buffer_context, size);
+}
+size_t split_buft_get_alignment(ggml_backend_buffer_type_t) { return Q4K_TENSOR_ALIGN; }
+size_t split_buft_get_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * tensor) { return ggml_nbytes(tensor); }
+bool split_buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i split_buft_iface = {
+    /* .get_name       = */ split_buft_get_name,
+    /* .alloc_buffer   = */ split_buft_alloc_buffer,
+    /* .get_alignment  = */ split_buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ split_buft_get_alloc_size,
+    /* .is_host        = */ split_buft_is_host,
+};
+
+// the proc L/src/llama-model.cpp looks up (ggml_backend_split_buffer_type_t: (int main_device, const float * tensor_split));
+// one buffer type object per distinct (main device, shares), kept for the life of the process like the registry itself
+ggml_backend_buffer_type_t split_buffer_type(int main_device, const float * tensor_split) {
+    static std::mutex mutex;
+    static std::vector<ggml_backend_buffer_type *> made;
+    std::lock_guard<std::mutex> lock(mutex);
+    const size_t n = devices().size();
+    if (n == 0 || main_device < 0 || (size_t) main_device >= n) return nullptr;
+    std::vector<float> fr(n, 0.0f);
+    if (tensor_split) for (size_t i = 0; i < n; ++i) fr[i] = tensor_split[i];
+    for (auto * b : made) {
+        auto * c = (split_buft_context *) b->context;
+        if (c->main_device == main_device && c->fractions == fr) return b;
+    }
+    auto * c = new split_buft_context;
+    c->main_device = main_device;
+    c->fractions = fr;
+    c->name = "Q4K_B200_Split";
+    made.push_back(new ggml_backend_buffer_type{split_buft_iface, &devices()[main_device], c});
+    return made.back();
+}
+
 }  // namespace
 
 namespace {
@@ -274,7 +379,12 @@ bool mul_mat_supported(const ggml_tensor * op) {
     // broadcast of src0 over dims 2 / 3 as in ggml_compute_forward_mul_mat (ggml-cpu.c:1142-1143)
     if (src0->ne[2] == 0 || src0->ne[3] == 0) return false;
     if (src1->ne[2] % src0->ne[2] != 0 || src1->ne[3] % src0->ne[3] != 0) return false;
-    // the weights must live in this backend's memory: tensor->data is a device pointer here
+    // the weights must live in this backend's memory: tensor->data is a device pointer here — or in its split buffer type
+    // (rows dealt to the devices, shards in ->extra): whole 2-D matrices only, activations and result dense
+    if (tensor_is_split(src0)) {
+        return src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && ggml_is_contiguous(src0) && !src0->view_src &&
+               op->nb[1] >= (size_t) src0->ne[1] * sizeof(float);
+    }
     if (src0->buffer && !buft_is_ours(src0->buffer->buft)) return false;
     return true;
 }
@@ -288,6 +398,15 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node, bool reus
     if (M == 0 || N == 0 || ne12 == 0 || ne13 == 0) return GGML_STATUS_SUCCESS;
 
     const bool q6 = src0->type == GGML_TYPE_Q6_K;
+    if (tensor_is_split(src0)) {           // row-sharded weights: every device runs its rows, results land in this device's dst
+        const int rc = q4k_split_mul_mat((q4k_split *) src0->extra, q6 ? 1 : 0, K, (const float *) src1->data, N, (int64_t) src1->nb[1],
+                                         (float *) node->data, (int64_t) node->nb[1], ctx->dev->cuda_device, ctx->stream);
+        if (rc != Q4K_OK) {
+            GGML_LOG_ERROR("Q4K_B200: q4k_split_mul_mat(%s) failed: rc=%d cudaError=%d\n", node->name, rc, q4k_last_cuda_error());
+            return GGML_STATUS_FAILED;
+        }
+        return GGML_STATUS_SUCCESS;
+    }
     const size_t need = q6 ? q6k_mul_mat_workspace_bytes(K, N) : q4k_mul_mat_workspace_bytes(K, N);
     if (need > ctx->workspace_bytes) {
         GGML_LOG_ERROR("Q4K_B200: %s: workspace was not sized before the launches (need %zu, have %zu)\n", node->name, need, ctx->workspace_bytes);
@@ -322,6 +441,7 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node, bool reus
 bool groupable(const ggml_tensor * node) {
     const ggml_tensor * src0 = node->src[0];
     const ggml_tensor * src1 = node->src[1];
+    if (tensor_is_split(src0)) return false;
     return src0->type == GGML_TYPE_Q4_K && src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src1->ne[1] >= 1 &&
            src1->ne[1] <= Q4K_GEMV_MAX_N && src0->ne[1] > 0 && node->nb[1] == (size_t) src0->ne[1] * sizeof(float);
 }
@@ -588,7 +708,7 @@ ggml_status enqueue_nodes(backend_context * ctx, ggml_cgraph * cgraph) {
                 if (fused > 0) { last_quantized = nullptr; break; }
                 // consecutive prefill mul_mats on one src1 (q/k/v, gate/up) share the quantized copy of the activations
                 const ggml_tensor * s0 = node->src[0], * s1 = node->src[1];
-                const bool plain2d = s0->ne[2] == 1 && s0->ne[3] == 1 && s1->ne[2] == 1 && s1->ne[3] == 1;
+                const bool plain2d = s0->ne[2] == 1 && s0->ne[3] == 1 && s1->ne[2] == 1 && s1->ne[3] == 1 && !tensor_is_split(s0);
                 const bool reuse = plain2d && s0->type == GGML_TYPE_Q4_K && last_quantized == s1 && last_quantized_data == s1->data;
                 const ggml_status st = compute_mul_mat(ctx, node, reuse);
                 if (st != GGML_STATUS_SUCCESS) return st;
@@ -656,6 +776,8 @@ ggml_status compute_cached(backend_context * ctx, ggml_cgraph * cgraph, graph_ca
     int launching = 0;
     graph_signature(cgraph, sig, launching);
     if (launching < 2) return enqueue_nodes(ctx, cgraph);                    // nothing to amortise
+    for (int i = 0; i < cgraph->n_nodes; ++i)                                // shard launches fork onto other devices' streams with events:
+        if (cgraph->nodes[i]->op == GGML_OP_MUL_MAT && tensor_is_split(cgraph->nodes[i]->src[0])) return enqueue_nodes(ctx, cgraph);   // plain launches
     const bool same = sig == cache.sig;
     if (same && cache.graph && cache.ws_generation == ctx->ws_generation) {
         if (q4k_graph_launch(cache.graph, ctx->stream) == Q4K_OK) return GGML_STATUS_SUCCESS;
@@ -802,6 +924,9 @@ bool cheap_ops_enabled() {
 }
 
 bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    if (op->op != GGML_OP_MUL_MAT)       // a split tensor has no address: only MUL_MAT (as src0) knows how to read it
+        for (int k = 0; k < GGML_MAX_SRC; ++k) if (tensor_is_split(op->src[k])) return false;
+    if (op->op == GGML_OP_MUL_MAT && tensor_is_split(op->src[1])) return false;
     switch (op->op) {
         // test-backend-ops asks about every tensor of the context, leaves and views included
         // (L/tests/test-backend-ops.cpp:1152-1161); these are no-ops for a backend
@@ -831,6 +956,7 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
 }
 
 bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    if (buft_is_split(buft)) return true;              // any of our devices can be the main device of a split matrix
     return buft_is_ours(buft) && buft->context == dev->context;
 }
 
@@ -859,7 +985,10 @@ ggml_backend_dev_t reg_get_device(ggml_backend_reg_t, size_t index) {
     GGML_ASSERT(index < devices().size());
     return &devices()[index];
 }
-void * reg_get_proc_address(ggml_backend_reg_t, const char *) { return nullptr; }
+void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
+    if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;
+    return nullptr;
+}
 
 const ggml_backend_reg_i reg_iface = {
     /* .get_name         = */ reg_get_name,

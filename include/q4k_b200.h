@@ -339,6 +339,26 @@ int q4k_op_get_rows_f32(const float *src_dev, int64_t src_row_stride_bytes, int6
 int q4k_op_rope(const float *x_dev, const int64_t *x_nb, const int32_t *pos_dev, const float *freq_factors_dev, float *dst_dev,
                 const int64_t *dst_nb, const int64_t *ne, int n_dims, int neox, float theta_scale, float freq_scale, float ext_factor,
                 float attn_factor, float corr_lo, float corr_hi, void *stream);
+/* ---- row-sharded weights over the GPUs of one process (SURVEY.md §8e inside the boundary) ---------------------------------
+ * What ggml-cuda's split buffer does for --split-mode row (L/ggml/src/ggml-cuda/ggml-cuda.cu:774-787 get_row_split, :795-1000
+ * the split buffer type / buffer, :1672 and :1720 the src1 / dst peer copies), for this path: a weight matrix is dealt to the
+ * devices in contiguous row ranges (multiples of row_granule; fractions[i] = share of device i, NULL or all zero = equal) when it
+ * is uploaded; q4k_split_mul_mat launches every device's shard on that device's own stream — the shard kernels read the
+ * activations from the main device's memory and write their rows straight into the main device's dst over NVLink peer
+ * mappings — and joins them into main_stream with events.  x_dev / dst_dev live on main_device; dst = N columns of M floats.
+ * Results equal the single-GPU results bit for bit.  The plugin's split buffer type ("ggml_backend_split_buffer_type",
+ * looked up by L/src/llama-model.cpp:382-394 for -sm row) sits on these.  Not thread-safe per device: shards of all split
+ * matrices share one stream and one workspace per device. */
+typedef struct q4k_split q4k_split;
+q4k_split *q4k_split_create(const int *devices, int n_devices, const float *fractions, int64_t M, int64_t row_bytes, int row_granule);
+void q4k_split_destroy(q4k_split *s);
+int  q4k_split_parts(const q4k_split *s);
+int  q4k_split_range(const q4k_split *s, int part, int *device, int64_t *row_low, int64_t *row_high);
+/* buffer_i.set_tensor / get_tensor on a split tensor: bytes [offset, offset + size) of the full row-major matrix; synchronous */
+int  q4k_split_set(q4k_split *s, const void *host, size_t offset, size_t size);
+int  q4k_split_get(q4k_split *s, void *host, size_t offset, size_t size);
+int  q4k_split_mul_mat(q4k_split *s, int q6k, int64_t K, const float *x_dev, int64_t N, int64_t x_row_stride_bytes, float *dst_dev,
+                       int64_t dst_col_stride_bytes, int main_device, void *main_stream);
 
 #ifdef __cplusplus
 }

@@ -72,6 +72,8 @@ def libs():
         shim.ref_mul_mat_set_ex.argtypes = [i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i32), i64, i32, i32, i32, i32,
                                             C.POINTER(C.c_double), C.POINTER(C.c_double)]
         shim.ref_mul_mat_set_ex.restype = i32
+        shim.ref_plugin_split_mul_mat.argtypes = [C.c_char_p, i32, vp, i64, i64, vp, i64, vp, vp, vp, C.POINTER(i32)]
+        shim.ref_plugin_split_mul_mat.restype = i32
         shim.ref_cheap_ops.argtypes = [vp, vp, vp, vp, vp, i64, i64, C.c_float, i32, vp, vp, vp]
         shim.ref_cheap_ops.restype = i32
         f32 = C.c_float
@@ -352,3 +354,26 @@ def rope(x: np.ndarray, pos: np.ndarray, n_dims: int, mode: int = 0, freq_base: 
     if rc != 0:
         raise RuntimeError(f"ref_rope failed: {rc}")
     return y
+
+
+def plugin_split_mul_mat(plugin_path: str, w: np.ndarray, x: np.ndarray, q6k: bool = False, tensor_split=None):
+    """ggml_mul_mat with the weights in the plugin's split (row-sharded) buffer type, as llama.cpp's --split-mode row places
+    them (oracle/ref_shim.c: ref_plugin_split_mul_mat).  -> (y [N, M], weights read back through get_tensor, device count)."""
+    *_, shim = libs()
+    blk = 210 if q6k else Q4K_BLOCK
+    M, K = w.shape[0], w.shape[1] // blk * QK_K
+    x = np.ascontiguousarray(x, np.float32)
+    w = np.ascontiguousarray(w)
+    y = np.empty((x.shape[0], M), np.float32)
+    wb = np.empty_like(w)
+    nd = C.c_int32(0)
+    ts = None
+    if tensor_split is not None:
+        ts = np.zeros(16, np.float32)
+        ts[:len(tensor_split)] = tensor_split
+    rc = shim.ref_plugin_split_mul_mat(plugin_path.encode(), int(q6k), w.ctypes.data_as(C.c_void_p), M, K, x.ctypes.data_as(C.c_void_p),
+                                       x.shape[0], y.ctypes.data_as(C.c_void_p), ts.ctypes.data_as(C.c_void_p) if ts is not None else None,
+                                       wb.ctypes.data_as(C.c_void_p), C.byref(nd))
+    if rc != 0:
+        raise RuntimeError(f"ref_plugin_split_mul_mat failed: rc={rc}")
+    return y, wb, nd.value

@@ -486,3 +486,52 @@ int ref_rope(const float *x, const int32_t *pos, int64_t ne0, int64_t n_heads, i
     ggml_backend_free(cpu);
     return rc;
 }
+
+/* --split-mode row through the plugin: the weights in the buffer type the registry's "ggml_backend_split_buffer_type" proc
+ * returns (L/src/llama-model.cpp:375-401), activations and result in the main device's default buffer, one ggml_mul_mat node
+ * computed by the main device's backend.  w_back (optional) receives the weights read back through get_tensor (the gather).
+ * q6k: 0 = Q4_K weights, 1 = Q6_K.  Returns 0, or -20 if the plugin has no such proc, -21 no buffer type, -12 not supported. */
+typedef ggml_backend_buffer_type_t (*split_buft_fn)(int main_device, const float *tensor_split);
+int ref_plugin_split_mul_mat(const char *path, int q6k, const void *w, int64_t M, int64_t K, const float *x, int64_t N, float *dst,
+                             const float *tensor_split, void *w_back, int *n_devices) {
+    static ggml_backend_reg_t reg = NULL;
+    if (!reg) reg = ggml_backend_load(path);
+    if (!reg) return -10;
+    if (n_devices) *n_devices = (int)ggml_backend_reg_dev_count(reg);
+    if (ggml_backend_reg_dev_count(reg) < 1) return -11;
+    split_buft_fn fn = (split_buft_fn)ggml_backend_reg_get_proc_address(reg, "ggml_backend_split_buffer_type");
+    if (!fn) return -20;
+    ggml_backend_buffer_type_t sbuft = fn(0, tensor_split);
+    if (!sbuft) return -21;
+    ggml_backend_dev_t dev = ggml_backend_reg_dev_get(reg, 0);
+    ggml_backend_t be = ggml_backend_dev_init(dev, NULL);
+    if (!be) return -13;
+    struct ggml_init_params ip = { ggml_tensor_overhead() * 8 + ggml_graph_overhead(), NULL, true };
+    struct ggml_context *cw = ggml_init(ip), *cc = ggml_init(ip);
+    struct ggml_tensor *tw = ggml_new_tensor_2d(cw, q6k ? GGML_TYPE_Q6_K : GGML_TYPE_Q4_K, K, M);
+    ggml_backend_buffer_t bw = ggml_backend_alloc_ctx_tensors_from_buft(cw, sbuft);
+    struct ggml_tensor *tx = ggml_new_tensor_2d(cc, GGML_TYPE_F32, K, N);
+    struct ggml_tensor *ty = ggml_mul_mat(cc, tw, tx);
+    struct ggml_cgraph *gf = ggml_new_graph(cc);
+    ggml_build_forward_expand(gf, ty);
+    ggml_backend_buffer_t bc = ggml_backend_alloc_ctx_tensors(cc, be);
+    int rc = (bw && bc) ? 0 : -2;
+    if (rc == 0 && !(ggml_backend_dev_supports_buft(dev, sbuft) && ggml_backend_dev_supports_op(dev, ty))) rc = -12;
+    if (rc == 0) {
+        ggml_backend_tensor_set(tw, w, 0, ggml_nbytes(tw));
+        ggml_backend_tensor_set(tx, x, 0, ggml_nbytes(tx));
+        for (int it = 0; it < 2 && rc == 0; ++it)          /* twice: the second compute reuses streams, events and workspaces */
+            if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -3;
+        if (rc == 0) {
+            ggml_backend_synchronize(be);
+            ggml_backend_tensor_get(ty, dst, 0, ggml_nbytes(ty));
+            if (w_back) ggml_backend_tensor_get(tw, w_back, 0, ggml_nbytes(tw));
+        }
+    }
+    if (bc) ggml_backend_buffer_free(bc);
+    if (bw) ggml_backend_buffer_free(bw);
+    ggml_free(cc);
+    ggml_free(cw);
+    ggml_backend_free(be);
+    return rc;
+}
