@@ -250,7 +250,24 @@ class MatSet:
         """One step with inputs resident in HBM: quantize + GEMV per mul_mat on the current stream."""
         st = self.torch.cuda.current_stream().cuda_stream
         ws, wsn, N, f = self.ws.data_ptr(), self.ws.numel(), self.N, self.lib.q4k_mul_mat
-        for it in self.items:
+        import ctypes as C
+        i = 0
+        while i < len(self.items):
+            it = self.items[i]
+            j = i + 1
+            while j < len(self.items) and j - i < 4 and self.items[j]["reuse"]:
+                j += 1
+            if j - i > 1:          # prefill mul_mats of a layer on one activation tensor (q/k/v, gate/up): one quantizer pass, one GEMM launch
+                g = self.items[i:j]
+                n = len(g)
+                rc = self.lib.q4k_mul_mat_group_ws(n, (C.c_void_p * n)(*[x["w"].data_ptr() for x in g]), (C.c_int64 * n)(*[x["M"] for x in g]), it["K"],
+                                                   it["w"].stride(0), it["x"].data_ptr(), N, it["K"] * 4,
+                                                   (C.c_void_p * n)(*[x["dst"].data_ptr() for x in g]), ws, wsn, st)
+                if rc != 0:
+                    raise RuntimeError(f"q4k_mul_mat_group_ws rc={rc} cuda={self.lib.q4k_last_cuda_error()}")
+                i = j
+                continue
+            i = j
             if it["reuse"]:
                 rc = self.lib.q4k_mul_mat_reuse(it["w"].data_ptr(), it["M"], it["K"], it["w"].stride(0), N, it["dst"].data_ptr(), it["M"] * 4, ws, wsn, st)
             else:
@@ -672,6 +689,47 @@ def full_token_extra(torch, q4k, device, steps, no_cpu, peak):
 
 
 # ------------------------------------------------------------------------------------------------ main
+def llama_bench_obj(reps=2):
+    """The reference's own headline tool (README.md:189-193: llama-bench -p 512 -n 128) on a random-init TinyLlama-1.1B Q4_K_M
+    GGUF (tools/make_gguf.py): on the host cores alone, and with the plugin loaded through GGML_BACKEND_PATH (-ngl 99; the KV cache
+    and the attention stay on the host: -nkvo 1).  Scheduler-bound end-to-end figures of the whole llama graph, not kernel numbers."""
+    import subprocess
+    import tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "llama-bench")
+    plugin = os.path.join(ROOT, "ggml-neon-opt_b200", "lib", "libggml-q4k-b200.so")
+    if not (os.path.exists(exe) and os.path.exists(plugin)):
+        return {"unavailable": "oracle/_ref/llama-bench or the plugin is not built"}
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import make_gguf
+        gguf = os.path.join(tempfile.gettempdir(), "q4k_b200_tinyllama_random_q4_k_m.gguf")
+        info = make_gguf.write(gguf)
+        nt = min(host_threads(), 16)
+        out = {"model": "tinyllama-1.1b-shaped, random-init, Q4_K_M tensor types, no_vocab", "gguf_bytes": info["file_bytes"], "threads": nt,
+               "command": "llama-bench -p 512 -n 128", "unit": "tokens/s"}
+
+        def run(extra, env):
+            r = subprocess.run([exe, "-m", gguf, "-p", "512", "-n", "128", "-t", str(nt), "-r", str(reps), "-o", "json"] + extra,
+                               capture_output=True, text=True, timeout=300, env=env, cwd=os.path.dirname(exe))
+            try:
+                rows = json.loads(r.stdout[r.stdout.index("["):])
+                return {("pp512" if row["n_prompt"] else "tg128"): round(row["avg_ts"], 2) for row in rows}
+            except Exception:
+                return {"unavailable": (r.stderr or r.stdout).strip().splitlines()[-2:]}
+
+        base_env = {k: v for k, v in os.environ.items() if k not in ("GGML_BACKEND_PATH", "Q4K_B200_CHEAP_OPS")}
+        out["cpu_reference"] = run([], base_env)
+        out["plugin"] = dict(run(["-ngl", "99", "-nkvo", "1", "-sm", "none"], dict(base_env, GGML_BACKEND_PATH=plugin)),
+                             flags="-ngl 99 -nkvo 1 -sm none", graph_splits_per_token=46)
+        out["plugin_mul_mat_only"] = dict(run(["-ngl", "99", "-nkvo", "1", "-sm", "none", "-p", "0"],
+                                              dict(base_env, GGML_BACKEND_PATH=plugin, Q4K_B200_CHEAP_OPS="0")),
+                                          flags="Q4K_B200_CHEAP_OPS=0", graph_splits_per_token=266)
+        os.remove(gguf)
+        return out
+    except Exception as e:                   # a reported extra, never a dependency of the GPU path
+        return {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     if not torch.cuda.is_available():
@@ -833,7 +891,8 @@ def run_ours(args, rank, world, local_rank):
     achieved = per_slot_bytes / per_slot_us / 1e3
     tr = NCU_TRAFFIC.get(args.workload) if world == 1 else None
     if args.workload == "ffn70b":
-        kernel = ("gemv_q4k_tma_kernel<1, 2> (large-matrix decode launch; K = 28672 activations quantized by quantize_q8_K_kernel in front of it)" if world == 1
+        kernel = ("gemv_q4k_tma_kernel<1, 2> for 28672x8192 (large-matrix decode launch, quantizer fused) and gemv_q4k_n1s_kernel for 8192x28672 "
+                  "(activations quantized once by quantize_q8_K_n1s_kernel and streamed next to the weights)" if world == 1
                   else "gemv_q4k_mma_kernel / gemv_q4k_tma_kernel on this rank's row shard + the cross-GPU exchange")
     else:
         kernel = "gemv_q4k_mma_kernel (Q8_K quantizer fused into the launch)"
@@ -876,9 +935,11 @@ def run_ours(args, rank, world, local_rank):
             line["decode_token"] = decode_token_obj(torch, q4k_b200, device, max(args.steps, 20), args.warmup, peak, peak_src, args.no_cpu)
         line["shapes"] = gemv_shape_table(torch, q4k_b200, device,
                                           [(5632, 2048, 1), (4096, 14336, 1), (14336, 4096, 1), (4096, 14336, 8), (14336, 4096, 8),
-                                           (28672, 8192, 1), (8192, 28672, 1), (28672, 8192, 8), (8192, 28672, 8)], peak, cpu=cpu)
+                                           (4096, 14336, 16), (28672, 8192, 1), (8192, 28672, 1), (28672, 8192, 8), (8192, 28672, 8), (28672, 8192, 16)], peak, cpu=cpu)
         line["prefill"] = gemm_table(torch, q4k_b200, device, peak, int8_peaks((clk or {}).get("sm_mhz")), cpu=cpu)
         line["full_q4_k_m_token"] = full_token_extra(torch, q4k_b200, device, max(args.steps, 20), args.no_cpu, peak)
+        if cpu:
+            line["llama_bench"] = llama_bench_obj()
         line["q6k_shapes"] = q6k_shape_table(torch, q4k_b200, device, [(2048, 5632, 1), (32000, 2048, 1), (14336, 4096, 1), (28672, 8192, 1)], peak)
     print(json.dumps(line), flush=True)
     if dist is not None:

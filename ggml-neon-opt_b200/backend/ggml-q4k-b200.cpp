@@ -437,13 +437,14 @@ ggml_status compute_mul_mat(backend_context * ctx, ggml_tensor * node, bool reus
     return GGML_STATUS_SUCCESS;
 }
 
-// A decode-shaped mul_mat that can share a launch with its neighbours: plain 2-D, batch <= 8, dense rows on both sides.
+// A mul_mat that can share a launch with its neighbours: plain 2-D, dense rows on both sides (decode batches: one launch of the
+// decode kernel; prefill batches: one GEMM launch over all row tiles; q4k_mul_mat_group_ws declines the sizes in between).
 bool groupable(const ggml_tensor * node) {
     const ggml_tensor * src0 = node->src[0];
     const ggml_tensor * src1 = node->src[1];
     if (tensor_is_split(src0)) return false;
     return src0->type == GGML_TYPE_Q4_K && src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src1->ne[1] >= 1 &&
-           src1->ne[1] <= Q4K_GEMV_MAX_N && src0->ne[1] > 0 && node->nb[1] == (size_t) src0->ne[1] * sizeof(float);
+           src0->ne[1] > 0 && node->nb[1] == (size_t) src0->ne[1] * sizeof(float);
 }
 
 bool is_noop(const ggml_tensor * node);
@@ -500,11 +501,11 @@ int try_fused_group(backend_context * ctx, ggml_cgraph * cgraph, int i, std::vec
     }
     if (n < 2) return 0;
     const ggml_tensor * src1 = first->src[1];
-    const int rc = q4k_mul_mat_group(n, w, M, first->src[0]->ne[0], (int64_t) first->src[0]->nb[1], x, src1->ne[1], (int64_t) src1->nb[1], dst,
-                                     ctx->stream);
+    const int rc = q4k_mul_mat_group_ws(n, w, M, first->src[0]->ne[0], (int64_t) first->src[0]->nb[1], x[0], src1->ne[1], (int64_t) src1->nb[1], dst,
+                                        ctx->workspace, ctx->workspace_bytes, ctx->stream);
     if (rc == Q4K_ERR_UNSUPPORTED) return 0;
     if (rc != Q4K_OK) {
-        GGML_LOG_ERROR("Q4K_B200: q4k_mul_mat_group(%s ...) failed: rc=%d cudaError=%d\n", first->name, rc, q4k_last_cuda_error());
+        GGML_LOG_ERROR("Q4K_B200: q4k_mul_mat_group_ws(%s ...) failed: rc=%d cudaError=%d\n", first->name, rc, q4k_last_cuda_error());
         return -1;
     }
     for (int k = 0; k < n; ++k) done[idx[k]] = 1;

@@ -355,6 +355,33 @@ int q4k_mul_mat_group(int n_mats, const void *const *w_dev, const int64_t *M, in
     return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
 }
 
+int q4k_mul_mat_group_ws(int n_mats, const void *const *w_dev, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes, float *const *dst_dev,
+                         void *workspace_dev, size_t workspace_bytes, void *stream) {
+    if (n_mats < 1 || n_mats > 4 || N < 1) return Q4K_ERR_UNSUPPORTED;
+    if (K <= 0 || K % Q4K_QK_K != 0 || !w_dev || !M || !x_dev || !dst_dev) return Q4K_ERR_BAD_SHAPE;
+    if (N <= Q4K_GEMV_MAX_N) {                      // decode: the group launch of the decode kernel (quantizer fused in)
+        const float *xs[4] = {x_dev, x_dev, x_dev, x_dev};
+        return q4k_mul_mat_group(n_mats, w_dev, M, K, w_row_stride_bytes, xs, N, x_row_stride_bytes, dst_dev, stream);
+    }
+    if (N <= knobs().midn_max || !knobs().gemm_enabled) return Q4K_ERR_UNSUPPORTED;      // the batched decode kernel takes one matrix at a time
+    const int64_t nb = K / Q4K_QK_K;
+    if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15)) return Q4K_ERR_BAD_SHAPE;
+    if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (!workspace_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
+    if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
+    int64_t strides[4];
+    for (int i = 0; i < n_mats; ++i) {
+        if (M[i] < 0) return Q4K_ERR_BAD_SHAPE;
+        if (!w_dev[i] || !dst_dev[i] || !aligned16(w_dev[i])) return Q4K_ERR_BAD_POINTER;
+        strides[i] = M[i] * 4;
+    }
+    const cudaError_t e = launch_gemm_q4k_f32_group(n_mats, w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev, strides,
+                                                    workspace_dev, (cudaStream_t)stream);
+    if (e == cudaErrorNotSupported) return Q4K_ERR_UNSUPPORTED;
+    return e == cudaSuccess ? Q4K_OK : cuda_fail(e);
+}
+
 int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, size_t bx, const void *vy_dev, size_t by, int nrc) {
     (void)bs; (void)bx; (void)by;
     if (nrc != 1) return Q4K_ERR_UNSUPPORTED;      // the reference asserts nrc == 1 on x86 (arch/x86/quants.c:1743)

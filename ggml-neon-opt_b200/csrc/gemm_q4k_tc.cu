@@ -82,16 +82,20 @@ __device__ long long g_gemm_trace[16][256];
 #endif
 
 struct GemmParams {
-    CUtensorMap wmap;       // the weights as a 2-D byte tensor [M][row stride], box = 128 rows x one block_q4_K (144 bytes)
-    const uint8_t *w;
-    int64_t M, w_stride;
+    // up to four weight matrices with the same K that read the SAME activations (attn_q / attn_k / attn_v, ffn_gate / ffn_up) in one
+    // launch: row tiles are numbered through all of them, tend[i] = row tiles of matrices 0..i
+    CUtensorMap wmap[4];    // the weights as 2-D byte tensors [M][row stride], box = 128 rows x one block_q4_K (144 bytes)
+    const uint8_t *w[4];
+    int64_t M[4];
+    float *dst[4];
+    int64_t dst_stride[4];  // floats between dst columns
+    int tend[4], nmat;
+    int64_t w_stride;
     int nb;
     const int8_t *xq;       // int8 activations, pre-tiled: [column tile][superblock][half][16 KB canonical B tile]
     const float *xd;        // [nb][Nld]
     const uint8_t *bmin;    // fp16 mins tiles: [column tile][superblock][4 KB canonical tile: 128 columns x (bh[8] | bl[8])]
     int64_t N, Nld;
-    float *dst;
-    int64_t dst_stride;     // floats between dst columns
     int ksplit;             // CTAs along K per output tile (gridDim.z); 1 = the tile's CTA owns all of K
     int *flags;             // ksplit > 1: one zero-initialised turnstile word per output tile
     int32_t *dump_sumi, *dump_summ;   // DUMP instantiation (parity): [(n*M + m)*nb + b] = the integers the epilogue read from TMEM
@@ -257,9 +261,9 @@ __device__ __forceinline__ void tma_g2s_2d(uint32_t dst, const CUtensorMap *map,
 // `step` counts from the CTA's first superblock kb0 (split-K); slots are indexed by the local step / superblock.
 // The raw weights do not depend on the quantizer kernel in front of this one (programmatic dependent launch), the B and
 // mins tiles do: the loader issues the first raw boxes before griddepcontrol.wait.
-__device__ __forceinline__ void loader_issue_raw(const GemmParams &p, uint32_t smem0, uint32_t rawfull, int m0, int kb, int kb0) {
+__device__ __forceinline__ void loader_issue_raw(const CUtensorMap *wmap, uint32_t smem0, uint32_t rawfull, int m0, int kb, int kb0) {
     mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
-    tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, &p.wmap, (kb0 + kb) * BLK_Q4K, m0, rawfull);
+    tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, wmap, (kb0 + kb) * BLK_Q4K, m0, rawfull);
 }
 __device__ __forceinline__ void loader_issue_act(const GemmParams &p, uint32_t smem0, uint32_t full, int64_t ntile, int step, int kb0) {
     const int kb = step >> 1, hh = step & 1, gkb = kb0 + kb;
@@ -324,7 +328,13 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     auto rawfull_bar = [&](int s) { return bar0 + 8u * (2 * B_SLOTS + 4 + s); };   // [RAW_SLOTS] loader -> producers
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+    int mat = 0;                                          // which matrix of a grouped launch this row tile belongs to
+    while (mat + 1 < p.nmat && (int)blockIdx.y >= p.tend[mat]) ++mat;
+    const CUtensorMap *wmap = &p.wmap[mat];
+    const uint8_t *w_base = p.w[mat];
+    const int64_t M_mat = p.M[mat], dst_stride = p.dst_stride[mat];
+    float *dst_mat = p.dst[mat];
+    const int64_t m0 = (int64_t)((int)blockIdx.y - (mat ? p.tend[mat - 1] : 0)) * BM, n0 = (int64_t)blockIdx.x * BN;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     // split-K: CTA z of a tile owns superblocks [kb0, kb0 + nb) (balanced contiguous parts)
     const int kb0 = (int)((int64_t)p.nb * blockIdx.z / p.ksplit);
@@ -352,7 +362,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         // ===================== epilogue: TMEM -> registers, per-superblock fp32 scales =====================
         const int qd = warp & 3, g = warp >> 2;                               // lane quadrant, column group (16 wide, both halves)
         const int64_t row = m0 + 32 * qd + lane;
-        const uint8_t *wrow = p.w + (row < p.M ? row : p.M - 1) * p.w_stride;
+        const uint8_t *wrow = w_base + (row < M_mat ? row : M_mat - 1) * p.w_stride;
         float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 64;   // [buffer][half 0: 16 | half 1: 16], private to the warp
         int64_t ncl = n0 + HALF_N * (lane >> 4) + EPI_COLS * g + (lane & 15); // the column whose d_x this lane fetches
         if (ncl >= p.N) ncl = p.N - 1;
@@ -404,13 +414,13 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                         const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
                         if constexpr (DUMP) {
                             const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 8 * c8 + 2 * i;
-                            if (row < p.M && n < p.N) {
-                                p.dump_sumi[(n * p.M + row) * p.nb + kb0 + kb] = s0;
-                                p.dump_summ[(n * p.M + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
+                            if (row < M_mat && n < p.N) {
+                                p.dump_sumi[(n * M_mat + row) * p.nb + kb0 + kb] = s0;
+                                p.dump_summ[(n * M_mat + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
                             }
-                            if (row < p.M && n + 1 < p.N) {
-                                p.dump_sumi[((n + 1) * p.M + row) * p.nb + kb0 + kb] = s1;
-                                p.dump_summ[((n + 1) * p.M + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
+                            if (row < M_mat && n + 1 < p.N) {
+                                p.dump_sumi[((n + 1) * M_mat + row) * p.nb + kb0 + kb] = s1;
+                                p.dump_summ[((n + 1) * M_mat + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
                             }
                         }
                         uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
@@ -461,7 +471,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
             }
             __syncwarp();
         }
-        if (row < p.M) {
+        if (row < M_mat) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (h >= nh) break;
@@ -470,7 +480,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
 #pragma unroll
                     for (int c = 0; c < EPI_COLS; ++c) {
                         const int64_t n = n0 + HALF_N * h + EPI_COLS * g + c;
-                        prev[c] = n < p.N ? __ldcg(p.dst + n * p.dst_stride + row) : 0.0f;
+                        prev[c] = n < p.N ? __ldcg(dst_mat + n * dst_stride + row) : 0.0f;
                     }
 #pragma unroll
                     for (int c = 0; c < EPI_COLS / 2; ++c) {
@@ -484,8 +494,8 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                     const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 2 * c;
                     float a0, a1;
                     unpack2(acc[h][c], a0, a1);
-                    if (n < p.N) p.dst[n * p.dst_stride + row] = a0;
-                    if (n + 1 < p.N) p.dst[(n + 1) * p.dst_stride + row] = a1;
+                    if (n < p.N) dst_mat[n * dst_stride + row] = a0;
+                    if (n + 1 < p.N) dst_mat[(n + 1) * dst_stride + row] = a1;
                 }
             }
         }
@@ -582,13 +592,13 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         // ===================== loader (one thread): TMA copies, up to B_SLOTS steps ahead of the tensor core =====================
         const uint32_t smem0 = smem_addr(smem);
         const int pre = min(nb, RAW_SLOTS);                     // raw boxes that can go out before the quantizer has finished
-        for (int kb = 0; kb < pre; ++kb) loader_issue_raw(p, smem0, rawfull_bar(kb % RAW_SLOTS), (int)m0, kb, kb0);
+        for (int kb = 0; kb < pre; ++kb) loader_issue_raw(wmap, smem0, rawfull_bar(kb % RAW_SLOTS), (int)m0, kb, kb0);
         asm volatile("griddepcontrol.wait;" ::: "memory");      // the activation tiles come from the kernel in front of this one
         for (int step = 0; step < nsteps; ++step) {
             // slot reuse: the MMAs of step - B_SLOTS have completed, so its B slot is free; every producer had arrived for that
             // step, so the raw slot of superblock step / 2 - RAW_SLOTS has been read; the mins slots likewise
             if (step >= B_SLOTS) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar(step % B_SLOTS), (uint32_t)(((step - B_SLOTS) / B_SLOTS) & 1));
-            if ((step & 1) == 0 && (step >> 1) >= pre) loader_issue_raw(p, smem0, rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, step >> 1, kb0);
+            if ((step & 1) == 0 && (step >> 1) >= pre) loader_issue_raw(wmap, smem0, rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, step >> 1, kb0);
             loader_issue_act(p, smem0, full_bar(step % B_SLOTS), (int64_t)blockIdx.x, step, kb0);
         }
     }
@@ -701,18 +711,35 @@ static cudaError_t make_weight_map(CUtensorMap *map, const void *w, int64_t M, i
 
 // F32 activations: quantize into `workspace` (gemm_workspace_bytes), then the tensor-core GEMM.  Two launches.
 // x == nullptr: the quantized copy in `workspace` is reused (q4k_mul_mat_reuse) — one launch.
-cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
-                                const float *x, int64_t N, int64_t x_row_stride_bytes,
-                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream,
-                                const IntDump *dump) {
-    if (M == 0 || N == 0) return cudaSuccess;
+// nmat (1..4) matrices with the same K that read the same activations go out as ONE GEMM launch: the row tiles of all of them
+// form one grid (TinyLlama's attn_k / attn_v are 2 row tiles each — 8 CTAs on 148 SMs when launched alone, and a launch costs
+// ~20 us whatever its size).  dst[i]: N columns of M[i] floats, column stride dst_col_stride_bytes[i].
+cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                                      const float *x, int64_t N, int64_t x_row_stride_bytes, float *const *dst,
+                                      const int64_t *dst_col_stride_bytes, void *workspace, cudaStream_t stream, const IntDump *dump) {
+    if (nmat < 1 || nmat > 4 || (dump && nmat != 1)) return cudaErrorInvalidValue;
+    if (N == 0) return cudaSuccess;
     const int64_t nb = K / QK_K;
     const int64_t ntiles = (N + BN - 1) / BN;             // whole column tiles; columns >= N hold stale bytes, never stored
     int8_t *qs = reinterpret_cast<int8_t *>(workspace);
     uint8_t *bmin = reinterpret_cast<uint8_t *>(qs + ntiles * BN * K);
     float *d = reinterpret_cast<float *>(bmin + ntiles * nb * MIN_TILE_BYTES);
     int *flags = reinterpret_cast<int *>(reinterpret_cast<char *>(d) + ((nb * (size_t)N * 4 + 255) & ~(size_t)255));
-    const int64_t mtiles = (M + BM - 1) / BM;
+    GemmParams p;
+    int64_t mtiles = 0;
+    p.nmat = 0;
+    for (int i = 0; i < 4; ++i) { p.w[i] = nullptr; p.M[i] = 0; p.dst[i] = nullptr; p.dst_stride[i] = 0; p.tend[i] = 0; }
+    for (int i = 0; i < nmat; ++i) {
+        if (M[i] == 0) continue;                          // an empty matrix has no tiles
+        const int k = p.nmat++;
+        const cudaError_t em = make_weight_map(&p.wmap[k], w[i], M[i], nb, w_row_stride_bytes);
+        if (em != cudaSuccess) return em;
+        p.w[k] = (const uint8_t *)w[i]; p.M[k] = M[i]; p.dst[k] = dst[i]; p.dst_stride[k] = dst_col_stride_bytes[i] / 4;
+        mtiles += (M[i] + BM - 1) / BM;
+        p.tend[k] = (int)mtiles;
+    }
+    if (p.nmat == 0) return cudaSuccess;
+    if (mtiles > 65535) return cudaErrorNotSupported;
     const int ksplit = choose_ksplit(ntiles * mtiles, nb);
     const int64_t total = nb * N;
     cudaLaunchAttribute pdl_attr[1];
@@ -735,13 +762,8 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
         count_launch();
         if (e != cudaSuccess) return e;
     }
-
-    GemmParams p;
-    e = make_weight_map(&p.wmap, w, M, nb, w_row_stride_bytes);
-    if (e != cudaSuccess) return e;
-    p.w = (const uint8_t *)w; p.M = M; p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
+    p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
     p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
-    p.dst = dst; p.dst_stride = dst_col_stride_bytes / 4;
     p.ksplit = ksplit; p.flags = flags;
     p.dump_sumi = dump ? dump->sumi : nullptr; p.dump_summ = dump ? dump->summ : nullptr;
     auto kern = dump ? gemm_q4k_tc_kernel<true> : gemm_q4k_tc_kernel<false>;
@@ -758,6 +780,15 @@ cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
     return e;
+}
+
+cudaError_t launch_gemm_q4k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
+                                const float *x, int64_t N, int64_t x_row_stride_bytes,
+                                float *dst, int64_t dst_col_stride_bytes, void *workspace, cudaStream_t stream,
+                                const IntDump *dump) {
+    const void *wv[1] = {w};
+    float *dv[1] = {dst};
+    return launch_gemm_q4k_f32_group(1, wv, &M, K, w_row_stride_bytes, x, N, x_row_stride_bytes, dv, &dst_col_stride_bytes, workspace, stream, dump);
 }
 
 }  // namespace q4k

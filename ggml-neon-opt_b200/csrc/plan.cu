@@ -71,7 +71,7 @@ int enqueue_range(q4k_plan *p, cudaStream_t st, size_t begin, size_t end) {
     while (i < end) {
         const q4k_plan::Item &a = p->items[i];
         size_t j = i + 1;
-        if (a.N <= Q4K_GEMV_MAX_N && !a.q6) {
+        if (!a.q6) {          // decode: the group launch of the decode kernel; prefill: one GEMM launch over all row tiles
             while (j < end && j - i < 4 && !p->items[j].q6 && p->items[j].input_id == a.input_id && p->items[j].K == a.K &&
                    p->items[j].N == a.N && p->items[j].w_stride == a.w_stride) ++j;
         }
@@ -87,7 +87,7 @@ int enqueue_range(q4k_plan *p, cudaStream_t st, size_t begin, size_t end) {
                 w[k - i] = p->items[k].w; M[k - i] = p->items[k].M; xs[k - i] = x;
                 dst[k - i] = reinterpret_cast<float *>(p->out_dev + p->items[k].out_off);
             }
-            rc = q4k_mul_mat_group((int)(j - i), w, M, a.K, a.w_stride, xs, a.N, a.K * 4, dst, st);
+            rc = q4k_mul_mat_group_ws((int)(j - i), w, M, a.K, a.w_stride, x, a.N, a.K * 4, dst, p->ws_dev, p->ws_bytes, st);
             if (rc != Q4K_OK && rc != Q4K_ERR_UNSUPPORTED) return rc;
         }
         if (rc == Q4K_ERR_UNSUPPORTED) {            // not fusable (or a single mul_mat): one q4k_mul_mat each

@@ -96,6 +96,12 @@ size_t n1s_workspace_bytes(int64_t K);
 cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x, float *dst,
                                 void *workspace, bool pdl, cudaStream_t stream);
 
+// up to four matrices with the same K on ONE activation tensor as one GEMM launch (one quantizer pass, one grid over all row tiles)
+cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                                      const float *x, int64_t N, int64_t x_row_stride_bytes, float *const *dst,
+                                      const int64_t *dst_col_stride_bytes, void *workspace, cudaStream_t stream,
+                                      const IntDump *dump = nullptr);
+
 // Q6_K decode GEMV (gemv_q6k.cu), 1 <= N <= 8; dump != nullptr also writes the per-superblock integer sums
 cudaError_t launch_gemv_q6k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                             const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,

@@ -5,9 +5,9 @@ streams.  There is no CPU or eager fallback: if the CUDA library is missing or n
 present, the ops raise.
 """
 from .lib import (op_rms_norm, op_binary, op_swiglu, op_get_rows, op_rope, debug_reset, debug_set, Q4K_BLOCK, Q6K_BLOCK, debug_partials_q6k, mul_mat_q6k, mul_mat_q6k_q8, Q8K_BLOCK, QK_K, GraphPlan, HostPlan, Q4KError, abi_version, build_info, mul_mat_dump, DUMP_DISPATCH, DUMP_TENSOR_PIPE, DUMP_BULK, DUMP_BULK_EXACT, DUMP_BIG, DUMP_GEMM, DUMP_WIDE,
-                  kernel_launches, lib_path, load, mul_mat, mul_mat_group, mul_mat_host, mul_mat_q8, quantize_q8_K,
+                  kernel_launches, lib_path, load, mul_mat, mul_mat_group, mul_mat_group_ws, mul_mat_host, mul_mat_q8, quantize_q8_K,
                   vec_dot_q4_K_q8_K, workspace_bytes)
 
 __all__ = ["op_rms_norm", "op_binary", "op_swiglu", "op_get_rows", "op_rope", "debug_reset", "debug_set", "Q6K_BLOCK", "debug_partials_q6k", "mul_mat_q6k", "mul_mat_q6k_q8", "GraphPlan", "HostPlan", "Q4K_BLOCK", "Q8K_BLOCK", "QK_K", "Q4KError", "abi_version", "build_info", "mul_mat_dump", "DUMP_DISPATCH", "DUMP_TENSOR_PIPE", "DUMP_BULK", "DUMP_BULK_EXACT", "DUMP_BIG", "DUMP_GEMM", "DUMP_WIDE",
-           "kernel_launches", "lib_path", "load", "mul_mat", "mul_mat_group", "mul_mat_host", "mul_mat_q8", "quantize_q8_K",
+           "kernel_launches", "lib_path", "load", "mul_mat", "mul_mat_group", "mul_mat_group_ws", "mul_mat_host", "mul_mat_q8", "quantize_q8_K",
            "vec_dot_q4_K_q8_K", "workspace_bytes"]

@@ -64,6 +64,7 @@ def load():
         L.q4k_mul_mat_peers_ws.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp, sz, vp]
         L.q4k_mul_mat_peers_sync.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i32, i64, i64, vp, sz, vp, i32, i32, vp, vp, vp]
         L.q4k_mul_mat_group.argtypes = [i32, vp, vp, i64, i64, vp, i64, i64, vp, vp]
+        L.q4k_mul_mat_group_ws.argtypes = [i32, vp, vp, i64, i64, vp, i64, i64, vp, vp, sz, vp]
         L.q4k_plan_create.argtypes = [i32]
         L.q4k_plan_create.restype = vp
         L.q4k_plan_add_mul_mat.argtypes = [vp, vp, i64, i64, i64, i64, i32]
@@ -408,6 +409,26 @@ def mul_mat_group(ws, xs, outs=None):
         _check("q4k_mul_mat_group", load().q4k_mul_mat_group(n, vpa(*[w.data_ptr() for w in ws]), i64a(*[w.shape[0] for w in ws]), K,
                                                              ws[0].stride(0), vpa(*[x.data_ptr() for x in xs]), N, K * 4,
                                                              vpa(*[o.data_ptr() for o in outs]), _stream()))
+    return outs
+
+
+def mul_mat_group_ws(ws, x, workspace=None):
+    """q4k_mul_mat_group_ws: up to 4 Q4_K matrices with the same K on ONE activation tensor x [N, K], any N outside 9..32
+    (decode group launch, or one quantizer pass + one GEMM launch over all row tiles) -> list of float32 [N, M_i]."""
+    n = len(ws)
+    N, K = x.shape
+    for w in ws:
+        _dev_u8(w, "w")
+        if w.shape[1] != K // QK_K * Q4K_BLOCK or w.stride(0) != ws[0].stride(0):
+            raise ValueError("shape mismatch between w and x")
+    outs = [torch.empty((N, w.shape[0]), dtype=torch.float32, device=w.device) for w in ws]
+    if workspace is None:
+        workspace = torch.empty(max(workspace_bytes(K, N), 16), dtype=torch.uint8, device=x.device)
+    vpa, i64a = C.c_void_p * n, C.c_int64 * n
+    with torch.cuda.device(ws[0].device):
+        _check("q4k_mul_mat_group_ws", load().q4k_mul_mat_group_ws(n, vpa(*[w.data_ptr() for w in ws]), i64a(*[w.shape[0] for w in ws]), K,
+                                                                   ws[0].stride(0), x.data_ptr(), N, K * 4, vpa(*[o.data_ptr() for o in outs]),
+                                                                   workspace.data_ptr(), workspace.numel(), _stream()))
     return outs
 
 

@@ -174,6 +174,14 @@ int q4k_peer_signal_wait(void *const *flags_peers, int world, int rank, void *ep
  * copy.  Results are dense: dst_dev[i] is [N][M[i]].  Q4K_ERR_UNSUPPORTED when the shapes do not fit one launch. */
 int q4k_mul_mat_group(int n_mats, const void *const *w_dev, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
                       const float *const *x_dev, int64_t N, int64_t x_row_stride_bytes, float *const *dst_dev, void *stream);
+/* The same for ANY batch size when every matrix reads the SAME activation tensor x_dev: N <= 8 -> q4k_mul_mat_group; N above the
+ * batched decode kernel's range (32) -> one quantizer pass + ONE tensor-core GEMM launch whose grid covers the row tiles of all
+ * matrices (a prefill launch costs ~20 us whatever its size: TinyLlama's attn_k / attn_v are 8 CTAs each when launched alone);
+ * in between Q4K_ERR_UNSUPPORTED (run them one by one).  dst_dev[i] = dense [N][M_i].  Results equal the one-by-one results bit
+ * for bit unless the grouped grid changes the GEMM's split-K choice (then within 1e-5). */
+int q4k_mul_mat_group_ws(int n_mats, const void *const *w_dev, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
+                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes, float *const *dst_dev,
+                         void *workspace_dev, size_t workspace_bytes, void *stream);
 
 /* Graph plans — the backend_i.graph_plan_create / graph_plan_compute pair of L/ggml/src/ggml-backend-impl.h:100-108 for
  * this path: a fixed sequence of Q4_K mul_mats (one decode token's worth, say) recorded once, replayed as ONE CUDA

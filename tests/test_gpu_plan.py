@@ -205,3 +205,27 @@ def test_plan_default_dispatch_batch_4(q4k, order):
     for i, (w, (name, _, _, iid)) in enumerate(zip(ws, shapes)):
         check(f"plan N=4 {name}", plan.output(i).cpu().numpy(), w.cpu().numpy(), xs[iid])
     plan.close()
+
+
+@pytest.mark.parametrize("Ms,K,N", [((2048, 256, 256), 2048, 130), ((640, 640), 1024, 512), ((100, 37, 300, 5), 512, 64), ((96,), 512, 200)])
+def test_prefill_group_is_one_gemm_launch_with_the_single_launch_bits(q4k, order, Ms, K, N):
+    """attn_q / attn_k / attn_v (or ffn_gate / ffn_up) at prefill batch sizes: one quantizer pass + ONE GEMM launch whose grid covers the
+    row tiles of all matrices (ragged last tiles of each included); every output carries the bits of its own q4k_mul_mat."""
+    if order == "exact":
+        pytest.skip("float-order modes concern the decode kernels")
+    ws = [t(make_weights(M, K, seed=31 + i)) for i, M in enumerate(Ms)]
+    x = t(make_acts(N, K, seed=8))
+    n0 = q4k.kernel_launches()
+    outs = q4k.mul_mat_group_ws(ws, x)
+    assert q4k.kernel_launches() - n0 == 2
+    for w, o in zip(ws, outs):
+        assert np.array_equal(bits(o), bits(q4k.mul_mat(w, x)))
+
+
+def test_group_ws_declines_the_batched_decode_range(q4k):
+    ws = [t(make_weights(64, 512, seed=1)), t(make_weights(32, 512, seed=2))]
+    with pytest.raises(q4k.Q4KError) as e:
+        q4k.mul_mat_group_ws(ws, t(make_acts(16, 512)))
+    assert e.value.rc == -5
+    outs = q4k.mul_mat_group_ws(ws, t(make_acts(4, 512)))                 # decode sizes: the decode group launch
+    assert len(outs) == 2 and outs[0].shape == (4, 64)
