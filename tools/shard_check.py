@@ -15,6 +15,10 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "ggml-neon-opt_b200"))
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 import q4k_b200  # noqa: E402
+
+# the row-sharded path runs the decode kernel (gemv_q4k_mma.cu / gemv_q4k_tma.cu) for every N <= 8; the single-GPU comparison must
+# use the same kernel family (q4k_mul_mat alone hands N >= 3 to the batched decode kernel, whose float association differs)
+q4k_b200.debug_set("wide_min", 9)
 from q4k_b200.shard import RowShardedQ4K, shard_rows  # noqa: E402
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
