@@ -234,17 +234,11 @@ static cudaError_t launch_n(const GemvParams &p, cudaStream_t stream) {
 
 template <bool EXACT>
 static cudaError_t launch_e(int N, const GemvParams &p, cudaStream_t stream) {
-    switch (N) {
-        case 1: return launch_n<1, EXACT>(p, stream);
-        case 2: return launch_n<2, EXACT>(p, stream);
-        case 3: return launch_n<3, EXACT>(p, stream);
-        case 4: return launch_n<4, EXACT>(p, stream);
-        case 5: return launch_n<5, EXACT>(p, stream);
-        case 6: return launch_n<6, EXACT>(p, stream);
-        case 7: return launch_n<7, EXACT>(p, stream);
-        case 8: return launch_n<8, EXACT>(p, stream);
-        default: return cudaErrorInvalidValue;
-    }
+    // Only N == 1 is instantiated: this direct-load kernel is the last resort for ONE activation row too long for a shared-memory
+    // residency (K > ~200 000); wider batches are halved by the caller until they fit the staged kernels or reach one column.
+    // (The other seven batch sizes were 98 more kernels in the library for no reachable launch.)
+    if (N == 1) return launch_n<1, EXACT>(p, stream);
+    return cudaErrorNotSupported;
 }
 
 cudaError_t launch_gemv_q4k_q8k(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes,

@@ -21,3 +21,7 @@ for CHEAP in 0 1; do
   grep -E "graph splits|graph nodes|model buffer size|compute buffer size" gpurun_out/r2_llama_bench_verbose_$CHEAP.txt | sort | uniq -c >> $OUT
 done
 tail -45 $OUT
+# thread sweep of the plugin run, decode only: the host side of a token is ~45 tiny CPU graph computes, so fewer threads can be faster
+echo "== plugin, decode only, host thread sweep" >> $OUT
+(cd oracle/_ref && Q4K_B200_CHEAP_OPS=1 timeout 600 ./llama-bench -m $GG -p 0 -n 128 -t 1,2,4,8 -ngl 99 -nkvo 1 -sm none -r 2) 2>&1 | grep -E "tg128|threads" >> $OUT
+tail -8 $OUT
