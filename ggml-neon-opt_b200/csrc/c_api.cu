@@ -152,7 +152,9 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
         if (workspace_bytes < q4k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
         if (!workspace_dev) return Q4K_ERR_BAD_POINTER;
         // (the bit-exact AVX2 order, when asked for, exists only in the decode kernel)
-        const bool wide = N >= knobs().wide_min && N <= knobs().midn_max && !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N));
+        // (two columns of a short K stay on the decode kernel: 5632 x 2048 N = 2 4.5 vs 5.1 us; from K = 4096 the batched kernel wins)
+        const bool wide = N >= knobs().wide_min && N <= knobs().midn_max && !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N)) &&
+                          !(N == 2 && K < 4096);
         // one column of a matrix that streams tens of MB or has a long K: quantize once, stream the activations next to the weights
         // (gemv_q4k_n1s.cu; the bits of the decode kernel below)
         // Measured (profiles/r2_n1s_sweep.txt): wins where K is long and there are enough tiles for every SM — 4096 x 14336
@@ -413,7 +415,7 @@ int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_
     cudaStream_t st = (cudaStream_t)stream;
     // which product kernel: the one q4k_mul_mat would launch for this shape, unless the caller names one
     const bool wide = kernel == Q4K_DUMP_WIDE || (kernel == Q4K_DUMP_DISPATCH && N >= knobs().wide_min && N <= knobs().midn_max &&
-                                                  !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N)));
+                                                  !(N <= Q4K_GEMV_MAX_N && gemv_exact_for((int)N)) && !(N == 2 && K < 4096));
     if (wide) {
         if (!p_dev || !aligned16(workspace_dev)) return Q4K_ERR_BAD_POINTER;
         const IntDump d{p_dev, sumi_dev, summ_dev};

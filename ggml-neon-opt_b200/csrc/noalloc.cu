@@ -57,7 +57,7 @@ extern "C" int q4k_mul_mat_noalloc(const void *w_dev, int64_t M, int64_t K, int6
                                    float *dst_dev, int64_t dst_col_stride_bytes, void *stream) {
     if (M < 0 || N < 0 || K < 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
     if (N > Q4K_GEMV_MAX_N) return Q4K_ERR_STATIC_LIMIT;                       // decode shapes only
-    const size_t need = q4k_mul_mat_workspace_bytes(K, N);                     // N * K/256 * 292 for N <= 2; the eight-column staged copy of gemv_q4k_wide.cu for N = 3..8
+    const size_t need = q4k_mul_mat_workspace_bytes(K, N);                     // N * K/256 * 292 for N = 1; the eight-column staged copy of gemv_q4k_wide.cu for N = 2..8
     if (need > (size_t)Q4K_NOALLOC_SCRATCH_BYTES) return Q4K_ERR_STATIC_LIMIT;
     if (M == 0 || N == 0) return Q4K_OK;
     void *scratch = nullptr;

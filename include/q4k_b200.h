@@ -94,8 +94,8 @@ int q4k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
  * that forbid cudaMalloc): the same decode mul_mat (N <= 8) with the Q8_K scratch in a static device array inside the library
  * instead of a caller-supplied workspace.  No counterpart in the reference.
  *   - calls no cudaMalloc / cudaFree / allocating library routine; inputs and outputs are still the caller's;
- *   - limit: N <= 8 and q4k_mul_mat_workspace_bytes(K, N) <= Q4K_NOALLOC_SCRATCH_BYTES (1 MiB: K up to 112640 for N = 3..8, whose
- *     staged Q8_K copy is padded to eight columns, 9.25 B per K; 292 B per 256 activations for N <= 2), else Q4K_ERR_STATIC_LIMIT; every GPU that loads the library holds the 1 MiB until the process exits;
+ *   - limit: N <= 8 and q4k_mul_mat_workspace_bytes(K, N) <= Q4K_NOALLOC_SCRATCH_BYTES (1 MiB: K up to 112640 for N = 2..8 (N = 2: from K = 4096), whose
+ *     staged Q8_K copy is padded to eight columns, 9.25 B per K; 292 B per 256 activations for N = 1), else Q4K_ERR_STATIC_LIMIT; every GPU that loads the library holds the 1 MiB until the process exits;
  *   - runs on the CURRENT device; results are bit-identical to q4k_mul_mat on the same inputs;
  *   - all calls on a device share the one array, which keeps the last call's contents (nothing in it needs to start at zero:
  *     the quantizer overwrites every block the decode kernel reads).  Calls that OVERLAP on the GPU (two streams, two threads

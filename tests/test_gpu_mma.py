@@ -18,7 +18,7 @@ def fast_order(q4k):
     q4k.debug_set("wide_min", 9)            # N = 3..8 through THIS kernel (q4k_mul_mat hands them to gemv_q4k_wide.cu by default)
     yield lib
     lib.q4k_debug_set_gemv_order(0)
-    q4k.debug_set("wide_min", 3)
+    q4k.debug_set("wide_min", 2)
 
 
 @pytest.mark.parametrize("M,K,N", [(5632, 2048, 1), (2048, 5632, 1), (100, 512, 1), (1, 256, 1), (17, 2560, 1), (64, 14336, 1),

@@ -26,7 +26,7 @@ def order(request, q4k):
     q4k.debug_set("wide_min", 9)        # N = 3..8 stay on the decode kernels here: q4k_mul_mat alone would hand them to gemv_q4k_wide.cu
     yield request.param
     lib.q4k_debug_set_gemv_order(0)
-    q4k.debug_set("wide_min", 3)
+    q4k.debug_set("wide_min", 2)
 
 
 @pytest.mark.parametrize("Ms,K,N", [((2048, 256, 256), 2048, 1), ((5632, 5632), 2048, 1), ((37, 4, 129, 1), 512, 2),
@@ -189,7 +189,7 @@ def test_plan_default_dispatch_batch_4(q4k, order):
     from parity_util import check
     if order == "exact":
         pytest.skip("the AVX2-order mode keeps N <= 8 on the decode kernel")
-    q4k.debug_set("wide_min", 3)
+    q4k.debug_set("wide_min", 2)
     N = 4
     shapes, ws = _layer(q4k, N, seed=3)
     plan = q4k.GraphPlan(0)

@@ -14,22 +14,24 @@ def t(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
 
-@pytest.mark.parametrize("M,K", [(64, 512), (300, 1024), (37, 2304), (16, 256), (1, 256), (129, 2560), (9600, 512)])
-@pytest.mark.parametrize("N", [3, 5, 8, 9, 12, 13, 16, 17, 24, 32, 33, 40, 64])
+@pytest.mark.parametrize("M,K", [(64, 512), (300, 1024), (37, 2304), (16, 256), (1, 256), (129, 2560), (9600, 512), (40, 4096)])
+@pytest.mark.parametrize("N", [2, 3, 5, 8, 9, 12, 13, 16, 17, 24, 32, 33, 40, 64])
 def test_wide_within_tolerance_and_integers_exact(q4k, M, K, N):
     """ragged tiles (M % 16, odd tile counts), ragged rounds (K / 256 % 4), padded column tiles (N % 8), two column groups (N > 32)"""
     from oracle import port
     w, x = make_weights(M, K, seed=M + N), make_acts(N, K, seed=K + N)
     n0 = q4k.kernel_launches()
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
-    if N <= 32:
+    if N == 2 and K < 4096:       # two columns of a short K stay on the decode kernel (one launch, quantizer fused)
+        assert q4k.kernel_launches() - n0 == 1
+    elif N <= 32:
         assert q4k.kernel_launches() - n0 == 2                       # quantizer + batched decode kernel: not the GEMM, not decode passes
     if N <= 32:           # (above 32 columns q4k_mul_mat is the GEMM: tests/test_gpu_parity.py; this kernel's result is checked below)
         check(f"batched decode {M}x{K} N={N}", got, w, x)
     dst, p, si, sm = q4k.mul_mat_dump(t(w), t(x), q4k.DUMP_WIDE)         # N > 32: two column groups through the same kernel
     rp, rsi, rsm = port.partials_matrix(w, port.quantize_q8_K(x))
     assert np.array_equal(p.cpu().numpy(), rp) and np.array_equal(si.cpu().numpy(), rsi) and np.array_equal(sm.cpu().numpy(), rsm)
-    if N <= 32:
+    if N <= 32 and not (N == 2 and K < 4096):
         assert np.array_equal(dst.cpu().numpy().view(np.uint32), got.view(np.uint32))     # the dump build computes the same floats
     else:
         check(f"batched decode (two column groups) {M}x{K} N={N}", dst.cpu().numpy(), w, x)

@@ -34,7 +34,7 @@ for M, K in shapes:
             q4k_b200.debug_set("wide_min", wmin)
             res[name] = round(graph_time_us(lambda i: q4k_b200.mul_mat(w[i % copies], x, dst, ws), per_graph=max(copies, 10), replays=5), 1)
         q4k_b200.debug_set("midn_max", 64)
-        q4k_b200.debug_set("wide_min", 3)
+        q4k_b200.debug_set("wide_min", 2)
         algo = wbytes + N * K * 4 + M * N * 4
         gbs = algo / res["wide"] / 1e3
         print(json.dumps(dict(M=M, K=K, N=N, us_wide=res["wide"], us_before=res["before"], gbs=round(gbs, 1), frac_measured=round(gbs / PEAK, 3))), flush=True)
