@@ -56,7 +56,10 @@ extern "C" {
 
 size_t q6k_mul_mat_workspace_bytes(int64_t K, int64_t N) {
     if (K <= 0 || N <= 0 || K % Q4K_QK_K != 0) return 0;
-    return (size_t)N * (size_t)(K / Q4K_QK_K) * Q4K_BLOCK_Q8K;
+    size_t need = (size_t)N * (size_t)(K / Q4K_QK_K) * Q4K_BLOCK_Q8K;
+    const int gmin = knobs().q6k_gemm_min;
+    if (gmin > 0 && N >= gmin) need = need > gemm_q6k_workspace_bytes(K, N) ? need : gemm_q6k_workspace_bytes(K, N);
+    return need;
 }
 
 int q6k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
@@ -97,10 +100,36 @@ int q6k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_by
     }
     if (workspace_bytes < q6k_mul_mat_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
     if (!workspace_dev || (reinterpret_cast<uintptr_t>(workspace_dev) & 3u)) return Q4K_ERR_BAD_POINTER;
+    if (knobs().q6k_gemm_min > 0 && N >= knobs().q6k_gemm_min) {                 // prefill: tcgen05 kind::f16 GEMM
+        if (reinterpret_cast<uintptr_t>(workspace_dev) & 15u) return Q4K_ERR_BAD_POINTER;
+        const cudaError_t eg = launch_gemm_q6k_f32(w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev,
+                                                   dst_col_stride_bytes, workspace_dev, st);
+        if (eg != cudaErrorNotSupported) return eg == cudaSuccess ? Q4K_OK : note_cuda_error(eg);
+    }
     const cudaError_t e = launch_quantize_q8_K(x_dev, workspace_dev, K, N, x_row_stride_bytes, st);
     if (e != cudaSuccess) return note_cuda_error(e);
     return run_columns(w_dev, M, K, w_row_stride_bytes, workspace_dev, nullptr, N, nb * Q4K_BLOCK_Q8K, dst_dev,
                        dst_col_stride_bytes, nullptr, st);
+}
+
+/* parity tooling: the prefill GEMM's DUMP instantiation at any N — sumi[(n*M + m)*nb + b] = the integers its epilogue read from
+ * tensor memory, dst = the product floats */
+int q6k_mul_mat_dump(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x_dev, int64_t N,
+                     int64_t x_row_stride_bytes, int32_t *sumi_dev, float *dst_dev, void *workspace_dev, size_t workspace_bytes,
+                     void *stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || K % Q4K_QK_K != 0) return Q4K_ERR_BAD_SHAPE;
+    if (!w_dev || !x_dev || !sumi_dev || !dst_dev || !workspace_dev) return Q4K_ERR_BAD_POINTER;
+    if (check_w(w_dev, K / Q4K_QK_K, w_row_stride_bytes)) return Q4K_ERR_BAD_SHAPE;
+    if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev) || !aligned16(workspace_dev)) return Q4K_ERR_BAD_SHAPE;
+    if (workspace_bytes < gemm_q6k_workspace_bytes(K, N)) return Q4K_ERR_WORKSPACE;
+    const cudaError_t e = launch_gemm_q6k_f32(w_dev, M, K, w_row_stride_bytes, x_dev, N, x_row_stride_bytes, dst_dev, M * 4,
+                                              workspace_dev, (cudaStream_t)stream, sumi_dev);
+    return e == cudaSuccess ? Q4K_OK : e == cudaErrorNotSupported ? Q4K_ERR_UNSUPPORTED : note_cuda_error(e);
+}
+
+size_t q6k_gemm_workspace_bytes(int64_t K, int64_t N) {
+    if (K <= 0 || N <= 0 || K % Q4K_QK_K != 0) return 0;
+    return gemm_q6k_workspace_bytes(K, N);
 }
 
 int q6k_debug_partials(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,

@@ -42,6 +42,7 @@
 #include <cuda.h>
 #include <cuda_fp16.h>
 
+#include "gemm_tc_ptx.cuh"
 #include "q4k_common.cuh"
 #include "q4k_kernels.h"
 
@@ -49,8 +50,7 @@ namespace q4k {
 
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 128;          // CTA tile; BK = K bytes per pipeline step (half a superblock)
-constexpr int HALF_N = 64;                            // columns per accumulator half / per MMA
+constexpr int BN = 128, BK = 128;                    // CTA tile (BM = 128 rows); BK = K bytes per pipeline step (half a superblock)
 constexpr int B_SLOTS = 6;                            // activation tiles, written in place by cp.async
 constexpr int RAW_SLOTS = 4;                          // raw block_q4_K bytes of 128 rows x one superblock
 constexpr int AM_SLOTS = 2, BMIN_SLOTS = 4;           // mins operands (per superblock): weights side, activation side
@@ -70,7 +70,6 @@ constexpr int TMEM_COLS = 512;
 constexpr uint32_t TM_HI = 0, TM_LO = 128, TM_MIN = 256, TM_A = 384;   // TMEM column of each region
 constexpr uint32_t TM_A_STAGE = 64, TM_A_TILE = 32;  // columns per A stage (hi + lo) and per tile (128 bytes of K)
 constexpr uint32_t SBO_BYTES = 8 * BK;                // int8 B tile: next 8-column group of core matrices
-constexpr uint32_t LBO_BYTES = 128;                   // next 16-byte K chunk (core matrices of a group are contiguous)
 constexpr uint32_t MIN_SBO_BYTES = 256;               // mins tiles: 8 rows x (2 chunks x 16 bytes)
 constexpr size_t FLAG_BYTES = 1024;                   // split-K turnstiles at the end of the workspace (<= 148 tiles x 4 bytes)
 
@@ -100,159 +99,6 @@ struct GemmParams {
     int *flags;             // ksplit > 1: one zero-initialised turnstile word per output tile
     int32_t *dump_sumi, *dump_summ;   // DUMP instantiation (parity): [(n*M + m)*nb + b] = the integers the epilogue read from TMEM
 };
-
-__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-}
-// long waits (a whole pipeline stage): polling steals issue slots from the warps that work.  mode 1: hardware suspend
-// hint, mode 2: nanosleep backoff, 0: plain polling
-template <int MODE>
-__device__ __forceinline__ void mbar_wait_long(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    if (MODE == 1) {
-        do {
-            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                         : "=r"(done) : "r"(bar), "r"(parity), "r"(100000u) : "memory");
-        } while (!done);
-    } else if (MODE == 2) {
-        for (;;) {
-            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                         : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-            if (done) break;
-            __nanosleep(32);
-        }
-    } else {
-        mbar_wait(bar, parity);
-    }
-}
-#ifndef Q4K_GEMM_WAIT
-#define Q4K_GEMM_WAIT 1
-#endif
-// the two waits of the accumulator hand-off (tensor core <-> epilogue) are on the critical path: a suspended wait wakes up
-// ~300 cycles after the arrive (measured), plain polling does not
-#ifndef Q4K_GEMM_WAIT_TFULL
-#define Q4K_GEMM_WAIT_TFULL 1
-#endif
-#ifndef Q4K_GEMM_WAIT_TEMPTY
-#define Q4K_GEMM_WAIT_TEMPTY 1
-#endif
-#ifndef Q4K_GEMM_DRAIN
-#define Q4K_GEMM_DRAIN 0
-#endif
-__device__ __forceinline__ uint64_t pack2(float a, float b) {
-    uint64_t r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-    return r;
-}
-__device__ __forceinline__ void unpack2(uint64_t v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-// packed fp32 pairs (sm_100): the same round-to-nearest results as two scalar operations, half the issue slots
-__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
-    uint64_t d;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
-__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
-    uint64_t d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-    return d;
-}
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// shared-memory matrix descriptor, K-major, SWIZZLE_NONE ("interleave"): 8-row x 16-byte core matrices,
-// LBO = byte distance between the two 16-byte K chunks of one MMA, SBO = byte distance between 8-row groups
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3ffffu) >> 4);                    // start address, bits [0,14)
-    d |= (uint64_t)(LBO_BYTES >> 4) << 16;                       // leading byte offset, bits [16,30)
-    d |= (uint64_t)(sbo_bytes >> 4) << 32;                       // stride byte offset, bits [32,46)
-    d |= (uint64_t)1 << 46;                                      // descriptor version 1 (sm_100)
-    return d;                                                    // base offset 0, layout type 0 = no swizzle
-}
-
-// instruction descriptors, M = 128, N = 64, both operands K-major.  kind::i8: D = S32, A = B = signed 8-bit;
-// kind::f16: D = F32, A = B = F16
-__device__ __forceinline__ uint32_t umma_idesc(bool f16) {
-    uint32_t d = 0;
-    d |= (f16 ? 1u : 2u) << 4;      // c_format: F32 / S32
-    if (!f16) {
-        d |= 1u << 7;               // a_format: signed 8-bit   (F16 = 0)
-        d |= 1u << 10;              // b_format: signed 8-bit
-    }
-    d |= (uint32_t)(HALF_N >> 3) << 17;
-    d |= (uint32_t)(BM >> 4) << 24;
-    return d;
-}
-
-// D[tmem] (+)= A[tmem] * B[smem]   — the A operand comes from tensor memory: lane = row, 4 int8 per 32-bit column
-__device__ __forceinline__ void umma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// D[tmem] = A[smem] * B[smem], fp16 operands, fp32 accumulator (the mins)
-__device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// arrives on the mbarrier when every MMA issued so far by this thread has completed
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                 : "r"(taddr) : "memory");
-}
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
-                 : "r"(taddr) : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-// 16 consecutive 32-bit columns of the thread's TMEM lane
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
-                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-
-// TMA tile copy of a 2-D box global -> shared (coordinates: c0 = byte inside the row, c1 = row)
-__device__ __forceinline__ void tma_g2s_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
 
 // Global -> shared copies of one pipeline step, issued by one lane of the loader warp:
 //   B tile of `step`        : one 16 KB bulk copy (the activations are stored pre-tiled in exactly the shared-memory order)

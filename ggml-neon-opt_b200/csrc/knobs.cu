@@ -39,6 +39,7 @@ Knobs read_defaults() {
     k.tma_stages = env_int("Q4K_DBG_STAGES", 0);
     k.tma_per_sm = env_int("Q4K_DBG_PER_SM", 0);
     k.gemm_ksplit = env_int("Q4K_DBG_GEMM_KSPLIT", 0);
+    k.q6k_gemm_min = env_int("Q4K_DBG_Q6K_GEMM_MIN", 33);
     k.midn_max = env_int("Q4K_DBG_MIDN_MAX", 32);        // above 32 columns the tcgen05 GEMM wins on the large shapes (profiles/r2_wide_sweep.txt)
     k.wide_min = env_int("Q4K_DBG_WIDE_MIN", 2);       // measured: the batched kernel wins from N = 3 at every shape, at N = 2 from K = 4096 (profiles/r2_wide_sweep.txt)
     k.wide_dbg = env_int("Q4K_DBG_WIDE_DBG", 0);
@@ -92,7 +93,7 @@ int q4k_debug_set(const char *name, int64_t value) {
         {"big_matrix_bytes", nullptr, &k.big_matrix_bytes}, {"pdl", &k.pdl, nullptr}, {"gemv_config", &k.gemv_config, nullptr},
         {"mma_off", &k.mma_off, nullptr}, {"mma_kparts", &k.mma_kparts, nullptr}, {"mma_stages", &k.mma_stages, nullptr},
         {"mma_per_sm", &k.mma_per_sm, nullptr}, {"mma_contig", &k.mma_contig, nullptr}, {"tma_stages", &k.tma_stages, nullptr},
-        {"tma_per_sm", &k.tma_per_sm, nullptr}, {"gemm_ksplit", &k.gemm_ksplit, nullptr}, {"midn_max", &k.midn_max, nullptr}, {"wide_min", &k.wide_min, nullptr}, {"wide_dbg", &k.wide_dbg, nullptr}, {"tma_boxes", &k.tma_boxes, nullptr}, {"n1s_min_bytes", nullptr, &k.n1s_min_bytes}, {"n1s_min_k", nullptr, &k.n1s_min_k},
+        {"tma_per_sm", &k.tma_per_sm, nullptr}, {"gemm_ksplit", &k.gemm_ksplit, nullptr}, {"midn_max", &k.midn_max, nullptr}, {"q6k_gemm_min", &k.q6k_gemm_min, nullptr}, {"wide_min", &k.wide_min, nullptr}, {"wide_dbg", &k.wide_dbg, nullptr}, {"tma_boxes", &k.tma_boxes, nullptr}, {"n1s_min_bytes", nullptr, &k.n1s_min_bytes}, {"n1s_min_k", nullptr, &k.n1s_min_k},
         {"q6k_fuse_limit", nullptr, &k.q6k_fuse_limit}, {"q6k_stages", &k.q6k_stages, nullptr},
     };
     for (auto &t : tab) {

@@ -30,6 +30,7 @@ struct Knobs {
     int     midn_max;           // largest N served by the batched tensor-pipe decode kernel (gemv_q4k_wide.cu); 0 = off
     int64_t q6k_fuse_limit;
     int     q6k_stages;
+    int     q6k_gemm_min;       // smallest N q6k_mul_mat hands to the tcgen05 GEMM (gemm_q6k_tc.cu); 0 = never
 };
 
 Knobs &knobs();                  // the calling thread's settings (initialised from the process defaults)

@@ -107,6 +107,13 @@ cudaError_t launch_gemv_q6k(const void *w, int64_t M, int64_t K, int64_t w_row_s
                             const void *xq, const float *xf, int N, int64_t x_row_stride_bytes,
                             float *dst, int64_t dst_col_stride_bytes, int32_t *dump, bool pdl, cudaStream_t stream);
 
+// Q6_K prefill GEMM on tcgen05 kind::f16 (gemm_q6k_tc.cu): F32 activations, quantized into `workspace` (gemm_q6k_workspace_bytes)
+// as fp16 tiles; dump_sumi != nullptr runs the parity instantiation that also writes every superblock's integer sum
+size_t gemm_q6k_workspace_bytes(int64_t K, int64_t N);
+cudaError_t launch_gemm_q6k_f32(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x, int64_t N,
+                                int64_t x_row_stride_bytes, float *dst, int64_t dst_col_stride_bytes, void *workspace,
+                                cudaStream_t stream, int32_t *dump_sumi = nullptr);
+
 // request handed from the C ABI (q4k_mul_mat_peers_sync) to whichever launcher ends up launching the single decode kernel
 // of the call: the kernel's last CTA then performs the cross-GPU flag exchange itself (gemv_stage.cuh peer_sync_tail)
 struct PeerSyncReq {

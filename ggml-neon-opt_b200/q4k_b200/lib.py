@@ -93,6 +93,9 @@ def load():
         L.q6k_mul_mat.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp, sz, vp]
         L.q6k_mul_mat_q8.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, i64, vp]
         L.q6k_debug_partials.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, vp, vp]
+        L.q6k_gemm_workspace_bytes.argtypes = [i64, i64]
+        L.q6k_gemm_workspace_bytes.restype = sz
+        L.q6k_mul_mat_dump.argtypes = [vp, i64, i64, i64, vp, i64, i64, vp, vp, vp, sz, vp]
         L.q4k_op_rms_norm.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_float, vp]
         L.q4k_op_binary.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.q4k_op_swiglu.argtypes = [vp, i64, vp, i64, vp, i64, i64, i64, vp]
@@ -280,6 +283,20 @@ def debug_partials_q6k(w: torch.Tensor, xq: torch.Tensor):
     with torch.cuda.device(w.device):
         _check("q6k_debug_partials", load().q6k_debug_partials(w.data_ptr(), M, nb * QK_K, w.stride(0), xq.data_ptr(), N,
                                                                xq.stride(0), si.data_ptr(), y.data_ptr(), _stream()))
+    return si, y
+
+
+def mul_mat_q6k_dump(w: torch.Tensor, x: torch.Tensor):
+    """The Q6_K prefill GEMM with its integer dump on (include/q4k_b200.h: q6k_mul_mat_dump): (sumi int32 [N, M, nb], y [N, M])."""
+    M, N, K = w.shape[0], x.shape[0], x.shape[1]
+    nb = K // QK_K
+    si = torch.zeros((N, M, nb), dtype=torch.int32, device=x.device)
+    y = torch.empty((N, M), dtype=torch.float32, device=x.device)
+    nbytes = load().q6k_gemm_workspace_bytes(K, N)
+    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        _check("q6k_mul_mat_dump", load().q6k_mul_mat_dump(w.data_ptr(), M, K, w.stride(0), x.data_ptr(), N, K * 4, si.data_ptr(),
+                                                           y.data_ptr(), ws.data_ptr(), nbytes, _stream()))
     return si, y
 
 

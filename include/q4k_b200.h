@@ -246,7 +246,7 @@ int q4k_mul_mat_dump(int kernel, const void *w_dev, int64_t M, int64_t K, int64_
  * different threads cannot change each other's numerics (SURVEY.md §8b "Threading"); the ggml plugin never calls a setter.
  * q4k_debug_set(name, value): "gemv_order", "fuse_limit", "gemm", "big_matrix_bytes", "pdl", "gemv_config", "mma_off",
  * "mma_kparts", "mma_stages", "mma_per_sm", "mma_contig", "tma_stages", "tma_per_sm", "gemm_ksplit", "midn_max",
- * "q6k_fuse_limit", "q6k_stages" (0 = the launch heuristic chooses); Q4K_ERR_UNSUPPORTED for an unknown name.
+ * "q6k_fuse_limit", "q6k_stages" (0 = the launch heuristic chooses), "q6k_gemm_min"; Q4K_ERR_UNSUPPORTED for an unknown name.
  * q4k_debug_reset(): this thread back to the process defaults. */
 int  q4k_debug_set(const char *name, int64_t value);
 void q4k_debug_reset(void);
@@ -295,8 +295,9 @@ int q4k_mul_mat_host_async(const void *w_dev, int64_t M, int64_t K, int64_t w_ro
  * (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401 with type_traits_cpu[GGML_TYPE_Q6_K], :296-301: vec_dot =
  * ggml_vec_dot_q6_K_q8_K, L/ggml/src/ggml-cpu/arch/x86/quants.c:2129-2218; vec_dot_type = Q8_K).
  * Weights: M rows of K/256 block_q6_K (210 B each); w_dev and w_row_stride_bytes need only be even (210-byte blocks
- * are 2-byte aligned by nature).  Every N is served by the HBM-bound decode kernel, eight columns per pass (there is no
- * tensor-core Q6_K kernel yet).  Integer sums per superblock are exactly the reference's; fp32 within 1e-5. */
+ * are 2-byte aligned by nature).  N <= 32: the HBM-bound decode kernel, eight columns per pass; N > 32 ("q6k_gemm_min"): the
+ * tcgen05 kind::f16 prefill GEMM (csrc/gemm_q6k_tc.cu; workspace 16-byte aligned).  Integer sums per superblock are exactly the
+ * reference's on both; fp32 within 1e-5. */
 size_t q6k_mul_mat_workspace_bytes(int64_t K, int64_t N);
 int q6k_mul_mat(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                 const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
@@ -312,6 +313,13 @@ int q6k_mul_mat_q8(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride
 int q6k_debug_partials(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes,
                        const void *xq_dev, int64_t N, int64_t xq_row_stride_bytes,
                        int32_t *sumi_dev, float *dst_dev, void *stream);
+
+/* parity: the prefill GEMM's dump instantiation at any N >= 1 (F32 activations; workspace >= q6k_gemm_workspace_bytes, 16-byte
+ * aligned): sumi_dev as above = the integers its epilogue read from tensor memory (16 * S_hi + S_lo, gemm_q6k_tc.cu). */
+size_t q6k_gemm_workspace_bytes(int64_t K, int64_t N);
+int q6k_mul_mat_dump(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x_dev, int64_t N,
+                     int64_t x_row_stride_bytes, int32_t *sumi_dev, float *dst_dev, void *workspace_dev, size_t workspace_bytes,
+                     void *stream);
 
 /* ---- adjacent cheap ops of a decoder layer ----------------------------------------------
  * The F32 ops between the weight mul_mats of the reference's llama graph (build_norm / build_ffn / the residual adds,
