@@ -18,18 +18,21 @@
 //   Building the pieces: the 6-bit q lands in the low byte of an fp16 with exponent byte 0x64 (= 1024 + q, one PRMT per
 //   pair), and  fma(1024 + q, s, -1056 s) = (q - 32) s  exactly (the constants 1056 s are multiples of 32 below 2^14).
 // The price: kind::f16 runs at half the int8 rate and the B tile is two bytes per activation; two f16 MMAs per weight make the
-// ceiling a quarter of the dense fp16 rate (~1.1 POPS of useful int ops on B200; DESIGN.md §4.3b).
+// ceiling a quarter of the dense fp16 rate (~1.1 POPS of useful int ops on B200; DESIGN.md §4.5b).
 //
-// CTA = 128 weight rows x 128 activation columns, 26 warps, warp-specialised; a pipeline step is 64 elements of K (4 per
+// CTA = 128 weight rows x 128 activation columns, 27 warps, warp-specialised; a pipeline step is 64 elements of K (4 per
 // superblock):
-//   warps 0-15   epilogue (thread <-> TMEM lane = weight row, column group g = warp / 4 of both 64-column halves) AND the raw
-//                weight feed: Q6_K rows are 210-byte blocks at 2-byte alignment, which neither TMA nor cp.async can copy, so
-//                these warps — idle most of a superblock — load them as aligned words, funnel-shift them into place and store
-//                a 16-byte aligned image (row pitch 240 B: conflict-free 16-byte reads) two superblocks ahead.
-//   warps 16-23  producers: thread <-> weight row (quadrant = warp % 4) and K half (warp / 4) of the step: 6-bit unpack,
-//                two HFMA2 per pair, tcgen05.st into one of four A stages.
-//   warp 24      allocates TMEM; one lane issues the MMAs (M = 128, N = 64, K = 16) and commits to mbarriers.
-//   warp 25      one lane: bulk copies of the activation tiles (pre-tiled by the quantizer in exactly the shared-memory order).
+//   warps 0-15   epilogue (thread <-> TMEM lane = weight row, column group g = warp / 4 of both 64-column halves) AND the
+//                weight feed: Q6_K rows are 210-byte blocks at 2-byte alignment, which neither TMA nor cp.async can lay down
+//                aligned, so these warps — idle most of a superblock — stage the 53 aligned words that cover each row's block
+//                (4-byte cp.async) and, a superblock later, unpack the stage into the image the producers read: 256 six-bit
+//                values as bytes in element order + 16 scales, row pitch 272 B (conflict-free 16-byte reads), two superblocks
+//                ahead of the tensor core.
+//   warps 16-23  producers: thread <-> weight row (quadrant = warp % 4) and K half (warp / 4) of the step: two 16-byte reads,
+//                one PRMT and two HFMA2 per pair of weights, tcgen05.st into one of four A stages.
+//   warps 24-25  allocate TMEM (24); one lane of each issues the MMAs (M = 128, N = 64, K = 16) of ITS column half and commits
+//                to mbarriers.
+//   warp 26      one lane: bulk copies of the activation tiles (pre-tiled by the quantizer in exactly the shared-memory order).
 // TMEM columns: [0,128) S_hi, [128,256) S_lo, [256,512) four A stages x (hi, lo) x 32.
 // K order inside a step (both operands agree, any order is a valid dot product): step (n, hp) of a superblock holds the 64
 // elements 128 n + 32 e + 16 hp + j  (e < 4, j < 16) at slot 16 e + j — the four runs of 16 that one 16-byte piece of ql / qh
@@ -48,19 +51,29 @@ namespace {
 
 constexpr int BLK_Q6K = 210;
 constexpr int BN = 128, KS = 64, SB_STEPS = QK_K / KS;      // column tile; K elements per step; steps per superblock
-constexpr int B_SLOTS = 6, A_STAGES = 4, RAW_SLOTS = 3;
+constexpr int B_SLOTS = 6, A_STAGES = 4, Q_SLOTS = 2;
 constexpr int TILE_BYTES = BN * KS * 2;                      // 16 KB: the fp16 activation tile of a step
-constexpr int RAW_PITCH = 240, RAW_WORDS = 53;               // realigned block image: 53 words (212 B), row pitch 240 B
-constexpr int RAW_SLOT_BYTES = BM * RAW_PITCH;
+constexpr int RAW_PITCH = 240, RAW_WORDS = 53;               // staged raw block: the 53 aligned words that cover its 210 bytes
+constexpr int RAW_STAGE_BYTES = BM * RAW_PITCH;              // one staging area (30 KB): refilled as soon as it has been converted
+constexpr int Q_PITCH = 272, Q_SLOT_BYTES = BM * Q_PITCH;    // unpacked image of a block: 256 six-bit values as bytes | 16 scales; 17 x 16 B: conflict-free 16-byte reads
 constexpr int EPI_WARPS = 16, PROD_WARPS = 8, PROD_THREADS = PROD_WARPS * 32, EPI_COLS = 16;
-constexpr int MMA_WARP = EPI_WARPS + PROD_WARPS, LOAD_WARP = MMA_WARP + 1;
-constexpr int THREADS = (LOAD_WARP + 1) * 32;                // 832
-constexpr int SMEM_B = 0, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES, SMEM_DX = SMEM_RAW + RAW_SLOTS * RAW_SLOT_BYTES;
-constexpr int SMEM_BARS = SMEM_DX + EPI_WARPS * 2 * 32 * 4, SMEM_TOTAL = SMEM_BARS + 256;
+constexpr int MMA_WARP = EPI_WARPS + PROD_WARPS, LOAD_WARP = MMA_WARP + 2;   // two MMA issuers: one per column half
+constexpr int THREADS = (LOAD_WARP + 1) * 32;                // 864
+constexpr int SMEM_B = 0, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES, SMEM_Q = SMEM_RAW + RAW_STAGE_BYTES, SMEM_DX = SMEM_Q + Q_SLOTS * Q_SLOT_BYTES;
+constexpr int SMEM_BARS = SMEM_DX + EPI_WARPS * 2 * 3 * 32 * 4, SMEM_TOTAL = SMEM_BARS + 256;   // DX: d_x and d, three buffers each per warp
 constexpr int TMEM_COLS = 512;
 constexpr uint32_t TM_HI = 0, TM_LO = 128, TM_A = 256, TM_A_STAGE = 64, TM_A_PIECE = 32;
 constexpr uint32_t SBO_BYTES = 8 * KS * 2;                   // next 8-column group of core matrices (1024 B)
 constexpr size_t FLAG_BYTES = 1024;
+#ifndef Q6K_ISSUERS
+#define Q6K_ISSUERS 2
+#endif
+#ifndef Q6K_WAIT_TFULL
+#define Q6K_WAIT_TFULL 1
+#endif
+#ifndef Q6K_WAIT_TEMPTY
+#define Q6K_WAIT_TEMPTY 1
+#endif
 
 struct Gemm6Params {
     const uint8_t *w;
@@ -103,37 +116,75 @@ __device__ __forceinline__ void unpack16(uint32_t *hi, uint32_t *lo, const uint3
     }
 }
 
-__device__ __forceinline__ uint32_t ldg_nc_u32(const void *p) {
-    uint32_t v;
-    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
-    return v;
+// Stage the raw blocks of superblock `gkb` of the tile's 128 rows: warp `warp` (of 16) copies rows 8 warp .. 8 warp + 7 with
+// 4-byte cp.async — the 53 aligned words that cover the row's 210-byte block, staged word j = global word j from
+// (block address & ~3).  What is left of the misalignment is a per-row shift of 0 or 2 bytes (convert_rows).
+// Row offsets are 32-bit (the launcher refuses matrices of 4 GB and more).
+__device__ __forceinline__ void stage_raw(const Gemm6Params &p, uint8_t *stage, int warp, int lane, uint32_t row_off, int gkb) {
+    // one row at a time, lanes = consecutive words
+    uint32_t *dst0 = reinterpret_cast<uint32_t *>(stage + (8 * warp) * RAW_PITCH) + lane;
+    const uint32_t last = (uint32_t)(p.M - 1) * (uint32_t)p.w_stride, step = (uint32_t)p.w_stride;
+    uint32_t off = row_off;                                   // row 8 warp of the tile (warp-uniform), then one stride per row
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p.w) + (uintptr_t)((off < last ? off : last) + (uint32_t)gkb * BLK_Q6K);
+        const uint8_t *src = reinterpret_cast<const uint8_t *>(a & ~(uintptr_t)3) + 4 * lane;
+        const uint32_t dst = smem_addr(dst0) + (uint32_t)i * RAW_PITCH;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+        if (lane + 32 < RAW_WORDS) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 128u), "l"(src + 128) : "memory");
+        off += step;
+    }
 }
 
-// the raw image of superblock `gkb` of the tile's 128 rows: warp `warp` (of 16) realigns rows 8 warp .. 8 warp + 7
-__device__ __forceinline__ void feed_raw(const Gemm6Params &p, uint8_t *slot, int warp, int lane, int64_t m0, int gkb) {
-    uint32_t a0[8], a1[8];
-    uint32_t sh[8];
+// The same warp, once its copies have landed: staged raw rows -> the unpacked image the producers read.  A unit = sixteen l
+// values of one 128-half (16 bytes each of ql[l], ql[l + 32], qh[l]) -> four 16-byte runs of 6-bit values, e = 0..3, at element
+// 128 n + 32 e + l (dequantize_row_q6_K's order, L/ggml/src/ggml-quants.c:1762-1795).  Four units per row, one per thread:
+// lane = row (8) + 8 x unit, so that the eight lanes of a quarter-warp read / write 16-byte pieces 15 (stage) and 17 (image)
+// pieces apart — conflict-free.
+__device__ __forceinline__ void convert_rows(const Gemm6Params &p, const uint8_t *stage, uint8_t *qimg, int warp, int lane, int64_t m0, int gkb) {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
+    const uint32_t w_lo = (uint32_t)reinterpret_cast<uintptr_t>(p.w) + (uint32_t)gkb * BLK_Q6K, stride_lo = (uint32_t)p.w_stride;
+    auto shift_of = [&](int rl) {                                 // 0 or 16 bits: bit 1 of the row's block address
+        int64_t row = m0 + rl;
+        if (row >= p.M) row = p.M - 1;
+        return ((w_lo + (uint32_t)row * stride_lo) & 2u) * 8u;
+    };
+    {
+        const int rl = 8 * warp + (lane & 7), u = lane >> 3, n = u >> 1, jh = u & 1;
+        const uint32_t sh = shift_of(rl);
+        const uint8_t *A = stage + rl * RAW_PITCH;
+        auto run16 = [&](int byte_off, uint32_t (&o)[4]) {       // 16 block bytes from staged offset byte_off (16-byte aligned) on
+            const uint4 a = *reinterpret_cast<const uint4 *>(A + byte_off);
+            const uint32_t b = *reinterpret_cast<const uint32_t *>(A + byte_off + 16);
+            o[0] = __funnelshift_r(a.x, a.y, sh); o[1] = __funnelshift_r(a.y, a.z, sh);
+            o[2] = __funnelshift_r(a.z, a.w, sh); o[3] = __funnelshift_r(a.w, b, sh);
+        };
+        uint32_t wa[4], wb[4], wh[4];
+        run16(64 * n + 16 * jh, wa);
+        run16(64 * n + 32 + 16 * jh, wb);
+        run16(128 + 32 * n + 16 * jh, wh);
+        uint4 e0, e1, e2, e3;
+        uint32_t *o0 = &e0.x, *o1 = &e1.x, *o2 = &e2.x, *o3 = &e3.x;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        int64_t row = m0 + 8 * warp + i;
-        if (row >= p.M) row = p.M - 1;                       // rows past M: valid memory, results never stored
-        const uintptr_t base = reinterpret_cast<uintptr_t>(p.w) + (uintptr_t)(row * p.w_stride) + (uintptr_t)gkb * BLK_Q6K;
-        const uint8_t *al = reinterpret_cast<const uint8_t *>(base & ~(uintptr_t)3);
-        sh[i] = (uint32_t)(base & 2u) * 8u;
-        a0[i] = ldg_nc_u32(al + 4 * lane);
-        a1[i] = lane + 32 < RAW_WORDS ? ldg_nc_u32(al + 4 * (lane + 32)) : 0u;
+        for (int i = 0; i < 4; ++i) {
+            o0[i] = (wa[i] & 0x0f0f0f0fu) | ((wh[i] << 4) & 0x30303030u);
+            o1[i] = (wb[i] & 0x0f0f0f0fu) | ((wh[i] << 2) & 0x30303030u);
+            o2[i] = ((wa[i] >> 4) & 0x0f0f0f0fu) | (wh[i] & 0x30303030u);
+            o3[i] = ((wb[i] >> 4) & 0x0f0f0f0fu) | ((wh[i] >> 2) & 0x30303030u);
+        }
+        uint8_t *out = qimg + rl * Q_PITCH + 128 * n + 16 * jh;
+        *reinterpret_cast<uint4 *>(out) = e0;
+        *reinterpret_cast<uint4 *>(out + 32) = e1;
+        *reinterpret_cast<uint4 *>(out + 64) = e2;
+        *reinterpret_cast<uint4 *>(out + 96) = e3;
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        // word k of the image = bytes [4k, 4k + 4) of the block = funnel of aligned words k, k + 1 (the word past the block's
-        // last one is never loaded: lanes >= 21 of the second pass hold zero)
-        uint32_t n0 = __shfl_down_sync(0xffffffffu, a0[i], 1);
-        const uint32_t first1 = __shfl_sync(0xffffffffu, a1[i], 0), n1 = __shfl_down_sync(0xffffffffu, a1[i], 1);
-        if (lane == 31) n0 = first1;
-        uint32_t *dst = reinterpret_cast<uint32_t *>(slot + (8 * warp + i) * RAW_PITCH);
-        dst[lane] = __funnelshift_r(a0[i], n0, sh[i]);
-        if (lane + 32 < RAW_WORDS) dst[lane + 32] = __funnelshift_r(a1[i], lane + 33 < RAW_WORDS ? n1 : 0u, sh[i]);
+    {   // the 16 scales of each of the 8 rows: one word per lane
+        const int rl = 8 * warp + (lane >> 2), c = lane & 3;
+        const uint32_t *A = reinterpret_cast<const uint32_t *>(stage + rl * RAW_PITCH);
+        reinterpret_cast<uint32_t *>(qimg + rl * Q_PITCH + 256)[c] = __funnelshift_r(A[48 + c], A[49 + c], shift_of(rl));
     }
+    __syncwarp();                                                 // every lane has read the stage: it may be refilled
 }
 
 template <bool DUMP>
@@ -147,7 +198,8 @@ gemm_q6k_tc_kernel(const __grid_constant__ Gemm6Params p) {
     auto done_bar = [&](int s) { return bar0 + 8u * (B_SLOTS + s); };      // [B_SLOTS]  MMA -> producers / loader
     auto tfull_bar = [&](int h) { return bar0 + 8u * (2 * B_SLOTS + h); };
     auto tempty_bar = [&](int h) { return bar0 + 8u * (2 * B_SLOTS + 2 + h); };
-    auto rawfull_bar = [&](int s) { return bar0 + 8u * (2 * B_SLOTS + 4 + s); };   // [RAW_SLOTS] epilogue warps -> producers
+    auto qfull_bar = [&](int s) { return bar0 + 8u * (2 * B_SLOTS + 4 + s); };     // [Q_SLOTS] epilogue warps -> producers
+    auto qempty_bar = [&](int s) { return bar0 + 8u * (2 * B_SLOTS + 4 + Q_SLOTS + s); };   // [Q_SLOTS] producers -> epilogue warps: the slot has been read
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
@@ -157,8 +209,8 @@ gemm_q6k_tc_kernel(const __grid_constant__ Gemm6Params p) {
     const int nh = n0 + HALF_N < p.N ? 2 : 1;               // column halves that hold real columns
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_THREADS + 1); mbar_init(done_bar(s), 1); }
-        for (int s = 0; s < RAW_SLOTS; ++s) mbar_init(rawfull_bar(s), EPI_WARPS * 32);
+        for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_THREADS + 1); mbar_init(done_bar(s), Q6K_ISSUERS == 2 ? (uint32_t)nh : 1u); }
+        for (int s = 0; s < Q_SLOTS; ++s) { mbar_init(qfull_bar(s), EPI_WARPS * 32); mbar_init(qempty_bar(s), PROD_THREADS); }
         for (int h = 0; h < 2; ++h) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), EPI_WARPS * 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -175,47 +227,71 @@ gemm_q6k_tc_kernel(const __grid_constant__ Gemm6Params p) {
         // ===================== epilogue + raw weight feed =====================
         const int qd = warp & 3, g = warp >> 2;
         const int64_t row = m0 + 32 * qd + lane;
-        float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 64;   // [buffer][half 0: 16 | half 1: 16]
+        // the two float scales of a (row, column, superblock) — d of the row's block, d_x of the column — are prefetched by the
+        // warp itself with 4-byte cp.async into private buffers, two superblocks ahead (kb % 3), next to the raw blocks:
+        // plain global loads in this loop are sunk to their use by the compiler and stalled every warp ~800 cycles per
+        // superblock right where the tensor core waits for its accumulator back (profiles/r2_q6k_gemm_experiments.txt)
+        float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 96;                              // [3][half 0: 16 | half 1: 16]
+        uint32_t *dww = reinterpret_cast<uint32_t *>(smem + SMEM_DX + EPI_WARPS * 96 * 4) + warp * 96;   // [3][lane]: the word that holds d
         int64_t ncl = n0 + HALF_N * (lane >> 4) + EPI_COLS * g + (lane & 15);
         if (ncl >= p.N) ncl = p.N - 1;
         uint64_t acc[2][EPI_COLS / 2];
 #pragma unroll
         for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
-        // the weights do not depend on the quantizer in front of this kernel: the first two superblocks go out before the wait
-        for (int kb = 0; kb < min(nb, RAW_SLOTS - 1); ++kb) {
-            feed_raw(p, smem + SMEM_RAW + kb * RAW_SLOT_BYTES, warp, lane, m0, kb0 + kb);
-            mbar_arrive(rawfull_bar(kb));
+        const uintptr_t wd0 = reinterpret_cast<uintptr_t>(p.w) + (uintptr_t)((row < p.M ? row : p.M - 1) * p.w_stride) + (uintptr_t)kb0 * BLK_Q6K + 208;
+        const float *xdk = p.xd + (int64_t)kb0 * p.N + ncl;
+        auto prefetch_dw = [&](int kb) {
+            const uintptr_t a = (wd0 + (uintptr_t)kb * BLK_Q6K) & ~(uintptr_t)3;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(dww + (kb % 3) * 32 + lane)), "l"(a) : "memory");
+        };
+        auto prefetch_dx = [&](int kb) {
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(dxw + (kb % 3) * 32 + lane)), "l"(xdk + (int64_t)kb * p.N) : "memory");
+        };
+        // the weights do not depend on the quantizer in front of this kernel: superblocks 0 and 1 are unpacked and superblock 2
+        // is on its way before the wait
+        uint8_t *stage = smem + SMEM_RAW;
+        const int64_t srow = m0 + 8 * warp;                                   // first of the eight rows this warp stages
+        const uint32_t row_off = (uint32_t)((srow < p.M ? srow : p.M - 1) * p.w_stride);   // (rows past M are clamped: valid memory, results never stored)
+        stage_raw(p, stage, warp, lane, row_off, kb0);
+        prefetch_dw(0);
+        convert_rows(p, stage, smem + SMEM_Q, warp, lane, m0, kb0);
+        mbar_arrive(qfull_bar(0));
+        if (nb > 1) {
+            stage_raw(p, stage, warp, lane, row_off, kb0 + 1);
+            prefetch_dw(1);
+            convert_rows(p, stage, smem + SMEM_Q + Q_SLOT_BYTES, warp, lane, m0, kb0 + 1);
+            mbar_arrive(qfull_bar(1));
         }
-        // d of this thread's row, one superblock ahead (2-byte loads at block offset 208; not from the raw image, whose slots
-        // the faster warps recycle while a slower one is still on the previous superblock)
-        const uint8_t *wd = p.w + (row < p.M ? row : p.M - 1) * p.w_stride + (int64_t)kb0 * BLK_Q6K + 208;
-        unsigned short dh_next = __ldg(reinterpret_cast<const unsigned short *>(wd));
-        const float *xdk = p.xd + (int64_t)kb0 * p.N;
+        if (nb > 2) stage_raw(p, stage, warp, lane, row_off, kb0 + 2);
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        dxw[lane] = xdk[ncl];
-        __syncwarp();
+        prefetch_dx(0);
+        if (nb > 1) prefetch_dx(1);
         const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g);
         const uint64_t k16 = pack2(16.0f, 16.0f);
         for (int kb = 0; kb < nb; ++kb) {
-            // superblock kb + 2 takes the raw slot of kb - 1, whose last MMA completed before the tfull this warp saw last
-            if (kb + RAW_SLOTS - 1 < nb) {
-                const int kn = kb + RAW_SLOTS - 1;
-                feed_raw(p, smem + SMEM_RAW + (kn % RAW_SLOTS) * RAW_SLOT_BYTES, warp, lane, m0, kb0 + kn);
-                mbar_arrive(rawfull_bar(kn % RAW_SLOTS));
+            // everything this thread has in flight (raw blocks of kb + 2, scales up to kb + 1) has landed.  Superblock kb + 2 is
+            // unpacked into the slot of kb as soon as the producers have read that (they run up to four steps ahead of the tensor
+            // core, so this is early in the MMAs of kb: the image is ready a whole superblock before it is needed and the warp is
+            // back in time for this superblock's accumulators); then kb + 3 goes into the stage
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            __syncwarp();
+            if (kb + 2 < nb) {
+                mbar_wait_long<Q4K_GEMM_WAIT>(qempty_bar(kb % Q_SLOTS), (uint32_t)((kb / Q_SLOTS) & 1));
+                convert_rows(p, stage, smem + SMEM_Q + (kb % Q_SLOTS) * Q_SLOT_BYTES, warp, lane, m0, kb0 + kb + 2);
+                mbar_arrive(qfull_bar(kb % Q_SLOTS));
+                if (kb + 3 < nb) stage_raw(p, stage, warp, lane, row_off, kb0 + kb + 3);
+                prefetch_dw(kb + 2);
+                prefetch_dx(kb + 2);
             }
-            float dx_next = 0.0f;
-            const float dw = __half2float(__ushort_as_half(dh_next));
+            const uint32_t dbits = dww[(kb % 3) * 32 + lane] >> (8u * (uint32_t)((wd0 + (uintptr_t)kb * BLK_Q6K) & 2u));
+            const float dw = __half2float(__ushort_as_half((unsigned short)(dbits & 0xffffu)));
             const uint64_t d2 = pack2(dw, dw);
-            if (kb + 1 < nb) {
-                dx_next = xdk[(int64_t)(kb + 1) * p.N + ncl];
-                dh_next = __ldg(reinterpret_cast<const unsigned short *>(wd + (int64_t)(kb + 1) * BLK_Q6K));
-            }
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (h >= nh) break;
-                mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (uint32_t)(kb & 1));
+                mbar_wait_long<Q6K_WAIT_TFULL>(tfull_bar(h), (uint32_t)(kb & 1));
                 tc_fence_after();
-                const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + (kb & 1) * 32 + 16 * h);
+                const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + (kb % 3) * 32 + 16 * h);
 #pragma unroll
                 for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
                     uint32_t vh[8], vl[8];
@@ -242,8 +318,6 @@ gemm_q6k_tc_kernel(const __grid_constant__ Gemm6Params p) {
                     }
                 }
             }
-            dxw[((kb + 1) & 1) * 32 + lane] = dx_next;
-            __syncwarp();
         }
         // split-K turnstile: parts add in K order (gemm_q4k_tc.cu)
         const int z = blockIdx.z;
@@ -286,26 +360,20 @@ gemm_q6k_tc_kernel(const __grid_constant__ Gemm6Params p) {
         uint4 scw = make_uint4(0, 0, 0, 0);
         for (int step = 0; step < nsteps; ++step) {
             const int kb = step >> 2, st = step & 3, n = st >> 1, hp = st & 1;
-            if (st == 0) mbar_wait_long<Q4K_GEMM_WAIT>(rawfull_bar(kb % RAW_SLOTS), (uint32_t)((kb / RAW_SLOTS) & 1));
-            const uint8_t *raw = smem + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES + r * RAW_PITCH;
-            if (st == 0) scw = *reinterpret_cast<const uint4 *>(raw + 192);
-            const uint4 la = *reinterpret_cast<const uint4 *>(raw + 64 * n + 16 * hp);            // ql[l],      l = 16 hp ..
-            const uint4 lb = *reinterpret_cast<const uint4 *>(raw + 64 * n + 32 + 16 * hp);       // ql[32 + l]
-            const uint4 hq = *reinterpret_cast<const uint4 *>(raw + 128 + 32 * n + 16 * hp);      // qh[l]
-            const uint32_t wa[4] = {la.x, la.y, la.z, la.w}, wb[4] = {lb.x, lb.y, lb.z, lb.w}, wh[4] = {hq.x, hq.y, hq.z, hq.w};
-            uint32_t qa[4], qb[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {        // e = 2k: nibble k of ql[l], qh bits 4k, 4k+1;  e = 2k + 1: nibble k of ql[32 + l], bits 4k+2, 4k+3
-                const uint32_t h4 = k ? wh[i] >> 4 : wh[i];
-                qa[i] = ((k ? wa[i] >> 4 : wa[i]) & 0x0f0f0f0fu) | ((h4 << 4) & 0x30303030u);
-                qb[i] = ((k ? wb[i] >> 4 : wb[i]) & 0x0f0f0f0fu) | ((h4 << 2) & 0x30303030u);
-            }
+            if (st == 0) mbar_wait_long<Q4K_GEMM_WAIT>(qfull_bar(kb % Q_SLOTS), (uint32_t)((kb / Q_SLOTS) & 1));
+            const uint8_t *qrow = smem + SMEM_Q + (kb % Q_SLOTS) * Q_SLOT_BYTES + r * Q_PITCH;
+            if (st == 0) scw = *reinterpret_cast<const uint4 *>(qrow + 256);
+            // e = 2k and 2k + 1, l = 16 hp .. 16 hp + 15: elements 128 n + 64 k + 16 hp .. and 32 further on
+            const uint4 va = *reinterpret_cast<const uint4 *>(qrow + 128 * n + 64 * k + 16 * hp);
+            const uint4 vb = *reinterpret_cast<const uint4 *>(qrow + 128 * n + 64 * k + 32 + 16 * hp);
+            const uint32_t qa[4] = {va.x, va.y, va.z, va.w}, qb[4] = {vb.x, vb.y, vb.z, vb.w};
             // scales of sub-blocks 8n + 2e + hp: bytes 8n + 4k + hp and + 2 of the 16
             const uint32_t sw = n ? (k ? scw.w : scw.z) : (k ? scw.y : scw.x);
             const int sa = (int)(int8_t)(sw >> (8 * hp)), sb = (int)(int8_t)(sw >> (8 * hp + 16));
             uint32_t hi[16], lo[16];
             unpack16(hi, lo, qa, sa);
             unpack16(hi + 8, lo + 8, qb, sb);
+            if (st == SB_STEPS - 1) mbar_arrive(qempty_bar(kb % Q_SLOTS));     // this thread has read the superblock's image
             // A stage step % 4 was last read by the MMAs of step - 4
             if (step >= A_STAGES) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar((step - A_STAGES) % B_SLOTS), (uint32_t)(((step - A_STAGES) / B_SLOTS) & 1));
             tc_fence_after();
@@ -316,40 +384,46 @@ gemm_q6k_tc_kernel(const __grid_constant__ Gemm6Params p) {
             tc_fence_before();
             mbar_arrive(full_bar(step % B_SLOTS));
         }
-    } else if (warp == MMA_WARP) {
-        // ===================== MMA issuer =====================
-        const uint32_t idesc = umma_idesc(true);
-        const uint32_t smem0 = smem_addr(smem);
-        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
-        const uint64_t desc0 = umma_desc(0, SBO_BYTES);
-        // per superblock: the 32 MMAs of column half 0 (four K steps x two pieces x four K = 16 slices), then those of half 1;
-        // the epilogue drains one half while the tensor core works on the other
-        for (int kb = 0; kb < nb; ++kb) {
+    } else if (warp < LOAD_WARP) {
+        // ===================== MMA issuers: warp MMA_WARP + h owns column half h =====================
+        // (Q6K_ISSUERS = 1: one warp issues both halves, half 0 first — measured the same, profiles/r2_q6k_gemm_experiments.txt)
+        const int hsel = warp - MMA_WARP;
+        const int h_begin = Q6K_ISSUERS == 2 ? hsel : 0, h_end = Q6K_ISSUERS == 2 ? min(hsel + 1, nh) : (hsel == 0 ? nh : 0);
+        if (h_begin < h_end) {
+            const uint32_t idesc = umma_idesc(true);
+            const uint32_t smem0 = smem_addr(smem);
+            const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+            const uint64_t desc0 = umma_desc(0, SBO_BYTES) + (uint64_t)((smem0 + SMEM_B) >> 4);
+            int bslot0 = 0;
+            uint32_t bpar0 = 0u;
+            for (int kb = 0; kb < nb; ++kb) {
+                int bslot = bslot0;
+                uint32_t bpar = bpar0;
+                for (int h = h_begin; h < h_end; ++h) {
+                    bslot = bslot0; bpar = bpar0;
+                    const uint32_t d_hi = tm + TM_HI + h * HALF_N, d_lo = tm + TM_LO + h * HALF_N;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (h >= nh) break;
-#pragma unroll
-                for (int st = 0; st < SB_STEPS; ++st) {
-                    const int step = SB_STEPS * kb + st, bslot = step % B_SLOTS;
-                    if (h == 0) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));
-                    if (st == 0) mbar_wait_long<Q4K_GEMM_WAIT_TEMPTY>(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
-                    tc_fence_after();
-                    const uint32_t ta = tm + TM_A + (uint32_t)(step % A_STAGES) * TM_A_STAGE;
-                    const uint64_t bd0 = desc0 + (uint64_t)((smem0 + SMEM_B + (uint32_t)bslot * TILE_BYTES) >> 4);
-                    if (elect_one()) {
-#pragma unroll
-                        for (int o = 0; o < 2; ++o) {
+                    for (int st = 0; st < SB_STEPS; ++st) {
+                        if (h == h_begin) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot), bpar);
+                        if (st == 0) mbar_wait_long<Q6K_WAIT_TEMPTY>(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
+                        tc_fence_after();
+                        const uint32_t ta = tm + TM_A + (uint32_t)st * TM_A_STAGE;                   // A stage = step % 4
+                        const uint64_t bd0 = desc0 + (uint64_t)((uint32_t)bslot * (TILE_BYTES >> 4) + (uint32_t)h * ((HALF_N / 8) * SBO_BYTES >> 4));
+                        if (elect_one()) {
 #pragma unroll
                             for (int j = 0; j < KS / 16; ++j) {
-                                const uint64_t b_desc = bd0 + (uint64_t)((h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES) >> 4);
-                                umma_f16_ts(tm + (o ? TM_LO : TM_HI) + h * HALF_N, ta + o * TM_A_PIECE + 8 * j, b_desc, idesc, (uint32_t)((st | j) != 0));
+                                const uint64_t b_desc = bd0 + (uint64_t)((j * 2 * LBO_BYTES) >> 4);
+                                umma_f16_ts(d_hi, ta + 8 * j, b_desc, idesc, (uint32_t)((st | j) != 0));
+                                umma_f16_ts(d_lo, ta + TM_A_PIECE + 8 * j, b_desc, idesc, (uint32_t)((st | j) != 0));
                             }
+                            if (st == SB_STEPS - 1) umma_commit(tfull_bar(h));
+                            if (Q6K_ISSUERS == 2 || h == nh - 1) umma_commit(done_bar(bslot));   // reads of the A stage and the B slot are done
                         }
-                        if (st == SB_STEPS - 1) umma_commit(tfull_bar(h));
-                        if (h == nh - 1) umma_commit(done_bar(bslot));
+                        __syncwarp();
+                        if (++bslot == B_SLOTS) { bslot = 0; bpar ^= 1u; }
                     }
-                    __syncwarp();
                 }
+                bslot0 = bslot; bpar0 = bpar;
             }
         }
     } else if (lane == 0) {
@@ -417,7 +491,7 @@ int choose_ksplit6(int64_t tiles, int64_t nb) {              // as gemm_q4k_tc.c
     double best_cost = (double)nb;
     for (int s = 2; s <= 4; ++s) {
         if (tiles * s > sms || nb / s < 4) break;
-        const double cost = (double)((nb + s - 1) / s) + 10.0 * (s - 1);
+        const double cost = (double)((nb + s - 1) / s) + 5.0 * (s - 1);       // a superblock costs ~2.5 us here, a hand-off ~12
         if (cost < best_cost - 2.0) { best_cost = cost; best = s; }
     }
     return best;
@@ -438,7 +512,7 @@ cudaError_t launch_gemm_q6k_f32(const void *w, int64_t M, int64_t K, int64_t w_r
     if (N == 0 || M == 0) return cudaSuccess;
     const int64_t nb = K / QK_K;
     const int64_t ntiles = (N + BN - 1) / BN, mtiles = (M + BM - 1) / BM;
-    if (mtiles > 65535) return cudaErrorNotSupported;
+    if (mtiles > 65535 || M * w_row_stride_bytes >= ((int64_t)1 << 32)) return cudaErrorNotSupported;     // (the caller runs the decode kernel instead)
     uint8_t *qs = reinterpret_cast<uint8_t *>(workspace);
     float *d = reinterpret_cast<float *>(qs + ntiles * BN * K * 2);
     int *flags = reinterpret_cast<int *>(reinterpret_cast<char *>(d) + ((nb * (size_t)N * 4 + 255) & ~(size_t)255));

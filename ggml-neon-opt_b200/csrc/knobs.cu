@@ -39,7 +39,7 @@ Knobs read_defaults() {
     k.tma_stages = env_int("Q4K_DBG_STAGES", 0);
     k.tma_per_sm = env_int("Q4K_DBG_PER_SM", 0);
     k.gemm_ksplit = env_int("Q4K_DBG_GEMM_KSPLIT", 0);
-    k.q6k_gemm_min = env_int("Q4K_DBG_Q6K_GEMM_MIN", 33);
+    k.q6k_gemm_min = env_int("Q4K_DBG_Q6K_GEMM_MIN", 9);
     k.midn_max = env_int("Q4K_DBG_MIDN_MAX", 32);        // above 32 columns the tcgen05 GEMM wins on the large shapes (profiles/r2_wide_sweep.txt)
     k.wide_min = env_int("Q4K_DBG_WIDE_MIN", 2);       // measured: the batched kernel wins from N = 3 at every shape, at N = 2 from K = 4096 (profiles/r2_wide_sweep.txt)
     k.wide_dbg = env_int("Q4K_DBG_WIDE_DBG", 0);

@@ -295,7 +295,7 @@ int q4k_mul_mat_host_async(const void *w_dev, int64_t M, int64_t K, int64_t w_ro
  * (L/ggml/src/ggml-cpu/ggml-cpu.c:1205-1401 with type_traits_cpu[GGML_TYPE_Q6_K], :296-301: vec_dot =
  * ggml_vec_dot_q6_K_q8_K, L/ggml/src/ggml-cpu/arch/x86/quants.c:2129-2218; vec_dot_type = Q8_K).
  * Weights: M rows of K/256 block_q6_K (210 B each); w_dev and w_row_stride_bytes need only be even (210-byte blocks
- * are 2-byte aligned by nature).  N <= 32: the HBM-bound decode kernel, eight columns per pass; N > 32 ("q6k_gemm_min"): the
+ * are 2-byte aligned by nature).  N <= 8: the HBM-bound decode kernel; N > 8 ("q6k_gemm_min"): the
  * tcgen05 kind::f16 prefill GEMM (csrc/gemm_q6k_tc.cu; workspace 16-byte aligned).  Integer sums per superblock are exactly the
  * reference's on both; fp32 within 1e-5. */
 size_t q6k_mul_mat_workspace_bytes(int64_t K, int64_t N);

@@ -61,13 +61,18 @@ def test_mul_mat_within_tolerance(q4k, M, K, N):
 
 def test_many_columns_and_long_k(q4k):
     """N > 8 runs eight columns per pass; K = 28672 with 8 columns does not fit shared memory and splits further"""
+    import q4k_b200
     from oracle import port
-    for M, K, N in [(40, 1024, 19), (12, 28672, 8)]:
-        w = make_q6(M, K, real=False)
-        x = make_acts(N, K)
-        y = q4k.mul_mat_q6k(t(w), t(x)).cpu().numpy()
-        ref = port.mul_mat_q6(w, x, port.ORDER_AVX2)
-        assert_close(y, ref, port.mul_mat_q6_f64(w, x))
+    try:
+        q4k_b200.debug_set("q6k_gemm_min", 0)              # keep this test on the decode kernel (N > 8 goes to the GEMM by default)
+        for M, K, N in [(40, 1024, 19), (12, 28672, 8)]:
+            w = make_q6(M, K, real=False)
+            x = make_acts(N, K)
+            y = q4k.mul_mat_q6k(t(w), t(x)).cpu().numpy()
+            ref = port.mul_mat_q6(w, x, port.ORDER_AVX2)
+            assert_close(y, ref, port.mul_mat_q6_f64(w, x))
+    finally:
+        q4k_b200.debug_set("q6k_gemm_min", 9)
 
 
 def test_row_results_do_not_depend_on_position_or_batch(q4k):

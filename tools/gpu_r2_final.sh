@@ -19,6 +19,11 @@ python tools/ncu_target.py --M 8192 --K 28672 --N 1 > gpurun_out/plain_c5b.log 2
 ncu --set full --clock-control none --import-source on -k regex:gemv_q4k -s 2 -c 1 -f -o gpurun_out/prof_r2_c5_8192x28672 \
     python tools/ncu_target.py --M 8192 --K 28672 --N 1 > gpurun_out/ncu_c5b.log 2>&1
 echo "c5b rc=$?"
+timeout -k 5 300 python tools/q6k_gemm_bench.py > gpurun_out/r2_q6k_gemm_bench.txt 2>&1; echo "q6k bench rc=$?"; head -4 gpurun_out/r2_q6k_gemm_bench.txt
+timeout -k 5 120 python tools/q6k_gemm_one.py 4096 14336 512 > gpurun_out/plain_q6k.log 2>&1 &&
+timeout -k 5 400 ncu --set full --clock-control none --import-source on -k regex:gemm_q6k_tc -s 2 -c 1 -f -o gpurun_out/prof_r2_q6k_gemm_4096x14336x512 \
+    python tools/q6k_gemm_one.py 4096 14336 512 > gpurun_out/ncu_q6k.log 2>&1
+echo "q6k ncu rc=$?"
 export GGML_BACKEND_PATH=$PWD/ggml-neon-opt_b200/lib/libggml-q4k-b200.so
 timeout 600 oracle/_ref/test-backend-ops perf -o MUL_MAT -b Q4K_B200_0 -p type_a=q4_K > gpurun_out/r2_test_backend_ops_perf_q4k_final.txt 2>&1; echo "tbo perf rc=$?"
 unset GGML_BACKEND_PATH
