@@ -584,6 +584,55 @@ def q6k_shape_table(torch, q4k, device, shapes, peak, steps=20):
     return out
 
 
+def q6k_prefill_obj(torch, q4k, device, peaks_json):
+    """Q6_K prefill (q6k_mul_mat at N = 512: quantizer + tcgen05 kind::f16 GEMM, csrc/gemm_q6k_tc.cu) per shape, and the whole
+    TinyLlama-1.1B Q4_K_M prompt pass — all 155 weight mul_mats, Q4_K and Q6_K — as one q4k_plan at N = 512.
+    ops = 2*M*N*K.  The exact integers take two fp16 MMAs per weight: ceiling = half the dense fp16 rate."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(9)
+    bf16 = float(peaks_json.get("bf16_tflops", 0.0)) or None
+    out = {"shapes": [], "fp16_dense_tflops": bf16, "fp16_source": "MEASURED_PEAKS.json bf16_tflops (cuBLAS burst)" if bf16 else "unavailable"}
+    L = q4k.load()
+    N = 512
+    for M, K in [(32000, 2048), (2048, 5632), (256, 2048), (4096, 14336)]:
+        w = rand_q6k(torch, M, K, device, gen)
+        x = torch.randn((N, K), device=device, generator=gen)
+        dst = torch.empty((N, M), device=device)
+        ws = torch.empty(L.q6k_mul_mat_workspace_bytes(K, N), dtype=torch.uint8, device=device)
+
+        def call():
+            q4k.mul_mat_q6k(w, x, dst, ws)
+        for _ in range(2):
+            call()
+        t = timed_steps(torch, call, 10, 1, lambda: None) / 10
+        tops = 2.0 * M * K * N / t / 1e9
+        row = {"M": M, "K": K, "N": N, "us": round(t * 1e3, 1), "tops": round(tops, 1), "bound": "tensor"}
+        if bf16:
+            row["frac_exact_ceiling"] = round(tops / (bf16 / 2), 4)
+        out["shapes"].append(row)
+        del w, x, dst, ws
+        torch.cuda.empty_cache()
+    mats = tinyllama_full_token_matmuls()
+    ids = shared_input_ids([(n, M, K) for n, M, K, _ in mats])
+    plan = q4k.GraphPlan(torch.device(device).index or 0)
+    keep = []
+    for (name, M, K, q6), iid in zip(mats, ids):
+        w = (rand_q6k if q6 else rand_q4k)(torch, M, K, device, gen)
+        keep.append(w)
+        plan.add(w, N, iid, q6k=q6)
+    plan.finalize()
+    for iid in set(ids):
+        plan.input(iid).normal_(generator=gen)
+    t = timed_steps(torch, plan.run, 3, 2, lambda: None) / 3
+    ops = sum(2.0 * M * K * N for _, M, K, _ in mats)
+    out["tinyllama_pp512_full"] = {"workload": "every weight mul_mat of a TinyLlama-1.1B Q4_K_M prompt pass at 512 tokens: 134 Q4_K + 21 Q6_K",
+                                   "mul_mats": len(mats), "launches_per_pass": int(plan.launches), "ms_per_pass": round(t, 3),
+                                   "tops": round(ops / t / 1e9, 1), "tok_s": round(512 / t * 1e3, 0)}
+    del plan, keep
+    torch.cuda.empty_cache()
+    return out
+
+
 def plugin_e2e(mats_typed, ids, iters):
     """`e2e_plugin`: the same mul_mat set as ONE ggml graph on the backend plugin, through the reference's public backend API
     (oracle/_ref's libggml drives it: tensor_set_async -> graph_compute_async | graph_plan_compute -> tensor_get_async ->
@@ -880,7 +929,7 @@ def run_ours(args, rank, world, local_rank):
             dist.destroy_process_group()
         return
 
-    peak, peak_src, _ = measured_peaks()
+    peak, peak_src, peaks_json = measured_peaks()
     per_step_ms = ms_total / steps_timed
     value = total_bytes / (per_step_ms * 1e-3) / 1e9
     e2e_val = total_bytes / (ms_e2e / args.steps * 1e-3) / 1e9
@@ -941,6 +990,10 @@ def run_ours(args, rank, world, local_rank):
         line["full_q4_k_m_token"] = full_token_extra(torch, q4k_b200, device, max(args.steps, 20), args.no_cpu, peak)
         if cpu:
             line["llama_bench"] = llama_bench_obj()
+        try:
+            line["q6k_prefill"] = q6k_prefill_obj(torch, q4k_b200, device, peaks_json)
+        except Exception as e:
+            line["q6k_prefill"] = {"unavailable": f"{type(e).__name__}: {e}"}
         line["q6k_shapes"] = q6k_shape_table(torch, q4k_b200, device, [(2048, 5632, 1), (32000, 2048, 1), (14336, 4096, 1), (28672, 8192, 1)], peak)
     print(json.dumps(line), flush=True)
     if dist is not None:
