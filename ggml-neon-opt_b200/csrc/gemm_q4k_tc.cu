@@ -478,8 +478,8 @@ quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, 
     const int64_t row = blk / nb_per_row, b = blk - row * nb_per_row;
     const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + row * x_row_stride_bytes) + b * QK_K;
     // plain (coherent) loads: under programmatic dependent launch the kernel that produces x may still have been running at entry
-    const float4 a = reinterpret_cast<const float4 *>(src)[lane];
-    const float4 c = reinterpret_cast<const float4 *>(src)[32 + lane];
+    const float4 a = ld_act16(src + 4 * lane);
+    const float4 c = ld_act16(src + 128 + 4 * lane);
     const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
     uint32_t w_lo, w_hi;
     int s_lo, s_hi;

@@ -461,8 +461,8 @@ quantize_q8_f16_tiles_kernel(const float *__restrict__ x, uint8_t *__restrict__ 
     if (blk >= nblocks_total) return;
     const int64_t col = blk / nb_per_row, b = blk - col * nb_per_row;
     const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + col * x_row_stride_bytes) + b * QK_K;
-    const float4 a = reinterpret_cast<const float4 *>(src)[lane];
-    const float4 c = reinterpret_cast<const float4 *>(src)[32 + lane];
+    const float4 a = ld_act16(src + 4 * lane);
+    const float4 c = ld_act16(src + 128 + 4 * lane);
     const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
     uint32_t w_lo, w_hi;
     int s_lo, s_hi;

@@ -162,7 +162,7 @@ quantize_q8_K_n1s_kernel(const float *__restrict__ x, uint8_t *__restrict__ xs, 
     const int b = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (b >= nb) return;
     const float *src = x + (int64_t)b * QK_K;
-    const float4 a = reinterpret_cast<const float4 *>(src)[lane], e = reinterpret_cast<const float4 *>(src)[32 + lane];
+    const float4 a = ld_act16(src + 4 * lane), e = ld_act16(src + 128 + 4 * lane);
     const float v[8] = {a.x, a.y, a.z, a.w, e.x, e.y, e.z, e.w};
     uint32_t w_lo, w_hi;
     int s_lo, s_hi;

@@ -283,7 +283,7 @@ quantize_q8_K_wide_kernel(const float *__restrict__ x, uint8_t *__restrict__ xs,
     float d = 0.0f;
     if (col < N) {
         const float *src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + col * x_row_stride_bytes) + b * QK_K;
-        const float4 a = reinterpret_cast<const float4 *>(src)[lane], e = reinterpret_cast<const float4 *>(src)[32 + lane];
+        const float4 a = ld_act16(src + 4 * lane), e = ld_act16(src + 128 + 4 * lane);
         const float v[8] = {a.x, a.y, a.z, a.w, e.x, e.y, e.z, e.w};
         d = quantize_block_q8_K<8>(v, lane, w_lo, w_hi, s_lo, s_hi);
     }

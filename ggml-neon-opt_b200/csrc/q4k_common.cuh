@@ -37,6 +37,15 @@ struct __align__(16) block_q4_K {
 };
 static_assert(sizeof(block_q4_K) == BLK_Q4K, "block_q4_K must stay 144 bytes");
 
+// Coherent 16-byte load of activations.  The quantizer kernels run under programmatic dependent launch: their lifetime overlaps
+// the kernel (or the peer GPU) that produces x, so the read-only contract of ld.global.nc — which nvcc picks for a
+// `const __restrict__` pointer — does not hold, even though every load sits behind griddepcontrol.wait.
+__device__ __forceinline__ float4 ld_act16(const float *p) {
+    float4 v;
+    asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
 // streaming 16-byte load of weights: read once, keep out of L1
 __device__ __forceinline__ uint4 ldg_stream16(const void *p) {
     uint4 r;

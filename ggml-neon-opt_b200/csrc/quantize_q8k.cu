@@ -34,8 +34,8 @@ quantize_q8_K_kernel(const float *__restrict__ x, uint8_t *__restrict__ y, int64
 
     // plain (coherent) loads, not ld.global.nc: under programmatic dependent launch this kernel's lifetime overlaps the kernel
     // that produces x (peer GPUs storing over NVLink included)
-    const float4 a = reinterpret_cast<const float4 *>(src)[lane];
-    const float4 b = reinterpret_cast<const float4 *>(src)[32 + lane];
+    const float4 a = ld_act16(src + 4 * lane);
+    const float4 b = ld_act16(src + 128 + 4 * lane);
     const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 
     uint32_t w_lo, w_hi;
