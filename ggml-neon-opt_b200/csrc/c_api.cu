@@ -278,6 +278,12 @@ int q4k_mul_mat_peers_ll(const void *w_dev, int64_t M_local, int64_t K, int64_t 
     const int64_t nb = K / Q4K_QK_K;
     if (w_row_stride_bytes < nb * Q4K_BLOCK_Q4K || (w_row_stride_bytes & 15) || !aligned16(w_dev)) return Q4K_ERR_BAD_SHAPE;
     if (x_row_stride_bytes < K * 4 || (x_row_stride_bytes & 15) || !aligned16(x_dev)) return Q4K_ERR_BAD_SHAPE;
+    // one column of a long K with enough rows per rank: the streamed kernel, as q4k_mul_mat would choose for the shard alone
+    if (N == 1 && !gemv_exact_for(1) && knobs().gemv_config == 0 && !knobs().mma_off && K >= knobs().n1s_min_k && M_local >= knobs().n1s_ll_min_rows &&
+        workspace_dev && workspace_bytes >= n1s_workspace_bytes(K) && aligned16(workspace_dev)) {
+        const cudaError_t e1 = launch_gemv_q4k_n1s(w_dev, M_local, K, w_row_stride_bytes, x_dev, nullptr, workspace_dev, knobs().pdl != 0, st, &ll, dst_row0);
+        if (e1 != cudaErrorNotSupported) return e1 == cudaSuccess ? Q4K_OK : cuda_fail(e1);
+    }
     const void *xq = nullptr;
     int64_t xq_stride = x_row_stride_bytes;
     if (N * K > knobs().fuse_limit && workspace_dev && workspace_bytes >= (size_t)(N * nb * Q4K_BLOCK_Q8K)) {

@@ -49,8 +49,18 @@ struct N1sParams {
     float *dst;
     int64_t tiles, passes;
     int stages;
+    // LL exchange of the row-sharded path (q4k_kernels.h LLExchange; the field names gemv_stage.cuh's ll_* helpers use):
+    // ll_world > 0 = row `dst_row0 + m` leaves as a {value, epoch} pair for every rank and the tail of the launch gathers
+    uint2 *ll_peers[8];
+    const uint2 *ll_local;
+    int64_t ll_half, ll_M, ll_dst_stride;
+    uint32_t *ll_cnt;
+    float *ll_dst;
+    int ll_world, ll_rank;
+    int64_t dst_row0;
 };
 
+template <bool LL>
 __global__ void __launch_bounds__(NS_THREADS, 1)
 gemv_q4k_n1s_kernel(const __grid_constant__ N1sParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -106,6 +116,12 @@ gemv_q4k_n1s_kernel(const __grid_constant__ N1sParams p) {
     int slot = 0, buf = 0;
     uint32_t ph = 0u;
     const DumpAt da{};
+    uint32_t ll_ep = 0u;
+    if (LL && cls == 0) {       // the storing warps: this call's epoch (the previous call of the object has completed behind the wait)
+        griddep_wait();
+        ll_ep = ll_epoch(p);
+        if (blockIdx.x == 0 && ts == 0) ll_presence(p, ll_ep, lane);
+    }
     for (int64_t ip = 0; ip < my_passes; ++ip) {
         const int64_t tile = (blockIdx.x + ip * gridDim.x) * NS_TS + ts;
         const bool tile_ok = tile < p.tiles;
@@ -148,9 +164,14 @@ gemv_q4k_n1s_kernel(const __grid_constant__ N1sParams p) {
         }
         if (cls == 0 && lane < MROWS && tile_ok) {
             const int64_t row = tile * MROWS + lane;
-            if (row < p.M) p.dst[row] = tot;
+            if (row < p.M) {
+                if (LL) ll_store(p, ll_ep, 0, p.dst_row0 + row, tot);
+                else p.dst[row] = tot;
+            }
         }
     }
+    // the gather: one warp per CTA takes its slice of the full vector out of this rank's LL buffer (every CTA is resident)
+    if (LL && warp == 0) ll_tail(p, 1, ll_ep, blockIdx.x, gridDim.x, lane, 32);
 }
 
 // quantize_row_q8_K for one activation row into staged blocks (the arithmetic of quantize_q8k.cu; one warp per block)
@@ -184,7 +205,7 @@ size_t n1s_workspace_bytes(int64_t K) { return (size_t)((K / QK_K + KW - 1) / KW
 
 // F32 activation row -> quantizer + the streamed single-column kernel.  cudaErrorNotSupported when no tensor map can be made.
 cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x, float *dst,
-                                void *workspace, bool pdl, cudaStream_t stream) {
+                                void *workspace, bool pdl, cudaStream_t stream, const LLExchange *ll, int64_t dst_row0) {
     if (M <= 0) return cudaSuccess;
     const int nb = (int)(K / QK_K);
     N1sParams p;
@@ -206,6 +227,9 @@ cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_r
     p.M = M; p.nb = nb;
     p.xs = (const uint8_t *)workspace;
     p.dst = dst;
+    fill_ll(p, ll);
+    p.dst_row0 = dst_row0;
+    auto kern = ll ? gemv_q4k_n1s_kernel<true> : gemv_q4k_n1s_kernel<false>;
     p.tiles = (M + MROWS - 1) / MROWS;
     p.passes = (p.tiles + NS_TS - 1) / NS_TS;
     const size_t fixed = NS_XBLK + (size_t)2 * NS_TS * KW * MROWS * 4 + 256;
@@ -213,7 +237,7 @@ cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_r
     if (knobs().mma_stages > 0) stages = std::min(stages, std::max(2, knobs().mma_stages));
     p.stages = stages;
     const size_t smem = (size_t)stages * NS_STAGE + fixed + (size_t)stages * 16;
-    if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)gemv_q4k_n1s_kernel, (int)NS_SMEM_MAX)) return ea;
+    if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)NS_SMEM_MAX)) return ea;
     int64_t grid = sm_count();
     if (grid > p.passes) grid = p.passes;
     cudaLaunchConfig_t cfg = {};
@@ -223,7 +247,7 @@ cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_r
     cfg.stream = stream;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, gemv_q4k_n1s_kernel, p);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
     return e;
 }

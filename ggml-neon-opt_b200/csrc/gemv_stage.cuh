@@ -76,7 +76,8 @@ struct TmaBoxParams : TmaGemvParams {
     int use_tma;            // 1 = wmap[] are valid and the kernel fetches tiles through them
 };
 
-inline void fill_ll(TmaGemvParams &p, const LLExchange *ll) {
+template <class P>
+inline void fill_ll(P &p, const LLExchange *ll) {
     for (int r = 0; r < 8; ++r) p.ll_peers[r] = nullptr;
     p.ll_local = nullptr; p.ll_half = p.ll_M = p.ll_dst_stride = 0; p.ll_cnt = nullptr; p.ll_dst = nullptr; p.ll_world = 0; p.ll_rank = 0;
     if (!ll) return;
@@ -371,21 +372,24 @@ __device__ __forceinline__ void peer_sync_tail(const TmaGemvParams &p, int lane)
 // ---- LL exchange -------------------------------------------------------------------------------------------------------
 // epoch of this call: one more than the calls this object has completed (read after griddepcontrol.wait: the previous call's
 // last CTA wrote it)
-__device__ __forceinline__ uint32_t ll_epoch(const TmaGemvParams &p) {
+template <class P>
+__device__ __forceinline__ uint32_t ll_epoch(const P &p) {
     uint32_t c;
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(p.ll_cnt) : "memory");
     return c + 1u;
 }
 // one result -> every rank's LL buffer.  The value and its epoch travel in ONE 8-byte store (atomic over NVLink), so the
 // receiver needs no fence: a pair whose epoch matches carries the value.
-__device__ __forceinline__ void ll_store(const TmaGemvParams &p, uint32_t ep, int64_t col, int64_t row_full, float v) {
+template <class P>
+__device__ __forceinline__ void ll_store(const P &p, uint32_t ep, int64_t col, int64_t row_full, float v) {
     const int64_t i = (int64_t)(ep & 1u) * p.ll_half + col * p.ll_M + row_full;
     for (int g = 0; g < p.ll_world; ++g)
         asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p.ll_peers[g] + i), "r"(__float_as_uint(v)), "r"(ep) : "memory");
 }
 // "this rank has started call ep" -> every rank (ONE warp of the launch, after it has read the epoch, i.e. after this rank's
 // previous call has completed): see the back-pressure note at LLExchange
-__device__ __forceinline__ void ll_presence(const TmaGemvParams &p, uint32_t ep, int lane) {
+template <class P>
+__device__ __forceinline__ void ll_presence(const P &p, uint32_t ep, int lane) {
     if (lane < p.ll_world) {
         uint2 *slot = p.ll_peers[lane] + 2 * p.ll_half + (int64_t)(ep & 1u) * 8 + p.ll_rank;
         asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(slot), "r"(0u), "r"(ep) : "memory");
@@ -395,7 +399,8 @@ __device__ __forceinline__ void ll_presence(const TmaGemvParams &p, uint32_t ep,
 // [N][M_full] vector, wait for each pair of this call to arrive in the rank's own LL buffer (whoever computes it: another
 // rank over NVLink, or a CTA of this launch) and write it out as a plain float.  The last CTA to finish publishes the call
 // counter.  Every CTA of the launch is resident (persistent grid), so nobody waits for a CTA that cannot run.
-__device__ __forceinline__ void ll_tail(const TmaGemvParams &p, int N, uint32_t ep, int64_t part, int64_t nparts, int lane, int nlanes) {
+template <class P>
+__device__ __forceinline__ void ll_tail(const P &p, int N, uint32_t ep, int64_t part, int64_t nparts, int lane, int nlanes) {
     const int64_t total = (int64_t)N * p.ll_M;
     const int64_t i0 = total * part / nparts, i1 = total * (part + 1) / nparts;
     const uint2 *src = p.ll_local + (int64_t)(ep & 1u) * p.ll_half;

@@ -24,6 +24,7 @@ struct Knobs {
     int     gemm_ksplit;        // gemm_q4k_tc.cu: CTAs along K per tile (0 = choose)
     int     wide_min;           // smallest N q4k_mul_mat hands to the batched decode kernel (gemv_q4k_wide.cu); below it: gemv_q4k_mma.cu
     int64_t n1s_min_k;          // N == 1: matrices with at least this many columns (and >= 2048 rows) take the streamed kernel (gemv_q4k_n1s.cu)
+    int64_t n1s_ll_min_rows;    // row-sharded LL form: shards with at least this many rows (and K >= n1s_min_k) take the streamed kernel
     int64_t n1s_min_bytes;      // ... or, if > 0, with at least this many weight bytes (development)
     int     tma_boxes;          // 1 = the decode kernels fetch weight tiles with TMA tensor copies (one per tile), 0 = one bulk copy per row
     int     wide_dbg;           // gemv_q4k_wide.cu timing experiments (results are wrong when set)

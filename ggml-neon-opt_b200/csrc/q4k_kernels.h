@@ -93,8 +93,9 @@ cudaError_t launch_gemv_q4k_wide(const void *w, int64_t M, int64_t K, int64_t w_
 // streamed single-column decode (gemv_q4k_n1s.cu): F32 activation row, quantized into `workspace` (n1s_workspace_bytes) and
 // streamed next to the weights; same bits as gemv_q4k_mma.cu at N == 1
 size_t n1s_workspace_bytes(int64_t K);
+// ll != nullptr: the row-sharded form — rows leave as LL pairs at row offset dst_row0 and the launch's tail gathers (dst unused)
 cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_row_stride_bytes, const float *x, float *dst,
-                                void *workspace, bool pdl, cudaStream_t stream);
+                                void *workspace, bool pdl, cudaStream_t stream, const LLExchange *ll = nullptr, int64_t dst_row0 = 0);
 
 // up to four matrices with the same K on ONE activation tensor as one GEMM launch (one quantizer pass, one grid over all row tiles)
 cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int64_t *M, int64_t K, int64_t w_row_stride_bytes,
