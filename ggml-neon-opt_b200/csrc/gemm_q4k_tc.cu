@@ -64,14 +64,15 @@ constexpr int MMA_WARP = EPI_WARPS + PROD_WARPS, LOAD_WARP = MMA_WARP + 1;
 constexpr int GEMM_THREADS = (LOAD_WARP + 1) * 32;   // 832
 constexpr int SMEM_B = 0, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES, SMEM_AM = SMEM_RAW + RAW_SLOTS * RAW_SLOT_BYTES;
 constexpr int SMEM_BMIN = SMEM_AM + AM_SLOTS * MIN_TILE_BYTES, SMEM_DX = SMEM_BMIN + BMIN_SLOTS * MIN_TILE_BYTES;
-constexpr int SMEM_BARS = SMEM_DX + EPI_WARPS * 2 * 32 * 4;
+constexpr int SMEM_BARS = SMEM_DX + EPI_WARPS * 3 * 32 * 4;   // DX: d_x, three buffers per epilogue warp
 constexpr int SMEM_TOTAL = SMEM_BARS + 256;
 constexpr int TMEM_COLS = 512;
 constexpr uint32_t TM_HI = 0, TM_LO = 128, TM_MIN = 256, TM_A = 384;   // TMEM column of each region
 constexpr uint32_t TM_A_STAGE = 64, TM_A_TILE = 32;  // columns per A stage (hi + lo) and per tile (128 bytes of K)
 constexpr uint32_t SBO_BYTES = 8 * BK;                // int8 B tile: next 8-column group of core matrices
 constexpr uint32_t MIN_SBO_BYTES = 256;               // mins tiles: 8 rows x (2 chunks x 16 bytes)
-constexpr size_t FLAG_BYTES = 1024;                   // split-K turnstiles at the end of the workspace (<= 148 tiles x 4 bytes)
+constexpr size_t FLAG_BYTES = 1024;                   // one flag word per CTA behind the quantized activations
+constexpr size_t MAX_CTAS = 160, PARTIAL_BYTES = (size_t)BM * 128 * 4;   // persistent grid <= SM count; a parked 128 x 128 fp32 tile per CTA
 
 #ifdef Q4K_GEMM_TRACE
 __device__ long long g_gemm_trace[16][256];
@@ -95,8 +96,10 @@ struct GemmParams {
     const float *xd;        // [nb][Nld]
     const uint8_t *bmin;    // fp16 mins tiles: [column tile][superblock][4 KB canonical tile: 128 columns x (bh[8] | bl[8])]
     int64_t N, Nld;
-    int ksplit;             // CTAs along K per output tile (gridDim.z); 1 = the tile's CTA owns all of K
-    int *flags;             // ksplit > 1: one zero-initialised turnstile word per output tile
+    int ntn;                // column tiles
+    int64_t units;          // (tile, superblock) work units of the launch = tiles x nb, cut into gridDim.x equal ranges
+    int *flags;             // one zero-initialised word per CTA: "this CTA's parked partial sums are in the workspace"
+    float *partial;         // [gridDim.x][128 columns][128 rows] fp32: the sums of a range's first tile when that tile started earlier
     int32_t *dump_sumi, *dump_summ;   // DUMP instantiation (parity): [(n*M + m)*nb + b] = the integers the epilogue read from TMEM
 };
 
@@ -104,25 +107,13 @@ struct GemmParams {
 //   B tile of `step`        : one 16 KB bulk copy (the activations are stored pre-tiled in exactly the shared-memory order)
 //   mins tile of `sb`       : one 4 KB bulk copy                                          } with the B tile of step 2*sb
 //   raw weights of `sb`     : one TMA box, 128 rows x 144 bytes (rows past M read as zero) }
-// `step` counts from the CTA's first superblock kb0 (split-K); slots are indexed by the local step / superblock.
+// Slots are indexed by the CTA's running step / superblock count (they run on through the CTA's work items).
 // The raw weights do not depend on the quantizer kernel in front of this one (programmatic dependent launch), the B and
 // mins tiles do: the loader issues the first raw boxes before griddepcontrol.wait.
 __device__ __forceinline__ void loader_issue_raw(const CUtensorMap *wmap, uint32_t smem0, uint32_t rawfull, int m0, int kb, int kb0) {
     mbar_expect_tx(rawfull, RAW_SLOT_BYTES);
     tma_g2s_2d(smem0 + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES, wmap, (kb0 + kb) * BLK_Q4K, m0, rawfull);
 }
-__device__ __forceinline__ void loader_issue_act(const GemmParams &p, uint32_t smem0, uint32_t full, int64_t ntile, int step, int kb0) {
-    const int kb = step >> 1, hh = step & 1, gkb = kb0 + kb;
-#ifdef Q4K_GEMM_DBG_NOB            // timing experiment only (wrong results): the B tile is copied for the first steps only
-    const bool copy_b = step < B_SLOTS;
-#else
-    const bool copy_b = true;
-#endif
-    mbar_expect_tx(full, (copy_b ? TILE_BYTES : 0) + (hh == 0 ? MIN_TILE_BYTES : 0));
-    if (copy_b) bulk_g2s(smem0 + SMEM_B + (step % B_SLOTS) * TILE_BYTES, p.xq + (((ntile * p.nb + gkb) * 2 + hh) << 14), TILE_BYTES, full);
-    if (hh == 0) bulk_g2s(smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + ((ntile * p.nb + gkb) << 12), MIN_TILE_BYTES, full);
-}
-
 // the thread's 64 weights of this step (one 32-byte group of its raw row: low nibbles = sub-block 2j, high nibbles
 // = sub-block 2j + 1) -> 2 x 16 TMEM columns: A_hi = sh * q4, A_lo = sl * q4, K order = element order
 __device__ __forceinline__ void producer_unpack(uint32_t (&hi)[16], uint32_t (&lo)[16], const uint8_t *raw, const uint4 sm, int j) {
@@ -159,6 +150,42 @@ __device__ __forceinline__ void producer_mins(uint8_t *am_tile, int row, const u
     *reinterpret_cast<uint4 *>(dst + LBO_BYTES) = make_uint4(m1[0], m1[1], m1[2], m1[3]);
 }
 
+// One work item of a CTA: superblocks [kb0, kb0 + nbk) of output tile (mat, m0, n0).  The launch is PERSISTENT and split
+// "stream-K" fashion: all (tile, superblock) units of the launch — tiles in (row tile, column tile) order, column tiles of one
+// row tile next to each other (L2) — form one sequence that is cut into gridDim.x contiguous, equal ranges, so every SM works
+// the same number of superblocks whatever the tile count (448 tiles on 148 SMs used to be four waves for three waves' work,
+// the 64-80 tiles of TinyLlama's matrices left half the SMs idle).  A range covers the tail of one tile, whole tiles, and the
+// head of another.  Every role of the CTA walks the same item sequence; barrier slots and phases run on through the items
+// (counters, not tile-local indices), so the next tile's weights and activations are in flight while this one's last
+// accumulators drain.
+struct WorkItem {
+    int tile, kb0, nbk;                 // what the loops need: everything else is derived from `tile` where it is used (registers)
+    int mat, nh, m0, n0, ntile;
+    __device__ __forceinline__ void decode(const GemmParams &p) {
+        const int rt = tile / p.ntn;
+        ntile = tile - rt * p.ntn;
+        mat = 0;
+        while (mat + 1 < p.nmat && rt >= p.tend[mat]) ++mat;
+        m0 = (rt - (mat ? p.tend[mat - 1] : 0)) * BM;
+        n0 = ntile * BN;
+        nh = (int64_t)n0 + HALF_N < p.N ? 2 : 1;           // column halves that hold real columns
+    }
+};
+
+struct WorkRange {
+    int u, u1;                          // units fit 32 bits (the launcher checks)
+    __device__ __forceinline__ WorkRange(const GemmParams &p, int64_t cta, int64_t nctas) : u((int)(p.units * cta / nctas)), u1((int)(p.units * (cta + 1) / nctas)) {}
+    __device__ __forceinline__ bool next(const GemmParams &p, WorkItem &it) {
+        if (u >= u1) return false;
+        it.tile = u / p.nb;
+        it.kb0 = u - it.tile * p.nb;
+        it.nbk = min(p.nb - it.kb0, u1 - u);
+        u += it.nbk;
+        it.decode(p);
+        return true;
+    }
+};
+
 // DUMP: parity instantiation — the same code; the epilogue also writes out every superblock's sumi (= 8 hi + lo) and summ
 template <bool DUMP>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -174,20 +201,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     auto rawfull_bar = [&](int s) { return bar0 + 8u * (2 * B_SLOTS + 4 + s); };   // [RAW_SLOTS] loader -> producers
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int mat = 0;                                          // which matrix of a grouped launch this row tile belongs to
-    while (mat + 1 < p.nmat && (int)blockIdx.y >= p.tend[mat]) ++mat;
-    const CUtensorMap *wmap = &p.wmap[mat];
-    const uint8_t *w_base = p.w[mat];
-    const int64_t M_mat = p.M[mat], dst_stride = p.dst_stride[mat];
-    float *dst_mat = p.dst[mat];
-    const int64_t m0 = (int64_t)((int)blockIdx.y - (mat ? p.tend[mat - 1] : 0)) * BM, n0 = (int64_t)blockIdx.x * BN;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    // split-K: CTA z of a tile owns superblocks [kb0, kb0 + nb) (balanced contiguous parts)
-    const int kb0 = (int)((int64_t)p.nb * blockIdx.z / p.ksplit);
-    const int nb = (int)((int64_t)p.nb * (blockIdx.z + 1) / p.ksplit) - kb0, nsteps = 2 * nb;
-    // column halves of this tile that hold real columns: a tile with <= 64 of them (N <= 64, or the ragged last tile) runs
-    // half the MMAs and half the epilogue
-    const int nh = n0 + HALF_N < p.N ? 2 : 1;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < B_SLOTS; ++s) { mbar_init(full_bar(s), PROD_THREADS + 1); mbar_init(done_bar(s), 1); }
@@ -203,187 +217,207 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_ptr_s;
-
     if (warp < EPI_WARPS) {
+        WorkRange range(p, blockIdx.x, gridDim.x);
+        WorkItem it;
         // ===================== epilogue: TMEM -> registers, per-superblock fp32 scales =====================
         const int qd = warp & 3, g = warp >> 2;                               // lane quadrant, column group (16 wide, both halves)
-        const int64_t row = m0 + 32 * qd + lane;
-        const uint8_t *wrow = w_base + (row < M_mat ? row : M_mat - 1) * p.w_stride;
-        float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 64;   // [buffer][half 0: 16 | half 1: 16], private to the warp
-        int64_t ncl = n0 + HALF_N * (lane >> 4) + EPI_COLS * g + (lane & 15); // the column whose d_x this lane fetches
-        if (ncl >= p.N) ncl = p.N - 1;
-        uint64_t acc[2][EPI_COLS / 2];                                        // fp32 pairs
-#pragma unroll
-        for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
-        wrow += (int64_t)kb0 * BLK_Q4K;
-        const float *xdk = p.xd + (int64_t)kb0 * p.Nld;
-        uint32_t dd_next = *reinterpret_cast<const uint32_t *>(wrow);
-        asm volatile("griddepcontrol.wait;" ::: "memory");      // xd is written by the quantizer kernel in front of this one
-        dxw[lane] = xdk[ncl];                                                 // superblock 0 -> buffer 0
-        __syncwarp();
-        const uint32_t tbase = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g);
-        for (int kb = 0; kb < nb; ++kb) {
-            const uint32_t dd = dd_next;
-            float dx_next = 0.0f;
-            if (kb + 1 < nb) {
-                dd_next = *reinterpret_cast<const uint32_t *>(wrow + (int64_t)(kb + 1) * BLK_Q4K);
-                dx_next = xdk[(int64_t)(kb + 1) * p.Nld + ncl];
+        // d_x of a (column, superblock) is prefetched by the warp itself with a 4-byte cp.async into a private buffer, two
+        // superblocks ahead: as a plain global load in this loop it is sunk to its use by the compiler and stalls the warp for a
+        // global-memory round trip at the top of every superblock.  {d, dmin} of a (row, superblock) is read from the raw row in
+        // shared memory (a cp.async per lane from 32 different rows costs 31 extra shared-memory wavefronts per warp and superblock,
+        // +8% run time: profiles/r2_gemm_streamk.txt).
+        float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 96;                              // [3][half 0: 16 | half 1: 16]
+        // (warp-uniform: the shuffle lets the compiler keep it in a uniform register instead of spilling it around the loop)
+        const uint32_t tbase = __shfl_sync(0xffffffffu, tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g), 0);
+        uint32_t hpar = 0u;                                                   // bit h: phase of accumulator half h's barriers
+        int bc = 0, bn = 0;                                                   // d_x buffers: of the current superblock, of the next request
+        int gsb = 0;                                                          // superblocks of this CTA so far (the loader's raw slots)
+        bool waited = false;
+        while (range.next(p, it)) {
+            const int nh = it.nh;
+            // next d_x to request: this lane's column, one row of xd per superblock
+            const float *xnext;
+            {
+                int64_t ncl = (int64_t)it.n0 + HALF_N * (lane >> 4) + EPI_COLS * g + (lane & 15);   // the column whose d_x this lane fetches
+                if (ncl >= p.N) ncl = p.N - 1;
+                xnext = p.xd + (int64_t)it.kb0 * p.Nld + ncl;
             }
-            const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));   // {d, dmin} of this row's superblock
-            const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
+            auto prefetch = [&]() {          // into buffer bn
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(dxw + bn * 32 + lane)), "l"(xnext) : "memory");
+                bn = bn == 2 ? 0 : bn + 1;
+                xnext += p.Nld;
+            };
+            uint64_t acc[2][EPI_COLS / 2];                                        // fp32 pairs
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (h >= nh) break;
-                mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (uint32_t)(kb & 1));
-                if (lane == 0 && g == 0 && qd == 0) TR(8 + 2 * h, kb);
-                tc_fence_after();
-                const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + (kb & 1) * 32 + 16 * h);
-#if Q4K_GEMM_DRAIN == 0
+            for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
+            if (!waited) {                   // xd is written by the quantizer kernel in front of this one
+                asm volatile("griddepcontrol.wait;" ::: "memory");
+                waited = true;
+            }
+            prefetch();
+            if (it.nbk > 1) prefetch();
+            for (int kb = 0; kb < it.nbk; ++kb) {
+                asm volatile("cp.async.wait_all;" ::: "memory");    // the scales of superblocks kb and kb + 1 have landed
+                __syncwarp();
+                if (kb + 2 < it.nbk) prefetch();
+                // {d, dmin} of this row's block: the first four bytes of its raw row, in the loader's slot since before the producers
+                // unpacked it (the wait below is long complete: it acquires the TMA's bytes) and until every epilogue thread has
+                // handed this superblock's accumulators back (the loader refills the slot for superblock + 4 behind MMAs that need them)
+                mbar_wait(rawfull_bar(gsb % RAW_SLOTS), (uint32_t)((gsb / RAW_SLOTS) & 1));
+                const uint32_t dd = *reinterpret_cast<const uint32_t *>(smem + SMEM_RAW + (gsb % RAW_SLOTS) * RAW_SLOT_BYTES + (32 * qd + lane) * RAW_ROW_BYTES);
+                const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));
+                const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
 #pragma unroll
-                for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
-                    uint32_t vh[8], vl[8], vm[8];
-                    const uint32_t ta = tbase + HALF_N * h + 8 * c8;
-#ifdef Q4K_GEMM_DBG_NOLD          // timing experiment only (wrong results): no tcgen05.ld traffic
+                for (int h = 0; h < 2; ++h) {
+                    if (h >= nh) break;
+                    mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (hpar >> h) & 1u);
+                    hpar ^= 1u << h;
+                    tc_fence_after();
+                    const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + bc * 32 + 16 * h);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) { vh[i] = kb + i; vl[i] = kb; vm[i] = 0; }
-#else
-                    tmem_ld8(ta + TM_HI, vh); tmem_ld8(ta + TM_LO, vl); tmem_ld8(ta + TM_MIN, vm);
-                    tmem_ld_wait();
-#endif
-                    if (c8 == EPI_COLS / 8 - 1) {          // everything of this half is in registers: hand the columns back
-                        tc_fence_before();
-                        if (lane == 0 && g == 0 && qd == 0) TR(9 + 2 * h, kb);
-                        mbar_arrive(tempty_bar(h));
-                    }
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
-                        const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
-                        if constexpr (DUMP) {
-                            const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 8 * c8 + 2 * i;
-                            if (row < M_mat && n < p.N) {
-                                p.dump_sumi[(n * M_mat + row) * p.nb + kb0 + kb] = s0;
-                                p.dump_summ[(n * M_mat + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
-                            }
-                            if (row < M_mat && n + 1 < p.N) {
-                                p.dump_sumi[((n + 1) * M_mat + row) * p.nb + kb0 + kb] = s1;
-                                p.dump_summ[((n + 1) * M_mat + row) * p.nb + kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
-                            }
+                    for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
+                        uint32_t vh[8], vl[8], vm[8];
+                        const uint32_t ta = tbase + HALF_N * h + 8 * c8;
+                        tmem_ld8(ta + TM_HI, vh); tmem_ld8(ta + TM_LO, vl); tmem_ld8(ta + TM_MIN, vm);
+                        tmem_ld_wait();
+                        if (c8 == EPI_COLS / 8 - 1) {          // everything of this half is in registers: hand the columns back
+                            tc_fence_before();
+                            mbar_arrive(tempty_bar(h));
                         }
-                        uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
-                        t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
-                        acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
+                            const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
+                            if constexpr (DUMP) {
+                                const int64_t M_mat = p.M[it.mat], row = (int64_t)it.m0 + 32 * qd + lane;
+                                const int64_t n = (int64_t)it.n0 + HALF_N * h + EPI_COLS * g + 8 * c8 + 2 * i;
+                                if (row < M_mat && n < p.N) {
+                                    p.dump_sumi[(n * M_mat + row) * p.nb + it.kb0 + kb] = s0;
+                                    p.dump_summ[(n * M_mat + row) * p.nb + it.kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
+                                }
+                                if (row < M_mat && n + 1 < p.N) {
+                                    p.dump_sumi[((n + 1) * M_mat + row) * p.nb + it.kb0 + kb] = s1;
+                                    p.dump_summ[((n + 1) * M_mat + row) * p.nb + it.kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
+                                }
+                            }
+                            // (packed f32x2: measured faster than scalar fp32 despite the register-pair moves it needs)
+                            uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
+                            t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
+                            acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
+                        }
                     }
                 }
-#else
-                // The hand-back of this half's TMEM columns is on the kernel's critical path (the tensor core cannot start
-                // the next superblock's half before it: profiles/r1_gemm_trace_v5.txt), so: every load first, arithmetic
-                // after the arrive.  hi / lo are folded to sumi before the mins are loaded (register budget: 78).
-                const uint32_t ta = tbase + HALF_N * h;
-                int si[EPI_COLS];
-                {
-                    uint32_t vh[EPI_COLS], vl[EPI_COLS];
-                    tmem_ld16(ta + TM_HI, vh); tmem_ld16(ta + TM_LO, vl);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < EPI_COLS; ++i) si[i] = ((int)vh[i] << 3) + (int)vl[i];
-                }
-                uint32_t vm[EPI_COLS];
-                tmem_ld16(ta + TM_MIN, vm);
-                tmem_ld_wait();
-                tc_fence_before();
-                if (lane == 0 && g == 0 && qd == 0) TR(9 + 2 * h, kb);
-                mbar_arrive(tempty_bar(h));
-#pragma unroll
-                for (int i = 0; i < EPI_COLS / 2; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
-                    uint64_t t = mul2(d2, pack2((float)si[2 * i], (float)si[2 * i + 1]));
-                    t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
-                    acc[h][i] = fma2(dxk[i], t, acc[h][i]);
-                }
-#endif
-                if (lane == 0 && g == 0 && qd == 0) TR(12 + 2 * h, kb);
+                bc = bc == 2 ? 0 : bc + 1;
+                ++gsb;
             }
-            dxw[((kb + 1) & 1) * 32 + lane] = dx_next;                        // last read during superblock kb - 1
-            __syncwarp();
-        }
-        // split-K: the parts of a tile add their sums in K order through a turnstile (part z waits until z - 1 has stored),
-        // so the float result is one fixed association.  All CTAs of a split launch are co-resident (the launcher only
-        // splits while tiles x parts <= SMs), so the wait cannot deadlock.
-        const int z = blockIdx.z;
-        int *flag = p.ksplit > 1 ? p.flags + (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
-        if (z > 0) {
-            if (lane == 0) {
-                int seen;
-                do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory"); } while (seen != z);
+            // ---- the item's sums leave the registers.  A tile that lies inside one range is stored.  A split tile: the CTAs that
+            // hold its LATER superblocks meet it FIRST in their ranges and park their sums in the workspace (one slot per CTA, then
+            // a flag); the CTA that holds its first superblocks meets it LAST, adds the parked parts in K order and stores — it
+            // never waits for work that has not been done long ago, and nobody waits for it.  One fixed association per launch
+            // shape and SM count; two runs give the same bits.
+            {   // the tile's coordinates again, from the tile number alone: nothing of them stays live through the superblock loop
+                int tile = it.tile;
+                asm volatile("" : "+r"(tile));
+                it.tile = tile;
+                it.decode(p);
             }
-            __syncwarp();
-        }
-        if (row < M_mat) {
+            const int64_t M_mat = p.M[it.mat];
+            const int64_t row = (int64_t)it.m0 + 32 * qd + lane;
+            const bool first = it.kb0 == 0, last = it.kb0 + it.nbk == p.nb;
+            if (!first) {
+                float *part = p.partial + (size_t)blockIdx.x * (BM * BN);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (h >= nh) break;
-                if (z > 0) {     // the earlier parts' sums: all loads of a half first (independent: one L2 round trip), then the adds
-                    float prev[EPI_COLS];
-#pragma unroll
-                    for (int c = 0; c < EPI_COLS; ++c) {
-                        const int64_t n = n0 + HALF_N * h + EPI_COLS * g + c;
-                        prev[c] = n < p.N ? __ldcg(dst_mat + n * dst_stride + row) : 0.0f;
-                    }
+                for (int h = 0; h < 2; ++h) {
+                    if (h >= it.nh) break;
 #pragma unroll
                     for (int c = 0; c < EPI_COLS / 2; ++c) {
                         float a0, a1;
                         unpack2(acc[h][c], a0, a1);
-                        acc[h][c] = pack2(__fadd_rn(prev[2 * c], a0), __fadd_rn(prev[2 * c + 1], a1));
+                        const int col = HALF_N * h + EPI_COLS * g + 2 * c;
+                        __stcg(part + col * BM + 32 * qd + lane, a0);
+                        __stcg(part + (col + 1) * BM + 32 * qd + lane, a1);
                     }
                 }
+                __threadfence();
+                asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // all 16 epilogue warps have stored
+                if (threadIdx.x == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p.flags + blockIdx.x), "r"(1) : "memory");
+            } else {
+                if (!last) {
+                    // the parts that follow: CTA c + 1 starts with superblock kb0 + nbk of this tile, and so on until K is covered
+                    int covered = it.nbk;
+                    for (int64_t c = (int64_t)blockIdx.x + 1; covered < p.nb; ++c) {
+                        const int64_t r0 = p.units * c / gridDim.x, r1 = p.units * (c + 1) / gridDim.x;
+                        if (lane == 0) {
+                            int seen;
+                            do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(p.flags + c) : "memory"); } while (seen != 1);
+                        }
+                        __syncwarp();
+                        const float *part = p.partial + (size_t)c * (BM * BN);
 #pragma unroll
-                for (int c = 0; c < EPI_COLS / 2; ++c) {
-                    const int64_t n = n0 + HALF_N * h + EPI_COLS * g + 2 * c;
-                    float a0, a1;
-                    unpack2(acc[h][c], a0, a1);
-                    if (n < p.N) dst_mat[n * dst_stride + row] = a0;
-                    if (n + 1 < p.N) dst_mat[(n + 1) * dst_stride + row] = a1;
+                        for (int h = 0; h < 2; ++h) {
+                            if (h >= it.nh) break;
+                            float prev[EPI_COLS];
+#pragma unroll
+                            for (int cc = 0; cc < EPI_COLS; ++cc) prev[cc] = __ldcg(part + (HALF_N * h + EPI_COLS * g + cc) * BM + 32 * qd + lane);
+#pragma unroll
+                            for (int cc = 0; cc < EPI_COLS / 2; ++cc) {
+                                float a0, a1;
+                                unpack2(acc[h][cc], a0, a1);
+                                acc[h][cc] = pack2(__fadd_rn(a0, prev[2 * cc]), __fadd_rn(a1, prev[2 * cc + 1]));
+                            }
+                        }
+                        covered += (int)min((int64_t)(p.nb - covered), r1 - r0);
+                    }
+                }
+                if (row < M_mat) {
+                    float *dst_mat = p.dst[it.mat];
+                    const int64_t dst_stride = p.dst_stride[it.mat];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        if (h >= it.nh) break;
+#pragma unroll
+                        for (int c = 0; c < EPI_COLS / 2; ++c) {
+                            const int64_t n = (int64_t)it.n0 + HALF_N * h + EPI_COLS * g + 2 * c;
+                            float a0, a1;
+                            unpack2(acc[h][c], a0, a1);
+                            if (n < p.N) dst_mat[n * dst_stride + row] = a0;
+                            if (n + 1 < p.N) dst_mat[(n + 1) * dst_stride + row] = a1;
+                        }
+                    }
                 }
             }
-        }
-        if (p.ksplit > 1 && z + 1 < p.ksplit) {
-            __threadfence();
-            asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // all 16 epilogue warps have stored
-            if (threadIdx.x == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(flag), "r"(z + 1) : "memory");
         }
     } else if (warp < EPI_WARPS + PROD_WARPS) {
         // ===================== producers: Q4_K bytes -> A_hi / A_lo in TMEM; activations -> B slot =====================
         const int t = threadIdx.x - EPI_WARPS * 32, pw = t >> 5;
         const int qd = pw & 3, khalf = pw >> 2, r = 32 * qd + lane;           // TMEM lane = weight row of the tile; which 64 of the 128 K
-        const uint32_t ta_base = tmem + ((uint32_t)(32 * qd) << 16) + TM_A + 16u * khalf;
+        const uint32_t ta_base = __shfl_sync(0xffffffffu, tmem + ((uint32_t)(32 * qd) << 16) + TM_A + 16u * khalf, 0);
         uint4 sm = make_uint4(0, 0, 0, 0);
-        for (int step = 0; step < nsteps; ++step) {
-            const int kb = step >> 1, hh = step & 1;
-            if (hh == 0) mbar_wait_long<Q4K_GEMM_WAIT>(rawfull_bar(kb % RAW_SLOTS), (uint32_t)((kb / RAW_SLOTS) & 1));
-            if (t == 0) TR(0, step);
-            const uint8_t *raw = smem + SMEM_RAW + (kb % RAW_SLOTS) * RAW_SLOT_BYTES + r * RAW_ROW_BYTES;
-            if (hh == 0) sm = unpack_scales_mins(*reinterpret_cast<const uint4 *>(raw));
-            uint32_t hi[16], lo[16];
-            producer_unpack(hi, lo, raw, sm, 2 * hh + khalf);
-            // A stage step % 2 was last read by the MMAs of step - 2
-            if (step >= 2) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar((step - 2) % B_SLOTS), (uint32_t)(((step - 2) / B_SLOTS) & 1));
-            if (t == 0) TR(1, step);
-            tc_fence_after();
-            const uint32_t ta = ta_base + (uint32_t)(step & 1) * TM_A_STAGE;
-#ifdef Q4K_GEMM_DBG_NOST           // timing experiment only (wrong results): no tcgen05.st traffic after the first steps
-            if (step < 2)
-#endif
-            {
-            tmem_st16(ta, hi);
-            tmem_st16(ta + TM_A_TILE, lo);
+        int gstep = 0;                                                        // pipeline steps of this CTA so far
+        WorkRange range(p, blockIdx.x, gridDim.x);
+        WorkItem it;
+        while (range.next(p, it)) {
+            for (int ls = 0; ls < 2 * it.nbk; ++ls, ++gstep) {
+                const int gkb = gstep >> 1, hh = gstep & 1;
+                if (hh == 0) mbar_wait_long<Q4K_GEMM_WAIT>(rawfull_bar(gkb % RAW_SLOTS), (uint32_t)((gkb / RAW_SLOTS) & 1));
+                const uint8_t *raw = smem + SMEM_RAW + (gkb % RAW_SLOTS) * RAW_SLOT_BYTES + r * RAW_ROW_BYTES;
+                if (hh == 0) sm = unpack_scales_mins(*reinterpret_cast<const uint4 *>(raw));
+                uint32_t hi[16], lo[16];
+                producer_unpack(hi, lo, raw, sm, 2 * hh + khalf);
+                // A stage gstep % 2 was last read by the MMAs of step gstep - 2
+                if (gstep >= 2) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar((gstep - 2) % B_SLOTS), (uint32_t)(((gstep - 2) / B_SLOTS) & 1));
+                tc_fence_after();
+                const uint32_t ta = ta_base + (uint32_t)(gstep & 1) * TM_A_STAGE;
+                tmem_st16(ta, hi);
+                tmem_st16(ta + TM_A_TILE, lo);
+                if (hh == 0 && khalf == 0) {
+                    producer_mins(smem + SMEM_AM + (gkb % AM_SLOTS) * MIN_TILE_BYTES, r, sm);
+                    fence_async_smem();                      // generic-proxy st.shared -> the tensor core's async proxy
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                mbar_arrive(full_bar(gstep % B_SLOTS));
             }
-            if (hh == 0 && khalf == 0) {
-                producer_mins(smem + SMEM_AM + (kb % AM_SLOTS) * MIN_TILE_BYTES, r, sm);
-                fence_async_smem();                      // generic-proxy st.shared -> the tensor core's async proxy
-            }
-            tmem_st_wait();
-            tc_fence_before();
-            mbar_arrive(full_bar(step % B_SLOTS));
-            if (t == 0) TR(2, step);
         }
     } else if (warp == MMA_WARP) {
         // ===================== MMA issuer: the whole warp runs the loop (uniform control flow keeps the descriptors in
@@ -392,60 +426,81 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         const uint32_t smem0 = smem_addr(smem);
         const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         const uint64_t desc_hi = umma_desc(0, SBO_BYTES), desc_min_hi = umma_desc(0, MIN_SBO_BYTES);
+        uint32_t hpar = 0u;
+        int gkb = 0;
+        WorkRange range(p, blockIdx.x, gridDim.x);
+        WorkItem it;
         // Per superblock: all 16 MMAs of column half 0 (both K steps), then all 16 of half 1.  A half's TMEM columns are
         // drained by the epilogue while the tensor core works on the other half (a window of half a superblock).
-        for (int kb = 0; kb < nb; ++kb) {
+        while (range.next(p, it)) {
+            for (int kb = 0; kb < it.nbk; ++kb, ++gkb) {
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (h >= nh) break;
+                for (int h = 0; h < 2; ++h) {
+                    if (h >= it.nh) break;
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    const int step = 2 * kb + hh, bslot = step % B_SLOTS;
-                    if (h == 0) {                  // the step's operands: A stage in TMEM, B slot in shared memory
-                        if (lane == 0) TR(4, step);
-                        mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));
-                        if (lane == 0) TR(5, step);
-                    }
-                    if (hh == 0) {                 // new superblock: the previous one must have left this half of TMEM
-                        mbar_wait_long<Q4K_GEMM_WAIT_TEMPTY>(tempty_bar(h), (uint32_t)((kb & 1) ^ 1));
-                        if (lane == 0) TR(6 + h, step);
-                    }
-                    tc_fence_after();
-                    const uint32_t ta = tm + TM_A + (uint32_t)(step & 1) * TM_A_STAGE;
-                    const uint64_t bd0 = desc_hi + (uint64_t)((smem0 + SMEM_B + (uint32_t)bslot * TILE_BYTES) >> 4);
-                    if (elect_one()) {
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int step = 2 * gkb + hh, bslot = step % B_SLOTS;
+                        if (h == 0) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));   // the step's operands
+                        if (hh == 0) {                 // new superblock: the previous one must have left this half of TMEM
+                            mbar_wait_long<Q4K_GEMM_WAIT_TEMPTY>(tempty_bar(h), ((hpar >> h) & 1u) ^ 1u);
+                            hpar ^= 1u << h;
+                        }
+                        tc_fence_after();
+                        const uint32_t ta = tm + TM_A + (uint32_t)(step & 1) * TM_A_STAGE;
+                        const uint64_t bd0 = desc_hi + (uint64_t)((smem0 + SMEM_B + (uint32_t)bslot * TILE_BYTES) >> 4);
+                        if (elect_one()) {
 #pragma unroll
-                        for (int o = 0; o < 2; ++o) {
+                            for (int o = 0; o < 2; ++o) {
 #pragma unroll
-                            for (int j = 0; j < BK / 32; ++j) {
-                                const uint64_t b_desc = bd0 + (uint64_t)((h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES) >> 4);
-                                umma_i8_ts(tm + (o ? TM_LO : TM_HI) + h * HALF_N, ta + o * TM_A_TILE + 8 * j, b_desc, idesc, (uint32_t)((hh | j) != 0));
+                                for (int j = 0; j < BK / 32; ++j) {
+                                    const uint64_t b_desc = bd0 + (uint64_t)((h * (HALF_N / 8) * SBO_BYTES + j * 2 * LBO_BYTES) >> 4);
+                                    umma_i8_ts(tm + (o ? TM_LO : TM_HI) + h * HALF_N, ta + o * TM_A_TILE + 8 * j, b_desc, idesc, (uint32_t)((hh | j) != 0));
+                                }
                             }
+                            if (hh == 1) {             // the superblock's mins (K = 16, fp16), then this half is complete -> epilogue
+                                const uint64_t a_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_AM + (gkb % AM_SLOTS) * MIN_TILE_BYTES) >> 4);
+                                const uint64_t b_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_BMIN + (gkb % BMIN_SLOTS) * MIN_TILE_BYTES + h * (HALF_N / 8) * MIN_SBO_BYTES) >> 4);
+                                umma_f16_ss(tm + TM_MIN + h * HALF_N, a_desc, b_desc, idesc_min, 0u);
+                                umma_commit(tfull_bar(h));
+                            }
+                            if (h == it.nh - 1) umma_commit(done_bar(bslot));   // A stage and B slot consumed by every half -> producers
                         }
-                        if (hh == 1) {             // the superblock's mins (K = 16, fp16), then this half is complete -> epilogue
-                            const uint64_t a_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_AM + (kb % AM_SLOTS) * MIN_TILE_BYTES) >> 4);
-                            const uint64_t b_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_BMIN + (kb % BMIN_SLOTS) * MIN_TILE_BYTES + h * (HALF_N / 8) * MIN_SBO_BYTES) >> 4);
-                            umma_f16_ss(tm + TM_MIN + h * HALF_N, a_desc, b_desc, idesc_min, 0u);
-                            umma_commit(tfull_bar(h));
-                        }
-                        if (h == nh - 1) umma_commit(done_bar(bslot));   // A stage and B slot consumed by every half -> producers
+                        __syncwarp();
                     }
-                    __syncwarp();
                 }
             }
         }
     } else if (lane == 0) {
-        // ===================== loader (one thread): TMA copies, up to B_SLOTS steps ahead of the tensor core =====================
+        // ===================== loader (one thread): TMA copies, up to B_SLOTS steps ahead of the tensor core — through the item
+        // boundaries: the next tile's operands are on their way while this one's last steps run =====================
         const uint32_t smem0 = smem_addr(smem);
-        const int pre = min(nb, RAW_SLOTS);                     // raw boxes that can go out before the quantizer has finished
-        for (int kb = 0; kb < pre; ++kb) loader_issue_raw(wmap, smem0, rawfull_bar(kb % RAW_SLOTS), (int)m0, kb, kb0);
-        asm volatile("griddepcontrol.wait;" ::: "memory");      // the activation tiles come from the kernel in front of this one
-        for (int step = 0; step < nsteps; ++step) {
-            // slot reuse: the MMAs of step - B_SLOTS have completed, so its B slot is free; every producer had arrived for that
-            // step, so the raw slot of superblock step / 2 - RAW_SLOTS has been read; the mins slots likewise
-            if (step >= B_SLOTS) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar(step % B_SLOTS), (uint32_t)(((step - B_SLOTS) / B_SLOTS) & 1));
-            if ((step & 1) == 0 && (step >> 1) >= pre) loader_issue_raw(wmap, smem0, rawfull_bar((step >> 1) % RAW_SLOTS), (int)m0, step >> 1, kb0);
-            loader_issue_act(p, smem0, full_bar(step % B_SLOTS), (int64_t)blockIdx.x, step, kb0);
+        int gstep = 0, pre = 0;
+        bool waited = false;
+        WorkRange range(p, blockIdx.x, gridDim.x);
+        WorkItem it;
+        while (range.next(p, it)) {
+            const CUtensorMap *wmap = &p.wmap[it.mat];
+            if (!waited) {                                          // raw boxes that can go out before the quantizer has finished
+                pre = min(it.nbk, RAW_SLOTS);
+                for (int kb = 0; kb < pre; ++kb) loader_issue_raw(wmap, smem0, rawfull_bar(kb % RAW_SLOTS), (int)it.m0, kb, it.kb0);
+                asm volatile("griddepcontrol.wait;" ::: "memory");  // the activation tiles come from the kernel in front of this one
+                waited = true;
+            }
+            for (int ls = 0; ls < 2 * it.nbk; ++ls, ++gstep) {
+                // slot reuse: the MMAs of step - B_SLOTS have completed, so its B slot is free; every producer had arrived for that
+                // step, so the raw slot of superblock step / 2 - RAW_SLOTS has been read; the mins slots likewise
+                if (gstep >= B_SLOTS) mbar_wait_long<Q4K_GEMM_WAIT>(done_bar(gstep % B_SLOTS), (uint32_t)(((gstep - B_SLOTS) / B_SLOTS) & 1));
+                const int gkb = gstep >> 1;
+                if ((gstep & 1) == 0 && gkb >= pre) {
+                    mbar_expect_tx(rawfull_bar(gkb % RAW_SLOTS), RAW_SLOT_BYTES);
+                    tma_g2s_2d(smem0 + SMEM_RAW + (gkb % RAW_SLOTS) * RAW_SLOT_BYTES, wmap, (it.kb0 + (ls >> 1)) * BLK_Q4K, (int)it.m0, rawfull_bar(gkb % RAW_SLOTS));
+                }
+                const int hh = gstep & 1, akb = it.kb0 + (ls >> 1);
+                const uint32_t full = full_bar(gstep % B_SLOTS);
+                mbar_expect_tx(full, TILE_BYTES + (hh == 0 ? MIN_TILE_BYTES : 0));
+                bulk_g2s(smem0 + SMEM_B + (gstep % B_SLOTS) * TILE_BYTES, p.xq + ((((int64_t)it.ntile * p.nb + akb) * 2 + hh) << 14), TILE_BYTES, full);
+                if (hh == 0) bulk_g2s(smem0 + SMEM_BMIN + (gkb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + (((int64_t)it.ntile * p.nb + akb) << 12), MIN_TILE_BYTES, full);
+            }
         }
     }
 
@@ -511,25 +566,23 @@ cudaError_t launch_gemm_q4k_q8k(const void *, int64_t, int64_t, int64_t, const v
 // workspace layout of the prefill path: int8 tiles | mins tiles | float d   (q4k_mul_mat_workspace_bytes adds them up)
 size_t gemm_workspace_bytes(int64_t K, int64_t N) {
     const size_t nb = (size_t)(K / QK_K), ntiles = ((size_t)N + BN - 1) / BN;
-    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + ((nb * (size_t)N * 4 + 255) & ~(size_t)255) + FLAG_BYTES;
+    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + ((nb * (size_t)N * 4 + 255) & ~(size_t)255) + FLAG_BYTES + MAX_CTAS * PARTIAL_BYTES;
 }
 
-// How many CTAs share one output tile along K.  A launch with fewer tiles than SMs leaves the rest idle (the 32 tiles of
-// 4096 x 14336 x 32).  Measured on B200 (profiles/r1_gemm_split_k.txt): a part costs ~1.5 us per superblock, a turnstile
-// hand-off ~10 superblocks' worth (stores, fence, flag, the next part's L2 reads), so splitting pays only for long K:
-// minimise nb / s + 10 (s - 1) while all CTAs stay co-resident.  4096 x 14336 x 32: 80.7 -> 55 us at s = 2; the
-// 8- and 22-superblock TinyLlama matrices stay unsplit (28.7 vs 23.0 us at 2048 x 2048 x 512).
-static int choose_ksplit(int64_t tiles, int64_t nb) {
-    if (knobs().gemm_ksplit >= 1) return (int)std::min<int64_t>(knobs().gemm_ksplit, nb);      // development / test knob
-    const int sms = sm_count();
-    int best = 1;
-    double best_cost = (double)nb;
-    for (int s = 2; s <= 4; ++s) {
-        if (tiles * s > sms || nb / s < 4) break;
-        const double cost = (double)((nb + s - 1) / s) + 10.0 * (s - 1);
-        if (cost < best_cost - 2.0) { best_cost = cost; best = s; }
-    }
-    return best;
+// The persistent grid.  More tiles than SMs: one CTA per SM, the units cut evenly (no partial last wave: 448 tiles on 148 SMs
+// were four waves for three waves' work).  Fewer tiles than SMs: k CTAs per tile while a part keeps at least 8 superblocks — a
+// split costs a parked tile, a flag and a second pipeline fill, which a short K does not earn back (2048 x 2048 x 512, 64 tiles of
+// 8 superblocks: 21.7 us whole, 24.4 us cut over 148 CTAs), and with every SM on the tensor pipe the chip runs into its power
+// cap, so SMs added to a launch that already fills most of them buy less than their count (4096 x 14336 x 512: 128 tiles whole
+// 95 us, cut over 148 CTAs 102 us).  The development / test knob gemm_ksplit = k > 0 forces tiles x k CTAs (capped at the SM
+// count): another split, another float association, the same integers.
+static int choose_grid(int64_t tiles, int64_t nb) {
+    const int64_t sms = std::min<int64_t>(sm_count(), (int64_t)MAX_CTAS), units = tiles * nb;
+    int64_t g;
+    if (knobs().gemm_ksplit >= 1) g = std::min(sms, tiles * knobs().gemm_ksplit);
+    else if (tiles >= sms) g = sms;
+    else g = tiles * std::max<int64_t>(1, std::min(sms / tiles, nb / 8));
+    return (int)std::max<int64_t>(1, std::min(g, units));
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
@@ -585,8 +638,8 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
         p.tend[k] = (int)mtiles;
     }
     if (p.nmat == 0) return cudaSuccess;
-    if (mtiles > 65535) return cudaErrorNotSupported;
-    const int ksplit = choose_ksplit(ntiles * mtiles, nb);
+    if (ntiles * mtiles * nb >= ((int64_t)1 << 31)) return cudaErrorNotSupported;
+    const int grid_ctas = choose_grid(ntiles * mtiles, nb);
     const int64_t total = nb * N;
     cudaLaunchAttribute pdl_attr[1];
     pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -595,7 +648,7 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
     if (!x) {
         // the workspace already holds the quantized copy of these activations (the mul_mat in front of this one read the same
         // src1: q/k/v, gate/up): only the split-K turnstiles have to be reset
-        if (ksplit > 1 && (e = cudaMemsetAsync(flags, 0, FLAG_BYTES, stream)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(flags, 0, FLAG_BYTES, stream)) != cudaSuccess) return e;
     } else {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)((total + 7) / 8));
@@ -603,19 +656,20 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
         cfg.stream = stream;
         cfg.attrs = pdl_attr;
         cfg.numAttrs = knobs().pdl ? 1 : 0;
-        int *qflags = ksplit > 1 ? flags : nullptr;
+        int *qflags = flags;
         e = cudaLaunchKernelEx(&cfg, quantize_q8_planar_kernel, x, qs, d, bmin, nb, total, x_row_stride_bytes, N, qflags);
         count_launch();
         if (e != cudaSuccess) return e;
     }
     p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
     p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
-    p.ksplit = ksplit; p.flags = flags;
+    p.ntn = (int)ntiles; p.units = ntiles * mtiles * nb; p.flags = flags;
+    p.partial = reinterpret_cast<float *>(reinterpret_cast<char *>(flags) + FLAG_BYTES);
     p.dump_sumi = dump ? dump->sumi : nullptr; p.dump_summ = dump ? dump->summ : nullptr;
     auto kern = dump ? gemm_q4k_tc_kernel<true> : gemm_q4k_tc_kernel<false>;
     constexpr size_t smem = SMEM_TOTAL;
     if ((e = ensure_max_dynamic_smem((const void *)kern, (int)smem)) != cudaSuccess) return e;
-    const dim3 grid((unsigned)ntiles, (unsigned)mtiles, (unsigned)ksplit);              // column tiles of one row tile run together (L2)
+    const dim3 grid((unsigned)grid_ctas);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(GEMM_THREADS);
