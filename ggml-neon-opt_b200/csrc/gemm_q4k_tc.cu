@@ -526,7 +526,7 @@ quantize_q8_planar_kernel(const float *__restrict__ x, int8_t *__restrict__ qs, 
     // reading, so everything waits for that; the GEMM behind it may start its prologue (barriers, TMEM, raw weights) now
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (flags && blockIdx.x == 0) flags[threadIdx.x] = 0;        // the split-K turnstiles of the GEMM that follows (FLAG_BYTES = 256 words)
+    if (flags && blockIdx.x == 0) flags[threadIdx.x] = 0;        // the per-CTA "parked tile" flags of the GEMM that follows (FLAG_BYTES = 256 words)
     const int lane = threadIdx.x & 31;
     const int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (blk >= nblocks_total) return;
@@ -647,7 +647,7 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
     cudaError_t e;
     if (!x) {
         // the workspace already holds the quantized copy of these activations (the mul_mat in front of this one read the same
-        // src1: q/k/v, gate/up): only the split-K turnstiles have to be reset
+        // src1: q/k/v, gate/up): only the per-CTA flags have to be reset
         if ((e = cudaMemsetAsync(flags, 0, FLAG_BYTES, stream)) != cudaSuccess) return e;
     } else {
         cudaLaunchConfig_t cfg = {};

@@ -21,7 +21,7 @@ struct Knobs {
     int     mma_off;            // Q4K_DBG_MMA < 0: never the tensor-pipe decode kernel
     int     mma_kparts, mma_stages, mma_per_sm, mma_contig;   // gemv_q4k_mma.cu launch shape (0 = choose)
     int     tma_stages, tma_per_sm;                            // gemv_q4k_tma.cu
-    int     gemm_ksplit;        // gemm_q4k_tc.cu: CTAs along K per tile (0 = choose)
+    int     gemm_ksplit;        // gemm_q4k_tc.cu: k > 0 forces a persistent grid of tiles x k CTAs; gemm_q6k_tc.cu: CTAs along K per tile (0 = choose)
     int     wide_min;           // smallest N q4k_mul_mat hands to the batched decode kernel (gemv_q4k_wide.cu); below it: gemv_q4k_mma.cu
     int64_t n1s_min_k;          // N == 1: matrices with at least this many columns (and >= 2048 rows) take the streamed kernel (gemv_q4k_n1s.cu)
     int64_t n1s_ll_min_rows;    // row-sharded LL form: shards with at least this many rows (and K >= n1s_min_k) take the streamed kernel

@@ -204,8 +204,9 @@ def test_gemm_integer_stage_is_exact(q4k, gemm_path):
 
 @pytest.mark.parametrize("ksplit", [1, 2, 3, 8])
 def test_gemm_split_k_integer_stage_is_exact_and_deterministic(q4k, gemm_path, ksplit):
-    """Launches with fewer tiles than SMs split K over several CTAs per tile (turnstile epilogue: parts add in K order).
-    Same exact-float construction as above at K = 2048: any lost / doubled superblock or a race in the turnstile shows as a
+    """The persistent grid forced to tiles x ksplit CTAs: tiles are split between CTAs (later parts parked in the workspace, the
+    part with the first superblocks adds them in K order; tests/test_gpu_gemm_streamk.py has the launches with more tiles than SMs).
+    Same exact-float construction as above at K = 2048: any lost / doubled superblock or a race on the flags shows as a
     wrong integer; two runs give identical bits."""
     from oracle import port
     q4k.debug_set("gemm_ksplit", ksplit)

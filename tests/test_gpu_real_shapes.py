@@ -1,6 +1,6 @@
 """GPU parity at BASELINE.json's REAL shapes, through the default dispatch (no forced knobs): C3 (5632x2048x512), C4 (4096x14336 and
-14336x4096 at N = 1 / 8 / 32 / 512: decode kernel with cluster split-K, the batched decode kernel, the GEMM with its automatic
-split-K policy) and C5 (28672x8192 and 8192x28672 at N = 1 / 8: the large-matrix kernel, the separate quantizer).
+14336x4096 at N = 1 / 8 / 32 / 512: decode kernel with cluster split-K, the batched decode kernel, the GEMM with its persistent
+grid) and C5 (28672x8192 and 8192x28672 at N = 1 / 8: the large-matrix kernel, the separate quantizer).
 
 Every row of the matrix is streamed by the kernel under test; a fixed sample of 256 rows — the first tile, a tile in the middle,
 the last rows of the matrix and 64 rows scattered over it — holds weights really quantized by quantize_row_q4_K (the oracle's
