@@ -480,6 +480,7 @@ cudaError_t launch_mma_n(TmaGemvParams p, bool pdl, cudaStream_t stream) {
     const size_t smem = fixed + (size_t)stages * slot;
     if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)MMA_SMEM_MAX)) return ea;
     int64_t grid = (int64_t)sm_count() * per_sm;
+    if (knobs().grid_balance & 4) grid = balanced_grid(p.n_groups, grid / KP) * KP;      // (measured slower here: off by default)
     if (grid > p.n_groups * KP) grid = p.n_groups * KP;
     grid -= grid % KP;                               // whole clusters
     if (grid < KP) grid = KP;

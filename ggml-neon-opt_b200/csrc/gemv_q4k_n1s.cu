@@ -238,7 +238,10 @@ cudaError_t launch_gemv_q4k_n1s(const void *w, int64_t M, int64_t K, int64_t w_r
     p.stages = stages;
     const size_t smem = (size_t)stages * NS_STAGE + fixed + (size_t)stages * 16;
     if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)NS_SMEM_MAX)) return ea;
-    int64_t grid = sm_count();
+    // every CTA the same number of passes: 8192 x 28672 is 256 passes — on 148 CTAs the second round runs with 108 of them, below
+    // what the memory system can feed (26.6 us); on 128 CTAs both rounds run full (24.0 us = 85% of the measured HBM peak)
+    int64_t grid = (knobs().grid_balance & 1) ? balanced_grid(p.passes, sm_count()) : sm_count();
+    if (knobs().n1s_grid > 0) grid = std::min<int64_t>(grid, knobs().n1s_grid);
     if (grid > p.passes) grid = p.passes;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);

@@ -311,7 +311,7 @@ cudaError_t launch_wide_cfg(WideParams p, bool pdl, cudaStream_t stream) {
     p.passes = (p.tiles + TS - 1) / TS;
     const size_t smem = (size_t)stages * stage + fixed + (size_t)stages * 16;
     if (const cudaError_t ea = ensure_max_dynamic_smem((const void *)kern, (int)WIDE_SMEM_MAX)) return ea;
-    int64_t grid = sm_count();
+    int64_t grid = (knobs().grid_balance & 2) ? balanced_grid(p.passes, sm_count()) : sm_count();
     if (grid > p.passes) grid = p.passes;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);

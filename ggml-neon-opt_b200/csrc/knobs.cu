@@ -46,6 +46,8 @@ Knobs read_defaults() {
     k.tma_boxes = env_int("Q4K_DBG_TMA_BOXES", 1);
     k.n1s_min_bytes = env_i64("Q4K_DBG_N1S_MIN_BYTES", 0);           // 0 = no size rule (development: 1 = always)
     k.n1s_min_k = env_i64("Q4K_DBG_N1S_MIN_K", 14336);
+    k.n1s_grid = env_i64("Q4K_DBG_N1S_GRID", 0);
+    k.grid_balance = env_int("Q4K_DBG_GRID_BALANCE", 3);
     k.n1s_ll_min_rows = env_i64("Q4K_DBG_N1S_LL_MIN_ROWS", 4096);
     k.q6k_fuse_limit = env_i64("Q6K_DBG_FUSE_LIMIT", 32768);
     k.q6k_stages = env_int("Q6K_DBG_STAGES", 0);
@@ -94,7 +96,7 @@ int q4k_debug_set(const char *name, int64_t value) {
         {"big_matrix_bytes", nullptr, &k.big_matrix_bytes}, {"pdl", &k.pdl, nullptr}, {"gemv_config", &k.gemv_config, nullptr},
         {"mma_off", &k.mma_off, nullptr}, {"mma_kparts", &k.mma_kparts, nullptr}, {"mma_stages", &k.mma_stages, nullptr},
         {"mma_per_sm", &k.mma_per_sm, nullptr}, {"mma_contig", &k.mma_contig, nullptr}, {"tma_stages", &k.tma_stages, nullptr},
-        {"tma_per_sm", &k.tma_per_sm, nullptr}, {"gemm_ksplit", &k.gemm_ksplit, nullptr}, {"midn_max", &k.midn_max, nullptr}, {"q6k_gemm_min", &k.q6k_gemm_min, nullptr}, {"wide_min", &k.wide_min, nullptr}, {"wide_dbg", &k.wide_dbg, nullptr}, {"tma_boxes", &k.tma_boxes, nullptr}, {"n1s_min_bytes", nullptr, &k.n1s_min_bytes}, {"n1s_min_k", nullptr, &k.n1s_min_k}, {"n1s_ll_min_rows", nullptr, &k.n1s_ll_min_rows},
+        {"tma_per_sm", &k.tma_per_sm, nullptr}, {"gemm_ksplit", &k.gemm_ksplit, nullptr}, {"midn_max", &k.midn_max, nullptr}, {"grid_balance", &k.grid_balance, nullptr}, {"q6k_gemm_min", &k.q6k_gemm_min, nullptr}, {"wide_min", &k.wide_min, nullptr}, {"wide_dbg", &k.wide_dbg, nullptr}, {"tma_boxes", &k.tma_boxes, nullptr}, {"n1s_min_bytes", nullptr, &k.n1s_min_bytes}, {"n1s_min_k", nullptr, &k.n1s_min_k}, {"n1s_grid", nullptr, &k.n1s_grid}, {"n1s_ll_min_rows", nullptr, &k.n1s_ll_min_rows},
         {"q6k_fuse_limit", nullptr, &k.q6k_fuse_limit}, {"q6k_stages", &k.q6k_stages, nullptr},
     };
     for (auto &t : tab) {

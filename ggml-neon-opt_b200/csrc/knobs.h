@@ -25,6 +25,8 @@ struct Knobs {
     int     wide_min;           // smallest N q4k_mul_mat hands to the batched decode kernel (gemv_q4k_wide.cu); below it: gemv_q4k_mma.cu
     int64_t n1s_min_k;          // N == 1: matrices with at least this many columns (and >= 2048 rows) take the streamed kernel (gemv_q4k_n1s.cu)
     int64_t n1s_ll_min_rows;    // row-sharded LL form: shards with at least this many rows (and K >= n1s_min_k) take the streamed kernel
+    int64_t n1s_grid;           // gemv_q4k_n1s.cu: CTAs of the launch (0 = choose)
+    int     grid_balance;       // bit 0: n1s, bit 1: wide, bit 2: mma — persistent grids sized so that every CTA gets the same number of units
     int64_t n1s_min_bytes;      // ... or, if > 0, with at least this many weight bytes (development)
     int     tma_boxes;          // 1 = the decode kernels fetch weight tiles with TMA tensor copies (one per tile), 0 = one bulk copy per row
     int     wide_dbg;           // gemv_q4k_wide.cu timing experiments (results are wrong when set)
@@ -33,6 +35,17 @@ struct Knobs {
     int     q6k_stages;
     int     q6k_gemm_min;       // smallest N q6k_mul_mat hands to the tcgen05 GEMM (gemm_q6k_tc.cu); 0 = never
 };
+
+// A persistent grid of at most gmax CTAs over `units` equal work units: the smallest grid that needs no more rounds than gmax
+// would — every CTA then works the same number of rounds, and no round runs with a fraction of the machine.
+// Only for a few rounds: with many, the partial last round is a small share of the time and the CTAs given up for the balance
+// cost more (measured, tools/knob_sweep.py: 8192 x 28672 N = 1, 256 passes: 148 CTAs 26.8 us, 128 CTAs 24.1 us; 28672 x 8192 N = 8,
+// 448 passes: 28.7 -> 27.5 us; 28672 x 8192 N = 16, 896 passes: 43.6 -> 44.4 us, left alone).
+inline int64_t balanced_grid(int64_t units, int64_t gmax) {
+    if (units <= gmax || gmax < 1) return units;
+    const int64_t rounds = (units + gmax - 1) / gmax;
+    return rounds > 4 ? gmax : (units + rounds - 1) / rounds;
+}
 
 Knobs &knobs();                  // the calling thread's settings (initialised from the process defaults)
 void reset_knobs();              // back to the process defaults (this thread)
