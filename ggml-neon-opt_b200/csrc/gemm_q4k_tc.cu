@@ -57,6 +57,7 @@ constexpr int AM_SLOTS = 2, BMIN_SLOTS = 4;           // mins operands (per supe
 constexpr int TILE_BYTES = BN * BK;                   // 16 KB: the int8 activation tile of a step
 constexpr int MIN_TILE_BYTES = 128 * 16 * 2;          // 4 KB: 128 rows (or columns) x 16 fp16
 constexpr int RAW_ROW_BYTES = BLK_Q4K, RAW_SLOT_BYTES = BM * RAW_ROW_BYTES;
+static_assert(B_SLOTS % 2 == 0 && AM_SLOTS == 2 && (BMIN_SLOTS & (BMIN_SLOTS - 1)) == 0, "the MMA issuer's running slot indices");
 constexpr int EPI_WARPS = 16, PROD_WARPS = 8;
 constexpr int PROD_THREADS = PROD_WARPS * 32;
 constexpr int EPI_COLS = 16;                          // columns per epilogue thread per half
@@ -427,27 +428,32 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         const uint64_t desc_hi = umma_desc(0, SBO_BYTES), desc_min_hi = umma_desc(0, MIN_SBO_BYTES);
         uint32_t hpar = 0u;
-        int gkb = 0;
+        // running slot indices instead of step % 6 etc. (this warp's instruction count sits between the MMAs): B slots are taken
+        // two per superblock (6 slots: a superblock's pair never wraps), the A stage is the K half, mins slots follow the superblock
+        int bslot = 0, amslot = 0, bmslot = 0;
+        uint32_t bpar = 0u;
         WorkRange range(p, blockIdx.x, gridDim.x);
         WorkItem it;
         // Per superblock: all 16 MMAs of column half 0 (both K steps), then all 16 of half 1.  A half's TMEM columns are
         // drained by the epilogue while the tensor core works on the other half (a window of half a superblock).
         while (range.next(p, it)) {
-            for (int kb = 0; kb < it.nbk; ++kb, ++gkb) {
+            const int nh = it.nh;
+            for (int kb = 0; kb < it.nbk; ++kb) {
+                const uint64_t a_min = desc_min_hi + (uint64_t)((smem0 + SMEM_AM + amslot * MIN_TILE_BYTES) >> 4);
+                const uint64_t b_min = desc_min_hi + (uint64_t)((smem0 + SMEM_BMIN + bmslot * MIN_TILE_BYTES) >> 4);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    if (h >= it.nh) break;
+                    if (h >= nh) break;
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) {
-                        const int step = 2 * gkb + hh, bslot = step % B_SLOTS;
-                        if (h == 0) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot), (uint32_t)((step / B_SLOTS) & 1));   // the step's operands
+                        if (h == 0) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot + hh), bpar);   // the step's operands
                         if (hh == 0) {                 // new superblock: the previous one must have left this half of TMEM
                             mbar_wait_long<Q4K_GEMM_WAIT_TEMPTY>(tempty_bar(h), ((hpar >> h) & 1u) ^ 1u);
                             hpar ^= 1u << h;
                         }
                         tc_fence_after();
-                        const uint32_t ta = tm + TM_A + (uint32_t)(step & 1) * TM_A_STAGE;
-                        const uint64_t bd0 = desc_hi + (uint64_t)((smem0 + SMEM_B + (uint32_t)bslot * TILE_BYTES) >> 4);
+                        const uint32_t ta = tm + TM_A + (uint32_t)hh * TM_A_STAGE;
+                        const uint64_t bd0 = desc_hi + (uint64_t)((smem0 + SMEM_B + (uint32_t)(bslot + hh) * TILE_BYTES) >> 4);
                         if (elect_one()) {
 #pragma unroll
                             for (int o = 0; o < 2; ++o) {
@@ -458,16 +464,18 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                                 }
                             }
                             if (hh == 1) {             // the superblock's mins (K = 16, fp16), then this half is complete -> epilogue
-                                const uint64_t a_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_AM + (gkb % AM_SLOTS) * MIN_TILE_BYTES) >> 4);
-                                const uint64_t b_desc = desc_min_hi + (uint64_t)((smem0 + SMEM_BMIN + (gkb % BMIN_SLOTS) * MIN_TILE_BYTES + h * (HALF_N / 8) * MIN_SBO_BYTES) >> 4);
-                                umma_f16_ss(tm + TM_MIN + h * HALF_N, a_desc, b_desc, idesc_min, 0u);
+                                umma_f16_ss(tm + TM_MIN + h * HALF_N, a_min, b_min + (uint64_t)((h * (HALF_N / 8) * MIN_SBO_BYTES) >> 4), idesc_min, 0u);
                                 umma_commit(tfull_bar(h));
                             }
-                            if (h == it.nh - 1) umma_commit(done_bar(bslot));   // A stage and B slot consumed by every half -> producers
+                            if (h == nh - 1) umma_commit(done_bar(bslot + hh));   // A stage and B slot consumed by every half -> producers
                         }
                         __syncwarp();
                     }
                 }
+                bslot += 2;
+                if (bslot == B_SLOTS) { bslot = 0; bpar ^= 1u; }
+                amslot ^= 1;
+                bmslot = (bmslot + 1) & (BMIN_SLOTS - 1);
             }
         }
     } else if (lane == 0) {
