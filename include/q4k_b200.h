@@ -105,7 +105,7 @@ int q4k_mul_mat_noalloc(const void *w_dev, int64_t M, int64_t K, int64_t w_row_s
                         const float *x_dev, int64_t N, int64_t x_row_stride_bytes,
                         float *dst_dev, int64_t dst_col_stride_bytes, void *stream);
 
-/* prefill (N > 12): the mul_mat in front of this one (same stream, same workspace) read the SAME activations — attn_q /
+/* prefill (N > 32, "midn_max"): the mul_mat in front of this one (same stream, same workspace) read the SAME activations — attn_q /
  * attn_k / attn_v or ffn_gate / ffn_up of a layer, separate ggml_mul_mat nodes on one src1 in the reference's graph — so their
  * quantized copy is still in the workspace: run the GEMM only.  The reference quantizes src1 once per node
  * (L/ggml/src/ggml-cpu/ggml-cpu.c:1267-1307).  Q4K_ERR_UNSUPPORTED for N <= 12 (call q4k_mul_mat). */
@@ -227,7 +227,7 @@ int q4k_vec_dot_q4_K_q8_K(int n, float *s_dev, size_t bs, const void *vx_dev, si
  *   summ_dev[(n*M + m)*nb + b]          int32  sum_j m[j] * bsum32[j]
  * dst_dev = dense [N][M] fp32 results of the same launch.  `kernel` picks the product kernel: */
 enum {
-    Q4K_DUMP_DISPATCH    = 0,    /* whatever q4k_mul_mat launches for this shape (decode kernel, or the GEMM for N > 12) */
+    Q4K_DUMP_DISPATCH    = 0,    /* whatever q4k_mul_mat launches for this shape (decode kernels, the batched decode kernel for 2..32 columns, the GEMM above) */
     Q4K_DUMP_TENSOR_PIPE = 1,    /* gemv_q4k_mma_kernel (the default decode kernel; p[j] are its MMA C fragments) */
     Q4K_DUMP_BULK        = 2,    /* gemv_q4k_tma_kernel, default float order */
     Q4K_DUMP_BULK_EXACT  = 3,    /* gemv_q4k_tma_kernel in the reference's AVX2 order */
