@@ -108,7 +108,7 @@ int q4k_mul_mat_noalloc(const void *w_dev, int64_t M, int64_t K, int64_t w_row_s
 /* prefill (N > 32, "midn_max"): the mul_mat in front of this one (same stream, same workspace) read the SAME activations — attn_q /
  * attn_k / attn_v or ffn_gate / ffn_up of a layer, separate ggml_mul_mat nodes on one src1 in the reference's graph — so their
  * quantized copy is still in the workspace: run the GEMM only.  The reference quantizes src1 once per node
- * (L/ggml/src/ggml-cpu/ggml-cpu.c:1267-1307).  Q4K_ERR_UNSUPPORTED for N <= 12 (call q4k_mul_mat). */
+ * (L/ggml/src/ggml-cpu/ggml-cpu.c:1267-1307).  Q4K_ERR_UNSUPPORTED for N <= 32 (call q4k_mul_mat). */
 int q4k_mul_mat_reuse(const void *w_dev, int64_t M, int64_t K, int64_t w_row_stride_bytes, int64_t N,
                       float *dst_dev, int64_t dst_col_stride_bytes, void *workspace_dev, size_t workspace_bytes, void *stream);
 
