@@ -98,6 +98,7 @@ struct GemmParams {
     const uint8_t *bmin;    // fp16 mins tiles: [column tile][superblock][4 KB canonical tile: 128 columns x (bh[8] | bl[8])]
     int64_t N, Nld;
     int ntn;                // column tiles
+    int halves;             // 1: the work units are 64-column HALF tiles (few tiles, every tile has two real halves: twice the CTAs, each half as wide)
     int64_t units;          // (tile, superblock) work units of the launch = tiles x nb, cut into gridDim.x equal ranges
     int *flags;             // one zero-initialised word per CTA: "this CTA's parked partial sums are in the workspace"
     float *partial;         // [gridDim.x][128 columns][128 rows] fp32: the sums of a range's first tile when that tile started earlier
@@ -161,15 +162,17 @@ __device__ __forceinline__ void producer_mins(uint8_t *am_tile, int row, const u
 // accumulators drain.
 struct WorkItem {
     int tile, kb0, nbk;                 // what the loops need: everything else is derived from `tile` where it is used (registers)
-    int mat, nh, m0, n0, ntile;
+    int mat, h0, h1, m0, n0, ntile;     // [h0, h1): the 64-column halves of the tile this item computes
     __device__ __forceinline__ void decode(const GemmParams &p) {
-        const int rt = tile / p.ntn;
-        ntile = tile - rt * p.ntn;
+        const int t = p.halves ? tile >> 1 : tile;
+        const int rt = t / p.ntn;
+        ntile = t - rt * p.ntn;
         mat = 0;
         while (mat + 1 < p.nmat && rt >= p.tend[mat]) ++mat;
         m0 = (rt - (mat ? p.tend[mat - 1] : 0)) * BM;
         n0 = ntile * BN;
-        nh = (int64_t)n0 + HALF_N < p.N ? 2 : 1;           // column halves that hold real columns
+        if (p.halves) { h0 = tile & 1; h1 = h0 + 1; }
+        else { h0 = 0; h1 = (int64_t)n0 + HALF_N < p.N ? 2 : 1; }     // halves that hold real columns
     }
 };
 
@@ -236,7 +239,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         int gsb = 0;                                                          // superblocks of this CTA so far (the loader's raw slots)
         bool waited = false;
         while (range.next(p, it)) {
-            const int nh = it.nh;
+            const int h0 = it.h0, h1 = it.h1;
             // next d_x to request: this lane's column, one row of xd per superblock
             const float *xnext;
             {
@@ -271,7 +274,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                 const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    if (h >= nh) break;
+                    if (h < h0 || h >= h1) continue;
                     mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (hpar >> h) & 1u);
                     hpar ^= 1u << h;
                     tc_fence_after();
@@ -329,7 +332,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                 float *part = p.partial + (size_t)blockIdx.x * (BM * BN);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    if (h >= it.nh) break;
+                    if (h < it.h0 || h >= it.h1) continue;
 #pragma unroll
                     for (int c = 0; c < EPI_COLS / 2; ++c) {
                         float a0, a1;
@@ -356,7 +359,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                         const float *part = p.partial + (size_t)c * (BM * BN);
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
-                            if (h >= it.nh) break;
+                            if (h < it.h0 || h >= it.h1) continue;
                             float prev[EPI_COLS];
 #pragma unroll
                             for (int cc = 0; cc < EPI_COLS; ++cc) prev[cc] = __ldcg(part + (HALF_N * h + EPI_COLS * g + cc) * BM + 32 * qd + lane);
@@ -375,7 +378,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                     const int64_t dst_stride = p.dst_stride[it.mat];
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        if (h >= it.nh) break;
+                        if (h < it.h0 || h >= it.h1) continue;
 #pragma unroll
                         for (int c = 0; c < EPI_COLS / 2; ++c) {
                             const int64_t n = (int64_t)it.n0 + HALF_N * h + EPI_COLS * g + 2 * c;
@@ -437,16 +440,16 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         // Per superblock: all 16 MMAs of column half 0 (both K steps), then all 16 of half 1.  A half's TMEM columns are
         // drained by the epilogue while the tensor core works on the other half (a window of half a superblock).
         while (range.next(p, it)) {
-            const int nh = it.nh;
+            const int h0 = it.h0, h1 = it.h1;
             for (int kb = 0; kb < it.nbk; ++kb) {
                 const uint64_t a_min = desc_min_hi + (uint64_t)((smem0 + SMEM_AM + amslot * MIN_TILE_BYTES) >> 4);
                 const uint64_t b_min = desc_min_hi + (uint64_t)((smem0 + SMEM_BMIN + bmslot * MIN_TILE_BYTES) >> 4);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    if (h >= nh) break;
+                    if (h < h0 || h >= h1) continue;
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) {
-                        if (h == 0) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot + hh), bpar);   // the step's operands
+                        if (h == h0) mbar_wait_long<Q4K_GEMM_WAIT>(full_bar(bslot + hh), bpar);   // the step's operands
                         if (hh == 0) {                 // new superblock: the previous one must have left this half of TMEM
                             mbar_wait_long<Q4K_GEMM_WAIT_TEMPTY>(tempty_bar(h), ((hpar >> h) & 1u) ^ 1u);
                             hpar ^= 1u << h;
@@ -467,7 +470,7 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                                 umma_f16_ss(tm + TM_MIN + h * HALF_N, a_min, b_min + (uint64_t)((h * (HALF_N / 8) * MIN_SBO_BYTES) >> 4), idesc_min, 0u);
                                 umma_commit(tfull_bar(h));
                             }
-                            if (h == nh - 1) umma_commit(done_bar(bslot + hh));   // A stage and B slot consumed by every half -> producers
+                            if (h == h1 - 1) umma_commit(done_bar(bslot + hh));   // A stage and B slot consumed by every half -> producers
                         }
                         __syncwarp();
                     }
@@ -505,9 +508,12 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                 }
                 const int hh = gstep & 1, akb = it.kb0 + (ls >> 1);
                 const uint32_t full = full_bar(gstep % B_SLOTS);
-                mbar_expect_tx(full, TILE_BYTES + (hh == 0 ? MIN_TILE_BYTES : 0));
-                bulk_g2s(smem0 + SMEM_B + (gstep % B_SLOTS) * TILE_BYTES, p.xq + ((((int64_t)it.ntile * p.nb + akb) * 2 + hh) << 14), TILE_BYTES, full);
-                if (hh == 0) bulk_g2s(smem0 + SMEM_BMIN + (gkb % BMIN_SLOTS) * MIN_TILE_BYTES, p.bmin + (((int64_t)it.ntile * p.nb + akb) << 12), MIN_TILE_BYTES, full);
+                // half-tile units copy only their 64 columns: the first or second 8 KB of the B tile, 2 KB of the mins tile
+                const uint32_t bsz = p.halves ? TILE_BYTES / 2 : TILE_BYTES, msz = p.halves ? MIN_TILE_BYTES / 2 : MIN_TILE_BYTES;
+                const uint32_t boff = p.halves ? it.h0 * bsz : 0u, moff = p.halves ? it.h0 * msz : 0u;
+                mbar_expect_tx(full, bsz + (hh == 0 ? msz : 0));
+                bulk_g2s(smem0 + SMEM_B + (gstep % B_SLOTS) * TILE_BYTES + boff, p.xq + ((((int64_t)it.ntile * p.nb + akb) * 2 + hh) << 14) + boff, bsz, full);
+                if (hh == 0) bulk_g2s(smem0 + SMEM_BMIN + (gkb % BMIN_SLOTS) * MIN_TILE_BYTES + moff, p.bmin + (((int64_t)it.ntile * p.nb + akb) << 12) + moff, msz, full);
             }
         }
     }
@@ -584,8 +590,15 @@ size_t gemm_workspace_bytes(int64_t K, int64_t N) {
 // cap, so SMs added to a launch that already fills most of them buy less than their count (4096 x 14336 x 512: 128 tiles whole
 // 95 us, cut over 148 CTAs 102 us).  The development / test knob gemm_ksplit = k > 0 forces tiles x k CTAs (capped at the SM
 // count): another split, another float association, the same integers.
-static int choose_grid(int64_t tiles, int64_t nb) {
-    const int64_t sms = std::min<int64_t>(sm_count(), (int64_t)MAX_CTAS), units = tiles * nb;
+static int choose_grid(int64_t tiles, int64_t nb, int64_t N, int &halves) {
+    const int64_t sms = std::min<int64_t>(sm_count(), (int64_t)MAX_CTAS);
+    // Few tiles (TinyLlama's attn_output at 512 tokens: 64 tiles on 148 SMs): 64-column half tiles as the work unit — twice the
+    // CTAs, each with half the MMAs and half the scale application per superblock, whole K per CTA, nothing parked.  Only when
+    // every tile has two halves with real columns.
+    // (a long K is cut between two CTAs per tile instead: 2048 x 5632 x 512 36.3 us that way, 37.4 us as half tiles)
+    halves = knobs().gemm_ksplit < 1 && 2 * tiles <= sms && nb < 16 && N > HALF_N && (N % BN == 0 || N % BN > HALF_N) ? 1 : 0;
+    if (halves) tiles *= 2;
+    const int64_t units = tiles * nb;
     int64_t g;
     if (knobs().gemm_ksplit >= 1) g = std::min(sms, tiles * knobs().gemm_ksplit);
     else if (tiles >= sms) g = sms;
@@ -647,7 +660,8 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
     }
     if (p.nmat == 0) return cudaSuccess;
     if (ntiles * mtiles * nb >= ((int64_t)1 << 31)) return cudaErrorNotSupported;
-    const int grid_ctas = choose_grid(ntiles * mtiles, nb);
+    int halves = 0;
+    const int grid_ctas = choose_grid(ntiles * mtiles, nb, N, halves);
     const int64_t total = nb * N;
     cudaLaunchAttribute pdl_attr[1];
     pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -671,7 +685,7 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
     }
     p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
     p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
-    p.ntn = (int)ntiles; p.units = ntiles * mtiles * nb; p.flags = flags;
+    p.ntn = (int)ntiles; p.halves = halves; p.units = ntiles * mtiles * nb * (halves ? 2 : 1); p.flags = flags;
     p.partial = reinterpret_cast<float *>(reinterpret_cast<char *>(flags) + FLAG_BYTES);
     p.dump_sumi = dump ? dump->sumi : nullptr; p.dump_summ = dump ? dump->summ : nullptr;
     auto kern = dump ? gemm_q4k_tc_kernel<true> : gemm_q4k_tc_kernel<false>;

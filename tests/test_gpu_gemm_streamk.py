@@ -88,3 +88,23 @@ def test_real_weights_through_split_tiles_stay_within_tolerance(q4k):
     got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
     rows = np.unique(np.r_[0:40, 600:680, M - 40:M])
     check("gemm stream-k", got[:, rows], w[rows], x)
+
+
+@pytest.mark.parametrize("M,K,N", [(2048, 2048, 512), (1000, 768, 200), (300, 5632, 384)])
+def test_half_tile_units_give_the_whole_tile_bits(q4k, M, K, N):
+    """launches whose tiles fill at most half the SMs take 64-column half tiles as work units (twice the CTAs): every output still sums
+    its whole K inside one CTA in K order, so the bits are those of the whole-tile grid (gemm_ksplit = 1 forces that) and the oracle
+    tolerance holds"""
+    from conftest import make_acts, make_weights
+    from parity_util import check
+    w, x = make_weights(M, K, seed=M), make_acts(N, K)
+    got = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    try:
+        q4k.debug_set("gemm_ksplit", 1)
+        whole = q4k.mul_mat(t(w), t(x)).cpu().numpy()
+    finally:
+        q4k.debug_set("gemm_ksplit", 0)
+    if K // 256 < 16:                    # (a long K is also cut between two CTAs per half tile: another association, tolerance only)
+        assert np.array_equal(got.view(np.uint32), whole.view(np.uint32))
+    rows = np.unique(np.r_[0:24, M // 2:M // 2 + 24, M - 24:M])
+    check("gemm half tiles", got[:, rows], w[rows], x)
