@@ -65,7 +65,8 @@ constexpr int MMA_WARP = EPI_WARPS + PROD_WARPS, LOAD_WARP = MMA_WARP + 1;
 constexpr int GEMM_THREADS = (LOAD_WARP + 1) * 32;   // 832
 constexpr int SMEM_B = 0, SMEM_RAW = SMEM_B + B_SLOTS * TILE_BYTES, SMEM_AM = SMEM_RAW + RAW_SLOTS * RAW_SLOT_BYTES;
 constexpr int SMEM_BMIN = SMEM_AM + AM_SLOTS * MIN_TILE_BYTES, SMEM_DX = SMEM_BMIN + BMIN_SLOTS * MIN_TILE_BYTES;
-constexpr int SMEM_BARS = SMEM_DX + EPI_WARPS * 3 * 32 * 4;   // DX: d_x, three buffers per epilogue warp
+constexpr int DX_SLOTS = 8, DX_BYTES = BN * 4;        // d_x of the tile's 128 columns for one superblock, copied by the loader with the B tile
+constexpr int SMEM_BARS = SMEM_DX + DX_SLOTS * DX_BYTES;
 constexpr int SMEM_TOTAL = SMEM_BARS + 256;
 constexpr int TMEM_COLS = 512;
 constexpr uint32_t TM_HI = 0, TM_LO = 128, TM_MIN = 256, TM_A = 384;   // TMEM column of each region
@@ -226,45 +227,21 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         WorkItem it;
         // ===================== epilogue: TMEM -> registers, per-superblock fp32 scales =====================
         const int qd = warp & 3, g = warp >> 2;                               // lane quadrant, column group (16 wide, both halves)
-        // d_x of a (column, superblock) is prefetched by the warp itself with a 4-byte cp.async into a private buffer, two
-        // superblocks ahead: as a plain global load in this loop it is sunk to its use by the compiler and stalls the warp for a
-        // global-memory round trip at the top of every superblock.  {d, dmin} of a (row, superblock) is read from the raw row in
-        // shared memory (a cp.async per lane from 32 different rows costs 31 extra shared-memory wavefronts per warp and superblock,
-        // +8% run time: profiles/r2_gemm_streamk.txt).
-        float *dxw = reinterpret_cast<float *>(smem + SMEM_DX) + warp * 96;                              // [3][half 0: 16 | half 1: 16]
+        // The scales of a superblock come out of shared memory: d_x of the tile's 128 columns is copied by the loader next to the B tile
+        // (a ring of 8: refilled only behind MMAs that need this superblock's accumulators back twice over), {d, dmin} of a row are
+        // the first four bytes of its raw row in the loader's slot.  In this loop every instruction counts: run time follows the
+        // epilogue's instruction count almost one to one (profiles/r2_gemm_streamk.txt).  Tried and slower: plain global loads one
+        // superblock ahead (sunk to their use by the compiler), cp.async per lane (31 extra shared-memory wavefronts for the rows).
         // (warp-uniform: the shuffle lets the compiler keep it in a uniform register instead of spilling it around the loop)
         const uint32_t tbase = __shfl_sync(0xffffffffu, tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g), 0);
         uint32_t hpar = 0u;                                                   // bit h: phase of accumulator half h's barriers
-        int bc = 0, bn = 0;                                                   // d_x buffers: of the current superblock, of the next request
-        int gsb = 0;                                                          // superblocks of this CTA so far (the loader's raw slots)
-        bool waited = false;
+        int gsb = 0;                                                          // superblocks of this CTA so far (the loader's slots)
         while (range.next(p, it)) {
             const int h0 = it.h0, h1 = it.h1;
-            // next d_x to request: this lane's column, one row of xd per superblock
-            const float *xnext;
-            {
-                int64_t ncl = (int64_t)it.n0 + HALF_N * (lane >> 4) + EPI_COLS * g + (lane & 15);   // the column whose d_x this lane fetches
-                if (ncl >= p.N) ncl = p.N - 1;
-                xnext = p.xd + (int64_t)it.kb0 * p.Nld + ncl;
-            }
-            auto prefetch = [&]() {          // into buffer bn
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(dxw + bn * 32 + lane)), "l"(xnext) : "memory");
-                bn = bn == 2 ? 0 : bn + 1;
-                xnext += p.Nld;
-            };
             uint64_t acc[2][EPI_COLS / 2];                                        // fp32 pairs
 #pragma unroll
             for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
-            if (!waited) {                   // xd is written by the quantizer kernel in front of this one
-                asm volatile("griddepcontrol.wait;" ::: "memory");
-                waited = true;
-            }
-            prefetch();
-            if (it.nbk > 1) prefetch();
             for (int kb = 0; kb < it.nbk; ++kb) {
-                asm volatile("cp.async.wait_all;" ::: "memory");    // the scales of superblocks kb and kb + 1 have landed
-                __syncwarp();
-                if (kb + 2 < it.nbk) prefetch();
                 // {d, dmin} of this row's block: the first four bytes of its raw row, in the loader's slot since before the producers
                 // unpacked it (the wait below is long complete: it acquires the TMA's bytes) and until every epilogue thread has
                 // handed this superblock's accumulators back (the loader refills the slot for superblock + 4 behind MMAs that need them)
@@ -278,7 +255,8 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                     mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (hpar >> h) & 1u);
                     hpar ^= 1u << h;
                     tc_fence_after();
-                    const uint64_t *dxk = reinterpret_cast<const uint64_t *>(dxw + bc * 32 + 16 * h);
+                    // (d_x arrived on the step's `full` barrier, which the MMAs behind this tfull had waited for)
+                    const uint64_t *dxk = reinterpret_cast<const uint64_t *>(smem + SMEM_DX + (gsb % DX_SLOTS) * DX_BYTES + (HALF_N * h + EPI_COLS * g) * 4);
 #pragma unroll
                     for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
                         uint32_t vh[8], vl[8], vm[8];
@@ -311,7 +289,6 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                         }
                     }
                 }
-                bc = bc == 2 ? 0 : bc + 1;
                 ++gsb;
             }
             // ---- the item's sums leave the registers.  A tile that lies inside one range is stored.  A split tile: the CTAs that
@@ -511,7 +488,8 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
                 // half-tile units copy only their 64 columns: the first or second 8 KB of the B tile, 2 KB of the mins tile
                 const uint32_t bsz = p.halves ? TILE_BYTES / 2 : TILE_BYTES, msz = p.halves ? MIN_TILE_BYTES / 2 : MIN_TILE_BYTES;
                 const uint32_t boff = p.halves ? it.h0 * bsz : 0u, moff = p.halves ? it.h0 * msz : 0u;
-                mbar_expect_tx(full, bsz + (hh == 0 ? msz : 0));
+                mbar_expect_tx(full, bsz + (hh == 0 ? msz + DX_BYTES : 0));
+                if (hh == 0) bulk_g2s(smem0 + SMEM_DX + (gkb % DX_SLOTS) * DX_BYTES, p.xd + (int64_t)akb * p.Nld + it.n0, DX_BYTES, full);
                 bulk_g2s(smem0 + SMEM_B + (gstep % B_SLOTS) * TILE_BYTES + boff, p.xq + ((((int64_t)it.ntile * p.nb + akb) * 2 + hh) << 14) + boff, bsz, full);
                 if (hh == 0) bulk_g2s(smem0 + SMEM_BMIN + (gkb % BMIN_SLOTS) * MIN_TILE_BYTES + moff, p.bmin + (((int64_t)it.ntile * p.nb + akb) << 12) + moff, msz, full);
             }
@@ -580,7 +558,7 @@ cudaError_t launch_gemm_q4k_q8k(const void *, int64_t, int64_t, int64_t, const v
 // workspace layout of the prefill path: int8 tiles | mins tiles | float d   (q4k_mul_mat_workspace_bytes adds them up)
 size_t gemm_workspace_bytes(int64_t K, int64_t N) {
     const size_t nb = (size_t)(K / QK_K), ntiles = ((size_t)N + BN - 1) / BN;
-    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + ((nb * (size_t)N * 4 + 255) & ~(size_t)255) + FLAG_BYTES + MAX_CTAS * PARTIAL_BYTES;
+    return ntiles * BN * (size_t)K + ntiles * nb * MIN_TILE_BYTES + nb * ntiles * BN * 4 + FLAG_BYTES + MAX_CTAS * PARTIAL_BYTES;      // d_x rows are padded to whole column tiles (512-byte bulk copies)
 }
 
 // The persistent grid.  More tiles than SMs: one CTA per SM, the units cut evenly (no partial last wave: 448 tiles on 148 SMs
@@ -644,7 +622,8 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
     int8_t *qs = reinterpret_cast<int8_t *>(workspace);
     uint8_t *bmin = reinterpret_cast<uint8_t *>(qs + ntiles * BN * K);
     float *d = reinterpret_cast<float *>(bmin + ntiles * nb * MIN_TILE_BYTES);
-    int *flags = reinterpret_cast<int *>(reinterpret_cast<char *>(d) + ((nb * (size_t)N * 4 + 255) & ~(size_t)255));
+    const int64_t Nld = ntiles * BN;                       // d_x rows padded to whole column tiles: the loader copies 512 bytes per tile and superblock
+    int *flags = reinterpret_cast<int *>(reinterpret_cast<char *>(d) + (size_t)nb * Nld * 4);
     GemmParams p;
     int64_t mtiles = 0;
     p.nmat = 0;
@@ -679,12 +658,12 @@ cudaError_t launch_gemm_q4k_f32_group(int nmat, const void *const *w, const int6
         cfg.attrs = pdl_attr;
         cfg.numAttrs = knobs().pdl ? 1 : 0;
         int *qflags = flags;
-        e = cudaLaunchKernelEx(&cfg, quantize_q8_planar_kernel, x, qs, d, bmin, nb, total, x_row_stride_bytes, N, qflags);
+        e = cudaLaunchKernelEx(&cfg, quantize_q8_planar_kernel, x, qs, d, bmin, nb, total, x_row_stride_bytes, Nld, qflags);
         count_launch();
         if (e != cudaSuccess) return e;
     }
     p.w_stride = w_row_stride_bytes; p.nb = (int)nb;
-    p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = N;
+    p.xq = qs; p.xd = d; p.bmin = bmin; p.N = N; p.Nld = Nld;
     p.ntn = (int)ntiles; p.halves = halves; p.units = ntiles * mtiles * nb * (halves ? 2 : 1); p.flags = flags;
     p.partial = reinterpret_cast<float *>(reinterpret_cast<char *>(flags) + FLAG_BYTES);
     p.dump_sumi = dump ? dump->sumi : nullptr; p.dump_summ = dump ? dump->summ : nullptr;
