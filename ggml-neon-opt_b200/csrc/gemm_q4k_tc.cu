@@ -191,6 +191,62 @@ struct WorkRange {
     }
 };
 
+// The epilogue's superblock loop for one work item.  HS: 0 / 1 = only that 64-column half, 2 = both.  Everything in here is on the
+// kernel's critical path (the tensor core waits for its accumulator halves): run time follows this loop's instruction count.
+template <bool DUMP, int HS>
+__device__ __forceinline__ void drain_superblocks(const GemmParams &p, const WorkItem &it, uint8_t *smem, uint32_t bar0, uint32_t tbase,
+                                                  int qd, int g, int lane, uint32_t &hpar, uint32_t &gsb, uint64_t (&acc)[2][EPI_COLS / 2]) {
+    for (int kb = 0; kb < it.nbk; ++kb) {
+        // {d, dmin} of this row's block: the first four bytes of its raw row, in the loader's slot since before the producers
+        // unpacked it (the wait below is long complete: it acquires the TMA's bytes) and until every epilogue thread has
+        // handed this superblock's accumulators back (the loader refills the slot for superblock + 4 behind MMAs that need them)
+        mbar_wait(bar0 + 8u * (2 * B_SLOTS + 4 + (gsb % RAW_SLOTS)), (gsb / RAW_SLOTS) & 1u);
+        const uint32_t dd = *reinterpret_cast<const uint32_t *>(smem + SMEM_RAW + (gsb % RAW_SLOTS) * RAW_SLOT_BYTES + (32 * qd + lane) * RAW_ROW_BYTES);
+        const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));
+        const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
+#pragma unroll
+        for (int h = (HS == 1 ? 1 : 0); h < (HS == 0 ? 1 : 2); ++h) {
+            mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(bar0 + 8u * (2 * B_SLOTS + h), (hpar >> h) & 1u);
+            hpar ^= 1u << h;
+            tc_fence_after();
+            // (d_x arrived on the step's `full` barrier, which the MMAs behind this tfull had waited for)
+            const uint64_t *dxk = reinterpret_cast<const uint64_t *>(smem + SMEM_DX + (gsb % DX_SLOTS) * DX_BYTES + (HALF_N * h + EPI_COLS * g) * 4);
+#pragma unroll
+            for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
+                uint32_t vh[8], vl[8], vm[8];
+                const uint32_t ta = tbase + HALF_N * h + 8 * c8;
+                tmem_ld8(ta + TM_HI, vh); tmem_ld8(ta + TM_LO, vl); tmem_ld8(ta + TM_MIN, vm);
+                tmem_ld_wait();
+                if (c8 == EPI_COLS / 8 - 1) {          // everything of this half is in registers: hand the columns back
+                    tc_fence_before();
+                    mbar_arrive(bar0 + 8u * (2 * B_SLOTS + 2 + h));
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
+                    const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
+                    if constexpr (DUMP) {
+                        const int64_t M_mat = p.M[it.mat], row = (int64_t)it.m0 + 32 * qd + lane;
+                        const int64_t n = (int64_t)it.n0 + HALF_N * h + EPI_COLS * g + 8 * c8 + 2 * i;
+                        if (row < M_mat && n < p.N) {
+                            p.dump_sumi[(n * M_mat + row) * p.nb + it.kb0 + kb] = s0;
+                            p.dump_summ[(n * M_mat + row) * p.nb + it.kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
+                        }
+                        if (row < M_mat && n + 1 < p.N) {
+                            p.dump_sumi[((n + 1) * M_mat + row) * p.nb + it.kb0 + kb] = s1;
+                            p.dump_summ[((n + 1) * M_mat + row) * p.nb + it.kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
+                        }
+                    }
+                    // (packed f32x2: measured faster than scalar fp32 despite the register-pair moves it needs)
+                    uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
+                    t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
+                    acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
+                }
+            }
+        }
+        ++gsb;
+    }
+}
+
 // DUMP: parity instantiation — the same code; the epilogue also writes out every superblock's sumi (= 8 hi + lo) and summ
 template <bool DUMP>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -235,62 +291,16 @@ gemm_q4k_tc_kernel(const __grid_constant__ GemmParams p) {
         // (warp-uniform: the shuffle lets the compiler keep it in a uniform register instead of spilling it around the loop)
         const uint32_t tbase = __shfl_sync(0xffffffffu, tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(EPI_COLS * g), 0);
         uint32_t hpar = 0u;                                                   // bit h: phase of accumulator half h's barriers
-        int gsb = 0;                                                          // superblocks of this CTA so far (the loader's slots)
+        uint32_t gsb = 0u;                                                    // superblocks of this CTA so far (the loader's slots)
         while (range.next(p, it)) {
-            const int h0 = it.h0, h1 = it.h1;
             uint64_t acc[2][EPI_COLS / 2];                                        // fp32 pairs
 #pragma unroll
             for (int i = 0; i < EPI_COLS / 2; ++i) acc[0][i] = acc[1][i] = 0ull;
-            for (int kb = 0; kb < it.nbk; ++kb) {
-                // {d, dmin} of this row's block: the first four bytes of its raw row, in the loader's slot since before the producers
-                // unpacked it (the wait below is long complete: it acquires the TMA's bytes) and until every epilogue thread has
-                // handed this superblock's accumulators back (the loader refills the slot for superblock + 4 behind MMAs that need them)
-                mbar_wait(rawfull_bar(gsb % RAW_SLOTS), (uint32_t)((gsb / RAW_SLOTS) & 1));
-                const uint32_t dd = *reinterpret_cast<const uint32_t *>(smem + SMEM_RAW + (gsb % RAW_SLOTS) * RAW_SLOT_BYTES + (32 * qd + lane) * RAW_ROW_BYTES);
-                const float2 dw = __half22float2(*reinterpret_cast<const __half2 *>(&dd));
-                const uint64_t d2 = pack2(dw.x, dw.x), ndmin2 = pack2(-dw.y, -dw.y);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    if (h < h0 || h >= h1) continue;
-                    mbar_wait_long<Q4K_GEMM_WAIT_TFULL>(tfull_bar(h), (hpar >> h) & 1u);
-                    hpar ^= 1u << h;
-                    tc_fence_after();
-                    // (d_x arrived on the step's `full` barrier, which the MMAs behind this tfull had waited for)
-                    const uint64_t *dxk = reinterpret_cast<const uint64_t *>(smem + SMEM_DX + (gsb % DX_SLOTS) * DX_BYTES + (HALF_N * h + EPI_COLS * g) * 4);
-#pragma unroll
-                    for (int c8 = 0; c8 < EPI_COLS / 8; ++c8) {
-                        uint32_t vh[8], vl[8], vm[8];
-                        const uint32_t ta = tbase + HALF_N * h + 8 * c8;
-                        tmem_ld8(ta + TM_HI, vh); tmem_ld8(ta + TM_LO, vl); tmem_ld8(ta + TM_MIN, vm);
-                        tmem_ld_wait();
-                        if (c8 == EPI_COLS / 8 - 1) {          // everything of this half is in registers: hand the columns back
-                            tc_fence_before();
-                            mbar_arrive(tempty_bar(h));
-                        }
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {     // t = d * sumi - dmin * summ (two roundings), acc = fma(d_x, t, acc): pairs of columns
-                            const int s0 = ((int)vh[2 * i] << 3) + (int)vl[2 * i], s1 = ((int)vh[2 * i + 1] << 3) + (int)vl[2 * i + 1];
-                            if constexpr (DUMP) {
-                                const int64_t M_mat = p.M[it.mat], row = (int64_t)it.m0 + 32 * qd + lane;
-                                const int64_t n = (int64_t)it.n0 + HALF_N * h + EPI_COLS * g + 8 * c8 + 2 * i;
-                                if (row < M_mat && n < p.N) {
-                                    p.dump_sumi[(n * M_mat + row) * p.nb + it.kb0 + kb] = s0;
-                                    p.dump_summ[(n * M_mat + row) * p.nb + it.kb0 + kb] = (int)__uint_as_float(vm[2 * i]);
-                                }
-                                if (row < M_mat && n + 1 < p.N) {
-                                    p.dump_sumi[((n + 1) * M_mat + row) * p.nb + it.kb0 + kb] = s1;
-                                    p.dump_summ[((n + 1) * M_mat + row) * p.nb + it.kb0 + kb] = (int)__uint_as_float(vm[2 * i + 1]);
-                                }
-                            }
-                            // (packed f32x2: measured faster than scalar fp32 despite the register-pair moves it needs)
-                            uint64_t t = mul2(d2, pack2((float)s0, (float)s1));
-                            t = fma2(ndmin2, pack2(__uint_as_float(vm[2 * i]), __uint_as_float(vm[2 * i + 1])), t);
-                            acc[h][4 * c8 + i] = fma2(dxk[4 * c8 + i], t, acc[h][4 * c8 + i]);
-                        }
-                    }
-                }
-                ++gsb;
-            }
+            // the superblock loop, specialised for "both halves" (the common case: no test, no merge of the accumulators behind a branch —
+            // that alone cost 16 register moves per superblock) and for one half (ragged last column tile, half-tile units)
+            if (it.h0 == 0 && it.h1 == 2) drain_superblocks<DUMP, 2>(p, it, smem, bar0, tbase, qd, g, lane, hpar, gsb, acc);
+            else if (it.h0 == 0) drain_superblocks<DUMP, 0>(p, it, smem, bar0, tbase, qd, g, lane, hpar, gsb, acc);
+            else drain_superblocks<DUMP, 1>(p, it, smem, bar0, tbase, qd, g, lane, hpar, gsb, acc);
             // ---- the item's sums leave the registers.  A tile that lies inside one range is stored.  A split tile: the CTAs that
             // hold its LATER superblocks meet it FIRST in their ranges and park their sums in the workspace (one slot per CTA, then
             // a flag); the CTA that holds its first superblocks meets it LAST, adds the parked parts in K order and stores — it
